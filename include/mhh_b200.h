@@ -1,0 +1,178 @@
+/* mhh_b200.h — C ABI of the B200-native MicroHH dynamical core (libmhh_b200.so).
+ *
+ * The reference has no FFI; its CPU/GPU seam is compile-time substitution of the member
+ * bodies guarded by `#ifndef USECUDA` (src/advec_2.cxx:265-336, src/diff_smag2.cxx:882-1189,
+ * src/pres_2.cxx:64-105, src/timeloop.cxx:356-412, src/boundary.cxx:445-470,917-1008).
+ * Each function below is what one of those guarded members binds to; INTEGRATION.md shows
+ * the 3-line C++ shim per member.
+ *
+ * Conventions
+ *  - All field pointers are DEVICE pointers to FP64 arrays in the reference layout:
+ *    ijk = i + j*icells + k*icells*jcells, ghost cells included (src/grid.cxx:153-166).
+ *    2-D planes are icells*jcells. Ownership stays with the caller (Field3d::fld_g,
+ *    src/field3d.cu:31-61). Tendencies are accumulated into (+=), never overwritten.
+ *  - Work is issued on the context stream (default: the legacy default stream, as the
+ *    reference does); functions returning a host scalar synchronise that stream.
+ *  - Return value: 0 on success, non-zero error code otherwise (the shim rethrows as
+ *    std::runtime_error, matching include/tools.h:78-85). mhh_last_error() gives text.
+ */
+#ifndef MHH_B200_H
+#define MHH_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef struct mhh_ctx mhh_ctx;
+
+/* Boundary_type, include/boundary.h:51 */
+enum { MHH_BC_DIRICHLET = 0, MHH_BC_NEUMANN = 1, MHH_BC_FLUX = 2, MHH_BC_USTAR = 3, MHH_BC_OFF = 4 };
+/* Boundary_w_type, include/boundary.h:52 */
+enum { MHH_BCW_NORMAL = 0, MHH_BCW_CONSERVATION = 1 };
+/* Edge, include/boundary_cyclic.h:33 */
+enum { MHH_EDGE_EAST_WEST = 0, MHH_EDGE_NORTH_SOUTH = 1, MHH_EDGE_BOTH = 2 };
+/* [advec] swadvec = 2 | 2i5 | 4 (src/advec.cxx:42-83) */
+enum { MHH_ADVEC_2 = 2, MHH_ADVEC_2I5 = 25, MHH_ADVEC_4 = 4 };
+
+/* Mirror of the scalars of Grid_data<TF> (include/grid.h:50-135) that define a grid.
+ * npy/rank_y describe the y-slab decomposition (npx = 1): jmax = jtot/npy. */
+typedef struct
+{
+    int itot, jtot, ktot;
+    int igc, jgc, kgc;          /* ghost cells: 1,1,1 (order 2), 3,3,3 (order 4), 3,3,1|2 (advec 2i5) */
+    double xsize, ysize, zsize;
+    int order;                  /* [grid] swspatialorder: 2 or 4 */
+    int npy, rank_y;            /* 1, 0 for a single GPU */
+} mhh_grid_desc;
+
+/* --- context / Grid (src/grid.cxx:106-189 init, :237-368 calculate) ------------------------ */
+int mhh_create(const mhh_grid_desc* desc, const double* z_host /* ktot cell centres */, mhh_ctx** out);
+int mhh_destroy(mhh_ctx* ctx);
+const char* mhh_last_error(const mhh_ctx* ctx);
+int mhh_set_stream(mhh_ctx* ctx, void* cuda_stream);
+/* Fields::rhoref / rhorefh (kcells each, host). Default is 1 (Boussinesq, src/fields.cxx:394-395). */
+int mhh_set_rhoref(mhh_ctx* ctx, const double* rhoref_host, const double* rhorefh_host);
+/* out[20]: itot jtot ktot imax jmax kmax igc jgc kgc icells jcells kcells ijcells ncells
+ *          istart iend jstart jend kstart kend */
+int mhh_get_dims(const mhh_ctx* ctx, int* out);
+/* name in {z,zh,dz,dzh,dzi,dzhi,dzi4,dzhi4,rhoref,rhorefh}: copies kcells doubles to host. */
+int mhh_get_metric(const mhh_ctx* ctx, const char* name, double* out_host);
+/* device pointer of the same arrays (for callers that launch their own kernels) */
+const double* mhh_get_metric_device(const mhh_ctx* ctx, const char* name);
+
+/* --- Advec<TF> (include/advec.h:54-60) ------------------------------------------------------ */
+/* Advec_2/2i5/4::exec — src/advec_2.cxx:298, src/advec_2i5.cxx:977, src/advec_4.cxx:592.
+ * limit_flags[n] != 0 selects the flux-limited scalar scheme of include/advec_monotonic.h:77 (2i5 only). */
+int mhh_advec_exec(mhh_ctx* ctx, int scheme,
+                   const double* u, const double* v, const double* w,
+                   double* ut, double* vt, double* wt,
+                   int nscalars, const double* const* s, double* const* st, const int* limit_flags);
+/* Advec_*::get_cfl — src/advec_2.cxx:267 (calc_cfl :51): cfl = dt * max(|u|/dx + |v|/dy + |w|/dz). */
+int mhh_advec_cfl(mhh_ctx* ctx, int scheme, const double* u, const double* v, const double* w,
+                  double dt, double* cfl_out);
+/* Advec_*::get_time_limit — src/advec_2.cxx:281: idt * cflmax / max(cflmin, cfl). */
+int mhh_advec_time_limit(mhh_ctx* ctx, int scheme, const double* u, const double* v, const double* w,
+                         unsigned long idt, double dt, double cflmax, unsigned long* idtlim_out);
+
+/* --- Diff<TF> (include/diff.h:45-64) ---------------------------------------------------------- */
+/* Diff_2::exec src/diff_2.cxx:162 (diff_c :39 for u,v,scalars; diff_w :64). svisc[n] per scalar. */
+int mhh_diff2_exec(mhh_ctx* ctx, const double* u, const double* v, const double* w,
+                   double* ut, double* vt, double* wt, double visc,
+                   int nscalars, const double* const* s, double* const* st, const double* svisc);
+/* Diff_4::exec src/diff_4.cxx:253 (diff_c :42, diff_w :109). */
+int mhh_diff4_exec(mhh_ctx* ctx, const double* u, const double* v, const double* w,
+                   double* ut, double* vt, double* wt, double visc,
+                   int nscalars, const double* const* s, double* const* st, const double* svisc);
+/* Diff_2/4::get_dn: dnmul is static (src/diff_2.cxx:139-151). Returns dnmul (not * dt). */
+int mhh_diff_const_dnmul(mhh_ctx* ctx, double viscmax, double* dnmul_out);
+
+/* Diff_smag2::exec_viscosity — src/diff_smag2.cxx:1046 (calc_strain2 :48, calc_evisc :255,
+ * calc_evisc_neutral :158), including the trailing boundary_cyclic.exec(evisc) and, for
+ * resolved walls, the mirrored ghost rows.
+ *  surface_model: boundary.get_switch() != "default";  N2 == NULL selects the neutral branch
+ *  (thermo.get_switch() == "0").  dudz/dvdz/dbdz/z0m are 2-D planes (NULL when surface_model == 0). */
+int mhh_smag2_exec_viscosity(mhh_ctx* ctx, int surface_model,
+                             const double* u, const double* v, const double* w,
+                             const double* N2, const double* dudz, const double* dvdz,
+                             const double* dbdz, const double* z0m,
+                             double cs, double tPr, double visc, double* evisc);
+/* Diff_smag2::exec — src/diff_smag2.cxx:939 (diff_u :370, diff_v :472, diff_w :575, diff_c :620). */
+int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
+                   const double* u, const double* v, const double* w, const double* evisc,
+                   double* ut, double* vt, double* wt,
+                   const double* ufluxbot, const double* ufluxtop,
+                   const double* vfluxbot, const double* vfluxtop, double visc,
+                   int nscalars, const double* const* s, double* const* st,
+                   const double* const* sfluxbot, const double* const* sfluxtop,
+                   const double* svisc, double tPr);
+/* calc_strain2 alone (src/diff_smag2.cxx:48) — stage check for parity tests; the product path fuses it. */
+int mhh_smag2_strain2(mhh_ctx* ctx, int surface_model, const double* u, const double* v, const double* w,
+                      const double* dudz, const double* dvdz, double* strain2);
+/* calc_dnmul — src/diff_smag2.cxx:712; get_dn :904 multiplies by dt, get_time_limit :884. */
+int mhh_smag2_dnmul(mhh_ctx* ctx, const double* evisc, double tPr, double* dnmul_out);
+
+/* --- Pres<TF> (include/pres.h:48-58) --------------------------------------------------------------- */
+/* Pres_2/4::init + set_values — src/pres_2.cxx:107-153, src/pres_4.cxx:159-252. Uses ctx rhoref. */
+int mhh_pres_set_values(mhh_ctx* ctx);
+/* Pres_2/4::exec(dt) — src/pres_2.cxx:66, src/pres_4.cxx:77: input, solve, output. p is ghosted. */
+int mhh_pres_exec(mhh_ctx* ctx, const double* u, const double* v, const double* w,
+                  double* ut, double* vt, double* wt, double* p, double dt);
+/* Pres_2/4::check_divergence — src/pres_2.cxx:99,391; src/pres_4.cxx:144,733. */
+int mhh_pres_check_divergence(mhh_ctx* ctx, const double* u, const double* v, const double* w,
+                              double* divmax_out);
+/* Stages, exposed for parity tests and for the multi-GPU driver (transposes happen between them):
+ *  input : Pres_2::input src/pres_2.cxx:156 -> ghost-free work array (device, imax*jmax*kmax)
+ *  fft   : FFT::exec_forward/backward src/fft.cxx:588-599, half-complex in place
+ *  solve : solve_in + tdma/hdma src/pres_2.cxx:292-327, src/pres_4.cxx:320-505
+ *  output: scatter + ghost rows + cyclic + Pres_*::output src/pres_2.cxx:340-387 */
+double* mhh_pres_work(mhh_ctx* ctx);
+int mhh_pres_input(mhh_ctx* ctx, const double* u, const double* v, const double* w,
+                   double* ut, double* vt, double* wt, double dt);
+int mhh_fft_forward(mhh_ctx* ctx, double* data);
+int mhh_fft_backward(mhh_ctx* ctx, double* data);      /* normalised by 1/(itot*jtot), in place */
+int mhh_pres_solve_spectral(mhh_ctx* ctx, double* data);
+int mhh_pres_output(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p);
+int mhh_pres_scatter(mhh_ctx* ctx, double* p, const double* ghost_free_src);   /* src/pres_2.cxx:340-348 */
+/* copies bmati(itot), bmatj(jtot) and a,c (kmax each; order 2) or m1..m7 (7*kmax; order 4) to host */
+int mhh_pres_get_coefs(const mhh_ctx* ctx, double* bmati, double* bmatj, double* a_or_bands, double* c);
+
+/* --- Boundary<TF> / Boundary_cyclic<TF> (include/boundary.h:92-98, include/boundary_cyclic.h) ---------- */
+/* Boundary_cyclic::exec / exec_2d — src/boundary_cyclic.cxx:369,445. */
+int mhh_cyclic(mhh_ctx* ctx, double* fld, int edge);
+int mhh_cyclic_2d(mhh_ctx* ctx, double* fld2d);
+/* calc_ghost_cells_{bot,top}_{2nd,4th} — src/boundary.cxx:687-836, one field; order from ctx. */
+int mhh_ghost_cells(mhh_ctx* ctx, double* a, int bcbot, int bctop,
+                    double* abot, double* atop, const double* agradbot, const double* agradtop);
+/* Boundary::set_ghost_cells_w — src/boundary.cxx:986 (no-op for order 2). */
+int mhh_ghost_cells_w(mhh_ctx* ctx, double* w, int type);
+/* Boundary::set_values for one field: fill the 2-D planes from scalar BC values
+ * (set_bc, src/boundary.cxx:51-91).  visc and no_offset as in the reference. */
+int mhh_set_bc(mhh_ctx* ctx, double* a2d, double* agrad2d, double* aflux2d, int sw, double aval,
+               double visc, double offset);
+
+/* --- Timeloop<TF>::exec (src/timeloop.cxx:358; rk3 :250, rk4 :288) -------------------------------------- */
+int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, double dt,
+                   int nfields, double* const* a, double* const* at);
+double mhh_rk_sub_dt(int rkorder, int substep, double dt);   /* Timeloop::get_sub_time_step :415 */
+
+/* --- Field3d_operators<TF> (include/field3d_operators.h:40-51) and Fields diagnostics -------------------- */
+int mhh_mean_profile(mhh_ctx* ctx, const double* fld, double* prof_host /* kcells */);
+int mhh_level_sums(mhh_ctx* ctx, const double* fld, double* sums_host /* kcells, this rank only */);
+int mhh_mean(mhh_ctx* ctx, const double* fld, double* mean_out);
+int mhh_mean_2d(mhh_ctx* ctx, const double* fld2d, double* mean_out);
+int mhh_max(mhh_ctx* ctx, const double* fld, double* max_out);   /* calc_max_g: max over interior */
+/* Fields::check_momentum/tke/mass — src/fields.cxx:144,175,209 */
+int mhh_check_momentum(mhh_ctx* ctx, const double* u, const double* v, const double* w, double* out);
+int mhh_check_tke(mhh_ctx* ctx, const double* u, const double* v, const double* w, double* out);
+int mhh_check_mass(mhh_ctx* ctx, const double* s, double* out);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif

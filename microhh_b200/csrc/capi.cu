@@ -1,0 +1,499 @@
+// extern "C" surface declared in include/mhh_b200.h.
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/mhh_b200.h"
+#include "ctx.h"
+#include "fft.h"
+
+namespace mhh
+{
+// ctx.cu
+int ctx_init_grid(Ctx*, int, int, int, int, int, int, double, double, double, int, int, int);
+int ctx_upload_metrics(Ctx*);
+int ctx_alloc_scratch(Ctx*);
+void ctx_free(Ctx*);
+// advec_2.cu
+int advec2_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*);
+int advec2_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+// advec_2i5.cu / advec_4.cu
+int advec2i5_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*, const int*);
+int advec2i5_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+int advec4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*);
+int advec4_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+// diff_2.cu / diff_4.cu / diff_smag2.cu
+int diff2_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
+int diff4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
+int smag2_exec_viscosity(Ctx*, int, const double*, const double*, const double*, const double*, const double*, const double*,
+                         const double*, const double*, double, double, double, double*, int);
+int smag2_exec(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
+               const double*, const double*, const double*, const double*, double, int, const double* const*, double* const*,
+               const double* const*, const double* const*, const double*, double);
+int smag2_dnmul_bits(Ctx*, const double*, double, unsigned long long*);
+// boundary.cu
+int cyclic_exec(Ctx*, double*, int);
+int cyclic_exec_2d(Ctx*, double*);
+int ghost_cells_exec(Ctx*, double*, int, int, double*, double*, const double*, const double*);
+int ghost_cells_w_exec(Ctx*, double*, int);
+int set_bc_exec(Ctx*, double*, double*, double*, int, double, double, double);
+// timeloop.cu
+int rk_substep(Ctx*, int, int, double, int, double* const*, double* const*);
+double rk_sub_dt(int, int, double);
+// reduce.cu
+int level_sums(Ctx*, const double*, double*);
+int weighted_sum(Ctx*, int, const double*, const double*, const double*, double*);
+int interior_max(Ctx*, const double*, double*);
+int plane_sum(Ctx*, const double*, double*);
+// pres_2.cu / pres_4.cu
+int pres2_set_values(Ctx*);
+int pres2_input(Ctx*, const double*, const double*, const double*, const double*, const double*, const double*, double, double*);
+int pres2_solve_spectral(Ctx*, double*);
+int pres2_output(Ctx*, double*, double*, double*, double*);
+int pres2_divergence_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+int pres_scatter(Ctx*, double*, const double*);
+int pres4_set_values(Ctx*);
+int pres4_input(Ctx*, const double*, const double*, const double*, const double*, const double*, double*, double, double*);
+int pres4_solve_spectral(Ctx*, double*);
+int pres4_output(Ctx*, double*, double*, double*, double*);
+int pres4_divergence_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+
+static int read_max(Ctx* c, unsigned long long* slot, double* out)
+{
+    unsigned long long* h = reinterpret_cast<unsigned long long*>(c->host_pinned);
+    MHH_CUDA_CHECK(cudaMemcpyAsync(h, slot, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    double d;
+    std::memcpy(&d, h, sizeof(double));
+    *out = d;
+    return MHH_OK;
+}
+
+// FFT::exec_forward (src/fft.cxx:335-389): x lines then y lines, in place.
+static int fft_forward_inplace(Ctx* c, double* data)
+{
+    const GridD& gd = c->gd;
+    if (c->npy != 1) return MHH_ERR_STATE;
+    FftLayout L;
+    L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0;
+    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.base_out = 0; L.scale = 1.;
+    if (int e = fft_lines(c->stream, c->plan_i, -1, data, data, L)) return e;
+    L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
+    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
+    return fft_lines(c->stream, c->plan_j, -1, data, data, L);
+}
+
+// FFT::exec_backward (src/fft.cxx:392-448): y then x, each normalised by its length.
+// If p != nullptr the x pass scatters into the ghost-celled array p instead of `data`.
+static int fft_backward_impl(Ctx* c, double* data, double* p)
+{
+    const GridD& gd = c->gd;
+    if (c->npy != 1) return MHH_ERR_STATE;
+    FftLayout L;
+    L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
+    L.base_in = 0; L.base_out = 0;
+    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.scale = 1. / gd.jtot;
+    if (int e = fft_lines(c->stream, c->plan_j, +1, data, data, L)) return e;
+    L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.scale = 1. / gd.itot;
+    if (p == nullptr)
+    {
+        L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
+        return fft_lines(c->stream, c->plan_i, +1, data, data, L);
+    }
+    L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells; L.sno = 1;
+    L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
+    return fft_lines(c->stream, c->plan_i, +1, data, p, L);
+}
+}  // namespace mhh
+
+using namespace mhh;
+
+#define CTX_CHECK(ctx) do { if ((ctx) == nullptr) return MHH_ERR_ARG; } while (0)
+
+extern "C" {
+
+int mhh_create(const mhh_grid_desc* d, const double* z_host, mhh_ctx** out)
+{
+    if (!d || !z_host || !out) return MHH_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    {
+        std::fprintf(stderr, "mhh_b200: no CUDA device: the B200 path has no CPU fallback\n");
+        return MHH_ERR_CUDA;
+    }
+    mhh_ctx* c = new (std::nothrow) mhh_ctx;
+    if (!c) return MHH_ERR_ARG;
+    int e = ctx_init_grid(c, d->itot, d->jtot, d->ktot, d->igc, d->jgc, d->kgc, d->xsize, d->ysize, d->zsize,
+                          d->order, d->npy < 1 ? 1 : d->npy, d->rank_y);
+    if (!e) e = ctx_set_metrics(c, z_host);
+    if (!e)
+    {
+        c->rhoref.assign(c->gd.kcells, 1.);
+        c->rhorefh.assign(c->gd.kcells, 1.);
+        e = ctx_upload_metrics(c);
+    }
+    if (!e) e = ctx_alloc_scratch(c);
+    if (e)
+    {
+        std::fprintf(stderr, "mhh_create: %s\n", c->last_error.c_str());
+        ctx_free(c);
+        delete c;
+        return e;
+    }
+    *out = c;
+    return MHH_OK;
+}
+
+int mhh_destroy(mhh_ctx* c)
+{
+    CTX_CHECK(c);
+    cudaStreamSynchronize(c->stream);
+    ctx_free(c);
+    delete c;
+    return MHH_OK;
+}
+
+const char* mhh_last_error(const mhh_ctx* c) { return c ? c->last_error.c_str() : "null context"; }
+
+int mhh_set_stream(mhh_ctx* c, void* s) { CTX_CHECK(c); c->stream = static_cast<cudaStream_t>(s); return MHH_OK; }
+
+int mhh_set_rhoref(mhh_ctx* c, const double* rhoref, const double* rhorefh)
+{
+    CTX_CHECK(c);
+    c->rhoref.assign(rhoref, rhoref + c->gd.kcells);
+    c->rhorefh.assign(rhorefh, rhorefh + c->gd.kcells);
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    if (int e = ctx_upload_metrics(c)) return e;
+    c->pres_ready = false;
+    return MHH_OK;
+}
+
+int mhh_get_dims(const mhh_ctx* c, int* out)
+{
+    CTX_CHECK(c);
+    const GridD& gd = c->gd;
+    const int v[20] = {gd.itot, gd.jtot, gd.ktot, gd.imax, gd.jmax, gd.kmax, gd.igc, gd.jgc, gd.kgc,
+                       gd.icells, gd.jcells, gd.kcells, gd.ijcells, gd.ncells,
+                       gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart, gd.kend};
+    std::memcpy(out, v, sizeof(v));
+    return MHH_OK;
+}
+
+static const std::vector<double>* metric_host(const mhh_ctx* c, const char* name)
+{
+    const std::string n(name);
+    if (n == "z") return &c->z; if (n == "zh") return &c->zh; if (n == "dz") return &c->dz;
+    if (n == "dzh") return &c->dzh; if (n == "dzi") return &c->dzi; if (n == "dzhi") return &c->dzhi;
+    if (n == "dzi4") return &c->dzi4; if (n == "dzhi4") return &c->dzhi4;
+    if (n == "rhoref") return &c->rhoref; if (n == "rhorefh") return &c->rhorefh;
+    return nullptr;
+}
+
+int mhh_get_metric(const mhh_ctx* c, const char* name, double* out)
+{
+    CTX_CHECK(c);
+    const std::string n(name);
+    if (n == "scalars")
+    {
+        out[0] = c->gd.dx; out[1] = c->gd.dy; out[2] = c->gd.dxi; out[3] = c->gd.dyi;
+        out[4] = c->gd.dzhi4bot; out[5] = c->gd.dzhi4top;
+        return MHH_OK;
+    }
+    const std::vector<double>* v = metric_host(c, name);
+    if (!v) return MHH_ERR_ARG;
+    std::memcpy(out, v->data(), sizeof(double) * v->size());
+    return MHH_OK;
+}
+
+const double* mhh_get_metric_device(const mhh_ctx* c, const char* name)
+{
+    if (!c) return nullptr;
+    const std::string n(name);
+    const GridD& gd = c->gd;
+    if (n == "z") return gd.z; if (n == "zh") return gd.zh; if (n == "dz") return gd.dz;
+    if (n == "dzh") return gd.dzh; if (n == "dzi") return gd.dzi; if (n == "dzhi") return gd.dzhi;
+    if (n == "dzi4") return gd.dzi4; if (n == "dzhi4") return gd.dzhi4;
+    if (n == "rhoref") return gd.rhoref; if (n == "rhorefh") return gd.rhorefh;
+    return nullptr;
+}
+
+// ---------------------------------------------------------------- Advec
+int mhh_advec_exec(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w,
+                   double* ut, double* vt, double* wt, int ns, const double* const* s, double* const* st,
+                   const int* limit_flags)
+{
+    CTX_CHECK(c);
+    switch (scheme)
+    {
+        case MHH_ADVEC_2: return advec2_exec(c, u, v, w, ut, vt, wt, ns, s, st);
+        case MHH_ADVEC_2I5: return advec2i5_exec(c, u, v, w, ut, vt, wt, ns, s, st, limit_flags);
+        case MHH_ADVEC_4: return advec4_exec(c, u, v, w, ut, vt, wt, ns, s, st);
+        default: c->last_error = "illegal value for swadvec"; return MHH_ERR_ARG;
+    }
+}
+
+int mhh_advec_cfl(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w, double dt, double* cfl)
+{
+    CTX_CHECK(c);
+    int e;
+    switch (scheme)
+    {
+        case MHH_ADVEC_2: e = advec2_cfl_bits(c, u, v, w, c->max_bits_d); break;
+        case MHH_ADVEC_2I5: e = advec2i5_cfl_bits(c, u, v, w, c->max_bits_d); break;
+        case MHH_ADVEC_4: e = advec4_cfl_bits(c, u, v, w, c->max_bits_d); break;
+        default: return MHH_ERR_ARG;
+    }
+    if (e) return e;
+    double m;
+    if ((e = read_max(c, c->max_bits_d, &m))) return e;
+    *cfl = m * dt;     // cfl = cfl*dt after the global max, src/advec_2.cxx:73-75
+    return MHH_OK;
+}
+
+int mhh_advec_time_limit(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w,
+                         unsigned long idt, double dt, double cflmax, unsigned long* out)
+{
+    double cfl;
+    if (int e = mhh_advec_cfl(c, scheme, u, v, w, dt, &cfl)) return e;
+    const double cflmin = 1.e-5;                 // src/advec.cxx:42-60
+    cfl = std::fmax(cflmin, cfl);
+    *out = static_cast<unsigned long>(idt * cflmax / cfl);   // src/advec_2.cxx:293
+    return MHH_OK;
+}
+
+// ---------------------------------------------------------------- Diff
+int mhh_diff2_exec(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+                   double visc, int ns, const double* const* s, double* const* st, const double* svisc)
+{ CTX_CHECK(c); return diff2_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
+
+int mhh_diff4_exec(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+                   double visc, int ns, const double* const* s, double* const* st, const double* svisc)
+{ CTX_CHECK(c); return diff4_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
+
+int mhh_diff_const_dnmul(mhh_ctx* c, double viscmax, double* out)
+{
+    CTX_CHECK(c);
+    const GridD& gd = c->gd;
+    double dnmul = 0;
+    if (c->order == 2)   // src/diff_2.cxx:147-150
+        for (int k = gd.kstart; k < gd.kend; ++k)
+            dnmul = std::fmax(dnmul, std::abs(viscmax * (1. / (gd.dx * gd.dx) + 1. / (gd.dy * gd.dy) + 1. / (c->dz[k] * c->dz[k]))));
+    else                 // src/diff_4.cxx:230-242
+    {
+        const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
+        for (int k = gd.kstart; k < gd.kend; ++k)
+            dnmul = std::fmax(dnmul, std::abs(viscmax * (dxidxi + dyidyi + 1. / (c->dz[k] * c->dz[k]))));
+    }
+    *out = dnmul;
+    return MHH_OK;
+}
+
+int mhh_smag2_exec_viscosity(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,
+                             const double* N2, const double* dudz, const double* dvdz, const double* dbdz,
+                             const double* z0m, double cs, double tPr, double visc, double* evisc)
+{
+    CTX_CHECK(c);
+    if (surface_model && (!dudz || !dvdz || !z0m || (N2 && !dbdz))) return MHH_ERR_ARG;
+    return smag2_exec_viscosity(c, surface_model, u, v, w, N2, dudz, dvdz, dbdz, z0m, cs, tPr, visc, evisc, 0);
+}
+
+int mhh_smag2_strain2(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,
+                      const double* dudz, const double* dvdz, double* strain2)
+{
+    CTX_CHECK(c);
+    return smag2_exec_viscosity(c, surface_model, u, v, w, nullptr, dudz, dvdz, nullptr, nullptr, 0.1, 1., 0., strain2, 1);
+}
+
+int mhh_smag2_exec(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                   double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
+                   double visc, int ns, const double* const* s, double* const* st,
+                   const double* const* sfb, const double* const* sft, const double* svisc, double tPr)
+{
+    CTX_CHECK(c);
+    if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
+    return smag2_exec(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, ns, s, st, sfb, sft, svisc, tPr);
+}
+
+int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
+{
+    CTX_CHECK(c);
+    if (int e = smag2_dnmul_bits(c, evisc, tPr, c->max_bits_d + 1)) return e;
+    return read_max(c, c->max_bits_d + 1, out);
+}
+
+// ---------------------------------------------------------------- Pres
+int mhh_pres_set_values(mhh_ctx* c)
+{
+    CTX_CHECK(c);
+    const GridD& gd = c->gd;
+    int e = (c->order == 2) ? pres2_set_values(c) : pres4_set_values(c);
+    if (e) return e;
+    if (!c->plan_i.tw) { if ((e = fft_plan_create(&c->plan_i, gd.itot))) { c->last_error = "itot has a prime factor > 13"; return e; } }
+    if (!c->plan_j.tw) { if ((e = fft_plan_create(&c->plan_j, gd.jtot))) { c->last_error = "jtot has a prime factor > 13"; return e; } }
+    auto upload = [&](double** d, const std::vector<double>& h) -> int
+    {
+        if (h.empty()) return MHH_OK;
+        if (!*d) MHH_CUDA_CHECK(cudaMalloc(d, sizeof(double) * h.size()));
+        MHH_CUDA_CHECK(cudaMemcpy(*d, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice));
+        return MHH_OK;
+    };
+    if ((e = upload(&c->bmati_d, c->bmati))) return e;
+    if ((e = upload(&c->bmatj_d, c->bmatj))) return e;
+    if ((e = upload(&c->pres_a_d, c->pres_a))) return e;
+    if ((e = upload(&c->pres_c_d, c->pres_c))) return e;
+    if ((e = upload(&c->bands_d, c->bands))) return e;
+    const size_t n = (size_t)gd.imax * gd.jmax * gd.kmax;
+    if (!c->work_p)
+    {
+        MHH_CUDA_CHECK(cudaMalloc(&c->work_p, sizeof(double) * n));
+        MHH_CUDA_CHECK(cudaMalloc(&c->work_c, sizeof(double) * n));
+        c->work_elems = n;
+    }
+    c->pres_ready = true;
+    return MHH_OK;
+}
+
+double* mhh_pres_work(mhh_ctx* c) { return c ? c->work_p : nullptr; }
+
+#define PRES_READY(c) do { CTX_CHECK(c); if (!(c)->pres_ready) { if (int e__ = mhh_pres_set_values(c)) return e__; } } while (0)
+
+int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt, double dt)
+{
+    PRES_READY(c);
+    // cyclic BCs of the tendencies, src/pres_2.cxx:180-181 / src/pres_4.cxx:284-286
+    if (c->npy == 1)
+    {
+        if (int e = cyclic_exec(c, ut, MHH_EDGE_EAST_WEST)) return e;
+        if (int e = cyclic_exec(c, vt, MHH_EDGE_NORTH_SOUTH)) return e;
+    }
+    if (c->order == 2) return pres2_input(c, u, v, w, ut, vt, wt, dt, c->work_p);
+    return pres4_input(c, u, v, w, ut, vt, wt, dt, c->work_p);
+}
+
+int mhh_fft_forward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_forward_inplace(c, data); }
+int mhh_fft_backward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_backward_impl(c, data, nullptr); }
+
+int mhh_pres_solve_spectral(mhh_ctx* c, double* data)
+{
+    PRES_READY(c);
+    return c->order == 2 ? pres2_solve_spectral(c, data) : pres4_solve_spectral(c, data);
+}
+
+int mhh_pres_output(mhh_ctx* c, double* ut, double* vt, double* wt, double* p)
+{
+    PRES_READY(c);
+    return c->order == 2 ? pres2_output(c, ut, vt, wt, p) : pres4_output(c, ut, vt, wt, p);
+}
+
+int mhh_pres_scatter(mhh_ctx* c, double* p, const double* src) { CTX_CHECK(c); return pres_scatter(c, p, src); }
+
+int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
+                  double* ut, double* vt, double* wt, double* p, double dt)
+{
+    PRES_READY(c);
+    if (c->npy != 1) { c->last_error = "mhh_pres_exec is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
+    int e;
+    if ((e = mhh_pres_input(c, u, v, w, ut, vt, wt, dt))) return e;
+    if ((e = fft_forward_inplace(c, c->work_p))) return e;
+    if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
+    if ((e = fft_backward_impl(c, c->work_p, p))) return e;
+    return mhh_pres_output(c, ut, vt, wt, p);
+}
+
+int mhh_pres_check_divergence(mhh_ctx* c, const double* u, const double* v, const double* w, double* out)
+{
+    CTX_CHECK(c);
+    int e = (c->order == 2) ? pres2_divergence_bits(c, u, v, w, c->max_bits_d + 2)
+                            : pres4_divergence_bits(c, u, v, w, c->max_bits_d + 2);
+    if (e) return e;
+    return read_max(c, c->max_bits_d + 2, out);
+}
+
+int mhh_pres_get_coefs(const mhh_ctx* c, double* bmati, double* bmatj, double* a_or_bands, double* cc)
+{
+    CTX_CHECK(c);
+    if (!c->pres_ready) return MHH_ERR_STATE;
+    std::memcpy(bmati, c->bmati.data(), sizeof(double) * c->bmati.size());
+    std::memcpy(bmatj, c->bmatj.data(), sizeof(double) * c->bmatj.size());
+    if (c->order == 2)
+    {
+        std::memcpy(a_or_bands, c->pres_a.data(), sizeof(double) * c->pres_a.size());
+        if (cc) std::memcpy(cc, c->pres_c.data(), sizeof(double) * c->pres_c.size());
+    }
+    else
+        std::memcpy(a_or_bands, c->bands.data(), sizeof(double) * c->bands.size());
+    return MHH_OK;
+}
+
+// ---------------------------------------------------------------- Boundary
+int mhh_cyclic(mhh_ctx* c, double* fld, int edge) { CTX_CHECK(c); return cyclic_exec(c, fld, edge); }
+int mhh_cyclic_2d(mhh_ctx* c, double* fld) { CTX_CHECK(c); return cyclic_exec_2d(c, fld); }
+int mhh_ghost_cells(mhh_ctx* c, double* a, int bcbot, int bctop, double* abot, double* atop,
+                    const double* agradbot, const double* agradtop)
+{ CTX_CHECK(c); return ghost_cells_exec(c, a, bcbot, bctop, abot, atop, agradbot, agradtop); }
+int mhh_ghost_cells_w(mhh_ctx* c, double* w, int type) { CTX_CHECK(c); return ghost_cells_w_exec(c, w, type); }
+int mhh_set_bc(mhh_ctx* c, double* a, double* agrad, double* aflux, int sw, double aval, double visc, double offset)
+{ CTX_CHECK(c); return set_bc_exec(c, a, agrad, aflux, sw, aval, visc, offset); }
+
+// ---------------------------------------------------------------- Timeloop
+int mhh_rk_substep(mhh_ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
+{ CTX_CHECK(c); return rk_substep(c, rkorder, substep, dt, nfields, a, at); }
+double mhh_rk_sub_dt(int rkorder, int substep, double dt) { return rk_sub_dt(rkorder, substep, dt); }
+
+// ---------------------------------------------------------------- Field3d_operators / diagnostics
+int mhh_mean_profile(mhh_ctx* c, const double* fld, double* prof)
+{
+    CTX_CHECK(c);
+    if (int e = level_sums(c, fld, prof)) return e;
+    const double n = (double)c->gd.itot * c->gd.jtot;   // src/field3d_operators.cxx:49
+    for (int k = 0; k < c->gd.kcells; ++k) prof[k] = prof[k] / n;
+    return MHH_OK;
+}
+int mhh_level_sums(mhh_ctx* c, const double* fld, double* sums) { CTX_CHECK(c); return level_sums(c, fld, sums); }
+
+int mhh_mean(mhh_ctx* c, const double* fld, double* out)
+{
+    CTX_CHECK(c);
+    double s;
+    if (int e = weighted_sum(c, 1, fld, nullptr, nullptr, &s)) return e;
+    *out = s / (c->gd.itot * c->gd.jtot * c->gd.zsize);   // src/field3d_operators.cxx:152
+    return MHH_OK;
+}
+int mhh_mean_2d(mhh_ctx* c, const double* fld, double* out)
+{
+    CTX_CHECK(c);
+    double s;
+    if (int e = plane_sum(c, fld, &s)) return e;
+    *out = s / ((double)c->gd.itot * c->gd.jtot);
+    return MHH_OK;
+}
+int mhh_max(mhh_ctx* c, const double* fld, double* out) { CTX_CHECK(c); return interior_max(c, fld, out); }
+
+int mhh_check_momentum(mhh_ctx* c, const double* u, const double* v, const double* w, double* out)
+{
+    CTX_CHECK(c);
+    double s;
+    if (int e = weighted_sum(c, 2, u, v, w, &s)) return e;
+    *out = s / (c->gd.itot * c->gd.jtot * c->gd.zsize);
+    return MHH_OK;
+}
+int mhh_check_tke(mhh_ctx* c, const double* u, const double* v, const double* w, double* out)
+{
+    CTX_CHECK(c);
+    double s;
+    if (int e = weighted_sum(c, 3, u, v, w, &s)) return e;
+    s /= (c->gd.itot * c->gd.jtot * c->gd.zsize);
+    *out = s * 0.5;
+    return MHH_OK;
+}
+int mhh_check_mass(mhh_ctx* c, const double* s_fld, double* out)
+{
+    CTX_CHECK(c);
+    double s;
+    if (int e = weighted_sum(c, 1, s_fld, nullptr, nullptr, &s)) return e;
+    *out = s / (c->gd.itot * c->gd.jtot * c->gd.zsize);
+    return MHH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// Host-side context behind the opaque `mhh_ctx*` of include/mhh_b200.h.
+// Owns only what the reference's operators own (small coefficient arrays, FFT twiddles,
+// solver scratch: src/pres_2.cu:217-250, src/diff_smag2.cu:521-548); all 3-D fields stay
+// owned by the host model and arrive as device pointers.
+#pragma once
+
+#include <string>
+#include <vector>
+
+#include "mhh_common.cuh"
+
+namespace mhh
+{
+
+struct FftPlan
+{
+    int n = 0;
+    int nfac = 0;
+    int fac[20];
+    double2* tw = nullptr;   // device, n entries exp(-2 pi i k/n)
+};
+
+struct Ctx
+{
+    GridD gd;
+    int order = 2;           // swspatialorder
+    int npy = 1, rank_y = 0; // y-slab decomposition (npx = 1), SURVEY 8(e)
+    int iblock = 0, jblock = 0;
+    cudaStream_t stream = 0;
+
+    // host copies of metric arrays (length kcells)
+    std::vector<double> z, zh, dz, dzh, dzi, dzhi, dzi4, dzhi4, rhoref, rhorefh;
+    // device storage backing gd.* pointers: 10 arrays of kcells
+    double* metrics_d = nullptr;
+
+    // reductions
+    unsigned long long* max_bits_d = nullptr;   // 8 slots
+    double* sum_d = nullptr;                    // kcells + 16 slots
+    double* host_pinned = nullptr;              // kcells + 16 doubles, pinned
+
+    // pressure solver
+    bool pres_ready = false;
+    FftPlan plan_i, plan_j;
+    double* bmati_d = nullptr;
+    double* bmatj_d = nullptr;
+    double* pres_a_d = nullptr;     // pres_2: a, c ; pres_4: m1..m7 (7*kmax)
+    double* pres_c_d = nullptr;
+    double* bands_d = nullptr;
+    std::vector<double> bmati, bmatj, pres_a, pres_c, bands;
+    double* work_p = nullptr;       // ghost-free imax*jmax*kmax (spectral work array)
+    double* work_c = nullptr;       // tdma c' / transpose buffer
+    double* work_h = nullptr;       // pres_4 hdma factors
+    size_t work_elems = 0;
+
+    // smag2: per-level Smagorinsky length table (rebuilt when cs changes)
+    double* mlen0_d = nullptr;
+    double mlen0_cs = -1.;
+
+    std::string last_error;
+};
+
+int ctx_set_metrics(Ctx* c, const double* z_host);
+int pres_set_values(Ctx* c);
+
+}  // namespace mhh
+
+struct mhh_ctx : public mhh::Ctx {};

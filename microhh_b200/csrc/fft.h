@@ -1,0 +1,22 @@
+// Batched real <-> half-complex line FFTs (fft.cu).
+#pragma once
+#include "ctx.h"
+
+namespace mhh
+{
+// Line l (0 <= l < nlines), element m (0 <= m < n):
+//   input  address = base_in  + (l % n1 )*s1  + (l / n1 )*s2  + m*sn
+//   output address = base_out + (l % n1o)*s1o + (l / n1o)*s2o + m*sno
+struct FftLayout
+{
+    int nlines;
+    int n1;  long s1, s2, sn;   long base_in;
+    int n1o; long s1o, s2o, sno; long base_out;
+    double scale;
+};
+
+int fft_plan_create(FftPlan* p, int n);
+void fft_plan_destroy(FftPlan* p);
+// dir = -1: real -> half-complex (FFTW_R2HC); +1: half-complex -> real (FFTW_HC2R); both unnormalised * scale.
+int fft_lines(cudaStream_t stream, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L);
+}

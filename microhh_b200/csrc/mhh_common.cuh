@@ -1,0 +1,170 @@
+// Shared device/host definitions for the B200-native dynamical core.
+//
+// Data layout (same as the reference so fields are drop-in): flat, i-fastest,
+//   ijk = i + j*icells + k*ijcells, ghost-celled icells x jcells x kcells
+// (reference: src/grid.cxx:153-166, src/advec_2.cxx:69).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <vector>
+
+namespace mhh
+{
+
+// Grid description passed BY VALUE to kernels (mirrors Grid_data<TF>, include/grid.h:50-135).
+struct GridD
+{
+    int itot, jtot, ktot;
+    int imax, jmax, kmax;
+    int igc, jgc, kgc;
+    int icells, jcells, kcells, ijcells, ncells;
+    int istart, iend, jstart, jend, kstart, kend;
+    double dx, dy, dxi, dyi;
+    double xsize, ysize, zsize;
+    double dzhi4bot, dzhi4top;
+    // device metric arrays, length kcells
+    const double* z;
+    const double* zh;
+    const double* dz;
+    const double* dzh;
+    const double* dzi;
+    const double* dzhi;
+    const double* dzi4;
+    const double* dzhi4;
+    const double* rhoref;
+    const double* rhorefh;
+};
+
+constexpr double kDsmall = 1.e-9;   // Constants::dsmall, include/constants.h
+constexpr double kDhuge  = 1.e9;    // Constants::dhuge
+constexpr double kKappa  = 0.4;     // Constants::kappa<TF>
+
+// Error codes returned through the C ABI (0 = ok).
+enum : int
+{
+    MHH_OK = 0,
+    MHH_ERR_ARG = 1,
+    MHH_ERR_CUDA = 2,
+    MHH_ERR_UNSUPPORTED = 3,
+    MHH_ERR_STATE = 4
+};
+
+#define MHH_CUDA_CHECK(expr)                                                            \
+    do {                                                                                \
+        cudaError_t err__ = (expr);                                                     \
+        if (err__ != cudaSuccess) {                                                     \
+            std::fprintf(stderr, "mhh_b200: CUDA error %s at %s:%d\n",                  \
+                         cudaGetErrorString(err__), __FILE__, __LINE__);                \
+            return MHH_ERR_CUDA;                                                        \
+        }                                                                               \
+    } while (0)
+
+#define MHH_LAUNCH_CHECK() MHH_CUDA_CHECK(cudaGetLastError())
+
+// Launch shape for "one thread per interior point" kernels: x fastest, 128 threads along i.
+struct Launch3
+{
+    dim3 grid, block;
+};
+
+inline Launch3 launch_interior(int ni, int nj, int nk)
+{
+    Launch3 l;
+    const int bx = ni >= 128 ? 128 : (ni >= 64 ? 64 : 32);
+    const int by = 256 / bx;
+    l.block = dim3(bx, by, 1);
+    l.grid = dim3((ni + bx - 1) / bx, (nj + by - 1) / by, nk);
+    return l;
+}
+
+// ---- max reduction on |x| that PROPAGATES NaN/inf (the reference's CFL guard, src/model.cxx:832-836,
+// must stay meaningful): non-negative doubles order like their bit patterns, and NaN patterns sort
+// above +inf, so the reduction runs on unsigned 64-bit integers.
+__device__ __forceinline__ unsigned long long abs_bits(double x)
+{
+    return static_cast<unsigned long long>(__double_as_longlong(fabs(x))) & 0x7fffffffffffffffULL;
+}
+
+__device__ __forceinline__ void block_max_bits(unsigned long long v, unsigned long long* out)
+{
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, v, o);
+        v = other > v ? other : v;
+    }
+    __shared__ unsigned long long warp_max[32];
+    const int tid = threadIdx.x + threadIdx.y * blockDim.x + threadIdx.z * blockDim.x * blockDim.y;
+    const int nwarps = (blockDim.x * blockDim.y * blockDim.z + 31) >> 5;
+    if ((tid & 31) == 0) warp_max[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32)
+    {
+        v = tid < nwarps ? warp_max[tid] : 0ULL;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+        {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, v, o);
+            v = other > v ? other : v;
+        }
+        if (tid == 0 && v != 0ULL) atomicMax(out, v);
+    }
+}
+
+// Deterministic block sum (fixed tree order) of doubles; result valid in thread 0.
+__device__ __forceinline__ double block_sum(double v)
+{
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        v += __shfl_down_sync(0xffffffffu, v, o);
+    __shared__ double warp_sum[32];
+    const int tid = threadIdx.x + threadIdx.y * blockDim.x;
+    const int nwarps = (blockDim.x * blockDim.y + 31) >> 5;
+    if ((tid & 31) == 0) warp_sum[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32)
+    {
+        v = tid < nwarps ? warp_sum[tid] : 0.;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+            v += __shfl_down_sync(0xffffffffu, v, o);
+    }
+    return v;
+}
+
+// ---- finite-difference helpers (restated from include/finite_difference.h:34-156) ----------
+namespace fd
+{
+    __device__ __forceinline__ double interp2(double a, double b) { return 0.5 * (a + b); }
+
+    // O4 coefficients (include/finite_difference.h:57-90)
+    constexpr double ci0 = -1. / 16., ci1 = 9. / 16., ci2 = 9. / 16., ci3 = -1. / 16.;
+    constexpr double bi0 = 5. / 16., bi1 = 15. / 16., bi2 = -5. / 16., bi3 = 1. / 16.;
+    constexpr double ti0 = 1. / 16., ti1 = -5. / 16., ti2 = 15. / 16., ti3 = 5. / 16.;
+    constexpr double cg0 = 1. / 24., cg1 = -27. / 24., cg2 = 27. / 24., cg3 = -1. / 24.;
+    constexpr double bg0 = -23. / 24., bg1 = 21. / 24., bg2 = 3. / 24., bg3 = -1. / 24.;
+    constexpr double tg0 = 1. / 24., tg1 = -3. / 24., tg2 = -21. / 24., tg3 = 23. / 24.;
+    constexpr double cdg0 = -1460. / 576., cdg1 = 783. / 576., cdg2 = -54. / 576., cdg3 = 1. / 576.;
+
+    __device__ __forceinline__ double interp22(double a, double b, double c, double d) { return 0.25 * (a + b + c + d); }
+    __device__ __forceinline__ double interp4c(double a, double b, double c, double d)
+    { return ci0 * (a + d) + ci1 * (b + c); }
+    __device__ __forceinline__ double interp4b(double a, double b, double c, double d)
+    { return bi0 * a + bi1 * b - bi2 * c + bi3 * d; }   // sign quirk kept; unused by the path
+    __device__ __forceinline__ double interp4t(double a, double b, double c, double d)
+    { return ti0 * a + ti1 * b + ti2 * c + ti3 * d; }
+    __device__ __forceinline__ double interp4_ws(double a, double b, double c, double d)
+    { return (7. / 12.) * (b + c) - (1. / 12.) * (a + d); }
+    __device__ __forceinline__ double interp3_ws(double a, double b, double c, double d)
+    { return (3. / 12.) * (c - b) - (1. / 12.) * (d - a); }
+    __device__ __forceinline__ double grad4(double a, double b, double c, double d)
+    { return (-cg0 * (d - a) - cg1 * (c - b)); }
+    __device__ __forceinline__ double interp6_ws(double a, double b, double c, double d, double e, double f)
+    { return (37. / 60.) * (c + d) - (8. / 60.) * (b + e) + (1. / 60.) * (a + f); }
+    __device__ __forceinline__ double interp5_ws(double a, double b, double c, double d, double e, double f)
+    { return (10. / 60.) * (d - c) - (5. / 60.) * (e - b) + (1. / 60.) * (f - a); }
+}
+
+}  // namespace mhh

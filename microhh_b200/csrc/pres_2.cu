@@ -1,0 +1,259 @@
+// 2nd-order Poisson pressure solver for sm_100a (reference: src/pres_2.cxx, src/fft.cxx).
+//
+//   input   : rho-weighted divergence of (u/dt + ut) into a ghost-free work array      (:156-196)
+//   forward : x then y real->half-complex FFTs (fft.cu)                                 (fft.cxx:335-389)
+//   solve   : per-(kx,ky) tridiagonal system over k; the diagonal b and the dz^2 scaling of the
+//             RHS (solve loop :292-304, BCs :306-324) are computed on the fly inside the Thomas
+//             sweep (tdma :202-263), so only p and the c' work array touch HBM
+//   backward: y then x half-complex->real, normalised; the x pass scatters straight into the
+//             ghost-celled p (replaces the copy loop :340-348)
+//   output  : bottom Neumann ghost row, cyclic halos, ut/vt/wt -= grad p                 (:352-387)
+#include <cmath>
+
+#include "ctx.h"
+#include "fft.h"
+
+namespace mhh
+{
+int cyclic_exec(Ctx* c, double* fld, int edge);
+
+namespace
+{
+    constexpr int KCHUNK = 32;
+
+    // Pres_2::input, src/pres_2.cxx:183-195
+    __global__ void __launch_bounds__(256)
+    pres2_in_kernel(double* __restrict__ p, const double* __restrict__ u, const double* __restrict__ v,
+                    const double* __restrict__ w, const double* __restrict__ ut, const double* __restrict__ vt,
+                    const double* __restrict__ wt, const double dti, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y;
+        if (i >= gd.imax || j >= gd.jmax) return;
+        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
+        const int jjp = gd.imax, kkp = gd.imax * gd.jmax;
+        const int k0 = blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kmax);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+
+        int ijk = i + gd.igc + (j + gd.jgc) * jj + (k0 + gd.kgc) * kk;
+        double wflux_b = wt[ijk] + w[ijk] * dti;
+        for (int k = k0; k < k1; ++k, ijk += kk)
+        {
+            const int ijkp = i + j * jjp + k * kkp;
+            const double rho = gd.rhoref[k + gd.kgc];
+            const double wflux_t = wt[ijk + kk] + w[ijk + kk] * dti;
+            p[ijkp] = rho * ((ut[ijk + ii] + u[ijk + ii] * dti) - (ut[ijk] + u[ijk] * dti)) * dxi
+                    + rho * ((vt[ijk + jj] + v[ijk + jj] * dti) - (vt[ijk] + v[ijk] * dti)) * dyi
+                    + (gd.rhorefh[k + gd.kgc + 1] * wflux_t - gd.rhorefh[k + gd.kgc] * wflux_b) * gd.dzi[k + gd.kgc];
+            wflux_b = wflux_t;
+        }
+    }
+
+    // solve_in + tdma fused: one thread per (kx,ky) column, k sequential, i-fastest coalescing.
+    __global__ void __launch_bounds__(128)
+    pres2_tdma_kernel(double* __restrict__ p, double* __restrict__ work3d,
+                      const double* __restrict__ a, const double* __restrict__ c,
+                      const double* __restrict__ bmati, const double* __restrict__ bmatj,
+                      const int iblock, const int jblock, const int ioff, const int joff, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        const int j = blockIdx.y;
+        if (i >= iblock) return;
+        const int kmax = gd.kmax, kgc = gd.kgc;
+        const int kk = iblock * jblock;
+        const int ij = i + j * iblock;
+        const int iindex = ioff + i, jindex = joff + j;
+        const double bm = bmati[iindex] + bmatj[jindex];
+        const bool mode0 = (iindex == 0 && jindex == 0);
+
+        // b at level k with the boundary substitutions of src/pres_2.cxx:306-324
+        auto bdiag = [&](int k) -> double
+        {
+            const double dz = gd.dz[k + kgc];
+            double b = dz * dz * gd.rhoref[k + kgc] * bm - (a[k] + c[k]);
+            if (k == 0) b += a[0];
+            if (k == kmax - 1) { if (mode0) b -= c[kmax - 1]; else b += c[kmax - 1]; }
+            return b;
+        };
+        auto rhs = [&](int k) -> double
+        {
+            const double dz = gd.dz[k + kgc];
+            return dz * dz * p[ij + k * kk];
+        };
+
+        double work2d = bdiag(0);
+        double pprev = rhs(0) / work2d;
+        p[ij] = pprev;
+        for (int k = 1; k < kmax; ++k)
+        {
+            const double w3 = c[k - 1] / work2d;
+            work3d[ij + k * kk] = w3;
+            work2d = bdiag(k) - a[k] * w3;
+            double pk = rhs(k);
+            pk -= a[k] * pprev;
+            pk /= work2d;
+            p[ij + k * kk] = pk;
+            pprev = pk;
+        }
+        for (int k = kmax - 2; k >= 0; --k)
+        {
+            double pk = p[ij + k * kk];
+            pk -= work3d[ij + (k + 1) * kk] * pprev;
+            p[ij + k * kk] = pk;
+            pprev = pk;
+        }
+    }
+
+    // p[kstart-1] = p[kstart] on interior columns, src/pres_2.cxx:352-358
+    __global__ void pres2_bottom_ghost_kernel(double* __restrict__ p, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y + gd.jstart;
+        if (i >= gd.iend) return;
+        const int ijk = i + j * gd.icells + gd.kstart * gd.ijcells;
+        p[ijk - gd.ijcells] = p[ijk];
+    }
+
+    // ghost-free -> ghost-celled copy (stage API only; the fused path scatters from the FFT kernel)
+    __global__ void pres_scatter_kernel(double* __restrict__ p, const double* __restrict__ src, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        const int j = blockIdx.y;
+        const int k = blockIdx.z;
+        if (i >= gd.imax) return;
+        p[i + gd.igc + (j + gd.jgc) * gd.icells + (k + gd.kgc) * gd.ijcells] = src[i + j * gd.imax + k * gd.imax * gd.jmax];
+    }
+
+    // Pres_2::output, src/pres_2.cxx:365-387
+    __global__ void __launch_bounds__(256)
+    pres2_out_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
+                     const double* __restrict__ p, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        if (i >= gd.iend || j >= gd.jend) return;
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        int ijk = i + j * jj + k0 * kk;
+        double p_b = p[ijk - kk];
+        for (int k = k0; k < k1; ++k, ijk += kk)
+        {
+            const double p_c = p[ijk];
+            ut[ijk] -= (p_c - p[ijk - 1]) * dxi;
+            vt[ijk] -= (p_c - p[ijk - jj]) * dyi;
+            wt[ijk] -= (p_c - p_b) * gd.dzhi[k];
+            p_b = p_c;
+        }
+    }
+
+    // Pres_2::calc_divergence, src/pres_2.cxx:391-422
+    __global__ void __launch_bounds__(256)
+    pres2_div_kernel(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
+                     const GridD gd, unsigned long long* __restrict__ out)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        unsigned long long m = 0ULL;
+        if (i < gd.iend && j < gd.jend)
+            for (int k = k0; k < k1; ++k)
+            {
+                const int ijk = i + j * jj + k * kk;
+                const double div = gd.rhoref[k] * ((u[ijk + 1] - u[ijk]) * dxi + (v[ijk + jj] - v[ijk]) * dyi)
+                                 + (gd.rhorefh[k + 1] * w[ijk + kk] - gd.rhorefh[k] * w[ijk]) * gd.dzi[k];
+                const unsigned long long b = abs_bits(div);
+                m = b > m ? b : m;
+            }
+        block_max_bits(m, out);
+    }
+}  // namespace
+
+// Pres_2::set_values, src/pres_2.cxx:125-153
+int pres2_set_values(Ctx* c)
+{
+    const GridD& gd = c->gd;
+    const double dxidxi = 1. / (gd.dx * gd.dx);
+    const double dyidyi = 1. / (gd.dy * gd.dy);
+    const double pi = std::acos(-1.);
+    c->bmati.assign(gd.itot, 0.);
+    c->bmatj.assign(gd.jtot, 0.);
+    for (int j = 0; j < gd.jtot / 2 + 1; ++j)
+        c->bmatj[j] = 2. * (std::cos(2. * pi * (double)j / (double)gd.jtot) - 1.) * dyidyi;
+    for (int j = gd.jtot / 2 + 1; j < gd.jtot; ++j)
+        c->bmatj[j] = c->bmatj[gd.jtot - j];
+    for (int i = 0; i < gd.itot / 2 + 1; ++i)
+        c->bmati[i] = 2. * (std::cos(2. * pi * (double)i / (double)gd.itot) - 1.) * dxidxi;
+    for (int i = gd.itot / 2 + 1; i < gd.itot; ++i)
+        c->bmati[i] = c->bmati[gd.itot - i];
+    c->pres_a.assign(gd.kmax, 0.);
+    c->pres_c.assign(gd.kmax, 0.);
+    for (int k = 0; k < gd.kmax; ++k)
+    {
+        c->pres_a[k] = c->dz[k + gd.kgc] * c->rhorefh[k + gd.kgc] * c->dzhi[k + gd.kgc];
+        c->pres_c[k] = c->dz[k + gd.kgc] * c->rhorefh[k + gd.kgc + 1] * c->dzhi[k + gd.kgc + 1];
+    }
+    return MHH_OK;
+}
+
+int pres2_input(Ctx* c, const double* u, const double* v, const double* w,
+                const double* ut, const double* vt, const double* wt, double dt, double* work)
+{
+    const GridD& gd = c->gd;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    pres2_in_kernel<<<l.grid, l.block, 0, c->stream>>>(work, u, v, w, ut, vt, wt, 1. / dt, gd);
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+int pres2_solve_spectral(Ctx* c, double* data)
+{
+    const GridD& gd = c->gd;
+    dim3 b(128), g((c->iblock + 127) / 128, c->jblock);
+    pres2_tdma_kernel<<<g, b, 0, c->stream>>>(data, c->work_c, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+                                              c->iblock, c->jblock, c->rank_y * c->iblock, 0, gd);
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+int pres_scatter(Ctx* c, double* p, const double* src)
+{
+    const GridD& gd = c->gd;
+    dim3 b(128), g((gd.imax + 127) / 128, gd.jmax, gd.kmax);
+    pres_scatter_kernel<<<g, b, 0, c->stream>>>(p, src, gd);
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+// p already holds the interior (scattered); finish ghost rows/halos and apply the gradient.
+int pres2_output(Ctx* c, double* ut, double* vt, double* wt, double* p)
+{
+    const GridD& gd = c->gd;
+    {
+        dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
+        pres2_bottom_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd);
+        MHH_LAUNCH_CHECK();
+    }
+    if (int e = cyclic_exec(c, p, 2)) return e;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    pres2_out_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd);
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+int pres2_divergence_bits(Ctx* c, const double* u, const double* v, const double* w, unsigned long long* slot)
+{
+    const GridD& gd = c->gd;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    MHH_CUDA_CHECK(cudaMemsetAsync(slot, 0, sizeof(unsigned long long), c->stream));
+    pres2_div_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot);
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+}  // namespace mhh

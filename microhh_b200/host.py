@@ -1,0 +1,480 @@
+"""Host-side mirror of the reference's operator interfaces for the dynamical core.
+
+Same class names, factory keys and method names as the reference (``include/advec.h:45-70``,
+``include/diff.h:37-71``, ``include/pres.h:39-85``, ``include/boundary.h:74-185``,
+``include/timeloop.h``), each method a thin call into the C ABI (``include/mhh_b200.h``).
+PyTorch is used only to own device memory (``torch.empty(..., device="cuda")``) and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import lib as L
+
+
+class Grid:
+    """Grid / Grid_data (include/grid.h:50-135). ``settings`` holds the [grid] keys of the .ini."""
+
+    def __init__(self, itot, jtot, ktot, xsize, ysize, zsize, z, swspatialorder="2", gc=(0, 0, 0),
+                 npy=1, rank_y=0, device=None):
+        if not torch.cuda.is_available():
+            raise L.MhhError("microhh_b200 needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.lib = L.load()
+        order = int(swspatialorder)
+        if order not in (2, 4):
+            raise L.MhhError(f"{swspatialorder} is an illegal value for swspatialorder")
+        d = L.GridDesc(itot, jtot, ktot, gc[0], gc[1], gc[2], xsize, ysize, zsize, order, npy, rank_y)
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        assert z.shape == (ktot,)
+        self.ctx = C.c_void_p()
+        with torch.cuda.device(self.device):
+            err = self.lib.mhh_create(C.byref(d), z.ctypes.data_as(C.c_void_p), C.byref(self.ctx))
+        if err:
+            raise L.MhhError(f"mhh_create failed with code {err}")
+        dims = (C.c_int * 20)()
+        self.lib.mhh_get_dims(self.ctx, dims)
+        (self.itot, self.jtot, self.ktot, self.imax, self.jmax, self.kmax, self.igc, self.jgc, self.kgc,
+         self.icells, self.jcells, self.kcells, self.ijcells, self.ncells,
+         self.istart, self.iend, self.jstart, self.jend, self.kstart, self.kend) = (int(x) for x in dims)
+        self.order = order
+        self.npy, self.rank_y = npy, rank_y
+        self.xsize, self.ysize, self.zsize = xsize, ysize, zsize
+        self.dx, self.dy = xsize / itot, ysize / jtot
+        self.shape = (self.kcells, self.jcells, self.icells)
+        self.shape2d = (self.jcells, self.icells)
+        for name in ("z", "zh", "dz", "dzh", "dzi", "dzhi", "dzi4", "dzhi4"):
+            setattr(self, name, self.metric(name))
+
+    def metric(self, name):
+        a = np.zeros(self.kcells)
+        L.check(self.ctx, self.lib.mhh_get_metric(self.ctx, name.encode(), a.ctypes.data_as(C.c_void_p)), "mhh_get_metric")
+        return a
+
+    def set_rhoref(self, rhoref, rhorefh):
+        rhoref = np.ascontiguousarray(rhoref, dtype=np.float64)
+        rhorefh = np.ascontiguousarray(rhorefh, dtype=np.float64)
+        assert rhoref.shape == (self.kcells,) and rhorefh.shape == (self.kcells,)
+        L.check(self.ctx, self.lib.mhh_set_rhoref(self.ctx, rhoref.ctypes.data_as(C.c_void_p),
+                                                  rhorefh.ctypes.data_as(C.c_void_p)), "mhh_set_rhoref")
+
+    def zeros(self):
+        return torch.zeros(self.shape, dtype=torch.float64, device=self.device)
+
+    def zeros2d(self):
+        return torch.zeros(self.shape2d, dtype=torch.float64, device=self.device)
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.mhh_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Field3d:
+    """Field3d (include/field3d.h:47-76): a 3-D array plus six 2-D boundary planes."""
+
+    def __init__(self, grid: Grid, name: str, visc: float = 0.0):
+        self.name, self.visc = name, visc
+        self.fld = grid.zeros()
+        self.fld_bot, self.fld_top = grid.zeros2d(), grid.zeros2d()
+        self.grad_bot, self.grad_top = grid.zeros2d(), grid.zeros2d()
+        self.flux_bot, self.flux_top = grid.zeros2d(), grid.zeros2d()
+
+
+class Fields:
+    """Fields (include/fields.h:132-182): the named maps mp/mt/sp/st/sd/ap/at."""
+
+    def __init__(self, grid: Grid, slist=(), visc=0.0, svisc=0.0):
+        self.grid, self.visc = grid, visc
+        self.mp, self.mt, self.sp, self.st, self.sd = {}, {}, {}, {}, {}
+        for n in ("u", "v", "w"):
+            self.mp[n] = Field3d(grid, n, visc)
+            self.mt[n] = Field3d(grid, n + "t")
+        for n in slist:
+            self.init_prognostic_field(n, svisc)
+        self.sd["p"] = Field3d(grid, "p")
+        self.rhoref = np.ones(grid.kcells)
+        self.rhorefh = np.ones(grid.kcells)
+
+    def init_prognostic_field(self, name, visc):
+        self.sp[name] = Field3d(self.grid, name, visc)
+        self.st[name] = Field3d(self.grid, name + "t")
+
+    def init_diagnostic_field(self, name):
+        if name not in self.sd:
+            self.sd[name] = Field3d(self.grid, name)
+
+    @property
+    def ap(self):
+        return {**self.mp, **self.sp}
+
+    @property
+    def at(self):
+        return {**self.mt, **self.st}
+
+    def set_rhoref(self, rhoref, rhorefh):
+        self.rhoref, self.rhorefh = np.asarray(rhoref, dtype=np.float64), np.asarray(rhorefh, dtype=np.float64)
+        self.grid.set_rhoref(self.rhoref, self.rhorefh)
+
+    # Fields::check_momentum/tke/mass, src/fields.cxx:1175-1217
+    def _scalar(self, fn, *flds):
+        out = C.c_double()
+        L.check(self.grid.ctx, fn(self.grid.ctx, *[L.ptr(f) for f in flds], C.byref(out)), fn.__name__)
+        return out.value
+
+    def check_momentum(self):
+        return self._scalar(self.grid.lib.mhh_check_momentum, self.mp["u"].fld, self.mp["v"].fld, self.mp["w"].fld)
+
+    def check_tke(self):
+        return self._scalar(self.grid.lib.mhh_check_tke, self.mp["u"].fld, self.mp["v"].fld, self.mp["w"].fld)
+
+    def check_mass(self):
+        if not self.sp:
+            return 0.0
+        first = sorted(self.sp)[0]          # std::map iteration order
+        return self._scalar(self.grid.lib.mhh_check_mass, self.sp[first].fld)
+
+
+class Field3d_operators:
+    """Field3d_operators (include/field3d_operators.h:40-51)."""
+
+    def __init__(self, grid: Grid):
+        self.grid = grid
+
+    def calc_mean_profile(self, fld):
+        prof = np.zeros(self.grid.kcells)
+        L.check(self.grid.ctx, self.grid.lib.mhh_mean_profile(self.grid.ctx, L.ptr(fld), prof.ctypes.data_as(C.c_void_p)),
+                "mhh_mean_profile")
+        return prof
+
+    def _scalar(self, fn, fld):
+        out = C.c_double()
+        L.check(self.grid.ctx, fn(self.grid.ctx, L.ptr(fld), C.byref(out)), fn.__name__)
+        return out.value
+
+    def calc_mean(self, fld):
+        return self._scalar(self.grid.lib.mhh_mean, fld)
+
+    def calc_mean_2d(self, fld2d):
+        return self._scalar(self.grid.lib.mhh_mean_2d, fld2d)
+
+    def calc_max(self, fld):
+        return self._scalar(self.grid.lib.mhh_max, fld)
+
+
+class Boundary_cyclic:
+    """Boundary_cyclic (include/boundary_cyclic.h:36-49)."""
+
+    def __init__(self, grid: Grid):
+        self.grid = grid
+
+    def exec(self, fld, edge=L.EDGE_BOTH):
+        L.check(self.grid.ctx, self.grid.lib.mhh_cyclic(self.grid.ctx, L.ptr(fld), edge), "mhh_cyclic")
+
+    def exec_2d(self, fld2d):
+        L.check(self.grid.ctx, self.grid.lib.mhh_cyclic_2d(self.grid.ctx, L.ptr(fld2d)), "mhh_cyclic_2d")
+
+
+_BC = {"dirichlet": L.BC_DIRICHLET, "neumann": L.BC_NEUMANN, "flux": L.BC_FLUX, "ustar": L.BC_USTAR, "off": L.BC_OFF,
+       "noslip": L.BC_DIRICHLET, "freeslip": L.BC_NEUMANN}
+
+
+@dataclass
+class Field3dBc:
+    """Field3dBc (include/boundary.h:60-67)."""
+    bot: float = 0.0
+    top: float = 0.0
+    bcbot: int = L.BC_NEUMANN
+    bctop: int = L.BC_NEUMANN
+
+
+class Boundary:
+    """Boundary base class = swboundary=default (include/boundary.h:74-185, src/boundary.cxx)."""
+
+    def __init__(self, grid: Grid, fields: Fields, mbcbot="noslip", mbctop="noslip", ubot=0., utop=0., vbot=0., vtop=0.,
+                 sbc=None, swboundary="default"):
+        self.grid, self.fields = grid, fields
+        self.swboundary = swboundary
+        self.mbcbot, self.mbctop = _BC[mbcbot], _BC[mbctop]
+        self.ubot, self.utop, self.vbot, self.vtop = ubot, utop, vbot, vtop
+        self.sbc = {}
+        for name in fields.sp:
+            spec = (sbc or {}).get(name, {})
+            self.sbc[name] = Field3dBc(spec.get("sbot", 0.), spec.get("stop", 0.),
+                                       _BC[spec.get("sbcbot", "neumann")], _BC[spec.get("sbctop", "neumann")])
+        self.boundary_cyclic = Boundary_cyclic(grid)
+
+    def get_switch(self):
+        return self.swboundary
+
+    def _set_bc(self, a, agrad, aflux, sw, aval, visc, offset):
+        L.check(self.grid.ctx, self.grid.lib.mhh_set_bc(self.grid.ctx, L.ptr(a), L.ptr(agrad), L.ptr(aflux), sw,
+                                                        C.c_double(aval), C.c_double(visc), C.c_double(offset)), "mhh_set_bc")
+
+    def set_values(self):
+        """Boundary::set_values, src/boundary.cxx:598-682 (no Galilean offset: utrans=vtrans=0)."""
+        f = self.fields
+        for name, bot, top in (("u", self.ubot, self.utop), ("v", self.vbot, self.vtop)):
+            fld = f.mp[name]
+            self._set_bc(fld.fld_bot, fld.grad_bot, fld.flux_bot, self.mbcbot, bot, f.visc, 0.)
+            self._set_bc(fld.fld_top, fld.grad_top, fld.flux_top, self.mbctop, top, f.visc, 0.)
+        for name, fld in f.sp.items():
+            bc = self.sbc[name]
+            self._set_bc(fld.fld_bot, fld.grad_bot, fld.flux_bot, bc.bcbot, bc.bot, fld.visc, 0.)
+            self._set_bc(fld.fld_top, fld.grad_top, fld.flux_top, bc.bctop, bc.top, fld.visc, 0.)
+
+    def set_prognostic_cyclic_bcs(self):
+        """src/boundary.cxx:447-458"""
+        for fld in self.fields.ap.values():
+            self.boundary_cyclic.exec(fld.fld)
+
+    def _ghost(self, fld, bcbot, bctop):
+        L.check(self.grid.ctx, self.grid.lib.mhh_ghost_cells(self.grid.ctx, L.ptr(fld.fld), bcbot, bctop,
+                                                             L.ptr(fld.fld_bot), L.ptr(fld.fld_top),
+                                                             L.ptr(fld.grad_bot), L.ptr(fld.grad_top)), "mhh_ghost_cells")
+
+    def set_ghost_cells(self):
+        """Boundary::set_ghost_cells, src/boundary.cxx:919-983 (update_slave_bcs is host bookkeeping, not needed here)."""
+        f = self.fields
+        self._ghost(f.mp["u"], self.mbcbot, self.mbctop)
+        self._ghost(f.mp["v"], self.mbcbot, self.mbctop)
+        if self.grid.order == 4:
+            self.set_ghost_cells_w(L.BCW_NORMAL)
+        for name, fld in f.sp.items():
+            self._ghost(fld, self.sbc[name].bcbot, self.sbc[name].bctop)
+
+    def set_ghost_cells_w(self, boundary_w_type):
+        """src/boundary.cxx:986-1007"""
+        L.check(self.grid.ctx, self.grid.lib.mhh_ghost_cells_w(self.grid.ctx, L.ptr(self.fields.mp["w"].fld), boundary_w_type),
+                "mhh_ghost_cells_w")
+
+
+class Advec:
+    """Advec (include/advec.h:45-70); factory keyed on [advec] swadvec (src/advec.cxx:62-83)."""
+    _schemes = {"2": L.ADVEC_2, "2i5": L.ADVEC_2I5, "4": L.ADVEC_4}
+
+    def __init__(self, grid, fields, swadvec, cflmax=1.0, fluxlimit_list=()):
+        self.grid, self.fields = grid, fields
+        self.swadvec, self.scheme = swadvec, self._schemes[swadvec]
+        self.cflmax, self.cflmin = cflmax, 1.e-5
+        self.fluxlimit_list = tuple(fluxlimit_list)
+
+    @staticmethod
+    def factory(grid, fields, swadvec=None, **kw):
+        if swadvec is None:
+            swadvec = str(grid.order)
+        if swadvec not in Advec._schemes:
+            raise L.MhhError(f"{swadvec} is an illegal value for swadvec")
+        return Advec(grid, fields, swadvec, **kw)
+
+    def get_switch(self):
+        return self.swadvec
+
+    def exec(self, stats=None):
+        f, g = self.fields, self.grid
+        names = list(f.sp)
+        s = L.ptr_array([f.sp[n].fld for n in names])
+        st = L.ptr_array([f.st[n].fld for n in names])
+        flags = (C.c_int * max(len(names), 1))(*[1 if n in self.fluxlimit_list else 0 for n in names])
+        L.check(g.ctx, g.lib.mhh_advec_exec(g.ctx, self.scheme, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
+                                            L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
+                                            len(names), s, st, flags), "mhh_advec_exec")
+
+    def get_cfl(self, dt):
+        f, g = self.fields, self.grid
+        out = C.c_double()
+        L.check(g.ctx, g.lib.mhh_advec_cfl(g.ctx, self.scheme, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
+                                           C.c_double(dt), C.byref(out)), "mhh_advec_cfl")
+        return out.value
+
+    def get_time_limit(self, idt, dt):
+        cfl = max(self.cflmin, self.get_cfl(dt))
+        return int(idt * self.cflmax / cfl)
+
+
+class Diff:
+    """Diff (include/diff.h:37-71); factory keyed on [diff] swdiff (src/diff.cxx:57-85)."""
+
+    def __init__(self, grid, fields, boundary, swdiff, dnmax=0.4, cs=0.23, tPr=1. / 3.):
+        self.grid, self.fields, self.boundary = grid, fields, boundary
+        self.swdiff, self.dnmax, self.cs, self.tPr = swdiff, dnmax, cs, tPr
+        if swdiff == "smag2":
+            fields.init_diagnostic_field("evisc")
+        self.dnmul = 0.0
+
+    @staticmethod
+    def factory(grid, fields, boundary, swdiff=None, **kw):
+        if swdiff is None:
+            swdiff = str(grid.order)
+        if swdiff not in ("0", "2", "4", "smag2"):
+            raise L.MhhError(f"{swdiff} is an illegal value for swdiff")
+        return Diff(grid, fields, boundary, swdiff, **kw)
+
+    def get_switch(self):
+        return self.swdiff
+
+    def create(self):
+        """static dnmul, src/diff_2.cxx:139-151 / src/diff_smag2.cxx:921-936"""
+        g, f = self.grid, self.fields
+        viscmax = max([f.visc] + [s.visc for s in f.sp.values()])
+        out = C.c_double()
+        L.check(g.ctx, g.lib.mhh_diff_const_dnmul(g.ctx, C.c_double(viscmax), C.byref(out)), "mhh_diff_const_dnmul")
+        self.dnmul = out.value
+
+    def _surface_model(self):
+        return 1 if self.boundary.get_switch() != "default" else 0
+
+    def exec_viscosity(self, thermo=None, surface=None):
+        """Diff_smag2::exec_viscosity, src/diff_smag2.cxx:1046. ``thermo`` supplies N2 (get_thermo_field("N2"));
+        ``surface`` supplies z0m/dudz/dvdz/dbdz planes when a surface model is on."""
+        if self.swdiff != "smag2":
+            return
+        g, f = self.grid, self.fields
+        sm = self._surface_model()
+        N2 = thermo.get_thermo_field("N2") if thermo is not None and thermo.get_switch() != "0" else None
+        planes = surface or {}
+        L.check(g.ctx, g.lib.mhh_smag2_exec_viscosity(
+            g.ctx, sm, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(N2),
+            L.ptr(planes.get("dudz")), L.ptr(planes.get("dvdz")), L.ptr(planes.get("dbdz")), L.ptr(planes.get("z0m")),
+            C.c_double(self.cs), C.c_double(self.tPr), C.c_double(f.visc), L.ptr(f.sd["evisc"].fld)), "mhh_smag2_exec_viscosity")
+
+    def exec(self, stats=None):
+        g, f = self.grid, self.fields
+        if self.swdiff == "0":
+            return
+        names = list(f.sp)
+        s = L.ptr_array([f.sp[n].fld for n in names])
+        st = L.ptr_array([f.st[n].fld for n in names])
+        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        u, v, w = (L.ptr(f.mp[n].fld) for n in "uvw")
+        ut, vt, wt = (L.ptr(f.mt[n].fld) for n in "uvw")
+        if self.swdiff == "2":
+            L.check(g.ctx, g.lib.mhh_diff2_exec(g.ctx, u, v, w, ut, vt, wt, C.c_double(f.visc), len(names), s, st, svisc), "mhh_diff2_exec")
+        elif self.swdiff == "4":
+            L.check(g.ctx, g.lib.mhh_diff4_exec(g.ctx, u, v, w, ut, vt, wt, C.c_double(f.visc), len(names), s, st, svisc), "mhh_diff4_exec")
+        else:
+            sfb = L.ptr_array([f.sp[n].flux_bot for n in names])
+            sft = L.ptr_array([f.sp[n].flux_top for n in names])
+            L.check(g.ctx, g.lib.mhh_smag2_exec(
+                g.ctx, self._surface_model(), u, v, w, L.ptr(f.sd["evisc"].fld), ut, vt, wt,
+                L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
+                C.c_double(f.visc), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_smag2_exec")
+
+    def _dnmul(self):
+        if self.swdiff != "smag2":
+            return self.dnmul
+        g, f = self.grid, self.fields
+        out = C.c_double()
+        L.check(g.ctx, g.lib.mhh_smag2_dnmul(g.ctx, L.ptr(f.sd["evisc"].fld), C.c_double(self.tPr), C.byref(out)), "mhh_smag2_dnmul")
+        return out.value
+
+    def get_dn(self, dt):
+        return self._dnmul() * dt
+
+    def get_time_limit(self, idt, dt):
+        if self.swdiff == "0":
+            return int(1e18)
+        dnmul = max(1.e-9, self._dnmul()) if self.swdiff == "smag2" else self._dnmul()
+        return int(idt * self.dnmax / (dt * dnmul))
+
+
+class Pres:
+    """Pres (include/pres.h:39-85); factory keyed on [pres] swpres (src/pres.cxx:66-84)."""
+
+    def __init__(self, grid, fields, swpres):
+        self.grid, self.fields, self.swpres = grid, fields, swpres
+
+    @staticmethod
+    def factory(grid, fields, swpres=None):
+        if swpres is None:
+            swpres = str(grid.order)
+        if swpres not in ("0", "2", "4"):
+            raise L.MhhError(f"{swpres} is an illegal value for swpres")
+        if swpres != "0" and int(swpres) != grid.order:
+            raise L.MhhError("swpres must match swspatialorder (ghost-cell depth)")
+        return Pres(grid, fields, swpres)
+
+    def set_values(self):
+        g = self.grid
+        L.check(g.ctx, g.lib.mhh_pres_set_values(g.ctx), "mhh_pres_set_values")
+
+    def exec(self, dt, stats=None):
+        if self.swpres == "0":
+            return
+        g, f = self.grid, self.fields
+        L.check(g.ctx, g.lib.mhh_pres_exec(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
+                                           L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
+                                           L.ptr(f.sd["p"].fld), C.c_double(dt)), "mhh_pres_exec")
+
+    def check_divergence(self):
+        g, f = self.grid, self.fields
+        out = C.c_double()
+        L.check(g.ctx, g.lib.mhh_pres_check_divergence(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
+                                                       C.byref(out)), "mhh_pres_check_divergence")
+        return out.value
+
+
+class Timeloop:
+    """Timeloop (include/timeloop.h; src/timeloop.cxx): integer-nanosecond clock + low-storage RK."""
+    ifactor = 1e9
+
+    def __init__(self, grid, fields, rkorder=3, dt=0.1, dtmax=1e9, adaptivestep=True, starttime=0., endtime=1e9):
+        if rkorder not in (3, 4):
+            raise L.MhhError("rkorder must be 3 or 4")
+        self.grid, self.fields = grid, fields
+        self.rkorder, self.adaptivestep = rkorder, adaptivestep
+        self.dt, self.dtmax = dt, dtmax
+        self.substep = 0
+        self.itime = int(self.ifactor * starttime + 0.5)
+        self.iendtime = int(self.ifactor * endtime + 0.5)
+        self.idt = int(self.ifactor * dt + 0.5)
+        self.idtmax = int(self.ifactor * dtmax + 0.5)
+        self.time = starttime
+        self.iteration = 0
+
+    def in_substep(self):
+        return self.substep > 0
+
+    def get_sub_time_step(self):
+        return self.grid.lib.mhh_rk_sub_dt(self.rkorder, self.substep, C.c_double(self.dt))
+
+    def set_time_step_limit(self):
+        """src/timeloop.cxx:138-152 (no save/stat-time limits in this harness)"""
+        self.idtlim = min(self.idtmax, self.iendtime - self.itime) if self.iendtime > self.itime else self.idtmax
+
+    def set_time_step(self, *limits):
+        """src/timeloop.cxx:229-245 + src/model.cxx:731-751"""
+        if self.in_substep() or not self.adaptivestep:
+            return
+        self.set_time_step_limit()
+        idtlim = min([self.idtlim, *limits])
+        self.idt = max(int(idtlim), 1)
+        self.dt = self.idt / self.ifactor
+
+    def step_time(self):
+        """src/timeloop.cxx:160-180: advance the clock after the last substep."""
+        if self.in_substep():
+            return
+        self.itime += self.idt
+        self.time = self.itime / self.ifactor
+        self.iteration += 1
+
+    def exec(self):
+        """Timeloop::exec, src/timeloop.cxx:358-411."""
+        g, f = self.grid, self.fields
+        names = list(f.at)
+        a = L.ptr_array([f.ap[n].fld for n in names])
+        at = L.ptr_array([f.at[n].fld for n in names])
+        L.check(g.ctx, g.lib.mhh_rk_substep(g.ctx, self.rkorder, self.substep, C.c_double(self.dt), len(names), a, at),
+                "mhh_rk_substep")
+        self.substep = (self.substep + 1) % (3 if self.rkorder == 3 else 5)

@@ -1,0 +1,86 @@
+"""ctypes binding of ``libmhh_b200.so`` (the C ABI in ``include/mhh_b200.h``).
+
+There is no CPU fallback: if the shared library is missing this module raises on first use,
+and ``mhh_create`` itself fails when no CUDA device is visible.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmhh_b200.so")
+
+ADVEC_2, ADVEC_2I5, ADVEC_4 = 2, 25, 4
+BC_DIRICHLET, BC_NEUMANN, BC_FLUX, BC_USTAR, BC_OFF = 0, 1, 2, 3, 4
+BCW_NORMAL, BCW_CONSERVATION = 0, 1
+EDGE_EAST_WEST, EDGE_NORTH_SOUTH, EDGE_BOTH = 0, 1, 2
+
+
+class GridDesc(C.Structure):
+    _fields_ = [("itot", C.c_int), ("jtot", C.c_int), ("ktot", C.c_int),
+                ("igc", C.c_int), ("jgc", C.c_int), ("kgc", C.c_int),
+                ("xsize", C.c_double), ("ysize", C.c_double), ("zsize", C.c_double),
+                ("order", C.c_int), ("npy", C.c_int), ("rank_y", C.c_int)]
+
+
+class MhhError(RuntimeError):
+    pass
+
+
+_lib = None
+
+# every symbol include/mhh_b200.h declares (tests/test_abi.py checks the header against this list)
+EXPORTS = [
+    "mhh_create", "mhh_destroy", "mhh_last_error", "mhh_set_stream", "mhh_set_rhoref", "mhh_get_dims",
+    "mhh_get_metric", "mhh_get_metric_device",
+    "mhh_advec_exec", "mhh_advec_cfl", "mhh_advec_time_limit",
+    "mhh_diff2_exec", "mhh_diff4_exec", "mhh_diff_const_dnmul",
+    "mhh_smag2_exec_viscosity", "mhh_smag2_exec", "mhh_smag2_strain2", "mhh_smag2_dnmul",
+    "mhh_pres_set_values", "mhh_pres_exec", "mhh_pres_check_divergence", "mhh_pres_work", "mhh_pres_input",
+    "mhh_fft_forward", "mhh_fft_backward", "mhh_pres_solve_spectral", "mhh_pres_output", "mhh_pres_scatter",
+    "mhh_pres_get_coefs",
+    "mhh_cyclic", "mhh_cyclic_2d", "mhh_ghost_cells", "mhh_ghost_cells_w", "mhh_set_bc",
+    "mhh_rk_substep", "mhh_rk_sub_dt",
+    "mhh_mean_profile", "mhh_level_sums", "mhh_mean", "mhh_mean_2d", "mhh_max",
+    "mhh_check_momentum", "mhh_check_tke", "mhh_check_mass",
+]
+
+
+def load():
+    """Load the CUDA library or raise — never falls back to anything else."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MhhError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(the B200 path has no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    lib.mhh_last_error.restype = C.c_char_p
+    lib.mhh_pres_work.restype = C.c_void_p
+    lib.mhh_get_metric_device.restype = C.c_void_p
+    lib.mhh_rk_sub_dt.restype = C.c_double
+    lib.mhh_rk_sub_dt.argtypes = [C.c_int, C.c_int, C.c_double]
+    _lib = lib
+    return lib
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or NULL)."""
+    if t is None:
+        return C.c_void_p(0)
+    return C.c_void_p(t.data_ptr())
+
+
+def ptr_array(tensors):
+    """C array of device pointers."""
+    arr = (C.c_void_p * max(len(tensors), 1))()
+    for n, t in enumerate(tensors):
+        arr[n] = t.data_ptr() if t is not None else 0
+    return arr
+
+
+def check(ctx, err, what):
+    if err != 0:
+        msg = load().mhh_last_error(ctx).decode() if ctx else ""
+        raise MhhError(f"{what} failed with code {err}: {msg}")
