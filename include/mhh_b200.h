@@ -63,6 +63,12 @@ int mhh_get_metric(const mhh_ctx* ctx, const char* name, double* out_host);
 /* device pointer of the same arrays (for callers that launch their own kernels) */
 const double* mhh_get_metric_device(const mhh_ctx* ctx, const char* name);
 
+/* --- launch accounting and live per-kernel timing (no reference counterpart; used by bench.py) -------- */
+unsigned long long mhh_launch_count(const mhh_ctx* ctx);          /* kernels launched so far by this ctx */
+int mhh_profile_enable(mhh_ctx* ctx, int on);                     /* bracket every launch with CUDA events */
+/* Sums recorded intervals per kernel since the last report. names: ';'-joined. Returns the entry count. */
+int mhh_profile_report(mhh_ctx* ctx, char* names, int names_size, double* ms, long* counts, int max_entries);
+
 /* --- Advec<TF> (include/advec.h:54-60) ------------------------------------------------------ */
 /* Advec_2/2i5/4::exec — src/advec_2.cxx:298, src/advec_2i5.cxx:977, src/advec_4.cxx:592.
  * limit_flags[n] != 0 selects the flux-limited scalar scheme of include/advec_monotonic.h:77 (2i5 only). */
@@ -113,6 +119,14 @@ int mhh_smag2_strain2(mhh_ctx* ctx, int surface_model, const double* u, const do
                       const double* dudz, const double* dvdz, double* strain2);
 /* calc_dnmul — src/diff_smag2.cxx:712; get_dn :904 multiplies by dt, get_time_limit :884. */
 int mhh_smag2_dnmul(mhh_ctx* ctx, const double* evisc, double tPr, double* dnmul_out);
+
+/* --- Thermo_dry pieces inside the substep ---------------------------------------- */
+/* base state thref/threfh (kcells each, host): Thermo_dry::create_basestate, src/thermo_dry.cxx */
+int mhh_thermo_set_ref(mhh_ctx* ctx, const double* thref_host, const double* threfh_host);
+/* Thermo_dry::exec — calc_buoyancy_tend_2nd/4th, src/thermo_dry.cxx:165-198,459-491: wt += g/threfh*(th_h - threfh) */
+int mhh_thermo_dry_exec(mhh_ctx* ctx, double* wt, const double* th);
+/* Thermo_dry::get_thermo_field("N2") — calc_N2, src/thermo_dry.cxx:66-79 */
+int mhh_thermo_dry_N2(mhh_ctx* ctx, const double* th, double* N2);
 
 /* --- Pres<TF> (include/pres.h:48-58) --------------------------------------------------------------- */
 /* Pres_2/4::init + set_values — src/pres_2.cxx:107-153, src/pres_4.cxx:159-252. Uses ctx rhoref. */

@@ -142,11 +142,11 @@ int advec2_exec(Ctx* c, const double* u, const double* v, const double* w, doubl
 {
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    advec2_uvw_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, gd);
+    MHH_LAUNCH(c, "advec2_uvw_kernel", advec2_uvw_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, gd));
     MHH_LAUNCH_CHECK();
     for (int n = 0; n < nscalars; ++n)
     {
-        advec2_s_kernel<<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], u, v, w, gd);
+        MHH_LAUNCH(c, "advec2_s_kernel", advec2_s_kernel<<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], u, v, w, gd));
         MHH_LAUNCH_CHECK();
     }
     return MHH_OK;
@@ -157,7 +157,7 @@ int advec2_cfl_bits(Ctx* c, const double* u, const double* v, const double* w, u
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     MHH_CUDA_CHECK(cudaMemsetAsync(slot, 0, sizeof(unsigned long long), c->stream));
-    advec2_cfl_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot);
+    MHH_LAUNCH(c, "advec2_cfl_kernel", advec2_cfl_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

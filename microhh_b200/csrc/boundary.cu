@@ -178,7 +178,7 @@ int cyclic_exec_k(Ctx* c, double* fld, int edge, int nk_total, bool is2d)
     {
         const int n = gd.igc * gd.jcells;
         dim3 b(128), g((n + 127) / 128, nk_total);
-        cyclic_x_kernel<<<g, b, 0, c->stream>>>(fld, gd, nk_total);
+        MHH_LAUNCH(c, "cyclic_x_kernel", cyclic_x_kernel<<<g, b, 0, c->stream>>>(fld, gd, nk_total));
         MHH_LAUNCH_CHECK();
     }
     if (edge == 1 || edge == 2)
@@ -187,18 +187,18 @@ int cyclic_exec_k(Ctx* c, double* fld, int edge, int nk_total, bool is2d)
         if (gd.jtot > 1)
         {
             dim3 g((gd.icells + 127) / 128, gd.jgc, nk_total);
-            cyclic_y_kernel<<<g, b, 0, c->stream>>>(fld, gd);
+            MHH_LAUNCH(c, "cyclic_y_kernel", cyclic_y_kernel<<<g, b, 0, c->stream>>>(fld, gd));
         }
         else if (is2d)
         {
             // exec_2d with jtot == 1 (src/boundary_cyclic.cxx:~480): single slice
             dim3 g((gd.icells + 127) / 128, gd.jgc, 1);
-            cyclic_y_2drun_kernel<<<g, b, 0, c->stream>>>(fld, gd, 0);
+            MHH_LAUNCH(c, "cyclic_y_2drun_kernel", cyclic_y_2drun_kernel<<<g, b, 0, c->stream>>>(fld, gd, 0));
         }
         else
         {
             dim3 g((gd.icells + 127) / 128, gd.jgc, gd.kmax);
-            cyclic_y_2drun_kernel<<<g, b, 0, c->stream>>>(fld, gd, gd.kstart);
+            MHH_LAUNCH(c, "cyclic_y_2drun_kernel", cyclic_y_2drun_kernel<<<g, b, 0, c->stream>>>(fld, gd, gd.kstart));
         }
         MHH_LAUNCH_CHECK();
     }
@@ -214,9 +214,9 @@ int ghost_cells_exec(Ctx* c, double* a, int bcbot, int bctop, double* abot, doub
     const GridD& gd = c->gd;
     dim3 b(128), g((gd.icells + 127) / 128, gd.jcells);
     if (c->order == 2)
-        ghost_2nd_kernel<<<g, b, 0, c->stream>>>(a, bcbot, bctop, abot, atop, agradbot, agradtop, gd);
+        MHH_LAUNCH(c, "ghost_2nd_kernel", ghost_2nd_kernel<<<g, b, 0, c->stream>>>(a, bcbot, bctop, abot, atop, agradbot, agradtop, gd));
     else
-        ghost_4th_kernel<<<g, b, 0, c->stream>>>(a, bcbot, bctop, abot, atop, agradbot, agradtop, gd);
+        MHH_LAUNCH(c, "ghost_4th_kernel", ghost_4th_kernel<<<g, b, 0, c->stream>>>(a, bcbot, bctop, abot, atop, agradbot, agradtop, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -226,7 +226,7 @@ int ghost_cells_w_exec(Ctx* c, double* w, int type)
     if (c->order != 4) return MHH_OK;   // src/boundary.cxx:990
     const GridD& gd = c->gd;
     dim3 b(128), g((gd.icells + 127) / 128, gd.jcells);
-    ghost_w_4th_kernel<<<g, b, 0, c->stream>>>(w, type, gd);
+    MHH_LAUNCH(c, "ghost_w_4th_kernel", ghost_w_4th_kernel<<<g, b, 0, c->stream>>>(w, type, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -234,7 +234,7 @@ int ghost_cells_w_exec(Ctx* c, double* w, int type)
 int set_bc_exec(Ctx* c, double* a, double* agrad, double* aflux, int sw, double aval, double visc, double offset)
 {
     const int n = c->gd.ijcells;
-    set_bc_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(a, agrad, aflux, sw, aval, visc, offset, n);
+    MHH_LAUNCH(c, "set_bc_kernel", set_bc_kernel<<<(n + 255) / 256, 256, 0, c->stream>>>(a, agrad, aflux, sw, aval, visc, offset, n));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

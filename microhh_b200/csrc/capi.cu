@@ -11,6 +11,7 @@
 namespace mhh
 {
 // ctx.cu
+int prof_collect(Ctx*, std::vector<double>&, std::vector<long>&);
 int ctx_init_grid(Ctx*, int, int, int, int, int, int, double, double, double, int, int, int);
 int ctx_upload_metrics(Ctx*);
 int ctx_alloc_scratch(Ctx*);
@@ -46,6 +47,10 @@ int level_sums(Ctx*, const double*, double*);
 int weighted_sum(Ctx*, int, const double*, const double*, const double*, double*);
 int interior_max(Ctx*, const double*, double*);
 int plane_sum(Ctx*, const double*, double*);
+// thermo.cu
+int thermo_set_ref(Ctx*, const double*, const double*);
+int thermo_buoyancy_tend(Ctx*, double*, const double*);
+int thermo_n2(Ctx*, double*, const double*);
 // pres_2.cu / pres_4.cu
 int pres2_set_values(Ctx*);
 int pres2_input(Ctx*, const double*, const double*, const double*, const double*, const double*, const double*, double, double*);
@@ -78,10 +83,10 @@ static int fft_forward_inplace(Ctx* c, double* data)
     FftLayout L;
     L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0;
     L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.base_out = 0; L.scale = 1.;
-    if (int e = fft_lines(c->stream, c->plan_i, -1, data, data, L)) return e;
+    if (int e = fft_lines(c, c->plan_i, -1, data, data, L)) return e;
     L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
     L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
-    return fft_lines(c->stream, c->plan_j, -1, data, data, L);
+    return fft_lines(c, c->plan_j, -1, data, data, L);
 }
 
 // FFT::exec_backward (src/fft.cxx:392-448): y then x, each normalised by its length.
@@ -94,16 +99,16 @@ static int fft_backward_impl(Ctx* c, double* data, double* p)
     L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
     L.base_in = 0; L.base_out = 0;
     L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.scale = 1. / gd.jtot;
-    if (int e = fft_lines(c->stream, c->plan_j, +1, data, data, L)) return e;
+    if (int e = fft_lines(c, c->plan_j, +1, data, data, L)) return e;
     L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.scale = 1. / gd.itot;
     if (p == nullptr)
     {
         L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
-        return fft_lines(c->stream, c->plan_i, +1, data, data, L);
+        return fft_lines(c, c->plan_i, +1, data, data, L);
     }
     L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells; L.sno = 1;
     L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
-    return fft_lines(c->stream, c->plan_i, +1, data, p, L);
+    return fft_lines(c, c->plan_i, +1, data, p, L);
 }
 }  // namespace mhh
 
@@ -218,6 +223,27 @@ const double* mhh_get_metric_device(const mhh_ctx* c, const char* name)
     return nullptr;
 }
 
+// ---------------------------------------------------------------- launch accounting / live kernel timing
+unsigned long long mhh_launch_count(const mhh_ctx* c) { return c ? c->launches : 0ULL; }
+int mhh_profile_enable(mhh_ctx* c, int on) { CTX_CHECK(c); c->prof_on = on != 0; return MHH_OK; }
+int mhh_profile_report(mhh_ctx* c, char* names, int names_size, double* ms, long* counts, int max_entries)
+{
+    CTX_CHECK(c);
+    std::vector<double> t; std::vector<long> n;
+    const int k = prof_collect(c, t, n);
+    std::string joined;
+    int written = 0;
+    for (int i = 0; i < k && i < max_entries; ++i)
+    {
+        if ((int)(joined.size() + c->prof_names[i].size() + 2) > names_size) break;
+        joined += c->prof_names[i]; joined += ';';
+        ms[i] = t[i]; counts[i] = n[i];
+        ++written;
+    }
+    if (names_size > 0) { std::strncpy(names, joined.c_str(), names_size - 1); names[names_size - 1] = 0; }
+    return written;   // number of entries (>= 0)
+}
+
 // ---------------------------------------------------------------- Advec
 int mhh_advec_exec(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w,
                    double* ut, double* vt, double* wt, int ns, const double* const* s, double* const* st,
@@ -321,6 +347,11 @@ int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
     if (int e = smag2_dnmul_bits(c, evisc, tPr, c->max_bits_d + 1)) return e;
     return read_max(c, c->max_bits_d + 1, out);
 }
+
+// ---------------------------------------------------------------- Thermo_dry (next row)
+int mhh_thermo_set_ref(mhh_ctx* c, const double* thref, const double* threfh) { CTX_CHECK(c); return thermo_set_ref(c, thref, threfh); }
+int mhh_thermo_dry_exec(mhh_ctx* c, double* wt, const double* th) { CTX_CHECK(c); return thermo_buoyancy_tend(c, wt, th); }
+int mhh_thermo_dry_N2(mhh_ctx* c, const double* th, double* N2) { CTX_CHECK(c); return thermo_n2(c, N2, th); }
 
 // ---------------------------------------------------------------- Pres
 int mhh_pres_set_values(mhh_ctx* c)

@@ -164,8 +164,64 @@ int ctx_alloc_scratch(Ctx* c)
     return MHH_OK;
 }
 
+static cudaEvent_t prof_get_event(Ctx* c)
+{
+    if (!c->prof_pool.empty())
+    {
+        cudaEvent_t e = c->prof_pool.back();
+        c->prof_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
+ProfScope::ProfScope(Ctx* ctx, const char* name) : c(ctx)
+{
+    ++c->launches;
+    if (!c->prof_on) return;
+    int id = -1;
+    for (size_t n = 0; n < c->prof_names.size(); ++n)
+        if (c->prof_names[n] == name) { id = (int)n; break; }
+    if (id < 0) { id = (int)c->prof_names.size(); c->prof_names.push_back(name); }
+    Ctx::ProfEntry pe;
+    pe.id = id;
+    pe.e0 = prof_get_event(c);
+    pe.e1 = prof_get_event(c);
+    cudaEventRecord(pe.e0, c->stream);
+    e1 = pe.e1;
+    c->prof_entries.push_back(pe);
+}
+
+ProfScope::~ProfScope()
+{
+    if (e1) cudaEventRecord(e1, c->stream);
+}
+
+// Sums the recorded intervals per kernel name; returns the number of names. ms/counts sized >= names.
+int prof_collect(Ctx* c, std::vector<double>& ms, std::vector<long>& counts)
+{
+    cudaStreamSynchronize(c->stream);
+    ms.assign(c->prof_names.size(), 0.);
+    counts.assign(c->prof_names.size(), 0);
+    for (auto& pe : c->prof_entries)
+    {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, pe.e0, pe.e1);
+        ms[pe.id] += t;
+        counts[pe.id] += 1;
+        c->prof_pool.push_back(pe.e0);
+        c->prof_pool.push_back(pe.e1);
+    }
+    c->prof_entries.clear();
+    return (int)c->prof_names.size();
+}
+
 void ctx_free(Ctx* c)
 {
+    for (auto& pe : c->prof_entries) { cudaEventDestroy(pe.e0); cudaEventDestroy(pe.e1); }
+    for (auto e : c->prof_pool) cudaEventDestroy(e);
     cudaFree(c->metrics_d);
     cudaFree(c->max_bits_d);
     cudaFree(c->sum_d);
@@ -173,6 +229,7 @@ void ctx_free(Ctx* c)
     cudaFree(c->bmati_d); cudaFree(c->bmatj_d); cudaFree(c->pres_a_d); cudaFree(c->pres_c_d); cudaFree(c->bands_d);
     cudaFree(c->work_p); cudaFree(c->work_c); cudaFree(c->work_h);
     cudaFree(c->mlen0_d);
+    cudaFree(c->thref_d);
     fft_plan_destroy(&c->plan_i);
     fft_plan_destroy(&c->plan_j);
 }

@@ -56,8 +56,30 @@ struct Ctx
     double* mlen0_d = nullptr;
     double mlen0_cs = -1.;
 
+    // thermo_dry base state: thref (kcells) followed by threfh (kcells)
+    double* thref_d = nullptr;
+
+    // launch accounting / live per-kernel timing (bench.py: gpu_launches and roofline.achieved)
+    unsigned long long launches = 0;
+    bool prof_on = false;
+    std::vector<std::string> prof_names;
+    struct ProfEntry { int id; cudaEvent_t e0, e1; };
+    std::vector<ProfEntry> prof_entries;
+    std::vector<cudaEvent_t> prof_pool;
+
     std::string last_error;
 };
+
+// Counts one kernel launch; when profiling is on, brackets it with CUDA events on the launch stream.
+struct ProfScope
+{
+    Ctx* c;
+    cudaEvent_t e1 = nullptr;
+    ProfScope(Ctx* ctx, const char* name);
+    ~ProfScope();
+};
+
+#define MHH_LAUNCH(c, name, ...) do { mhh::ProfScope ps__(c, name); __VA_ARGS__; } while (0)
 
 int ctx_set_metrics(Ctx* c, const double* z_host);
 int pres_set_values(Ctx* c);

@@ -68,11 +68,11 @@ int diff2_exec(Ctx* c, const double* u, const double* v, const double* w, double
 {
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    diff2_uvw_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, visc, gd);
+    MHH_LAUNCH(c, "diff2_uvw_kernel", diff2_uvw_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, visc, gd));
     MHH_LAUNCH_CHECK();
     for (int n = 0; n < nscalars; ++n)
     {
-        diff2_c_kernel<<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], svisc[n], gd);
+        MHH_LAUNCH(c, "diff2_c_kernel", diff2_c_kernel<<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], svisc[n], gd));
         MHH_LAUNCH_CHECK();
     }
     return MHH_OK;

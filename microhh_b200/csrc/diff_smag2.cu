@@ -350,27 +350,27 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd
     if (strain_only)
     {
-        if (surface_model) evisc_kernel<true, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
-        else               evisc_kernel<false, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
         MHH_LAUNCH_CHECK();
         return MHH_OK;
     }
     if (N2 != nullptr)
     {
-        if (surface_model) evisc_kernel<true, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
-        else               evisc_kernel<false, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
     }
     else
     {
-        if (surface_model) evisc_kernel<true, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
-        else               evisc_kernel<false, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS);
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
     }
     #undef EV_ARGS
     MHH_LAUNCH_CHECK();
     if (!surface_model)
     {
         dim3 b(128), g((gd.icells + 127) / 128, gd.jcells);
-        evisc_mirror_kernel<<<g, b, 0, c->stream>>>(evisc, gd);
+        MHH_LAUNCH(c, "evisc_mirror_kernel", evisc_mirror_kernel<<<g, b, 0, c->stream>>>(evisc, gd));
         MHH_LAUNCH_CHECK();
     }
     return cyclic_exec(c, evisc, 2);
@@ -385,18 +385,18 @@ int smag2_exec(Ctx* c, int surface_model, const double* u, const double* v, cons
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     if (surface_model)
-        smag2_diff_uvw_kernel<true><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, gd);
+        MHH_LAUNCH(c, "smag2_diff_uvw_kernel", smag2_diff_uvw_kernel<true><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
+                ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, gd));
     else
-        smag2_diff_uvw_kernel<false><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                nullptr, nullptr, nullptr, nullptr, visc, gd);
+        MHH_LAUNCH(c, "smag2_diff_uvw_kernel", smag2_diff_uvw_kernel<false><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
+                nullptr, nullptr, nullptr, nullptr, visc, gd));
     MHH_LAUNCH_CHECK();
     for (int n = 0; n < nscalars; ++n)
     {
         if (surface_model)
-            smag2_diff_c_kernel<true><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, sfluxbot[n], sfluxtop[n], tPr, svisc[n], gd);
+            MHH_LAUNCH(c, "smag2_diff_c_kernel", smag2_diff_c_kernel<true><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, sfluxbot[n], sfluxtop[n], tPr, svisc[n], gd));
         else
-            smag2_diff_c_kernel<false><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, nullptr, nullptr, tPr, svisc[n], gd);
+            MHH_LAUNCH(c, "smag2_diff_c_kernel", smag2_diff_c_kernel<false><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, nullptr, nullptr, tPr, svisc[n], gd));
         MHH_LAUNCH_CHECK();
     }
     return MHH_OK;
@@ -408,7 +408,7 @@ int smag2_dnmul_bits(Ctx* c, const double* evisc, double tPr, unsigned long long
     const double tPrfac_i = 1. / std::fmin(1., tPr);
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     MHH_CUDA_CHECK(cudaMemsetAsync(slot, 0, sizeof(unsigned long long), c->stream));
-    smag2_dnmul_kernel<<<l.grid, l.block, 0, c->stream>>>(evisc, tPrfac_i, gd, slot);
+    MHH_LAUNCH(c, "smag2_dnmul_kernel", smag2_dnmul_kernel<<<l.grid, l.block, 0, c->stream>>>(evisc, tPrfac_i, gd, slot));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

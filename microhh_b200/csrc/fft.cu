@@ -269,7 +269,7 @@ void fft_plan_destroy(FftPlan* p)
     p->tw = nullptr;
 }
 
-int fft_lines(cudaStream_t stream, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L)
+int fft_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L)
 {
     FftArgs A;
     A.n = plan.n; A.nfac = plan.nfac;
@@ -298,13 +298,13 @@ int fft_lines(cudaStream_t stream, const FftPlan& plan, int dir, const double* i
     {
         static bool attr_f = false;
         if (!attr_f) { cudaFuncSetAttribute(fft_lines_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_f = true; }
-        fft_lines_kernel<-1><<<nblocks, 256, smem, stream>>>(in, out, A, lines);
+        MHH_LAUNCH(c, A.line_fast ? "fft_fwd_y" : "fft_fwd_x", fft_lines_kernel<-1><<<nblocks, 256, smem, c->stream>>>(in, out, A, lines));
     }
     else
     {
         static bool attr_b = false;
         if (!attr_b) { cudaFuncSetAttribute(fft_lines_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr_b = true; }
-        fft_lines_kernel<1><<<nblocks, 256, smem, stream>>>(in, out, A, lines);
+        MHH_LAUNCH(c, A.line_fast ? "fft_bwd_y" : "fft_bwd_x", fft_lines_kernel<1><<<nblocks, 256, smem, c->stream>>>(in, out, A, lines));
     }
     MHH_LAUNCH_CHECK();
     return MHH_OK;

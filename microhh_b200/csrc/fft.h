@@ -18,5 +18,5 @@ struct FftLayout
 int fft_plan_create(FftPlan* p, int n);
 void fft_plan_destroy(FftPlan* p);
 // dir = -1: real -> half-complex (FFTW_R2HC); +1: half-complex -> real (FFTW_HC2R); both unnormalised * scale.
-int fft_lines(cudaStream_t stream, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L);
+int fft_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L);
 }

@@ -206,7 +206,7 @@ int pres2_input(Ctx* c, const double* u, const double* v, const double* w,
 {
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    pres2_in_kernel<<<l.grid, l.block, 0, c->stream>>>(work, u, v, w, ut, vt, wt, 1. / dt, gd);
+    MHH_LAUNCH(c, "pres2_in_kernel", pres2_in_kernel<<<l.grid, l.block, 0, c->stream>>>(work, u, v, w, ut, vt, wt, 1. / dt, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -215,8 +215,8 @@ int pres2_solve_spectral(Ctx* c, double* data)
 {
     const GridD& gd = c->gd;
     dim3 b(128), g((c->iblock + 127) / 128, c->jblock);
-    pres2_tdma_kernel<<<g, b, 0, c->stream>>>(data, c->work_c, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
-                                              c->iblock, c->jblock, c->rank_y * c->iblock, 0, gd);
+    MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, b, 0, c->stream>>>(data, c->work_c, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+                                              c->iblock, c->jblock, c->rank_y * c->iblock, 0, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -225,7 +225,7 @@ int pres_scatter(Ctx* c, double* p, const double* src)
 {
     const GridD& gd = c->gd;
     dim3 b(128), g((gd.imax + 127) / 128, gd.jmax, gd.kmax);
-    pres_scatter_kernel<<<g, b, 0, c->stream>>>(p, src, gd);
+    MHH_LAUNCH(c, "pres_scatter_kernel", pres_scatter_kernel<<<g, b, 0, c->stream>>>(p, src, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -236,12 +236,12 @@ int pres2_output(Ctx* c, double* ut, double* vt, double* wt, double* p)
     const GridD& gd = c->gd;
     {
         dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
-        pres2_bottom_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd);
+        MHH_LAUNCH(c, "pres2_bottom_ghost_kernel", pres2_bottom_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
         MHH_LAUNCH_CHECK();
     }
     if (int e = cyclic_exec(c, p, 2)) return e;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    pres2_out_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd);
+    MHH_LAUNCH(c, "pres2_out_kernel", pres2_out_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -251,7 +251,7 @@ int pres2_divergence_bits(Ctx* c, const double* u, const double* v, const double
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     MHH_CUDA_CHECK(cudaMemsetAsync(slot, 0, sizeof(unsigned long long), c->stream));
-    pres2_div_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot);
+    MHH_LAUNCH(c, "pres2_div_kernel", pres2_div_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

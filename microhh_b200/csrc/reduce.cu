@@ -81,7 +81,7 @@ namespace
     template<int OP>
     int run_levels(Ctx* c, const double* a, const double* b, const double* w, int kfirst, int nk)
     {
-        level_reduce_kernel<OP><<<nk, 256, 0, c->stream>>>(c->sum_d, a, b, w, c->gd, kfirst);
+        MHH_LAUNCH(c, "level_reduce_kernel", level_reduce_kernel<OP><<<nk, 256, 0, c->stream>>>(c->sum_d, a, b, w, c->gd, kfirst));
         MHH_LAUNCH_CHECK();
         MHH_CUDA_CHECK(cudaMemcpyAsync(c->host_pinned, c->sum_d, nk * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
         MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -127,7 +127,7 @@ int interior_max(Ctx* c, const double* a, double* out)
 
 int plane_sum(Ctx* c, const double* a2d, double* out)
 {
-    plane_sum_kernel<<<1, 256, 0, c->stream>>>(c->sum_d, a2d, c->gd);
+    MHH_LAUNCH(c, "plane_sum_kernel", plane_sum_kernel<<<1, 256, 0, c->stream>>>(c->sum_d, a2d, c->gd));
     MHH_LAUNCH_CHECK();
     MHH_CUDA_CHECK(cudaMemcpyAsync(c->host_pinned, c->sum_d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));

@@ -1,0 +1,80 @@
+// Thermo_dry pieces that sit inside the dynamical-core substep:
+// buoyancy tendency on w (src/thermo_dry.cxx:165-198) and N2 = g/thref * dth/dz (:66-79), the
+// stability input of Diff_smag2::exec_viscosity (src/diff_smag2.cxx:1143).
+#include "ctx.h"
+
+namespace mhh
+{
+namespace
+{
+    constexpr int KCHUNK = 32;
+    constexpr double kGrav = 9.81;   // Constants::grav
+
+    template<int ORDER>
+    __global__ void __launch_bounds__(256)
+    buoyancy_tend_kernel(double* __restrict__ wt, const double* __restrict__ th, const double* __restrict__ threfh, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        if (i >= gd.iend || j >= gd.jend) return;
+        const int kk = gd.ijcells;
+        const int k0 = max(gd.kstart + (int)blockIdx.z * KCHUNK, gd.kstart + 1);
+        const int k1 = min(gd.kstart + ((int)blockIdx.z + 1) * KCHUNK, gd.kend);
+        for (int k = k0; k < k1; ++k)
+        {
+            const int ijk = i + j * gd.icells + k * kk;
+            if (ORDER == 2)
+                wt[ijk] += kGrav / threfh[k] * (fd::interp2(th[ijk - kk], th[ijk]) - threfh[k]);
+            else
+                wt[ijk] += kGrav / threfh[k] * (fd::interp4c(th[ijk - 2 * kk], th[ijk - kk], th[ijk], th[ijk + kk]) - threfh[k]);
+        }
+    }
+
+    __global__ void __launch_bounds__(256)
+    n2_kernel(double* __restrict__ N2, const double* __restrict__ th, const double* __restrict__ thref, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        if (i >= gd.iend || j >= gd.jend) return;
+        const int kk = gd.ijcells;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        for (int k = k0; k < k1; ++k)
+        {
+            const int ijk = i + j * gd.icells + k * kk;
+            N2[ijk] = kGrav / thref[k] * 0.5 * (th[ijk + kk] - th[ijk - kk]) * gd.dzi[k];
+        }
+    }
+}  // namespace
+
+int thermo_set_ref(Ctx* c, const double* thref, const double* threfh)
+{
+    const int kcells = c->gd.kcells;
+    if (!c->thref_d) MHH_CUDA_CHECK(cudaMalloc(&c->thref_d, sizeof(double) * 2 * kcells));
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    MHH_CUDA_CHECK(cudaMemcpy(c->thref_d, thref, sizeof(double) * kcells, cudaMemcpyHostToDevice));
+    MHH_CUDA_CHECK(cudaMemcpy(c->thref_d + kcells, threfh, sizeof(double) * kcells, cudaMemcpyHostToDevice));
+    return MHH_OK;
+}
+
+int thermo_buoyancy_tend(Ctx* c, double* wt, const double* th)
+{
+    if (!c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
+    const GridD& gd = c->gd;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    if (c->order == 2) MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<2><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, gd));
+    else               MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<4><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, gd));
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+int thermo_n2(Ctx* c, double* N2, const double* th)
+{
+    if (!c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
+    const GridD& gd = c->gd;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    MHH_LAUNCH(c, "n2_kernel", n2_kernel<<<l.grid, l.block, 0, c->stream>>>(N2, th, c->thref_d, gd));
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+}  // namespace mhh

@@ -75,7 +75,7 @@ int rk_substep(Ctx* c, int rkorder, int substep, double dt, int nfields, double*
         const int nf = nfields - f0 < MAXF ? nfields - f0 : MAXF;
         for (int f = 0; f < nf; ++f) { tab.a[f] = a[f0 + f]; tab.at[f] = at[f0 + f]; }
         dim3 b(256), g((gd.ncells + 255) / 256, nf);
-        rk_kernel<<<g, b, 0, c->stream>>>(tab, cB_dt, cA_next, substepn == 0, gd);
+        MHH_LAUNCH(c, "rk_kernel", rk_kernel<<<g, b, 0, c->stream>>>(tab, cB_dt, cA_next, substepn == 0, gd));
         MHH_LAUNCH_CHECK();
     }
     return MHH_OK;

@@ -62,6 +62,22 @@ class Grid:
         L.check(self.ctx, self.lib.mhh_set_rhoref(self.ctx, rhoref.ctypes.data_as(C.c_void_p),
                                                   rhorefh.ctypes.data_as(C.c_void_p)), "mhh_set_rhoref")
 
+    # launch accounting / live per-kernel CUDA-event timing (bench.py)
+    def launch_count(self):
+        return int(self.lib.mhh_launch_count(self.ctx))
+
+    def profile_enable(self, on=True):
+        L.check(self.ctx, self.lib.mhh_profile_enable(self.ctx, 1 if on else 0), "mhh_profile_enable")
+
+    def profile_report(self):
+        """{kernel name: (total ms, launches)} since the last report."""
+        names = C.create_string_buffer(8192)
+        ms = (C.c_double * 256)()
+        cnt = (C.c_long * 256)()
+        n = self.lib.mhh_profile_report(self.ctx, names, 8192, ms, cnt, 256)
+        keys = [k for k in names.value.decode().split(";") if k]
+        return {keys[i]: (ms[i], int(cnt[i])) for i in range(min(n, len(keys)))}
+
     def zeros(self):
         return torch.zeros(self.shape, dtype=torch.float64, device=self.device)
 

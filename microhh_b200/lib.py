@@ -34,9 +34,11 @@ _lib = None
 EXPORTS = [
     "mhh_create", "mhh_destroy", "mhh_last_error", "mhh_set_stream", "mhh_set_rhoref", "mhh_get_dims",
     "mhh_get_metric", "mhh_get_metric_device",
+    "mhh_launch_count", "mhh_profile_enable", "mhh_profile_report",
     "mhh_advec_exec", "mhh_advec_cfl", "mhh_advec_time_limit",
     "mhh_diff2_exec", "mhh_diff4_exec", "mhh_diff_const_dnmul",
     "mhh_smag2_exec_viscosity", "mhh_smag2_exec", "mhh_smag2_strain2", "mhh_smag2_dnmul",
+    "mhh_thermo_set_ref", "mhh_thermo_dry_exec", "mhh_thermo_dry_N2",
     "mhh_pres_set_values", "mhh_pres_exec", "mhh_pres_check_divergence", "mhh_pres_work", "mhh_pres_input",
     "mhh_fft_forward", "mhh_fft_backward", "mhh_pres_solve_spectral", "mhh_pres_output", "mhh_pres_scatter",
     "mhh_pres_get_coefs",
@@ -59,6 +61,7 @@ def load():
     lib.mhh_last_error.restype = C.c_char_p
     lib.mhh_pres_work.restype = C.c_void_p
     lib.mhh_get_metric_device.restype = C.c_void_p
+    lib.mhh_launch_count.restype = C.c_ulonglong
     lib.mhh_rk_sub_dt.restype = C.c_double
     lib.mhh_rk_sub_dt.argtypes = [C.c_int, C.c_int, C.c_double]
     _lib = lib

@@ -1,0 +1,115 @@
+"""Thermo (dry) and the in-scope part of Model::exec's time loop, on top of ``microhh_b200.host``."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import lib as L
+from .host import Advec, Boundary, Diff, Fields, Grid, Pres, Timeloop
+
+
+class Thermo:
+    """Thermo_dry pieces inside the substep (src/thermo_dry.cxx): buoyancy tendency and N2.
+    swthermo in {"0", "dry"}; Boussinesq base state thref = threfh = thref0 (swbasestate=boussinesq)."""
+
+    def __init__(self, grid, fields, swthermo="dry", thref0=300., thref=None, threfh=None):
+        self.grid, self.fields, self.swthermo = grid, fields, swthermo
+        if swthermo not in ("0", "dry"):
+            raise L.MhhError(f"{swthermo} is an illegal value for swthermo (this path supports 0 and dry)")
+        if swthermo == "dry":
+            self.thref = np.full(grid.kcells, thref0) if thref is None else np.ascontiguousarray(thref, dtype=np.float64)
+            self.threfh = np.full(grid.kcells, thref0) if threfh is None else np.ascontiguousarray(threfh, dtype=np.float64)
+            L.check(grid.ctx, grid.lib.mhh_thermo_set_ref(grid.ctx, self.thref.ctypes.data_as(C.c_void_p),
+                                                          self.threfh.ctypes.data_as(C.c_void_p)), "mhh_thermo_set_ref")
+            self._n2 = grid.zeros()
+
+    def get_switch(self):
+        return self.swthermo
+
+    def exec(self, dt=None, stats=None):
+        if self.swthermo == "0":
+            return
+        g, f = self.grid, self.fields
+        L.check(g.ctx, g.lib.mhh_thermo_dry_exec(g.ctx, L.ptr(f.mt["w"].fld), L.ptr(f.sp["th"].fld)), "mhh_thermo_dry_exec")
+
+    def get_thermo_field(self, name):
+        if name != "N2":
+            raise L.MhhError("only N2 is provided on this path")
+        g, f = self.grid, self.fields
+        L.check(g.ctx, g.lib.mhh_thermo_dry_N2(g.ctx, L.ptr(f.sp["th"].fld), L.ptr(self._n2)), "mhh_thermo_dry_N2")
+        return self._n2
+
+
+class Model:
+    """The in-scope part of Model::exec's time loop (src/model.cxx:336-545), one call per RK substep.
+
+    ``ini`` is a dict of dicts with the reference's .ini blocks/keys ([grid], [advec], [diff], [pres],
+    [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
+    (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
+
+    def __init__(self, ini, z, device=None, surface=None):
+        gi = ini["grid"]
+        order = str(gi.get("swspatialorder", "2"))
+        swadvec = str(ini.get("advec", {}).get("swadvec", order))
+        gc = (0, 0, 0)
+        if swadvec == "2i5":
+            gc = (3, 3, 2 if ini.get("advec", {}).get("fluxlimit_list") else 1)   # src/advec_2i5.cxx:42-45
+        self.grid = Grid(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z,
+                         swspatialorder=order, gc=gc, device=device)
+        fi = ini.get("fields", {})
+        slist = list(fi.get("slist", []))
+        th = ini.get("thermo", {})
+        swthermo = str(th.get("swthermo", "0"))
+        if swthermo == "dry" and "th" not in slist:
+            slist = ["th"] + slist
+        self.fields = Fields(self.grid, slist=slist, visc=fi.get("visc", 0.), svisc=fi.get("svisc", 0.))
+        bi = ini.get("boundary", {})
+        self.boundary = Boundary(self.grid, self.fields, mbcbot=bi.get("mbcbot", "noslip"), mbctop=bi.get("mbctop", "noslip"),
+                                 ubot=bi.get("ubot", 0.), utop=bi.get("utop", 0.), vbot=bi.get("vbot", 0.), vtop=bi.get("vtop", 0.),
+                                 sbc=bi.get("sbc"), swboundary=bi.get("swboundary", "default"))
+        ai = ini.get("advec", {})
+        self.advec = Advec.factory(self.grid, self.fields, swadvec, cflmax=ai.get("cflmax", 1.0),
+                                   fluxlimit_list=ai.get("fluxlimit_list", ()))
+        di = ini.get("diff", {})
+        self.diff = Diff.factory(self.grid, self.fields, self.boundary, str(di.get("swdiff", order)), dnmax=di.get("dnmax", 0.4),
+                                 cs=di.get("cs", 0.23), tPr=di.get("tPr", 1. / 3.))
+        self.pres = Pres.factory(self.grid, self.fields, str(ini.get("pres", {}).get("swpres", order)))
+        self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
+        ti = ini.get("time", {})
+        self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
+                                 dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True))
+        self.surface = surface or {}
+        self.boundary.set_values()
+        self.pres.set_values()
+        self.diff.create()
+
+    def exec_substep(self):
+        b, tl = self.boundary, self.timeloop
+        b.set_prognostic_cyclic_bcs()                      # src/model.cxx:346
+        b.set_ghost_cells()                                # :348
+        self.diff.exec_viscosity(self.thermo, surface=self.surface)   # :354
+        if not tl.in_substep() and tl.adaptivestep:        # set_time_step, :357 -> :731-751
+            tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
+        self.thermo.exec()                                 # :366
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :387
+        self.advec.exec()                                  # :388
+        b.set_ghost_cells_w(L.BCW_NORMAL)                  # :389
+        self.diff.exec()                                   # :392
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
+        self.pres.exec(tl.get_sub_time_step())             # :411
+        b.set_ghost_cells_w(L.BCW_NORMAL)                  # :412
+        tl.exec()                                          # :484
+        tl.step_time()                                     # :487
+
+    def step(self):
+        """One full time step = 3 (RK3) or 5 (RK4) substeps."""
+        for _ in range(3 if self.timeloop.rkorder == 3 else 5):
+            self.exec_substep()
+
+    def print_status(self):
+        """The observables of the <case>.out line (src/model.cxx:801-828)."""
+        tl = self.timeloop
+        return dict(iter=tl.iteration, time=tl.time, dt=tl.dt, cfl=self.advec.get_cfl(tl.dt), dn=self.diff.get_dn(tl.dt),
+                    div=self.pres.check_divergence(), mom=self.fields.check_momentum(), tke=self.fields.check_tke(),
+                    mass=self.fields.check_mass())
