@@ -145,6 +145,7 @@ int mhh_pres_check_divergence(mhh_ctx* ctx, const double* u, const double* v, co
 double* mhh_pres_work(mhh_ctx* ctx);
 int mhh_pres_input(mhh_ctx* ctx, const double* u, const double* v, const double* w,
                    double* ut, double* vt, double* wt, double dt);
+int mhh_fft_force_generic(mhh_ctx* ctx, int on);   /* tests: use the mixed-radix kernel even for 2^k sizes */
 int mhh_fft_forward(mhh_ctx* ctx, double* data);
 int mhh_fft_backward(mhh_ctx* ctx, double* data);      /* normalised by 1/(itot*jtot), in place */
 int mhh_pres_solve_spectral(mhh_ctx* ctx, double* data);

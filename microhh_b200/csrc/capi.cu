@@ -402,6 +402,7 @@ int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w
     return pres4_input(c, u, v, w, ut, vt, wt, dt, c->work_p);
 }
 
+int mhh_fft_force_generic(mhh_ctx* c, int on) { CTX_CHECK(c); c->fft_force_generic = on != 0; return MHH_OK; }
 int mhh_fft_forward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_forward_inplace(c, data); }
 int mhh_fft_backward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_backward_impl(c, data, nullptr); }
 

@@ -18,6 +18,12 @@ struct FftPlan
     int nfac = 0;
     int fac[20];
     double2* tw = nullptr;   // device, n entries exp(-2 pi i k/n)
+    // register-resident power-of-two path (fft_pow2.cu): radices in {8,4,2}, per-stage twiddle tables
+    // laid out [r-1][k] (k < ns) so that consecutive lanes read consecutive entries
+    int p2_nst = 0;
+    int p2_rad[8];
+    int p2_off[8];
+    double2* p2_tw = nullptr;
 };
 
 struct Ctx
@@ -41,6 +47,7 @@ struct Ctx
     // pressure solver
     bool pres_ready = false;
     FftPlan plan_i, plan_j;
+    bool fft_force_generic = false;   // tests: exercise the mixed-radix kernel on power-of-two sizes too
     double* bmati_d = nullptr;
     double* bmatj_d = nullptr;
     double* pres_a_d = nullptr;     // pres_2: a, c ; pres_4: m1..m7 (7*kmax)

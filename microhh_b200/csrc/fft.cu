@@ -242,6 +242,10 @@ namespace
     }
 }  // namespace
 
+bool fft_pow2_supported(int n);
+int fft_pow2_plan(FftPlan* p);
+int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L);
+
 int fft_plan_create(FftPlan* p, int n)
 {
     p->n = n;
@@ -260,13 +264,15 @@ int fft_plan_create(FftPlan* p, int n)
     }
     MHH_CUDA_CHECK(cudaMalloc(&p->tw, sizeof(double2) * n));
     MHH_CUDA_CHECK(cudaMemcpy(p->tw, tw.data(), sizeof(double2) * n, cudaMemcpyHostToDevice));
-    return MHH_OK;
+    return fft_pow2_plan(p);
 }
 
 void fft_plan_destroy(FftPlan* p)
 {
     if (p->tw) cudaFree(p->tw);
+    if (p->p2_tw) cudaFree(p->p2_tw);
     p->tw = nullptr;
+    p->p2_tw = nullptr;
 }
 
 int fft_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L)
@@ -281,6 +287,7 @@ int fft_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* ou
     A.line_fast = (L.sn != 1);
     A.scale = L.scale;
     if (L.nlines == 0) return MHH_OK;
+    if (plan.p2_nst > 0 && !c->fft_force_generic) return fft_pow2_lines(c, plan, dir, in, out, L);
     if (plan.n == 1)
     {
         // length-1 transform = identity (2-D runs, jtot == 1): only scale / relayout

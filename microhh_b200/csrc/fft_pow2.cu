@@ -1,0 +1,404 @@
+// Register-resident power-of-two real <-> half-complex line FFTs (the fast path behind fft_lines).
+//
+// Same semantics as fft.cu (FFTW R2HC / HC2R, two real lines per complex transform), different
+// execution shape, chosen after the first B200 measurement (profiles/r01_*: the generic kernel
+// ran at 7 % of HBM peak, bound by index arithmetic, 5 radix-4/2 stages and bank conflicts):
+//   * N = 8^a 4^b 2^c: radix-8 stages first, every thread owns 8 complex values in registers and
+//     ALWAYS reads the same 8 shared-memory slots tf + m*N/8 (Stockham autosort, one buffer,
+//     read -> sync -> write -> sync), so a 512-point transform takes 3 exchanges, not 5;
+//   * all index arithmetic is shifts/masks; twiddles come from per-stage tables laid out [r][k]
+//     so consecutive lanes read consecutive entries (L1-resident, __ldg);
+//   * one slot of padding per 8 keeps the stride-8 writes of the first stage conflict-free;
+//   * contiguous (x) transforms load their inputs straight into registers and store the result
+//     straight from registers (the backward pass scatters into the ghost-celled pressure field);
+//     strided (y) transforms stage a [n][line] tile through the same buffer so that global
+//     accesses stay coalesced along i.
+#include <cmath>
+#include <vector>
+
+#include "ctx.h"
+#include "fft.h"
+
+namespace mhh
+{
+namespace
+{
+    constexpr int BLOCK = 256;
+    constexpr double kS = 0.70710678118654752440;
+
+    struct P2Args
+    {
+        int n, log2n, nst;
+        int rad[8];
+        int off[8];
+        const double2* tw;
+        int nlines, n1;
+        long s1, s2, sn, base_in;
+        int n1o;
+        long s1o, s2o, sno, base_out;
+        double scale;
+    };
+
+    __device__ __forceinline__ double2 cmul(double2 a, double2 b)
+    { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+    __device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+    __device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+    template<int DIR> __device__ __forceinline__ double2 rot(double2 a)      // * (-i) fwd, * (+i) bwd
+    { return DIR < 0 ? make_double2(a.y, -a.x) : make_double2(-a.y, a.x); }
+    template<int DIR> __device__ __forceinline__ double2 w8_1(double2 a)     // * W8^1
+    { return DIR < 0 ? make_double2(kS * (a.x + a.y), kS * (a.y - a.x)) : make_double2(kS * (a.x - a.y), kS * (a.x + a.y)); }
+    template<int DIR> __device__ __forceinline__ double2 w8_3(double2 a)     // * W8^3
+    { return DIR < 0 ? make_double2(kS * (a.y - a.x), kS * (-a.x - a.y)) : make_double2(kS * (-a.x - a.y), kS * (a.x - a.y)); }
+    template<int DIR> __device__ __forceinline__ double2 ldtw(const double2* __restrict__ t, int idx)
+    {
+        const double2 w = __ldg(t + idx);
+        return DIR < 0 ? w : make_double2(w.x, -w.y);
+    }
+
+    __device__ __forceinline__ int pad(int n) { return n + (n >> 3); }
+
+    // DFT of size R on v[b + NB*r] (r < R), NB = 8/R butterflies interleaved in the 8 registers.
+    template<int DIR> __device__ __forceinline__ void dft8(double2* v)
+    {
+        const double2 b0 = cadd(v[0], v[4]), b4 = csub(v[0], v[4]);
+        const double2 b1 = cadd(v[1], v[5]), b5 = w8_1<DIR>(csub(v[1], v[5]));
+        const double2 b2 = cadd(v[2], v[6]), b6 = rot<DIR>(csub(v[2], v[6]));
+        const double2 b3 = cadd(v[3], v[7]), b7 = w8_3<DIR>(csub(v[3], v[7]));
+        const double2 c0 = cadd(b0, b2), c2 = csub(b0, b2), c1 = cadd(b1, b3), c3 = rot<DIR>(csub(b1, b3));
+        const double2 c4 = cadd(b4, b6), c6 = csub(b4, b6), c5 = cadd(b5, b7), c7 = rot<DIR>(csub(b5, b7));
+        v[0] = cadd(c0, c1); v[4] = csub(c0, c1); v[2] = cadd(c2, c3); v[6] = csub(c2, c3);
+        v[1] = cadd(c4, c5); v[5] = csub(c4, c5); v[3] = cadd(c6, c7); v[7] = csub(c6, c7);
+    }
+    template<int DIR> __device__ __forceinline__ void dft4(double2& v0, double2& v1, double2& v2, double2& v3)
+    {
+        const double2 a = cadd(v0, v2), b = csub(v0, v2), c = cadd(v1, v3), d = rot<DIR>(csub(v1, v3));
+        v0 = cadd(a, c); v2 = csub(a, c); v1 = cadd(b, d); v3 = csub(b, d);
+    }
+
+    // One Stockham stage of radix R at sub-transform length ns (log2 = lns): twiddle, butterfly,
+    // and scatter of the 8 register values to their output slots in z (this pair's buffer).
+    template<int R, int DIR>
+    __device__ __forceinline__ void stage(double2* v, double2* __restrict__ z, const double2* __restrict__ tw,
+                                          const int tf, const int n8, const int lns, const bool first)
+    {
+        constexpr int NB = 8 / R;
+        const int ns = 1 << lns;
+        #pragma unroll
+        for (int b = 0; b < NB; ++b)
+        {
+            const int j = tf + b * n8;
+            const int k = j & (ns - 1);
+            if (!first)
+            {
+                #pragma unroll
+                for (int r = 1; r < R; ++r)
+                    v[b + NB * r] = cmul(v[b + NB * r], ldtw<DIR>(tw, (r - 1) * ns + k));
+            }
+        }
+        if (R == 8) dft8<DIR>(v);
+        else if (R == 4) { dft4<DIR>(v[0], v[2], v[4], v[6]); dft4<DIR>(v[1], v[3], v[5], v[7]); }
+        else
+        {
+            #pragma unroll
+            for (int b = 0; b < 4; ++b)
+            {
+                const double2 a = v[b], c = v[b + 4];
+                v[b] = cadd(a, c); v[b + 4] = csub(a, c);
+            }
+        }
+        #pragma unroll
+        for (int b = 0; b < NB; ++b)
+        {
+            const int j = tf + b * n8;
+            const int k = j & (ns - 1);
+            const int j0 = ((j >> lns) << lns) * R + k;
+            #pragma unroll
+            for (int q = 0; q < R; ++q)
+                z[pad(j0 + (q << lns))] = v[b + NB * q];
+        }
+    }
+
+    // Runs all stages. On return the transform is in registers in "position order": v[m] is element
+    // tf + m*N/8 of the result (the last stage's output slots coincide with the read slots).
+    template<int DIR>
+    __device__ __forceinline__ void run(double2* v, double2* __restrict__ z, const P2Args& A, const int tf)
+    {
+        const int n8 = A.n >> 3;
+        int lns = 0;
+        for (int s = 0; s < A.nst; ++s)
+        {
+            const int R = A.rad[s];
+            const bool last = (s == A.nst - 1);
+            if (last)
+            {
+                // twiddle + butterfly only; outputs stay in registers (slot of v[b+NB*q] is tf + (b+NB*q)*N/8)
+                const int ns = 1 << lns;
+                const double2* tw = A.tw + A.off[s];
+                if (R == 8)
+                {
+                    if (s > 0) { const int k = tf & (ns - 1);
+                        #pragma unroll
+                        for (int r = 1; r < 8; ++r) v[r] = cmul(v[r], ldtw<DIR>(tw, (r - 1) * ns + k)); }
+                    dft8<DIR>(v);
+                }
+                else if (R == 4)
+                {
+                    #pragma unroll
+                    for (int b = 0; b < 2; ++b)
+                    {
+                        const int k = (tf + b * n8) & (ns - 1);
+                        if (s > 0) {
+                            #pragma unroll
+                            for (int r = 1; r < 4; ++r) v[b + 2 * r] = cmul(v[b + 2 * r], ldtw<DIR>(tw, (r - 1) * ns + k)); }
+                    }
+                    dft4<DIR>(v[0], v[2], v[4], v[6]); dft4<DIR>(v[1], v[3], v[5], v[7]);
+                }
+                else
+                {
+                    #pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                    {
+                        const int k = (tf + b * n8) & (ns - 1);
+                        if (s > 0) v[b + 4] = cmul(v[b + 4], ldtw<DIR>(tw, k));
+                        const double2 a = v[b], c = v[b + 4];
+                        v[b] = cadd(a, c); v[b + 4] = csub(a, c);
+                    }
+                }
+            }
+            else
+            {
+                if (s > 0) __syncthreads();      // everyone has read its inputs of this stage
+                const double2* tw = A.tw + A.off[s];
+                if (R == 8) stage<8, DIR>(v, z, tw, tf, n8, lns, s == 0);
+                else if (R == 4) stage<4, DIR>(v, z, tw, tf, n8, lns, s == 0);
+                else stage<2, DIR>(v, z, tw, tf, n8, lns, s == 0);
+                __syncthreads();
+                #pragma unroll
+                for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8)];
+            }
+            lns += (R == 8) ? 3 : (R == 4 ? 2 : 1);
+        }
+    }
+
+    __device__ __forceinline__ long line_addr(int l, int n1, long s1, long s2)
+    {
+        return (long)(l % n1) * s1 + (long)(l / n1) * s2;
+    }
+
+    // DIR = -1: real lines -> half-complex; +1: half-complex -> real lines (unnormalised * scale).
+    // STRIDED: element stride sn != 1 (lines adjacent in memory): stage tiles through shared memory.
+    template<int DIR, bool STRIDED>
+    __global__ void __launch_bounds__(BLOCK)
+    fft_pow2_kernel(const double* __restrict__ in, double* __restrict__ out, const P2Args A)
+    {
+        extern __shared__ double2 zbuf[];
+        const int n = A.n, n8 = n >> 3, nh = n >> 1;
+        const int tfn = n8;                              // threads per complex transform
+        const int npairs = BLOCK / tfn;                  // complex transforms per CTA
+        const int lines = 2 * npairs;
+        const int NP = pad(n) + 1;                       // slots per pair (odd skew between pairs)
+        const int p = threadIdx.x / tfn;
+        const int tf = threadIdx.x - p * tfn;
+        double2* z = zbuf + p * NP;
+        double* zr = reinterpret_cast<double*>(zbuf);
+        const int l0 = blockIdx.x * lines;
+        const int la = l0 + 2 * p, lb = la + 1;
+        const bool va = la < A.nlines, vb = lb < A.nlines;
+        double2 v[8];
+
+        // ---------------- load ----------------
+        if (STRIDED || DIR > 0)
+        {
+            // cooperative, coalesced tile load: slot n of pair q holds (line 2q elem n, line 2q+1 elem n)
+            const int total = lines * n;
+            for (int t = threadIdx.x; t < total; t += BLOCK)
+            {
+                int ll, m;
+                if (STRIDED) { ll = t % lines; m = t / lines; }
+                else         { m = t & (n - 1); ll = t >> A.log2n; }
+                const int l = l0 + ll;
+                double val = 0.;
+                if (l < A.nlines) val = in[A.base_in + line_addr(l, A.n1, A.s1, A.s2) + (long)m * A.sn];
+                zr[2 * ((ll >> 1) * NP + pad(m)) + (ll & 1)] = val;
+            }
+            __syncthreads();
+            if (DIR < 0)
+            {
+                #pragma unroll
+                for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8)];
+            }
+            else
+            {
+                // Z_n = A_n + i B_n rebuilt from the two half-complex lines
+                #pragma unroll
+                for (int m = 0; m < 8; ++m)
+                {
+                    const int pos = tf + m * n8;
+                    const int np = pos <= nh ? pos : n - pos;
+                    const bool self = (np == 0) || (np == nh);
+                    const double s = pos <= nh ? 1. : -1.;
+                    const double2 re = z[pad(np)];
+                    const double2 im = self ? make_double2(0., 0.) : z[pad(n - np)];
+                    v[m] = make_double2(re.x - s * im.y, s * im.x + re.y);
+                }
+            }
+            __syncthreads();
+        }
+        else
+        {
+            const double* pa = in + A.base_in + line_addr(va ? la : 0, A.n1, A.s1, A.s2);
+            const double* pb = in + A.base_in + line_addr(vb ? lb : 0, A.n1, A.s1, A.s2);
+            #pragma unroll
+            for (int m = 0; m < 8; ++m)
+            {
+                const int pos = tf + m * n8;
+                v[m] = make_double2(va ? pa[pos] : 0., vb ? pb[pos] : 0.);
+            }
+        }
+
+        run<DIR>(v, z, A, tf);
+
+        // ---------------- store ----------------
+        if (DIR > 0)
+        {
+            if (!STRIDED)
+            {
+                double* qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
+                double* qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
+                #pragma unroll
+                for (int m = 0; m < 8; ++m)
+                {
+                    const int pos = tf + m * n8;
+                    if (va) qa[pos] = v[m].x * A.scale;
+                    if (vb) qb[pos] = v[m].y * A.scale;
+                }
+                return;
+            }
+            __syncthreads();
+            #pragma unroll
+            for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
+            __syncthreads();
+        }
+        else
+        {
+            // result to natural order in shared memory, then the Hermitian split
+            if (A.nst > 1) __syncthreads();
+            #pragma unroll
+            for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
+            __syncthreads();
+            double* qa = nullptr; double* qb = nullptr;
+            if (!STRIDED)
+            {
+                qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
+                qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
+            }
+            // k = tf + m*n8 for m < 4 covers 0..n/2-1; thread 0 also does k = n/2
+            #pragma unroll
+            for (int m = 0; m < 5; ++m)
+            {
+                if (m == 4 && tf != 0) break;
+                const int k = (m == 4) ? nh : tf + m * n8;
+                const int kn = (k == 0) ? 0 : n - k;
+                const double2 zk = z[pad(k)], zn = z[pad(kn)];
+                const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
+                const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
+                const bool has_im = (k > 0) && (k < nh);
+                if (!STRIDED)
+                {
+                    if (va) { qa[k] = are * A.scale; if (has_im) qa[n - k] = aim * A.scale; }
+                    if (vb) { qb[k] = bre * A.scale; if (has_im) qb[n - k] = bim * A.scale; }
+                }
+                else
+                {
+                    z[pad(k)] = make_double2(are, bre);
+                    if (has_im) z[pad(n - k)] = make_double2(aim, bim);
+                }
+            }
+            if (!STRIDED) return;
+            __syncthreads();
+        }
+        // cooperative coalesced tile store (STRIDED only)
+        {
+            const int total = lines * n;
+            for (int t = threadIdx.x; t < total; t += BLOCK)
+            {
+                const int ll = t % lines, m = t / lines;
+                const int l = l0 + ll;
+                if (l < A.nlines)
+                    out[A.base_out + line_addr(l, A.n1o, A.s1o, A.s2o) + (long)m * A.sno]
+                        = zr[2 * ((ll >> 1) * NP + pad(m)) + (ll & 1)] * A.scale;
+            }
+        }
+    }
+}  // namespace
+
+bool fft_pow2_supported(int n) { return n >= 8 && n <= 8 * BLOCK && (n & (n - 1)) == 0; }
+
+int fft_pow2_plan(FftPlan* p)
+{
+    const int n = p->n;
+    if (!fft_pow2_supported(n)) return MHH_OK;
+    int m = n, nst = 0;
+    while (m % 8 == 0 && m > 1) { p->p2_rad[nst++] = 8; m /= 8; }
+    if (m == 4) { p->p2_rad[nst++] = 4; m = 1; }
+    if (m == 2) { p->p2_rad[nst++] = 2; m = 1; }
+    p->p2_nst = nst;
+    std::vector<double2> tw;
+    const long double pi = std::acos(-1.0L);
+    int ns = 1;
+    for (int s = 0; s < nst; ++s)
+    {
+        const int R = p->p2_rad[s];
+        p->p2_off[s] = (int)tw.size();
+        for (int r = 1; r < R; ++r)
+            for (int k = 0; k < ns; ++k)
+            {
+                const long double ang = -2.0L * pi * (long double)k * (long double)r / ((long double)ns * R);
+                tw.push_back(make_double2((double)std::cos(ang), (double)std::sin(ang)));
+            }
+        ns *= R;
+    }
+    MHH_CUDA_CHECK(cudaMalloc(&p->p2_tw, sizeof(double2) * tw.size()));
+    MHH_CUDA_CHECK(cudaMemcpy(p->p2_tw, tw.data(), sizeof(double2) * tw.size(), cudaMemcpyHostToDevice));
+    return MHH_OK;
+}
+
+int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* out, const FftLayout& L)
+{
+    P2Args A;
+    A.n = plan.n; A.nst = plan.p2_nst;
+    A.log2n = 0; while ((1 << A.log2n) < plan.n) ++A.log2n;
+    for (int s = 0; s < plan.p2_nst; ++s) { A.rad[s] = plan.p2_rad[s]; A.off[s] = plan.p2_off[s]; }
+    A.tw = plan.p2_tw;
+    A.nlines = L.nlines; A.n1 = L.n1; A.s1 = L.s1; A.s2 = L.s2; A.sn = L.sn; A.base_in = L.base_in;
+    A.n1o = L.n1o; A.s1o = L.s1o; A.s2o = L.s2o; A.sno = L.sno; A.base_out = L.base_out;
+    A.scale = L.scale;
+    const bool strided = (L.sn != 1) || (L.sno != 1);
+    const int npairs = BLOCK / (plan.n / 8);
+    const int lines = 2 * npairs;
+    const size_t smem = (size_t)npairs * ((plan.n + plan.n / 8) + 1) * sizeof(double2);
+    const int nblocks = (L.nlines + lines - 1) / lines;
+    static bool attr = false;
+    if (!attr)
+    {
+        cudaFuncSetAttribute(fft_pow2_kernel<-1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<-1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        attr = true;
+    }
+    if (dir < 0)
+    {
+        if (strided) MHH_LAUNCH(c, "fft_fwd_y", fft_pow2_kernel<-1, true><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+        else         MHH_LAUNCH(c, "fft_fwd_x", fft_pow2_kernel<-1, false><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+    }
+    else
+    {
+        if (strided) MHH_LAUNCH(c, "fft_bwd_y", fft_pow2_kernel<1, true><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+        else         MHH_LAUNCH(c, "fft_bwd_x", fft_pow2_kernel<1, false><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+    }
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+}  // namespace mhh
