@@ -13,9 +13,9 @@ using fd::interp2;
 
 namespace
 {
-    constexpr int KCHUNK = 32;
+    constexpr int KCHUNK = MHH_KCHUNK;
 
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     advec2_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                       const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                       const GridD gd)
@@ -32,6 +32,12 @@ namespace
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * jj + k * kk;
+            if (k + MHH_PF < gd.kcells - 1)
+            {
+                const int pf = ijk + (MHH_PF + 1) * kk;
+                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
+                prefetch_l2(ut + pf - kk); prefetch_l2(vt + pf - kk); prefetch_l2(wt + pf - kk);
+            }
             const double rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k], rho = gd.rhoref[k], dzi = gd.dzi[k];
 
             const double u_c = u[ijk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
@@ -73,7 +79,7 @@ namespace
         }
     }
 
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     advec2_s_kernel(double* __restrict__ st, const double* __restrict__ s,
                     const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                     const GridD gd)
@@ -92,6 +98,11 @@ namespace
         double w_c = w[ijk];
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
+            if (k + MHH_PF < gd.kcells - 1)
+            {
+                const int pf = ijk + (MHH_PF + 1) * kk;
+                prefetch_l2(s + pf); prefetch_l2(w + pf); prefetch_l2(u + pf - kk); prefetch_l2(v + pf - kk); prefetch_l2(st + pf - kk);
+            }
             const double s_t = s[ijk + kk];
             const double w_t = w[ijk + kk];
             // advec_s, src/advec_2.cxx:191-202
@@ -107,7 +118,7 @@ namespace
     }
 
     // calc_cfl, src/advec_2.cxx:51-78, fused with the max reduction.
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     advec2_cfl_kernel(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                       const GridD gd, unsigned long long* __restrict__ out)
     {

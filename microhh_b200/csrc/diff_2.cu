@@ -5,7 +5,7 @@ namespace mhh
 {
 namespace
 {
-    constexpr int KCHUNK = 32;
+    constexpr int KCHUNK = MHH_KCHUNK;
 
     // diff_c, src/diff_2.cxx:39-62
     __device__ __forceinline__ double lap_c(const double* __restrict__ a, int ijk, int jj, int kk,
@@ -18,7 +18,7 @@ namespace
                 + ( (a[ijk + kk] - a[ijk]) * dzhi_t - (a[ijk] - a[ijk - kk]) * dzhi_c ) * dzi_c );
     }
 
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     diff2_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                      const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                      const double visc, const GridD gd)
@@ -45,7 +45,7 @@ namespace
         }
     }
 
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     diff2_c_kernel(double* __restrict__ at, const double* __restrict__ a, const double visc, const GridD gd)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;

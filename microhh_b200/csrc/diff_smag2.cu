@@ -14,7 +14,7 @@ namespace mhh
 {
 namespace
 {
-    constexpr int KCHUNK = 32;
+    constexpr int KCHUNK = MHH_KCHUNK;
 
     __device__ __forceinline__ double pow2(double x) { return x * x; }
 
@@ -72,7 +72,7 @@ namespace
 
     // MODE 0: thermo on (calc_evisc), 1: neutral (calc_evisc_neutral), 2: strain2 only (stage test)
     template<bool SURF, int MODE>
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
@@ -106,6 +106,12 @@ namespace
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = ij + k * kk;
+            if (k + MHH_PF < gd.kcells - 1)
+            {
+                const int pf = ijk + (MHH_PF + 1) * kk;
+                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
+                if (MODE == 0) prefetch_l2(N2 + pf - kk);
+            }
             const bool bot = SURF && (k == gd.kstart);
             const double s2 = bot
                 ? strain2_at<true>(u, v, w, ijk, jj, kk, dxi, dyi, gd.dzi[k], 0., 0., dudz[ij], dvdz[ij])
@@ -162,7 +168,7 @@ namespace
     }
 
     template<bool SURF>
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     smag2_diff_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                           const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                           const double* __restrict__ evisc,
@@ -182,6 +188,12 @@ namespace
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = ij + k * kk;
+            if (k + MHH_PF < gd.kcells - 1)
+            {
+                const int pf = ijk + (MHH_PF + 1) * kk;
+                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf); prefetch_l2(evisc + pf);
+                prefetch_l2(ut + pf - kk); prefetch_l2(vt + pf - kk); prefetch_l2(wt + pf - kk);
+            }
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
             const double rho = gd.rhoref[k], rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k];
@@ -257,7 +269,7 @@ namespace
 
     // diff_c, src/diff_smag2.cxx:620-708
     template<bool SURF>
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     smag2_diff_c_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
                         const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
                         const double tPr, const double visc, const GridD gd)
@@ -276,6 +288,11 @@ namespace
         double e_b = evisc[ijk - kk], e_c = evisc[ijk];
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
+            if (k + MHH_PF < gd.kcells - 1)
+            {
+                const int pf = ijk + (MHH_PF + 1) * kk;
+                prefetch_l2(a + pf); prefetch_l2(evisc + pf); prefetch_l2(at + pf - kk);
+            }
             const double a_t = a[ijk + kk], e_t = evisc[ijk + kk];
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
@@ -301,7 +318,7 @@ namespace
     }
 
     // calc_dnmul, src/diff_smag2.cxx:712-735, fused with the max reduction
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     smag2_dnmul_kernel(const double* __restrict__ evisc, const double tPrfac_i, const GridD gd,
                        unsigned long long* __restrict__ out)
     {

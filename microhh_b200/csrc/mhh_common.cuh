@@ -10,6 +10,15 @@
 #include <cstdio>
 #include <vector>
 
+// minimum resident CTAs per SM requested from ptxas for the 256-thread stencil kernels
+#ifndef MHH_MINB
+#define MHH_MINB 4
+#endif
+// k levels marched by one thread of the stencil kernels
+#ifndef MHH_KCHUNK
+#define MHH_KCHUNK 32
+#endif
+
 namespace mhh
 {
 
@@ -132,6 +141,18 @@ __device__ __forceinline__ double block_sum(double v)
             v += __shfl_down_sync(0xffffffffu, v, o);
     }
     return v;
+}
+
+// L2 prefetch of the line a later k iteration will need (hides DRAM latency of the k-marching loops:
+// ncu showed every stencil kernel stalled on long_scoreboard, profiles/r01a_*).
+#ifndef MHH_PF
+#define MHH_PF 1
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p)
+{
+#if MHH_PF > 0
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+#endif
 }
 
 // ---- finite-difference helpers (restated from include/finite_difference.h:34-156) ----------

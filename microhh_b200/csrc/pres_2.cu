@@ -19,10 +19,10 @@ int cyclic_exec(Ctx* c, double* fld, int edge);
 
 namespace
 {
-    constexpr int KCHUNK = 32;
+    constexpr int KCHUNK = MHH_KCHUNK;
 
     // Pres_2::input, src/pres_2.cxx:183-195
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     pres2_in_kernel(double* __restrict__ p, const double* __restrict__ u, const double* __restrict__ v,
                     const double* __restrict__ w, const double* __restrict__ ut, const double* __restrict__ vt,
                     const double* __restrict__ wt, const double dti, const GridD gd)
@@ -87,6 +87,7 @@ namespace
         p[ij] = pprev;
         for (int k = 1; k < kmax; ++k)
         {
+            if (k + 4 < kmax) prefetch_l2(p + ij + (k + 4) * kk);
             const double w3 = c[k - 1] / work2d;
             work3d[ij + k * kk] = w3;
             work2d = bdiag(k) - a[k] * w3;
@@ -98,6 +99,7 @@ namespace
         }
         for (int k = kmax - 2; k >= 0; --k)
         {
+            if (k >= 4) { prefetch_l2(p + ij + (k - 4) * kk); prefetch_l2(work3d + ij + (k - 3) * kk); }
             double pk = p[ij + k * kk];
             pk -= work3d[ij + (k + 1) * kk] * pprev;
             p[ij + k * kk] = pk;
@@ -126,7 +128,7 @@ namespace
     }
 
     // Pres_2::output, src/pres_2.cxx:365-387
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     pres2_out_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                      const double* __restrict__ p, const GridD gd)
     {
@@ -150,7 +152,7 @@ namespace
     }
 
     // Pres_2::calc_divergence, src/pres_2.cxx:391-422
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     pres2_div_kernel(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                      const GridD gd, unsigned long long* __restrict__ out)
     {

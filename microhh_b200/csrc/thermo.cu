@@ -7,11 +7,11 @@ namespace mhh
 {
 namespace
 {
-    constexpr int KCHUNK = 32;
+    constexpr int KCHUNK = MHH_KCHUNK;
     constexpr double kGrav = 9.81;   // Constants::grav
 
     template<int ORDER>
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     buoyancy_tend_kernel(double* __restrict__ wt, const double* __restrict__ th, const double* __restrict__ threfh, const GridD gd)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
@@ -30,7 +30,7 @@ namespace
         }
     }
 
-    __global__ void __launch_bounds__(256)
+    __global__ void __launch_bounds__(256, MHH_MINB)
     n2_kernel(double* __restrict__ N2, const double* __restrict__ th, const double* __restrict__ thref, const GridD gd)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
