@@ -150,6 +150,21 @@ int mhh_fft_forward(mhh_ctx* ctx, double* data);
 int mhh_fft_backward(mhh_ctx* ctx, double* data);      /* normalised by 1/(itot*jtot), in place */
 int mhh_pres_solve_spectral(mhh_ctx* ctx, double* data);
 int mhh_pres_output(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p);
+/* y-slab (multi-GPU) stages. Layouts: X = [k][j<jmax][i<itot] (slab), Y = [k][j<jtot][ii<iblock];
+ * transpose modes: 0 X->chunks, 1 chunks->Y (Transpose::exec_xy, src/transpose.cxx:163-190),
+ *                  2 Y->chunks, 3 chunks->X (Transpose::exec_yx, :191-217); chunk r = [k][j<jmax][ii<iblock].
+ * The all-to-all between pack and unpack is the host's (NCCL over NVLink). dir: -1 forward, +1 backward. */
+int mhh_pres_input_to(mhh_ctx* ctx, const double* u, const double* v, const double* w, const double* ut,
+                      const double* vt, const double* wt, double dt, double* dst_X);
+int mhh_fft_x(mhh_ctx* ctx, int dir, double* data_X, double* p_or_null);
+int mhh_fft_y(mhh_ctx* ctx, int dir, double* data_Y);
+int mhh_transpose_copy(mhh_ctx* ctx, int mode, double* dst, const double* src);
+int mhh_pres_solve_spectral_ws(mhh_ctx* ctx, double* data_Y, double* work3d);
+int mhh_pres_output_stage(mhh_ctx* ctx, int stage, double* ut, double* vt, double* wt, double* p);
+/* north/south halo rows of a ghosted field <-> [k][g<jgc][i<icells] buffers (Boundary_cyclic MPI path,
+ * src/boundary_cyclic.cxx:139-174). unpack=0: north<-rows [jend-jgc,jend), south<-rows [jstart,jstart+jgc);
+ * unpack=1: rows [jend,jend+jgc)<-north buffer, rows [0,jgc)<-south buffer. */
+int mhh_halo_ns(mhh_ctx* ctx, double* fld, double* north_buf, double* south_buf, int unpack, int is2d);
 int mhh_pres_scatter(mhh_ctx* ctx, double* p, const double* ghost_free_src);   /* src/pres_2.cxx:340-348 */
 /* copies bmati(itot), bmatj(jtot) and a,c (kmax each; order 2) or m1..m7 (7*kmax; order 4) to host */
 int mhh_pres_get_coefs(const mhh_ctx* ctx, double* bmati, double* bmatj, double* a_or_bands, double* c);

@@ -169,10 +169,12 @@ namespace
 int cyclic_exec_k(Ctx* c, double* fld, int edge, int nk_total, bool is2d)
 {
     const GridD& gd = c->gd;
+    // On a y-slab rank (npy > 1) only the east/west part is local; the north/south rows are the
+    // caller's halo exchange (mhh_halo_ns + NCCL send/recv), done AFTER this call so corners are right.
     if (c->npy != 1)
     {
-        c->last_error = "mhh_cyclic: north/south halos of a y-slab rank need the multi-GPU halo exchange";
-        if (edge != 0) return MHH_ERR_STATE;
+        if (edge == 1) return MHH_OK;
+        edge = 0;
     }
     if (edge == 0 || edge == 2)
     {

@@ -75,41 +75,54 @@ static int read_max(Ctx* c, unsigned long long* slot, double* out)
     return MHH_OK;
 }
 
-// FFT::exec_forward (src/fft.cxx:335-389): x lines then y lines, in place.
-static int fft_forward_inplace(Ctx* c, double* data)
+// FFT stages (src/fft.cxx:335-448 serial, :452-583 MPI). x lines live in the slab layout
+// X = [k][j<jmax][i<itot]; y lines in Y = [k][j<jtot][ii<iblock] (identical when npy == 1).
+static int fft_x(Ctx* c, int dir, double* data, double* p)
 {
     const GridD& gd = c->gd;
-    if (c->npy != 1) return MHH_ERR_STATE;
     FftLayout L;
-    L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0;
-    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.base_out = 0; L.scale = 1.;
-    if (int e = fft_lines(c, c->plan_i, -1, data, data, L)) return e;
-    L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
+    L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0; L.base_out = 0;
     L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
-    return fft_lines(c, c->plan_j, -1, data, data, L);
+    L.scale = dir < 0 ? 1. : 1. / gd.itot;
+    if (dir > 0 && p != nullptr)
+    {
+        // scatter straight into the ghost-celled pressure field (replaces src/pres_2.cxx:340-348)
+        L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells; L.sno = 1;
+        L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
+        return fft_lines(c, c->plan_i, +1, data, p, L);
+    }
+    return fft_lines(c, c->plan_i, dir, data, data, L);
 }
 
-// FFT::exec_backward (src/fft.cxx:392-448): y then x, each normalised by its length.
-// If p != nullptr the x pass scatters into the ghost-celled array p instead of `data`.
-static int fft_backward_impl(Ctx* c, double* data, double* p)
+static int fft_y(Ctx* c, int dir, double* data)
 {
     const GridD& gd = c->gd;
-    if (c->npy != 1) return MHH_ERR_STATE;
     FftLayout L;
     L.nlines = c->iblock * gd.kmax; L.n1 = c->iblock; L.s1 = 1; L.s2 = (long)c->iblock * gd.jtot; L.sn = c->iblock;
     L.base_in = 0; L.base_out = 0;
-    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.scale = 1. / gd.jtot;
-    if (int e = fft_lines(c, c->plan_j, +1, data, data, L)) return e;
-    L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.scale = 1. / gd.itot;
-    if (p == nullptr)
-    {
-        L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
-        return fft_lines(c, c->plan_i, +1, data, data, L);
-    }
-    L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells; L.sno = 1;
-    L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
-    return fft_lines(c, c->plan_i, +1, data, p, L);
+    L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn;
+    L.scale = dir < 0 ? 1. : 1. / gd.jtot;
+    return fft_lines(c, c->plan_j, dir, data, data, L);
 }
+
+static int fft_forward_inplace(Ctx* c, double* data)
+{
+    if (c->npy != 1) return MHH_ERR_STATE;
+    if (int e = fft_x(c, -1, data, nullptr)) return e;
+    return fft_y(c, -1, data);
+}
+
+static int fft_backward_impl(Ctx* c, double* data, double* p)
+{
+    if (c->npy != 1) return MHH_ERR_STATE;
+    if (int e = fft_y(c, +1, data)) return e;
+    return fft_x(c, +1, data, p);
+}
+// slab.cu
+int transpose_copy(Ctx*, int, double*, const double*);
+int halo_ns(Ctx*, double*, double*, double*, int, int);
+int pres2_solve_spectral_ws(Ctx*, double*, double*);
+int pres2_output_stage(Ctx*, int, double*, double*, double*, double*);
 }  // namespace mhh
 
 using namespace mhh;
@@ -375,7 +388,7 @@ int mhh_pres_set_values(mhh_ctx* c)
     if ((e = upload(&c->pres_c_d, c->pres_c))) return e;
     if ((e = upload(&c->bands_d, c->bands))) return e;
     const size_t n = (size_t)gd.imax * gd.jmax * gd.kmax;
-    if (!c->work_p)
+    if (!c->work_p && c->npy == 1)
     {
         MHH_CUDA_CHECK(cudaMalloc(&c->work_p, sizeof(double) * n));
         MHH_CUDA_CHECK(cudaMalloc(&c->work_c, sizeof(double) * n));
@@ -402,6 +415,14 @@ int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w
     return pres4_input(c, u, v, w, ut, vt, wt, dt, c->work_p);
 }
 
+// Pres_2::input into a caller-supplied ghost-free array (y-slab driver); halos of ut/vt are the caller's.
+int mhh_pres_input_to(mhh_ctx* c, const double* u, const double* v, const double* w, const double* ut, const double* vt,
+                      const double* wt, double dt, double* dst)
+{
+    PRES_READY(c);
+    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    return pres2_input(c, u, v, w, ut, vt, wt, dt, dst);
+}
 int mhh_fft_force_generic(mhh_ctx* c, int on) { CTX_CHECK(c); c->fft_force_generic = on != 0; return MHH_OK; }
 int mhh_fft_forward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_forward_inplace(c, data); }
 int mhh_fft_backward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_backward_impl(c, data, nullptr); }
@@ -416,6 +437,25 @@ int mhh_pres_output(mhh_ctx* c, double* ut, double* vt, double* wt, double* p)
 {
     PRES_READY(c);
     return c->order == 2 ? pres2_output(c, ut, vt, wt, p) : pres4_output(c, ut, vt, wt, p);
+}
+
+// ---- y-slab stages (multi-GPU driver): see microhh_b200/multigpu.py for the call order
+int mhh_fft_x(mhh_ctx* c, int dir, double* data, double* p_or_null) { PRES_READY(c); return fft_x(c, dir, data, p_or_null); }
+int mhh_fft_y(mhh_ctx* c, int dir, double* data) { PRES_READY(c); return fft_y(c, dir, data); }
+int mhh_transpose_copy(mhh_ctx* c, int mode, double* dst, const double* src) { CTX_CHECK(c); return transpose_copy(c, mode, dst, src); }
+int mhh_halo_ns(mhh_ctx* c, double* fld, double* north, double* south, int unpack, int is2d)
+{ CTX_CHECK(c); return halo_ns(c, fld, north, south, unpack, is2d ? 1 : c->gd.kcells); }
+int mhh_pres_solve_spectral_ws(mhh_ctx* c, double* data, double* work3d)
+{
+    PRES_READY(c);
+    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    return pres2_solve_spectral_ws(c, data, work3d);
+}
+int mhh_pres_output_stage(mhh_ctx* c, int stage, double* ut, double* vt, double* wt, double* p)
+{
+    PRES_READY(c);
+    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    return pres2_output_stage(c, stage, ut, vt, wt, p);
 }
 
 int mhh_pres_scatter(mhh_ctx* c, double* p, const double* src) { CTX_CHECK(c); return pres_scatter(c, p, src); }

@@ -213,15 +213,17 @@ int pres2_input(Ctx* c, const double* u, const double* v, const double* w,
     return MHH_OK;
 }
 
-int pres2_solve_spectral(Ctx* c, double* data)
+int pres2_solve_spectral_ws(Ctx* c, double* data, double* work3d)
 {
     const GridD& gd = c->gd;
     dim3 b(128), g((c->iblock + 127) / 128, c->jblock);
-    MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, b, 0, c->stream>>>(data, c->work_c, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+    MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, b, 0, c->stream>>>(data, work3d, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
                                               c->iblock, c->jblock, c->rank_y * c->iblock, 0, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
+
+int pres2_solve_spectral(Ctx* c, double* data) { return pres2_solve_spectral_ws(c, data, c->work_c); }
 
 int pres_scatter(Ctx* c, double* p, const double* src)
 {
@@ -232,16 +234,26 @@ int pres_scatter(Ctx* c, double* p, const double* src)
     return MHH_OK;
 }
 
+int pres2_output_stage(Ctx* c, int stage, double* ut, double* vt, double* wt, double* p);
+
 // p already holds the interior (scattered); finish ghost rows/halos and apply the gradient.
 int pres2_output(Ctx* c, double* ut, double* vt, double* wt, double* p)
 {
+    if (int e = pres2_output_stage(c, 0, ut, vt, wt, p)) return e;
+    return pres2_output_stage(c, 1, ut, vt, wt, p);
+}
+
+// stage 0: bottom ghost row + cyclic halos (east/west only on a y-slab rank); stage 1: gradient.
+int pres2_output_stage(Ctx* c, int stage, double* ut, double* vt, double* wt, double* p)
+{
     const GridD& gd = c->gd;
+    if (stage == 0)
     {
         dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
         MHH_LAUNCH(c, "pres2_bottom_ghost_kernel", pres2_bottom_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
         MHH_LAUNCH_CHECK();
     }
-    if (int e = cyclic_exec(c, p, 2)) return e;
+    if (stage == 0) return cyclic_exec(c, p, 2);
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     MHH_LAUNCH(c, "pres2_out_kernel", pres2_out_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd));
     MHH_LAUNCH_CHECK();

@@ -48,7 +48,7 @@ class Model:
     [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
     (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
 
-    def __init__(self, ini, z, device=None, surface=None):
+    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0):
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
@@ -56,7 +56,7 @@ class Model:
         if swadvec == "2i5":
             gc = (3, 3, 2 if ini.get("advec", {}).get("fluxlimit_list") else 1)   # src/advec_2i5.cxx:42-45
         self.grid = Grid(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z,
-                         swspatialorder=order, gc=gc, device=device)
+                         swspatialorder=order, gc=gc, device=device, npy=npy, rank_y=rank_y)
         fi = ini.get("fields", {})
         slist = list(fi.get("slist", []))
         th = ini.get("thermo", {})
@@ -110,6 +110,8 @@ class Model:
     def print_status(self):
         """The observables of the <case>.out line (src/model.cxx:801-828)."""
         tl = self.timeloop
+        for fld in self.fields.mp.values():      # halos are refreshed before the status line (src/model.cxx:346,360)
+            self.boundary.boundary_cyclic.exec(fld.fld)
         return dict(iter=tl.iteration, time=tl.time, dt=tl.dt, cfl=self.advec.get_cfl(tl.dt), dn=self.diff.get_dn(tl.dt),
                     div=self.pres.check_divergence(), mom=self.fields.check_momentum(), tke=self.fields.check_tke(),
                     mass=self.fields.check_mass())

@@ -1,0 +1,187 @@
+"""y-slab multi-GPU driver: one process per GPU, ``torch.distributed`` (NCCL over NVLink).
+
+Decomposition = the reference's MPI layout with npx = 1, npy = N (src/grid.cxx:142-150):
+  * stencil phases: north/south halo rows exchanged with the two ring neighbours
+    (Boundary_cyclic MPI path, src/boundary_cyclic.cxx:139-174); east/west wrap stays local;
+  * Poisson solve: x FFT local -> all-to-all (Transpose::exec_xy) -> y FFT + tridiagonal solve local
+    -> inverse y FFT -> all-to-all (exec_yx) -> inverse x FFT  (src/fft.cxx:452-583 with npx = 1);
+  * CFL / dnmul / divergence maxima and means: all-reduce (Master::max/sum, src/master_parallel.cxx:233-256).
+
+``SlabComm`` is pure ``torch.distributed`` (tested with gloo on CPU, world_size 2); the pack/unpack around
+each collective are CUDA kernels of libmhh_b200 (``mhh_transpose_copy``, ``mhh_halo_ns``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import lib as L
+from .host import Boundary_cyclic, Pres
+from .model import Model
+
+
+class SlabComm:
+    """Ring neighbours, halo send/recv, all-to-all and reductions for ``world`` y-slabs."""
+
+    def __init__(self, rank, world, group=None):
+        self.rank, self.world, self.group = rank, world, group
+        self.north = (rank + 1) % world      # holds rows j >= my jend   (MPI nnorth)
+        self.south = (rank - 1) % world      # holds rows j <  my jstart (MPI nsouth)
+
+    def halo_exchange(self, to_north, to_south, from_south, from_north):
+        """Send my top interior rows north and bottom interior rows south; receive the matching ghosts."""
+        if self.world == 1:
+            from_south.copy_(to_north)
+            from_north.copy_(to_south)
+            return
+        ops = [dist.P2POp(dist.isend, to_north, self.north, self.group),
+               dist.P2POp(dist.irecv, from_south, self.south, self.group),
+               dist.P2POp(dist.isend, to_south, self.south, self.group),
+               dist.P2POp(dist.irecv, from_north, self.north, self.group)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+    def all_to_all(self, out, inp):
+        """Equal chunks, chunk r of ``inp`` goes to rank r (Transpose::exec_xy / exec_yx)."""
+        if self.world == 1:
+            out.copy_(inp)
+        else:
+            dist.all_to_all_single(out, inp, group=self.group)
+
+    def allreduce_max(self, value, device):
+        t = torch.tensor([value], dtype=torch.float64, device=device)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return float(t.item())
+
+    def allreduce_sum(self, value, device):
+        t = torch.as_tensor(value, dtype=torch.float64, device=device).reshape(-1).clone()
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t
+
+
+class SlabBoundaryCyclic(Boundary_cyclic):
+    """Boundary_cyclic on a y-slab rank: east/west local, north/south through the ring neighbours."""
+
+    def __init__(self, grid, comm):
+        super().__init__(grid)
+        self.comm = comm
+        n3 = grid.kcells * grid.jgc * grid.icells
+        mk = lambda n: torch.empty(n, dtype=torch.float64, device=grid.device)
+        self.to_n, self.to_s, self.from_s, self.from_n = mk(n3), mk(n3), mk(n3), mk(n3)
+
+    def _ns(self, fld, is2d):
+        g = self.grid
+        n = (1 if is2d else g.kcells) * g.jgc * g.icells
+        L.check(g.ctx, g.lib.mhh_halo_ns(g.ctx, L.ptr(fld), L.ptr(self.to_n), L.ptr(self.to_s), 0, int(is2d)), "mhh_halo_ns pack")
+        self.comm.halo_exchange(self.to_n[:n], self.to_s[:n], self.from_s[:n], self.from_n[:n])
+        L.check(g.ctx, g.lib.mhh_halo_ns(g.ctx, L.ptr(fld), L.ptr(self.from_n), L.ptr(self.from_s), 1, int(is2d)), "mhh_halo_ns unpack")
+
+    def exec(self, fld, edge=L.EDGE_BOTH):
+        g = self.grid
+        if edge in (L.EDGE_EAST_WEST, L.EDGE_BOTH):
+            L.check(g.ctx, g.lib.mhh_cyclic(g.ctx, L.ptr(fld), L.EDGE_EAST_WEST), "mhh_cyclic")
+        if edge in (L.EDGE_NORTH_SOUTH, L.EDGE_BOTH) and g.jtot > 1:
+            self._ns(fld, False)
+
+    def exec_2d(self, fld2d):
+        g = self.grid
+        L.check(g.ctx, g.lib.mhh_cyclic_2d(g.ctx, L.ptr(fld2d)), "mhh_cyclic_2d")
+        if g.jtot > 1:
+            self._ns(fld2d, True)
+
+
+class SlabPres(Pres):
+    """Pres_2 on y-slabs: the stage calls of the C ABI with the two all-to-alls in between."""
+
+    def __init__(self, grid, fields, swpres, comm, cyclic):
+        super().__init__(grid, fields, swpres)
+        if swpres != "2":
+            raise L.MhhError("the y-slab pressure pipeline is built for swpres=2 this round")
+        self.comm, self.cyclic = comm, cyclic
+        n = grid.imax * grid.jmax * grid.kmax
+        self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
+        self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
+
+    def exec(self, dt, stats=None):
+        g, f, lib = self.grid, self.fields, self.grid.lib
+        u, v, w = (f.mp[n].fld for n in "uvw")
+        ut, vt, wt = (f.mt[n].fld for n in "uvw")
+        p = f.sd["p"].fld
+        A, B = L.ptr(self.A), L.ptr(self.B)
+        ck = lambda err, what: L.check(g.ctx, err, what)
+        # Pres_2::input: halos of the tendencies first (src/pres_2.cxx:180-181)
+        self.cyclic.exec(ut, L.EDGE_EAST_WEST)
+        self.cyclic.exec(vt, L.EDGE_NORTH_SOUTH)
+        ck(lib.mhh_pres_input_to(g.ctx, L.ptr(u), L.ptr(v), L.ptr(w), L.ptr(ut), L.ptr(vt), L.ptr(wt), C.c_double(dt), A), "pres_input")
+        # forward: x FFT, exec_xy, y FFT (src/fft.cxx:452-516 with npx = 1)
+        ck(lib.mhh_fft_x(g.ctx, -1, A, None), "fft_x fwd")
+        ck(lib.mhh_transpose_copy(g.ctx, 0, B, A), "pack xy")
+        self.comm.all_to_all(self.A, self.B)
+        ck(lib.mhh_transpose_copy(g.ctx, 1, B, A), "unpack xy")
+        ck(lib.mhh_fft_y(g.ctx, -1, B), "fft_y fwd")
+        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, B, A), "tdma")
+        # backward: y FFT, exec_yx, x FFT scattering into the ghost-celled p (src/fft.cxx:519-583)
+        ck(lib.mhh_fft_y(g.ctx, +1, B), "fft_y bwd")
+        ck(lib.mhh_transpose_copy(g.ctx, 2, A, B), "pack yx")
+        self.comm.all_to_all(self.B, self.A)
+        ck(lib.mhh_transpose_copy(g.ctx, 3, A, B), "unpack yx")
+        ck(lib.mhh_fft_x(g.ctx, +1, A, L.ptr(p)), "fft_x bwd")
+        # Pres_2::solve tail + output (src/pres_2.cxx:352-387)
+        ck(lib.mhh_pres_output_stage(g.ctx, 0, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p)), "pres_output 0")
+        self.cyclic.exec(p, L.EDGE_NORTH_SOUTH)
+        ck(lib.mhh_pres_output_stage(g.ctx, 1, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p)), "pres_output 1")
+
+    def check_divergence(self):
+        return self.comm.allreduce_max(super().check_divergence(), self.grid.device)
+
+
+class SlabModel(Model):
+    """Model on one y-slab of an npy = world decomposition."""
+
+    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None):
+        super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank)
+        self.comm = SlabComm(rank, world, group)
+        self.cyclic = SlabBoundaryCyclic(self.grid, self.comm)
+        self.boundary.boundary_cyclic = self.cyclic
+        self.pres = SlabPres(self.grid, self.fields, self.pres.swpres, self.comm, self.cyclic)
+
+    def exec_substep(self):
+        b, tl, dev = self.boundary, self.timeloop, self.grid.device
+        b.set_prognostic_cyclic_bcs()
+        b.set_ghost_cells()
+        self.diff.exec_viscosity(self.thermo, surface=self.surface)
+        if self.diff.swdiff == "smag2":
+            self.cyclic.exec(self.fields.sd["evisc"].fld, L.EDGE_NORTH_SOUTH)   # east/west was done inside the call
+        if not tl.in_substep() and tl.adaptivestep:
+            cfl = max(self.advec.cflmin, self.comm.allreduce_max(self.advec.get_cfl(tl.dt), dev))
+            lim = [int(tl.idt * self.advec.cflmax / cfl)]
+            if self.diff.swdiff != "0":
+                dnmul = self.comm.allreduce_max(self.diff._dnmul(), dev)
+                dnmul = max(1.e-9, dnmul) if self.diff.swdiff == "smag2" else dnmul
+                lim.append(int(tl.idt * self.diff.dnmax / (tl.dt * dnmul)))
+            tl.set_time_step(*lim)
+        self.thermo.exec()
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)
+        self.advec.exec()
+        b.set_ghost_cells_w(L.BCW_NORMAL)
+        self.diff.exec()
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)
+        self.pres.exec(tl.get_sub_time_step())
+        b.set_ghost_cells_w(L.BCW_NORMAL)
+        tl.exec()
+        tl.step_time()
+
+    def print_status(self):
+        g, f, tl, dev = self.grid, self.fields, self.timeloop, self.grid.device
+        for fld in f.mp.values():
+            self.cyclic.exec(fld.fld)
+        # per-rank sums are already divided by the GLOBAL itot*jtot*zsize inside the library
+        sums = self.comm.allreduce_sum([f.check_momentum(), f.check_tke(), f.check_mass()], dev).tolist()
+        return dict(iter=tl.iteration, time=tl.time, dt=tl.dt,
+                    cfl=self.comm.allreduce_max(self.advec.get_cfl(tl.dt), dev),
+                    dn=self.comm.allreduce_max(self.diff.get_dn(tl.dt), dev),
+                    div=self.pres.check_divergence(), mom=sums[0], tke=sums[1], mass=sums[2])
