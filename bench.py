@@ -120,7 +120,28 @@ def measured_hbm_peak():
 
 
 # ------------------------------------------------------------------------------------------------------
+class quiet_stdout:
+    """The reference's Master/FFT print status lines to stdout (src/master_serial.cxx, src/fft.cxx);
+    bench.py must print exactly ONE JSON line, so fd 1 points at /dev/null while reference code runs."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *exc):
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        os.close(self.null)
+
+
 def cpu_reference_run(n, steps, warmup):
+    with quiet_stdout():
+        return _cpu_reference_run(n, steps, warmup)
+
+
+def _cpu_reference_run(n, steps, warmup):
     """The reference's own CPU code (oracle/_ref, 1 thread: its non-MPI build is single-threaded,
     src/model.cxx:325) on a bounded n^3 sample of the same LES configuration."""
     from oracle.les import OracleLES
