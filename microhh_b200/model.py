@@ -78,7 +78,8 @@ class Model:
         self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
-                                 dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True))
+                                 dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True),
+                                 starttime=ti.get("starttime", 0.), endtime=ti.get("endtime", 1e9))
         self.surface = surface or {}
         self.boundary.set_values()
         self.pres.set_values()
@@ -112,6 +113,9 @@ class Model:
         tl = self.timeloop
         for fld in self.fields.mp.values():      # halos are refreshed before the status line (src/model.cxx:346,360)
             self.boundary.boundary_cyclic.exec(fld.fld)
+        self.boundary.set_ghost_cells_w(L.BCW_CONSERVATION)     # src/model.cxx:815-817
+        div = self.pres.check_divergence()
+        self.boundary.set_ghost_cells_w(L.BCW_NORMAL)
         return dict(iter=tl.iteration, time=tl.time, dt=tl.dt, cfl=self.advec.get_cfl(tl.dt), dn=self.diff.get_dn(tl.dt),
-                    div=self.pres.check_divergence(), mom=self.fields.check_momentum(), tke=self.fields.check_tke(),
+                    div=div, mom=self.fields.check_momentum(), tke=self.fields.check_tke(),
                     mass=self.fields.check_mass())

@@ -17,10 +17,12 @@ class OracleLES:
     def __init__(self, itot, jtot, ktot, xsize, ysize, zsize, z, fields, *, swadvec="2", swdiff="smag2", order=2,
                  visc=1e-5, svisc=1e-5, cs=0.23, tPr=1. / 3., thref0=300., swthermo="dry", surface=None,
                  mbcbot="freeslip", mbctop="freeslip", sbc=None, rkorder=3, dt=1.0, dtmax=1e9, adaptivestep=True,
-                 cflmax=1.0, dnmax=0.4, rhoref=None, rhorefh=None):
+                 cflmax=1.0, dnmax=0.4, rhoref=None, rhorefh=None, fluxlimit_list=(), endtime=None):
         gc = None
         if swadvec == "2i5":
-            gc = (3, 3, 1)
+            gc = (3, 3, 2 if fluxlimit_list else 1)      # src/advec_2i5.cxx:42-45
+        self.fluxlimit_list = tuple(fluxlimit_list)
+        self.iendtime = None if endtime is None else int(1e9 * endtime + 0.5)
         self.W = RefWorld(itot, jtot, ktot, xsize, ysize, zsize, z, order=order, gc=gc, rhoref=rhoref, rhorefh=rhorefh)
         W = self.W
         self.names = list(fields)                       # e.g. ["u","v","w","th"]
@@ -91,6 +93,10 @@ class OracleLES:
             if self.swdiff == "smag2":
                 dnmul = max(1e-9, W.call("ref_smag2_dnmul", self.evisc, self.tPr))
                 lim.append(int(self.idt * self.dnmax / (self.dt * dnmul)))
+            elif self.swdiff in ("2", "4"):
+                lim.append(int(self.idt * self.dnmax / (self.dt * self.static_dnmul())))
+            if self.iendtime is not None:
+                lim.append(self.iendtime - self.itime)
             self.idt = max(min(lim), 1)
             self.dt = self.idt / self.ifactor
         if self.swthermo == "dry":
@@ -104,7 +110,7 @@ class OracleLES:
         elif self.swadvec == "2i5":
             W.call("ref_advec2i5_uvw", at["u"], at["v"], at["w"], u, v, w)
             for n in self.scalars:
-                W.call("ref_advec2i5_s", at[n], a[n], u, v, w)
+                W.call("ref_advec2i5_s", at[n], a[n], u, v, w, 1 if n in self.fluxlimit_list else 0)
         elif self.swadvec == "4":
             W.call("ref_advec4_uvw", at["u"], at["v"], at["w"], u, v, w)
             for n in self.scalars:
@@ -125,7 +131,9 @@ class OracleLES:
             for n in self.scalars:
                 W.call("ref_diff2_c", at[n], a[n], self.svisc)
         elif self.swdiff == "4":
-            W.call("ref_diff4_uvw", at["u"], at["v"], at["w"], u, v, w, self.visc)
+            W.call("ref_diff4_c", at["u"], u, self.visc)
+            W.call("ref_diff4_c", at["v"], v, self.visc)
+            W.call("ref_diff4_w", at["w"], w, self.visc)
             for n in self.scalars:
                 W.call("ref_diff4_c", at[n], a[n], self.svisc)
         sub_dt = lib().ref_rk_subdt(C.c_int(self.rkorder), C.c_double(self.dt), C.c_int(self.substep))
@@ -143,6 +151,12 @@ class OracleLES:
             self.time = self.itime / self.ifactor
             self.iteration += 1
 
+    def static_dnmul(self):
+        """Diff_2/4::create, src/diff_2.cxx:139-151 / src/diff_4.cxx:236-246"""
+        W = self.W
+        viscmax = max([self.visc] + [self.svisc for _ in self.scalars])
+        return max(abs(viscmax * (1. / (W.dx * W.dx) + 1. / (W.dy * W.dy) + 1. / (W.dz[k] * W.dz[k]))) for k in range(W.kstart, W.kend))
+
     def step(self):
         for _ in range(3 if self.rkorder == 3 else 5):
             self.exec_substep()
@@ -156,4 +170,6 @@ class OracleLES:
         f = [self.a[n].copy() for n in "uvw"]
         for x in f:
             W.call("ref_cyclic", x, 2)
+        if W.order == 4:
+            W.call("ref_ghost_cells_w", f[2], 1)      # Conservation, src/model.cxx:815
         return W.call("ref_pres4_divergence" if W.order == 4 else "ref_pres2_divergence", *f)
