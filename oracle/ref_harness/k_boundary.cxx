@@ -39,3 +39,11 @@ API void ref_ghost_cells_w(void* h, double* w, int type)
         calc_ghost_cells_topw_cons_4th<double>(w, gd.kend, gd.icells, gd.jcells, gd.ijcells);
     }
 }
+
+// set_bc<TF,true> (src/boundary.cxx:50-91) as used by Boundary::set_values (:598-682).
+API void ref_set_bc(void* h, double* a, double* agrad, double* aflux, int sw, double aval, double visc, double offset)
+{
+    World* W = static_cast<World*>(h);
+    const Grid_data<double>& gd = W->grid->get_grid_data();
+    set_bc<double, true>(a, agrad, aflux, static_cast<Boundary_type>(sw), aval, visc, offset, gd.icells, gd.jcells);
+}

@@ -1,0 +1,193 @@
+"""GPU parity, per call, of the small operators around the stencils: Boundary_cyclic, vertical ghost rows (2nd/4th order,
+every Boundary_type), set_bc, RK3/RK4 substeps, Field3d_operators reductions, Fields diagnostics, thermo_dry pieces —
+each through the C ABI against the reference's own code (oracle/_ref) or, for src/fields.cxx (not compilable here),
+the numpy restatement in oracle/restate.py.  Copies and ghost rows are bit-exact; arithmetic is within 1e-13."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.helpers import make_case, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _worlds(case):
+    import torch
+    from microhh_b200 import host as H
+    from oracle.ref import RefWorld
+    c = case
+    g = H.Grid(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], swspatialorder=str(c["order"]),
+               gc=c["gc"], device=torch.device("cuda:0"))
+    W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], order=c["order"], gc=c["gc"],
+                 rhoref=c["rhoref"], rhorefh=c["rhorefh"])
+    return g, W
+
+
+def _up(g, a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(g.device)
+
+
+CASES = [dict(itot=16, jtot=12, ktot=8), dict(itot=16, jtot=12, ktot=8, order=4, alpha=1.5), dict(itot=16, jtot=1, ktot=8),
+         dict(itot=16, jtot=1, ktot=8, order=4), dict(itot=20, jtot=8, ktot=10, gc=(3, 3, 2))]
+IDS = ["o2", "o4_stretched", "o2_2d", "o4_2d", "gc332"]
+
+
+@pytest.mark.parametrize("kw", CASES, ids=IDS)
+def test_cyclic_bit_exact(cuda_lib, kw):
+    from microhh_b200 import host as H
+    case = make_case(**kw)
+    g, W = _worlds(case)
+    bc = H.Boundary_cyclic(g)
+    for edge in (0, 1, 2):
+        a = case["u"].copy()
+        d = _up(g, a)
+        bc.exec(d, edge)
+        W.call("ref_cyclic", a, edge)
+        assert np.array_equal(d.cpu().numpy(), a), edge
+    a2 = case["v"][0].copy()
+    d2 = _up(g, a2)
+    bc.exec_2d(d2)
+    W.call("ref_cyclic_2d", a2)
+    assert np.array_equal(d2.cpu().numpy(), a2)
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("kw", CASES[:4], ids=IDS[:4])
+@pytest.mark.parametrize("bcbot,bctop", [(0, 0), (1, 1), (2, 1), (0, 2)])
+def test_ghost_cells(cuda_lib, kw, bcbot, bctop):
+    case = make_case(**kw)
+    g, W = _worlds(case)
+    rng = np.random.default_rng(3)
+    pl = [rng.uniform(-1, 1, (W.jcells, W.icells)) for _ in range(4)]
+    a = case["s"][0].copy()
+    d = _up(g, a)
+    dp = [_up(g, p) for p in pl]
+    from microhh_b200 import lib as L
+    L.check(g.ctx, g.lib.mhh_ghost_cells(g.ctx, L.ptr(d), bcbot, bctop, L.ptr(dp[0]), L.ptr(dp[1]), L.ptr(dp[2]), L.ptr(dp[3])), "ghost")
+    W.call("ref_ghost_cells", a, bcbot, bctop, pl[0], pl[1], pl[2], pl[3])
+    got = d.cpu().numpy()
+    assert np.array_equal(got[W.kstart:W.kend], a[W.kstart:W.kend])
+    assert rel_err(got, a) <= 1e-15
+    if case["order"] == 4:
+        for t in (0, 1):
+            w = case["w"].copy()
+            w[W.kstart + 1:W.kend] = rng.uniform(-1, 1, w[W.kstart + 1:W.kend].shape)
+            dw = _up(g, w)
+            L.check(g.ctx, g.lib.mhh_ghost_cells_w(g.ctx, L.ptr(dw), t), "ghost_w")
+            W.call("ref_ghost_cells_w", w, t)
+            assert np.array_equal(dw.cpu().numpy(), w), t
+    g.close(); W.close()
+
+
+def test_set_bc(cuda_lib):
+    from microhh_b200 import lib as L
+    case = make_case(itot=16, jtot=12, ktot=8)
+    g, W = _worlds(case)
+    for sw, aval in ((0, 1.25), (1, 0.003), (2, -0.1)):
+        ref = [np.full((W.jcells, W.icells), 7.) for _ in range(3)]
+        dev = [_up(g, r) for r in ref]
+        W.call("ref_set_bc", ref[0], ref[1], ref[2], sw, aval, 1e-5, 0.5)
+        L.check(g.ctx, g.lib.mhh_set_bc(g.ctx, L.ptr(dev[0]), L.ptr(dev[1]), L.ptr(dev[2]), sw, C.c_double(aval), C.c_double(1e-5),
+                                        C.c_double(0.5)), "set_bc")
+        for r, d in zip(ref, dev):
+            assert np.array_equal(d.cpu().numpy(), r), sw
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("rkorder", [3, 4])
+def test_rk_substeps(cuda_lib, rkorder):
+    """rk3/rk4, src/timeloop.cxx:250-334: a += cB*dt*at on the interior; at *= cA_next (0 after the last substep).
+    The CPU reference zeroes/rescales ALL cells of the tendency (ghosts too): whole arrays are compared."""
+    from microhh_b200 import lib as L
+    case = make_case(itot=16, jtot=12, ktot=8, nscalars=2)
+    g, W = _worlds(case)
+    rng = np.random.default_rng(1)
+    names = ["u", "v", "w", "s0", "s1"]
+    a = {n: rng.uniform(-1, 1, W.shape) for n in names}
+    at = {n: rng.uniform(-1, 1, W.shape) for n in names}
+    da = {n: _up(g, a[n]) for n in names}
+    dat = {n: _up(g, at[n]) for n in names}
+    dt = 0.37
+    for sub in range(3 if rkorder == 3 else 5):
+        pa, pat = L.ptr_array([da[n] for n in names]), L.ptr_array([dat[n] for n in names])
+        L.check(g.ctx, g.lib.mhh_rk_substep(g.ctx, rkorder, sub, C.c_double(dt), len(names), pa, pat), "rk")
+        for n in names:
+            W.call("ref_rk", rkorder, a[n], at[n], sub, dt)
+            assert rel_err(da[n].cpu().numpy(), a[n]) <= 1e-15, (n, sub)
+            assert rel_err(dat[n].cpu().numpy(), at[n]) <= 1e-15, (n, sub)
+        import oracle.ref as R
+        sd = R.lib().ref_rk_subdt(C.c_int(rkorder), C.c_double(dt), C.c_int(sub))
+        assert g.lib.mhh_rk_sub_dt(rkorder, sub, C.c_double(dt)) == sd
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("kw", [dict(itot=32, jtot=24, ktot=16, alpha=1.2), dict(itot=64, jtot=1, ktot=12), dict(itot=24, jtot=20, ktot=10, order=4)],
+                         ids=["3d_stretched", "2d", "o4"])
+def test_reductions_and_diagnostics(cuda_lib, kw):
+    from microhh_b200 import host as H
+    from oracle import restate as RS
+    case = make_case(**kw)
+    g, W = _worlds(case)
+    ops = H.Field3d_operators(g)
+    th = case["s"][0]
+    d = _up(g, th)
+    prof = ops.calc_mean_profile(d)
+    ref = np.zeros(W.kcells)
+    W.call("ref_mean_profile", ref, th)
+    assert np.abs(prof - ref).max() <= 1e-13 * np.abs(ref).max()
+    assert abs(ops.calc_mean(d) - W.call("ref_mean", th)) <= 1e-13 * 300.
+    assert abs(ops.calc_mean_2d(_up(g, th[3])) - W.call("ref_mean_2d", th[3].copy())) <= 1e-13 * 300.
+    assert ops.calc_max(_up(g, case["u"])) == RS.calc_max(W, case["u"])
+    if case["order"] == 2:
+        f = H.Fields(g, slist=["s0"])
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+        f.sp["s0"].fld.copy_(d)
+        u, v, w = case["u"], case["v"], case["w"]
+        for got, want in ((f.check_momentum(), RS.check_momentum(W, u, v, w)), (f.check_tke(), RS.check_tke(W, u, v, w)),
+                          (f.check_mass(), RS.check_mass(W, th))):
+            assert abs(got - want) <= 1e-12 * max(abs(want), 1e-3), (got, want)
+    g.close(); W.close()
+
+
+def test_reduction_propagates_nan(cuda_lib):
+    """The CFL guard of Model::print_status (src/model.cxx:832-836) needs a NaN/inf in the fields to reach the host."""
+    from microhh_b200 import host as H
+    case = make_case(itot=16, jtot=12, ktot=8)
+    g, W = _worlds(case)
+    f = H.Fields(g)
+    for n in "uvw":
+        f.mp[n].fld.copy_(_up(g, case[n]))
+    f.mp["u"].fld[5, 6, 7] = float("nan")
+    cfl = H.Advec.factory(g, f, "2").get_cfl(1.0)
+    assert not (0. <= cfl < 10.)
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("order", [2, 4])
+def test_thermo_dry(cuda_lib, order):
+    from microhh_b200.model import Thermo
+    from microhh_b200 import host as H
+    case = make_case(itot=16, jtot=12, ktot=10, order=order, alpha=1.3)
+    g, W = _worlds(case)
+    f = H.Fields(g, slist=["th"])
+    th = case["s"][0]
+    f.sp["th"].fld.copy_(_up(g, th))
+    rng = np.random.default_rng(2)
+    thref = 300. + rng.uniform(0, 1, W.kcells)
+    threfh = 300. + rng.uniform(0, 1, W.kcells)
+    t = Thermo(g, f, "dry", thref=thref, threfh=threfh)
+    wt0 = rng.uniform(-1, 1, W.shape)
+    f.mt["w"].fld.copy_(_up(g, wt0))
+    t.exec()
+    ref = wt0.copy()
+    W.call("ref_thermo_buoyancy_tend", ref, th, threfh)
+    assert rel_err(f.mt["w"].fld.cpu().numpy(), ref) <= 1e-14
+    if order == 2:
+        n2 = t.get_thermo_field("N2").cpu().numpy()
+        rn2 = np.zeros(W.shape)
+        W.call("ref_thermo_N2", rn2, th, thref)
+        assert rel_err(n2[W.kstart:W.kend], rn2[W.kstart:W.kend]) <= 1e-14
+    g.close(); W.close()
