@@ -47,7 +47,7 @@ struct GridD
 };
 
 constexpr double kDsmall = 1.e-9;   // Constants::dsmall, include/constants.h
-constexpr double kDhuge  = 1.e9;    // Constants::dhuge
+constexpr double kDhuge  = 1.e30;   // Constants::dhuge, include/constants.h:99
 constexpr double kKappa  = 0.4;     // Constants::kappa<TF>
 
 // Error codes returned through the C ABI (0 = ok).
