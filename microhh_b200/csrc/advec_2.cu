@@ -15,7 +15,10 @@ namespace
 {
     constexpr int KCHUNK = MHH_KCHUNK;
 
-    __global__ void __launch_bounds__(256, MHH_MINB)
+    // Register queues while marching k: the centre columns of u,v,w at k-1,k,k+1 and the columns the cross terms
+    // need at the neighbouring level (u_e and v_n at k-1; w_w and w_s at k+1).  20 global loads per point instead
+    // of 30 (ncu r01: the kernel was held by L1 wavefront throughput at 80 %, not by HBM).
+    __global__ void __launch_bounds__(256, 3)
     advec2_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                       const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                       const GridD gd)
@@ -29,9 +32,13 @@ namespace
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
 
-        for (int k = k0; k < k1; ++k)
+        int ijk = i + j * jj + k0 * kk;
+        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk];
+        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk];
+        double w_b = w[ijk - kk], w_c = w[ijk], w_w = w[ijk - ii], w_s = w[ijk - jj];
+
+        for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            const int ijk = i + j * jj + k * kk;
             if (k + MHH_PF < gd.kcells - 1)
             {
                 const int pf = ijk + (MHH_PF + 1) * kk;
@@ -39,13 +46,12 @@ namespace
                 prefetch_l2(ut + pf - kk); prefetch_l2(vt + pf - kk); prefetch_l2(wt + pf - kk);
             }
             const double rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k], rho = gd.rhoref[k], dzi = gd.dzi[k];
+            const double rho_i = gd.rhoref_i[k];
 
-            const double u_c = u[ijk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
-            const double u_t = u[ijk + kk], u_b = u[ijk - kk];
-            const double v_c = v[ijk], v_e = v[ijk + ii], v_w = v[ijk - ii], v_n = v[ijk + jj], v_s = v[ijk - jj];
-            const double v_t = v[ijk + kk], v_b = v[ijk - kk];
-            const double w_c = w[ijk], w_e = w[ijk + ii], w_w = w[ijk - ii], w_n = w[ijk + jj], w_s = w[ijk - jj];
-            const double w_t = w[ijk + kk], w_b = w[ijk - kk];
+            const double u_t = u[ijk + kk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
+            const double v_t = v[ijk + kk], v_n = v[ijk + jj], v_e = v[ijk + ii], v_w = v[ijk - ii], v_s = v[ijk - jj];
+            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_st = w[ijk - jj + kk];
+            const double w_e = w[ijk + ii], w_n = w[ijk + jj];
 
             // advec_u, src/advec_2.cxx:98-109
             ut[ijk] +=
@@ -53,8 +59,8 @@ namespace
                   - interp2(u_w, u_c) * interp2(u_w, u_c) ) * dxi
                 - ( interp2(v[ijk - ii + jj], v_n) * interp2(u_c, u_n)
                   - interp2(v_w, v_c) * interp2(u_s, u_c) ) * dyi
-                - ( rhoh_t * interp2(w[ijk - ii + kk], w_t) * interp2(u_c, u_t)
-                  - rhoh_b * interp2(w_w, w_c) * interp2(u_b, u_c) ) / rho * dzi;
+                - div_by( rhoh_t * interp2(w_wt, w_t) * interp2(u_c, u_t)
+                        - rhoh_b * interp2(w_w, w_c) * interp2(u_b, u_c), rho, rho_i ) * dzi;
 
             // advec_v, src/advec_2.cxx:129-140
             vt[ijk] +=
@@ -62,20 +68,23 @@ namespace
                   - interp2(u_s, u_c) * interp2(v_w, v_c) ) * dxi
                 - ( interp2(v_c, v_n) * interp2(v_c, v_n)
                   - interp2(v_s, v_c) * interp2(v_s, v_c) ) * dyi
-                - ( rhoh_t * interp2(w[ijk - jj + kk], w_t) * interp2(v_c, v_t)
-                  - rhoh_b * interp2(w_s, w_c) * interp2(v_b, v_c) ) / rho * dzi;
+                - div_by( rhoh_t * interp2(w_st, w_t) * interp2(v_c, v_t)
+                        - rhoh_b * interp2(w_s, w_c) * interp2(v_b, v_c), rho, rho_i ) * dzi;
 
             // advec_w, src/advec_2.cxx:160-171 (k from kstart+1)
             if (k > gd.kstart)
             {
                 wt[ijk] +=
-                    - ( interp2(u[ijk + ii - kk], u_e) * interp2(w_c, w_e)
+                    - ( interp2(u_eb, u_e) * interp2(w_c, w_e)
                       - interp2(u_b, u_c) * interp2(w_w, w_c) ) * dxi
-                    - ( interp2(v[ijk + jj - kk], v_n) * interp2(w_c, w_n)
+                    - ( interp2(v_nb, v_n) * interp2(w_c, w_n)
                       - interp2(v_b, v_c) * interp2(w_s, w_c) ) * dyi
-                    - ( gd.rhoref[k] * interp2(w_c, w_t) * interp2(w_c, w_t)
-                      - gd.rhoref[k - 1] * interp2(w_b, w_c) * interp2(w_b, w_c) ) / gd.rhorefh[k] * gd.dzhi[k];
+                    - div_by( rho * interp2(w_c, w_t) * interp2(w_c, w_t)
+                            - gd.rhoref[k - 1] * interp2(w_b, w_c) * interp2(w_b, w_c), rhoh_b, gd.rhorefh_i[k] ) * gd.dzhi[k];
             }
+            u_b = u_c; u_c = u_t; u_eb = u_e;
+            v_b = v_c; v_c = v_t; v_nb = v_n;
+            w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
         }
     }
 
@@ -111,8 +120,8 @@ namespace
                   - u[ijk] * interp2(s[ijk - ii], s_c) ) * dxi
                 - ( v[ijk + jj] * interp2(s_c, s[ijk + jj])
                   - v[ijk] * interp2(s[ijk - jj], s_c) ) * dyi
-                - ( gd.rhorefh[k + 1] * w_t * interp2(s_c, s_t)
-                  - gd.rhorefh[k] * w_c * interp2(s_b, s_c) ) / gd.rhoref[k] * gd.dzi[k];
+                - div_by( gd.rhorefh[k + 1] * w_t * interp2(s_c, s_t)
+                        - gd.rhorefh[k] * w_c * interp2(s_b, s_c), gd.rhoref[k], gd.rhoref_i[k] ) * gd.dzi[k];
             s_b = s_c; s_c = s_t; w_c = w_t;
         }
     }

@@ -140,16 +140,20 @@ int ctx_upload_metrics(Ctx* c)
 {
     GridD& gd = c->gd;
     const int kcells = gd.kcells;
-    if (!c->metrics_d) MHH_CUDA_CHECK(cudaMalloc(&c->metrics_d, sizeof(double) * kcells * 10));
-    const std::vector<double>* src[10] = {&c->z, &c->zh, &c->dz, &c->dzh, &c->dzi, &c->dzhi, &c->dzi4, &c->dzhi4,
-                                          &c->rhoref, &c->rhorefh};
-    for (int n = 0; n < 10; ++n)
+    if (!c->metrics_d) MHH_CUDA_CHECK(cudaMalloc(&c->metrics_d, sizeof(double) * kcells * 12));
+    // correctly rounded reciprocals of the density profiles: operands of div_by() (mhh_common.cuh)
+    std::vector<double> rho_i(kcells), rhoh_i(kcells);
+    for (int k = 0; k < kcells; ++k) { rho_i[k] = 1. / c->rhoref[k]; rhoh_i[k] = 1. / c->rhorefh[k]; }
+    const std::vector<double>* src[12] = {&c->z, &c->zh, &c->dz, &c->dzh, &c->dzi, &c->dzhi, &c->dzi4, &c->dzhi4,
+                                          &c->rhoref, &c->rhorefh, &rho_i, &rhoh_i};
+    for (int n = 0; n < 12; ++n)
         MHH_CUDA_CHECK(cudaMemcpy(c->metrics_d + (size_t)n * kcells, src[n]->data(), sizeof(double) * kcells,
                                   cudaMemcpyHostToDevice));
     const double* m = c->metrics_d;
     gd.z = m; gd.zh = m + kcells; gd.dz = m + 2 * kcells; gd.dzh = m + 3 * kcells; gd.dzi = m + 4 * kcells;
     gd.dzhi = m + 5 * kcells; gd.dzi4 = m + 6 * kcells; gd.dzhi4 = m + 7 * kcells;
     gd.rhoref = m + 8 * kcells; gd.rhorefh = m + 9 * kcells;
+    gd.rhoref_i = m + 10 * kcells; gd.rhorefh_i = m + 11 * kcells;
     return MHH_OK;
 }
 

@@ -18,61 +18,14 @@ namespace
 
     __device__ __forceinline__ double pow2(double x) { return x * x; }
 
-    // |S|^2 at one cell; src/diff_smag2.cxx:120-154 (interior) and :80-114 (MO bottom row).
-    template<bool bottom_mo>
-    __device__ __forceinline__ double strain2_at(const double* __restrict__ u, const double* __restrict__ v,
-                                                 const double* __restrict__ w, int ijk, int jj, int kk,
-                                                 double dxi, double dyi, double dzi_k, double dzhi_k, double dzhi_kp,
-                                                 double ugradbot, double vgradbot)
-    {
-        const int ii = 1;
-        double s;
-        if (bottom_mo)
-        {
-            s = 2. * (
-                + pow2((u[ijk + ii] - u[ijk]) * dxi)
-                + pow2((v[ijk + jj] - v[ijk]) * dyi)
-                + pow2((w[ijk + kk] - w[ijk]) * dzi_k)
-                + 0.125 * pow2((u[ijk] - u[ijk - jj]) * dyi + (v[ijk] - v[ijk - ii]) * dxi)
-                + 0.125 * pow2((u[ijk + ii] - u[ijk + ii - jj]) * dyi + (v[ijk + ii] - v[ijk]) * dxi)
-                + 0.125 * pow2((u[ijk + jj] - u[ijk]) * dyi + (v[ijk + jj] - v[ijk - ii + jj]) * dxi)
-                + 0.125 * pow2((u[ijk + ii + jj] - u[ijk + ii]) * dyi + (v[ijk + ii + jj] - v[ijk + jj]) * dxi)
-                + 0.5 * pow2(ugradbot)
-                + 0.125 * pow2((w[ijk] - w[ijk - ii]) * dxi)
-                + 0.125 * pow2((w[ijk + ii] - w[ijk]) * dxi)
-                + 0.125 * pow2((w[ijk + kk] - w[ijk - ii + kk]) * dxi)
-                + 0.125 * pow2((w[ijk + ii + kk] - w[ijk + kk]) * dxi)
-                + 0.5 * pow2(vgradbot)
-                + 0.125 * pow2((w[ijk] - w[ijk - jj]) * dyi)
-                + 0.125 * pow2((w[ijk + jj] - w[ijk]) * dyi)
-                + 0.125 * pow2((w[ijk + kk] - w[ijk - jj + kk]) * dyi)
-                + 0.125 * pow2((w[ijk + jj + kk] - w[ijk + kk]) * dyi));
-        }
-        else
-        {
-            s = 2. * (
-                + pow2((u[ijk + ii] - u[ijk]) * dxi)
-                + pow2((v[ijk + jj] - v[ijk]) * dyi)
-                + pow2((w[ijk + kk] - w[ijk]) * dzi_k)
-                + 0.125 * pow2((u[ijk] - u[ijk - jj]) * dyi + (v[ijk] - v[ijk - ii]) * dxi)
-                + 0.125 * pow2((u[ijk + ii] - u[ijk + ii - jj]) * dyi + (v[ijk + ii] - v[ijk]) * dxi)
-                + 0.125 * pow2((u[ijk + jj] - u[ijk]) * dyi + (v[ijk + jj] - v[ijk - ii + jj]) * dxi)
-                + 0.125 * pow2((u[ijk + ii + jj] - u[ijk + ii]) * dyi + (v[ijk + ii + jj] - v[ijk + jj]) * dxi)
-                + 0.125 * pow2((u[ijk] - u[ijk - kk]) * dzhi_k + (w[ijk] - w[ijk - ii]) * dxi)
-                + 0.125 * pow2((u[ijk + ii] - u[ijk + ii - kk]) * dzhi_k + (w[ijk + ii] - w[ijk]) * dxi)
-                + 0.125 * pow2((u[ijk + kk] - u[ijk]) * dzhi_kp + (w[ijk + kk] - w[ijk - ii + kk]) * dxi)
-                + 0.125 * pow2((u[ijk + ii + kk] - u[ijk + ii]) * dzhi_kp + (w[ijk + ii + kk] - w[ijk + kk]) * dxi)
-                + 0.125 * pow2((v[ijk] - v[ijk - kk]) * dzhi_k + (w[ijk] - w[ijk - jj]) * dyi)
-                + 0.125 * pow2((v[ijk + jj] - v[ijk + jj - kk]) * dzhi_k + (w[ijk + jj] - w[ijk]) * dyi)
-                + 0.125 * pow2((v[ijk + kk] - v[ijk]) * dzhi_kp + (w[ijk + kk] - w[ijk - jj + kk]) * dyi)
-                + 0.125 * pow2((v[ijk + jj + kk] - v[ijk + jj]) * dzhi_kp + (w[ijk + jj + kk] - w[ijk + kk]) * dyi));
-        }
-        return s + kDsmall;
-    }
-
     // MODE 0: thermo on (calc_evisc), 1: neutral (calc_evisc_neutral), 2: strain2 only (stage test)
+    //
+    // |S|^2 (src/diff_smag2.cxx:120-154 interior, :80-114 MO bottom row) needs u at (i,i+1) x (j-1,j,j+1) x (k-1,k,k+1),
+    // v at (i-1,i,i+1) x (j,j+1) x (k-1,k,k+1) and w at the 5-point star on levels k and k+1.  Marching k, the columns
+    // u_c, u_e, v_c, v_n (three levels) and the w star (two levels) stay in registers: 18 global loads per point instead
+    // of 31 (ncu r01: L1 68 %, DRAM 30 %).
     template<bool SURF, int MODE>
-    __global__ void __launch_bounds__(256, MHH_MINB)
+    __global__ void __launch_bounds__(256, 3)
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
@@ -82,11 +35,12 @@ namespace
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
         const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
         if (i >= gd.iend || j >= gd.jend) return;
-        const int jj = gd.icells, kk = gd.ijcells;
+        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
         const int ij = i + j * jj;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        const double tPr_i = 1. / tPr;
 
         double z0 = 0.;
         if (SURF && MODE != 2) z0 = z0m[ij];
@@ -103,19 +57,71 @@ namespace
                                 + pow2(visc * (v[ijk_top] - v[ijk_top - kk]) * gd.dzhi[gd.kend])));
         }
 
-        for (int k = k0; k < k1; ++k)
+        int ijk = ij + k0 * kk;
+        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk], u_e = u[ijk + ii];
+        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk], v_n = v[ijk + jj];
+        double w_c = w[ijk], w_w = w[ijk - ii], w_e = w[ijk + ii], w_s = w[ijk - jj], w_n = w[ijk + jj];
+
+        for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            const int ijk = ij + k * kk;
             if (k + MHH_PF < gd.kcells - 1)
             {
                 const int pf = ijk + (MHH_PF + 1) * kk;
                 prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
                 if (MODE == 0) prefetch_l2(N2 + pf - kk);
             }
+            const double u_t = u[ijk + kk], u_et = u[ijk + ii + kk];
+            const double u_s = u[ijk - jj], u_es = u[ijk + ii - jj], u_n = u[ijk + jj], u_en = u[ijk + ii + jj];
+            const double v_t = v[ijk + kk], v_nt = v[ijk + jj + kk];
+            const double v_w = v[ijk - ii], v_e = v[ijk + ii], v_wn = v[ijk - ii + jj], v_en = v[ijk + ii + jj];
+            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_et = w[ijk + ii + kk];
+            const double w_st = w[ijk - jj + kk], w_nt = w[ijk + jj + kk];
+            const double dzi_k = gd.dzi[k], dzhi_k = gd.dzhi[k], dzhi_kp = gd.dzhi[k + 1];
+
             const bool bot = SURF && (k == gd.kstart);
-            const double s2 = bot
-                ? strain2_at<true>(u, v, w, ijk, jj, kk, dxi, dyi, gd.dzi[k], 0., 0., dudz[ij], dvdz[ij])
-                : strain2_at<false>(u, v, w, ijk, jj, kk, dxi, dyi, gd.dzi[k], gd.dzhi[k], gd.dzhi[k + 1], 0., 0.);
+            double s2;
+            if (bot)
+            {
+                const double ugradbot = dudz[ij], vgradbot = dvdz[ij];
+                s2 = 2. * (
+                    + pow2((u_e - u_c) * dxi)
+                    + pow2((v_n - v_c) * dyi)
+                    + pow2((w_t - w_c) * dzi_k)
+                    + 0.125 * pow2((u_c - u_s) * dyi + (v_c - v_w) * dxi)
+                    + 0.125 * pow2((u_e - u_es) * dyi + (v_e - v_c) * dxi)
+                    + 0.125 * pow2((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
+                    + 0.125 * pow2((u_en - u_e) * dyi + (v_en - v_n) * dxi)
+                    + 0.5 * pow2(ugradbot)
+                    + 0.125 * pow2((w_c - w_w) * dxi)
+                    + 0.125 * pow2((w_e - w_c) * dxi)
+                    + 0.125 * pow2((w_t - w_wt) * dxi)
+                    + 0.125 * pow2((w_et - w_t) * dxi)
+                    + 0.5 * pow2(vgradbot)
+                    + 0.125 * pow2((w_c - w_s) * dyi)
+                    + 0.125 * pow2((w_n - w_c) * dyi)
+                    + 0.125 * pow2((w_t - w_st) * dyi)
+                    + 0.125 * pow2((w_nt - w_t) * dyi));
+            }
+            else
+            {
+                s2 = 2. * (
+                    + pow2((u_e - u_c) * dxi)
+                    + pow2((v_n - v_c) * dyi)
+                    + pow2((w_t - w_c) * dzi_k)
+                    + 0.125 * pow2((u_c - u_s) * dyi + (v_c - v_w) * dxi)
+                    + 0.125 * pow2((u_e - u_es) * dyi + (v_e - v_c) * dxi)
+                    + 0.125 * pow2((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
+                    + 0.125 * pow2((u_en - u_e) * dyi + (v_en - v_n) * dxi)
+                    + 0.125 * pow2((u_c - u_b) * dzhi_k + (w_c - w_w) * dxi)
+                    + 0.125 * pow2((u_e - u_eb) * dzhi_k + (w_e - w_c) * dxi)
+                    + 0.125 * pow2((u_t - u_c) * dzhi_kp + (w_t - w_wt) * dxi)
+                    + 0.125 * pow2((u_et - u_e) * dzhi_kp + (w_et - w_t) * dxi)
+                    + 0.125 * pow2((v_c - v_b) * dzhi_k + (w_c - w_s) * dyi)
+                    + 0.125 * pow2((v_n - v_nb) * dzhi_k + (w_n - w_c) * dyi)
+                    + 0.125 * pow2((v_t - v_c) * dzhi_kp + (w_t - w_st) * dyi)
+                    + 0.125 * pow2((v_nt - v_n) * dzhi_kp + (w_nt - w_t) * dyi));
+            }
+            s2 = s2 + kDsmall;
 
             double ev;
             if (MODE == 2)
@@ -123,7 +129,7 @@ namespace
             else if (MODE == 0)
             {
                 // src/diff_smag2.cxx:291-295 / :332-338 / :355-361
-                double rit = (bot ? dbdz[ij] : N2[ijk]) / s2 / tPr;
+                double rit = div_by((bot ? dbdz[ij] : N2[ijk]) / s2, tPr, tPr_i);
                 rit = fmin(rit, 1. - kDsmall);
                 if (SURF)
                 {
@@ -153,6 +159,9 @@ namespace
                 }
             }
             evisc[ijk] = ev;
+            u_b = u_c; u_c = u_t; u_eb = u_e; u_e = u_et;
+            v_b = v_c; v_c = v_t; v_nb = v_n; v_n = v_nt;
+            w_c = w_t; w_w = w_wt; w_e = w_et; w_s = w_st; w_n = w_nt;
         }
     }
 
@@ -167,8 +176,12 @@ namespace
         evisc[ij + gd.kend * gd.ijcells] = evisc[ij + (gd.kend - 1) * gd.ijcells];
     }
 
+    // u, v, w stress divergences in one pass.  While marching k the kernel keeps in registers: evisc at the centre, west
+    // and south columns (k-1,k,k+1) and the east / north columns (k-1,k); the centre columns of u,v,w (k-1,k,k+1);
+    // u_e, v_n at k-1 and w_w, w_s at k+1 for the cross terms.  28 global loads per point instead of 46 (ncu r01: L1
+    // wavefront throughput 86 %, DRAM 37 %); the density divisions go through div_by().
     template<bool SURF>
-    __global__ void __launch_bounds__(256, MHH_MINB)
+    __global__ void __launch_bounds__(256, 2)
     smag2_diff_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                           const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                           const double* __restrict__ evisc,
@@ -185,9 +198,17 @@ namespace
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
 
-        for (int k = k0; k < k1; ++k)
+        int ijk = ij + k0 * kk;
+        double e_b = evisc[ijk - kk], e_c = evisc[ijk];
+        double e_wb = evisc[ijk - ii - kk], e_w = evisc[ijk - ii];
+        double e_sb = evisc[ijk - jj - kk], e_s = evisc[ijk - jj];
+        double e_eb = evisc[ijk + ii - kk], e_nb = evisc[ijk + jj - kk];
+        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk];
+        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk];
+        double w_b = w[ijk - kk], w_c = w[ijk], w_w = w[ijk - ii], w_s = w[ijk - jj];
+
+        for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            const int ijk = ij + k * kk;
             if (k + MHH_PF < gd.kcells - 1)
             {
                 const int pf = ijk + (MHH_PF + 1) * kk;
@@ -197,73 +218,85 @@ namespace
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
             const double rho = gd.rhoref[k], rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k];
+            const double rho_i = gd.rhoref_i[k];
             const double dzi = gd.dzi[k], dzhi_t = gd.dzhi[k + 1], dzhi_b = gd.dzhi[k];
 
-            const double e_c = evisc[ijk], e_w = evisc[ijk - ii], e_s = evisc[ijk - jj];
+            // level k+1: centre, west, south columns of evisc; level k: east, north and the three corners
+            const double e_t = evisc[ijk + kk], e_wt = evisc[ijk - ii + kk], e_st = evisc[ijk - jj + kk];
             const double e_e = evisc[ijk + ii], e_n = evisc[ijk + jj];
-            const double e_t = evisc[ijk + kk], e_b = evisc[ijk - kk];
+            const double e_wn = evisc[ijk - ii + jj], e_ws = evisc[ijk - ii - jj], e_es = evisc[ijk + ii - jj];
+            const double u_t = u[ijk + kk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
+            const double u_es = u[ijk + ii - jj];
+            const double v_t = v[ijk + kk], v_n = v[ijk + jj], v_e = v[ijk + ii], v_w = v[ijk - ii], v_s = v[ijk - jj];
+            const double v_wn = v[ijk - ii + jj];
+            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_st = w[ijk - jj + kk];
+            const double w_e = w[ijk + ii], w_n = w[ijk + jj];
 
             // ---- u: src/diff_smag2.cxx:395-467
             {
                 const double evisce = e_c + visc;
                 const double eviscw = e_w + visc;
-                const double eviscn = 0.25 * (e_w + e_c + evisc[ijk - ii + jj] + e_n) + visc;
-                const double eviscs = 0.25 * (evisc[ijk - ii - jj] + e_s + e_w + e_c) + visc;
-                const double evisct = 0.25 * (e_w + e_c + evisc[ijk - ii + kk] + e_t) + visc;
-                const double eviscb = 0.25 * (evisc[ijk - ii - kk] + e_b + e_w + e_c) + visc;
+                const double eviscn = 0.25 * (e_w + e_c + e_wn + e_n) + visc;
+                const double eviscs = 0.25 * (e_ws + e_s + e_w + e_c) + visc;
+                const double evisct = 0.25 * (e_w + e_c + e_wt + e_t) + visc;
+                const double eviscb = 0.25 * (e_wb + e_b + e_w + e_c) + visc;
 
                 const double hor =
-                    + ( evisce * (u[ijk + ii] - u[ijk]) * dxi
-                      - eviscw * (u[ijk] - u[ijk - ii]) * dxi ) * 2. * dxi
-                    + ( eviscn * ((u[ijk + jj] - u[ijk]) * dyi + (v[ijk + jj] - v[ijk - ii + jj]) * dxi)
-                      - eviscs * ((u[ijk] - u[ijk - jj]) * dyi + (v[ijk] - v[ijk - ii]) * dxi) ) * dyi;
-                const double grad_t = (u[ijk + kk] - u[ijk]) * dzhi_t + (w[ijk + kk] - w[ijk - ii + kk]) * dxi;
-                const double grad_b = (u[ijk] - u[ijk - kk]) * dzhi_b + (w[ijk] - w[ijk - ii]) * dxi;
+                    + ( evisce * (u_e - u_c) * dxi
+                      - eviscw * (u_c - u_w) * dxi ) * 2. * dxi
+                    + ( eviscn * ((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
+                      - eviscs * ((u_c - u_s) * dyi + (v_c - v_w) * dxi) ) * dyi;
+                const double grad_t = (u_t - u_c) * dzhi_t + (w_t - w_wt) * dxi;
+                const double grad_b = (u_c - u_b) * dzhi_b + (w_c - w_w) * dxi;
                 double ver;
-                if (bot)      ver = ( rhoh_t * evisct * grad_t + rhoh_b * ufluxbot[ij] ) / rho * dzi;
-                else if (top) ver = ( -rhoh_t * ufluxtop[ij] - rhoh_b * eviscb * grad_b ) / rho * dzi;
-                else          ver = ( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b ) / rho * dzi;
+                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * ufluxbot[ij], rho, rho_i ) * dzi;
+                else if (top) ver = div_by( -rhoh_t * ufluxtop[ij] - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
                 ut[ijk] += hor + ver;
             }
             // ---- v: src/diff_smag2.cxx:497-569
             {
-                const double evisce = 0.25 * (e_s + e_c + evisc[ijk + ii - jj] + e_e) + visc;
-                const double eviscw = 0.25 * (evisc[ijk - ii - jj] + e_w + e_s + e_c) + visc;
+                const double evisce = 0.25 * (e_s + e_c + e_es + e_e) + visc;
+                const double eviscw = 0.25 * (e_ws + e_w + e_s + e_c) + visc;
                 const double eviscn = e_c + visc;
                 const double eviscs = e_s + visc;
-                const double evisct = 0.25 * (e_s + e_c + evisc[ijk + kk - jj] + e_t) + visc;
-                const double eviscb = 0.25 * (evisc[ijk - kk - jj] + e_b + e_s + e_c) + visc;
+                const double evisct = 0.25 * (e_s + e_c + e_st + e_t) + visc;
+                const double eviscb = 0.25 * (e_sb + e_b + e_s + e_c) + visc;
 
                 const double hor =
-                    + ( evisce * ((v[ijk + ii] - v[ijk]) * dxi + (u[ijk + ii] - u[ijk + ii - jj]) * dyi)
-                      - eviscw * ((v[ijk] - v[ijk - ii]) * dxi + (u[ijk] - u[ijk - jj]) * dyi) ) * dxi
-                    + ( eviscn * (v[ijk + jj] - v[ijk]) * dyi
-                      - eviscs * (v[ijk] - v[ijk - jj]) * dyi ) * 2. * dyi;
-                const double grad_t = (v[ijk + kk] - v[ijk]) * dzhi_t + (w[ijk + kk] - w[ijk - jj + kk]) * dyi;
-                const double grad_b = (v[ijk] - v[ijk - kk]) * dzhi_b + (w[ijk] - w[ijk - jj]) * dyi;
+                    + ( evisce * ((v_e - v_c) * dxi + (u_e - u_es) * dyi)
+                      - eviscw * ((v_c - v_w) * dxi + (u_c - u_s) * dyi) ) * dxi
+                    + ( eviscn * (v_n - v_c) * dyi
+                      - eviscs * (v_c - v_s) * dyi ) * 2. * dyi;
+                const double grad_t = (v_t - v_c) * dzhi_t + (w_t - w_st) * dyi;
+                const double grad_b = (v_c - v_b) * dzhi_b + (w_c - w_s) * dyi;
                 double ver;
-                if (bot)      ver = ( rhoh_t * evisct * grad_t + rhoh_b * vfluxbot[ij] ) / rho * dzi;
-                else if (top) ver = ( -rhoh_t * vfluxtop[ij] - rhoh_b * eviscb * grad_b ) / rho * dzi;
-                else          ver = ( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b ) / rho * dzi;
+                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * vfluxbot[ij], rho, rho_i ) * dzi;
+                else if (top) ver = div_by( -rhoh_t * vfluxtop[ij] - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
                 vt[ijk] += hor + ver;
             }
             // ---- w: src/diff_smag2.cxx:594-614 (k from kstart+1)
             if (k > gd.kstart)
             {
-                const double evisce = 0.25 * (e_b + e_c + evisc[ijk + ii - kk] + e_e) + visc;
-                const double eviscw = 0.25 * (evisc[ijk - ii - kk] + e_w + e_b + e_c) + visc;
-                const double eviscn = 0.25 * (e_b + e_c + evisc[ijk + jj - kk] + e_n) + visc;
-                const double eviscs = 0.25 * (evisc[ijk - jj - kk] + e_s + e_b + e_c) + visc;
+                const double evisce = 0.25 * (e_b + e_c + e_eb + e_e) + visc;
+                const double eviscw = 0.25 * (e_wb + e_w + e_b + e_c) + visc;
+                const double eviscn = 0.25 * (e_b + e_c + e_nb + e_n) + visc;
+                const double eviscs = 0.25 * (e_sb + e_s + e_b + e_c) + visc;
                 const double evisct = e_c + visc;
                 const double eviscb = e_b + visc;
                 wt[ijk] +=
-                    + ( evisce * ((w[ijk + ii] - w[ijk]) * dxi + (u[ijk + ii] - u[ijk + ii - kk]) * dzhi_b)
-                      - eviscw * ((w[ijk] - w[ijk - ii]) * dxi + (u[ijk] - u[ijk - kk]) * dzhi_b) ) * dxi
-                    + ( eviscn * ((w[ijk + jj] - w[ijk]) * dyi + (v[ijk + jj] - v[ijk + jj - kk]) * dzhi_b)
-                      - eviscs * ((w[ijk] - w[ijk - jj]) * dyi + (v[ijk] - v[ijk - kk]) * dzhi_b) ) * dyi
-                    + ( gd.rhoref[k] * evisct * (w[ijk + kk] - w[ijk]) * dzi
-                      - gd.rhoref[k - 1] * eviscb * (w[ijk] - w[ijk - kk]) * gd.dzi[k - 1] ) / rhoh_b * 2. * dzhi_b;
+                    + ( evisce * ((w_e - w_c) * dxi + (u_e - u_eb) * dzhi_b)
+                      - eviscw * ((w_c - w_w) * dxi + (u_c - u_b) * dzhi_b) ) * dxi
+                    + ( eviscn * ((w_n - w_c) * dyi + (v_n - v_nb) * dzhi_b)
+                      - eviscs * ((w_c - w_s) * dyi + (v_c - v_b) * dzhi_b) ) * dyi
+                    + div_by( rho * evisct * (w_t - w_c) * dzi
+                            - gd.rhoref[k - 1] * eviscb * (w_c - w_b) * gd.dzi[k - 1], rhoh_b, gd.rhorefh_i[k] ) * 2. * dzhi_b;
             }
+            e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
+            u_b = u_c; u_c = u_t; u_eb = u_e;
+            v_b = v_c; v_c = v_t; v_nb = v_n;
+            w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
         }
     }
 
@@ -282,6 +315,7 @@ namespace
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
+        const double tPr_i = 1. / tPr;
 
         int ijk = ij + k0 * kk;
         double a_b = a[ijk - kk], a_c = a[ijk];
@@ -296,22 +330,23 @@ namespace
             const double a_t = a[ijk + kk], e_t = evisc[ijk + kk];
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
-            const double evisce = 0.5 * (e_c + evisc[ijk + ii]) / tPr + visc;
-            const double eviscw = 0.5 * (evisc[ijk - ii] + e_c) / tPr + visc;
-            const double eviscn = 0.5 * (e_c + evisc[ijk + jj]) / tPr + visc;
-            const double eviscs = 0.5 * (evisc[ijk - jj] + e_c) / tPr + visc;
-            const double evisct = 0.5 * (e_c + e_t) / tPr + visc;
-            const double eviscb = 0.5 * (e_b + e_c) / tPr + visc;
+            const double evisce = div_by(0.5 * (e_c + evisc[ijk + ii]), tPr, tPr_i) + visc;
+            const double eviscw = div_by(0.5 * (evisc[ijk - ii] + e_c), tPr, tPr_i) + visc;
+            const double eviscn = div_by(0.5 * (e_c + evisc[ijk + jj]), tPr, tPr_i) + visc;
+            const double eviscs = div_by(0.5 * (evisc[ijk - jj] + e_c), tPr, tPr_i) + visc;
+            const double evisct = div_by(0.5 * (e_c + e_t), tPr, tPr_i) + visc;
+            const double eviscb = div_by(0.5 * (e_b + e_c), tPr, tPr_i) + visc;
 
             const double hor =
                 + ( evisce * (a[ijk + ii] - a_c) - eviscw * (a_c - a[ijk - ii]) ) * dxidxi
                 + ( eviscn * (a[ijk + jj] - a_c) - eviscs * (a_c - a[ijk - jj]) ) * dyidyi;
             const double rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k];
             double ver;
-            if (bot)      ver = ( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1] + rhoh_b * fluxbot[ij] ) / gd.rhoref[k] * gd.dzi[k];
-            else if (top) ver = ( -rhoh_t * fluxtop[ij] - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k] ) / gd.rhoref[k] * gd.dzi[k];
-            else          ver = ( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1]
-                                - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k] ) / gd.rhoref[k] * gd.dzi[k];
+            const double rho = gd.rhoref[k], rho_i = gd.rhoref_i[k];
+            if (bot)      ver = div_by( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1] + rhoh_b * fluxbot[ij], rho, rho_i ) * gd.dzi[k];
+            else if (top) ver = div_by( -rhoh_t * fluxtop[ij] - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k], rho, rho_i ) * gd.dzi[k];
+            else          ver = div_by( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1]
+                                      - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k], rho, rho_i ) * gd.dzi[k];
             at[ijk] += hor + ver;
             a_b = a_c; a_c = a_t; e_b = e_c; e_c = e_t;
         }

@@ -44,6 +44,8 @@ struct GridD
     const double* dzhi4;
     const double* rhoref;
     const double* rhorefh;
+    const double* rhoref_i;    // RN(1/rhoref[k]), RN(1/rhorefh[k]): see div_by()
+    const double* rhorefh_i;
 };
 
 constexpr double kDsmall = 1.e-9;   // Constants::dsmall, include/constants.h
@@ -141,6 +143,17 @@ __device__ __forceinline__ double block_sum(double v)
             v += __shfl_down_sync(0xffffffffu, v, o);
     }
     return v;
+}
+
+// x / c for a divisor whose correctly rounded reciprocal rc = RN(1/c) is already known (per-level density, tPr):
+// q = RN(x*rc); r = x - q*c (exact, FMA); RN(q + r*rc) is the correctly rounded quotient (Markstein 1990) unless the
+// mantissa of c is all ones, where it can be 1 ulp off.  3 FP64 ops instead of the ~12 of a full IEEE division:
+// ncu showed the density / Prandtl divisions holding the diffusion kernels on the FP64 pipe.
+__device__ __forceinline__ double div_by(const double x, const double c, const double rc)
+{
+    const double q = x * rc;
+    const double r = fma(-q, c, x);
+    return fma(r, rc, q);
 }
 
 // L2 prefetch of the line a later k iteration will need (hides DRAM latency of the k-marching loops:
