@@ -105,6 +105,14 @@ int mhh_smag2_exec_viscosity(mhh_ctx* ctx, int surface_model,
                              const double* N2, const double* dudz, const double* dvdz,
                              const double* dbdz, const double* z0m,
                              double cs, double tPr, double visc, double* evisc);
+/* The same with Thermo_dry's N2 (calc_N2, src/thermo_dry.cxx:66-79; base state from mhh_thermo_set_ref) evaluated inside
+ * the kernel from th, i.e. exec_viscosity's `thermo.get_thermo_field(*N2, "N2")` + calc_evisc (src/diff_smag2.cxx:1143-1160)
+ * without materialising the N2 field. */
+int mhh_smag2_exec_viscosity_dry(mhh_ctx* ctx, int surface_model,
+                                 const double* u, const double* v, const double* w,
+                                 const double* th, const double* dudz, const double* dvdz,
+                                 const double* dbdz, const double* z0m,
+                                 double cs, double tPr, double visc, double* evisc);
 /* Diff_smag2::exec — src/diff_smag2.cxx:939 (diff_u :370, diff_v :472, diff_w :575, diff_c :620). */
 int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
                    const double* u, const double* v, const double* w, const double* evisc,

@@ -337,6 +337,15 @@ int mhh_smag2_exec_viscosity(mhh_ctx* c, int surface_model, const double* u, con
     return smag2_exec_viscosity(c, surface_model, u, v, w, N2, dudz, dvdz, dbdz, z0m, cs, tPr, visc, evisc, 0);
 }
 
+int mhh_smag2_exec_viscosity_dry(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,
+                                 const double* th, const double* dudz, const double* dvdz, const double* dbdz,
+                                 const double* z0m, double cs, double tPr, double visc, double* evisc)
+{
+    CTX_CHECK(c);
+    if (!th) { c->last_error = "th is required"; return MHH_ERR_ARG; }
+    return smag2_exec_viscosity(c, surface_model, u, v, w, th, dudz, dvdz, dbdz, z0m, cs, tPr, visc, evisc, 2);
+}
+
 int mhh_smag2_strain2(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,
                       const double* dudz, const double* dvdz, double* strain2)
 {

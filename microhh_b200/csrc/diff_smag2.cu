@@ -18,7 +18,9 @@ namespace
 
     __device__ __forceinline__ double pow2(double x) { return x * x; }
 
-    // MODE 0: thermo on (calc_evisc), 1: neutral (calc_evisc_neutral), 2: strain2 only (stage test)
+    // MODE 0: thermo on (calc_evisc), 1: neutral (calc_evisc_neutral), 2: strain2 only (stage test),
+    // MODE 3: as 0 with N2 = g/thref * dth/dz (calc_N2, src/thermo_dry.cxx:66-79) evaluated on the fly from th: the N2 pointer
+    //         then carries th and `mlen0 + kcells` the g/thref table (saves writing and re-reading the N2 field)
     //
     // |S|^2 (src/diff_smag2.cxx:120-154 interior, :80-114 MO bottom row) needs u at (i,i+1) x (j-1,j,j+1) x (k-1,k,k+1),
     // v at (i-1,i,i+1) x (j,j+1) x (k-1,k,k+1) and w at the 5-point star on levels k and k+1.  Marching k, the columns
@@ -61,6 +63,8 @@ namespace
         double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk], u_e = u[ijk + ii];
         double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk], v_n = v[ijk + jj];
         double w_c = w[ijk], w_w = w[ijk - ii], w_e = w[ijk + ii], w_s = w[ijk - jj], w_n = w[ijk + jj];
+        double th_b = 0., th_c = 0.;
+        if (MODE == 3) { th_b = N2[ijk - kk]; th_c = N2[ijk]; }
 
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
@@ -69,6 +73,7 @@ namespace
                 const int pf = ijk + (MHH_PF + 1) * kk;
                 prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
                 if (MODE == 0) prefetch_l2(N2 + pf - kk);
+                if (MODE == 3) prefetch_l2(N2 + pf);
             }
             const double u_t = u[ijk + kk], u_et = u[ijk + ii + kk];
             const double u_s = u[ijk - jj], u_es = u[ijk + ii - jj], u_n = u[ijk + jj], u_en = u[ijk + ii + jj];
@@ -126,10 +131,19 @@ namespace
             double ev;
             if (MODE == 2)
                 ev = s2;
-            else if (MODE == 0)
+            else if (MODE == 0 || MODE == 3)
             {
                 // src/diff_smag2.cxx:291-295 / :332-338 / :355-361
-                double rit = div_by((bot ? dbdz[ij] : N2[ijk]) / s2, tPr, tPr_i);
+                double n2;
+                if (MODE == 3)
+                {
+                    const double th_t = N2[ijk + kk];
+                    n2 = mlen0[gd.kcells + k] * 0.5 * (th_t - th_b) * dzi_k;
+                    th_b = th_c; th_c = th_t;
+                }
+                else
+                    n2 = bot ? 0. : N2[ijk];
+                double rit = div_by((bot ? dbdz[ij] : n2) / s2, tPr, tPr_i);
                 rit = fmin(rit, 1. - kDsmall);
                 if (SURF)
                 {
@@ -380,7 +394,7 @@ static int smag2_upload_mlen0(Ctx* c, double cs)
 {
     // mlen0[k] = cs * pow(dx*dy*dz[k], 1/3): src/diff_smag2.cxx:192,237,282,319,346 (host std::pow, as the CPU build)
     const GridD& gd = c->gd;
-    if (!c->mlen0_d) MHH_CUDA_CHECK(cudaMalloc(&c->mlen0_d, gd.kcells * sizeof(double)));
+    if (!c->mlen0_d) MHH_CUDA_CHECK(cudaMalloc(&c->mlen0_d, 2 * gd.kcells * sizeof(double)));
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // host_pinned may still be in flight
     double* h = c->host_pinned;
     for (int k = 0; k < gd.kcells; ++k)
@@ -398,16 +412,28 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     const GridD& gd = c->gd;
     if (c->mlen0_cs != cs || c->mlen0_d == nullptr)
         if (int e = smag2_upload_mlen0(c, cs)) return e;
+    if (strain_only == 2)
+    {
+        // fused dry-thermo variant: N2 carries th; the g/thref table sits behind mlen0
+        if (!c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
+        MHH_CUDA_CHECK(cudaMemcpyAsync(c->mlen0_d + gd.kcells, c->thref_d + 2 * gd.kcells, gd.kcells * sizeof(double),
+                                       cudaMemcpyDeviceToDevice, c->stream));
+    }
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd
-    if (strain_only)
+    if (strain_only == 1)
     {
         if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
         else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
         MHH_LAUNCH_CHECK();
         return MHH_OK;
     }
-    if (N2 != nullptr)
+    if (strain_only == 2)
+    {
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 3><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 3><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+    }
+    else if (N2 != nullptr)
     {
         if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
         else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));

@@ -12,7 +12,8 @@ namespace
 
     template<int ORDER>
     __global__ void __launch_bounds__(256, MHH_MINB)
-    buoyancy_tend_kernel(double* __restrict__ wt, const double* __restrict__ th, const double* __restrict__ threfh, const GridD gd)
+    buoyancy_tend_kernel(double* __restrict__ wt, const double* __restrict__ th, const double* __restrict__ threfh,
+                         const double* __restrict__ g_threfh, const GridD gd)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
         const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
@@ -24,14 +25,14 @@ namespace
         {
             const int ijk = i + j * gd.icells + k * kk;
             if (ORDER == 2)
-                wt[ijk] += kGrav / threfh[k] * (fd::interp2(th[ijk - kk], th[ijk]) - threfh[k]);
+                wt[ijk] += g_threfh[k] * (fd::interp2(th[ijk - kk], th[ijk]) - threfh[k]);
             else
-                wt[ijk] += kGrav / threfh[k] * (fd::interp4c(th[ijk - 2 * kk], th[ijk - kk], th[ijk], th[ijk + kk]) - threfh[k]);
+                wt[ijk] += g_threfh[k] * (fd::interp4c(th[ijk - 2 * kk], th[ijk - kk], th[ijk], th[ijk + kk]) - threfh[k]);
         }
     }
 
     __global__ void __launch_bounds__(256, MHH_MINB)
-    n2_kernel(double* __restrict__ N2, const double* __restrict__ th, const double* __restrict__ thref, const GridD gd)
+    n2_kernel(double* __restrict__ N2, const double* __restrict__ th, const double* __restrict__ g_thref, const GridD gd)
     {
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
         const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
@@ -42,7 +43,7 @@ namespace
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * gd.icells + k * kk;
-            N2[ijk] = kGrav / thref[k] * 0.5 * (th[ijk + kk] - th[ijk - kk]) * gd.dzi[k];
+            N2[ijk] = g_thref[k] * 0.5 * (th[ijk + kk] - th[ijk - kk]) * gd.dzi[k];
         }
     }
 }  // namespace
@@ -50,10 +51,17 @@ namespace
 int thermo_set_ref(Ctx* c, const double* thref, const double* threfh)
 {
     const int kcells = c->gd.kcells;
-    if (!c->thref_d) MHH_CUDA_CHECK(cudaMalloc(&c->thref_d, sizeof(double) * 2 * kcells));
+    // layout: thref | threfh | g/thref | g/threfh.  The two quotient tables are the per-level constants the reference
+    // evaluates per point (grav/thref[k], src/thermo_dry.cxx:76,176): same IEEE value, computed once on the host.
+    if (!c->thref_d) MHH_CUDA_CHECK(cudaMalloc(&c->thref_d, sizeof(double) * 4 * kcells));
+    std::vector<double> h(4 * (size_t)kcells);
+    for (int k = 0; k < kcells; ++k)
+    {
+        h[k] = thref[k]; h[kcells + k] = threfh[k];
+        h[2 * kcells + k] = kGrav / thref[k]; h[3 * kcells + k] = kGrav / threfh[k];
+    }
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    MHH_CUDA_CHECK(cudaMemcpy(c->thref_d, thref, sizeof(double) * kcells, cudaMemcpyHostToDevice));
-    MHH_CUDA_CHECK(cudaMemcpy(c->thref_d + kcells, threfh, sizeof(double) * kcells, cudaMemcpyHostToDevice));
+    MHH_CUDA_CHECK(cudaMemcpy(c->thref_d, h.data(), sizeof(double) * 4 * kcells, cudaMemcpyHostToDevice));
     return MHH_OK;
 }
 
@@ -62,8 +70,8 @@ int thermo_buoyancy_tend(Ctx* c, double* wt, const double* th)
     if (!c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    if (c->order == 2) MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<2><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, gd));
-    else               MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<4><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, gd));
+    if (c->order == 2) MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<2><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, c->thref_d + 3 * gd.kcells, gd));
+    else               MHH_LAUNCH(c, "buoyancy_tend_kernel", buoyancy_tend_kernel<4><<<l.grid, l.block, 0, c->stream>>>(wt, th, c->thref_d + gd.kcells, c->thref_d + 3 * gd.kcells, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
@@ -73,7 +81,7 @@ int thermo_n2(Ctx* c, double* N2, const double* th)
     if (!c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    MHH_LAUNCH(c, "n2_kernel", n2_kernel<<<l.grid, l.block, 0, c->stream>>>(N2, th, c->thref_d, gd));
+    MHH_LAUNCH(c, "n2_kernel", n2_kernel<<<l.grid, l.block, 0, c->stream>>>(N2, th, c->thref_d + 2 * gd.kcells, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

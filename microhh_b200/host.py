@@ -357,8 +357,15 @@ class Diff:
             return
         g, f = self.grid, self.fields
         sm = self._surface_model()
-        N2 = thermo.get_thermo_field("N2") if thermo is not None and thermo.get_switch() != "0" else None
         planes = surface or {}
+        if thermo is not None and getattr(thermo, "fuse_N2", False):
+            # Thermo_dry: N2 is evaluated inside the evisc kernel from th (no N2 field round trip through HBM)
+            L.check(g.ctx, g.lib.mhh_smag2_exec_viscosity_dry(
+                g.ctx, sm, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sp["th"].fld),
+                L.ptr(planes.get("dudz")), L.ptr(planes.get("dvdz")), L.ptr(planes.get("dbdz")), L.ptr(planes.get("z0m")),
+                C.c_double(self.cs), C.c_double(self.tPr), C.c_double(f.visc), L.ptr(f.sd["evisc"].fld)), "mhh_smag2_exec_viscosity_dry")
+            return
+        N2 = thermo.get_thermo_field("N2") if thermo is not None and thermo.get_switch() != "0" else None
         L.check(g.ctx, g.lib.mhh_smag2_exec_viscosity(
             g.ctx, sm, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(N2),
             L.ptr(planes.get("dudz")), L.ptr(planes.get("dvdz")), L.ptr(planes.get("dbdz")), L.ptr(planes.get("z0m")),

@@ -15,6 +15,7 @@ class Thermo:
 
     def __init__(self, grid, fields, swthermo="dry", thref0=300., thref=None, threfh=None):
         self.grid, self.fields, self.swthermo = grid, fields, swthermo
+        self.fuse_N2 = swthermo == "dry"      # Diff.exec_viscosity evaluates N2 in-kernel (mhh_smag2_exec_viscosity_dry)
         if swthermo not in ("0", "dry"):
             raise L.MhhError(f"{swthermo} is an illegal value for swthermo (this path supports 0 and dry)")
         if swthermo == "dry":

@@ -191,3 +191,28 @@ def test_thermo_dry(cuda_lib, order):
         W.call("ref_thermo_N2", rn2, th, thref)
         assert rel_err(n2[W.kstart:W.kend], rn2[W.kstart:W.kend]) <= 1e-14
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("sm", [0, 1])
+def test_fused_dry_viscosity_equals_two_step_path(cuda_lib, sm):
+    """mhh_smag2_exec_viscosity_dry (N2 evaluated in-kernel from th) is bit-identical to thermo N2 + mhh_smag2_exec_viscosity."""
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    case = make_case(itot=24, jtot=16, ktot=12, alpha=1.3, surface_model=sm, anelastic=True)
+    g, W = _worlds(case)
+    f = H.Fields(g, slist=["th"])
+    for n in "uvw":
+        f.mp[n].fld.copy_(_up(g, case[n]))
+    f.sp["th"].fld.copy_(_up(g, case["s"][0]))
+    rng = np.random.default_rng(2)
+    t = Thermo(g, f, "dry", thref=300. + rng.uniform(0, 1, W.kcells), threfh=300. + rng.uniform(0, 1, W.kcells))
+    b = H.Boundary(g, f, swboundary="surface" if sm else "default")
+    d = H.Diff.factory(g, f, b, "smag2", cs=0.17, tPr=1. / 3.)
+    P = {k: _up(g, v) for k, v in case["planes"].items()}
+    d.exec_viscosity(t, surface=P)                  # fused
+    fused = f.sd["evisc"].fld.cpu().numpy().copy()
+    t.fuse_N2 = False
+    f.sd["evisc"].fld.zero_()
+    d.exec_viscosity(t, surface=P)                  # N2 field, then evisc
+    assert np.array_equal(f.sd["evisc"].fld.cpu().numpy(), fused)
+    g.close(); W.close()
