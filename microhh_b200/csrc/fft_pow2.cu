@@ -186,147 +186,193 @@ namespace
     }
 
     // DIR = -1: real lines -> half-complex; +1: half-complex -> real lines (unnormalised * scale).
-    // STRIDED: element stride sn != 1 (lines adjacent in memory): stage tiles through shared memory.
-    template<int DIR, bool STRIDED>
-    __global__ void __launch_bounds__(BLOCK)
+    // STRIDED: element stride sn != 1 (lines adjacent in memory): tiles are staged through shared memory.
+    // NG: pair groups per CTA.  The CTA stages 2*npairs*NG lines at once (so a strided row of the tile is
+    //     16*NG contiguous doubles for n = 512) and transforms them group after group with the same threads.
+    // The cooperative tile loops use only shifts and ONE line-address computation per thread: BLOCK is a
+    // multiple of the (power-of-two) line count, so a thread always serves the same line (ncu r01: the y passes
+    // sat at 16 % of DRAM throughput behind per-element integer div/mod and 64-byte rows).
+    template<int DIR, bool STRIDED, int NG>
+    __global__ void __launch_bounds__(BLOCK, 3)
     fft_pow2_kernel(const double* __restrict__ in, double* __restrict__ out, const P2Args A)
     {
         extern __shared__ double2 zbuf[];
         const int n = A.n, n8 = n >> 3, nh = n >> 1;
         const int tfn = n8;                              // threads per complex transform
-        const int npairs = BLOCK / tfn;                  // complex transforms per CTA
-        const int lines = 2 * npairs;
+        const int npairs = BLOCK / tfn;                  // complex transforms per group
+        const int lines = 2 * npairs * NG;
         const int NP = pad(n) + 1;                       // slots per pair (odd skew between pairs)
         const int p = threadIdx.x / tfn;
         const int tf = threadIdx.x - p * tfn;
-        double2* z = zbuf + p * NP;
         double* zr = reinterpret_cast<double*>(zbuf);
         const int l0 = blockIdx.x * lines;
-        const int la = l0 + 2 * p, lb = la + 1;
-        const bool va = la < A.nlines, vb = lb < A.nlines;
         double2 v[8];
 
-        // ---------------- load ----------------
+        // ---------------- cooperative tile load (strided, or any backward transform) ----------------
         if (STRIDED || DIR > 0)
         {
-            // cooperative, coalesced tile load: slot n of pair q holds (line 2q elem n, line 2q+1 elem n)
-            const int total = lines * n;
-            for (int t = threadIdx.x; t < total; t += BLOCK)
+            if (STRIDED)
             {
-                int ll, m;
-                if (STRIDED) { ll = t % lines; m = t / lines; }
-                else         { m = t & (n - 1); ll = t >> A.log2n; }
-                const int l = l0 + ll;
-                double val = 0.;
-                if (l < A.nlines) val = in[A.base_in + line_addr(l, A.n1, A.s1, A.s2) + (long)m * A.sn];
-                zr[2 * ((ll >> 1) * NP + pad(m)) + (ll & 1)] = val;
-            }
-            __syncthreads();
-            if (DIR < 0)
-            {
-                #pragma unroll
-                for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8)];
+                // thread -> fixed line ll (lines <= BLOCK; for n = 8 a thread serves lines ll, ll + BLOCK),
+                // elements m = m0, m0 + BLOCK/lines, ...
+                const int lw = lines < BLOCK ? lines : BLOCK;
+                const int llog = 31 - __clz(lw);
+                const int mstep = BLOCK >> llog;
+                for (int ll = threadIdx.x & (lw - 1); ll < lines; ll += BLOCK)
+                {
+                    const int l = l0 + ll;
+                    double* dst = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
+                    if (l < A.nlines)
+                    {
+                        const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
+                        #pragma unroll 8
+                        for (int m = threadIdx.x >> llog; m < n; m += mstep)
+                            dst[2 * pad(m)] = src[(long)m * A.sn];
+                    }
+                    else
+                        for (int m = threadIdx.x >> llog; m < n; m += mstep) dst[2 * pad(m)] = 0.;
+                }
             }
             else
             {
-                // Z_n = A_n + i B_n rebuilt from the two half-complex lines
-                #pragma unroll
-                for (int m = 0; m < 8; ++m)
+                // contiguous lines: a thread keeps its element offsets and walks the lines (one address per line)
+                const int rp = (BLOCK >> A.log2n) > 0 ? (BLOCK >> A.log2n) : 1;
+                for (int ll = threadIdx.x >> A.log2n; ll < lines; ll += rp)
                 {
-                    const int pos = tf + m * n8;
-                    const int np = pos <= nh ? pos : n - pos;
-                    const bool self = (np == 0) || (np == nh);
-                    const double s = pos <= nh ? 1. : -1.;
-                    const double2 re = z[pad(np)];
-                    const double2 im = self ? make_double2(0., 0.) : z[pad(n - np)];
-                    v[m] = make_double2(re.x - s * im.y, s * im.x + re.y);
+                    const int l = l0 + ll;
+                    double* dst = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
+                    if (l < A.nlines)
+                    {
+                        const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
+                        for (int m = threadIdx.x & (n - 1); m < n; m += BLOCK) dst[2 * pad(m)] = src[m];
+                    }
+                    else
+                        for (int m = threadIdx.x & (n - 1); m < n; m += BLOCK) dst[2 * pad(m)] = 0.;
                 }
             }
             __syncthreads();
         }
-        else
-        {
-            const double* pa = in + A.base_in + line_addr(va ? la : 0, A.n1, A.s1, A.s2);
-            const double* pb = in + A.base_in + line_addr(vb ? lb : 0, A.n1, A.s1, A.s2);
-            #pragma unroll
-            for (int m = 0; m < 8; ++m)
-            {
-                const int pos = tf + m * n8;
-                v[m] = make_double2(va ? pa[pos] : 0., vb ? pb[pos] : 0.);
-            }
-        }
 
-        run<DIR>(v, z, A, tf);
+        #pragma unroll 1
+        for (int g = 0; g < NG; ++g)
+        {
+            double2* z = zbuf + (g * npairs + p) * NP;
+            const int la = l0 + 2 * (g * npairs + p), lb = la + 1;
+            const bool va = la < A.nlines, vb = lb < A.nlines;
 
-        // ---------------- store ----------------
-        if (DIR > 0)
-        {
-            if (!STRIDED)
+            if (STRIDED || DIR > 0)
             {
-                double* qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
-                double* qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
-                #pragma unroll
-                for (int m = 0; m < 8; ++m)
+                if (DIR < 0)
                 {
-                    const int pos = tf + m * n8;
-                    if (va) qa[pos] = v[m].x * A.scale;
-                    if (vb) qb[pos] = v[m].y * A.scale;
-                }
-                return;
-            }
-            __syncthreads();
-            #pragma unroll
-            for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
-            __syncthreads();
-        }
-        else
-        {
-            // result to natural order in shared memory, then the Hermitian split
-            if (A.nst > 1) __syncthreads();
-            #pragma unroll
-            for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
-            __syncthreads();
-            double* qa = nullptr; double* qb = nullptr;
-            if (!STRIDED)
-            {
-                qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
-                qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
-            }
-            // k = tf + m*n8 for m < 4 covers 0..n/2-1; thread 0 also does k = n/2
-            #pragma unroll
-            for (int m = 0; m < 5; ++m)
-            {
-                if (m == 4 && tf != 0) break;
-                const int k = (m == 4) ? nh : tf + m * n8;
-                const int kn = (k == 0) ? 0 : n - k;
-                const double2 zk = z[pad(k)], zn = z[pad(kn)];
-                const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
-                const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
-                const bool has_im = (k > 0) && (k < nh);
-                if (!STRIDED)
-                {
-                    if (va) { qa[k] = are * A.scale; if (has_im) qa[n - k] = aim * A.scale; }
-                    if (vb) { qb[k] = bre * A.scale; if (has_im) qb[n - k] = bim * A.scale; }
+                    #pragma unroll
+                    for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8)];
                 }
                 else
                 {
-                    z[pad(k)] = make_double2(are, bre);
-                    if (has_im) z[pad(n - k)] = make_double2(aim, bim);
+                    // Z_n = A_n + i B_n rebuilt from the two half-complex lines
+                    #pragma unroll
+                    for (int m = 0; m < 8; ++m)
+                    {
+                        const int pos = tf + m * n8;
+                        const int np = pos <= nh ? pos : n - pos;
+                        const bool self = (np == 0) || (np == nh);
+                        const double sg = pos <= nh ? 1. : -1.;
+                        const double2 re = z[pad(np)];
+                        const double2 im = self ? make_double2(0., 0.) : z[pad(n - np)];
+                        v[m] = make_double2(re.x - sg * im.y, sg * im.x + re.y);
+                    }
+                }
+                __syncthreads();
+            }
+            else
+            {
+                const double* pa = in + A.base_in + line_addr(va ? la : 0, A.n1, A.s1, A.s2);
+                const double* pb = in + A.base_in + line_addr(vb ? lb : 0, A.n1, A.s1, A.s2);
+                #pragma unroll
+                for (int m = 0; m < 8; ++m)
+                {
+                    const int pos = tf + m * n8;
+                    v[m] = make_double2(va ? pa[pos] : 0., vb ? pb[pos] : 0.);
                 }
             }
-            if (!STRIDED) return;
-            __syncthreads();
-        }
-        // cooperative coalesced tile store (STRIDED only)
-        {
-            const int total = lines * n;
-            for (int t = threadIdx.x; t < total; t += BLOCK)
+
+            run<DIR>(v, z, A, tf);
+
+            // ---------------- result back to shared memory / straight to global ----------------
+            if (DIR > 0)
             {
-                const int ll = t % lines, m = t / lines;
+                if (!STRIDED)
+                {
+                    double* qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
+                    double* qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
+                    #pragma unroll
+                    for (int m = 0; m < 8; ++m)
+                    {
+                        const int pos = tf + m * n8;
+                        if (va) qa[pos] = v[m].x * A.scale;
+                        if (vb) qb[pos] = v[m].y * A.scale;
+                    }
+                    continue;
+                }
+                __syncthreads();
+                #pragma unroll
+                for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
+                __syncthreads();
+            }
+            else
+            {
+                // result to natural order in shared memory, then the Hermitian split
+                if (A.nst > 1) __syncthreads();
+                #pragma unroll
+                for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
+                __syncthreads();
+                double* qa = nullptr; double* qb = nullptr;
+                if (!STRIDED)
+                {
+                    qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
+                    qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
+                }
+                // k = tf + m*n8 for m < 4 covers 0..n/2-1; thread 0 also does k = n/2
+                #pragma unroll
+                for (int m = 0; m < 5; ++m)
+                {
+                    if (m == 4 && tf != 0) break;
+                    const int k = (m == 4) ? nh : tf + m * n8;
+                    const int kn = (k == 0) ? 0 : n - k;
+                    const double2 zk = z[pad(k)], zn = z[pad(kn)];
+                    const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
+                    const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
+                    const bool has_im = (k > 0) && (k < nh);
+                    if (!STRIDED)
+                    {
+                        if (va) { qa[k] = are * A.scale; if (has_im) qa[n - k] = aim * A.scale; }
+                        if (vb) { qb[k] = bre * A.scale; if (has_im) qb[n - k] = bim * A.scale; }
+                    }
+                    else
+                    {
+                        z[pad(k)] = make_double2(are, bre);
+                        if (has_im) z[pad(n - k)] = make_double2(aim, bim);
+                    }
+                }
+                if (STRIDED) __syncthreads();
+            }
+        }
+        if (!STRIDED) return;
+
+        // ---------------- cooperative coalesced tile store (STRIDED only) ----------------
+        {
+            const int lw = lines < BLOCK ? lines : BLOCK;
+            const int llog = 31 - __clz(lw);
+            const int mstep = BLOCK >> llog;
+            for (int ll = threadIdx.x & (lw - 1); ll < lines; ll += BLOCK)
+            {
                 const int l = l0 + ll;
-                if (l < A.nlines)
-                    out[A.base_out + line_addr(l, A.n1o, A.s1o, A.s2o) + (long)m * A.sno]
-                        = zr[2 * ((ll >> 1) * NP + pad(m)) + (ll & 1)] * A.scale;
+                if (l >= A.nlines) continue;
+                double* dst = out + A.base_out + line_addr(l, A.n1o, A.s1o, A.s2o);
+                const double* src = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
+                #pragma unroll 8
+                for (int m = threadIdx.x >> llog; m < n; m += mstep)
+                    dst[(long)m * A.sno] = src[2 * pad(m)] * A.scale;
             }
         }
     }
@@ -375,27 +421,36 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     A.scale = L.scale;
     const bool strided = (L.sn != 1) || (L.sno != 1);
     const int npairs = BLOCK / (plan.n / 8);
-    const int lines = 2 * npairs;
-    const size_t smem = (size_t)npairs * ((plan.n + plan.n / 8) + 1) * sizeof(double2);
+    // strided (y) passes: two pair groups per CTA when that still leaves >= 2 CTAs of work per SM and fits 3 CTAs/SM
+    constexpr int NGS = 2;
+    const size_t pair_bytes = (size_t)((plan.n + plan.n / 8) + 1) * sizeof(double2);
+    const bool wide = strided && (size_t)NGS * npairs * pair_bytes <= 76 * 1024 && L.nlines >= 2 * npairs * NGS * 296;
+    const int ng = wide ? NGS : 1;
+    const int lines = 2 * npairs * ng;
+    const size_t smem = (size_t)npairs * ng * pair_bytes;
     const int nblocks = (L.nlines + lines - 1) / lines;
     static bool attr = false;
     if (!attr)
     {
-        cudaFuncSetAttribute(fft_pow2_kernel<-1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<-1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<-1, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<-1, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<1, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<1, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<-1, true, NGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        cudaFuncSetAttribute(fft_pow2_kernel<1, true, NGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
         attr = true;
     }
     if (dir < 0)
     {
-        if (strided) MHH_LAUNCH(c, "fft_fwd_y", fft_pow2_kernel<-1, true><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
-        else         MHH_LAUNCH(c, "fft_fwd_x", fft_pow2_kernel<-1, false><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+        if (strided && wide) MHH_LAUNCH(c, "fft_fwd_y", (fft_pow2_kernel<-1, true, NGS><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
+        else if (strided)    MHH_LAUNCH(c, "fft_fwd_y", (fft_pow2_kernel<-1, true, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
+        else                 MHH_LAUNCH(c, "fft_fwd_x", (fft_pow2_kernel<-1, false, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
     }
     else
     {
-        if (strided) MHH_LAUNCH(c, "fft_bwd_y", fft_pow2_kernel<1, true><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
-        else         MHH_LAUNCH(c, "fft_bwd_x", fft_pow2_kernel<1, false><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A));
+        if (strided && wide) MHH_LAUNCH(c, "fft_bwd_y", (fft_pow2_kernel<1, true, NGS><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
+        else if (strided)    MHH_LAUNCH(c, "fft_bwd_y", (fft_pow2_kernel<1, true, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
+        else                 MHH_LAUNCH(c, "fft_bwd_x", (fft_pow2_kernel<1, false, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
     }
     MHH_LAUNCH_CHECK();
     return MHH_OK;
