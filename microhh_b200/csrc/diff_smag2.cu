@@ -15,8 +15,19 @@ namespace mhh
 namespace
 {
     constexpr int KCHUNK = MHH_KCHUNK;
+#ifndef MHH_TILE_X
+#define MHH_TILE_X 32
+#endif
 
     __device__ __forceinline__ double pow2(double x) { return x * x; }
+
+    // load on a once-per-column path (wall rows): the index passes through an opaque asm so that the compiler does not
+    // hoist the address out of the k loop, where it would cost two registers (or a spill) on every level
+    __device__ __forceinline__ double rare_load(const double* __restrict__ p, int idx)
+    {
+        asm volatile("" : "+r"(idx));
+        return p[idx];
+    }
 
     // MODE 0: thermo on (calc_evisc), 1: neutral (calc_evisc_neutral), 2: strain2 only (stage test),
     // MODE 3: as 0 with N2 = g/thref * dth/dz (calc_N2, src/thermo_dry.cxx:66-79) evaluated on the fly from th: the N2 pointer
@@ -314,6 +325,173 @@ namespace
         }
     }
 
+    // Shared-memory variant of the kernel above (same expression trees, bit-identical results).  A CTA owns a TX x TY
+    // tile of columns and marches k through its chunk; the (TX+2) x (TY+2) tile planes of evisc,u,v,w live in a ring of
+    // four shared-memory slots filled by cp.async two levels ahead.  Per point and level: 25 shared-memory loads and the
+    // 3 tendency read-modify-writes; no global load sits on the dependent path (ncu r01b: the register-queue kernel
+    // was long-scoreboard bound at 2 CTAs/SM).
+    template<bool SURF, int TX, int TY>
+    __global__ void __launch_bounds__(TX * TY, 2)
+    smag2_diff_uvw_tile_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
+                               const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
+                               const double* __restrict__ evisc,
+                               const double* __restrict__ ufluxbot, const double* __restrict__ ufluxtop,
+                               const double* __restrict__ vfluxbot, const double* __restrict__ vfluxtop,
+                               const double visc, const GridD gd)
+    {
+        using Map = TileMap<TX, TY, 1>;
+        constexpr int W = Map::W, PS = Map::N, NS = 4;
+        __shared__ double sm[NS][4][PS];                 // [slot][evisc,u,v,w][tile plane]
+        __shared__ double met[6][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi at k0-1 .. k1
+
+        const int tid = threadIdx.y * TX + threadIdx.x;
+        const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
+        const int i = i0 + threadIdx.x, j = j0 + threadIdx.y;
+        const bool live = (i < gd.iend) && (j < gd.jend);
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
+        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+
+        Map map;
+        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
+        {
+            if (k <= k1)
+            {
+                const int sl = (k - k0 + 1) & (NS - 1);
+                const long off = (long)k * kk;
+                map.issue(sm[sl][0], evisc + off, tid); map.issue(sm[sl][1], u + off, tid);
+                map.issue(sm[sl][2], v + off, tid);     map.issue(sm[sl][3], w + off, tid);
+            }
+            cp_async_commit();
+        };
+        stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
+        if (tid < KCHUNK + 2)
+        {
+            const int k = min(k0 - 1 + tid, gd.kcells - 1);
+            met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
+            met[3][tid] = gd.rhorefh_i[k]; met[4][tid] = gd.dzi[k]; met[5][tid] = gd.dzhi[k];
+        }
+
+        // tile-plane offsets of the centre and its neighbours
+        const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
+        const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W, cwn = c + W - 1, cws = c - W - 1, ces = c - W + 1;
+
+        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        __syncthreads();
+        double e_b, e_c, e_wb, e_w, e_sb, e_s, e_eb, e_nb, u_b, u_c, u_eb, v_b, v_c, v_nb, w_b, w_c, w_w, w_s;
+        {
+            const double* B = sm[0][0]; const double* C = sm[1][0];
+            e_b = B[c]; e_wb = B[cw]; e_sb = B[cs]; e_eb = B[ce]; e_nb = B[cn];
+            e_c = C[c]; e_w = C[cw]; e_s = C[cs];
+            u_b = B[PS + c]; u_eb = B[PS + ce]; u_c = C[PS + c];
+            v_b = B[2 * PS + c]; v_nb = B[2 * PS + cn]; v_c = C[2 * PS + c];
+            w_b = B[3 * PS + c]; w_c = C[3 * PS + c]; w_w = C[3 * PS + cw]; w_s = C[3 * PS + cs];
+        }
+
+        int ijk = ij + k0 * kk;
+        double ut_c = 0., vt_c = 0., wt_c = 0.;
+        if (live) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
+        for (int k = k0; k < k1; ++k, ijk += kk)
+        {
+            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            __syncthreads();                             // ... for every thread; everyone is done with plane k-1
+            stage(k + 3);                                // into the slot of plane k-1
+            // tendencies of the next level: in flight during this level's arithmetic
+            double ut_n = 0., vt_n = 0., wt_n = 0.;
+            if (live && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
+
+            const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
+            const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
+            const bool bot = SURF && (k == gd.kstart);
+            const bool top = SURF && (k == gd.kend - 1);
+            const int km = k - k0 + 1;                   // row of level k in met[]
+            const double rho = met[0][km], rhoh_t = met[1][km + 1], rhoh_b = met[1][km];
+            const double rho_i = met[2][km];
+            const double dzi = met[4][km], dzhi_t = met[5][km + 1], dzhi_b = met[5][km];
+
+            const double e_t = T[c], e_wt = T[cw], e_st = T[cs];
+            const double e_e = C[ce], e_n = C[cn], e_wn = C[cwn], e_ws = C[cws], e_es = C[ces];
+            const double u_t = T[PS + c], u_e = C[PS + ce], u_w = C[PS + cw], u_n = C[PS + cn], u_s = C[PS + cs];
+            const double u_es = C[PS + ces];
+            const double v_t = T[2 * PS + c], v_n = C[2 * PS + cn], v_e = C[2 * PS + ce], v_w = C[2 * PS + cw], v_s = C[2 * PS + cs];
+            const double v_wn = C[2 * PS + cwn];
+            const double w_t = T[3 * PS + c], w_wt = T[3 * PS + cw], w_st = T[3 * PS + cs];
+            const double w_e = C[3 * PS + ce], w_n = C[3 * PS + cn];
+
+            // ---- u: src/diff_smag2.cxx:395-467
+            {
+                const double evisce = e_c + visc;
+                const double eviscw = e_w + visc;
+                const double eviscn = 0.25 * (e_w + e_c + e_wn + e_n) + visc;
+                const double eviscs = 0.25 * (e_ws + e_s + e_w + e_c) + visc;
+                const double evisct = 0.25 * (e_w + e_c + e_wt + e_t) + visc;
+                const double eviscb = 0.25 * (e_wb + e_b + e_w + e_c) + visc;
+
+                const double hor =
+                    + ( evisce * (u_e - u_c) * dxi
+                      - eviscw * (u_c - u_w) * dxi ) * 2. * dxi
+                    + ( eviscn * ((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
+                      - eviscs * ((u_c - u_s) * dyi + (v_c - v_w) * dxi) ) * dyi;
+                const double grad_t = (u_t - u_c) * dzhi_t + (w_t - w_wt) * dxi;
+                const double grad_b = (u_c - u_b) * dzhi_b + (w_c - w_w) * dxi;
+                double ver;
+                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * rare_load(ufluxbot, ij), rho, rho_i ) * dzi;
+                else if (top) ver = div_by( -rhoh_t * rare_load(ufluxtop, ij) - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                if (live) ut[ijk] = ut_c + (hor + ver);
+            }
+            // ---- v: src/diff_smag2.cxx:497-569
+            {
+                const double evisce = 0.25 * (e_s + e_c + e_es + e_e) + visc;
+                const double eviscw = 0.25 * (e_ws + e_w + e_s + e_c) + visc;
+                const double eviscn = e_c + visc;
+                const double eviscs = e_s + visc;
+                const double evisct = 0.25 * (e_s + e_c + e_st + e_t) + visc;
+                const double eviscb = 0.25 * (e_sb + e_b + e_s + e_c) + visc;
+
+                const double hor =
+                    + ( evisce * ((v_e - v_c) * dxi + (u_e - u_es) * dyi)
+                      - eviscw * ((v_c - v_w) * dxi + (u_c - u_s) * dyi) ) * dxi
+                    + ( eviscn * (v_n - v_c) * dyi
+                      - eviscs * (v_c - v_s) * dyi ) * 2. * dyi;
+                const double grad_t = (v_t - v_c) * dzhi_t + (w_t - w_st) * dyi;
+                const double grad_b = (v_c - v_b) * dzhi_b + (w_c - w_s) * dyi;
+                double ver;
+                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * rare_load(vfluxbot, ij), rho, rho_i ) * dzi;
+                else if (top) ver = div_by( -rhoh_t * rare_load(vfluxtop, ij) - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
+                if (live) vt[ijk] = vt_c + (hor + ver);
+            }
+            // ---- w: src/diff_smag2.cxx:594-614 (k from kstart+1)
+            if (k > gd.kstart)
+            {
+                const double evisce = 0.25 * (e_b + e_c + e_eb + e_e) + visc;
+                const double eviscw = 0.25 * (e_wb + e_w + e_b + e_c) + visc;
+                const double eviscn = 0.25 * (e_b + e_c + e_nb + e_n) + visc;
+                const double eviscs = 0.25 * (e_sb + e_s + e_b + e_c) + visc;
+                const double evisct = e_c + visc;
+                const double eviscb = e_b + visc;
+                const double wd =
+                    + ( evisce * ((w_e - w_c) * dxi + (u_e - u_eb) * dzhi_b)
+                      - eviscw * ((w_c - w_w) * dxi + (u_c - u_b) * dzhi_b) ) * dxi
+                    + ( eviscn * ((w_n - w_c) * dyi + (v_n - v_nb) * dzhi_b)
+                      - eviscs * ((w_c - w_s) * dyi + (v_c - v_b) * dzhi_b) ) * dyi
+                    + div_by( rho * evisct * (w_t - w_c) * dzi
+                            - met[0][km - 1] * eviscb * (w_c - w_b) * met[4][km - 1], rhoh_b, met[3][km] ) * 2. * dzhi_b;
+                if (live) wt[ijk] = wt_c + wd;
+            }
+            e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
+            u_b = u_c; u_c = u_t; u_eb = u_e;
+            v_b = v_c; v_c = v_t; v_nb = v_n;
+            w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
+            ut_c = ut_n; vt_c = vt_n; wt_c = wt_n;
+        }
+        cp_async_wait<0>();
+    }
+
     // diff_c, src/diff_smag2.cxx:620-708
     template<bool SURF>
     __global__ void __launch_bounds__(256, MHH_MINB)
@@ -462,12 +640,16 @@ int smag2_exec(Ctx* c, int surface_model, const double* u, const double* v, cons
 {
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    if (surface_model)
-        MHH_LAUNCH(c, "smag2_diff_uvw_kernel", smag2_diff_uvw_kernel<true><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, gd));
-    else
-        MHH_LAUNCH(c, "smag2_diff_uvw_kernel", smag2_diff_uvw_kernel<false><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                nullptr, nullptr, nullptr, nullptr, visc, gd));
+    {
+        constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
+        const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+        if (surface_model)
+            MHH_LAUNCH(c, "smag2_diff_uvw_kernel", (smag2_diff_uvw_tile_kernel<true, TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
+                    ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, gd)));
+        else
+            MHH_LAUNCH(c, "smag2_diff_uvw_kernel", (smag2_diff_uvw_tile_kernel<false, TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
+                    nullptr, nullptr, nullptr, nullptr, visc, gd)));
+    }
     MHH_LAUNCH_CHECK();
     for (int n = 0; n < nscalars; ++n)
     {

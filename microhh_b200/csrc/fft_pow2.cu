@@ -208,47 +208,27 @@ namespace
         const int l0 = blockIdx.x * lines;
         double2 v[8];
 
-        // ---------------- cooperative tile load (strided, or any backward transform) ----------------
-        if (STRIDED || DIR > 0)
+        // ---------------- cooperative tile load (strided passes only) ----------------
+        if (STRIDED)
         {
-            if (STRIDED)
+            // thread -> fixed line ll (lines <= BLOCK; for n = 8 a thread serves lines ll, ll + BLOCK),
+            // elements m = m0, m0 + BLOCK/lines, ...
+            const int lw = lines < BLOCK ? lines : BLOCK;
+            const int llog = 31 - __clz(lw);
+            const int mstep = BLOCK >> llog;
+            for (int ll = threadIdx.x & (lw - 1); ll < lines; ll += BLOCK)
             {
-                // thread -> fixed line ll (lines <= BLOCK; for n = 8 a thread serves lines ll, ll + BLOCK),
-                // elements m = m0, m0 + BLOCK/lines, ...
-                const int lw = lines < BLOCK ? lines : BLOCK;
-                const int llog = 31 - __clz(lw);
-                const int mstep = BLOCK >> llog;
-                for (int ll = threadIdx.x & (lw - 1); ll < lines; ll += BLOCK)
+                const int l = l0 + ll;
+                double* dst = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
+                if (l < A.nlines)
                 {
-                    const int l = l0 + ll;
-                    double* dst = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
-                    if (l < A.nlines)
-                    {
-                        const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
-                        #pragma unroll 8
-                        for (int m = threadIdx.x >> llog; m < n; m += mstep)
-                            dst[2 * pad(m)] = src[(long)m * A.sn];
-                    }
-                    else
-                        for (int m = threadIdx.x >> llog; m < n; m += mstep) dst[2 * pad(m)] = 0.;
+                    const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
+                    #pragma unroll 8
+                    for (int m = threadIdx.x >> llog; m < n; m += mstep)
+                        dst[2 * pad(m)] = src[(long)m * A.sn];
                 }
-            }
-            else
-            {
-                // contiguous lines: a thread keeps its element offsets and walks the lines (one address per line)
-                const int rp = (BLOCK >> A.log2n) > 0 ? (BLOCK >> A.log2n) : 1;
-                for (int ll = threadIdx.x >> A.log2n; ll < lines; ll += rp)
-                {
-                    const int l = l0 + ll;
-                    double* dst = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
-                    if (l < A.nlines)
-                    {
-                        const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
-                        for (int m = threadIdx.x & (n - 1); m < n; m += BLOCK) dst[2 * pad(m)] = src[m];
-                    }
-                    else
-                        for (int m = threadIdx.x & (n - 1); m < n; m += BLOCK) dst[2 * pad(m)] = 0.;
-                }
+                else
+                    for (int m = threadIdx.x >> llog; m < n; m += mstep) dst[2 * pad(m)] = 0.;
             }
             __syncthreads();
         }
@@ -260,7 +240,7 @@ namespace
             const int la = l0 + 2 * (g * npairs + p), lb = la + 1;
             const bool va = la < A.nlines, vb = lb < A.nlines;
 
-            if (STRIDED || DIR > 0)
+            if (STRIDED)
             {
                 if (DIR < 0)
                 {
@@ -284,7 +264,7 @@ namespace
                 }
                 __syncthreads();
             }
-            else
+            else if (DIR < 0)
             {
                 const double* pa = in + A.base_in + line_addr(va ? la : 0, A.n1, A.s1, A.s2);
                 const double* pb = in + A.base_in + line_addr(vb ? lb : 0, A.n1, A.s1, A.s2);
@@ -293,6 +273,30 @@ namespace
                 {
                     const int pos = tf + m * n8;
                     v[m] = make_double2(va ? pa[pos] : 0., vb ? pb[pos] : 0.);
+                }
+            }
+            else
+            {
+                // contiguous half-complex lines: Z_pos = A_pos + i B_pos rebuilt straight from global memory; the
+                // mirrored element n - pos is a second (L1-resident) load instead of a shared-memory round trip
+                const double* pa = in + A.base_in + line_addr(va ? la : 0, A.n1, A.s1, A.s2);
+                const double* pb = in + A.base_in + line_addr(vb ? lb : 0, A.n1, A.s1, A.s2);
+                double a1[8], a2[8], b1[8], b2[8];
+                #pragma unroll
+                for (int m = 0; m < 8; ++m)
+                {
+                    const int pos = tf + m * n8;
+                    const int mir = (n - pos) & (n - 1);
+                    a1[m] = va ? pa[pos] : 0.; a2[m] = va ? pa[mir] : 0.;
+                    b1[m] = vb ? pb[pos] : 0.; b2[m] = vb ? pb[mir] : 0.;
+                }
+                #pragma unroll
+                for (int m = 0; m < 8; ++m)
+                {
+                    const int pos = tf + m * n8;
+                    if (pos == 0 || pos == nh) v[m] = make_double2(a1[m], b1[m]);
+                    else if (pos < nh)         v[m] = make_double2(a1[m] - b2[m], a2[m] + b1[m]);
+                    else                       v[m] = make_double2(a2[m] + b1[m], b2[m] - a1[m]);
                 }
             }
 

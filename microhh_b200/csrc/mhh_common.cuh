@@ -168,6 +168,46 @@ __device__ __forceinline__ void prefetch_l2(const void* p)
 #endif
 }
 
+// ---- asynchronous staging of ghost-celled (i,j) tiles into shared memory ---------------------------------------------
+// The k-marching stencil kernels keep a ring of tile planes (interior TX x TY plus a halo of H) in shared memory.  Planes
+// are fetched with cp.async (LDGSTS, 8-byte elements: ghost-celled rows are only 8-byte aligned) two levels ahead of
+// the level being computed, so the global-memory latency overlaps the arithmetic of two full levels without holding
+// the loads in registers; horizontal neighbours then come from shared memory instead of the L1 wavefront path.
+__device__ __forceinline__ void cp_async8(double* smem, const double* g)
+{
+    const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(s), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template<int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+template<int TX, int TY, int H>
+struct TileMap
+{
+    static constexpr int W = TX + 2 * H, HT = TY + 2 * H, N = W * HT, NT = TX * TY, R = (N + NT - 1) / NT;
+    int g[R];      // offset of this thread's r-th element within a global (i,j) plane (clamped into the plane); -1: none
+
+    // (i0, j0): first interior point of the tile
+    __device__ __forceinline__ void init(const int i0, const int j0, const int icells, const int jcells, const int tid)
+    {
+        #pragma unroll
+        for (int r = 0; r < R; ++r)
+        {
+            const int e = tid + r * NT;
+            const int row = e / W, col = e - row * W;
+            const int gi = min(i0 - H + col, icells - 1), gj = min(j0 - H + row, jcells - 1);
+            g[r] = (e < N) ? gi + gj * icells : -1;
+        }
+    }
+    // one plane of one field: sm[e] = gplane[g(e)]
+    __device__ __forceinline__ void issue(double* sm, const double* __restrict__ gplane, const int tid) const
+    {
+        #pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (r + 1 < R || g[r] >= 0) cp_async8(sm + tid + r * NT, gplane + g[r]);
+    }
+};
+
 // ---- finite-difference helpers (restated from include/finite_difference.h:34-156) ----------
 namespace fd
 {
