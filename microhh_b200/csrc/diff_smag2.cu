@@ -37,23 +37,52 @@ namespace
     // v at (i-1,i,i+1) x (j,j+1) x (k-1,k,k+1) and w at the 5-point star on levels k and k+1.  Marching k, the columns
     // u_c, u_e, v_c, v_n (three levels) and the w star (two levels) stay in registers: 18 global loads per point instead
     // of 31 (ncu r01: L1 68 %, DRAM 30 %).
-    template<bool SURF, int MODE>
-    __global__ void __launch_bounds__(256, 3)
+    // Shared-memory tiles: the (TX+2) x (TY+2) planes of u,v,w sit in a ring of four slots filled by cp.async two levels
+    // ahead (see TileMap); the columns u_c, u_e, v_c, v_n (levels k-1, k) and the w star (level k) stay in registers.
+    template<bool SURF, int MODE, int TX, int TY>
+    __global__ void __launch_bounds__(TX * TY, 3)
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
                  const double* __restrict__ dbdz, const double* __restrict__ z0m,
                  const double* __restrict__ mlen0, const double tPr, const double visc, const GridD gd)
     {
-        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
-        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
-        if (i >= gd.iend || j >= gd.jend) return;
-        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
-        const int ij = i + j * jj;
+        using Map = TileMap<TX, TY, 1>;
+        constexpr int W = Map::W, PS = Map::N, NS = 4;
+        __shared__ double sm[NS][3][PS];                 // [slot][u,v,w][tile plane]
+        __shared__ double met[5][KCHUNK + 2];            // dzi, dzhi, z, mlen0, g/thref at k0-1 .. k1
+
+        const int tid = threadIdx.y * TX + threadIdx.x;
+        const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
+        const int i = i0 + threadIdx.x, j = j0 + threadIdx.y;
+        const bool live = (i < gd.iend) && (j < gd.jend);
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         const double tPr_i = 1. / tPr;
+
+        Map map;
+        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
+        {
+            if (k <= k1)
+            {
+                const int sl = (k - k0 + 1) & (NS - 1);
+                const long off = (long)k * kk;
+                map.issue(sm[sl][0], u + off, tid); map.issue(sm[sl][1], v + off, tid); map.issue(sm[sl][2], w + off, tid);
+            }
+            cp_async_commit();
+        };
+        stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
+        if (tid < KCHUNK + 2)
+        {
+            const int k = min(k0 - 1 + tid, gd.kcells - 1);
+            met[0][tid] = gd.dzi[k]; met[1][tid] = gd.dzhi[k]; met[2][tid] = gd.z[k];
+            if (MODE != 2) met[3][tid] = mlen0[k];
+            if (MODE == 3) met[4][tid] = mlen0[gd.kcells + k];
+        }
 
         double z0 = 0.;
         if (SURF && MODE != 2) z0 = z0m[ij];
@@ -70,73 +99,88 @@ namespace
                                 + pow2(visc * (v[ijk_top] - v[ijk_top - kk]) * gd.dzhi[gd.kend])));
         }
 
+        const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
+        const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W, cwn = c + W - 1, ces = c - W + 1, cen = c + W + 1;
+
         int ijk = ij + k0 * kk;
-        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk], u_e = u[ijk + ii];
-        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk], v_n = v[ijk + jj];
-        double w_c = w[ijk], w_w = w[ijk - ii], w_e = w[ijk + ii], w_s = w[ijk - jj], w_n = w[ijk + jj];
-        double th_b = 0., th_c = 0.;
-        if (MODE == 3) { th_b = N2[ijk - kk]; th_c = N2[ijk]; }
+        // centre-only columns come straight from global memory, one level ahead of their use
+        double th_b = 0., th_c = 0., th_n = 0., n2_n = 0.;
+        if (MODE == 3) { th_b = N2[ijk - kk]; th_c = N2[ijk]; th_n = N2[ijk + kk]; }
+        if (MODE == 0) n2_n = N2[ijk];
+
+        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        __syncthreads();
+        double u_b, u_c, u_eb, u_e, v_b, v_c, v_nb, v_n, w_c, w_w, w_e, w_s, w_n;
+        {
+            const double* B = sm[0][0]; const double* C = sm[1][0];
+            u_b = B[c]; u_eb = B[ce]; u_c = C[c]; u_e = C[ce];
+            v_b = B[PS + c]; v_nb = B[PS + cn]; v_c = C[PS + c]; v_n = C[PS + cn];
+            w_c = C[2 * PS + c]; w_w = C[2 * PS + cw]; w_e = C[2 * PS + ce]; w_s = C[2 * PS + cs]; w_n = C[2 * PS + cn];
+        }
+        double xz_c, xz_e, yz_c, yz_n;                  // lower-face vertical cross terms of the level being computed
+        {
+            const double dzhi_k = met[1][1];
+            xz_c = 0.125 * pow2((u_c - u_b) * dzhi_k + (w_c - w_w) * dxi);
+            xz_e = 0.125 * pow2((u_e - u_eb) * dzhi_k + (w_e - w_c) * dxi);
+            yz_c = 0.125 * pow2((v_c - v_b) * dzhi_k + (w_c - w_s) * dyi);
+            yz_n = 0.125 * pow2((v_n - v_nb) * dzhi_k + (w_n - w_c) * dyi);
+        }
 
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            if (k + MHH_PF < gd.kcells - 1)
-            {
-                const int pf = ijk + (MHH_PF + 1) * kk;
-                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
-                if (MODE == 0) prefetch_l2(N2 + pf - kk);
-                if (MODE == 3) prefetch_l2(N2 + pf);
-            }
-            const double u_t = u[ijk + kk], u_et = u[ijk + ii + kk];
-            const double u_s = u[ijk - jj], u_es = u[ijk + ii - jj], u_n = u[ijk + jj], u_en = u[ijk + ii + jj];
-            const double v_t = v[ijk + kk], v_nt = v[ijk + jj + kk];
-            const double v_w = v[ijk - ii], v_e = v[ijk + ii], v_wn = v[ijk - ii + jj], v_en = v[ijk + ii + jj];
-            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_et = w[ijk + ii + kk];
-            const double w_st = w[ijk - jj + kk], w_nt = w[ijk + jj + kk];
-            const double dzi_k = gd.dzi[k], dzhi_k = gd.dzhi[k], dzhi_kp = gd.dzhi[k + 1];
+            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            __syncthreads();                             // ... for every thread; everyone is done with plane k-1
+            stage(k + 3);                                // into the slot of plane k-1
+            const double th_t = th_n, n2_c = n2_n;
+            if (MODE == 3 && k + 1 < k1) th_n = N2[ijk + 2 * kk];
+            if (MODE == 0 && k + 1 < k1) n2_n = N2[ijk + kk];
+
+            const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
+            const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
+            const double u_t = T[c], u_et = T[ce];
+            const double u_s = C[cs], u_es = C[ces], u_n = C[cn], u_en = C[cen];
+            const double v_t = T[PS + c], v_nt = T[PS + cn];
+            const double v_w = C[PS + cw], v_e = C[PS + ce], v_wn = C[PS + cwn], v_en = C[PS + cen];
+            const double w_t = T[2 * PS + c], w_wt = T[2 * PS + cw], w_et = T[2 * PS + ce];
+            const double w_st = T[2 * PS + cs], w_nt = T[2 * PS + cn];
+            const int km = k - k0 + 1;                   // row of level k in met[]
+            const double dzi_k = met[0][km], dzhi_kp = met[1][km + 1];
 
             const bool bot = SURF && (k == gd.kstart);
-            double s2;
+            // the four vertical cross terms on the upper face of level k are the lower-face terms of level k+1: they are
+            // evaluated once and carried (same expression, same value)
+            const double xz_t  = 0.125 * pow2((u_t - u_c) * dzhi_kp + (w_t - w_wt) * dxi);
+            const double xz_et = 0.125 * pow2((u_et - u_e) * dzhi_kp + (w_et - w_t) * dxi);
+            const double yz_t  = 0.125 * pow2((v_t - v_c) * dzhi_kp + (w_t - w_st) * dyi);
+            const double yz_nt = 0.125 * pow2((v_nt - v_n) * dzhi_kp + (w_nt - w_t) * dyi);
+            // left-to-right sum of src/diff_smag2.cxx:120-154 (interior) / :80-114 (MO bottom row)
+            double acc = pow2((u_e - u_c) * dxi)
+                       + pow2((v_n - v_c) * dyi)
+                       + pow2((w_t - w_c) * dzi_k)
+                       + 0.125 * pow2((u_c - u_s) * dyi + (v_c - v_w) * dxi)
+                       + 0.125 * pow2((u_e - u_es) * dyi + (v_e - v_c) * dxi)
+                       + 0.125 * pow2((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
+                       + 0.125 * pow2((u_en - u_e) * dyi + (v_en - v_n) * dxi);
             if (bot)
             {
-                const double ugradbot = dudz[ij], vgradbot = dvdz[ij];
-                s2 = 2. * (
-                    + pow2((u_e - u_c) * dxi)
-                    + pow2((v_n - v_c) * dyi)
-                    + pow2((w_t - w_c) * dzi_k)
-                    + 0.125 * pow2((u_c - u_s) * dyi + (v_c - v_w) * dxi)
-                    + 0.125 * pow2((u_e - u_es) * dyi + (v_e - v_c) * dxi)
-                    + 0.125 * pow2((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
-                    + 0.125 * pow2((u_en - u_e) * dyi + (v_en - v_n) * dxi)
-                    + 0.5 * pow2(ugradbot)
-                    + 0.125 * pow2((w_c - w_w) * dxi)
-                    + 0.125 * pow2((w_e - w_c) * dxi)
-                    + 0.125 * pow2((w_t - w_wt) * dxi)
-                    + 0.125 * pow2((w_et - w_t) * dxi)
-                    + 0.5 * pow2(vgradbot)
-                    + 0.125 * pow2((w_c - w_s) * dyi)
-                    + 0.125 * pow2((w_n - w_c) * dyi)
-                    + 0.125 * pow2((w_t - w_st) * dyi)
-                    + 0.125 * pow2((w_nt - w_t) * dyi));
+                acc = acc + 0.5 * pow2(rare_load(dudz, ij));
+                acc = acc + 0.125 * pow2((w_c - w_w) * dxi);
+                acc = acc + 0.125 * pow2((w_e - w_c) * dxi);
+                acc = acc + 0.125 * pow2((w_t - w_wt) * dxi);
+                acc = acc + 0.125 * pow2((w_et - w_t) * dxi);
+                acc = acc + 0.5 * pow2(rare_load(dvdz, ij));
+                acc = acc + 0.125 * pow2((w_c - w_s) * dyi);
+                acc = acc + 0.125 * pow2((w_n - w_c) * dyi);
+                acc = acc + 0.125 * pow2((w_t - w_st) * dyi);
+                acc = acc + 0.125 * pow2((w_nt - w_t) * dyi);
             }
             else
             {
-                s2 = 2. * (
-                    + pow2((u_e - u_c) * dxi)
-                    + pow2((v_n - v_c) * dyi)
-                    + pow2((w_t - w_c) * dzi_k)
-                    + 0.125 * pow2((u_c - u_s) * dyi + (v_c - v_w) * dxi)
-                    + 0.125 * pow2((u_e - u_es) * dyi + (v_e - v_c) * dxi)
-                    + 0.125 * pow2((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
-                    + 0.125 * pow2((u_en - u_e) * dyi + (v_en - v_n) * dxi)
-                    + 0.125 * pow2((u_c - u_b) * dzhi_k + (w_c - w_w) * dxi)
-                    + 0.125 * pow2((u_e - u_eb) * dzhi_k + (w_e - w_c) * dxi)
-                    + 0.125 * pow2((u_t - u_c) * dzhi_kp + (w_t - w_wt) * dxi)
-                    + 0.125 * pow2((u_et - u_e) * dzhi_kp + (w_et - w_t) * dxi)
-                    + 0.125 * pow2((v_c - v_b) * dzhi_k + (w_c - w_s) * dyi)
-                    + 0.125 * pow2((v_n - v_nb) * dzhi_k + (w_n - w_c) * dyi)
-                    + 0.125 * pow2((v_t - v_c) * dzhi_kp + (w_t - w_st) * dyi)
-                    + 0.125 * pow2((v_nt - v_n) * dzhi_kp + (w_nt - w_t) * dyi));
+                acc = acc + xz_c; acc = acc + xz_e; acc = acc + xz_t; acc = acc + xz_et;
+                acc = acc + yz_c; acc = acc + yz_n; acc = acc + yz_t; acc = acc + yz_nt;
             }
+            double s2 = 2. * acc;
+            xz_c = xz_t; xz_e = xz_et; yz_c = yz_t; yz_n = yz_nt;
             s2 = s2 + kDsmall;
 
             double ev;
@@ -148,46 +192,46 @@ namespace
                 double n2;
                 if (MODE == 3)
                 {
-                    const double th_t = N2[ijk + kk];
-                    n2 = mlen0[gd.kcells + k] * 0.5 * (th_t - th_b) * dzi_k;
+                    n2 = met[4][km] * 0.5 * (th_t - th_b) * dzi_k;
                     th_b = th_c; th_c = th_t;
                 }
                 else
-                    n2 = bot ? 0. : N2[ijk];
-                double rit = div_by((bot ? dbdz[ij] : n2) / s2, tPr, tPr_i);
+                    n2 = bot ? 0. : n2_c;
+                double rit = div_by((bot ? rare_load(dbdz, ij) : n2) / s2, tPr, tPr_i);
                 rit = fmin(rit, 1. - kDsmall);
                 if (SURF)
                 {
-                    const double kz = kKappa * (gd.z[k] + z0);
-                    const double m0 = mlen0[k];
+                    const double kz = kKappa * (met[2][km] + z0);
+                    const double m0 = met[3][km];
                     const double mlen = sqrt(1. / (1. / (m0 * m0) + 1. / (kz * kz)));
                     ev = pow2(mlen) * sqrt(s2) * sqrt(1. - rit);
                 }
                 else
-                    ev = pow2(mlen0[k]) * sqrt(s2) * sqrt(1. - rit);
+                    ev = pow2(met[3][km]) * sqrt(s2) * sqrt(1. - rit);
             }
             else
             {
                 if (SURF)
                 {
                     // Mason length with n = 1, src/diff_smag2.cxx:243-247
-                    const double mlen = 1. / (1. / mlen0[k] + 1. / (kKappa * (gd.z[k] + z0)));
+                    const double mlen = 1. / (1. / met[3][km] + 1. / (kKappa * (met[2][km] + z0)));
                     ev = pow2(mlen) * sqrt(s2);
                 }
                 else
                 {
                     // van Driest damping, src/diff_smag2.cxx:206-211
-                    const double fac_bot = 1. - exp(-(gd.z[k] * u_tau_bot) / (26. * visc));
-                    const double fac_top = 1. - exp(-((gd.zsize - gd.z[k]) * u_tau_top) / (26. * visc));
+                    const double fac_bot = 1. - exp(-(met[2][km] * u_tau_bot) / (26. * visc));
+                    const double fac_top = 1. - exp(-((gd.zsize - met[2][km]) * u_tau_top) / (26. * visc));
                     const double fac = fmin(fac_bot, fac_top);
-                    ev = pow2(fac * mlen0[k]) * sqrt(s2);
+                    ev = pow2(fac * met[3][km]) * sqrt(s2);
                 }
             }
-            evisc[ijk] = ev;
-            u_b = u_c; u_c = u_t; u_eb = u_e; u_e = u_et;
-            v_b = v_c; v_c = v_t; v_nb = v_n; v_n = v_nt;
+            if (live) evisc[ijk] = ev;
+            u_c = u_t; u_e = u_et;
+            v_c = v_t; v_n = v_nt;
             w_c = w_t; w_w = w_wt; w_e = w_et; w_s = w_st; w_n = w_nt;
         }
+        cp_async_wait<0>();
     }
 
     // mirrored wall rows for resolved walls, src/diff_smag2.cxx:214-226, :300-312
@@ -597,29 +641,30 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
         MHH_CUDA_CHECK(cudaMemcpyAsync(c->mlen0_d + gd.kcells, c->thref_d + 2 * gd.kcells, gd.kcells * sizeof(double),
                                        cudaMemcpyDeviceToDevice, c->stream));
     }
-    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
+    const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
     #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd
     if (strain_only == 1)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
-        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 2><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 2, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 2, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
         MHH_LAUNCH_CHECK();
         return MHH_OK;
     }
     if (strain_only == 2)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 3><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
-        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 3><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
     }
     else if (N2 != nullptr)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
-        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 0><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
     }
     else
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<true, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
-        else               MHH_LAUNCH(c, "evisc_kernel", evisc_kernel<false, 1><<<l.grid, l.block, 0, c->stream>>>(EV_ARGS));
+        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 1, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 1, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
     }
     #undef EV_ARGS
     MHH_LAUNCH_CHECK();
