@@ -39,7 +39,8 @@ BYTES_PER_POINT = {
     "fft_fwd_x": 16, "fft_fwd_y": 16, "fft_bwd_y": 16, "fft_bwd_x": 16,
     "pres2_tdma_kernel": 32,
     "pres2_out_kernel": 56,
-    "rk_kernel": 128,                # 4 fields x (R a,at ; W a,at)
+    "pres2_out_rk_kernel": 104,      # R p,ut,vt,wt,u,v,w -> W ut,vt,wt,u,v,w (Pres_2::output + RK of u,v,w fused)
+    "rk_kernel": 32,                 # the scalar: R a,at ; W a,at
     "n2_kernel": 16, "buoyancy_tend_kernel": 24,
     "advec2_cfl_kernel": 24, "smag2_dnmul_kernel": 8,
 }

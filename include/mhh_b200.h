@@ -194,6 +194,13 @@ int mhh_set_bc(mhh_ctx* ctx, double* a2d, double* agrad2d, double* aflux2d, int 
 /* --- Timeloop<TF>::exec (src/timeloop.cxx:358; rk3 :250, rk4 :288) -------------------------------------- */
 int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, double dt,
                    int nfields, double* const* a, double* const* at);
+/* Fused tail of the substep (no reference counterpart: Pres_2::output src/pres_2.cxx:365-387 immediately followed by
+ * Timeloop::exec src/timeloop.cxx:358-411 for u,v,w).  Bit-identical to mhh_pres_output / mhh_pres_exec followed by
+ * mhh_rk_substep on (u,v,w); the caller runs mhh_rk_substep on the remaining fields with the same substep. */
+int mhh_pres_output_rk(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
+                       int rkorder, int substep, double dt);
+int mhh_pres_exec_rk(mhh_ctx* ctx, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,
+                     double dt_sub, int rkorder, int substep, double dt);
 double mhh_rk_sub_dt(int rkorder, int substep, double dt);   /* Timeloop::get_sub_time_step :415 */
 
 /* --- Field3d_operators<TF> (include/field3d_operators.h:40-51) and Fields diagnostics -------------------- */

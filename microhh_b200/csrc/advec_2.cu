@@ -15,77 +15,125 @@ namespace
 {
     constexpr int KCHUNK = MHH_KCHUNK;
 
-    // Register queues while marching k: the centre columns of u,v,w at k-1,k,k+1 and the columns the cross terms
-    // need at the neighbouring level (u_e and v_n at k-1; w_w and w_s at k+1).  20 global loads per point instead
-    // of 30 (ncu r01: the kernel was held by L1 wavefront throughput at 80 %, not by HBM).
-    __global__ void __launch_bounds__(256, 3)
+    // A CTA owns a TX x TY tile of columns and marches k through its chunk.  The (TX+2) x (TY+2) tile planes of u,v,w sit in
+    // a ring of four shared-memory slots filled by cp.async two levels ahead (TileMap, mhh_common.cuh); the centre columns
+    // at k-1,k and the cross-term columns (u_e, v_n at k-1; w_w, w_s at k) stay in registers.  Per point and level: 17
+    // shared-memory loads plus the three tendency read-modify-writes, whose loads are issued one level early.
+    template<int TX, int TY>
+    __global__ void __launch_bounds__(TX * TY, 3)
     advec2_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                       const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                       const GridD gd)
     {
-        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
-        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
-        if (i >= gd.iend || j >= gd.jend) return;
+        using Map = TileMap<TX, TY, 1>;
+        constexpr int W = Map::W, PS = Map::N, NS = 4;
+        __shared__ double sm[NS][3][PS];                 // [slot][u,v,w][tile plane]
+        __shared__ double met[6][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi at k0-1 .. k1
 
-        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
+        const int tid = threadIdx.y * TX + threadIdx.x;
+        const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
+        const int i = i0 + threadIdx.x, j = j0 + threadIdx.y;
+        const bool live = (i < gd.iend) && (j < gd.jend);
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
 
-        int ijk = i + j * jj + k0 * kk;
-        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk];
-        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk];
-        double w_b = w[ijk - kk], w_c = w[ijk], w_w = w[ijk - ii], w_s = w[ijk - jj];
+        Map map;
+        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
+        {
+            if (k <= k1)
+            {
+                const int sl = (k - k0 + 1) & (NS - 1);
+                const long off = (long)k * kk;
+                map.issue(sm[sl][0], u + off, tid); map.issue(sm[sl][1], v + off, tid); map.issue(sm[sl][2], w + off, tid);
+            }
+            cp_async_commit();
+        };
+        stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
+        if (tid < KCHUNK + 2)
+        {
+            const int k = min(k0 - 1 + tid, gd.kcells - 1);
+            met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
+            met[3][tid] = gd.rhorefh_i[k]; met[4][tid] = gd.dzi[k]; met[5][tid] = gd.dzhi[k];
+        }
+
+        const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
+        const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W, cwn = c + W - 1, ces = c - W + 1;
+
+        int ijk = ij + k0 * kk;
+        double ut_c = 0., vt_c = 0., wt_c = 0.;
+        if (live) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
+
+        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        __syncthreads();
+        double u_b, u_c, u_eb, v_b, v_c, v_nb, w_b, w_c, w_w, w_s;
+        {
+            const double* B = sm[0][0]; const double* C = sm[1][0];
+            u_b = B[c]; u_eb = B[ce]; u_c = C[c];
+            v_b = B[PS + c]; v_nb = B[PS + cn]; v_c = C[PS + c];
+            w_b = B[2 * PS + c]; w_c = C[2 * PS + c]; w_w = C[2 * PS + cw]; w_s = C[2 * PS + cs];
+        }
 
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            if (k + MHH_PF < gd.kcells - 1)
-            {
-                const int pf = ijk + (MHH_PF + 1) * kk;
-                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf);
-                prefetch_l2(ut + pf - kk); prefetch_l2(vt + pf - kk); prefetch_l2(wt + pf - kk);
-            }
-            const double rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k], rho = gd.rhoref[k], dzi = gd.dzi[k];
-            const double rho_i = gd.rhoref_i[k];
+            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            __syncthreads();                             // ... for every thread; everyone is done with plane k-1
+            stage(k + 3);                                // into the slot of plane k-1
+            double ut_n = 0., vt_n = 0., wt_n = 0.;
+            if (live && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
 
-            const double u_t = u[ijk + kk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
-            const double v_t = v[ijk + kk], v_n = v[ijk + jj], v_e = v[ijk + ii], v_w = v[ijk - ii], v_s = v[ijk - jj];
-            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_st = w[ijk - jj + kk];
-            const double w_e = w[ijk + ii], w_n = w[ijk + jj];
+            const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
+            const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
+            const int km = k - k0 + 1;                   // row of level k in met[]
+            const double rhoh_t = met[1][km + 1], rhoh_b = met[1][km], rho = met[0][km], dzi = met[4][km];
+            const double rho_i = met[2][km];
+
+            const double u_t = T[c], u_e = C[ce], u_w = C[cw], u_n = C[cn], u_s = C[cs], u_es = C[ces];
+            const double v_t = T[PS + c], v_n = C[PS + cn], v_e = C[PS + ce], v_w = C[PS + cw], v_s = C[PS + cs], v_wn = C[PS + cwn];
+            const double w_t = T[2 * PS + c], w_wt = T[2 * PS + cw], w_st = T[2 * PS + cs];
+            const double w_e = C[2 * PS + ce], w_n = C[2 * PS + cn];
 
             // advec_u, src/advec_2.cxx:98-109
-            ut[ijk] +=
+            const double ud =
                 - ( interp2(u_c, u_e) * interp2(u_c, u_e)
                   - interp2(u_w, u_c) * interp2(u_w, u_c) ) * dxi
-                - ( interp2(v[ijk - ii + jj], v_n) * interp2(u_c, u_n)
+                - ( interp2(v_wn, v_n) * interp2(u_c, u_n)
                   - interp2(v_w, v_c) * interp2(u_s, u_c) ) * dyi
                 - div_by( rhoh_t * interp2(w_wt, w_t) * interp2(u_c, u_t)
                         - rhoh_b * interp2(w_w, w_c) * interp2(u_b, u_c), rho, rho_i ) * dzi;
+            if (live) ut[ijk] = ut_c + ud;
 
             // advec_v, src/advec_2.cxx:129-140
-            vt[ijk] +=
-                - ( interp2(u[ijk + ii - jj], u_e) * interp2(v_c, v_e)
+            const double vd =
+                - ( interp2(u_es, u_e) * interp2(v_c, v_e)
                   - interp2(u_s, u_c) * interp2(v_w, v_c) ) * dxi
                 - ( interp2(v_c, v_n) * interp2(v_c, v_n)
                   - interp2(v_s, v_c) * interp2(v_s, v_c) ) * dyi
                 - div_by( rhoh_t * interp2(w_st, w_t) * interp2(v_c, v_t)
                         - rhoh_b * interp2(w_s, w_c) * interp2(v_b, v_c), rho, rho_i ) * dzi;
+            if (live) vt[ijk] = vt_c + vd;
 
             // advec_w, src/advec_2.cxx:160-171 (k from kstart+1)
             if (k > gd.kstart)
             {
-                wt[ijk] +=
+                const double wd =
                     - ( interp2(u_eb, u_e) * interp2(w_c, w_e)
                       - interp2(u_b, u_c) * interp2(w_w, w_c) ) * dxi
                     - ( interp2(v_nb, v_n) * interp2(w_c, w_n)
                       - interp2(v_b, v_c) * interp2(w_s, w_c) ) * dyi
                     - div_by( rho * interp2(w_c, w_t) * interp2(w_c, w_t)
-                            - gd.rhoref[k - 1] * interp2(w_b, w_c) * interp2(w_b, w_c), rhoh_b, gd.rhorefh_i[k] ) * gd.dzhi[k];
+                            - met[0][km - 1] * interp2(w_b, w_c) * interp2(w_b, w_c), rhoh_b, met[3][km] ) * met[5][km];
+                if (live) wt[ijk] = wt_c + wd;
             }
             u_b = u_c; u_c = u_t; u_eb = u_e;
             v_b = v_c; v_c = v_t; v_nb = v_n;
             w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
+            ut_c = ut_n; vt_c = vt_n; wt_c = wt_n;
         }
+        cp_async_wait<0>();
     }
 
     __global__ void __launch_bounds__(256, MHH_MINB)
@@ -162,7 +210,11 @@ int advec2_exec(Ctx* c, const double* u, const double* v, const double* w, doubl
 {
     const GridD& gd = c->gd;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    MHH_LAUNCH(c, "advec2_uvw_kernel", advec2_uvw_kernel<<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, u, v, w, gd));
+    {
+        constexpr int TX = 32, TY = 8;
+        const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+        MHH_LAUNCH(c, "advec2_uvw_kernel", (advec2_uvw_kernel<TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, gd)));
+    }
     MHH_LAUNCH_CHECK();
     for (int n = 0; n < nscalars; ++n)
     {

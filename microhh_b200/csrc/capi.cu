@@ -123,6 +123,7 @@ int transpose_copy(Ctx*, int, double*, const double*);
 int halo_ns(Ctx*, double*, double*, double*, int, int);
 int pres2_solve_spectral_ws(Ctx*, double*, double*);
 int pres2_output_stage(Ctx*, int, double*, double*, double*, double*);
+int pres2_output_rk(Ctx*, double*, double*, double*, double*, double*, double*, double*, int, int, double);
 }  // namespace mhh
 
 using namespace mhh;
@@ -480,6 +481,33 @@ int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
     if ((e = fft_backward_impl(c, c->work_p, p))) return e;
     return mhh_pres_output(c, ut, vt, wt, p);
+}
+
+// Pres_2::output's gradient stage fused with Timeloop::exec for u,v,w (the caller still runs mhh_rk_substep on the
+// remaining prognostic fields with the same substep).  p must carry its ghost row and halos (output stage 0).
+int mhh_pres_output_rk(mhh_ctx* c, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
+                       int rkorder, int substep, double dt)
+{
+    PRES_READY(c);
+    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    return pres2_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
+}
+
+// mhh_pres_exec with the fused last stage: on return u,v,w hold the substep's new velocities and ut,vt,wt the scaled
+// tendencies the next substep starts from
+int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,
+                     double dt_sub, int rkorder, int substep, double dt)
+{
+    PRES_READY(c);
+    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    if (c->npy != 1) { c->last_error = "mhh_pres_exec_rk is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
+    int e;
+    if ((e = mhh_pres_input(c, u, v, w, ut, vt, wt, dt_sub))) return e;
+    if ((e = fft_forward_inplace(c, c->work_p))) return e;
+    if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
+    if ((e = fft_backward_impl(c, c->work_p, p))) return e;
+    if ((e = pres2_output_stage(c, 0, ut, vt, wt, p))) return e;
+    return pres2_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
 }
 
 int mhh_pres_check_divergence(mhh_ctx* c, const double* u, const double* v, const double* w, double* out)

@@ -59,6 +59,16 @@ double rk_sub_dt(int rkorder, int substep, double dt)
     return (rkorder == 3 ? rk3_cB[substep] : rk4_cB[substep]) * dt;
 }
 
+// cB[substep]*dt is formed first, then multiplied by at: (cB*dt)*at as in the reference expression
+void rk_coefs(int rkorder, int substep, double dt, double* cB_dt, double* cA_next, int* zero_all)
+{
+    const int nsub = rkorder == 3 ? 3 : 5;
+    const int substepn = (substep + 1) % nsub;
+    *cB_dt = (rkorder == 3 ? rk3_cB[substep] : rk4_cB[substep]) * dt;
+    *cA_next = rkorder == 3 ? rk3_cA[substepn] : rk4_cA[substepn];
+    *zero_all = substepn == 0;
+}
+
 int rk_substep(Ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
 {
     if ((rkorder != 3 && rkorder != 4) || substep < 0 || substep >= (rkorder == 3 ? 3 : 5))

@@ -431,13 +431,22 @@ class Pres:
         g = self.grid
         L.check(g.ctx, g.lib.mhh_pres_set_values(g.ctx), "mhh_pres_set_values")
 
-    def exec(self, dt, stats=None):
+    def exec(self, dt, stats=None, timeloop=None):
+        """Pres::exec.  With `timeloop` (order 2 only) the gradient stage is fused with Timeloop::exec for u,v,w
+        (mhh_pres_exec_rk): returns True, and the caller must run timeloop.exec(skip=("u", "v", "w"))."""
         if self.swpres == "0":
-            return
+            return False
         g, f = self.grid, self.fields
+        if timeloop is not None and self.swpres == "2":
+            L.check(g.ctx, g.lib.mhh_pres_exec_rk(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
+                                                  L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
+                                                  L.ptr(f.sd["p"].fld), C.c_double(dt), timeloop.rkorder, timeloop.substep,
+                                                  C.c_double(timeloop.dt)), "mhh_pres_exec_rk")
+            return True
         L.check(g.ctx, g.lib.mhh_pres_exec(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
                                            L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
                                            L.ptr(f.sd["p"].fld), C.c_double(dt)), "mhh_pres_exec")
+        return False
 
     def check_divergence(self):
         g, f = self.grid, self.fields
@@ -492,10 +501,10 @@ class Timeloop:
         self.time = self.itime / self.ifactor
         self.iteration += 1
 
-    def exec(self):
-        """Timeloop::exec, src/timeloop.cxx:358-411."""
+    def exec(self, skip=()):
+        """Timeloop::exec, src/timeloop.cxx:358-411.  `skip`: fields already advanced by the fused pressure tail."""
         g, f = self.grid, self.fields
-        names = list(f.at)
+        names = [n for n in f.at if n not in skip]
         a = L.ptr_array([f.ap[n].fld for n in names])
         at = L.ptr_array([f.at[n].fld for n in names])
         L.check(g.ctx, g.lib.mhh_rk_substep(g.ctx, self.rkorder, self.substep, C.c_double(self.dt), len(names), a, at),

@@ -77,6 +77,7 @@ class Model:
                                  cs=di.get("cs", 0.23), tPr=di.get("tPr", 1. / 3.))
         self.pres = Pres.factory(self.grid, self.fields, str(ini.get("pres", {}).get("swpres", order)))
         self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
+        self.fuse_pres_rk = self.pres.swpres == "2"   # Pres_2::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
                                  dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True),
@@ -99,9 +100,10 @@ class Model:
         b.set_ghost_cells_w(L.BCW_NORMAL)                  # :389
         self.diff.exec()                                   # :392
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
-        self.pres.exec(tl.get_sub_time_step())             # :411
+        # :411 + :484 for u,v,w in one pass where the solver supports it (2nd order; set_ghost_cells_w is a 4th-order no-op there)
+        fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
         b.set_ghost_cells_w(L.BCW_NORMAL)                  # :412
-        tl.exec()                                          # :484
+        tl.exec(skip=("u", "v", "w") if fused else ())     # :484
         tl.step_time()                                     # :487
 
     def step(self):

@@ -106,7 +106,7 @@ class SlabPres(Pres):
         self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
 
-    def exec(self, dt, stats=None):
+    def exec(self, dt, stats=None, timeloop=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
         u, v, w = (f.mp[n].fld for n in "uvw")
         ut, vt, wt = (f.mt[n].fld for n in "uvw")
@@ -133,7 +133,12 @@ class SlabPres(Pres):
         # Pres_2::solve tail + output (src/pres_2.cxx:352-387)
         ck(lib.mhh_pres_output_stage(g.ctx, 0, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p)), "pres_output 0")
         self.cyclic.exec(p, L.EDGE_NORTH_SOUTH)
+        if timeloop is not None:       # gradient stage + Timeloop::exec for u,v,w in one pass
+            ck(lib.mhh_pres_output_rk(g.ctx, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p), L.ptr(u), L.ptr(v), L.ptr(w),
+                                      timeloop.rkorder, timeloop.substep, C.c_double(timeloop.dt)), "pres_output_rk")
+            return True
         ck(lib.mhh_pres_output_stage(g.ctx, 1, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p)), "pres_output 1")
+        return False
 
     def check_divergence(self):
         return self.comm.allreduce_max(super().check_divergence(), self.grid.device)
@@ -170,9 +175,9 @@ class SlabModel(Model):
         b.set_ghost_cells_w(L.BCW_NORMAL)
         self.diff.exec()
         b.set_ghost_cells_w(L.BCW_CONSERVATION)
-        self.pres.exec(tl.get_sub_time_step())
+        fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
         b.set_ghost_cells_w(L.BCW_NORMAL)
-        tl.exec()
+        tl.exec(skip=("u", "v", "w") if fused else ())
         tl.step_time()
 
     def print_status(self):

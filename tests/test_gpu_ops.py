@@ -216,3 +216,37 @@ def test_fused_dry_viscosity_equals_two_step_path(cuda_lib, sm):
     d.exec_viscosity(t, surface=P)                  # N2 field, then evisc
     assert np.array_equal(f.sd["evisc"].fld.cpu().numpy(), fused)
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("rkorder,substep", [(3, 0), (3, 1), (3, 2), (4, 3), (4, 4)])
+def test_fused_pressure_tail_equals_output_then_rk(cuda_lib, rkorder, substep):
+    """mhh_pres_exec_rk (Pres_2::output fused with Timeloop::exec for u,v,w) is bit-identical to mhh_pres_exec followed
+    by mhh_rk_substep, including the cleared tendency ghost cells after the last substep."""
+    import torch
+    from microhh_b200 import host as H
+    case = make_case(itot=24, jtot=16, ktot=12, alpha=1.3)
+    g, W = _worlds(case)
+    rng = np.random.default_rng(11)
+    res = []
+    for fused in (False, True):
+        f = H.Fields(g, slist=["th"])
+        b = H.Boundary(g, f)
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+            b.boundary_cyclic.exec(f.mp[n].fld)
+        f.sp["th"].fld.copy_(_up(g, case["s"][0]))
+        r = np.random.default_rng(11)
+        for n in ("u", "v", "w", "th"):
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        pres = H.Pres.factory(g, f, "2")
+        pres.set_values()
+        tl = H.Timeloop(g, f, rkorder=rkorder, dt=0.73)
+        tl.substep = substep
+        done = pres.exec(tl.get_sub_time_step(), timeloop=tl if fused else None)
+        assert done == fused
+        tl.exec(skip=("u", "v", "w") if done else ())
+        res.append({n: f.ap[n].fld.cpu().numpy().copy() for n in f.ap} | {n + "t": f.at[n].fld.cpu().numpy().copy() for n in f.at}
+                   | {"p": f.sd["p"].fld.cpu().numpy().copy()})
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    g.close(); W.close()
