@@ -122,6 +122,18 @@ int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
                    int nscalars, const double* const* s, double* const* st,
                    const double* const* sfluxbot, const double* const* sfluxtop,
                    const double* svisc, double tPr);
+/* One pass per prognostic field for the LES tendencies (no reference counterpart): Thermo_dry::exec's buoyancy on wt
+ * (src/thermo_dry.cxx:43-62; only when th_buoy != NULL), Advec_2::exec (src/advec_2.cxx:98-202) and Diff_smag2::exec, summed
+ * in the time loop's order so that the result is bit-identical to mhh_thermo_dry_exec, mhh_advec_exec, mhh_smag2_exec. */
+int mhh_advec2_smag2_exec(mhh_ctx* ctx, int surface_model,
+                          const double* u, const double* v, const double* w, const double* evisc,
+                          double* ut, double* vt, double* wt,
+                          const double* ufluxbot, const double* ufluxtop,
+                          const double* vfluxbot, const double* vfluxtop, double visc,
+                          const double* th_buoy,
+                          int nscalars, const double* const* s, double* const* st,
+                          const double* const* sfluxbot, const double* const* sfluxtop,
+                          const double* svisc, double tPr);
 /* calc_strain2 alone (src/diff_smag2.cxx:48) — stage check for parity tests; the product path fuses it. */
 int mhh_smag2_strain2(mhh_ctx* ctx, int surface_model, const double* u, const double* v, const double* w,
                       const double* dudz, const double* dvdz, double* strain2);

@@ -32,6 +32,9 @@ int smag2_exec_viscosity(Ctx*, int, const double*, const double*, const double*,
 int smag2_exec(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
                const double*, const double*, const double*, const double*, double, int, const double* const*, double* const*,
                const double* const*, const double* const*, const double*, double);
+int advec2_smag2_exec(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
+                      const double*, const double*, const double*, const double*, double, const double*, int,
+                      const double* const*, double* const*, const double* const*, const double* const*, const double*, double);
 int smag2_dnmul_bits(Ctx*, const double*, double, unsigned long long*);
 // boundary.cu
 int cyclic_exec(Ctx*, double*, int);
@@ -362,6 +365,18 @@ int mhh_smag2_exec(mhh_ctx* c, int surface_model, const double* u, const double*
     CTX_CHECK(c);
     if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
     return smag2_exec(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, ns, s, st, sfb, sft, svisc, tPr);
+}
+
+// Thermo_dry::exec (th_buoy != NULL) + Advec_2::exec + Diff_smag2::exec, one pass per prognostic field
+int mhh_advec2_smag2_exec(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                          double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
+                          double visc, const double* th_buoy, int ns, const double* const* s, double* const* st,
+                          const double* const* sfb, const double* const* sft, const double* svisc, double tPr)
+{
+    CTX_CHECK(c);
+    if (c->order != 2 || c->gd.igc != 1 || c->gd.jgc != 1) { c->last_error = "mhh_advec2_smag2_exec needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
+    if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
+    return advec2_smag2_exec(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft, svisc, tPr);
 }
 
 int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)

@@ -245,148 +245,31 @@ namespace
         evisc[ij + gd.kend * gd.ijcells] = evisc[ij + (gd.kend - 1) * gd.ijcells];
     }
 
-    // u, v, w stress divergences in one pass.  While marching k the kernel keeps in registers: evisc at the centre, west
-    // and south columns (k-1,k,k+1) and the east / north columns (k-1,k); the centre columns of u,v,w (k-1,k,k+1);
-    // u_e, v_n at k-1 and w_w, w_s at k+1 for the cross terms.  28 global loads per point instead of 46 (ncu r01: L1
-    // wavefront throughput 86 %, DRAM 37 %); the density divisions go through div_by().
-    template<bool SURF>
-    __global__ void __launch_bounds__(256, 2)
-    smag2_diff_uvw_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
-                          const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
-                          const double* __restrict__ evisc,
-                          const double* __restrict__ ufluxbot, const double* __restrict__ ufluxtop,
-                          const double* __restrict__ vfluxbot, const double* __restrict__ vfluxtop,
-                          const double visc, const GridD gd)
-    {
-        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
-        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
-        if (i >= gd.iend || j >= gd.jend) return;
-        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
-        const int ij = i + j * jj;
-        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
-        const int k1 = min(k0 + KCHUNK, gd.kend);
-        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
-
-        int ijk = ij + k0 * kk;
-        double e_b = evisc[ijk - kk], e_c = evisc[ijk];
-        double e_wb = evisc[ijk - ii - kk], e_w = evisc[ijk - ii];
-        double e_sb = evisc[ijk - jj - kk], e_s = evisc[ijk - jj];
-        double e_eb = evisc[ijk + ii - kk], e_nb = evisc[ijk + jj - kk];
-        double u_b = u[ijk - kk], u_c = u[ijk], u_eb = u[ijk + ii - kk];
-        double v_b = v[ijk - kk], v_c = v[ijk], v_nb = v[ijk + jj - kk];
-        double w_b = w[ijk - kk], w_c = w[ijk], w_w = w[ijk - ii], w_s = w[ijk - jj];
-
-        for (int k = k0; k < k1; ++k, ijk += kk)
-        {
-            if (k + MHH_PF < gd.kcells - 1)
-            {
-                const int pf = ijk + (MHH_PF + 1) * kk;
-                prefetch_l2(u + pf); prefetch_l2(v + pf); prefetch_l2(w + pf); prefetch_l2(evisc + pf);
-                prefetch_l2(ut + pf - kk); prefetch_l2(vt + pf - kk); prefetch_l2(wt + pf - kk);
-            }
-            const bool bot = SURF && (k == gd.kstart);
-            const bool top = SURF && (k == gd.kend - 1);
-            const double rho = gd.rhoref[k], rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k];
-            const double rho_i = gd.rhoref_i[k];
-            const double dzi = gd.dzi[k], dzhi_t = gd.dzhi[k + 1], dzhi_b = gd.dzhi[k];
-
-            // level k+1: centre, west, south columns of evisc; level k: east, north and the three corners
-            const double e_t = evisc[ijk + kk], e_wt = evisc[ijk - ii + kk], e_st = evisc[ijk - jj + kk];
-            const double e_e = evisc[ijk + ii], e_n = evisc[ijk + jj];
-            const double e_wn = evisc[ijk - ii + jj], e_ws = evisc[ijk - ii - jj], e_es = evisc[ijk + ii - jj];
-            const double u_t = u[ijk + kk], u_e = u[ijk + ii], u_w = u[ijk - ii], u_n = u[ijk + jj], u_s = u[ijk - jj];
-            const double u_es = u[ijk + ii - jj];
-            const double v_t = v[ijk + kk], v_n = v[ijk + jj], v_e = v[ijk + ii], v_w = v[ijk - ii], v_s = v[ijk - jj];
-            const double v_wn = v[ijk - ii + jj];
-            const double w_t = w[ijk + kk], w_wt = w[ijk - ii + kk], w_st = w[ijk - jj + kk];
-            const double w_e = w[ijk + ii], w_n = w[ijk + jj];
-
-            // ---- u: src/diff_smag2.cxx:395-467
-            {
-                const double evisce = e_c + visc;
-                const double eviscw = e_w + visc;
-                const double eviscn = 0.25 * (e_w + e_c + e_wn + e_n) + visc;
-                const double eviscs = 0.25 * (e_ws + e_s + e_w + e_c) + visc;
-                const double evisct = 0.25 * (e_w + e_c + e_wt + e_t) + visc;
-                const double eviscb = 0.25 * (e_wb + e_b + e_w + e_c) + visc;
-
-                const double hor =
-                    + ( evisce * (u_e - u_c) * dxi
-                      - eviscw * (u_c - u_w) * dxi ) * 2. * dxi
-                    + ( eviscn * ((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
-                      - eviscs * ((u_c - u_s) * dyi + (v_c - v_w) * dxi) ) * dyi;
-                const double grad_t = (u_t - u_c) * dzhi_t + (w_t - w_wt) * dxi;
-                const double grad_b = (u_c - u_b) * dzhi_b + (w_c - w_w) * dxi;
-                double ver;
-                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * ufluxbot[ij], rho, rho_i ) * dzi;
-                else if (top) ver = div_by( -rhoh_t * ufluxtop[ij] - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
-                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
-                ut[ijk] += hor + ver;
-            }
-            // ---- v: src/diff_smag2.cxx:497-569
-            {
-                const double evisce = 0.25 * (e_s + e_c + e_es + e_e) + visc;
-                const double eviscw = 0.25 * (e_ws + e_w + e_s + e_c) + visc;
-                const double eviscn = e_c + visc;
-                const double eviscs = e_s + visc;
-                const double evisct = 0.25 * (e_s + e_c + e_st + e_t) + visc;
-                const double eviscb = 0.25 * (e_sb + e_b + e_s + e_c) + visc;
-
-                const double hor =
-                    + ( evisce * ((v_e - v_c) * dxi + (u_e - u_es) * dyi)
-                      - eviscw * ((v_c - v_w) * dxi + (u_c - u_s) * dyi) ) * dxi
-                    + ( eviscn * (v_n - v_c) * dyi
-                      - eviscs * (v_c - v_s) * dyi ) * 2. * dyi;
-                const double grad_t = (v_t - v_c) * dzhi_t + (w_t - w_st) * dyi;
-                const double grad_b = (v_c - v_b) * dzhi_b + (w_c - w_s) * dyi;
-                double ver;
-                if (bot)      ver = div_by( rhoh_t * evisct * grad_t + rhoh_b * vfluxbot[ij], rho, rho_i ) * dzi;
-                else if (top) ver = div_by( -rhoh_t * vfluxtop[ij] - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
-                else          ver = div_by( rhoh_t * evisct * grad_t - rhoh_b * eviscb * grad_b, rho, rho_i ) * dzi;
-                vt[ijk] += hor + ver;
-            }
-            // ---- w: src/diff_smag2.cxx:594-614 (k from kstart+1)
-            if (k > gd.kstart)
-            {
-                const double evisce = 0.25 * (e_b + e_c + e_eb + e_e) + visc;
-                const double eviscw = 0.25 * (e_wb + e_w + e_b + e_c) + visc;
-                const double eviscn = 0.25 * (e_b + e_c + e_nb + e_n) + visc;
-                const double eviscs = 0.25 * (e_sb + e_s + e_b + e_c) + visc;
-                const double evisct = e_c + visc;
-                const double eviscb = e_b + visc;
-                wt[ijk] +=
-                    + ( evisce * ((w_e - w_c) * dxi + (u_e - u_eb) * dzhi_b)
-                      - eviscw * ((w_c - w_w) * dxi + (u_c - u_b) * dzhi_b) ) * dxi
-                    + ( eviscn * ((w_n - w_c) * dyi + (v_n - v_nb) * dzhi_b)
-                      - eviscs * ((w_c - w_s) * dyi + (v_c - v_b) * dzhi_b) ) * dyi
-                    + div_by( rho * evisct * (w_t - w_c) * dzi
-                            - gd.rhoref[k - 1] * eviscb * (w_c - w_b) * gd.dzi[k - 1], rhoh_b, gd.rhorefh_i[k] ) * 2. * dzhi_b;
-            }
-            e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
-            u_b = u_c; u_c = u_t; u_eb = u_e;
-            v_b = v_c; v_c = v_t; v_nb = v_n;
-            w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
-        }
-    }
-
-    // Shared-memory variant of the kernel above (same expression trees, bit-identical results).  A CTA owns a TX x TY
-    // tile of columns and marches k through its chunk; the (TX+2) x (TY+2) tile planes of evisc,u,v,w live in a ring of
-    // four shared-memory slots filled by cp.async two levels ahead.  Per point and level: 25 shared-memory loads and the
-    // 3 tendency read-modify-writes; no global load sits on the dependent path (ncu r01b: the register-queue kernel
-    // was long-scoreboard bound at 2 CTAs/SM).
-    template<bool SURF, int TX, int TY>
+    // u, v, w stress divergences in one pass (diff_u :370, diff_v :472, diff_w :575).  A CTA owns a TX x TY tile of columns
+    // and marches k through its chunk; the (TX+2) x (TY+2) tile planes of evisc,u,v,w live in a ring of four shared-memory
+    // slots filled by cp.async two levels ahead (TileMap, mhh_common.cuh).  Per point and level: 25 shared-memory loads
+    // and the 3 tendency read-modify-writes; no global load sits on the dependent path (ncu r01b: the register-queue
+    // version of this kernel was long-scoreboard bound at 2 CTAs/SM).
+    //
+    // ADVEC: the kernel first adds the 2nd-order advection tendencies (advec_u/v/w, src/advec_2.cxx:98-171), which need
+    //        exactly the u,v,w neighbours the stresses already hold; BUOY: before that, the dry buoyancy tendency on w
+    //        (src/thermo_dry.cxx:43-62).  The sums are formed in the time loop's order, ((t + buoyancy) + advection) +
+    //        diffusion, so the result is bit-identical to Thermo::exec, Advec::exec, Diff::exec run one after the other,
+    //        at 11 instead of 22 field passes over HBM.
+    template<bool SURF, bool ADVEC, bool BUOY, int TX, int TY>
     __global__ void __launch_bounds__(TX * TY, 2)
     smag2_diff_uvw_tile_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                                const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                                const double* __restrict__ evisc,
                                const double* __restrict__ ufluxbot, const double* __restrict__ ufluxtop,
                                const double* __restrict__ vfluxbot, const double* __restrict__ vfluxtop,
-                               const double visc, const GridD gd)
+                               const double visc, const double* __restrict__ th, const double* __restrict__ threfh,
+                               const double* __restrict__ g_threfh, const GridD gd)
     {
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4;
         __shared__ double sm[NS][4][PS];                 // [slot][evisc,u,v,w][tile plane]
-        __shared__ double met[6][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi at k0-1 .. k1
+        __shared__ double met[8][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi, threfh, g/threfh at k0-1 .. k1
 
         const int tid = threadIdx.y * TX + threadIdx.x;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
@@ -417,6 +300,7 @@ namespace
             const int k = min(k0 - 1 + tid, gd.kcells - 1);
             met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
             met[3][tid] = gd.rhorefh_i[k]; met[4][tid] = gd.dzi[k]; met[5][tid] = gd.dzhi[k];
+            if (BUOY) { met[6][tid] = threfh[k]; met[7][tid] = g_threfh[k]; }
         }
 
         // tile-plane offsets of the centre and its neighbours
@@ -438,6 +322,8 @@ namespace
         int ijk = ij + k0 * kk;
         double ut_c = 0., vt_c = 0., wt_c = 0.;
         if (live) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
+        double th_b = 0., th_c = 0., th_n = 0.;          // theta column (centre only), one level ahead from global memory
+        if (BUOY) { th_b = th[ijk - kk]; th_c = th[ijk]; th_n = th[ijk + kk]; }
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
@@ -446,6 +332,8 @@ namespace
             // tendencies of the next level: in flight during this level's arithmetic
             double ut_n = 0., vt_n = 0., wt_n = 0.;
             if (live && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
+            const double th_t = th_n;
+            if (BUOY && k + 1 < k1) th_n = th[ijk + 2 * kk];
 
             const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
             const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
@@ -465,6 +353,37 @@ namespace
             const double w_t = T[3 * PS + c], w_wt = T[3 * PS + cw], w_st = T[3 * PS + cs];
             const double w_e = C[3 * PS + ce], w_n = C[3 * PS + cn];
 
+            if (BUOY && k > gd.kstart)      // calc_buoyancy_tend_2nd, src/thermo_dry.cxx:43-62
+                wt_c = wt_c + met[7][km] * (fd::interp2(th_b, th_c) - met[6][km]);
+            if (ADVEC)
+            {
+                using fd::interp2;
+                // advec_u, src/advec_2.cxx:98-109
+                ut_c = ut_c +
+                    ( - ( interp2(u_c, u_e) * interp2(u_c, u_e)
+                        - interp2(u_w, u_c) * interp2(u_w, u_c) ) * dxi
+                      - ( interp2(v_wn, v_n) * interp2(u_c, u_n)
+                        - interp2(v_w, v_c) * interp2(u_s, u_c) ) * dyi
+                      - div_by( rhoh_t * interp2(w_wt, w_t) * interp2(u_c, u_t)
+                              - rhoh_b * interp2(w_w, w_c) * interp2(u_b, u_c), rho, rho_i ) * dzi );
+                // advec_v, src/advec_2.cxx:129-140
+                vt_c = vt_c +
+                    ( - ( interp2(u_es, u_e) * interp2(v_c, v_e)
+                        - interp2(u_s, u_c) * interp2(v_w, v_c) ) * dxi
+                      - ( interp2(v_c, v_n) * interp2(v_c, v_n)
+                        - interp2(v_s, v_c) * interp2(v_s, v_c) ) * dyi
+                      - div_by( rhoh_t * interp2(w_st, w_t) * interp2(v_c, v_t)
+                              - rhoh_b * interp2(w_s, w_c) * interp2(v_b, v_c), rho, rho_i ) * dzi );
+                // advec_w, src/advec_2.cxx:160-171 (k from kstart+1)
+                if (k > gd.kstart)
+                    wt_c = wt_c +
+                        ( - ( interp2(u_eb, u_e) * interp2(w_c, w_e)
+                            - interp2(u_b, u_c) * interp2(w_w, w_c) ) * dxi
+                          - ( interp2(v_nb, v_n) * interp2(w_c, w_n)
+                            - interp2(v_b, v_c) * interp2(w_s, w_c) ) * dyi
+                          - div_by( rho * interp2(w_c, w_t) * interp2(w_c, w_t)
+                                  - met[0][km - 1] * interp2(w_b, w_c) * interp2(w_b, w_c), rhoh_b, met[3][km] ) * dzhi_b );
+            }
             // ---- u: src/diff_smag2.cxx:395-467
             {
                 const double evisce = e_c + visc;
@@ -527,6 +446,7 @@ namespace
                             - met[0][km - 1] * eviscb * (w_c - w_b) * met[4][km - 1], rhoh_b, met[3][km] ) * 2. * dzhi_b;
                 if (live) wt[ijk] = wt_c + wd;
             }
+            if (BUOY) { th_b = th_c; th_c = th_t; }
             e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
             u_b = u_c; u_c = u_t; u_eb = u_e;
             v_b = v_c; v_c = v_t; v_nb = v_n;
@@ -536,56 +456,125 @@ namespace
         cp_async_wait<0>();
     }
 
-    // diff_c, src/diff_smag2.cxx:620-708
-    template<bool SURF>
-    __global__ void __launch_bounds__(256, MHH_MINB)
-    smag2_diff_c_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
-                        const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
-                        const double tPr, const double visc, const GridD gd)
+    // diff_c, src/diff_smag2.cxx:620-708, on shared-memory tiles (the scalar and evisc; with ADVEC also u and v).
+    // ADVEC: the kernel first adds the 2nd-order scalar advection (advec_s, src/advec_2.cxx:191-202), so that the scalar,
+    //        its tendency and evisc cross HBM once for both operators: (t + advection) + diffusion, bit-identical to
+    //        Advec::exec followed by Diff::exec.
+    template<bool SURF, bool ADVEC, int TX, int TY>
+    __global__ void __launch_bounds__(TX * TY, 3)
+    smag2_scalar_tile_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
+                             const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
+                             const double tPr, const double visc,
+                             const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
+                             const GridD gd)
     {
-        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
-        const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
-        if (i >= gd.iend || j >= gd.jend) return;
-        const int ii = 1, jj = gd.icells, kk = gd.ijcells;
-        const int ij = i + j * jj;
+        using Map = TileMap<TX, TY, 1>;
+        constexpr int W = Map::W, PS = Map::N, NS = 4, NF = ADVEC ? 4 : 2;
+        __shared__ double sm[NS][NF][PS];                // [slot][a, evisc(, u, v)][tile plane]
+        __shared__ double met[5][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, dzi, dzhi at k0-1 .. k1
+
+        const int tid = threadIdx.y * TX + threadIdx.x;
+        const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
+        const int i = i0 + threadIdx.x, j = j0 + threadIdx.y;
+        const bool live = (i < gd.iend) && (j < gd.jend);
+        const int jj = gd.icells, kk = gd.ijcells;
+        const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
+        const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
         const double tPr_i = 1. / tPr;
 
+        Map map;
+        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
+        {
+            if (k <= k1)
+            {
+                const int sl = (k - k0 + 1) & (NS - 1);
+                const long off = (long)k * kk;
+                map.issue(sm[sl][0], a + off, tid); map.issue(sm[sl][1], evisc + off, tid);
+                if (ADVEC) { map.issue(sm[sl][NF - 2], u + off, tid); map.issue(sm[sl][NF - 1], v + off, tid); }
+            }
+            cp_async_commit();
+        };
+        stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
+        if (tid < KCHUNK + 2)
+        {
+            const int k = min(k0 - 1 + tid, gd.kcells - 1);
+            met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
+            met[3][tid] = gd.dzi[k]; met[4][tid] = gd.dzhi[k];
+        }
+
+        const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
+        const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W;
+
         int ijk = ij + k0 * kk;
-        double a_b = a[ijk - kk], a_c = a[ijk];
-        double e_b = evisc[ijk - kk], e_c = evisc[ijk];
+        double at_c = 0.;
+        if (live) at_c = at[ijk];
+        double w_c = 0., w_n = 0.;                       // w column (centre only), one level ahead from global memory
+        if (ADVEC) { w_c = w[ijk]; w_n = w[ijk + kk]; }
+
+        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        __syncthreads();
+        double a_b = sm[0][0][c], a_c = sm[1][0][c], e_b = sm[0][1][c], e_c = sm[1][1][c];
+
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            if (k + MHH_PF < gd.kcells - 1)
-            {
-                const int pf = ijk + (MHH_PF + 1) * kk;
-                prefetch_l2(a + pf); prefetch_l2(evisc + pf); prefetch_l2(at + pf - kk);
-            }
-            const double a_t = a[ijk + kk], e_t = evisc[ijk + kk];
+            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            __syncthreads();                             // ... for every thread; everyone is done with plane k-1
+            stage(k + 3);                                // into the slot of plane k-1
+            double at_n = 0.;
+            if (live && k + 1 < k1) at_n = at[ijk + kk];
+            const double w_t = w_n;
+            if (ADVEC && k + 1 < k1) w_n = w[ijk + 2 * kk];
+
+            const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
+            const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
+            const int km = k - k0 + 1;                   // row of level k in met[]
+            const double rho = met[0][km], rho_i = met[2][km], rhoh_t = met[1][km + 1], rhoh_b = met[1][km];
+            const double dzi = met[3][km], dzhi_t = met[4][km + 1], dzhi_b = met[4][km];
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
-            const double evisce = div_by(0.5 * (e_c + evisc[ijk + ii]), tPr, tPr_i) + visc;
-            const double eviscw = div_by(0.5 * (evisc[ijk - ii] + e_c), tPr, tPr_i) + visc;
-            const double eviscn = div_by(0.5 * (e_c + evisc[ijk + jj]), tPr, tPr_i) + visc;
-            const double eviscs = div_by(0.5 * (evisc[ijk - jj] + e_c), tPr, tPr_i) + visc;
+
+            const double a_t = T[c], a_e = C[ce], a_w = C[cw], a_n = C[cn], a_s = C[cs];
+            const double e_t = T[PS + c], e_e = C[PS + ce], e_w = C[PS + cw], e_n = C[PS + cn], e_s = C[PS + cs];
+
+            if (ADVEC)
+            {
+                using fd::interp2;
+                const double u_c = C[2 * PS + c], u_e = C[2 * PS + ce], v_c = C[3 * PS + c], v_n = C[3 * PS + cn];
+                // advec_s, src/advec_2.cxx:191-202
+                at_c = at_c +
+                    ( - ( u_e * interp2(a_c, a_e)
+                        - u_c * interp2(a_w, a_c) ) * dxi
+                      - ( v_n * interp2(a_c, a_n)
+                        - v_c * interp2(a_s, a_c) ) * dyi
+                      - div_by( rhoh_t * w_t * interp2(a_c, a_t)
+                              - rhoh_b * w_c * interp2(a_b, a_c), rho, rho_i ) * dzi );
+                w_c = w_t;
+            }
+
+            const double evisce = div_by(0.5 * (e_c + e_e), tPr, tPr_i) + visc;
+            const double eviscw = div_by(0.5 * (e_w + e_c), tPr, tPr_i) + visc;
+            const double eviscn = div_by(0.5 * (e_c + e_n), tPr, tPr_i) + visc;
+            const double eviscs = div_by(0.5 * (e_s + e_c), tPr, tPr_i) + visc;
             const double evisct = div_by(0.5 * (e_c + e_t), tPr, tPr_i) + visc;
             const double eviscb = div_by(0.5 * (e_b + e_c), tPr, tPr_i) + visc;
 
             const double hor =
-                + ( evisce * (a[ijk + ii] - a_c) - eviscw * (a_c - a[ijk - ii]) ) * dxidxi
-                + ( eviscn * (a[ijk + jj] - a_c) - eviscs * (a_c - a[ijk - jj]) ) * dyidyi;
-            const double rhoh_t = gd.rhorefh[k + 1], rhoh_b = gd.rhorefh[k];
+                + ( evisce * (a_e - a_c) - eviscw * (a_c - a_w) ) * dxidxi
+                + ( eviscn * (a_n - a_c) - eviscs * (a_c - a_s) ) * dyidyi;
             double ver;
-            const double rho = gd.rhoref[k], rho_i = gd.rhoref_i[k];
-            if (bot)      ver = div_by( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1] + rhoh_b * fluxbot[ij], rho, rho_i ) * gd.dzi[k];
-            else if (top) ver = div_by( -rhoh_t * fluxtop[ij] - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k], rho, rho_i ) * gd.dzi[k];
-            else          ver = div_by( rhoh_t * evisct * (a_t - a_c) * gd.dzhi[k + 1]
-                                      - rhoh_b * eviscb * (a_c - a_b) * gd.dzhi[k], rho, rho_i ) * gd.dzi[k];
-            at[ijk] += hor + ver;
+            if (bot)      ver = div_by( rhoh_t * evisct * (a_t - a_c) * dzhi_t + rhoh_b * rare_load(fluxbot, ij), rho, rho_i ) * dzi;
+            else if (top) ver = div_by( -rhoh_t * rare_load(fluxtop, ij) - rhoh_b * eviscb * (a_c - a_b) * dzhi_b, rho, rho_i ) * dzi;
+            else          ver = div_by( rhoh_t * evisct * (a_t - a_c) * dzhi_t
+                                      - rhoh_b * eviscb * (a_c - a_b) * dzhi_b, rho, rho_i ) * dzi;
+            if (live) at[ijk] = at_c + (hor + ver);
             a_b = a_c; a_c = a_t; e_b = e_c; e_c = e_t;
+            at_c = at_n;
         }
+        cp_async_wait<0>();
     }
 
     // calc_dnmul, src/diff_smag2.cxx:712-735, fused with the max reduction
@@ -677,33 +666,90 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     return cyclic_exec(c, evisc, 2);
 }
 
+// Momentum tendencies.  advec == 0: Diff_smag2::exec for u,v,w.  advec == 1: preceded in the same pass by Advec_2::exec
+// for u,v,w and, when th != nullptr, by the dry buoyancy tendency on w (bit-identical to the separate calls, see kernel).
+int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const double* v, const double* w, const double* evisc,
+                   double* ut, double* vt, double* wt,
+                   const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
+                   double visc, const double* th)
+{
+    const GridD& gd = c->gd;
+    if (th != nullptr && (!advec || !c->thref_d)) { c->last_error = "fused buoyancy needs advec = 1 and the thermo reference profiles"; return MHH_ERR_STATE; }
+    constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
+    const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    const double* threfh = c->thref_d ? c->thref_d + gd.kcells : nullptr;
+    const double* g_threfh = c->thref_d ? c->thref_d + 3 * gd.kcells : nullptr;
+    #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd
+    #define UVW_LAUNCH(NAME, S, A, B) MHH_LAUNCH(c, NAME, (smag2_diff_uvw_tile_kernel<S, A, B, TX, TY><<<tg, tb, 0, c->stream>>>(UVW_ARGS)))
+    if (!advec)
+    {
+        if (surface_model) UVW_LAUNCH("smag2_diff_uvw_kernel", true, false, false);
+        else               UVW_LAUNCH("smag2_diff_uvw_kernel", false, false, false);
+    }
+    else if (th == nullptr)
+    {
+        if (surface_model) UVW_LAUNCH("advec2_smag2_uvw_kernel", true, true, false);
+        else               UVW_LAUNCH("advec2_smag2_uvw_kernel", false, true, false);
+    }
+    else
+    {
+        if (surface_model) UVW_LAUNCH("advec2_smag2_uvw_kernel", true, true, true);
+        else               UVW_LAUNCH("advec2_smag2_uvw_kernel", false, true, true);
+    }
+    #undef UVW_LAUNCH
+    #undef UVW_ARGS
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+// Scalar tendency.  advec == 0: Diff_smag2's diff_c.  advec == 1: preceded in the same pass by Advec_2's advec_s.
+int smag2_tend_scalar(Ctx* c, int surface_model, int advec, double* at, const double* a, const double* evisc,
+                      const double* fluxbot, const double* fluxtop, double tPr, double visc,
+                      const double* u, const double* v, const double* w)
+{
+    const GridD& gd = c->gd;
+    constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
+    const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    #define SC_LAUNCH(NAME, S, A) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, gd)))
+    if (!advec)
+    {
+        if (surface_model) SC_LAUNCH("smag2_diff_c_kernel", true, false);
+        else               SC_LAUNCH("smag2_diff_c_kernel", false, false);
+    }
+    else
+    {
+        if (surface_model) SC_LAUNCH("advec2_smag2_c_kernel", true, true);
+        else               SC_LAUNCH("advec2_smag2_c_kernel", false, true);
+    }
+    #undef SC_LAUNCH
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+// Thermo_dry::exec (th_buoy != nullptr) + Advec_2::exec + Diff_smag2::exec: one pass per prognostic field
+int advec2_smag2_exec(Ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                      double* ut, double* vt, double* wt,
+                      const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
+                      double visc, const double* th_buoy, int nscalars, const double* const* s, double* const* st,
+                      const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr)
+{
+    if (int e = smag2_tend_uvw(c, surface_model, 1, u, v, w, evisc, ut, vt, wt, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th_buoy)) return e;
+    for (int n = 0; n < nscalars; ++n)
+        if (int e = smag2_tend_scalar(c, surface_model, 1, st[n], s[n], evisc, surface_model ? sfluxbot[n] : nullptr,
+                                      surface_model ? sfluxtop[n] : nullptr, tPr, svisc[n], u, v, w)) return e;
+    return MHH_OK;
+}
+
 int smag2_exec(Ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
                double* ut, double* vt, double* wt,
                const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
                double visc, int nscalars, const double* const* s, double* const* st,
                const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr)
 {
-    const GridD& gd = c->gd;
-    Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    {
-        constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
-        const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
-        if (surface_model)
-            MHH_LAUNCH(c, "smag2_diff_uvw_kernel", (smag2_diff_uvw_tile_kernel<true, TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                    ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, gd)));
-        else
-            MHH_LAUNCH(c, "smag2_diff_uvw_kernel", (smag2_diff_uvw_tile_kernel<false, TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, evisc,
-                    nullptr, nullptr, nullptr, nullptr, visc, gd)));
-    }
-    MHH_LAUNCH_CHECK();
+    if (int e = smag2_tend_uvw(c, surface_model, 0, u, v, w, evisc, ut, vt, wt, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, nullptr)) return e;
     for (int n = 0; n < nscalars; ++n)
-    {
-        if (surface_model)
-            MHH_LAUNCH(c, "smag2_diff_c_kernel", smag2_diff_c_kernel<true><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, sfluxbot[n], sfluxtop[n], tPr, svisc[n], gd));
-        else
-            MHH_LAUNCH(c, "smag2_diff_c_kernel", smag2_diff_c_kernel<false><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], evisc, nullptr, nullptr, tPr, svisc[n], gd));
-        MHH_LAUNCH_CHECK();
-    }
+        if (int e = smag2_tend_scalar(c, surface_model, 0, st[n], s[n], evisc, surface_model ? sfluxbot[n] : nullptr,
+                                      surface_model ? sfluxtop[n] : nullptr, tPr, svisc[n], nullptr, nullptr, nullptr)) return e;
     return MHH_OK;
 }
 

@@ -393,6 +393,24 @@ class Diff:
                 L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
                 C.c_double(f.visc), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_smag2_exec")
 
+    def exec_with_advec2(self, th_buoy=None):
+        """Thermo_dry::exec (when th_buoy is given) + Advec_2::exec + Diff_smag2::exec in one pass per prognostic field
+        (mhh_advec2_smag2_exec); bit-identical to the three calls in the time loop's order."""
+        g, f = self.grid, self.fields
+        if self.swdiff != "smag2" or g.order != 2:
+            raise L.MhhError("the fused tendency pass needs swdiff=smag2 on the 2nd-order grid")
+        names = list(f.sp)
+        s = L.ptr_array([f.sp[n].fld for n in names])
+        st = L.ptr_array([f.st[n].fld for n in names])
+        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        sfb = L.ptr_array([f.sp[n].flux_bot for n in names])
+        sft = L.ptr_array([f.sp[n].flux_top for n in names])
+        L.check(g.ctx, g.lib.mhh_advec2_smag2_exec(
+            g.ctx, self._surface_model(), L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sd["evisc"].fld),
+            L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
+            L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
+            C.c_double(f.visc), L.ptr(th_buoy), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_advec2_smag2_exec")
+
     def _dnmul(self):
         if self.swdiff != "smag2":
             return self.dnmul

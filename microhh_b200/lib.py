@@ -37,7 +37,7 @@ EXPORTS = [
     "mhh_launch_count", "mhh_profile_enable", "mhh_profile_report",
     "mhh_advec_exec", "mhh_advec_cfl", "mhh_advec_time_limit",
     "mhh_diff2_exec", "mhh_diff4_exec", "mhh_diff_const_dnmul",
-    "mhh_smag2_exec_viscosity", "mhh_smag2_exec_viscosity_dry", "mhh_smag2_exec", "mhh_smag2_strain2", "mhh_smag2_dnmul",
+    "mhh_smag2_exec_viscosity", "mhh_smag2_exec_viscosity_dry", "mhh_smag2_exec", "mhh_advec2_smag2_exec", "mhh_smag2_strain2", "mhh_smag2_dnmul",
     "mhh_thermo_set_ref", "mhh_thermo_dry_exec", "mhh_thermo_dry_N2",
     "mhh_pres_set_values", "mhh_pres_exec", "mhh_pres_check_divergence", "mhh_pres_work", "mhh_pres_input",
     "mhh_fft_force_generic", "mhh_fft_forward", "mhh_fft_backward", "mhh_pres_solve_spectral", "mhh_pres_output", "mhh_pres_scatter",

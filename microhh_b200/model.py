@@ -77,6 +77,8 @@ class Model:
                                  cs=di.get("cs", 0.23), tPr=di.get("tPr", 1. / 3.))
         self.pres = Pres.factory(self.grid, self.fields, str(ini.get("pres", {}).get("swpres", order)))
         self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
+        # Thermo_dry + Advec_2 + Diff_smag2 tendencies in one pass per field (mhh_advec2_smag2_exec)
+        self.fuse_tend = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo in ("0", "dry")
         self.fuse_pres_rk = self.pres.swpres == "2"   # Pres_2::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
@@ -94,11 +96,14 @@ class Model:
         self.diff.exec_viscosity(self.thermo, surface=self.surface)   # :354
         if not tl.in_substep() and tl.adaptivestep:        # set_time_step, :357 -> :731-751
             tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
-        self.thermo.exec()                                 # :366
-        b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :387
-        self.advec.exec()                                  # :388
-        b.set_ghost_cells_w(L.BCW_NORMAL)                  # :389
-        self.diff.exec()                                   # :392
+        if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
+            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
+        else:
+            self.thermo.exec()                             # :366
+            b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387
+            self.advec.exec()                              # :388
+            b.set_ghost_cells_w(L.BCW_NORMAL)              # :389
+            self.diff.exec()                               # :392
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
         # :411 + :484 for u,v,w in one pass where the solver supports it (2nd order; set_ghost_cells_w is a 4th-order no-op there)
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)

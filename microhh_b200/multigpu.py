@@ -169,11 +169,14 @@ class SlabModel(Model):
                 dnmul = max(1.e-9, dnmul) if self.diff.swdiff == "smag2" else dnmul
                 lim.append(int(tl.idt * self.diff.dnmax / (tl.dt * dnmul)))
             tl.set_time_step(*lim)
-        self.thermo.exec()
-        b.set_ghost_cells_w(L.BCW_CONSERVATION)
-        self.advec.exec()
-        b.set_ghost_cells_w(L.BCW_NORMAL)
-        self.diff.exec()
+        if self.fuse_tend:
+            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
+        else:
+            self.thermo.exec()
+            b.set_ghost_cells_w(L.BCW_CONSERVATION)
+            self.advec.exec()
+            b.set_ghost_cells_w(L.BCW_NORMAL)
+            self.diff.exec()
         b.set_ghost_cells_w(L.BCW_CONSERVATION)
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
         b.set_ghost_cells_w(L.BCW_NORMAL)

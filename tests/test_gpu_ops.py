@@ -250,3 +250,45 @@ def test_fused_pressure_tail_equals_output_then_rk(cuda_lib, rkorder, substep):
     for k in res[0]:
         assert np.array_equal(res[0][k], res[1][k]), k
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("sm", [0, 1])
+@pytest.mark.parametrize("thermo", ["0", "dry"])
+@pytest.mark.parametrize("dims", [(24, 16, 12), (40, 10, 37), (33, 9, 5)], ids=["even", "ragged_tile", "odd"])
+def test_fused_tendency_pass_equals_thermo_advec_diff(cuda_lib, sm, thermo, dims):
+    """mhh_advec2_smag2_exec (buoyancy + advec_2 + smag2 diffusion in one pass per field) is bit-identical to
+    Thermo::exec, Advec::exec, Diff::exec called one after the other on non-zero starting tendencies; the tile edges
+    (imax, jmax not multiples of the tile; ktot not a multiple of the k chunk) are covered by the ragged / odd sizes."""
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    itot, jtot, ktot = dims
+    case = make_case(itot=itot, jtot=jtot, ktot=ktot, alpha=1.3, surface_model=sm, anelastic=True, nscalars=2)
+    g, W = _worlds(case)
+    res = []
+    for fused in (False, True):
+        f = H.Fields(g, slist=["th", "q"], visc=1e-3, svisc=2e-3)
+        f.set_rhoref(case["rhoref"], case["rhorefh"])
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+        f.sp["th"].fld.copy_(_up(g, case["s"][0]))
+        f.sp["q"].fld.copy_(_up(g, case["s"][1]))
+        r = np.random.default_rng(3)
+        for n in f.at:
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        for fld in list(f.mp.values()) + list(f.sp.values()):
+            fld.flux_bot.copy_(_up(g, r.uniform(-1e-2, 1e-2, (W.jcells, W.icells))))
+            fld.flux_top.copy_(_up(g, r.uniform(-1e-2, 1e-2, (W.jcells, W.icells))))
+        rr = np.random.default_rng(2)
+        t = Thermo(g, f, thermo, thref=300. + rr.uniform(0, 1, W.kcells), threfh=300. + rr.uniform(0, 1, W.kcells))
+        b = H.Boundary(g, f, swboundary="surface" if sm else "default")
+        a = H.Advec.factory(g, f, "2")
+        d = H.Diff.factory(g, f, b, "smag2", cs=0.17, tPr=1. / 3.)
+        f.sd["evisc"].fld.copy_(_up(g, r.uniform(0.1, 1., W.shape)))
+        if fused:
+            d.exec_with_advec2(f.sp["th"].fld if thermo == "dry" else None)
+        else:
+            t.exec(); a.exec(); d.exec()
+        res.append({n: f.at[n].fld.cpu().numpy().copy() for n in f.at})
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    g.close(); W.close()
