@@ -14,6 +14,7 @@ using fd::interp2;
 namespace
 {
     constexpr int KCHUNK = MHH_KCHUNK;
+    constexpr int KT = MHH_TILE_KCHUNK;          // advec2_uvw_kernel (shared-memory tiles)
 
     // A CTA owns a TX x TY tile of columns and marches k through its chunk.  The (TX+2) x (TY+2) tile planes of u,v,w sit in
     // a ring of four shared-memory slots filled by cp.async two levels ahead (TileMap, mhh_common.cuh); the centre columns
@@ -28,7 +29,7 @@ namespace
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4;
         __shared__ double sm[NS][3][PS];                 // [slot][u,v,w][tile plane]
-        __shared__ double met[6][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi at k0-1 .. k1
+        __shared__ double met[6][KT + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi at k0-1 .. k1
 
         const int tid = threadIdx.y * TX + threadIdx.x;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
@@ -36,8 +37,8 @@ namespace
         const bool live = (i < gd.iend) && (j < gd.jend);
         const int jj = gd.icells, kk = gd.ijcells;
         const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
-        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
-        const int k1 = min(k0 + KCHUNK, gd.kend);
+        const int k0 = gd.kstart + blockIdx.z * KT;
+        const int k1 = min(k0 + KT, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
 
         Map map;
@@ -53,7 +54,7 @@ namespace
             cp_async_commit();
         };
         stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
-        if (tid < KCHUNK + 2)
+        if (tid < KT + 2)
         {
             const int k = min(k0 - 1 + tid, gd.kcells - 1);
             met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
@@ -212,7 +213,7 @@ int advec2_exec(Ctx* c, const double* u, const double* v, const double* w, doubl
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     {
         constexpr int TX = 32, TY = 8;
-        const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+        const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KT - 1) / KT);
         MHH_LAUNCH(c, "advec2_uvw_kernel", (advec2_uvw_kernel<TX, TY><<<tg, tb, 0, c->stream>>>(ut, vt, wt, u, v, w, gd)));
     }
     MHH_LAUNCH_CHECK();

@@ -18,6 +18,10 @@
 #ifndef MHH_KCHUNK
 #define MHH_KCHUNK 32
 #endif
+// k levels per CTA of the shared-memory tile kernels: their three-plane pipeline fill is amortised over the chunk
+#ifndef MHH_TILE_KCHUNK
+#define MHH_TILE_KCHUNK 64
+#endif
 
 namespace mhh
 {
