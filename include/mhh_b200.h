@@ -178,6 +178,12 @@ int mhh_pres_input_to(mhh_ctx* ctx, const double* u, const double* v, const doub
                       const double* vt, const double* wt, double dt, double* dst_X);
 int mhh_fft_x(mhh_ctx* ctx, int dir, double* data_X, double* p_or_null);
 int mhh_fft_y(mhh_ctx* ctx, int dir, double* data_Y);
+/* FFT stages that read / write the all-to-all chunk layout directly (chunk for peer r = [k][j<jmax][ii<iblock]), fusing
+ * Transpose::exec_xy / exec_yx's pack and unpack copies (src/transpose.cxx:163-217) into the transforms:
+ *   x, dir<0: slab X -> chunks;  y, dir<0: received chunks -> Y;  y, dir>0: Y -> chunks;  x, dir>0: received chunks -> X or p */
+int mhh_fft_x_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, double* p_or_null);
+int mhh_fft_y_chunks(mhh_ctx* ctx, int dir, const double* in, double* out);
+int mhh_fft_chunks_supported(mhh_ctx* ctx);
 int mhh_transpose_copy(mhh_ctx* ctx, int mode, double* dst, const double* src);
 int mhh_pres_solve_spectral_ws(mhh_ctx* ctx, double* data_Y, double* work3d);
 int mhh_pres_output_stage(mhh_ctx* ctx, int stage, double* ut, double* vt, double* wt, double* p);

@@ -108,6 +108,56 @@ static int fft_y(Ctx* c, int dir, double* data)
     return fft_lines(c, c->plan_j, dir, data, data, L);
 }
 
+// y-slab variants that read / write the all-to-all chunk layout directly (slab.cu: chunk for peer r =
+// [k][j < jmax][ii < iblock], chunks ordered by r), so that no pack / unpack pass is needed around the collectives.
+//   x, dir < 0: X -> chunks (send side of exec_xy)       x, dir > 0: chunks (received, exec_yx) -> X or p
+//   y, dir < 0: chunks (received, exec_xy) -> Y          y, dir > 0: Y -> chunks (send side of exec_yx)
+static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* p)
+{
+    const GridD& gd = c->gd;
+    const long R = (long)gd.kmax * gd.jmax * c->iblock;       // one chunk
+    FftLayout L;
+    L.nlines = gd.jmax * gd.kmax; L.base_in = 0; L.base_out = 0;
+    L.scale = dir < 0 ? 1. : 1. / gd.itot;
+    if (dir < 0)
+    {
+        L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1;
+        L.n1o = L.nlines; L.s1o = c->iblock; L.s2o = 0; L.sno = 1; L.esplit_out = c->iblock; L.eseg_out = R;
+        return fft_lines(c, c->plan_i, -1, in, out, L);
+    }
+    L.n1 = L.nlines; L.s1 = c->iblock; L.s2 = 0; L.sn = 1; L.esplit_in = c->iblock; L.eseg_in = R;
+    L.n1o = L.nlines; L.s1o = gd.itot; L.s2o = 0; L.sno = 1;
+    if (p != nullptr)
+    {
+        L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells;
+        L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
+        out = p;
+    }
+    return fft_lines(c, c->plan_i, +1, in, out, L);
+}
+
+static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out)
+{
+    const GridD& gd = c->gd;
+    const long R = (long)gd.kmax * gd.jmax * c->iblock;
+    FftLayout L;
+    L.nlines = c->iblock * gd.kmax; L.base_in = 0; L.base_out = 0;
+    L.scale = dir < 0 ? 1. : 1. / gd.jtot;
+    // Y side: lines (ii, k), element j at stride iblock;  chunk side: element j = (r, j') at r*R + j'*iblock
+    L.n1 = c->iblock; L.s1 = 1; L.sn = c->iblock; L.n1o = c->iblock; L.s1o = 1; L.sno = c->iblock;
+    if (dir < 0)
+    {
+        L.s2 = (long)gd.jmax * c->iblock; L.esplit_in = gd.jmax; L.eseg_in = R;
+        L.s2o = (long)c->iblock * gd.jtot;
+    }
+    else
+    {
+        L.s2 = (long)c->iblock * gd.jtot;
+        L.s2o = (long)gd.jmax * c->iblock; L.esplit_out = gd.jmax; L.eseg_out = R;
+    }
+    return fft_lines(c, c->plan_j, dir, in, out, L);
+}
+
 static int fft_forward_inplace(Ctx* c, double* data)
 {
     if (c->npy != 1) return MHH_ERR_STATE;
@@ -467,6 +517,18 @@ int mhh_pres_output(mhh_ctx* c, double* ut, double* vt, double* wt, double* p)
 // ---- y-slab stages (multi-GPU driver): see microhh_b200/multigpu.py for the call order
 int mhh_fft_x(mhh_ctx* c, int dir, double* data, double* p_or_null) { PRES_READY(c); return fft_x(c, dir, data, p_or_null); }
 int mhh_fft_y(mhh_ctx* c, int dir, double* data) { PRES_READY(c); return fft_y(c, dir, data); }
+int mhh_fft_x_chunks(mhh_ctx* c, int dir, const double* in, double* out, double* p_or_null)
+{ PRES_READY(c); return fft_x_chunks(c, dir, in, out, p_or_null); }
+int mhh_fft_y_chunks(mhh_ctx* c, int dir, const double* in, double* out) { PRES_READY(c); return fft_y_chunks(c, dir, in, out); }
+// 1 when the chunk-layout FFT stages are available (both lengths on the register-resident power-of-two kernel and the
+// per-rank blocks powers of two); otherwise the driver falls back to mhh_transpose_copy around mhh_fft_x / mhh_fft_y
+int mhh_fft_chunks_supported(mhh_ctx* c)
+{
+    if (!c) return 0;
+    if (!c->pres_ready) { if (mhh_pres_set_values(c)) return 0; }
+    const int ib = c->iblock, jm = c->gd.jmax;
+    return (c->plan_i.p2_nst > 0 && c->plan_j.p2_nst > 0 && ib > 0 && jm > 0 && (ib & (ib - 1)) == 0 && (jm & (jm - 1)) == 0) ? 1 : 0;
+}
 int mhh_transpose_copy(mhh_ctx* c, int mode, double* dst, const double* src) { CTX_CHECK(c); return transpose_copy(c, mode, dst, src); }
 int mhh_halo_ns(mhh_ctx* c, double* fld, double* north, double* south, int unpack, int is2d)
 { CTX_CHECK(c); return halo_ns(c, fld, north, south, unpack, is2d ? 1 : c->gd.kcells); }

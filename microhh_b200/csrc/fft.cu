@@ -287,7 +287,9 @@ int fft_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, double* ou
     A.line_fast = (L.sn != 1);
     A.scale = L.scale;
     if (L.nlines == 0) return MHH_OK;
-    if (plan.p2_nst > 0 && !c->fft_force_generic) return fft_pow2_lines(c, plan, dir, in, out, L);
+    const bool split = L.esplit_in > 0 || L.esplit_out > 0;
+    if (plan.p2_nst > 0 && (!c->fft_force_generic || split)) return fft_pow2_lines(c, plan, dir, in, out, L);
+    if (split) return MHH_ERR_UNSUPPORTED;
     if (plan.n == 1)
     {
         // length-1 transform = identity (2-D runs, jtot == 1): only scale / relayout

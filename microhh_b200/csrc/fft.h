@@ -7,12 +7,16 @@ namespace mhh
 // Line l (0 <= l < nlines), element m (0 <= m < n):
 //   input  address = base_in  + (l % n1 )*s1  + (l / n1 )*s2  + m*sn
 //   output address = base_out + (l % n1o)*s1o + (l / n1o)*s2o + m*sno
+// Optional two-level element index (the all-to-all chunk layouts of the y-slab solver, slab.cu): with esplit > 0 (a power
+// of two) element m sits at (m / esplit)*eseg + (m % esplit)*sn instead of m*sn.  register-resident pow2 kernel only.
 struct FftLayout
 {
     int nlines;
     int n1;  long s1, s2, sn;   long base_in;
     int n1o; long s1o, s2o, sno; long base_out;
     double scale;
+    int esplit_in = 0;  long eseg_in = 0;
+    int esplit_out = 0; long eseg_out = 0;
 };
 
 int fft_plan_create(FftPlan* p, int n);

@@ -37,6 +37,8 @@ namespace
         int n1o;
         long s1o, s2o, sno, base_out;
         double scale;
+        int esh_in, esh_out;          // log2 of the element split (31: none)
+        long eseg_in, eseg_out;
     };
 
     __device__ __forceinline__ double2 cmul(double2 a, double2 b)
@@ -185,6 +187,13 @@ namespace
         return (long)(l % n1) * s1 + (long)(l / n1) * s2;
     }
 
+    // element offset within a line; SPLIT: two-level index of the slab chunk layouts (FftLayout, fft.h)
+    template<bool SPLIT> __device__ __forceinline__ long elem_off(int m, long sn, int esh, long eseg)
+    {
+        if (!SPLIT) return (long)m * sn;
+        return (long)(m >> esh) * eseg + (long)(m & ((1 << esh) - 1)) * sn;
+    }
+
     // DIR = -1: real lines -> half-complex; +1: half-complex -> real lines (unnormalised * scale).
     // STRIDED: element stride sn != 1 (lines adjacent in memory): tiles are staged through shared memory.
     // NG: pair groups per CTA.  The CTA stages 2*npairs*NG lines at once (so a strided row of the tile is
@@ -192,7 +201,7 @@ namespace
     // The cooperative tile loops use only shifts and ONE line-address computation per thread: BLOCK is a
     // multiple of the (power-of-two) line count, so a thread always serves the same line (ncu r01: the y passes
     // sat at 16 % of DRAM throughput behind per-element integer div/mod and 64-byte rows).
-    template<int DIR, bool STRIDED, int NG>
+    template<int DIR, bool STRIDED, int NG, bool SPLIT>
     __global__ void __launch_bounds__(BLOCK, 3)
     fft_pow2_kernel(const double* __restrict__ in, double* __restrict__ out, const P2Args A)
     {
@@ -225,7 +234,7 @@ namespace
                     const double* src = in + A.base_in + line_addr(l, A.n1, A.s1, A.s2);
                     #pragma unroll 8
                     for (int m = threadIdx.x >> llog; m < n; m += mstep)
-                        dst[2 * pad(m)] = src[(long)m * A.sn];
+                        dst[2 * pad(m)] = src[elem_off<SPLIT>(m, A.sn, A.esh_in, A.eseg_in)];
                 }
                 else
                     for (int m = threadIdx.x >> llog; m < n; m += mstep) dst[2 * pad(m)] = 0.;
@@ -272,7 +281,8 @@ namespace
                 for (int m = 0; m < 8; ++m)
                 {
                     const int pos = tf + m * n8;
-                    v[m] = make_double2(va ? pa[pos] : 0., vb ? pb[pos] : 0.);
+                    const long eo = elem_off<SPLIT>(pos, 1, A.esh_in, A.eseg_in);
+                    v[m] = make_double2(va ? pa[eo] : 0., vb ? pb[eo] : 0.);
                 }
             }
             else
@@ -287,8 +297,9 @@ namespace
                 {
                     const int pos = tf + m * n8;
                     const int mir = (n - pos) & (n - 1);
-                    a1[m] = va ? pa[pos] : 0.; a2[m] = va ? pa[mir] : 0.;
-                    b1[m] = vb ? pb[pos] : 0.; b2[m] = vb ? pb[mir] : 0.;
+                    const long ep = elem_off<SPLIT>(pos, 1, A.esh_in, A.eseg_in), em = elem_off<SPLIT>(mir, 1, A.esh_in, A.eseg_in);
+                    a1[m] = va ? pa[ep] : 0.; a2[m] = va ? pa[em] : 0.;
+                    b1[m] = vb ? pb[ep] : 0.; b2[m] = vb ? pb[em] : 0.;
                 }
                 #pragma unroll
                 for (int m = 0; m < 8; ++m)
@@ -313,8 +324,9 @@ namespace
                     for (int m = 0; m < 8; ++m)
                     {
                         const int pos = tf + m * n8;
-                        if (va) qa[pos] = v[m].x * A.scale;
-                        if (vb) qb[pos] = v[m].y * A.scale;
+                        const long eo = elem_off<SPLIT>(pos, 1, A.esh_out, A.eseg_out);
+                        if (va) qa[eo] = v[m].x * A.scale;
+                        if (vb) qb[eo] = v[m].y * A.scale;
                     }
                     continue;
                 }
@@ -349,8 +361,9 @@ namespace
                     const bool has_im = (k > 0) && (k < nh);
                     if (!STRIDED)
                     {
-                        if (va) { qa[k] = are * A.scale; if (has_im) qa[n - k] = aim * A.scale; }
-                        if (vb) { qb[k] = bre * A.scale; if (has_im) qb[n - k] = bim * A.scale; }
+                        const long ek = elem_off<SPLIT>(k, 1, A.esh_out, A.eseg_out), en = elem_off<SPLIT>(n - k, 1, A.esh_out, A.eseg_out);
+                        if (va) { qa[ek] = are * A.scale; if (has_im) qa[en] = aim * A.scale; }
+                        if (vb) { qb[ek] = bre * A.scale; if (has_im) qb[en] = bim * A.scale; }
                     }
                     else
                     {
@@ -376,7 +389,7 @@ namespace
                 const double* src = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
                 #pragma unroll 8
                 for (int m = threadIdx.x >> llog; m < n; m += mstep)
-                    dst[(long)m * A.sno] = src[2 * pad(m)] * A.scale;
+                    dst[elem_off<SPLIT>(m, A.sno, A.esh_out, A.eseg_out)] = src[2 * pad(m)] * A.scale;
             }
         }
     }
@@ -433,29 +446,23 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     const int lines = 2 * npairs * ng;
     const size_t smem = (size_t)npairs * ng * pair_bytes;
     const int nblocks = (L.nlines + lines - 1) / lines;
-    static bool attr = false;
-    if (!attr)
-    {
-        cudaFuncSetAttribute(fft_pow2_kernel<-1, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<-1, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<1, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<1, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<-1, true, NGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        cudaFuncSetAttribute(fft_pow2_kernel<1, true, NGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-        attr = true;
-    }
-    if (dir < 0)
-    {
-        if (strided && wide) MHH_LAUNCH(c, "fft_fwd_y", (fft_pow2_kernel<-1, true, NGS><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-        else if (strided)    MHH_LAUNCH(c, "fft_fwd_y", (fft_pow2_kernel<-1, true, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-        else                 MHH_LAUNCH(c, "fft_fwd_x", (fft_pow2_kernel<-1, false, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-    }
-    else
-    {
-        if (strided && wide) MHH_LAUNCH(c, "fft_bwd_y", (fft_pow2_kernel<1, true, NGS><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-        else if (strided)    MHH_LAUNCH(c, "fft_bwd_y", (fft_pow2_kernel<1, true, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-        else                 MHH_LAUNCH(c, "fft_bwd_x", (fft_pow2_kernel<1, false, 1><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A)));
-    }
+    const bool split = L.esplit_in > 0 || L.esplit_out > 0;
+    auto lg = [](int v) { int l = 0; while ((1 << l) < v) ++l; return l; };
+    if ((L.esplit_in > 0 && (L.esplit_in & (L.esplit_in - 1))) || (L.esplit_out > 0 && (L.esplit_out & (L.esplit_out - 1))))
+        return MHH_ERR_UNSUPPORTED;
+    A.esh_in = L.esplit_in > 0 ? lg(L.esplit_in) : 31;   A.eseg_in = L.eseg_in;
+    A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
+    const char* name = dir < 0 ? (strided ? "fft_fwd_y" : "fft_fwd_x") : (strided ? "fft_bwd_y" : "fft_bwd_x");
+    #define P2_LAUNCH(D, S, G, SP) do { \
+        static bool attr = false; \
+        if (!attr) { cudaFuncSetAttribute(fft_pow2_kernel<D, S, G, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; } \
+        MHH_LAUNCH(c, name, (fft_pow2_kernel<D, S, G, SP><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A))); } while (0)
+    #define P2_DISPATCH(SP) do { \
+        if (dir < 0) { if (strided && wide) P2_LAUNCH(-1, true, NGS, SP); else if (strided) P2_LAUNCH(-1, true, 1, SP); else P2_LAUNCH(-1, false, 1, SP); } \
+        else         { if (strided && wide) P2_LAUNCH(1, true, NGS, SP);  else if (strided) P2_LAUNCH(1, true, 1, SP);  else P2_LAUNCH(1, false, 1, SP); } } while (0)
+    if (split) P2_DISPATCH(true); else P2_DISPATCH(false);
+    #undef P2_DISPATCH
+    #undef P2_LAUNCH
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

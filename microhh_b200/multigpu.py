@@ -105,9 +105,12 @@ class SlabPres(Pres):
         n = grid.imax * grid.jmax * grid.kmax
         self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
+        self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
 
     def exec(self, dt, stats=None, timeloop=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
+        if self.chunk_fft is None:
+            self.chunk_fft = bool(lib.mhh_fft_chunks_supported(g.ctx))
         u, v, w = (f.mp[n].fld for n in "uvw")
         ut, vt, wt = (f.mt[n].fld for n in "uvw")
         p = f.sd["p"].fld
@@ -117,19 +120,29 @@ class SlabPres(Pres):
         self.cyclic.exec(ut, L.EDGE_EAST_WEST)
         self.cyclic.exec(vt, L.EDGE_NORTH_SOUTH)
         ck(lib.mhh_pres_input_to(g.ctx, L.ptr(u), L.ptr(v), L.ptr(w), L.ptr(ut), L.ptr(vt), L.ptr(wt), C.c_double(dt), A), "pres_input")
-        # forward: x FFT, exec_xy, y FFT (src/fft.cxx:452-516 with npx = 1)
-        ck(lib.mhh_fft_x(g.ctx, -1, A, None), "fft_x fwd")
-        ck(lib.mhh_transpose_copy(g.ctx, 0, B, A), "pack xy")
-        self.comm.all_to_all(self.A, self.B)
-        ck(lib.mhh_transpose_copy(g.ctx, 1, B, A), "unpack xy")
-        ck(lib.mhh_fft_y(g.ctx, -1, B), "fft_y fwd")
-        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, B, A), "tdma")
-        # backward: y FFT, exec_yx, x FFT scattering into the ghost-celled p (src/fft.cxx:519-583)
-        ck(lib.mhh_fft_y(g.ctx, +1, B), "fft_y bwd")
-        ck(lib.mhh_transpose_copy(g.ctx, 2, A, B), "pack yx")
-        self.comm.all_to_all(self.B, self.A)
-        ck(lib.mhh_transpose_copy(g.ctx, 3, A, B), "unpack yx")
-        ck(lib.mhh_fft_x(g.ctx, +1, A, L.ptr(p)), "fft_x bwd")
+        if self.chunk_fft:
+            # the transforms read / write the all-to-all chunk layout themselves: no pack / unpack passes
+            ck(lib.mhh_fft_x_chunks(g.ctx, -1, A, B, None), "fft_x fwd -> chunks")
+            self.comm.all_to_all(self.A, self.B)
+            ck(lib.mhh_fft_y_chunks(g.ctx, -1, A, B), "chunks -> fft_y fwd")
+            ck(lib.mhh_pres_solve_spectral_ws(g.ctx, B, A), "tdma")
+            ck(lib.mhh_fft_y_chunks(g.ctx, +1, B, A), "fft_y bwd -> chunks")
+            self.comm.all_to_all(self.B, self.A)
+            ck(lib.mhh_fft_x_chunks(g.ctx, +1, B, None, L.ptr(p)), "chunks -> fft_x bwd")
+        else:
+            # forward: x FFT, exec_xy, y FFT (src/fft.cxx:452-516 with npx = 1)
+            ck(lib.mhh_fft_x(g.ctx, -1, A, None), "fft_x fwd")
+            ck(lib.mhh_transpose_copy(g.ctx, 0, B, A), "pack xy")
+            self.comm.all_to_all(self.A, self.B)
+            ck(lib.mhh_transpose_copy(g.ctx, 1, B, A), "unpack xy")
+            ck(lib.mhh_fft_y(g.ctx, -1, B), "fft_y fwd")
+            ck(lib.mhh_pres_solve_spectral_ws(g.ctx, B, A), "tdma")
+            # backward: y FFT, exec_yx, x FFT scattering into the ghost-celled p (src/fft.cxx:519-583)
+            ck(lib.mhh_fft_y(g.ctx, +1, B), "fft_y bwd")
+            ck(lib.mhh_transpose_copy(g.ctx, 2, A, B), "pack yx")
+            self.comm.all_to_all(self.B, self.A)
+            ck(lib.mhh_transpose_copy(g.ctx, 3, A, B), "unpack yx")
+            ck(lib.mhh_fft_x(g.ctx, +1, A, L.ptr(p)), "fft_x bwd")
         # Pres_2::solve tail + output (src/pres_2.cxx:352-387)
         ck(lib.mhh_pres_output_stage(g.ctx, 0, L.ptr(ut), L.ptr(vt), L.ptr(wt), L.ptr(p)), "pres_output 0")
         self.cyclic.exec(p, L.EDGE_NORTH_SOUTH)
