@@ -18,6 +18,8 @@ namespace
 #ifndef MHH_TILE_X
 #define MHH_TILE_X 32
 #endif
+// slots of the momentum kernel's plane ring: 6 x 4 fields x (34 x 6) doubles = 39 KB keeps four CTAs on an SM
+constexpr int UVW_SLOTS = 6;
 #ifndef MHH_UVW_TILE_Y
 #define MHH_UVW_TILE_Y 4      // 32 x 4 columns per CTA, four CTAs per SM: shorter barrier waits than 32 x 8 (4.91 -> 4.66 ms)
 #endif
@@ -260,7 +262,7 @@ namespace
     //        diffusion, so the result is bit-identical to Thermo::exec, Advec::exec, Diff::exec run one after the other,
     //        at 11 instead of 22 field passes over HBM.
     template<bool SURF, bool ADVEC, bool BUOY, int TX, int TY>
-    __global__ void __launch_bounds__(TX * TY, 512 / (TX * TY))
+    __global__ void __launch_bounds__(TX * TY, 384 / (TX * TY))
     smag2_diff_uvw_tile_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                                const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                                const double* __restrict__ evisc,
@@ -270,9 +272,10 @@ namespace
                                const double* __restrict__ g_threfh, const GridD gd)
     {
         using Map = TileMap<TX, TY, 1>;
-        constexpr int W = Map::W, PS = Map::N, NS = 4;
-        __shared__ double sm[NS][4][PS];                 // [slot][evisc,u,v,w][tile plane]
+        constexpr int W = Map::W, PS = Map::N, NS = UVW_SLOTS, NT = TX * TY;
+        extern __shared__ __align__(16) double sm[];     // [slot][evisc,u,v,w][tile plane]: NS * 4 * PS doubles (dynamic)
         __shared__ double met[8][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi, threfh, g/threfh at k0-1 .. k1
+        __shared__ unsigned long long full[NS], empty[NS];
 
         const int tid = threadIdx.y * TX + threadIdx.x;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
@@ -286,18 +289,30 @@ namespace
 
         Map map;
         map.init(i0, j0, gd.icells, gd.jcells, tid);
-        auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
+        // Plane ring of NS slots.  Plane k has ordinal q = k - (k0-1) and lives in slot q & (NS-1); it is the (q / NS)-th fill
+        // of that slot.  full[slot] completes when all NT threads' copies of a fill have landed, empty[slot] when all NT
+        // threads have read the fill for the last time (as level k of iteration q-1).
+        if (tid == 0)
+            for (int sl = 0; sl < NS; ++sl) { mbar_init(&full[sl], NT); mbar_init(&empty[sl], NT); }
+        __syncthreads();
+        auto stage = [&](const int q)
         {
-            if (k <= k1)
-            {
-                const int sl = (k - k0 + 1) & (NS - 1);
-                const long off = (long)k * kk;
-                map.issue(sm[sl][0], evisc + off, tid); map.issue(sm[sl][1], u + off, tid);
-                map.issue(sm[sl][2], v + off, tid);     map.issue(sm[sl][3], w + off, tid);
-            }
-            cp_async_commit();
+            const int k = k0 - 1 + q;
+            if (k > k1) return;
+            const int sl = q % NS;
+            if (q >= NS) mbar_wait(&empty[sl], ((q / NS) - 1) & 1);     // the previous fill has been read by everyone
+            double* dst = sm + sl * 4 * PS;
+            const long off = (long)k * kk;
+            map.issue(dst, evisc + off, tid);      map.issue(dst + PS, u + off, tid);
+            map.issue(dst + 2 * PS, v + off, tid); map.issue(dst + 3 * PS, w + off, tid);
+            mbar_arrive_on_cp_async(&full[sl]);
         };
-        stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
+        auto plane = [&](const int q) -> const double*   // waits until plane q is complete in its slot
+        {
+            mbar_wait(&full[q % NS], (q / NS) & 1);
+            return sm + (q % NS) * 4 * PS;
+        };
+        stage(0); stage(1); stage(2); stage(3);
         if (tid < KCHUNK + 2)
         {
             const int k = min(k0 - 1 + tid, gd.kcells - 1);
@@ -310,17 +325,17 @@ namespace
         const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
         const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W, cwn = c + W - 1, cws = c - W - 1, ces = c - W + 1;
 
-        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
-        __syncthreads();
+        __syncthreads();                                 // met[] is complete
         double e_b, e_c, e_wb, e_w, e_sb, e_s, e_eb, e_nb, u_b, u_c, u_eb, v_b, v_c, v_nb, w_b, w_c, w_w, w_s;
         {
-            const double* B = sm[0][0]; const double* C = sm[1][0];
+            const double* B = plane(0); const double* C = plane(1);
             e_b = B[c]; e_wb = B[cw]; e_sb = B[cs]; e_eb = B[ce]; e_nb = B[cn];
             e_c = C[c]; e_w = C[cw]; e_s = C[cs];
             u_b = B[PS + c]; u_eb = B[PS + ce]; u_c = C[PS + c];
             v_b = B[2 * PS + c]; v_nb = B[2 * PS + cn]; v_c = C[2 * PS + c];
             w_b = B[3 * PS + c]; w_c = C[3 * PS + c]; w_w = C[3 * PS + cw]; w_s = C[3 * PS + cs];
         }
+        mbar_arrive(&empty[0]);                          // plane k0-1 is not read again
 
         int ijk = ij + k0 * kk;
         double ut_c = 0., vt_c = 0., wt_c = 0.;
@@ -329,17 +344,16 @@ namespace
         if (BUOY) { th_b = th[ijk - kk]; th_c = th[ijk]; th_n = th[ijk + kk]; }
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
-            __syncthreads();                             // ... for every thread; everyone is done with plane k-1
-            stage(k + 3);                                // into the slot of plane k-1
+            const int it = k - k0;                       // level k: planes it+1 (this level) and it+2 (the level above)
+            stage(it + 4);                               // plane k+3, into the slot last read NS - 4 levels ago
             // tendencies of the next level: in flight during this level's arithmetic
             double ut_n = 0., vt_n = 0., wt_n = 0.;
             if (live && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
             const double th_t = th_n;
             if (BUOY && k + 1 < k1) th_n = th[ijk + 2 * kk];
 
-            const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
-            const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
+            const double* C = sm + ((it + 1) % NS) * 4 * PS;      // complete: it was waited for as T one level ago
+            const double* T = plane(it + 2);
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
             const int km = k - k0 + 1;                   // row of level k in met[]
@@ -355,6 +369,7 @@ namespace
             const double v_wn = C[2 * PS + cwn];
             const double w_t = T[3 * PS + c], w_wt = T[3 * PS + cw], w_st = T[3 * PS + cs];
             const double w_e = C[3 * PS + ce], w_n = C[3 * PS + cn];
+            mbar_arrive(&empty[(it + 1) % NS]);   // this thread's last read of plane k
 
             if (BUOY && k > gd.kstart)      // calc_buoyancy_tend_2nd, src/thermo_dry.cxx:43-62
                 wt_c = wt_c + met[7][km] * (fd::interp2(th_b, th_c) - met[6][km]);
@@ -456,7 +471,6 @@ namespace
             w_b = w_c; w_c = w_t; w_w = w_wt; w_s = w_st;
             ut_c = ut_n; vt_c = vt_n; wt_c = wt_n;
         }
-        cp_async_wait<0>();
     }
 
     // diff_c, src/diff_smag2.cxx:620-708, on shared-memory tiles (the scalar and evisc; with ADVEC also u and v).
@@ -683,7 +697,11 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
     const double* threfh = c->thref_d ? c->thref_d + gd.kcells : nullptr;
     const double* g_threfh = c->thref_d ? c->thref_d + 3 * gd.kcells : nullptr;
     #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd
-    #define UVW_LAUNCH(NAME, S, A, B) MHH_LAUNCH(c, NAME, (smag2_diff_uvw_tile_kernel<S, A, B, TX, TY><<<tg, tb, 0, c->stream>>>(UVW_ARGS)))
+    constexpr size_t smem = (size_t)UVW_SLOTS * 4 * (TX + 2) * (TY + 2) * sizeof(double);
+    #define UVW_LAUNCH(NAME, S, A, B) do { \
+        static bool attr = false; \
+        if (!attr) { cudaFuncSetAttribute(smag2_diff_uvw_tile_kernel<S, A, B, TX, TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; } \
+        MHH_LAUNCH(c, NAME, (smag2_diff_uvw_tile_kernel<S, A, B, TX, TY><<<tg, tb, smem, c->stream>>>(UVW_ARGS))); } while (0)
     if (!advec)
     {
         if (surface_model) UVW_LAUNCH("smag2_diff_uvw_kernel", true, false, false);

@@ -185,6 +185,24 @@ __device__ __forceinline__ void cp_async8(double* smem, const double* g)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template<int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
+// ---- mbarrier (sm_90+) helpers for the plane ring: `full[slot]` is completed by the hardware when every thread's cp.async
+// copies of a plane have landed (cp.async.mbarrier.arrive.noinc), `empty[slot]` when every thread has finished reading it.
+// Both are waited on with try_wait, normally long after they completed: warps of a CTA no longer meet at a
+// __syncthreads() every level and may drift apart by up to the ring depth.
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, const unsigned count)
+{ asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(b)), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(unsigned long long* b)
+{ asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" :: "r"(smem_u32(b)) : "memory"); }
+// arrival triggered when all cp.async issued so far by this thread have completed (counts as this thread's arrival)
+__device__ __forceinline__ void mbar_arrive_on_cp_async(unsigned long long* b)
+{ asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(smem_u32(b)) : "memory"); }
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, const unsigned parity)
+{
+    asm volatile("{\n .reg .pred p;\n MBAR_WAIT:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra MBAR_DONE;\n bra MBAR_WAIT;\n MBAR_DONE:\n}"
+                 :: "r"(smem_u32(b)), "r"(parity) : "memory");
+}
+
 template<int TX, int TY, int H>
 struct TileMap
 {
