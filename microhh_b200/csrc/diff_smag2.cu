@@ -20,6 +20,12 @@ namespace
 #endif
 // slots of the momentum kernel's plane ring: 6 x 4 fields x (34 x 6) doubles = 39 KB keeps four CTAs on an SM
 constexpr int UVW_SLOTS = 6;
+#ifndef MHH_EVISC_MINB
+#define MHH_EVISC_MINB 3
+#endif
+#ifndef MHH_SCALAR_MINB
+#define MHH_SCALAR_MINB 4
+#endif
 #ifndef MHH_UVW_TILE_Y
 #define MHH_UVW_TILE_Y 4      // 32 x 4 columns per CTA, four CTAs per SM: shorter barrier waits than 32 x 8 (4.91 -> 4.66 ms)
 #endif
@@ -45,7 +51,7 @@ constexpr int UVW_SLOTS = 6;
     // Shared-memory tiles: the (TX+2) x (TY+2) planes of u,v,w sit in a ring of four slots filled by cp.async two levels
     // ahead (see TileMap); the columns u_c, u_e, v_c, v_n (levels k-1, k) and the w star (level k) stay in registers.
     template<bool SURF, int MODE, int TX, int TY>
-    __global__ void __launch_bounds__(TX * TY, 3)
+    __global__ void __launch_bounds__(TX * TY, MHH_EVISC_MINB)
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
@@ -55,7 +61,7 @@ constexpr int UVW_SLOTS = 6;
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4;
         __shared__ double sm[NS][3][PS];                 // [slot][u,v,w][tile plane]
-        __shared__ double met[5][KCHUNK + 2];            // dzi, dzhi, z, mlen0, g/thref at k0-1 .. k1
+        __shared__ double met[5][KCHUNK + 2];            // dzi, dzhi, z, mlen0 (thermo: mlen0^2 or its inverse), g/thref at k0-1 .. k1
 
         const int tid = threadIdx.y * TX + threadIdx.x;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
@@ -85,7 +91,8 @@ constexpr int UVW_SLOTS = 6;
         {
             const int k = min(k0 - 1 + tid, gd.kcells - 1);
             met[0][tid] = gd.dzi[k]; met[1][tid] = gd.dzhi[k]; met[2][tid] = gd.z[k];
-            if (MODE != 2) met[3][tid] = mlen0[k];
+            if (MODE == 1) met[3][tid] = mlen0[k];
+            if (MODE == 0 || MODE == 3) met[3][tid] = SURF ? 1. / (mlen0[k] * mlen0[k]) : mlen0[k] * mlen0[k];
             if (MODE == 3) met[4][tid] = mlen0[gd.kcells + k];
         }
 
@@ -204,15 +211,17 @@ constexpr int UVW_SLOTS = 6;
                     n2 = bot ? 0. : n2_c;
                 double rit = div_by((bot ? rare_load(dbdz, ij) : n2) / s2, tPr, tPr_i);
                 rit = fmin(rit, 1. - kDsmall);
+                // mlen^2 * sqrt(s2) * sqrt(1 - rit) with mlen^2 = 1 / (1/mlen0^2 + 1/(kappa (z+z0))^2) taken without the
+                // sqrt-then-square round trip and the two roots merged: <= 3 ulp from the reference expression, and 3 of
+                // the 6 FP64 divide / sqrt sequences per point (the kernel is FP64-issue bound, ncu r01d)
                 if (SURF)
                 {
                     const double kz = kKappa * (met[2][km] + z0);
-                    const double m0 = met[3][km];
-                    const double mlen = sqrt(1. / (1. / (m0 * m0) + 1. / (kz * kz)));
-                    ev = pow2(mlen) * sqrt(s2) * sqrt(1. - rit);
+                    const double mlen2 = 1. / (met[3][km] + 1. / (kz * kz));      // met[3] = 1 / mlen0^2
+                    ev = mlen2 * sqrt(s2 * (1. - rit));
                 }
                 else
-                    ev = pow2(met[3][km]) * sqrt(s2) * sqrt(1. - rit);
+                    ev = met[3][km] * sqrt(s2 * (1. - rit));                      // met[3] = mlen0^2
             }
             else
             {
@@ -478,7 +487,7 @@ constexpr int UVW_SLOTS = 6;
     //        its tendency and evisc cross HBM once for both operators: (t + advection) + diffusion, bit-identical to
     //        Advec::exec followed by Diff::exec.
     template<bool SURF, bool ADVEC, int TX, int TY>
-    __global__ void __launch_bounds__(TX * TY, 3)
+    __global__ void __launch_bounds__(TX * TY, MHH_SCALAR_MINB)
     smag2_scalar_tile_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
                              const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
                              const double tPr, const double visc,
