@@ -35,6 +35,9 @@ BYTES_PER_POINT = {
     "advec2_s_kernel": 48,
     "smag2_diff_uvw_kernel": 80,
     "smag2_diff_c_kernel": 32,
+    # one-pass tendencies (no SURVEY row: they replace thermo + advec + diff of the rows above)
+    "advec2_smag2_uvw_kernel": 88,   # R u,v,w,evisc,th ; R+W ut,vt,wt
+    "advec2_smag2_c_kernel": 56,     # R s,evisc,u,v,w ; R+W st
     "pres2_in_kernel": 56,
     "fft_fwd_x": 16, "fft_fwd_y": 16, "fft_bwd_y": 16, "fft_bwd_x": 16,
     "pres2_tdma_kernel": 32,
@@ -44,7 +47,21 @@ BYTES_PER_POINT = {
     "n2_kernel": 16, "buoyancy_tend_kernel": 24,
     "advec2_cfl_kernel": 24, "smag2_dnmul_kernel": 8,
 }
-BYTES_PER_STEP = 3 * 608 + 32       # 1856 B / grid-point-step
+BYTES_PER_STEP = 3 * 608 + 32       # 1856 B / grid-point-step (the reference's operator-by-operator passes)
+# what this implementation's fused passes move: evisc 40, momentum 88, scalar 56, pres_in 56, 4 FFT passes 64, tdma 32,
+# output+RK 104, scalar RK 32 per substep; cfl 24 + dnmul 8 per step
+BYTES_PER_STEP_FUSED = 3 * 472 + 32
+
+
+def ncu_traffic(kernel, n):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch (GB) from the committed ncu --set full capture of this
+    workload (profiles/r01_traffic.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            t = json.load(f)
+        return t["gb_per_launch"].get(kernel) if t.get("n") == n else None
+    except (OSError, ValueError, KeyError):
+        return None
 
 
 def les_ini(itot, jtot, ktot):
@@ -317,8 +334,10 @@ def main():
                 "steps": e2e_steps},
         "gpu_launches": int(launches),
         "step_hbm_frac": round(BYTES_PER_STEP * pts_local / (ms / args.steps * 1e-3) / 1e9 / peak, 4),
+        "step_hbm_frac_fused_passes": round(BYTES_PER_STEP_FUSED * pts_local / (ms / args.steps * 1e-3) / 1e9 / peak, 4),
         "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
-                     "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None},
+                     "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom_name, n) if world == 1 else None,
+                     "traffic_unit": "GB per launch (ncu dram read+write)", "algorithmic_gb_per_launch": round(algo_bytes / 1e9, 3)},
         "kernels": kernels,
         "status": status,
     }
