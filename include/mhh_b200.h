@@ -180,9 +180,11 @@ int mhh_fft_x(mhh_ctx* ctx, int dir, double* data_X, double* p_or_null);
 int mhh_fft_y(mhh_ctx* ctx, int dir, double* data_Y);
 /* FFT stages that read / write the all-to-all chunk layout directly (chunk for peer r = [k][j<jmax][ii<iblock]), fusing
  * Transpose::exec_xy / exec_yx's pack and unpack copies (src/transpose.cxx:163-217) into the transforms:
- *   x, dir<0: slab X -> chunks;  y, dir<0: received chunks -> Y;  y, dir>0: Y -> chunks;  x, dir>0: received chunks -> X or p */
-int mhh_fft_x_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, double* p_or_null);
-int mhh_fft_y_chunks(mhh_ctx* ctx, int dir, const double* in, double* out);
+ *   x, dir<0: slab X -> chunks;  y, dir<0: received chunks -> Y;  y, dir>0: Y -> chunks;  x, dir>0: received chunks -> X or p
+ * [k0, k0+nk) (nk = 0: all levels) selects a k range whose chunk buffer is laid out on its own,
+ * [k0..][r][k'<nk][j<jmax][ii<iblock], so that the collective of one range overlaps the transforms of the next. */
+int mhh_fft_x_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, double* p_or_null, int k0, int nk);
+int mhh_fft_y_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, int k0, int nk);
 int mhh_fft_chunks_supported(mhh_ctx* ctx);
 int mhh_transpose_copy(mhh_ctx* ctx, int mode, double* dst, const double* src);
 int mhh_pres_solve_spectral_ws(mhh_ctx* ctx, double* data_Y, double* work3d);

@@ -112,48 +112,57 @@ static int fft_y(Ctx* c, int dir, double* data)
 // [k][j < jmax][ii < iblock], chunks ordered by r), so that no pack / unpack pass is needed around the collectives.
 //   x, dir < 0: X -> chunks (send side of exec_xy)       x, dir > 0: chunks (received, exec_yx) -> X or p
 //   y, dir < 0: chunks (received, exec_xy) -> Y          y, dir > 0: Y -> chunks (send side of exec_yx)
-static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* p)
+// [k0, k0+nk): the k range handled by this call.  The chunk buffer of a k range is laid out on its own,
+// [k0 .. ][r][k' < nk][j < jmax][ii < iblock], so that the all-to-all of one k range can run while the transforms of the
+// next are computed (nk = kmax: one collective for the whole slab).
+static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* p, int k0, int nk)
 {
     const GridD& gd = c->gd;
-    const long R = (long)gd.kmax * gd.jmax * c->iblock;       // one chunk
+    if (nk <= 0) { k0 = 0; nk = gd.kmax; }
+    if (k0 < 0 || k0 + nk > gd.kmax) return MHH_ERR_ARG;
+    const long R = (long)nk * gd.jmax * c->iblock;            // one peer's chunk of this k range
+    const long cbase = (long)k0 * c->npy * gd.jmax * c->iblock, xbase = (long)k0 * gd.jmax * gd.itot;
     FftLayout L;
-    L.nlines = gd.jmax * gd.kmax; L.base_in = 0; L.base_out = 0;
+    L.nlines = gd.jmax * nk;
     L.scale = dir < 0 ? 1. : 1. / gd.itot;
     if (dir < 0)
     {
-        L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1;
-        L.n1o = L.nlines; L.s1o = c->iblock; L.s2o = 0; L.sno = 1; L.esplit_out = c->iblock; L.eseg_out = R;
+        L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = xbase;
+        L.n1o = L.nlines; L.s1o = c->iblock; L.s2o = 0; L.sno = 1; L.esplit_out = c->iblock; L.eseg_out = R; L.base_out = cbase;
         return fft_lines(c, c->plan_i, -1, in, out, L);
     }
-    L.n1 = L.nlines; L.s1 = c->iblock; L.s2 = 0; L.sn = 1; L.esplit_in = c->iblock; L.eseg_in = R;
-    L.n1o = L.nlines; L.s1o = gd.itot; L.s2o = 0; L.sno = 1;
+    L.n1 = L.nlines; L.s1 = c->iblock; L.s2 = 0; L.sn = 1; L.esplit_in = c->iblock; L.eseg_in = R; L.base_in = cbase;
+    L.n1o = L.nlines; L.s1o = gd.itot; L.s2o = 0; L.sno = 1; L.base_out = xbase;
     if (p != nullptr)
     {
         L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells;
-        L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
+        L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)(gd.kgc + k0) * gd.ijcells;
         out = p;
     }
     return fft_lines(c, c->plan_i, +1, in, out, L);
 }
 
-static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out)
+static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, int nk)
 {
     const GridD& gd = c->gd;
-    const long R = (long)gd.kmax * gd.jmax * c->iblock;
+    if (nk <= 0) { k0 = 0; nk = gd.kmax; }
+    if (k0 < 0 || k0 + nk > gd.kmax) return MHH_ERR_ARG;
+    const long R = (long)nk * gd.jmax * c->iblock;
+    const long cbase = (long)k0 * c->npy * gd.jmax * c->iblock, ybase = (long)k0 * c->iblock * gd.jtot;
     FftLayout L;
-    L.nlines = c->iblock * gd.kmax; L.base_in = 0; L.base_out = 0;
+    L.nlines = c->iblock * nk;
     L.scale = dir < 0 ? 1. : 1. / gd.jtot;
     // Y side: lines (ii, k), element j at stride iblock;  chunk side: element j = (r, j') at r*R + j'*iblock
     L.n1 = c->iblock; L.s1 = 1; L.sn = c->iblock; L.n1o = c->iblock; L.s1o = 1; L.sno = c->iblock;
     if (dir < 0)
     {
-        L.s2 = (long)gd.jmax * c->iblock; L.esplit_in = gd.jmax; L.eseg_in = R;
-        L.s2o = (long)c->iblock * gd.jtot;
+        L.s2 = (long)gd.jmax * c->iblock; L.esplit_in = gd.jmax; L.eseg_in = R; L.base_in = cbase;
+        L.s2o = (long)c->iblock * gd.jtot; L.base_out = ybase;
     }
     else
     {
-        L.s2 = (long)c->iblock * gd.jtot;
-        L.s2o = (long)gd.jmax * c->iblock; L.esplit_out = gd.jmax; L.eseg_out = R;
+        L.s2 = (long)c->iblock * gd.jtot; L.base_in = ybase;
+        L.s2o = (long)gd.jmax * c->iblock; L.esplit_out = gd.jmax; L.eseg_out = R; L.base_out = cbase;
     }
     return fft_lines(c, c->plan_j, dir, in, out, L);
 }
@@ -517,9 +526,10 @@ int mhh_pres_output(mhh_ctx* c, double* ut, double* vt, double* wt, double* p)
 // ---- y-slab stages (multi-GPU driver): see microhh_b200/multigpu.py for the call order
 int mhh_fft_x(mhh_ctx* c, int dir, double* data, double* p_or_null) { PRES_READY(c); return fft_x(c, dir, data, p_or_null); }
 int mhh_fft_y(mhh_ctx* c, int dir, double* data) { PRES_READY(c); return fft_y(c, dir, data); }
-int mhh_fft_x_chunks(mhh_ctx* c, int dir, const double* in, double* out, double* p_or_null)
-{ PRES_READY(c); return fft_x_chunks(c, dir, in, out, p_or_null); }
-int mhh_fft_y_chunks(mhh_ctx* c, int dir, const double* in, double* out) { PRES_READY(c); return fft_y_chunks(c, dir, in, out); }
+int mhh_fft_x_chunks(mhh_ctx* c, int dir, const double* in, double* out, double* p_or_null, int k0, int nk)
+{ PRES_READY(c); return fft_x_chunks(c, dir, in, out, p_or_null, k0, nk); }
+int mhh_fft_y_chunks(mhh_ctx* c, int dir, const double* in, double* out, int k0, int nk)
+{ PRES_READY(c); return fft_y_chunks(c, dir, in, out, k0, nk); }
 // 1 when the chunk-layout FFT stages are available (both lengths on the register-resident power-of-two kernel and the
 // per-rank blocks powers of two); otherwise the driver falls back to mhh_transpose_copy around mhh_fft_x / mhh_fft_y
 int mhh_fft_chunks_supported(mhh_ctx* c)

@@ -50,6 +50,13 @@ class SlabComm:
         else:
             dist.all_to_all_single(out, inp, group=self.group)
 
+    def all_to_all_async(self, out, inp):
+        """all_to_all on NCCL's own stream; returns a handle whose wait() makes the current stream wait for it (or None)."""
+        if self.world == 1:
+            out.copy_(inp)
+            return None
+        return dist.all_to_all_single(out, inp, group=self.group, async_op=True)
+
     def allreduce_max(self, value, device):
         t = torch.tensor([value], dtype=torch.float64, device=device)
         if self.world > 1:
@@ -106,6 +113,7 @@ class SlabPres(Pres):
         self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
+        self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours
 
     def exec(self, dt, stats=None, timeloop=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
@@ -121,14 +129,29 @@ class SlabPres(Pres):
         self.cyclic.exec(vt, L.EDGE_NORTH_SOUTH)
         ck(lib.mhh_pres_input_to(g.ctx, L.ptr(u), L.ptr(v), L.ptr(w), L.ptr(ut), L.ptr(vt), L.ptr(wt), C.c_double(dt), A), "pres_input")
         if self.chunk_fft:
-            # the transforms read / write the all-to-all chunk layout themselves: no pack / unpack passes
-            ck(lib.mhh_fft_x_chunks(g.ctx, -1, A, B, None), "fft_x fwd -> chunks")
-            self.comm.all_to_all(self.A, self.B)
-            ck(lib.mhh_fft_y_chunks(g.ctx, -1, A, B), "chunks -> fft_y fwd")
+            # The transforms read / write the all-to-all chunk layout themselves (no pack / unpack passes), and the slab is
+            # cut into k ranges: the collective of one range runs on NCCL's stream while the transforms of the next are
+            # computed (the tridiagonal solve in the middle needs all levels and is the only join).
+            nc = self.kranges if g.kmax % self.kranges == 0 else 1
+            nk, seg = g.kmax // nc, (g.kmax // nc) * g.jmax * g.itot
+            part = lambda t, c: t[c * seg:(c + 1) * seg]
+            works = []
+            for c in range(nc):
+                ck(lib.mhh_fft_x_chunks(g.ctx, -1, A, B, None, c * nk, nk), "fft_x fwd -> chunks")
+                works.append(self.comm.all_to_all_async(part(self.A, c), part(self.B, c)))
+            for c in range(nc):
+                if works[c] is not None:
+                    works[c].wait()
+                ck(lib.mhh_fft_y_chunks(g.ctx, -1, A, B, c * nk, nk), "chunks -> fft_y fwd")
             ck(lib.mhh_pres_solve_spectral_ws(g.ctx, B, A), "tdma")
-            ck(lib.mhh_fft_y_chunks(g.ctx, +1, B, A), "fft_y bwd -> chunks")
-            self.comm.all_to_all(self.B, self.A)
-            ck(lib.mhh_fft_x_chunks(g.ctx, +1, B, None, L.ptr(p)), "chunks -> fft_x bwd")
+            works = []
+            for c in range(nc):
+                ck(lib.mhh_fft_y_chunks(g.ctx, +1, B, A, c * nk, nk), "fft_y bwd -> chunks")
+                works.append(self.comm.all_to_all_async(part(self.B, c), part(self.A, c)))
+            for c in range(nc):
+                if works[c] is not None:
+                    works[c].wait()
+                ck(lib.mhh_fft_x_chunks(g.ctx, +1, B, None, L.ptr(p), c * nk, nk), "chunks -> fft_x bwd")
         else:
             # forward: x FFT, exec_xy, y FFT (src/fft.cxx:452-516 with npx = 1)
             ck(lib.mhh_fft_x(g.ctx, -1, A, None), "fft_x fwd")
