@@ -64,6 +64,20 @@ def ncu_traffic(kernel, n):
         return None
 
 
+def weak_scaling_shape(n, world):
+    """Global grid with n^3 points per GPU, y-slabs.  The point count per GPU is fixed (weak scaling); the extra points go
+    to y first, then x, then z, which keeps the transform lengths at <= 2n: 512^3, 512x1024x512, 1024x1024x512
+    (BASELINE configs[4]'s named shape, on 4 GPUs), 1024x1024x1024."""
+    shape = [n, n, n]               # itot, jtot, ktot
+    order = [1, 0, 2]
+    w, a = world, 0
+    while w > 1 and w % 2 == 0:
+        shape[order[a % 3]] *= 2
+        w //= 2; a += 1
+    shape[1] *= w                   # a non-power-of-two remainder goes to y
+    return tuple(shape)
+
+
 def les_ini(itot, jtot, ktot):
     size = 12.5
     return {
@@ -257,12 +271,11 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    ini = les_ini(n, n, n)
-    z = (np.arange(n) + 0.5) * (ini["grid"]["zsize"] / n)
+    itot, jtot, ktot = weak_scaling_shape(n, world)
+    ini = les_ini(itot, jtot, ktot)
+    z = (np.arange(ktot) + 0.5) * (ini["grid"]["zsize"] / ktot)
     if world > 1:
         from microhh_b200.multigpu import SlabModel
-        ini["grid"]["jtot"] = n * world
-        ini["grid"]["ysize"] = 12.5 * n * world
         model = SlabModel(ini, z, device=dev, rank=rank, world=world)
     else:
         model = Model(ini, z, device=dev)
@@ -357,8 +370,8 @@ def main():
         "metric": "grid-point-steps/s (full RK3 step)", "value": value, "unit": "grid-point-steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"gabls1-like LES {n}x{n * world}x{n} (advec_2, smag2+surface rows, thermo dry, pres_2, RK3), "
-                               f"{n}^3 per GPU, y-slabs", "l2": "inputs larger than L2 (each 3-D field 1.09 GB)",
+        "config": {"workload": f"gabls1-like LES {itot}x{jtot}x{ktot} (advec_2, smag2+surface rows, thermo dry, pres_2, RK3), "
+                               f"{n}^3 grid points per GPU, y-slabs", "l2": "inputs larger than L2 (each 3-D field 1.09 GB)",
                    "bytes_per_gridpoint_step": BYTES_PER_STEP},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_value, "unit": "grid-point-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 6 * 8,

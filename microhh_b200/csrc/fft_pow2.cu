@@ -16,6 +16,8 @@
 #include <cmath>
 #include <vector>
 
+#include <cstdlib>
+
 #include "ctx.h"
 #include "fft.h"
 
@@ -438,11 +440,16 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     A.scale = L.scale;
     const bool strided = (L.sn != 1) || (L.sno != 1);
     const int npairs = BLOCK / (plan.n / 8);
-    // strided (y) passes: two pair groups per CTA when that still leaves >= 2 CTAs of work per SM and fits 3 CTAs/SM
-    constexpr int NGS = 2;
+    // strided (y) passes: several pair groups per CTA (wider rows of the staged tile) while the tile fits the shared-memory
+    // budget and the grid still fills the machine; MHH_FFT_NG (test hook) caps the group count
     const size_t pair_bytes = (size_t)((plan.n + plan.n / 8) + 1) * sizeof(double2);
-    const bool wide = strided && (size_t)NGS * npairs * pair_bytes <= 76 * 1024 && L.nlines >= 2 * npairs * NGS * 296;
-    const int ng = wide ? NGS : 1;
+    int ng = 1;
+    if (strided)
+    {
+        static const int ng_cap = []() { const char* e = getenv("MHH_FFT_NG"); return e ? atoi(e) : 2; }();
+        for (int cand = 2; cand <= ng_cap && cand <= 4; cand *= 2)
+            if ((size_t)cand * npairs * pair_bytes <= (cand == 2 ? 76 : 200) * 1024 && L.nlines >= 2 * npairs * cand * 296) ng = cand;
+    }
     const int lines = 2 * npairs * ng;
     const size_t smem = (size_t)npairs * ng * pair_bytes;
     const int nblocks = (L.nlines + lines - 1) / lines;
@@ -455,11 +462,11 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     const char* name = dir < 0 ? (strided ? "fft_fwd_y" : "fft_fwd_x") : (strided ? "fft_bwd_y" : "fft_bwd_x");
     #define P2_LAUNCH(D, S, G, SP) do { \
         static bool attr = false; \
-        if (!attr) { cudaFuncSetAttribute(fft_pow2_kernel<D, S, G, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; } \
+        if (!attr) { cudaFuncSetAttribute(fft_pow2_kernel<D, S, G, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024); attr = true; } \
         MHH_LAUNCH(c, name, (fft_pow2_kernel<D, S, G, SP><<<nblocks, BLOCK, smem, c->stream>>>(in, out, A))); } while (0)
     #define P2_DISPATCH(SP) do { \
-        if (dir < 0) { if (strided && wide) P2_LAUNCH(-1, true, NGS, SP); else if (strided) P2_LAUNCH(-1, true, 1, SP); else P2_LAUNCH(-1, false, 1, SP); } \
-        else         { if (strided && wide) P2_LAUNCH(1, true, NGS, SP);  else if (strided) P2_LAUNCH(1, true, 1, SP);  else P2_LAUNCH(1, false, 1, SP); } } while (0)
+        if (dir < 0) { if (strided && ng == 4) P2_LAUNCH(-1, true, 4, SP); else if (strided && ng == 2) P2_LAUNCH(-1, true, 2, SP); else if (strided) P2_LAUNCH(-1, true, 1, SP); else P2_LAUNCH(-1, false, 1, SP); } \
+        else         { if (strided && ng == 4) P2_LAUNCH(1, true, 4, SP);  else if (strided && ng == 2) P2_LAUNCH(1, true, 2, SP);  else if (strided) P2_LAUNCH(1, true, 1, SP);  else P2_LAUNCH(1, false, 1, SP); } } while (0)
     if (split) P2_DISPATCH(true); else P2_DISPATCH(false);
     #undef P2_DISPATCH
     #undef P2_LAUNCH
