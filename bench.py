@@ -269,6 +269,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device(f"cuda:{local_rank}")
     if world > 1:
+        from microhh_b200.multigpu import nccl_env_defaults
+        nccl_env_defaults()
         dist.init_process_group("nccl", device_id=dev)
 
     itot, jtot, ktot = weak_scaling_shape(n, world)

@@ -69,6 +69,8 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
     if world > 1:
+        from microhh_b200.multigpu import nccl_env_defaults
+        nccl_env_defaults()
         dist.init_process_group("nccl", device_id=dev)
     out, status, ref = run(rank, world, dev, dims=(64, 64, 32))
     gathered = [None] * world
