@@ -217,7 +217,8 @@ constexpr int UVW_SLOTS = 6;
                 if (SURF)
                 {
                     const double kz = kKappa * (met[2][km] + z0);
-                    const double mlen2 = 1. / (met[3][km] + 1. / (kz * kz));      // met[3] = 1 / mlen0^2
+                    const double kz2 = kz * kz;
+                    const double mlen2 = kz2 / (met[3][km] * kz2 + 1.);           // met[3] = 1 / mlen0^2; one division, not two
                     ev = mlen2 * sqrt(s2 * (1. - rit));
                 }
                 else
