@@ -172,6 +172,18 @@ __device__ __forceinline__ void prefetch_l2(const void* p)
 #endif
 }
 
+// 1/x to within ~1 ulp for normal, non-zero x: hardware seed (rcp.approx, ~20 bits) + two Newton steps (4 FMAs) instead of
+// the ~20-instruction IEEE division sequence.  Used where a quotient feeds an iterative solve, not a compared tendency.
+__device__ __forceinline__ double fast_rcp(const double x)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.);
+    return fma(r, e, r);
+}
+
 // ---- asynchronous staging of ghost-celled (i,j) tiles into shared memory ---------------------------------------------
 // The k-marching stencil kernels keep a ring of tile planes (interior TX x TY plus a halo of H) in shared memory.  Planes
 // are fetched with cp.async (LDGSTS, 8-byte elements: ghost-celled rows are only 8-byte aligned) two levels ahead of

@@ -50,9 +50,16 @@ namespace
         }
     }
 
-    // solve_in + tdma fused: one thread per (kx,ky) column, k sequential, i-fastest coalescing.
+    // solve_in + tdma fused (src/pres_2.cxx:267-349, tdma :202-232): one thread per (kx,ky) column, k sequential, i-fastest
+    // coalescing.  The reference keeps c' = c[k-1]/work2d for the back substitution in a full 3-D work array; here only the
+    // reciprocal pivot 1/work2d is checkpointed every TDMA_M levels, and the back substitution recomputes the c' of one
+    // block of levels from its checkpoint into registers: 4 + 2/TDMA_M field passes over HBM instead of 6.  Each level
+    // costs one reciprocal (fast_rcp, ~1 ulp) per sweep instead of the reference's two divisions: the kernel is otherwise
+    // FP64-issue bound on B200 (the IEEE division sequence is ~20 instructions on a k-sequential chain).
+    constexpr int TDMA_M = 16;
+
     __global__ void __launch_bounds__(128)
-    pres2_tdma_kernel(double* __restrict__ p, double* __restrict__ work3d,
+    pres2_tdma_kernel(double* __restrict__ p, double* __restrict__ ckpt,
                       const double* __restrict__ a, const double* __restrict__ c,
                       const double* __restrict__ bmati, const double* __restrict__ bmatj,
                       const int iblock, const int jblock, const int ioff, const int joff, const GridD gd)
@@ -82,28 +89,55 @@ namespace
             return dz * dz * p[ij + k * kk];
         };
 
-        double work2d = bdiag(0);
-        double pprev = rhs(0) / work2d;
+        // forward elimination; r = 1/work2d of levels 0, M, 2M, ... goes to the checkpoint array
+        double r = fast_rcp(bdiag(0));
+        double pprev = rhs(0) * r;
         p[ij] = pprev;
+        ckpt[ij] = r;
         for (int k = 1; k < kmax; ++k)
         {
             if (k + 4 < kmax) prefetch_l2(p + ij + (k + 4) * kk);
-            const double w3 = c[k - 1] / work2d;
-            work3d[ij + k * kk] = w3;
-            work2d = bdiag(k) - a[k] * w3;
+            const double w3 = c[k - 1] * r;
+            r = fast_rcp(bdiag(k) - a[k] * w3);
             double pk = rhs(k);
             pk -= a[k] * pprev;
-            pk /= work2d;
+            pk *= r;
             p[ij + k * kk] = pk;
             pprev = pk;
+            if ((k & (TDMA_M - 1)) == 0) ckpt[ij + (k / TDMA_M) * kk] = r;
         }
-        for (int k = kmax - 2; k >= 0; --k)
+        // back substitution, block by block from the top: p[k] -= w3[k+1] * p[k+1]
+        for (int kb = ((kmax - 1) / TDMA_M) * TDMA_M; kb >= 0; kb -= TDMA_M)
         {
-            if (k >= 4) { prefetch_l2(p + ij + (k - 4) * kk); prefetch_l2(work3d + ij + (k - 3) * kk); }
-            double pk = p[ij + k * kk];
-            pk -= work3d[ij + (k + 1) * kk] * pprev;
-            p[ij + k * kk] = pk;
-            pprev = pk;
+            // w3 of levels kb+1 .. kb+M recomputed from 1/work2d(kb) exactly as the forward sweep formed them
+            double w3[TDMA_M];
+            double rr = ckpt[ij + (kb / TDMA_M) * kk];
+            #pragma unroll
+            for (int m = 0; m < TDMA_M; ++m)
+            {
+                const int k = kb + m + 1;
+                if (k < kmax)
+                {
+                    w3[m] = c[k - 1] * rr;
+                    if (m + 1 < TDMA_M) rr = fast_rcp(bdiag(k) - a[k] * w3[m]);
+                }
+                else
+                    w3[m] = 0.;
+            }
+            if (kb >= TDMA_M) prefetch_l2(ckpt + ij + (kb / TDMA_M - 1) * kk);
+            #pragma unroll
+            for (int m = TDMA_M - 1; m >= 0; --m)
+            {
+                const int k = kb + m;
+                if (k < kmax - 1)
+                {
+                    if (k >= 4) prefetch_l2(p + ij + (k - 4) * kk);
+                    double pk = p[ij + k * kk];
+                    pk -= w3[m] * pprev;
+                    p[ij + k * kk] = pk;
+                    pprev = pk;
+                }
+            }
         }
     }
 
