@@ -209,20 +209,21 @@ constexpr int UVW_SLOTS = 6;
                 }
                 else
                     n2 = bot ? 0. : n2_c;
-                double rit = div_by((bot ? rare_load(dbdz, ij) : n2) / s2, tPr, tPr_i);
+                double rit = div_by((bot ? rare_load(dbdz, ij) : n2) * fast_rcp(s2), tPr, tPr_i);
                 rit = fmin(rit, 1. - kDsmall);
                 // mlen^2 * sqrt(s2) * sqrt(1 - rit) with mlen^2 = 1 / (1/mlen0^2 + 1/(kappa (z+z0))^2) taken without the
-                // sqrt-then-square round trip and the two roots merged: <= 3 ulp from the reference expression, and 3 of
-                // the 6 FP64 divide / sqrt sequences per point (the kernel is FP64-issue bound, ncu r01d)
+                // sqrt-then-square round trip, the two roots merged, and the remaining quotients / root through fast_rcp /
+                // fast_sqrt (~1 ulp each): a few ulp from the reference expression (tolerance 1e-12) at a fraction of the six
+                // IEEE divide / sqrt sequences per point (the kernel is FP64-issue bound, ncu r01d)
                 if (SURF)
                 {
                     const double kz = kKappa * (met[2][km] + z0);
                     const double kz2 = kz * kz;
-                    const double mlen2 = kz2 / (met[3][km] * kz2 + 1.);           // met[3] = 1 / mlen0^2; one division, not two
-                    ev = mlen2 * sqrt(s2 * (1. - rit));
+                    const double mlen2 = kz2 * fast_rcp(met[3][km] * kz2 + 1.);   // met[3] = 1 / mlen0^2; one reciprocal, not two divisions
+                    ev = mlen2 * fast_sqrt(s2 * (1. - rit));
                 }
                 else
-                    ev = met[3][km] * sqrt(s2 * (1. - rit));                      // met[3] = mlen0^2
+                    ev = met[3][km] * fast_sqrt(s2 * (1. - rit));                 // met[3] = mlen0^2
             }
             else
             {

@@ -184,6 +184,19 @@ __device__ __forceinline__ double fast_rcp(const double x)
     return fma(r, e, r);
 }
 
+// sqrt(x) to within ~1 ulp for normal, positive x: hardware seed (rsqrt.approx) + two Newton steps on 1/sqrt(x) and one
+// correction of the root, instead of the IEEE sqrt sequence.
+__device__ __forceinline__ double fast_sqrt(const double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    y = fma(y, fma(-hx * y, y, 0.5), y);          // y += y (1/2 - x y^2 / 2)
+    y = fma(y, fma(-hx * y, y, 0.5), y);
+    const double s = x * y;
+    return fma(0.5 * y, fma(-s, s, x), s);        // s += (x - s^2) y / 2
+}
+
 // ---- asynchronous staging of ghost-celled (i,j) tiles into shared memory ---------------------------------------------
 // The k-marching stencil kernels keep a ring of tile planes (interior TX x TY plus a halo of H) in shared memory.  Planes
 // are fetched with cp.async (LDGSTS, 8-byte elements: ghost-celled rows are only 8-byte aligned) two levels ahead of
