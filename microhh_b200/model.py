@@ -127,3 +127,42 @@ class Model:
         return dict(iter=tl.iteration, time=tl.time, dt=tl.dt, cfl=self.advec.get_cfl(tl.dt), dn=self.diff.get_dn(tl.dt),
                     div=div, mom=self.fields.check_momentum(), tke=self.fields.check_tke(),
                     mass=self.fields.check_mass())
+
+
+class HostFeed:
+    """Double-buffered host -> device feed of the prognostic fields for a host model that keeps its state in (pinned) host
+    memory: the upload of step n+1 runs on a copy stream while step n computes.  submit() enqueues an upload into the free
+    staging slot, adopt() makes the compute stream wait for the oldest submitted upload and copies it into the model's
+    fields (device to device)."""
+
+    def __init__(self, model):
+        import torch
+        self.model, self.torch = model, torch
+        f = model.fields
+        self.targets = {**{n: f.mp[n].fld for n in f.mp}, **{n: f.sp[n].fld for n in f.sp}}
+        self.stage = [{n: torch.empty_like(t) for n, t in self.targets.items()} for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=model.grid.device)
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]      # upload into slot finished
+        self.free = [torch.cuda.Event(), torch.cuda.Event()]       # slot has been consumed by adopt()
+        self.nsub = self.nadopt = 0
+
+    def submit(self, pinned):
+        torch = self.torch
+        slot = self.nsub % 2
+        with torch.cuda.stream(self.copy_stream):
+            if self.nsub >= 2:
+                self.copy_stream.wait_event(self.free[slot])
+            for n, src in pinned.items():
+                self.stage[slot][n].copy_(src, non_blocking=True)
+            self.ready[slot].record(self.copy_stream)
+        self.nsub += 1
+
+    def adopt(self):
+        torch = self.torch
+        slot = self.nadopt % 2
+        cur = torch.cuda.current_stream(self.model.grid.device)
+        cur.wait_event(self.ready[slot])
+        for n, dst in self.targets.items():
+            dst.copy_(self.stage[slot][n], non_blocking=True)
+        self.free[slot].record(cur)
+        self.nadopt += 1
