@@ -48,9 +48,9 @@ BYTES_PER_POINT = {
     "advec2_cfl_kernel": 24, "smag2_dnmul_kernel": 8,
 }
 BYTES_PER_STEP = 3 * 608 + 32       # 1856 B / grid-point-step (the reference's operator-by-operator passes)
-# what this implementation's fused passes move: evisc 40, momentum 88, scalar 56, pres_in 56, 4 FFT passes 64, tdma 32,
-# output+RK 104, scalar RK 32 per substep; cfl 24 + dnmul 8 per step
-BYTES_PER_STEP_FUSED = 3 * 472 + 32
+# what this implementation's fused passes move: evisc 40, momentum 88, scalar 56, pres_in 56, 4 FFT passes 64, tdma 28
+# (two sweeps over p + pivot checkpoints), output+RK 104, scalar RK 32 per substep; cfl 24 + dnmul 8 per step
+BYTES_PER_STEP_FUSED = 3 * 468 + 32
 
 
 def ncu_traffic(kernel, n):
