@@ -39,6 +39,20 @@ def _worker(rank, world, port, q):
     comm.all_to_all(back, torch.from_numpy(np.ascontiguousarray(send2)).reshape(-1))
     c2 = back.numpy().reshape(world, kmax, jmax, iblock)
     ok &= np.array_equal(np.concatenate([c2[r] for r in range(world)], axis=2), X)
+    # the same transpose cut into k ranges, each with its own chunk buffer [c][r][k' < nk][j][ii] and its own
+    # asynchronous all-to-all (SlabPres.kranges): the segments must reassemble the same Y
+    nc, nk = 3, 1
+    seg = nk * jmax * itot
+    sendk = np.concatenate([np.stack([X[c * nk:(c + 1) * nk, :, r * iblock:(r + 1) * iblock] for r in range(world)]).reshape(-1)
+                            for c in range(nc)])
+    send_t, recv_t = torch.from_numpy(np.ascontiguousarray(sendk)), torch.zeros(sendk.size, dtype=torch.float64)
+    works = [comm.all_to_all_async(recv_t[c * seg:(c + 1) * seg], send_t[c * seg:(c + 1) * seg]) for c in range(nc)]
+    for w in works:
+        if w is not None:
+            w.wait()
+    Yk = np.concatenate([np.concatenate(list(recv_t.numpy()[c * seg:(c + 1) * seg].reshape(world, nk, jmax, iblock)), axis=1)
+                         for c in range(nc)], axis=0)
+    ok &= np.array_equal(Yk, Y)
     ok &= comm.allreduce_max(float(rank), "cpu") == world - 1
     ok &= float(comm.allreduce_sum([1.0, float(rank)], "cpu")[1]) == sum(range(world))
     q.put((rank, ok))
