@@ -77,7 +77,9 @@ namespace
         }
     }
 
-    struct Row { double u4, u5, u6, u7, y; };
+    // A row of U after elimination; the pivot is kept as its reciprocal (one fast_rcp per row instead of the reference's
+    // four divisions by it: three in the rows below, one in the back substitution)
+    struct Row { double u4i, u5, u6, u7, y; };
 
     // One elimination step of hdma (src/pres_4.cxx:636-647 and the reduced rows :597-634,:658-686) fused with
     // Ly = p (:691-708): a,b,c are rows r-1, r-2, r-3 after elimination.
@@ -85,10 +87,10 @@ namespace
                                              double rhs, const Row& a, const Row& b, const Row& c)
     {
         Row n;
-        const double l1 = m1 / c.u4;
-        const double l2 = (m2 - l1 * c.u5) / b.u4;
-        const double l3 = (m3 - l2 * b.u5 - l1 * c.u6) / a.u4;
-        n.u4 = m4 - l3 * a.u5 - l2 * b.u6 - l1 * c.u7;
+        const double l1 = m1 * c.u4i;
+        const double l2 = (m2 - l1 * c.u5) * b.u4i;
+        const double l3 = (m3 - l2 * b.u5 - l1 * c.u6) * a.u4i;
+        n.u4i = fast_rcp(m4 - l3 * a.u5 - l2 * b.u6 - l1 * c.u7);
         n.u5 = m5 - l3 * a.u6 - l2 * b.u7;
         n.u6 = m6 - l3 * a.u7;
         n.u7 = m7;
@@ -96,7 +98,10 @@ namespace
         return n;
     }
 
-    // bands: m1..m7, kmax each; fac: 4 arrays (u4,u5,u6,u7) of iblock*jblock*kmax
+    // bands: m1..m7, kmax each; fac: 3 arrays (1/u4, u5, u6) of iblock*jblock*kmax (u7 = m7 is a per-level constant and is
+    // re-read from the bands).  A checkpoint-and-recompute variant as in pres2_tdma_kernel (5.5 instead of 10 field
+    // passes) was measured SLOWER here (1.59 vs 1.39 ms at 512x512x256): one elimination step is ~30 dependent FP64
+    // operations, and rebuilding the rows doubles the k-sequential chain this kernel is bound by.
     __global__ void __launch_bounds__(128)
     pres4_hdma_kernel(double* __restrict__ p, double* __restrict__ fac, const double* __restrict__ bands,
                       const double* __restrict__ bmati, const double* __restrict__ bmatj,
@@ -122,9 +127,10 @@ namespace
         for (int k = 0; k < kmax; ++k)
         {
             const size_t o = ij + k * kk;
+            if (k + 4 < kmax) prefetch_l2(p + o + 4 * kk);
             const Row r = eliminate(bands[k], bands[kmax + k], bands[2 * kmax + k], bands[3 * kmax + k] + bm,
                                     bands[4 * kmax + k], bands[5 * kmax + k], bands[6 * kmax + k], p[o], a, b, c);
-            fac[o] = r.u4; fac[n + o] = r.u5; fac[2 * n + o] = r.u6; fac[3 * n + o] = r.u7;
+            fac[o] = r.u4i; fac[n + o] = r.u5; fac[2 * n + o] = r.u6;
             p[o] = r.y;
             c = b; b = a; a = r;
         }
@@ -141,14 +147,15 @@ namespace
             t3 = eliminate(-1., 0., 0., 1., 0., 0., 0., 0., t2, a, b);
         }
         // Ux = y backward (:711-728). x3 = x[r+3], x2 = x[r+2], x1 = x[r+1]
-        double x3 = t3.y / t3.u4;
-        double x2 = (t2.y - x3 * t2.u5) / t2.u4;
-        double x1 = (a.y - x2 * a.u5 - x3 * a.u6) / a.u4;      // row kmax+1 = level kmax-1
+        double x3 = t3.y * t3.u4i;
+        double x2 = (t2.y - x3 * t2.u5) * t2.u4i;
+        double x1 = (a.y - x2 * a.u5 - x3 * a.u6) * a.u4i;     // row kmax+1 = level kmax-1
         p[ij + (size_t)(kmax - 1) * kk] = x1;
         for (int k = kmax - 2; k >= 0; --k)
         {
             const size_t o = ij + k * kk;
-            const double x = (p[o] - x1 * fac[n + o] - x2 * fac[2 * n + o] - x3 * fac[3 * n + o]) / fac[o];
+            if (k >= 4) { prefetch_l2(p + o - 4 * kk); prefetch_l2(fac + o - 4 * kk); prefetch_l2(fac + n + o - 4 * kk); prefetch_l2(fac + 2 * n + o - 4 * kk); }
+            const double x = (p[o] - x1 * fac[n + o] - x2 * fac[2 * n + o] - x3 * bands[6 * kmax + k]) * fac[o];
             p[o] = x;
             x3 = x2; x2 = x1; x1 = x;
         }
@@ -315,7 +322,7 @@ int pres4_solve_spectral(Ctx* c, double* data)
     const GridD& gd = c->gd;
     const size_t n = (size_t)c->iblock * c->jblock * gd.kmax;
     if (!c->work_h)
-        MHH_CUDA_CHECK(cudaMalloc(&c->work_h, sizeof(double) * 4 * n));
+        MHH_CUDA_CHECK(cudaMalloc(&c->work_h, sizeof(double) * 3 * n));
     dim3 b(128), g((c->iblock + 127) / 128, c->jblock);
     MHH_LAUNCH(c, "pres4_hdma_kernel", pres4_hdma_kernel<<<g, b, 0, c->stream>>>(data, c->work_h, c->bands_d, c->bmati_d, c->bmatj_d,
                                               c->iblock, c->jblock, c->rank_y * c->iblock, 0, gd.kmax));
