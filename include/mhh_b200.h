@@ -214,9 +214,11 @@ int mhh_set_bc(mhh_ctx* ctx, double* a2d, double* agrad2d, double* aflux2d, int 
 /* --- Timeloop<TF>::exec (src/timeloop.cxx:358; rk3 :250, rk4 :288) -------------------------------------- */
 int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, double dt,
                    int nfields, double* const* a, double* const* at);
-/* Fused tail of the substep (no reference counterpart: Pres_2::output src/pres_2.cxx:365-387 immediately followed by
- * Timeloop::exec src/timeloop.cxx:358-411 for u,v,w).  Bit-identical to mhh_pres_output / mhh_pres_exec followed by
- * mhh_rk_substep on (u,v,w); the caller runs mhh_rk_substep on the remaining fields with the same substep. */
+/* Fused tail of the substep (no reference counterpart: Pres_2::output src/pres_2.cxx:365-387 / Pres_4::output
+ * src/pres_4.cxx:533-571 immediately followed by Timeloop::exec src/timeloop.cxx:358-411 for u,v,w).  Bit-identical to
+ * mhh_pres_output / mhh_pres_exec followed by mhh_rk_substep on (u,v,w); the caller runs mhh_rk_substep on the remaining
+ * fields with the same substep.  4th order (mhh_pres_exec_rk only): the call also performs
+ * Boundary::set_ghost_cells_w(Normal) on w (src/model.cxx:412) before the update, so the caller must not repeat it. */
 int mhh_pres_output_rk(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
                        int rkorder, int substep, double dt);
 int mhh_pres_exec_rk(mhh_ctx* ctx, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,

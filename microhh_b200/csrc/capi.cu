@@ -65,6 +65,7 @@ int pres4_set_values(Ctx*);
 int pres4_input(Ctx*, const double*, const double*, const double*, const double*, const double*, double*, double, double*);
 int pres4_solve_spectral(Ctx*, double*);
 int pres4_output(Ctx*, double*, double*, double*, double*);
+int pres4_output_rk(Ctx*, double*, double*, double*, double*, double*, double*, double*, int, int, double);
 int pres4_divergence_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
 
 static int read_max(Ctx* c, unsigned long long* slot, double* out)
@@ -586,13 +587,14 @@ int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, do
                      double dt_sub, int rkorder, int substep, double dt)
 {
     PRES_READY(c);
-    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
     if (c->npy != 1) { c->last_error = "mhh_pres_exec_rk is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
     int e;
     if ((e = mhh_pres_input(c, u, v, w, ut, vt, wt, dt_sub))) return e;
     if ((e = fft_forward_inplace(c, c->work_p))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
     if ((e = fft_backward_impl(c, c->work_p, p))) return e;
+    // 4th order: also leaves w's ghost rows in the Normal state of the not yet updated w (src/model.cxx:412)
+    if (c->order == 4) return pres4_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
     if ((e = pres2_output_stage(c, 0, ut, vt, wt, p))) return e;
     return pres2_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
 }

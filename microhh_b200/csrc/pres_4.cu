@@ -203,6 +203,47 @@ namespace
         }
     }
 
+    // Pres_4::output (src/pres_4.cxx:533-571) fused with the Runge-Kutta update of u,v,w (Timeloop::exec,
+    // src/timeloop.cxx:358-411), as pres2_out_rk_kernel: the corrected tendencies are consumed in registers, one thread per
+    // cell of the ghost-celled array, same operations in the same order as pres4_out_kernel followed by rk_kernel.
+    template<bool DIM3>
+    __global__ void __launch_bounds__(256)
+    pres4_out_rk_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
+                        double* __restrict__ u, double* __restrict__ v, double* __restrict__ w,
+                        const double* __restrict__ p, const double cB_dt, const double cA_next, const int zero_all,
+                        const GridD gd)
+    {
+        const int ijk = blockIdx.x * blockDim.x + threadIdx.x;
+        if (ijk >= gd.ncells) return;
+        const int i = ijk % gd.icells;
+        const int row = ijk / gd.icells;       // j + k*jcells
+        const int j = row % gd.jcells, k = row / gd.jcells;
+        const bool interior = i >= gd.istart && i < gd.iend && j >= gd.jstart && j < gd.jend
+                           && k >= gd.kstart && k < gd.kend;
+        if (interior)
+        {
+            const int jj = gd.icells, kk = gd.ijcells;
+            const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+            const double p0 = p[ijk];
+            const double tu0 = ut[ijk], tv0 = vt[ijk], tw0 = wt[ijk];
+            const double u0 = u[ijk], v0 = v[ijk], w0 = w[ijk];
+            const double tu = tu0 - G4(p[ijk - 2], p[ijk - 1], p0, p[ijk + 1]) * dxi;
+            double tv = tv0, tw = tw0;
+            if (DIM3) tv = tv0 - G4(p[ijk - 2 * jj], p[ijk - jj], p0, p[ijk + jj]) * dyi;
+            if (k > gd.kstart) tw = tw0 - G4(p[ijk - 2 * kk], p[ijk - kk], p0, p[ijk + kk]) * gd.dzhi4[k];
+            u[ijk] = u0 + cB_dt * tu;
+            v[ijk] = v0 + cB_dt * tv;
+            w[ijk] = w0 + cB_dt * tw;
+            ut[ijk] = zero_all ? 0. : tu * cA_next;
+            vt[ijk] = zero_all ? 0. : tv * cA_next;
+            wt[ijk] = zero_all ? 0. : tw * cA_next;
+        }
+        else if (zero_all)
+        {
+            ut[ijk] = 0.; vt[ijk] = 0.; wt[ijk] = 0.;
+        }
+    }
+
     // Pres_4::calc_divergence, src/pres_4.cxx:733-767 (the y term is always included)
     __global__ void __launch_bounds__(256, MHH_MINB)
     pres4_div_kernel(const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
@@ -345,6 +386,34 @@ int pres4_output(Ctx* c, double* ut, double* vt, double* wt, double* p)
         MHH_LAUNCH(c, "pres4_out_kernel", (pres4_out_kernel<false><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd)));
     else
         MHH_LAUNCH(c, "pres4_out_kernel", (pres4_out_kernel<true><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd)));
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
+void rk_coefs(int rkorder, int substep, double dt, double* cB_dt, double* cA_next, int* zero_all);
+int ghost_cells_w_exec(Ctx* c, double* w, int type);
+
+// ghost rows + halos of p, then w's ghost rows in their Normal state (the reference sets them between Pres::exec and
+// Timeloop::exec, src/model.cxx:412, from the not yet updated w), then the gradient fused with the RK substep of u,v,w
+int pres4_output_rk(Ctx* c, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
+                    int rkorder, int substep, double dt)
+{
+    if ((rkorder != 3 && rkorder != 4) || substep < 0 || substep >= (rkorder == 3 ? 3 : 5)) return MHH_ERR_ARG;
+    const GridD& gd = c->gd;
+    {
+        dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
+        MHH_LAUNCH(c, "pres4_ghost_kernel", pres4_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
+        MHH_LAUNCH_CHECK();
+    }
+    if (int e = cyclic_exec(c, p, 2)) return e;
+    if (int e = ghost_cells_w_exec(c, w, 0 /* MHH_BCW_NORMAL */)) return e;
+    double cB_dt, cA_next; int zero_all;
+    rk_coefs(rkorder, substep, dt, &cB_dt, &cA_next, &zero_all);
+    dim3 b(256), g((gd.ncells + 255) / 256);
+    if (gd.jtot == 1)
+        MHH_LAUNCH(c, "pres4_out_rk_kernel", (pres4_out_rk_kernel<false><<<g, b, 0, c->stream>>>(ut, vt, wt, u, v, w, p, cB_dt, cA_next, zero_all, gd)));
+    else
+        MHH_LAUNCH(c, "pres4_out_rk_kernel", (pres4_out_rk_kernel<true><<<g, b, 0, c->stream>>>(ut, vt, wt, u, v, w, p, cB_dt, cA_next, zero_all, gd)));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

@@ -450,12 +450,13 @@ class Pres:
         L.check(g.ctx, g.lib.mhh_pres_set_values(g.ctx), "mhh_pres_set_values")
 
     def exec(self, dt, stats=None, timeloop=None):
-        """Pres::exec.  With `timeloop` (order 2 only) the gradient stage is fused with Timeloop::exec for u,v,w
-        (mhh_pres_exec_rk): returns True, and the caller must run timeloop.exec(skip=("u", "v", "w"))."""
+        """Pres::exec.  With `timeloop` the gradient stage is fused with Timeloop::exec for u,v,w (mhh_pres_exec_rk):
+        returns True, and the caller must run timeloop.exec(skip=("u", "v", "w")) and must NOT call
+        set_ghost_cells_w(Normal) in between (4th order: the fused call has done it on the not yet updated w)."""
         if self.swpres == "0":
             return False
         g, f = self.grid, self.fields
-        if timeloop is not None and self.swpres == "2":
+        if timeloop is not None and self.swpres in ("2", "4") and g.npy == 1:
             L.check(g.ctx, g.lib.mhh_pres_exec_rk(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
                                                   L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
                                                   L.ptr(f.sd["p"].fld), C.c_double(dt), timeloop.rkorder, timeloop.substep,

@@ -79,7 +79,7 @@ class Model:
         self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
         # Thermo_dry + Advec_2 + Diff_smag2 tendencies in one pass per field (mhh_advec2_smag2_exec)
         self.fuse_tend = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo in ("0", "dry")
-        self.fuse_pres_rk = self.pres.swpres == "2"   # Pres_2::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
+        self.fuse_pres_rk = self.pres.swpres in ("2", "4")   # Pres::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
                                  dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True),
@@ -105,9 +105,10 @@ class Model:
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :389
             self.diff.exec()                               # :392
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
-        # :411 + :484 for u,v,w in one pass where the solver supports it (2nd order; set_ghost_cells_w is a 4th-order no-op there)
+        # :411 + :484 for u,v,w in one pass
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
-        b.set_ghost_cells_w(L.BCW_NORMAL)                  # :412
+        if not fused:
+            b.set_ghost_cells_w(L.BCW_NORMAL)              # :412 (inside the fused call otherwise)
         tl.exec(skip=("u", "v", "w") if fused else ())     # :484
         tl.step_time()                                     # :487
 

@@ -292,3 +292,40 @@ def test_fused_tendency_pass_equals_thermo_advec_diff(cuda_lib, sm, thermo, dims
     for k in res[0]:
         assert np.array_equal(res[0][k], res[1][k]), k
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("rkorder,substep", [(3, 0), (3, 2), (4, 4)])
+def test_fused_pressure_tail_order4(cuda_lib, rkorder, substep):
+    """4th order: mhh_pres_exec_rk = Pres_4::exec, Boundary::set_ghost_cells_w(Normal), Timeloop::exec(u,v,w) — bit-identical
+    to the three calls, including w's ghost rows (set from the not yet updated w, src/model.cxx:412)."""
+    from microhh_b200 import host as H
+    from microhh_b200 import lib as L
+    case = make_case(itot=24, jtot=16, ktot=12, alpha=1.3, order=4)
+    g, W = _worlds(case)
+    res = []
+    for fused in (False, True):
+        f = H.Fields(g, slist=[])
+        b = H.Boundary(g, f)
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+            b.boundary_cyclic.exec(f.mp[n].fld)
+        r = np.random.default_rng(11)
+        for n in "uvw":
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        f.mt["w"].fld[:g.kstart + 1] = 0.
+        f.mt["w"].fld[g.kend:] = 0.
+        pres = H.Pres.factory(g, f, "4")
+        pres.set_values()
+        tl = H.Timeloop(g, f, rkorder=rkorder, dt=0.73)
+        tl.substep = substep
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)
+        done = pres.exec(tl.get_sub_time_step(), timeloop=tl if fused else None)
+        assert done == fused
+        if not done:
+            b.set_ghost_cells_w(L.BCW_NORMAL)
+        tl.exec(skip=("u", "v", "w") if done else ())
+        res.append({n: f.ap[n].fld.cpu().numpy().copy() for n in f.ap} | {n + "t": f.at[n].fld.cpu().numpy().copy() for n in f.at}
+                   | {"p": f.sd["p"].fld.cpu().numpy().copy()})
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    g.close(); W.close()
