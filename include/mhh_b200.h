@@ -148,6 +148,31 @@ int mhh_thermo_dry_exec(mhh_ctx* ctx, double* wt, const double* th);
 /* Thermo_dry::get_thermo_field("N2") — calc_N2, src/thermo_dry.cxx:66-79 */
 int mhh_thermo_dry_N2(mhh_ctx* ctx, const double* th, double* N2);
 
+/* --- Buffer<TF> (sponge layer; include/buffer.h, src/buffer.cxx) — SURVEY 8(f) rank 3 --------------------- */
+/* Buffer::create, src/buffer.cxx:101-125: finds bufferkstart/bufferkstarth (first full/half level with z >= zstart),
+ * fails with "Buffer is too close to the model top" like the reference, and tabulates sigma*((z-zstart)/(zsize-zstart))^beta
+ * per level on the host (std::pow, :49). */
+int mhh_buffer_plan(mhh_ctx* ctx, double zstart, double sigma, double beta, int* bufferkstart, int* bufferkstarth);
+/* calc_buffer, src/buffer.cxx:37-58 (buffer_g, src/buffer.cu:36-60): at -= sigma(z)*(a - abuf[k]) above zstart.
+ * abuf: device profile (kcells) — bufferprofs[name] or fld_mean when swupdate; is_w selects the half-level table. */
+int mhh_buffer_exec(mhh_ctx* ctx, double* at, const double* a, const double* abuf, int is_w);
+
+/* --- Force<TF>::exec (include/force.h, src/force.cxx:586-720) ---------------------------------------------- */
+/* swlspres=dpdx: add_pressure_force(ut, -dpdx), src/force.cxx:46-60,603-611 */
+int mhh_force_pressure(mhh_ctx* ctx, double* ut, double fbody);
+/* swlspres=uflux: enforce_fixed_flux with the two calc_mean reductions, src/force.cxx:63-75,590-601 */
+int mhh_force_fixed_flux(mhh_ctx* ctx, double* ut, const double* u, double uflux, double utrans, double dt, double* fbody_out);
+/* swlspres=geo: calc_coriolis_2nd/_4th, src/force.cxx:78-144,613-634; ug, vg device profiles (kcells) */
+int mhh_force_coriolis(mhh_ctx* ctx, double* ut, double* vt, const double* u, const double* v,
+                       const double* ug, const double* vg, double fc, double utrans, double vtrans);
+/* swls=1: calc_large_scale_source, src/force.cxx:146-161 (sls: device profile) */
+int mhh_force_large_scale_source(mhh_ctx* ctx, double* st, const double* sls);
+/* swnudge=1: calc_nudging_tendency, src/force.cxx:163-183 (fldmean, ref, factor: device profiles) */
+int mhh_force_nudge(mhh_ctx* ctx, double* at, const double* fldmean, const double* ref, const double* factor);
+/* swwls: mode 0 = advec_wls_2nd_mean (s = mean profile), 1 = advec_wls_2nd_local, 2 = advec_wls_2nd_local_w
+ * (s = 3-D field), src/force.cxx:195-292 */
+int mhh_force_subsidence(mhh_ctx* ctx, int mode, double* st, const double* s, const double* wls);
+
 /* --- Pres<TF> (include/pres.h:48-58) --------------------------------------------------------------- */
 /* Pres_2/4::init + set_values — src/pres_2.cxx:107-153, src/pres_4.cxx:159-252. Uses ctx rhoref. */
 int mhh_pres_set_values(mhh_ctx* ctx);

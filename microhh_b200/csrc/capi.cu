@@ -54,6 +54,12 @@ int plane_sum(Ctx*, const double*, double*);
 int thermo_set_ref(Ctx*, const double*, const double*);
 int thermo_buoyancy_tend(Ctx*, double*, const double*);
 int thermo_n2(Ctx*, double*, const double*);
+// force.cu
+int buffer_plan(Ctx*, double, double, double);
+int buffer_exec(Ctx*, double*, const double*, const double*, int);
+int force_level_source(Ctx*, int, double*, double, const double*, const double*, const double*);
+int force_coriolis(Ctx*, double*, double*, const double*, const double*, const double*, const double*, double, double, double);
+int force_wls(Ctx*, int, double*, const double*, const double*);
 // pres_2.cu / pres_4.cu
 int pres2_set_values(Ctx*);
 int pres2_input(Ctx*, const double*, const double*, const double*, const double*, const double*, const double*, double, double*);
@@ -450,6 +456,40 @@ int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
 int mhh_thermo_set_ref(mhh_ctx* c, const double* thref, const double* threfh) { CTX_CHECK(c); return thermo_set_ref(c, thref, threfh); }
 int mhh_thermo_dry_exec(mhh_ctx* c, double* wt, const double* th) { CTX_CHECK(c); return thermo_buoyancy_tend(c, wt, th); }
 int mhh_thermo_dry_N2(mhh_ctx* c, const double* th, double* N2) { CTX_CHECK(c); return thermo_n2(c, N2, th); }
+
+// ---- Buffer / Force ----
+int mhh_buffer_plan(mhh_ctx* c, double zstart, double sigma, double beta, int* bufferkstart, int* bufferkstarth)
+{
+    CTX_CHECK(c);
+    if (int e = buffer_plan(c, zstart, sigma, beta)) return e;
+    if (bufferkstart) *bufferkstart = c->buffer_kstart;
+    if (bufferkstarth) *bufferkstarth = c->buffer_kstarth;
+    return MHH_OK;
+}
+int mhh_buffer_exec(mhh_ctx* c, double* at, const double* a, const double* abuf, int is_w)
+{ CTX_CHECK(c); if (!at || !a || !abuf) { c->last_error = "mhh_buffer_exec: null pointer"; return MHH_ERR_ARG; } return buffer_exec(c, at, a, abuf, is_w); }
+int mhh_force_pressure(mhh_ctx* c, double* ut, double fbody)
+{ CTX_CHECK(c); return force_level_source(c, 0, ut, fbody, nullptr, nullptr, nullptr); }
+int mhh_force_fixed_flux(mhh_ctx* c, double* ut, const double* u, double uflux, double utrans, double dt, double* fbody_out)
+{
+    CTX_CHECK(c);
+    // enforce_fixed_flux, src/force.cxx:63-75, with the two calc_mean calls of Force::exec :593-594
+    double u_mean, ut_mean;
+    if (int e = mhh_mean(c, u, &u_mean)) return e;
+    if (int e = mhh_mean(c, ut, &ut_mean)) return e;
+    const double fbody = (uflux - u_mean - utrans) / dt - ut_mean;
+    if (fbody_out) *fbody_out = fbody;
+    return force_level_source(c, 0, ut, fbody, nullptr, nullptr, nullptr);
+}
+int mhh_force_coriolis(mhh_ctx* c, double* ut, double* vt, const double* u, const double* v, const double* ug,
+                       const double* vg, double fc, double utrans, double vtrans)
+{ CTX_CHECK(c); return force_coriolis(c, ut, vt, u, v, ug, vg, fc, utrans, vtrans); }
+int mhh_force_large_scale_source(mhh_ctx* c, double* st, const double* sls)
+{ CTX_CHECK(c); return force_level_source(c, 1, st, 0., sls, nullptr, nullptr); }
+int mhh_force_nudge(mhh_ctx* c, double* at, const double* fldmean, const double* ref, const double* factor)
+{ CTX_CHECK(c); return force_level_source(c, 2, at, 0., fldmean, ref, factor); }
+int mhh_force_subsidence(mhh_ctx* c, int mode, double* st, const double* s, const double* wls)
+{ CTX_CHECK(c); return force_wls(c, mode, st, s, wls); }
 
 // ---------------------------------------------------------------- Pres
 int mhh_pres_set_values(mhh_ctx* c)

@@ -234,6 +234,7 @@ void ctx_free(Ctx* c)
     cudaFree(c->work_p); cudaFree(c->work_c); cudaFree(c->work_h);
     cudaFree(c->mlen0_d);
     cudaFree(c->thref_d);
+    cudaFree(c->buffer_sigma_d);
     fft_plan_destroy(&c->plan_i);
     fft_plan_destroy(&c->plan_j);
 }

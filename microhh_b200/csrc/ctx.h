@@ -66,6 +66,10 @@ struct Ctx
     // thermo_dry base state: thref (kcells) followed by threfh (kcells)
     double* thref_d = nullptr;
 
+    // Buffer (sponge layer): sigma(z[k]) (kcells) followed by sigma(zh[k]) (kcells); first levels inside the layer
+    double* buffer_sigma_d = nullptr;
+    int buffer_kstart = 0, buffer_kstarth = 0;
+
     // launch accounting / live per-kernel timing (bench.py: gpu_launches and roofline.achieved)
     unsigned long long launches = 0;
     bool prof_on = false;

@@ -102,6 +102,7 @@ class Field3d:
     def __init__(self, grid: Grid, name: str, visc: float = 0.0):
         self.name, self.visc = name, visc
         self.fld = grid.zeros()
+        self.fld_mean = torch.zeros(grid.kcells, dtype=torch.float64, device=self.fld.device)   # Field3d::fld_mean
         self.fld_bot, self.fld_top = grid.zeros2d(), grid.zeros2d()
         self.grad_bot, self.grad_top = grid.zeros2d(), grid.zeros2d()
         self.flux_bot, self.flux_top = grid.zeros2d(), grid.zeros2d()
@@ -121,6 +122,20 @@ class Fields:
         self.sd["p"] = Field3d(grid, "p")
         self.rhoref = np.ones(grid.kcells)
         self.rhorefh = np.ones(grid.kcells)
+        self.calc_mean_profs = False
+
+    def set_calc_mean_profs(self, sw):
+        self.calc_mean_profs = bool(sw)
+
+    def exec(self):
+        """Fields::exec, src/fields.cxx: xy-mean profile of every prognostic field into fld_mean (when a consumer asked)."""
+        if not self.calc_mean_profs:
+            return
+        g = self.grid
+        prof = np.zeros(g.kcells)
+        for fld in self.ap.values():
+            L.check(g.ctx, g.lib.mhh_mean_profile(g.ctx, L.ptr(fld.fld), prof.ctypes.data_as(C.c_void_p)), "mhh_mean_profile")
+            fld.fld_mean.copy_(torch.from_numpy(prof))
 
     def init_prognostic_field(self, name, visc):
         self.sp[name] = Field3d(self.grid, name, visc)
@@ -529,3 +544,124 @@ class Timeloop:
         L.check(g.ctx, g.lib.mhh_rk_substep(g.ctx, self.rkorder, self.substep, C.c_double(self.dt), len(names), a, at),
                 "mhh_rk_substep")
         self.substep = (self.substep + 1) % (3 if self.rkorder == 3 else 5)
+
+
+def _level_profile(grid, prof, name):
+    """ktot values -> device profile of kcells in the reference layout (std::rotate by kstart, src/buffer.cxx:139-141)."""
+    a = np.zeros(grid.kcells)
+    p = np.asarray(prof, dtype=np.float64)
+    if p.shape != (grid.ktot,):
+        raise L.MhhError(f"profile {name} must have ktot={grid.ktot} values")
+    a[grid.kstart:grid.kend] = p
+    return torch.from_numpy(a).to(grid.device)
+
+
+class Buffer:
+    """Buffer (include/buffer.h, src/buffer.cxx): damping towards a profile above zstart.  [buffer] swbuffer, swupdate,
+    zstart, sigma (default 2), beta (default 2); the profiles are the `init` profiles of the case input (ktot values)."""
+
+    def __init__(self, grid, fields, swbuffer=False, swupdate=False, zstart=None, sigma=2., beta=2., profs=None):
+        self.grid, self.fields = grid, fields
+        self.swbuffer, self.swupdate = bool(swbuffer), bool(swupdate)
+        if not self.swbuffer:
+            return
+        if zstart is None:
+            raise L.MhhError("[buffer] zstart is required when swbuffer=1")
+        self.zstart, self.sigma, self.beta = float(zstart), float(sigma), float(beta)
+        ks, ksh = C.c_int(), C.c_int()
+        L.check(grid.ctx, grid.lib.mhh_buffer_plan(grid.ctx, C.c_double(self.zstart), C.c_double(self.sigma),
+                                                   C.c_double(self.beta), C.byref(ks), C.byref(ksh)), "mhh_buffer_plan")
+        self.bufferkstart, self.bufferkstarth = ks.value, ksh.value
+        self.bufferprofs = {}
+        if self.swupdate:
+            fields.set_calc_mean_profs(True)
+        else:
+            profs = profs or {}
+            for name in fields.ap:      # w (and anything not given) relaxes to zero, src/buffer.cxx:94-96
+                self.bufferprofs[name] = (_level_profile(grid, profs[name], name) if name in profs
+                                          else torch.zeros(grid.kcells, dtype=torch.float64, device=grid.device))
+
+    def exec(self, stats=None):
+        if not self.swbuffer:
+            return
+        g, f = self.grid, self.fields
+        for name, fld in f.ap.items():
+            abuf = fld.fld_mean if self.swupdate else self.bufferprofs[name]
+            L.check(g.ctx, g.lib.mhh_buffer_exec(g.ctx, L.ptr(f.at[name].fld), L.ptr(fld.fld), L.ptr(abuf),
+                                                 1 if name == "w" else 0), "mhh_buffer_exec")
+
+
+class Force:
+    """Force (include/force.h, src/force.cxx:586-720): swlspres in {0, uflux, dpdx, geo}, swls, swwls in {0, mean, local}
+    (+ swwls_mom), swnudge.  Time-dependent profiles (Timedep) are out of scope: profiles are constant in time."""
+
+    def __init__(self, grid, fields, swlspres="0", uflux=0., dpdx=0., fc=-1., lat=0., swls="0", lslist=(), swwls="0",
+                 swwls_mom=False, swnudge="0", nudgelist=(), profs=None, utrans=0., vtrans=0.):
+        self.grid, self.fields = grid, fields
+        self.swlspres, self.swls, self.swwls, self.swnudge = str(swlspres), str(swls), str(swwls), str(swnudge)
+        if self.swwls == "1":
+            self.swwls = "local"                       # src/force.cxx:327-331
+        if self.swlspres not in ("0", "uflux", "dpdx", "geo"):
+            raise L.MhhError('Invalid option for "swlspres"')
+        if self.swls not in ("0", "1"):
+            raise L.MhhError('Invalid option for "swls"')
+        if self.swwls not in ("0", "mean", "local"):
+            raise L.MhhError('Invalid option for "swwls"')
+        if self.swnudge not in ("0", "1"):
+            raise L.MhhError('Invalid option for "swnduge"')
+        self.uflux, self.dpdx, self.utrans, self.vtrans = float(uflux), float(dpdx), float(utrans), float(vtrans)
+        self.swwls_mom = bool(swwls_mom)
+        profs = profs or {}
+        if self.swlspres == "geo":
+            self.fc = float(fc)
+            if self.fc < 0:                            # src/force.cxx:615-617 (Constants::e_rot = 7.2921e-5)
+                self.fc = 2. * 7.2921e-5 * np.sin(lat * np.pi / 180.)
+            self.ug, self.vg = _level_profile(grid, profs["u_geo"], "u_geo"), _level_profile(grid, profs["v_geo"], "v_geo")
+        self.lslist = list(lslist) if self.swls == "1" else []
+        for name in self.lslist:
+            if name not in fields.ap:
+                raise L.MhhError(f"field {name} in [force][lslist] is illegal")
+        self.lsprofs = {n: _level_profile(grid, profs[n + "_ls"], n + "_ls") for n in self.lslist}
+        if self.swwls != "0":
+            self.wls = _level_profile(grid, profs["w_ls"], "w_ls")
+            fields.set_calc_mean_profs(True)
+        self.nudgelist = list(nudgelist) if self.swnudge == "1" else []
+        if self.swnudge == "1":
+            for name in self.nudgelist:
+                if name not in fields.ap:
+                    raise L.MhhError(f"field {name} in [force][nudgelist] is illegal")
+            self.nudge_factor = _level_profile(grid, profs["nudgefac"], "nudgefac")
+            self.nudgeprofs = {}
+            for n in self.nudgelist:
+                p = np.asarray(profs[n + "_nudge"], dtype=np.float64)
+                p = p - (self.utrans if n == "u" else self.vtrans if n == "v" else 0.)
+                self.nudgeprofs[n] = _level_profile(grid, p, n + "_nudge")
+            fields.set_calc_mean_profs(True)
+
+    def exec(self, dt, thermo=None, stats=None):
+        g, f, lib = self.grid, self.fields, self.grid.lib
+        if self.swlspres == "uflux":
+            L.check(g.ctx, lib.mhh_force_fixed_flux(g.ctx, L.ptr(f.mt["u"].fld), L.ptr(f.mp["u"].fld), C.c_double(self.uflux),
+                                                    C.c_double(self.utrans), C.c_double(dt), None), "mhh_force_fixed_flux")
+        elif self.swlspres == "dpdx":
+            L.check(g.ctx, lib.mhh_force_pressure(g.ctx, L.ptr(f.mt["u"].fld), C.c_double(-1. * self.dpdx)), "mhh_force_pressure")
+        elif self.swlspres == "geo":
+            L.check(g.ctx, lib.mhh_force_coriolis(g.ctx, L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mp["u"].fld),
+                                                  L.ptr(f.mp["v"].fld), L.ptr(self.ug), L.ptr(self.vg), C.c_double(self.fc),
+                                                  C.c_double(self.utrans), C.c_double(self.vtrans)), "mhh_force_coriolis")
+        for name in self.lslist:
+            L.check(g.ctx, lib.mhh_force_large_scale_source(g.ctx, L.ptr(f.at[name].fld), L.ptr(self.lsprofs[name])),
+                    "mhh_force_large_scale_source")
+        if self.swwls != "0":
+            mean = self.swwls == "mean"
+            targets = (["u", "v"] if self.swwls_mom else []) + list(f.sp)
+            for name in targets:
+                s = f.ap[name].fld_mean if mean else f.ap[name].fld
+                L.check(g.ctx, lib.mhh_force_subsidence(g.ctx, 0 if mean else 1, L.ptr(f.at[name].fld), L.ptr(s), L.ptr(self.wls)),
+                        "mhh_force_subsidence")
+            if self.swwls_mom and not mean:
+                L.check(g.ctx, lib.mhh_force_subsidence(g.ctx, 2, L.ptr(f.mt["w"].fld), L.ptr(f.mp["w"].fld), L.ptr(self.wls)),
+                        "mhh_force_subsidence")
+        for name in self.nudgelist:
+            L.check(g.ctx, lib.mhh_force_nudge(g.ctx, L.ptr(f.at[name].fld), L.ptr(f.ap[name].fld_mean),
+                                               L.ptr(self.nudgeprofs[name]), L.ptr(self.nudge_factor)), "mhh_force_nudge")

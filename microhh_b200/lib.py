@@ -39,6 +39,8 @@ EXPORTS = [
     "mhh_diff2_exec", "mhh_diff4_exec", "mhh_diff_const_dnmul",
     "mhh_smag2_exec_viscosity", "mhh_smag2_exec_viscosity_dry", "mhh_smag2_exec", "mhh_advec2_smag2_exec", "mhh_smag2_strain2", "mhh_smag2_dnmul",
     "mhh_thermo_set_ref", "mhh_thermo_dry_exec", "mhh_thermo_dry_N2",
+    "mhh_buffer_plan", "mhh_buffer_exec", "mhh_force_pressure", "mhh_force_fixed_flux", "mhh_force_coriolis",
+    "mhh_force_large_scale_source", "mhh_force_nudge", "mhh_force_subsidence",
     "mhh_pres_set_values", "mhh_pres_exec", "mhh_pres_check_divergence", "mhh_pres_work", "mhh_pres_input",
     "mhh_fft_force_generic", "mhh_fft_forward", "mhh_fft_backward", "mhh_pres_solve_spectral", "mhh_pres_output", "mhh_pres_scatter",
     "mhh_pres_get_coefs", "mhh_pres_input_to", "mhh_fft_x", "mhh_fft_y", "mhh_transpose_copy", "mhh_pres_solve_spectral_ws",

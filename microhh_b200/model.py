@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 from . import lib as L
-from .host import Advec, Boundary, Diff, Fields, Grid, Pres, Timeloop
+from .host import Advec, Boundary, Buffer, Diff, Fields, Force, Grid, Pres, Timeloop
 
 
 class Thermo:
@@ -49,7 +49,7 @@ class Model:
     [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
     (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
 
-    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0):
+    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None):
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
@@ -84,6 +84,15 @@ class Model:
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
                                  dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True),
                                  starttime=ti.get("starttime", 0.), endtime=ti.get("endtime", 1e9))
+        # [buffer] / [force]; `profs` = the case's init profiles (ktot values each: u, v, th, u_geo, ...)
+        bu, fo = ini.get("buffer", {}), ini.get("force", {})
+        self.buffer = Buffer(self.grid, self.fields, swbuffer=bu.get("swbuffer", False), swupdate=bu.get("swupdate", False),
+                             zstart=bu.get("zstart"), sigma=bu.get("sigma", 2.), beta=bu.get("beta", 2.), profs=profs)
+        self.force = Force(self.grid, self.fields, swlspres=fo.get("swlspres", "0"), uflux=fo.get("uflux", 0.),
+                           dpdx=fo.get("dpdx", 0.), fc=fo.get("fc", -1.), lat=gi.get("lat", 0.), swls=fo.get("swls", "0"),
+                           lslist=fo.get("lslist", ()), swwls=fo.get("swwls", "0"), swwls_mom=fo.get("swwls_mom", False),
+                           swnudge=fo.get("swnudge", "0"), nudgelist=fo.get("nudgelist", ()), profs=profs,
+                           utrans=gi.get("utrans", 0.), vtrans=gi.get("vtrans", 0.))
         self.surface = surface or {}
         self.boundary.set_values()
         self.pres.set_values()
@@ -93,6 +102,7 @@ class Model:
         b, tl = self.boundary, self.timeloop
         b.set_prognostic_cyclic_bcs()                      # src/model.cxx:346
         b.set_ghost_cells()                                # :348
+        self.fields.exec()                                 # :351 (mean profiles, only when buffer/force asked for them)
         self.diff.exec_viscosity(self.thermo, surface=self.surface)   # :354
         if not tl.in_substep() and tl.adaptivestep:        # set_time_step, :357 -> :731-751
             tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
@@ -104,6 +114,8 @@ class Model:
             self.advec.exec()                              # :388
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :389
             self.diff.exec()                               # :392
+        self.buffer.exec()                                 # :395
+        self.force.exec(tl.get_sub_time_step(), self.thermo)   # :404
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
         # :411 + :484 for u,v,w in one pass
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)

@@ -17,7 +17,8 @@ class OracleLES:
     def __init__(self, itot, jtot, ktot, xsize, ysize, zsize, z, fields, *, swadvec="2", swdiff="smag2", order=2,
                  visc=1e-5, svisc=1e-5, cs=0.23, tPr=1. / 3., thref0=300., swthermo="dry", surface=None,
                  mbcbot="freeslip", mbctop="freeslip", sbc=None, rkorder=3, dt=1.0, dtmax=1e9, adaptivestep=True,
-                 cflmax=1.0, dnmax=0.4, rhoref=None, rhorefh=None, fluxlimit_list=(), endtime=None):
+                 cflmax=1.0, dnmax=0.4, rhoref=None, rhorefh=None, fluxlimit_list=(), endtime=None, buffer=None, force=None,
+                 profs=None):
         gc = None
         if swadvec == "2i5":
             gc = (3, 3, 2 if fluxlimit_list else 1)      # src/advec_2i5.cxx:42-45
@@ -61,6 +62,15 @@ class OracleLES:
         self.idtmax = int(self.ifactor * dtmax + 0.5)
         self.itime, self.time, self.iteration, self.substep = 0, 0., 0, 0
         self.zero2 = z2()
+        # Buffer / Force (src/buffer.cxx, src/force.cxx): dicts with the .ini keys; profs = init profiles (ktot values)
+        self.buffer, self.force = buffer or {}, force or {}
+        def lev(name):
+            p = np.zeros(W.kcells)
+            if profs and name in profs:
+                p[W.kstart:W.kend] = profs[name]
+            return p
+        self.bufferprofs = {n: lev(n) for n in self.names}
+        self.ug, self.vg = lev("u_geo"), lev("v_geo")
 
     def close(self):
         self.W.close()
@@ -137,6 +147,18 @@ class OracleLES:
             for n in self.scalars:
                 W.call("ref_diff4_c", at[n], a[n], self.svisc)
         sub_dt = lib().ref_rk_subdt(C.c_int(self.rkorder), C.c_double(self.dt), C.c_int(self.substep))
+        if self.buffer.get("swbuffer"):                 # Buffer::exec, src/model.cxx:395
+            b = self.buffer
+            for n in self.names:
+                W.call("ref_buffer", at[n], a[n], self.bufferprofs[n], float(b["zstart"]), float(b.get("sigma", 2.)),
+                       float(b.get("beta", 2.)), 1 if n == "w" else 0)
+        sw = self.force.get("swlspres", "0")           # Force::exec, src/model.cxx:404
+        if sw == "geo":
+            W.call("ref_force_coriolis", at["u"], at["v"], u, v, self.ug, self.vg, float(self.force["fc"]), 0., 0.)
+        elif sw == "uflux":
+            W.call("ref_force_fixed_flux", at["u"], u, float(self.force["uflux"]), 0., float(sub_dt))
+        elif sw == "dpdx":
+            W.call("ref_force_pressure", at["u"], -1. * float(self.force["dpdx"]))
         if W.order == 4:
             W.call("ref_ghost_cells_w", w, 1)
             W.call("ref_pres4_exec", self.p, u, v, w, at["u"], at["v"], at["w"], sub_dt)

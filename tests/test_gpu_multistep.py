@@ -27,12 +27,12 @@ def profiles(fields, ks, ke, js, je, is_, ie):
     return out
 
 
-def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None):
+def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None):
     import torch
     from microhh_b200.model import Model
     from oracle.les import OracleLES
     dev = torch.device("cuda:0")
-    m = Model(ini, z, device=dev)
+    m = Model(ini, z, device=dev, profs=profs)
     g, f = m.grid, m.fields
     up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     for n in "uvw":
@@ -56,7 +56,8 @@ def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None):
                   mbcbot=bi.get("mbcbot", "noslip"), mbctop=bi.get("mbctop", "noslip"), sbc=bi.get("sbc"),
                   rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1), dtmax=ti.get("dtmax", 1e9),
                   adaptivestep=ti.get("adaptivestep", True), cflmax=ai.get("cflmax", 1.0), dnmax=di.get("dnmax", 0.4),
-                  fluxlimit_list=ai.get("fluxlimit_list", ()), endtime=ti.get("endtime"), **(oracle_kw or {}))
+                  fluxlimit_list=ai.get("fluxlimit_list", ()), endtime=ti.get("endtime"), buffer=ini.get("buffer"),
+                  force=ini.get("force"), profs=profs, **(oracle_kw or {}))
     dts = []
     for _ in range(nsteps):
         m.step()
@@ -143,6 +144,23 @@ def test_les_100_steps_stats_profiles(cuda_lib, kind, tol, dt_ns):
     assert res["status"]["div"] <= max(10 * res["odiv"], 1e-12)
 
 
+def test_les_gabls1_with_buffer_and_geostrophic_forcing(cuda_lib):
+    """cases/gabls1 as shipped has swbuffer=1 and swlspres=geo (fc=1.39e-4, u_geo=8): 50 steps with the sponge layer and the
+    Coriolis/geostrophic term in the loop (Buffer::exec, Force::exec; src/model.cxx:395,404), same 1e-9 profile bar."""
+    ini, z, init, surface = les_case("gabls1_stable")
+    n = ini["grid"]["ktot"]
+    ini["buffer"] = dict(swbuffer=True, zstart=300., sigma=0.00223, beta=2.)
+    ini["force"] = dict(swlspres="geo", fc=1.39e-4)
+    th0 = 265. + 0.01 * np.clip(z - 100., 0., None)
+    profs = dict(u=np.full(n, 8.), v=np.zeros(n), th=th0, u_geo=np.full(n, 8.), v_geo=np.zeros(n))
+    res = run_both(ini, z, init, 50, surface=surface, profs=profs)
+    check_profiles(res, 1e-9, 100)
+    assert res["status"]["div"] <= max(10 * res["odiv"], 1e-12)
+    # the forcing terms were really active: v spins up through the Coriolis term
+    ks, ke, js, je, is_, ie = res["dims"]
+    assert np.abs(res["got"]["v"][ks:ke, js:je, is_:ie].mean(axis=(1, 2))).max() > 1e-4
+
+
 def test_dns_order4_steps(cuda_lib):
     """moser180-like channel DNS: advec_4, diff_4, pres_4 on a tanh-stretched grid, RK3, no-slip walls; RK4 as well."""
     itot, jtot, ktot = 32, 24, 32
@@ -158,9 +176,15 @@ def test_dns_order4_steps(cuda_lib):
                "advec": dict(swadvec="4", cflmax=1.0), "diff": dict(swdiff="4", dnmax=0.4), "pres": dict(swpres="4"),
                "boundary": dict(mbcbot="noslip", mbctop="noslip"), "fields": dict(visc=1e-3),
                "time": dict(rkorder=rk, dt=0.01, dtmax=0.1, adaptivestep=True)}
+        if rk == 3:
+            ini["force"] = dict(swlspres="uflux", uflux=0.0282)      # cases/moser180/moser180.ini: fixed mass flux
         res = run_both(ini, z, init, nsteps)
         check_profiles(res, 1e-9, 0)
         assert res["status"]["div"] <= max(10 * res["odiv"], 1e-12)
+        if rk == 3:     # enforce_fixed_flux holds the volume-mean u at uflux (checked here with 2nd-order dz: 1 % slack)
+            ks, ke, js, je, is_, ie = res["dims"]
+            dz = np.diff(np.concatenate([[0.], 0.5 * (z[1:] + z[:-1]), [2.]]))
+            assert abs((res["got"]["u"][ks:ke, js:je, is_:ie].mean(axis=(1, 2)) * dz).sum() / 2. - 0.0282) < 3e-4
 
 
 def test_les_2i5_limited_scalar_steps(cuda_lib):
