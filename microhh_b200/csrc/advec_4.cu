@@ -45,6 +45,24 @@ namespace
         const int sa = (COMP == 0) ? ii : (COMP == 1) ? jj : kk;     // staggering direction of a
         const double* __restrict__ mz = (COMP == 2) ? gd.dzhi4 : gd.dzi4;
 
+        // ---- z direction: every face product  F(l) = interp_sa(w)(l) * interp_z(a)(l)  (w: interp_z(w)(l)^2) is shared by
+        // the four levels l-2..l+1, so the march carries three of them and the a-column in registers: one new face per
+        // level (4+1 loads, 15 flops instead of 32 loads, 60 flops).  The first / last row swap the outermost
+        // interpolation for the biased one; those faces are used once (they leave the queue first / enter it last).
+        const int ij = i + j * jj;
+        auto face = [&](const int l, const double A) -> double
+        { return (COMP == 2) ? A * A : I4(w, ij + l * kk - 2 * sa, sa) * A; };
+        double qa = a[ij + (k0 - 1) * kk], qb = a[ij + k0 * kk], qc = a[ij + (k0 + 1) * kk], qd = a[ij + (k0 + 2) * kk];
+        double f0, f1, f2;
+        {
+            const double am2 = a[ij + (k0 - 2) * kk], am3 = a[ij + (k0 - 3) * kk];
+            const double A0 = (k0 == kfirst) ? bi0 * am2 + bi1 * qa + bi2 * qb + bi3 * qc
+                                             : ci0 * am3 + ci1 * am2 + ci2 * qa + ci3 * qb;
+            f0 = face(k0 - 1, A0);
+            f1 = face(k0, ci0 * am2 + ci1 * qa + ci2 * qb + ci3 * qc);
+            f2 = face(k0 + 1, ci0 * qa + ci1 * qb + ci2 * qc + ci3 * qd);
+        }
+
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * jj + k * kk;
@@ -83,19 +101,16 @@ namespace
                 }
             }
 
-            // ---- z direction: biased interpolation of `a` in the first / last row ----
-            const bool bot = (k == kfirst), top = (k == gd.kend - 1);
-            const double a0 = bot ? B4(a, ijk - 2 * kk, kk) : I4(a, ijk - 3 * kk, kk);
-            const double a1 = I4(a, ijk - 2 * kk, kk);
-            const double a2 = I4(a, ijk - kk, kk);
-            const double a3 = top ? T4(a, ijk - kk, kk) : I4(a, ijk, kk);
-            if (COMP == 2)
-                t -= G4(a0 * a0, a1 * a1, a2 * a2, a3 * a3) * mz[k];
-            else
-                t -= G4(I4(w, ijk - 2 * sa - kk, sa) * a0,
-                        I4(w, ijk - 2 * sa, sa) * a1,
-                        I4(w, ijk - 2 * sa + kk, sa) * a2,
-                        I4(w, ijk - 2 * sa + 2 * kk, sa) * a3) * mz[k];
+            // ---- z direction ----
+            {
+                const double qe = a[ijk + 3 * kk];
+                const double A3 = (k == gd.kend - 1) ? ti0 * qa + ti1 * qb + ti2 * qc + ti3 * qd
+                                                     : ci0 * qb + ci1 * qc + ci2 * qd + ci3 * qe;
+                const double f3 = face(k + 2, A3);
+                t -= G4(f0, f1, f2, f3) * mz[k];
+                f0 = f1; f1 = f2; f2 = f3;
+                qa = qb; qb = qc; qc = qd; qd = qe;
+            }
             at[ijk] = t;
         }
     }
@@ -162,13 +177,15 @@ namespace
     {
         const GridD& gd = c->gd;
         Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
-        MHH_LAUNCH(c, "advec4_u_kernel", (advec4_mom_kernel<0, DIM3><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, gd)));
-        MHH_LAUNCH_CHECK();
-        MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, gd)));
-        MHH_LAUNCH_CHECK();
         Launch3 lw = launch_interior(gd.imax, gd.jmax, (gd.kmax - 1 + KCHUNK - 1) / KCHUNK);
-        MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, gd)));
-        MHH_LAUNCH_CHECK();
+        {
+            MHH_LAUNCH(c, "advec4_u_kernel", (advec4_mom_kernel<0, DIM3><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, gd)));
+            MHH_LAUNCH_CHECK();
+            MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, gd)));
+            MHH_LAUNCH_CHECK();
+            MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, gd)));
+            MHH_LAUNCH_CHECK();
+        }
         for (int n = 0; n < nscalars; ++n)
         {
             MHH_LAUNCH(c, "advec4_s_kernel", (advec4_s_kernel<DIM3><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], u, v, w, gd)));

@@ -88,8 +88,7 @@ struct Launch3
 inline Launch3 launch_interior(int ni, int nj, int nk)
 {
     Launch3 l;
-    static const int bx_env = []{ const char* e = getenv("MHH_BLOCK_X"); return e ? atoi(e) : 0; }();
-    const int bx = bx_env > 0 ? bx_env : (ni >= 128 ? 128 : (ni >= 64 ? 64 : 32));
+    const int bx = ni >= 128 ? 128 : (ni >= 64 ? 64 : 32);
     const int by = 256 / bx;
     l.block = dim3(bx, by, 1);
     l.grid = dim3((ni + bx - 1) / bx, (nj + by - 1) / by, nk);
