@@ -28,11 +28,16 @@ namespace
     // Momentum component COMP (0 = u, 1 = v, 2 = w): src/advec_4.cxx:89 (advec_u), :189 (advec_v), :289 (advec_w).
     // `a` is the advected component itself; the advecting velocity in direction d is interpolated along the
     // staggering direction of `a` (ci over 4 points starting 2 below), exactly as in the reference.
-    template<int COMP, bool DIM3>
+    // DIFF: Diff_4's diff_c (src/diff_4.cxx:42-107) of the same component appended as three more `+=` terms — every value
+    // it reads (a at i-3..i+3, j-3..j+3 and the k-3..k+3 column) is already in flight for the advection stencil, so the
+    // fused pass costs no extra global traffic.  u and v only: diff_w reads Normal-type w ghost rows, advec the
+    // Conservation-type ones (src/model.cxx:387-392).
+    template<int COMP, bool DIM3, bool DIFF>
     __global__ void __launch_bounds__(256, 2)
     advec4_mom_kernel(double* __restrict__ at, const double* __restrict__ u, const double* __restrict__ v,
-                      const double* __restrict__ w, const GridD gd)
+                      const double* __restrict__ w, const double visc, const GridD gd)
     {
+        static_assert(!(DIFF && COMP == 2), "diff_w needs the other w ghost-row type");
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
         const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
         if (i >= gd.iend || j >= gd.jend) return;
@@ -54,8 +59,10 @@ namespace
         { return (COMP == 2) ? A * A : I4(w, ij + l * kk - 2 * sa, sa) * A; };
         double qa = a[ij + (k0 - 1) * kk], qb = a[ij + k0 * kk], qc = a[ij + (k0 + 1) * kk], qd = a[ij + (k0 + 2) * kk];
         double f0, f1, f2;
+        double qm2 = 0., qm3 = 0.;      // a[k-2], a[k-3]: only the diffusion stencil keeps them
         {
             const double am2 = a[ij + (k0 - 2) * kk], am3 = a[ij + (k0 - 3) * kk];
+            if (DIFF) { qm2 = am2; qm3 = am3; }
             const double A0 = (k0 == kfirst) ? bi0 * am2 + bi1 * qa + bi2 * qb + bi3 * qc
                                              : ci0 * am3 + ci1 * am2 + ci2 * qa + ci3 * qb;
             f0 = face(k0 - 1, A0);
@@ -109,6 +116,23 @@ namespace
                 const double f3 = face(k + 2, A3);
                 t -= G4(f0, f1, f2, f3) * mz[k];
                 f0 = f1; f1 = f2; f2 = f3;
+                if (DIFF)
+                {
+                    const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
+                    t += visc * (cdg3 * a[ijk - 3] + cdg2 * a[ijk - 2] + cdg1 * a[ijk - 1] + cdg0 * qb
+                                 + cdg1 * a[ijk + 1] + cdg2 * a[ijk + 2] + cdg3 * a[ijk + 3]) * dxidxi;
+                    if (DIM3)
+                        t += visc * (cdg3 * a[ijk - 3 * jj] + cdg2 * a[ijk - 2 * jj] + cdg1 * a[ijk - jj] + cdg0 * qb
+                                     + cdg1 * a[ijk + jj] + cdg2 * a[ijk + 2 * jj] + cdg3 * a[ijk + 3 * jj]) * dyidyi;
+                    const double d0 = (k == kfirst) ? (bg0 * qm2 + bg1 * qa + bg2 * qb + bg3 * qc) : G4(qm3, qm2, qa, qb);
+                    const double d3 = (k == gd.kend - 1) ? (tg0 * qa + tg1 * qb + tg2 * qc + tg3 * qd) : G4(qb, qc, qd, qe);
+                    t += visc * ( cg0 * d0 * gd.dzhi4[k - 1]
+                                + cg1 * G4(qm2, qa, qb, qc) * gd.dzhi4[k]
+                                + cg2 * G4(qa, qb, qc, qd) * gd.dzhi4[k + 1]
+                                + cg3 * d3 * gd.dzhi4[k + 2] )
+                         * gd.dzi4[k];
+                    qm3 = qm2; qm2 = qa;
+                }
                 qa = qb; qb = qc; qc = qd; qd = qe;
             }
             at[ijk] = t;
@@ -171,21 +195,30 @@ namespace
         block_max_bits(m, out);
     }
 
+    // fuse_diff: u and v get Diff_4::diff_c in the same pass; the caller then runs diff_w and the scalars' diff_c.
     template<bool DIM3>
     int exec_t(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
-               int nscalars, const double* const* s, double* const* st)
+               int nscalars, const double* const* s, double* const* st, bool fuse_diff, double visc)
     {
         const GridD& gd = c->gd;
         Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
         Launch3 lw = launch_interior(gd.imax, gd.jmax, (gd.kmax - 1 + KCHUNK - 1) / KCHUNK);
+        if (fuse_diff)
         {
-            MHH_LAUNCH(c, "advec4_u_kernel", (advec4_mom_kernel<0, DIM3><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, gd)));
+            MHH_LAUNCH(c, "advec4_diff4_u_kernel", (advec4_mom_kernel<0, DIM3, true><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, visc, gd)));
             MHH_LAUNCH_CHECK();
-            MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, gd)));
-            MHH_LAUNCH_CHECK();
-            MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, gd)));
+            MHH_LAUNCH(c, "advec4_diff4_v_kernel", (advec4_mom_kernel<1, DIM3, true><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, visc, gd)));
             MHH_LAUNCH_CHECK();
         }
+        else
+        {
+            MHH_LAUNCH(c, "advec4_u_kernel", (advec4_mom_kernel<0, DIM3, false><<<l.grid, l.block, 0, c->stream>>>(ut, u, v, w, 0., gd)));
+            MHH_LAUNCH_CHECK();
+            MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3, false><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, 0., gd)));
+            MHH_LAUNCH_CHECK();
+        }
+        MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3, false><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, 0., gd)));
+        MHH_LAUNCH_CHECK();
         for (int n = 0; n < nscalars; ++n)
         {
             MHH_LAUNCH(c, "advec4_s_kernel", (advec4_s_kernel<DIM3><<<l.grid, l.block, 0, c->stream>>>(st[n], s[n], u, v, w, gd)));
@@ -195,8 +228,7 @@ namespace
     }
 }  // namespace
 
-int advec4_exec(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
-                int nscalars, const double* const* s, double* const* st)
+static int advec4_check(Ctx* c)
 {
     const GridD& gd = c->gd;
     if (gd.igc < 3 || gd.kgc < 3 || (gd.jtot > 1 && gd.jgc < 3) || gd.kmax < 4)
@@ -204,8 +236,24 @@ int advec4_exec(Ctx* c, const double* u, const double* v, const double* w, doubl
         c->last_error = "advec_4 needs 3 ghost cells in every direction (swspatialorder=4) and ktot >= 4";
         return MHH_ERR_ARG;
     }
-    return gd.jtot == 1 ? exec_t<false>(c, u, v, w, ut, vt, wt, nscalars, s, st)
-                        : exec_t<true>(c, u, v, w, ut, vt, wt, nscalars, s, st);
+    return MHH_OK;
+}
+
+int advec4_exec(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+                int nscalars, const double* const* s, double* const* st)
+{
+    if (int e = advec4_check(c)) return e;
+    return c->gd.jtot == 1 ? exec_t<false>(c, u, v, w, ut, vt, wt, nscalars, s, st, false, 0.)
+                           : exec_t<true>(c, u, v, w, ut, vt, wt, nscalars, s, st, false, 0.);
+}
+
+// Advec_4::exec with Diff_4's diff_c of u and v in the same pass (the rest of Diff_4::exec follows in capi.cu).
+int advec4_exec_diff_uv(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
+                        int nscalars, const double* const* s, double* const* st, double visc)
+{
+    if (int e = advec4_check(c)) return e;
+    return c->gd.jtot == 1 ? exec_t<false>(c, u, v, w, ut, vt, wt, nscalars, s, st, true, visc)
+                           : exec_t<true>(c, u, v, w, ut, vt, wt, nscalars, s, st, true, visc);
 }
 
 int advec4_cfl_bits(Ctx* c, const double* u, const double* v, const double* w, unsigned long long* slot)

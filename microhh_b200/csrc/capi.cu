@@ -24,6 +24,8 @@ int advec2i5_exec(Ctx*, const double*, const double*, const double*, double*, do
 int advec2i5_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
 int advec4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*);
 int advec4_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
+int advec4_exec_diff_uv(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*, double);
+int diff4_exec_w_scalars(Ctx*, const double*, double*, double, int, const double* const*, double* const*, const double*);
 // diff_2.cu / diff_4.cu / diff_smag2.cu
 int diff2_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
 int diff4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
@@ -379,6 +381,17 @@ int mhh_diff2_exec(mhh_ctx* c, const double* u, const double* v, const double* w
 int mhh_diff4_exec(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
                    double visc, int ns, const double* const* s, double* const* st, const double* svisc)
 { CTX_CHECK(c); return diff4_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
+
+int mhh_advec4_diff4_exec(mhh_ctx* c, const double* u, const double* v, double* w, double* ut, double* vt, double* wt,
+                          double visc, int ns, const double* const* s, double* const* st, const double* svisc)
+{
+    CTX_CHECK(c);
+    if (c->order != 4) { c->last_error = "mhh_advec4_diff4_exec needs swspatialorder=4"; return MHH_ERR_ARG; }
+    // src/model.cxx:387-392: [w ghost rows Conservation-type on entry] advec->exec; set_ghost_cells_w(Normal); diff->exec
+    if (int e = advec4_exec_diff_uv(c, u, v, w, ut, vt, wt, ns, s, st, visc)) return e;
+    if (int e = ghost_cells_w_exec(c, w, 0)) return e;
+    return diff4_exec_w_scalars(c, w, wt, visc, ns, s, st, svisc);
+}
 
 int mhh_diff_const_dnmul(mhh_ctx* c, double viscmax, double* out)
 {

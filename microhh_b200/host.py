@@ -426,6 +426,22 @@ class Diff:
             L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
             C.c_double(f.visc), L.ptr(th_buoy), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_advec2_smag2_exec")
 
+    def exec_with_advec4(self):
+        """Advec_4::exec + set_ghost_cells_w(Normal) + Diff_4::exec (src/model.cxx:387-392) through mhh_advec4_diff4_exec:
+        diff_c of u and v rides in the advection pass; bit-identical to the separate calls.  w must hold Conservation-type
+        ghost rows on entry."""
+        g, f = self.grid, self.fields
+        if self.swdiff != "4" or g.order != 4:
+            raise L.MhhError("the fused 4th-order tendency pass needs swdiff=4 on the 4th-order grid")
+        names = list(f.sp)
+        s = L.ptr_array([f.sp[n].fld for n in names])
+        st = L.ptr_array([f.st[n].fld for n in names])
+        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        u, v, w = (L.ptr(f.mp[n].fld) for n in "uvw")
+        ut, vt, wt = (L.ptr(f.mt[n].fld) for n in "uvw")
+        L.check(g.ctx, g.lib.mhh_advec4_diff4_exec(g.ctx, u, v, w, ut, vt, wt, C.c_double(f.visc), len(names), s, st, svisc),
+                "mhh_advec4_diff4_exec")
+
     def _dnmul(self):
         if self.swdiff != "smag2":
             return self.dnmul

@@ -79,6 +79,7 @@ class Model:
         self.thermo = Thermo(self.grid, self.fields, swthermo, thref0=th.get("thref0", 300.))
         # Thermo_dry + Advec_2 + Diff_smag2 tendencies in one pass per field (mhh_advec2_smag2_exec)
         self.fuse_tend = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo in ("0", "dry")
+        self.fuse_tend4 = self.advec.swadvec == "4" and self.diff.swdiff == "4"     # mhh_advec4_diff4_exec
         self.fuse_pres_rk = self.pres.swpres in ("2", "4")   # Pres::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
@@ -108,6 +109,10 @@ class Model:
             tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
             self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
+        elif self.fuse_tend4:   # :387-392 in one call, diff_c of u and v inside the advection pass
+            self.thermo.exec()                             # :366
+            b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387
+            self.diff.exec_with_advec4()                   # :388-392
         else:
             self.thermo.exec()                             # :366
             b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387

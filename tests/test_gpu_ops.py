@@ -329,3 +329,42 @@ def test_fused_pressure_tail_order4(cuda_lib, rkorder, substep):
     for k in res[0]:
         assert np.array_equal(res[0][k], res[1][k]), k
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("dims", [dict(itot=24, jtot=16, ktot=12), dict(itot=20, jtot=9, ktot=37), dict(itot=16, jtot=1, ktot=8)],
+                         ids=["even", "ragged_2chunks", "2d"])
+@pytest.mark.parametrize("nscal", [0, 1])
+def test_fused_advec4_diff4_equals_separate_calls(cuda_lib, dims, nscal):
+    """mhh_advec4_diff4_exec = Advec_4::exec, set_ghost_cells_w(Normal), Diff_4::exec (src/model.cxx:387-392): bit-identical
+    tendencies and w ghost rows, on a stretched grid, with and without a scalar, over more than one k-chunk."""
+    from microhh_b200 import host as H
+    from microhh_b200 import lib as L
+    case = make_case(alpha=1.3, order=4, nscalars=nscal, **dims)
+    g, W = _worlds(case)
+    res = []
+    for fused in (False, True):
+        f = H.Fields(g, slist=["s"] if nscal else [], visc=1e-2, svisc=2e-2)
+        b = H.Boundary(g, f)
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+        if nscal:
+            f.sp["s"].fld.copy_(_up(g, case["s"][0]))
+        b.set_prognostic_cyclic_bcs()
+        b.set_ghost_cells()
+        r = np.random.default_rng(12)
+        for n in f.at:
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        advec = H.Advec.factory(g, f, "4")
+        diff = H.Diff.factory(g, f, b, "4")
+        b.set_ghost_cells_w(L.BCW_CONSERVATION)
+        if fused:
+            diff.exec_with_advec4()
+        else:
+            advec.exec()
+            b.set_ghost_cells_w(L.BCW_NORMAL)
+            diff.exec()
+        res.append({n + "t": f.at[n].fld.cpu().numpy().copy() for n in f.at} | {"w": f.mp["w"].fld.cpu().numpy().copy()})
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    assert np.abs(res[0]["ut"]).max() > 1e-2
+    g.close(); W.close()
