@@ -92,9 +92,10 @@ int mhh_diff2_exec(mhh_ctx* ctx, const double* u, const double* v, const double*
 int mhh_diff4_exec(mhh_ctx* ctx, const double* u, const double* v, const double* w,
                    double* ut, double* vt, double* wt, double visc,
                    int nscalars, const double* const* s, double* const* st, const double* svisc);
-/* Advec_4::exec, Boundary::set_ghost_cells_w(Normal_type) and Diff_4::exec (src/model.cxx:387-392) in one call: diff_c of u
- * and v rides in the advection pass of the same component (no extra global traffic), then the w ghost rows are switched
- * and diff_w / the scalars' diff_c follow.  w must hold Conservation-type ghost rows on entry (as for Advec::exec) and
+/* Advec_4::exec, Boundary::set_ghost_cells_w(Normal_type) and Diff_4::exec (src/model.cxx:387-392) in one call: diff_c / diff_w
+ * of u, v, w rides in the advection pass of the same component (no extra global traffic; the Normal-type w ghost values
+ * diff_w needs are evaluated in the kernel), then the w ghost rows are switched and the scalars' diff_c follows.
+ * w must hold Conservation-type ghost rows on entry (as for Advec::exec) and
  * holds Normal-type ones on return.  Bit-identical to the three separate calls. */
 int mhh_advec4_diff4_exec(mhh_ctx* ctx, const double* u, const double* v, double* w, double* ut, double* vt, double* wt,
                           double visc, int nscalars, const double* const* s, double* const* st, const double* svisc);

@@ -30,14 +30,16 @@ namespace
     // staggering direction of `a` (ci over 4 points starting 2 below), exactly as in the reference.
     // DIFF: Diff_4's diff_c (src/diff_4.cxx:42-107) of the same component appended as three more `+=` terms — every value
     // it reads (a at i-3..i+3, j-3..j+3 and the k-3..k+3 column) is already in flight for the advection stencil, so the
-    // fused pass costs no extra global traffic.  u and v only: diff_w reads Normal-type w ghost rows, advec the
-    // Conservation-type ones (src/model.cxx:387-392).
+    // fused pass costs no extra global traffic.  For w, diff_w (src/diff_4.cxx:109-174) reads Normal-type ghost rows while
+    // the advection reads the Conservation-type ones (src/model.cxx:387-392): the two Normal-type values a column needs
+    // (rows kstart-1 and kend+1, src/boundary.cxx:838-870) are evaluated in the kernel and substituted where the diffusion
+    // stencil touches those rows.
     template<int COMP, bool DIM3, bool DIFF>
     __global__ void __launch_bounds__(256, 2)
     advec4_mom_kernel(double* __restrict__ at, const double* __restrict__ u, const double* __restrict__ v,
                       const double* __restrict__ w, const double visc, const GridD gd)
     {
-        static_assert(!(DIFF && COMP == 2), "diff_w needs the other w ghost-row type");
+
         const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
         const int j = blockIdx.y * blockDim.y + threadIdx.y + gd.jstart;
         if (i >= gd.iend || j >= gd.jend) return;
@@ -60,6 +62,13 @@ namespace
         double qa = a[ij + (k0 - 1) * kk], qb = a[ij + k0 * kk], qc = a[ij + (k0 + 1) * kk], qd = a[ij + (k0 + 2) * kk];
         double f0, f1, f2;
         double qm2 = 0., qm3 = 0.;      // a[k-2], a[k-3]: only the diffusion stencil keeps them
+        double gbot = 0., gtop = 0.;    // Normal-type w ghost values of this column (COMP == 2 && DIFF)
+        if (COMP == 2 && DIFF)
+        {
+            const int b = ij + gd.kstart * kk, tp = ij + gd.kend * kk;
+            if (k0 <= gd.kstart + 2) gbot = -6. * w[b + kk] + 4. * w[b + 2 * kk] - w[b + 3 * kk];
+            if (k1 >= gd.kend - 2)   gtop = -6. * w[tp - kk] + 4. * w[tp - 2 * kk] - w[tp - 3 * kk];
+        }
         {
             const double am2 = a[ij + (k0 - 2) * kk], am3 = a[ij + (k0 - 3) * kk];
             if (DIFF) { qm2 = am2; qm3 = am3; }
@@ -124,13 +133,22 @@ namespace
                     if (DIM3)
                         t += visc * (cdg3 * a[ijk - 3 * jj] + cdg2 * a[ijk - 2 * jj] + cdg1 * a[ijk - jj] + cdg0 * qb
                                      + cdg1 * a[ijk + jj] + cdg2 * a[ijk + 2 * jj] + cdg3 * a[ijk + 3 * jj]) * dyidyi;
-                    const double d0 = (k == kfirst) ? (bg0 * qm2 + bg1 * qa + bg2 * qb + bg3 * qc) : G4(qm3, qm2, qa, qb);
-                    const double d3 = (k == gd.kend - 1) ? (tg0 * qa + tg1 * qb + tg2 * qc + tg3 * qd) : G4(qb, qc, qd, qe);
-                    t += visc * ( cg0 * d0 * gd.dzhi4[k - 1]
-                                + cg1 * G4(qm2, qa, qb, qc) * gd.dzhi4[k]
-                                + cg2 * G4(qa, qb, qc, qd) * gd.dzhi4[k + 1]
-                                + cg3 * d3 * gd.dzhi4[k + 2] )
-                         * gd.dzi4[k];
+                    // rows of the column as the diffusion sees them (w: Normal-type ghost rows)
+                    const bool isw = (COMP == 2);
+                    const double e3 = (isw && k == gd.kstart + 2) ? gbot : qm3;
+                    const double e2 = (isw && k == gd.kstart + 1) ? gbot : qm2;
+                    const double ed = (isw && k == gd.kend - 1) ? gtop : qd;
+                    const double ee = (isw && k == gd.kend - 2) ? gtop : qe;
+                    const double* __restrict__ min_ = isw ? gd.dzi4 : gd.dzhi4;     // inner / outer metric, diff_w / diff_c
+                    const double* __restrict__ mout = isw ? gd.dzhi4 : gd.dzi4;
+                    const int ms = isw ? -1 : 0;
+                    const double d0 = (k == kfirst) ? (bg0 * e2 + bg1 * qa + bg2 * qb + bg3 * qc) : G4(e3, e2, qa, qb);
+                    const double d3 = (k == gd.kend - 1) ? (tg0 * qa + tg1 * qb + tg2 * qc + tg3 * ed) : G4(qb, qc, ed, ee);
+                    t += visc * ( cg0 * d0 * min_[k - 1 + ms]
+                                + cg1 * G4(e2, qa, qb, qc) * min_[k + ms]
+                                + cg2 * G4(qa, qb, qc, ed) * min_[k + 1 + ms]
+                                + cg3 * d3 * min_[k + 2 + ms] )
+                         * mout[k];
                     qm3 = qm2; qm2 = qa;
                 }
                 qa = qb; qb = qc; qc = qd; qd = qe;
@@ -195,7 +213,7 @@ namespace
         block_max_bits(m, out);
     }
 
-    // fuse_diff: u and v get Diff_4::diff_c in the same pass; the caller then runs diff_w and the scalars' diff_c.
+    // fuse_diff: u, v, w get Diff_4::diff_c / diff_w in the same pass; the caller then runs the scalars' diff_c.
     template<bool DIM3>
     int exec_t(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
                int nscalars, const double* const* s, double* const* st, bool fuse_diff, double visc)
@@ -217,7 +235,8 @@ namespace
             MHH_LAUNCH(c, "advec4_v_kernel", (advec4_mom_kernel<1, DIM3, false><<<l.grid, l.block, 0, c->stream>>>(vt, u, v, w, 0., gd)));
             MHH_LAUNCH_CHECK();
         }
-        MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3, false><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, 0., gd)));
+        if (fuse_diff) MHH_LAUNCH(c, "advec4_diff4_w_kernel", (advec4_mom_kernel<2, DIM3, true><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, visc, gd)));
+        else           MHH_LAUNCH(c, "advec4_w_kernel", (advec4_mom_kernel<2, DIM3, false><<<lw.grid, lw.block, 0, c->stream>>>(wt, u, v, w, 0., gd)));
         MHH_LAUNCH_CHECK();
         for (int n = 0; n < nscalars; ++n)
         {
@@ -247,7 +266,7 @@ int advec4_exec(Ctx* c, const double* u, const double* v, const double* w, doubl
                            : exec_t<true>(c, u, v, w, ut, vt, wt, nscalars, s, st, false, 0.);
 }
 
-// Advec_4::exec with Diff_4's diff_c of u and v in the same pass (the rest of Diff_4::exec follows in capi.cu).
+// Advec_4::exec with Diff_4's diff_c / diff_w of u, v, w in the same pass (the scalars' diff_c follows in capi.cu).
 int advec4_exec_diff_uv(Ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
                         int nscalars, const double* const* s, double* const* st, double visc)
 {

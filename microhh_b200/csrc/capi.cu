@@ -25,7 +25,7 @@ int advec2i5_cfl_bits(Ctx*, const double*, const double*, const double*, unsigne
 int advec4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*);
 int advec4_cfl_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
 int advec4_exec_diff_uv(Ctx*, const double*, const double*, const double*, double*, double*, double*, int, const double* const*, double* const*, double);
-int diff4_exec_w_scalars(Ctx*, const double*, double*, double, int, const double* const*, double* const*, const double*);
+int diff4_exec_scalars(Ctx*, int, const double* const*, double* const*, const double*);
 // diff_2.cu / diff_4.cu / diff_smag2.cu
 int diff2_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
 int diff4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
@@ -390,7 +390,7 @@ int mhh_advec4_diff4_exec(mhh_ctx* c, const double* u, const double* v, double* 
     // src/model.cxx:387-392: [w ghost rows Conservation-type on entry] advec->exec; set_ghost_cells_w(Normal); diff->exec
     if (int e = advec4_exec_diff_uv(c, u, v, w, ut, vt, wt, ns, s, st, visc)) return e;
     if (int e = ghost_cells_w_exec(c, w, 0)) return e;
-    return diff4_exec_w_scalars(c, w, wt, visc, ns, s, st, svisc);
+    return diff4_exec_scalars(c, ns, s, st, svisc);
 }
 
 int mhh_diff_const_dnmul(mhh_ctx* c, double viscmax, double* out)

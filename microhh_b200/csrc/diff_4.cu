@@ -102,12 +102,10 @@ int diff4_exec(Ctx* c, const double* u, const double* v, const double* w, double
     return MHH_OK;
 }
 
-// The part of Diff_4::exec that mhh_advec4_diff4_exec does not fuse into the advection pass: w and the scalars.
-int diff4_exec_w_scalars(Ctx* c, const double* w, double* wt, double visc, int nscalars, const double* const* s,
-                         double* const* st, const double* svisc)
+// The part of Diff_4::exec that mhh_advec4_diff4_exec does not fuse into the advection pass: the scalars.
+int diff4_exec_scalars(Ctx* c, int nscalars, const double* const* s, double* const* st, const double* svisc)
 {
     int e;
-    if ((e = launch<true>(c, wt, w, visc))) return e;
     for (int n = 0; n < nscalars; ++n)
         if ((e = launch<false>(c, st[n], s[n], svisc[n]))) return e;
     return MHH_OK;

@@ -428,7 +428,7 @@ class Diff:
 
     def exec_with_advec4(self):
         """Advec_4::exec + set_ghost_cells_w(Normal) + Diff_4::exec (src/model.cxx:387-392) through mhh_advec4_diff4_exec:
-        diff_c of u and v rides in the advection pass; bit-identical to the separate calls.  w must hold Conservation-type
+        diff_c / diff_w of u, v, w rides in the advection pass; bit-identical to the separate calls.  w must hold Conservation-type
         ghost rows on entry."""
         g, f = self.grid, self.fields
         if self.swdiff != "4" or g.order != 4:

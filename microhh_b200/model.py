@@ -109,7 +109,7 @@ class Model:
             tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
             self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
-        elif self.fuse_tend4:   # :387-392 in one call, diff_c of u and v inside the advection pass
+        elif self.fuse_tend4:   # :387-392 in one call, the momentum diffusion inside the advection passes
             self.thermo.exec()                             # :366
             b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387
             self.diff.exec_with_advec4()                   # :388-392
