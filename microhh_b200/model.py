@@ -129,6 +129,47 @@ class Model:
         tl.exec(skip=("u", "v", "w") if fused else ())     # :484
         tl.step_time()                                     # :487
 
+    # ---- the reference's restart files (src/model.cxx:257-262,470-478; formats in microhh_b200.io) ----
+    def _gridshape(self):
+        g = self.grid
+        return dict(itot=g.itot, jtot=g.jtot, ktot=g.ktot, igc=g.igc, jgc=g.jgc, kgc=g.kgc)
+
+    def save(self, directory=".", iotime=None):
+        """Fields::save + Timeloop::save: <name>.<iotime:07d> for every prognostic field (u, v with the Galilean offset
+        added back, src/fields.cxx) and time.<iotime:07d>."""
+        from . import io as IO
+        tl = self.timeloop
+        iotime = int(tl.time) if iotime is None else iotime
+        for name, fld in self.fields.ap.items():
+            off = self.force.utrans if name == "u" else self.force.vtrans if name == "v" else 0.
+            IO.save_field3d(fld.fld.cpu().numpy(), self._gridshape(), name, iotime, offset=off, directory=directory)
+        IO.save_time(iotime, tl.itime, tl.idt, tl.iteration, directory=directory)
+
+    def load(self, directory=".", iotime=0):
+        """Fields::load + Timeloop::load (the files `microhh init` or a previous run wrote)."""
+        import torch
+        from . import io as IO
+        tl = self.timeloop
+        for name, fld in self.fields.ap.items():
+            off = self.force.utrans if name == "u" else self.force.vtrans if name == "v" else 0.
+            a = IO.load_field3d(self._gridshape(), name, iotime, offset=off, directory=directory)
+            fld.fld.copy_(torch.from_numpy(a))
+        tl.itime, tl.idt, tl.iteration = IO.load_time(iotime, directory=directory)
+        tl.time, tl.dt = tl.itime / tl.ifactor, tl.idt / tl.ifactor
+
+    @classmethod
+    def from_case(cls, ini_path, directory=None, device=None, surface=None, profs=None, iotime=0):
+        """`microhh run <case>` start-up: read <case>.ini, grid.0000000 and the restart files of `iotime`."""
+        import os
+        from . import io as IO
+        directory = os.path.dirname(os.path.abspath(ini_path)) if directory is None else directory
+        ini = IO.model_ini(IO.Input(ini_path))
+        gi = ini["grid"]
+        z = IO.load_grid(gi["itot"], gi["jtot"], gi["ktot"], directory=directory)["z"]
+        m = cls(ini, z, device=device, surface=surface, profs=profs)
+        m.load(directory=directory, iotime=iotime)
+        return m
+
     def step(self):
         """One full time step = 3 (RK3) or 5 (RK4) substeps."""
         for _ in range(3 if self.timeloop.rkorder == 3 else 5):

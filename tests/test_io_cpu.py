@@ -1,0 +1,125 @@
+"""CPU tests of the file formats either side of the path: the .ini reader's semantics and error
+texts (src/input.cxx), the raw binary grid/field/time layouts of the serial build (byte-exact), and the .out row format
+checked against the C library's own printf (the reference uses std::fprintf, src/model.cxx:827)."""
+import ctypes
+import os
+import struct
+
+import numpy as np
+import pytest
+
+from microhh_b200 import io as IO
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def test_ini_reader_semantics():
+    inp = IO.Input(os.path.join(HERE, "golden", "gabls1_like.ini"))
+    assert inp.get_item(int, "grid", "ktot") == 32                       # trailing comment stripped
+    assert inp.get_item(float, "boundary", "sbot", "th") == 264.5         # sub-item wins
+    assert inp.get_item(float, "boundary", "sbot", "qt") == 265.          # falls back to the plain item
+    assert inp.get_item(float, "boundary", "stop", "th") == 0.01
+    assert inp.get_item(bool, "time", "adaptivestep", "", False) is True
+    assert inp.get_item(bool, "buffer", "swbuffer") is True
+    assert inp.get_item(str, "advec", "swadvec", "", "4") == "2"
+    assert inp.get_item(float, "grid", "utrans", "", 0.) == 0.            # default
+    assert inp.get_list(str, "fields", "slist", "", []) == []
+    with pytest.raises(IO.InputError, match='Block "nope" does not exist'):
+        inp.get_item(int, "nope", "x")
+    with pytest.raises(IO.InputError, match='Item "x" in group "grid" does not exist'):
+        inp.get_item(int, "grid", "x")
+    with pytest.raises(IO.InputError, match=r"\[grid\]\[xsize\] = 400. is illegal."):
+        inp.get_item(int, "grid", "xsize", "", 3)                         # present but of the wrong type
+    with pytest.raises(IO.InputError, match="Item does not match type"):
+        inp.get_item(bool, "grid", "itot")
+    unused = inp.unused_items()
+    assert "[stats][swstats]" in unused and "[fields][rndamp][th]" in unused and "[grid][ktot]" not in unused
+
+
+def test_ini_reader_errors_and_lists():
+    with pytest.raises(IO.InputError, match="No block name found"):
+        IO.Input(text="a=1\n")
+    with pytest.raises(IO.InputError, match='Line "a=b=c" is illegal'):
+        IO.Input(text="[x]\na=b=c\n")
+    with pytest.raises(IO.InputError, match='Line "hello" is illegal'):
+        IO.Input(text="[x]\nhello\n")
+    with pytest.raises(IO.InputError, match="cannot be opened"):
+        IO.Input("/nonexistent/file.ini")
+    inp = IO.Input(text="[fields]\nslist = s1, s2 ,s3\nvals=1,2.5,3e2\n[t]\nflags=1,false,TRUE\n")
+    assert inp.get_list(str, "fields", "slist") == ["s1", "s2", "s3"]
+    assert inp.get_list(float, "fields", "vals") == [1., 2.5, 300.]
+    assert inp.get_list(bool, "t", "flags") == [True, False, True]
+    assert inp.get_list(int, "t", "absent", "", [7]) == [7]
+    with pytest.raises(IO.InputError):
+        inp.get_list(int, "fields", "vals")
+
+
+def test_model_ini_from_case_file():
+    ini = IO.model_ini(IO.Input(os.path.join(HERE, "golden", "gabls1_like.ini")))
+    assert ini["grid"]["swspatialorder"] == "2" and ini["grid"]["itot"] == 32 and ini["grid"]["lat"] == 73.
+    assert ini["advec"] == dict(swadvec="2", cflmax=1.0, fluxlimit_list=())
+    assert ini["diff"]["swdiff"] == "smag2" and ini["diff"]["dnmax"] == 0.3 and ini["diff"]["cs"] == 0.23
+    assert ini["pres"]["swpres"] == "2"                                   # defaults to swspatialorder
+    assert ini["thermo"] == dict(swthermo="dry", thref0=263.5)
+    assert ini["boundary"]["sbc"]["th"] == dict(sbcbot="dirichlet", sbctop="neumann", sbot=264.5, stop=0.01)
+    assert ini["boundary"]["swboundary"] == "surface" and ini["boundary"]["z0m"] == 0.1
+    assert ini["buffer"] == dict(swbuffer=True, swupdate=False, zstart=300., sigma=0.00223, beta=2.)
+    assert ini["force"]["swlspres"] == "geo" and ini["force"]["fc"] == 1.39e-4
+    assert ini["time"]["rkorder"] == 3 and ini["time"]["dtmax"] == 60. and ini["time"]["adaptivestep"] is True
+    bad = IO.Input(text="[grid]\nitot=4\njtot=4\nktot=4\nxsize=1\nysize=1\nzsize=1\nswspatialorder=3\n")
+    with pytest.raises(IO.InputError, match="swspatialorder"):
+        IO.model_ini(bad)
+
+
+def test_binary_layouts(tmp_path):
+    d = str(tmp_path)
+    itot, jtot, ktot, gc = 6, 4, 3, (2, 1, 3)
+    gs = dict(itot=itot, jtot=jtot, ktot=ktot, igc=gc[0], jgc=gc[1], kgc=gc[2])
+    rng = np.random.default_rng(0)
+    fld = rng.uniform(-1, 1, (ktot + 2 * gc[2], jtot + 2 * gc[1], itot + 2 * gc[0]))
+    IO.save_field3d(fld, gs, "u", 3600, offset=0.5, directory=d)
+    raw = np.fromfile(os.path.join(d, "u.0003600"), dtype="<f8")
+    assert raw.size == itot * jtot * ktot
+    # i fastest, then j, then k; ghost cells dropped; offset added (src/field3d_io.cxx:686-704)
+    assert raw[1] == fld[gc[2], gc[1], gc[0] + 1] + 0.5
+    assert raw[itot] == fld[gc[2], gc[1] + 1, gc[0]] + 0.5
+    assert raw[itot * jtot] == fld[gc[2] + 1, gc[1], gc[0]] + 0.5
+    back = IO.load_field3d(gs, "u", 3600, offset=0.5, directory=d)
+    inner = (slice(gc[2], gc[2] + ktot), slice(gc[1], gc[1] + jtot), slice(gc[0], gc[0] + itot))
+    assert np.allclose(back[inner], fld[inner], rtol=0, atol=1e-15) and back[0].max() == 0.
+    with pytest.raises(FileExistsError):                                  # fopen(..., "wbx")
+        IO.save_field3d(fld, gs, "u", 3600, directory=d)
+    with pytest.raises(RuntimeError):
+        IO.load_field3d(gs, "v", 0, directory=d)
+
+    x = (np.arange(itot) + 0.5); xh = np.arange(itot) * 1.; y = np.arange(jtot) + 0.5; yh = np.arange(jtot) * 1.
+    z = np.array([0.1, 0.4, 0.9]); zh = np.array([0., 0.25, 0.65])
+    IO.save_grid(x, xh, y, yh, z, zh, directory=d)
+    assert os.path.getsize(os.path.join(d, "grid.0000000")) == 8 * 2 * (itot + jtot + ktot)
+    g = IO.load_grid(itot, jtot, ktot, directory=d)
+    assert np.array_equal(g["z"], z) and np.array_equal(g["xh"], xh) and np.array_equal(g["yh"], yh)
+    with pytest.raises(RuntimeError, match="Error in grid"):
+        IO.load_grid(itot + 1, jtot, ktot, directory=d)
+
+    IO.save_time(3600, 3600 * 10**9, 6 * 10**9, 1234, directory=d)
+    b = open(os.path.join(d, "time.0003600"), "rb").read()
+    assert len(b) == 20 and struct.unpack("<Q", b[:8])[0] == 3600 * 10**9 and struct.unpack("<i", b[16:])[0] == 1234
+    assert IO.load_time(3600, directory=d) == (3600 * 10**9, 6 * 10**9, 1234)
+
+
+def test_out_row_matches_c_printf(tmp_path):
+    libc = ctypes.CDLL(None)
+    vals = (120, 1234.56789, 0.0123, 6.0, 0.98765, 0.01234, 3.2e-15, 7.99998, 32.2384)
+    buf = ctypes.create_string_buffer(512)
+    libc.snprintf(buf, 512, IO.OutWriter.ROW.encode(), ctypes.c_int(vals[0]), *[ctypes.c_double(v) for v in vals[1:]])
+    assert IO.OutWriter.format_row(*vals) == buf.value.decode()
+    w = IO.OutWriter("case", directory=str(tmp_path))
+    st = dict(iter=vals[0], time=vals[1], dt=vals[3], cfl=vals[4], dn=vals[5], div=vals[6], mom=vals[7], tke=vals[8], mass=0.)
+    w.write(st, cputime=vals[2])
+    with pytest.raises(RuntimeError, match="non-finite"):
+        w.write(dict(st, cfl=float("nan")))
+    w.close()
+    lines = open(os.path.join(str(tmp_path), "case.out")).read().splitlines()
+    assert lines[0].split() == ["ITER", "TIME", "CPUDT", "DT", "CFL", "DNUM", "DIV", "MOM", "TKE"]
+    rows = IO.read_out(os.path.join(str(tmp_path), "case.out"))
+    assert rows[0]["iter"] == 120 and abs(rows[0]["tke"] - 32.2384) < 1e-7
