@@ -155,6 +155,34 @@ int mhh_thermo_dry_exec(mhh_ctx* ctx, double* wt, const double* th);
 /* Thermo_dry::get_thermo_field("N2") — calc_N2, src/thermo_dry.cxx:66-79 */
 int mhh_thermo_dry_N2(mhh_ctx* ctx, const double* th, double* N2);
 
+/* --- Boundary_surface<TF> (Monin-Obukhov surface layer; include/boundary_surface.h, src/boundary_surface.cxx) —
+ * SURVEY 8(f) rank 4.  swconstantz0=true (lookup solver), no Charnock; bc codes as MHH_BC_*. --------------------------- */
+/* Boundary_surface::init_solver -> prepare_lut (include/boundary_surface_kernels.h:78-138), built on the host */
+int mhh_surface_init_solver(mhh_ctx* ctx, int mbcbot, int thermobc, double z0m, double z0h);
+/* copies the table out (2 x 10000 floats: zL_sl, f_sl) — for tests and restart checks */
+int mhh_surface_get_lut(mhh_ctx* ctx, float* zL_sl_host, float* f_sl_host);
+typedef struct mhh_surface_args
+{
+    int mbcbot;              /* MHH_BC_DIRICHLET (noslip) or MHH_BC_USTAR */
+    int thermo;              /* 0: thermo.get_switch() == "0" (stability_neutral); 1: dry (needs mhh_thermo_set_ref) */
+    int thermobc;            /* bottom bc of th: MHH_BC_DIRICHLET or MHH_BC_FLUX */
+    const double *u, *v;     /* 3-D */
+    double *ubot, *vbot, *ufluxbot, *vfluxbot, *ugradbot, *vgradbot;      /* Field3d planes of u, v */
+    const double* th;        /* 3-D (NULL when thermo == 0) */
+    double *thbot, *thgradbot, *thfluxbot;                                /* Field3d planes of th */
+    double *ustar, *obuk;    /* Boundary_surface::ustar, obuk (ijcells; persist between calls) */
+    int* nobuk;              /* Boundary_surface::nobuk (ijcells ints; the lookup resumes where it ended) */
+    const double *z0m, *z0h; /* ijcells */
+    double* dutot;           /* ijcells scratch (the reference borrows a tmp field) */
+    double *dudz, *dvdz, *dbdz;   /* dudz_mo, dvdz_mo, dbdz_mo: the bottom-row inputs of mhh_smag2_exec_viscosity */
+} mhh_surface_args;
+/* Boundary_surface::exec, src/boundary_surface.cxx:827-981: calc_dutot, stability / stability_neutral, surfm, surfs(th),
+ * calc_duvdz_mo, calc_dbdz_mo with the cyclic fills in between. */
+int mhh_boundary_surface_exec(mhh_ctx* ctx, const mhh_surface_args* args);
+/* surfs for a further scalar, src/boundary_surface.cxx:294-343,935-946 */
+int mhh_surface_scalar(mhh_ctx* ctx, int bcbot, const double* var, double* varbot, double* vargradbot, double* varfluxbot,
+                       const double* ustar, const double* obuk, const double* z0h);
+
 /* --- Buffer<TF> (sponge layer; include/buffer.h, src/buffer.cxx) — SURVEY 8(f) rank 3 --------------------- */
 /* Buffer::create, src/buffer.cxx:101-125: finds bufferkstart/bufferkstarth (first full/half level with z >= zstart),
  * fails with "Buffer is too close to the model top" like the reference, and tabulates sigma*((z-zstart)/(zsize-zstart))^beta

@@ -62,6 +62,22 @@ int buffer_exec(Ctx*, double*, const double*, const double*, int);
 int force_level_source(Ctx*, int, double*, double, const double*, const double*, const double*);
 int force_coriolis(Ctx*, double*, double*, const double*, const double*, const double*, const double*, double, double, double);
 int force_wls(Ctx*, int, double*, const double*, const double*);
+// surface.cu
+struct SurfaceArgs
+{
+    int mbcbot, thermo, thermobc;
+    const double *u, *v;
+    double *ubot, *vbot, *ufluxbot, *vfluxbot, *ugradbot, *vgradbot;
+    const double* th;
+    double *thbot, *thgradbot, *thfluxbot;
+    double *ustar, *obuk;
+    int* nobuk;
+    const double *z0m, *z0h;
+    double *dutot, *dudz, *dvdz, *dbdz;
+};
+int surface_lut(Ctx*, int, int, double, double);
+int surface_exec(Ctx*, const SurfaceArgs&);
+int surface_scalar(Ctx*, int, const double*, double*, double*, double*, const double*, const double*, const double*);
 // pres_2.cu / pres_4.cu
 int pres2_set_values(Ctx*);
 int pres2_input(Ctx*, const double*, const double*, const double*, const double*, const double*, const double*, double, double*);
@@ -469,6 +485,32 @@ int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
 int mhh_thermo_set_ref(mhh_ctx* c, const double* thref, const double* threfh) { CTX_CHECK(c); return thermo_set_ref(c, thref, threfh); }
 int mhh_thermo_dry_exec(mhh_ctx* c, double* wt, const double* th) { CTX_CHECK(c); return thermo_buoyancy_tend(c, wt, th); }
 int mhh_thermo_dry_N2(mhh_ctx* c, const double* th, double* N2) { CTX_CHECK(c); return thermo_n2(c, N2, th); }
+
+// ---- Boundary_surface ----
+int mhh_surface_init_solver(mhh_ctx* c, int mbcbot, int thermobc, double z0m, double z0h)
+{ CTX_CHECK(c); return surface_lut(c, mbcbot, thermobc, z0m, z0h); }
+int mhh_surface_get_lut(mhh_ctx* c, float* zL, float* f)
+{
+    CTX_CHECK(c);
+    if (c->surf_lut_host.empty()) { c->last_error = "surface solver not prepared (mhh_surface_init_solver)"; return MHH_ERR_STATE; }
+    const size_t n = c->surf_lut_host.size() / 2;
+    std::memcpy(zL, c->surf_lut_host.data(), n * sizeof(float));
+    std::memcpy(f, c->surf_lut_host.data() + n, n * sizeof(float));
+    return MHH_OK;
+}
+int mhh_boundary_surface_exec(mhh_ctx* c, const mhh_surface_args* a)
+{
+    CTX_CHECK(c);
+    if (!a || !a->u || !a->v || !a->ustar || !a->obuk || !a->dutot || !a->z0m || (a->thermo && (!a->th || !a->nobuk)))
+    { c->last_error = "mhh_boundary_surface_exec: null pointer"; return MHH_ERR_ARG; }
+    SurfaceArgs s{a->mbcbot, a->thermo, a->thermobc, a->u, a->v, a->ubot, a->vbot, a->ufluxbot, a->vfluxbot, a->ugradbot,
+                  a->vgradbot, a->th, a->thbot, a->thgradbot, a->thfluxbot, a->ustar, a->obuk, a->nobuk, a->z0m, a->z0h,
+                  a->dutot, a->dudz, a->dvdz, a->dbdz};
+    return surface_exec(c, s);
+}
+int mhh_surface_scalar(mhh_ctx* c, int bcbot, const double* var, double* varbot, double* vargradbot, double* varfluxbot,
+                       const double* ustar, const double* obuk, const double* z0h)
+{ CTX_CHECK(c); return surface_scalar(c, bcbot, var, varbot, vargradbot, varfluxbot, ustar, obuk, z0h); }
 
 // ---- Buffer / Force ----
 int mhh_buffer_plan(mhh_ctx* c, double zstart, double sigma, double beta, int* bufferkstart, int* bufferkstarth)

@@ -235,6 +235,7 @@ void ctx_free(Ctx* c)
     cudaFree(c->mlen0_d);
     cudaFree(c->thref_d);
     cudaFree(c->buffer_sigma_d);
+    cudaFree(c->surf_lut_d);
     fft_plan_destroy(&c->plan_i);
     fft_plan_destroy(&c->plan_j);
 }

@@ -65,6 +65,11 @@ struct Ctx
 
     // thermo_dry base state: thref (kcells) followed by threfh (kcells)
     double* thref_d = nullptr;
+    double thref_ks = 0., threfh_ks = 0.;    // thref[kstart], threfh[kstart] (surface buoyancy, src/thermo_dry.cxx:129-160)
+
+    // Boundary_surface: z/L lookup table of the surface solver (zL_sl | f_sl, nzL_lut floats each)
+    float* surf_lut_d = nullptr;
+    std::vector<float> surf_lut_host;
 
     // Buffer (sponge layer): sigma(z[k]) (kcells) followed by sigma(zh[k]) (kcells); first levels inside the layer
     double* buffer_sigma_d = nullptr;

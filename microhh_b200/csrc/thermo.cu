@@ -60,6 +60,7 @@ int thermo_set_ref(Ctx* c, const double* thref, const double* threfh)
         h[k] = thref[k]; h[kcells + k] = threfh[k];
         h[2 * kcells + k] = kGrav / thref[k]; h[3 * kcells + k] = kGrav / threfh[k];
     }
+    c->thref_ks = thref[c->gd.kstart]; c->threfh_ks = threfh[c->gd.kstart];
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     MHH_CUDA_CHECK(cudaMemcpy(c->thref_d, h.data(), sizeof(double) * 4 * kcells, cudaMemcpyHostToDevice));
     return MHH_OK;

@@ -681,3 +681,86 @@ class Force:
         for name in self.nudgelist:
             L.check(g.ctx, lib.mhh_force_nudge(g.ctx, L.ptr(f.at[name].fld), L.ptr(f.ap[name].fld_mean),
                                                L.ptr(self.nudgeprofs[name]), L.ptr(self.nudge_factor)), "mhh_force_nudge")
+
+
+class SurfaceArgs(C.Structure):
+    """mhh_surface_args, include/mhh_b200.h"""
+    _fields_ = ([("mbcbot", C.c_int), ("thermo", C.c_int), ("thermobc", C.c_int)]
+                + [(n, C.c_void_p) for n in ("u", "v", "ubot", "vbot", "ufluxbot", "vfluxbot", "ugradbot", "vgradbot", "th",
+                                             "thbot", "thgradbot", "thfluxbot", "ustar", "obuk", "nobuk", "z0m", "z0h",
+                                             "dutot", "dudz", "dvdz", "dbdz")])
+
+
+class Boundary_surface(Boundary):
+    """Boundary_surface (include/boundary_surface.h, src/boundary_surface.cxx): swboundary=surface, the Monin-Obukhov
+    surface layer.  swconstantz0=true (homogeneous z0m/z0h, lookup solver); mbcbot in {noslip, ustar}."""
+
+    def __init__(self, grid, fields, z0m=0.1, z0h=0.1, ustar=None, **kw):
+        mbcbot = kw.pop("mbcbot", "noslip")
+        super().__init__(grid, fields, mbcbot=mbcbot, swboundary="surface", **kw)
+        if self.mbcbot == L.BC_NEUMANN:
+            raise L.MhhError("Neumann bc is not supported in surface model")           # src/boundary_surface.cxx:483-487
+        for bc in self.sbc.values():
+            if bc.bcbot == L.BC_NEUMANN:
+                raise L.MhhError("Fixed Gradient bc is not supported in surface model")
+            if bc.bcbot == L.BC_DIRICHLET and self.mbcbot == L.BC_USTAR:
+                raise L.MhhError("Fixed Ustar bc in combination with Dirichlet bc for scalars is not supported")
+        if self.mbcbot == L.BC_USTAR and ustar is None:
+            raise L.MhhError('Item "ustar" in group "boundary" does not exist')
+        self.ustarin = ustar
+        self.thermobc = self.sbc["th"].bcbot if "th" in self.sbc else L.BC_FLUX          # :514-521
+        self.z0m_hom, self.z0h_hom = float(z0m), float(z0h)
+        z2 = lambda v=0.: torch.full(grid.shape2d, float(v), dtype=torch.float64, device=grid.device)
+        # init_surface, src/boundary_surface.cxx:536-572
+        self.obuk, self.ustar = z2(1e-9), z2(1e-2)
+        self.dudz_mo, self.dvdz_mo, self.dbdz_mo = z2(), z2(), z2()
+        self.z0m, self.z0h = z2(z0m), z2(z0h)
+        self.nobuk = torch.zeros(grid.shape2d, dtype=torch.int32, device=grid.device)
+        self._dutot = z2()
+
+    def set_values(self):
+        """Boundary_surface::set_values, src/boundary_surface.cxx:749-779"""
+        super().set_values()
+        f = self.fields
+        for name, val in (("u", self.ubot), ("v", self.vbot)):
+            fld = f.mp[name]
+            self._set_bc(fld.fld_bot, fld.grad_bot, fld.flux_bot, L.BC_DIRICHLET, val, f.visc, 0.)
+        if self.mbcbot == L.BC_USTAR:                      # set_ustar, :782-810
+            for name, val in (("u", self.ubot), ("v", self.vbot)):
+                fld = f.mp[name]
+                self._set_bc(fld.fld_bot, fld.grad_bot, fld.flux_bot, self.mbcbot, val, f.visc, 0.)
+            self.ustar.fill_(max(0.0001, self.ustarin))
+        g = self.grid
+        L.check(g.ctx, g.lib.mhh_surface_init_solver(g.ctx, self.mbcbot, self.thermobc, C.c_double(self.z0m_hom),
+                                                     C.c_double(self.z0h_hom)), "mhh_surface_init_solver")
+
+    def planes(self):
+        """The bottom-row inputs of Diff_smag2 (exec_viscosity: z0m, dudz, dvdz, dbdz)."""
+        return dict(z0m=self.z0m, dudz=self.dudz_mo, dvdz=self.dvdz_mo, dbdz=self.dbdz_mo)
+
+    def exec(self, thermo=None):
+        """Boundary_surface::exec, src/boundary_surface.cxx:827-981."""
+        g, f = self.grid, self.fields
+        dry = thermo is not None and thermo.get_switch() != "0"
+        u, v = f.mp["u"], f.mp["v"]
+        a = SurfaceArgs()
+        a.mbcbot, a.thermo, a.thermobc = self.mbcbot, 1 if dry else 0, self.thermobc
+        p = lambda t: t.data_ptr() if t is not None else None
+        a.u, a.v = p(u.fld), p(v.fld)
+        a.ubot, a.vbot, a.ufluxbot, a.vfluxbot = p(u.fld_bot), p(v.fld_bot), p(u.flux_bot), p(v.flux_bot)
+        a.ugradbot, a.vgradbot = p(u.grad_bot), p(v.grad_bot)
+        if dry:
+            th = f.sp["th"]
+            a.th, a.thbot, a.thgradbot, a.thfluxbot = p(th.fld), p(th.fld_bot), p(th.grad_bot), p(th.flux_bot)
+        a.ustar, a.obuk, a.nobuk, a.z0m, a.z0h = p(self.ustar), p(self.obuk), p(self.nobuk), p(self.z0m), p(self.z0h)
+        a.dutot, a.dudz, a.dvdz, a.dbdz = p(self._dutot), p(self.dudz_mo), p(self.dvdz_mo), p(self.dbdz_mo)
+        L.check(g.ctx, g.lib.mhh_boundary_surface_exec(g.ctx, C.byref(a)), "mhh_boundary_surface_exec")
+        for name, fld in f.sp.items():
+            if dry and name == "th":
+                continue
+            L.check(g.ctx, g.lib.mhh_surface_scalar(g.ctx, self.sbc[name].bcbot, L.ptr(fld.fld), L.ptr(fld.fld_bot), L.ptr(fld.grad_bot),
+                                                    L.ptr(fld.flux_bot), L.ptr(self.ustar), L.ptr(self.obuk), L.ptr(self.z0h)),
+                    "mhh_surface_scalar")
+
+    def update_slave_bcs(self):
+        pass        # the surface model computes the planes (src/boundary_surface.cxx:984-988)

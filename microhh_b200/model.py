@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 from . import lib as L
-from .host import Advec, Boundary, Buffer, Diff, Fields, Force, Grid, Pres, Timeloop
+from .host import Advec, Boundary, Boundary_surface, Buffer, Diff, Fields, Force, Grid, Pres, Timeloop
 
 
 class Thermo:
@@ -49,7 +49,7 @@ class Model:
     [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
     (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
 
-    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None):
+    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None, mo=False):
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
@@ -66,9 +66,16 @@ class Model:
             slist = ["th"] + slist
         self.fields = Fields(self.grid, slist=slist, visc=fi.get("visc", 0.), svisc=fi.get("svisc", 0.))
         bi = ini.get("boundary", {})
-        self.boundary = Boundary(self.grid, self.fields, mbcbot=bi.get("mbcbot", "noslip"), mbctop=bi.get("mbctop", "noslip"),
-                                 ubot=bi.get("ubot", 0.), utop=bi.get("utop", 0.), vbot=bi.get("vbot", 0.), vtop=bi.get("vtop", 0.),
-                                 sbc=bi.get("sbc"), swboundary=bi.get("swboundary", "default"))
+        bkw = dict(mbcbot=bi.get("mbcbot", "noslip"), mbctop=bi.get("mbctop", "noslip"), ubot=bi.get("ubot", 0.), utop=bi.get("utop", 0.),
+                   vbot=bi.get("vbot", 0.), vtop=bi.get("vtop", 0.), sbc=bi.get("sbc"))
+        # swboundary=surface: with mo=True the Monin-Obukhov surface layer runs on the device every substep
+        # (Boundary_surface); otherwise the caller prescribes the surface planes (z0m, dudz, dvdz, dbdz, fluxes) via `surface`.
+        self.mo = bool(mo) and bi.get("swboundary", "default") == "surface"
+        if self.mo:
+            self.boundary = Boundary_surface(self.grid, self.fields, z0m=bi.get("z0m", 0.1), z0h=bi.get("z0h", 0.1),
+                                             ustar=bi.get("ustar"), **bkw)
+        else:
+            self.boundary = Boundary(self.grid, self.fields, swboundary=bi.get("swboundary", "default"), **bkw)
         ai = ini.get("advec", {})
         self.advec = Advec.factory(self.grid, self.fields, swadvec, cflmax=ai.get("cflmax", 1.0),
                                    fluxlimit_list=ai.get("fluxlimit_list", ()))
@@ -94,7 +101,7 @@ class Model:
                            lslist=fo.get("lslist", ()), swwls=fo.get("swwls", "0"), swwls_mom=fo.get("swwls_mom", False),
                            swnudge=fo.get("swnudge", "0"), nudgelist=fo.get("nudgelist", ()), profs=profs,
                            utrans=gi.get("utrans", 0.), vtrans=gi.get("vtrans", 0.))
-        self.surface = surface or {}
+        self.surface = self.boundary.planes() if self.mo else (surface or {})
         self.boundary.set_values()
         self.pres.set_values()
         self.diff.create()
@@ -107,6 +114,9 @@ class Model:
         self.diff.exec_viscosity(self.thermo, surface=self.surface)   # :354
         if not tl.in_substep() and tl.adaptivestep:        # set_time_step, :357 -> :731-751
             tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
+        if self.mo:             # :376-377 (Thermo::exec of :366 only adds to wt, which the surface layer does not read)
+            b.exec(self.thermo)
+            b.set_ghost_cells()
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
             self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
         elif self.fuse_tend4:   # :387-392 in one call, the momentum diffusion inside the advection passes
@@ -166,7 +176,7 @@ class Model:
         ini = IO.model_ini(IO.Input(ini_path))
         gi = ini["grid"]
         z = IO.load_grid(gi["itot"], gi["jtot"], gi["ktot"], directory=directory)["z"]
-        m = cls(ini, z, device=device, surface=surface, profs=profs)
+        m = cls(ini, z, device=device, surface=surface, profs=profs, mo=surface is None)
         m.load(directory=directory, iotime=iotime)
         return m
 

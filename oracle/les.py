@@ -8,7 +8,7 @@ import ctypes as C
 
 import numpy as np
 
-from .ref import RefWorld, lib
+from .ref import RefWorld, lib, _p
 
 BC = {"dirichlet": 0, "neumann": 1, "flux": 2, "noslip": 0, "freeslip": 1}
 
@@ -18,7 +18,7 @@ class OracleLES:
                  visc=1e-5, svisc=1e-5, cs=0.23, tPr=1. / 3., thref0=300., swthermo="dry", surface=None,
                  mbcbot="freeslip", mbctop="freeslip", sbc=None, rkorder=3, dt=1.0, dtmax=1e9, adaptivestep=True,
                  cflmax=1.0, dnmax=0.4, rhoref=None, rhorefh=None, fluxlimit_list=(), endtime=None, buffer=None, force=None,
-                 profs=None):
+                 profs=None, mo=None):
         gc = None
         if swadvec == "2i5":
             gc = (3, 3, 2 if fluxlimit_list else 1)      # src/advec_2i5.cxx:42-45
@@ -62,6 +62,25 @@ class OracleLES:
         self.idtmax = int(self.ifactor * dtmax + 0.5)
         self.itime, self.time, self.iteration, self.substep = 0, 0., 0, 0
         self.zero2 = z2()
+        # Monin-Obukhov surface layer (Boundary_surface, swconstantz0=true): mo = dict(z0m=, z0h=); the surface planes are then
+        # computed every substep (src/model.cxx:376-377) instead of being prescribed through `surface`.
+        self.mo = mo
+        if mo:
+            self.sm = 1
+            self.ustar, self.obuk = z2(1e-2), z2(1e-9)
+            self.nobuk = np.zeros((W.jcells, W.icells), dtype=np.int32)
+            self.z0m, self.z0h, self.dutot = z2(mo["z0m"]), z2(mo["z0h"]), z2()
+            self.surface = dict(z0m=self.z0m, dudz=z2(), dvdz=z2(), dbdz=z2(), ufluxbot=z2(), vfluxbot=z2(), ufluxtop=z2(),
+                                vfluxtop=z2(), sfluxbot=z2(), sfluxtop=z2())
+            self.ugradbot, self.vgradbot = self.planes["u"]["gradbot"], self.planes["v"]["gradbot"]
+            self.thermobc = self.planes["th"]["bcbot"] if "th" in self.planes else 2
+            if "th" in self.planes:
+                pl = self.planes["th"]
+                if pl["bcbot"] == 2:          # flux bc: sbot is the prescribed surface flux (Boundary::set_values)
+                    self.surface["sfluxbot"][:] = pl["gradbot"]; pl["gradbot"][:] = 0.
+                if pl["bctop"] != 0:
+                    self.surface["sfluxtop"][:] = -svisc * pl["gradtop"]
+            lib().ref_surface_lut(W.h, C.c_int(self.mbc[0]), C.c_int(self.thermobc), C.c_double(mo["z0m"]), C.c_double(mo["z0h"]), None, None)
         # Buffer / Force (src/buffer.cxx, src/force.cxx): dicts with the .ini keys; profs = init profiles (ktot values)
         self.buffer, self.force = buffer or {}, force or {}
         def lev(name):
@@ -111,6 +130,23 @@ class OracleLES:
             self.dt = self.idt / self.ifactor
         if self.swthermo == "dry":
             W.call("ref_thermo_buoyancy_tend", at["w"], a["th"], self.threfh)
+        if self.mo:        # boundary->exec + set_ghost_cells, src/model.cxx:376-377
+            S = self.surface
+            dry = self.swthermo == "dry"
+            pth = self.planes.get("th", {})
+            lib().ref_surface_exec(
+                W.h, C.c_int(self.mbc[0]), C.c_int(1 if dry else 0), C.c_int(self.thermobc), _p(u), _p(v),
+                _p(self.planes["u"]["bot"]), _p(self.planes["v"]["bot"]), _p(S["ufluxbot"]), _p(S["vfluxbot"]),
+                _p(self.ugradbot), _p(self.vgradbot), _p(a["th"]) if dry else None, _p(pth.get("bot")), _p(pth.get("gradbot")),
+                _p(S["sfluxbot"]), _p(self.thref), _p(self.threfh), _p(self.ustar), _p(self.obuk),
+                self.nobuk.ctypes.data_as(C.c_void_p), _p(self.z0m), _p(self.z0h), _p(self.dutot), _p(S["dudz"]), _p(S["dvdz"]),
+                _p(S["dbdz"]))
+            for n in ("u", "v"):
+                pl = self.planes[n]
+                W.call("ref_ghost_cells", a[n], self.mbc[0], self.mbc[1], pl["bot"], pl["top"], pl["gradbot"], pl["gradtop"])
+            for n in self.scalars:
+                pl = self.planes[n]
+                W.call("ref_ghost_cells", a[n], pl["bcbot"], pl["bctop"], pl["bot"], pl["top"], pl["gradbot"], pl["gradtop"])
         if W.order == 4:
             W.call("ref_ghost_cells_w", w, 1)
         if self.swadvec == "2":

@@ -27,12 +27,12 @@ def profiles(fields, ks, ke, js, je, is_, ie):
     return out
 
 
-def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None):
+def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=False):
     import torch
     from microhh_b200.model import Model
     from oracle.les import OracleLES
     dev = torch.device("cuda:0")
-    m = Model(ini, z, device=dev, profs=profs)
+    m = Model(ini, z, device=dev, profs=profs, mo=mo)
     g, f = m.grid, m.fields
     up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     for n in "uvw":
@@ -57,7 +57,8 @@ def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None):
                   rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1), dtmax=ti.get("dtmax", 1e9),
                   adaptivestep=ti.get("adaptivestep", True), cflmax=ai.get("cflmax", 1.0), dnmax=di.get("dnmax", 0.4),
                   fluxlimit_list=ai.get("fluxlimit_list", ()), endtime=ti.get("endtime"), buffer=ini.get("buffer"),
-                  force=ini.get("force"), profs=profs, **(oracle_kw or {}))
+                  force=ini.get("force"), profs=profs,
+                  mo=dict(z0m=bi.get("z0m", 0.1), z0h=bi.get("z0h", 0.1)) if mo else None, **(oracle_kw or {}))
     dts = []
     for _ in range(nsteps):
         m.step()
@@ -141,6 +142,21 @@ def test_les_100_steps_stats_profiles(cuda_lib, kind, tol, dt_ns):
     ini, z, init, surface = les_case(kind)
     res = run_both(ini, z, init, 100, surface=surface)
     check_profiles(res, tol, dt_ns)
+    assert res["status"]["div"] <= max(10 * res["odiv"], 1e-12)
+
+
+@pytest.mark.parametrize("kind", ["gabls1_stable", "drycbl_from_rest"])
+def test_les_with_monin_obukhov_surface_layer(cuda_lib, kind):
+    """swboundary=surface computed on the device every substep (Boundary_surface::exec: total wind, Obukhov length from the
+    z/L lookup, u*, surface fluxes, MO gradients) instead of prescribed planes: 100 steps, stats profiles at 1e-9.
+    gabls1_stable: th Dirichlet at the surface (cooled, stable: the Dirichlet lookup); drycbl: prescribed heat flux
+    (unstable: the flux lookup)."""
+    ini, z, init, _ = les_case(kind)
+    if kind == "drycbl_from_rest":
+        ini["boundary"]["sbc"]["th"] = dict(sbcbot="flux", sbctop="neumann", sbot=0.1, stop=0.003)
+        init = dict(init, u=init["u"] + 0.5)            # a light wind so that the first steps are not at the |U| floor
+    res = run_both(ini, z, init, 100, mo=True)
+    check_profiles(res, 1e-9, 100)
     assert res["status"]["div"] <= max(10 * res["odiv"], 1e-12)
 
 

@@ -1,0 +1,122 @@
+"""GPU parity of the Monin-Obukhov surface layer: mhh_boundary_surface_exec / Boundary_surface.exec
+against the reference's own kernels (src/boundary_surface.cxx, include/boundary_surface_kernels.h, include/monin_obukhov.h
+compiled in place, oracle/_ref).  The lookup table is built on the host with the same libm on both sides: bit-exact.  The
+kernels call log/pow/exp from the CUDA math library instead of glibc (<= 2 ulp apart), so planes agree to 1e-12 relative."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.helpers import make_case, rel_err
+from tests.test_gpu_ops import _up, _worlds
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+def _lut(W, mbc, tbc, z0m, z0h):
+    from oracle.ref import lib
+    zL, f = np.zeros(10000, dtype=np.float32), np.zeros(10000, dtype=np.float32)
+    lib().ref_surface_lut(W.h, C.c_int(mbc), C.c_int(tbc), C.c_double(z0m), C.c_double(z0h),
+                          zL.ctypes.data_as(C.c_void_p), f.ctypes.data_as(C.c_void_p))
+    return zL, f
+
+
+@pytest.mark.parametrize("tbc", [0, 2], ids=["th_dirichlet", "th_flux"])
+def test_lookup_table_bit_exact(cuda_lib, tbc):
+    case = make_case(itot=8, jtot=8, ktot=8, zsize=400., xsize=400., ysize=400.)
+    g, W = _worlds(case)
+    zL, f = _lut(W, 0, tbc, 0.1, 0.05)
+    assert g.lib.mhh_surface_init_solver(g.ctx, 0, tbc, C.c_double(0.1), C.c_double(0.05)) == 0
+    gz, gf = np.zeros(10000, dtype=np.float32), np.zeros(10000, dtype=np.float32)
+    assert g.lib.mhh_surface_get_lut(g.ctx, gz.ctypes.data_as(C.c_void_p), gf.ctypes.data_as(C.c_void_p)) == 0
+    assert np.array_equal(gz, zL) and np.array_equal(gf, f)
+    assert zL[0] < -9e3 and abs(zL[-1] - 10.) < 1e-5 and np.all(np.diff(zL) > 0)
+    g.close(); W.close()
+
+
+@pytest.mark.parametrize("mode", ["noslip_dirichlet", "noslip_flux_unstable", "noslip_flux_stable", "neutral", "ustar_flux"])
+def test_boundary_surface_exec(cuda_lib, mode):
+    import torch
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    from oracle.ref import lib, _p
+    case = make_case(itot=24, jtot=16, ktot=8, xsize=400., ysize=400., zsize=400.)
+    g, W = _worlds(case)
+    rng = np.random.default_rng(31)
+    dry = mode != "neutral"
+    mb = "ustar" if mode == "ustar_flux" else "noslip"
+    sb = "dirichlet" if mode == "noslip_dirichlet" else "flux"
+    sbot = {"noslip_dirichlet": 299.5, "noslip_flux_unstable": 0.1, "noslip_flux_stable": -0.01, "ustar_flux": 0.05}.get(mode, 0.)
+    f = H.Fields(g, slist=["th", "s"] if dry else ["s"], visc=1e-5, svisc=1e-5)
+    u = 3. + case["u"]; v = 0.5 * case["v"]
+    f.mp["u"].fld.copy_(_up(g, u)); f.mp["v"].fld.copy_(_up(g, v))
+    th = case["s"][0]; s = 1. + rng.uniform(0, 1, W.shape)
+    if dry:
+        f.sp["th"].fld.copy_(_up(g, th))
+    f.sp["s"].fld.copy_(_up(g, s))
+    sbc = {"s": dict(sbcbot="flux", sbctop="neumann", sbot=0.02, stop=0.)}
+    if dry:
+        sbc["th"] = dict(sbcbot=sb, sbctop="neumann", sbot=sbot, stop=0.003)
+    b = H.Boundary_surface(g, f, z0m=0.1, z0h=0.02, mbcbot=mb, mbctop="freeslip", sbc=sbc, ustar=0.3 if mb == "ustar" else None)
+    b.set_values()
+    b.set_prognostic_cyclic_bcs()
+    thermo = Thermo(g, f, "dry" if dry else "0", thref0=300.)
+    # oracle state
+    z2 = lambda val=0.: np.full((W.jcells, W.icells), float(val))
+    mbc, tbc = (3 if mb == "ustar" else 0), (0 if sb == "dirichlet" else 2)
+    _lut(W, mbc, tbc, 0.1, 0.02)
+    ua, va = f.mp["u"].fld.cpu().numpy(), f.mp["v"].fld.cpu().numpy()
+    tha = f.sp["th"].fld.cpu().numpy() if dry else None
+    sa = f.sp["s"].fld.cpu().numpy()
+    o = dict(ubot=z2(), vbot=z2(), uflux=z2(), vflux=z2(), ugrad=z2(), vgrad=z2(),
+             thbot=z2(sbot if sb == "dirichlet" else 0.), thgrad=z2(), thflux=z2(sbot if sb == "flux" else 0.),
+             ustar=z2(0.3 if mb == "ustar" else 1e-2), obuk=z2(1e-9), nobuk=np.zeros((W.jcells, W.icells), dtype=np.int32),
+             z0m=z2(0.1), z0h=z2(0.02), dutot=z2(), dudz=z2(), dvdz=z2(), dbdz=z2(), sbot=z2(), sgrad=z2(), sflux=z2(0.02))
+    thref = np.full(W.kcells, 300.)
+    for rep in range(2):            # twice: the lookup resumes from the indices the first call left in nobuk
+        b.exec(thermo)
+        lib().ref_surface_exec(W.h, C.c_int(mbc), C.c_int(1 if dry else 0), C.c_int(tbc), _p(ua), _p(va), _p(o["ubot"]), _p(o["vbot"]),
+                               _p(o["uflux"]), _p(o["vflux"]), _p(o["ugrad"]), _p(o["vgrad"]), _p(tha), _p(o["thbot"]), _p(o["thgrad"]),
+                               _p(o["thflux"]), _p(thref), _p(thref), _p(o["ustar"]), _p(o["obuk"]), o["nobuk"].ctypes.data_as(C.c_void_p),
+                               _p(o["z0m"]), _p(o["z0h"]), _p(o["dutot"]), _p(o["dudz"]), _p(o["dvdz"]), _p(o["dbdz"]))
+        lib().ref_surface_scalar(W.h, C.c_int(2), _p(sa), _p(o["sbot"]), _p(o["sgrad"]), _p(o["sflux"]), _p(o["ustar"]), _p(o["obuk"]), _p(o["z0h"]))
+        inner = (slice(W.jstart, W.jend), slice(W.istart, W.iend))
+        got = dict(uflux=f.mp["u"].flux_bot, vflux=f.mp["v"].flux_bot, ugrad=f.mp["u"].grad_bot, vgrad=f.mp["v"].grad_bot,
+                   ustar=b.ustar, obuk=b.obuk, dudz=b.dudz_mo, dvdz=b.dvdz_mo, sbot=f.sp["s"].fld_bot, sgrad=f.sp["s"].grad_bot)
+        if dry:
+            got.update(thbot=f.sp["th"].fld_bot, thgrad=f.sp["th"].grad_bot, thflux=f.sp["th"].flux_bot, dbdz=b.dbdz_mo)
+        for k, t in got.items():
+            a = t.cpu().numpy()
+            sel = inner if k in ("dudz", "dvdz", "dbdz") else (slice(None), slice(None))
+            if mode == "neutral" and k == "obuk":
+                assert np.all(a == -1e9)
+                continue
+            assert rel_err(a[sel], o[k][sel]) <= TOL, (k, rep, rel_err(a[sel], o[k][sel]))
+        if dry and mb == "noslip":
+            assert np.array_equal(b.nobuk.cpu().numpy(), o["nobuk"])
+        # physically sensible: u* in (0, 2) m/s, the sign of L follows the surface buoyancy flux
+        us = b.ustar.cpu().numpy()[inner]
+        assert us.min() > 0. and us.max() < 2.
+        # perturb the wind a little so that the second call's lookup has to move
+        ua = ua * 1.05; f.mp["u"].fld.mul_(1.05)
+    L = b.obuk.cpu().numpy()[inner]
+    if mode in ("noslip_flux_unstable", "ustar_flux"):
+        assert L.max() < 0.
+    if mode in ("noslip_flux_stable", "noslip_dirichlet"):
+        assert L.min() > 0.
+    g.close(); W.close()
+
+
+def test_surface_model_rejects_unsupported_bcs(cuda_lib):
+    from microhh_b200 import host as H, lib as L
+    case = make_case(itot=8, jtot=8, ktot=8)
+    g, W = _worlds(case)
+    f = H.Fields(g, slist=["th"])
+    with pytest.raises(L.MhhError, match="Neumann bc is not supported in surface model"):
+        H.Boundary_surface(g, f, mbcbot="freeslip", sbc={"th": dict(sbcbot="flux")})
+    with pytest.raises(L.MhhError, match="Fixed Gradient bc is not supported in surface model"):
+        H.Boundary_surface(g, f, mbcbot="noslip", sbc={"th": dict(sbcbot="neumann")})
+    with pytest.raises(L.MhhError, match="Fixed Ustar bc in combination with Dirichlet"):
+        H.Boundary_surface(g, f, mbcbot="ustar", ustar=0.3, sbc={"th": dict(sbcbot="dirichlet")})
+    g.close(); W.close()
