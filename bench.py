@@ -37,7 +37,7 @@ BYTES_PER_POINT = {
     "smag2_diff_c_kernel": 32,
     # one-pass tendencies (no SURVEY row: they replace thermo + advec + diff of the rows above)
     "advec2_smag2_uvw_kernel": 88,   # R u,v,w,evisc,th ; R+W ut,vt,wt
-    "advec2_smag2_c_kernel": 56,     # R s,evisc,u,v,w ; R+W st
+    "advec2_smag2_c_kernel": 64,     # R s,evisc,u,v,w ; R+W st ; W s_new (the scalar's RK update rides in the pass)
     "pres2_in_kernel": 56,
     "fft_fwd_x": 16, "fft_fwd_y": 16, "fft_bwd_y": 16, "fft_bwd_x": 16,
     "pres2_tdma_kernel": 32,
@@ -48,9 +48,9 @@ BYTES_PER_POINT = {
     "advec2_cfl_kernel": 24, "smag2_dnmul_kernel": 8,
 }
 BYTES_PER_STEP = 3 * 608 + 32       # 1856 B / grid-point-step (the reference's operator-by-operator passes)
-# what this implementation's fused passes move: evisc 40, momentum 88, scalar 56, pres_in 56, 4 FFT passes 64, tdma 28
-# (two sweeps over p + pivot checkpoints), output+RK 104, scalar RK 32 per substep; cfl 24 + dnmul 8 per step
-BYTES_PER_STEP_FUSED = 3 * 468 + 32
+# what this implementation's fused passes move: evisc 40, momentum 88, scalar + its RK 64, pres_in 56, 4 FFT passes 64,
+# tdma 28 (two sweeps over p + pivot checkpoints), output+RK 104 per substep; cfl 24 + dnmul 8 per step
+BYTES_PER_STEP_FUSED = 3 * 444 + 32
 
 
 def ncu_traffic(kernel, n):

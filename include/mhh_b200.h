@@ -141,6 +141,25 @@ int mhh_advec2_smag2_exec(mhh_ctx* ctx, int surface_model,
                           int nscalars, const double* const* s, double* const* st,
                           const double* const* sfluxbot, const double* const* sfluxtop,
                           const double* svisc, double tPr);
+/* The same pass with, per scalar, the two operators that follow Diff::exec in Model::exec when nothing else adds to the
+ * scalar's tendency (no [force] term on it), applied to the finished tendency before it is stored:
+ *   sbuf[n] != NULL : Buffer::exec of that scalar (src/buffer.cxx:37-58; needs mhh_buffer_plan), profile sbuf[n];
+ *   s_new[n] != NULL: Timeloop::exec of that scalar (src/timeloop.cxx:250-304): s_new = s + cB dt st, st = cA st (zeroed,
+ *                     ghost cells included, after the last substep).  s_new[n] is a second array of the same size — the
+ *                     interior holds the updated field on return, the caller swaps the two pointers and refreshes the
+ *                     ghost cells as at the start of every substep (src/model.cxx:346-348).
+ * sbuf / s_new may be NULL (then identical to mhh_advec2_smag2_exec).  Bit-identical to the separate calls; saves 3 of the 4
+ * field passes of the scalar's RK update (and the 3 of its Buffer pass). */
+int mhh_advec2_smag2_exec_rk(mhh_ctx* ctx, int surface_model,
+                             const double* u, const double* v, const double* w, const double* evisc,
+                             double* ut, double* vt, double* wt,
+                             const double* ufluxbot, const double* ufluxtop,
+                             const double* vfluxbot, const double* vfluxtop, double visc,
+                             const double* th_buoy,
+                             int nscalars, const double* const* s, double* const* st,
+                             const double* const* sfluxbot, const double* const* sfluxtop,
+                             const double* svisc, double tPr,
+                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt);
 /* calc_strain2 alone (src/diff_smag2.cxx:48) — stage check for parity tests; the product path fuses it. */
 int mhh_smag2_strain2(mhh_ctx* ctx, int surface_model, const double* u, const double* v, const double* w,
                       const double* dudz, const double* dvdz, double* strain2);

@@ -37,6 +37,10 @@ int smag2_exec(Ctx*, int, const double*, const double*, const double*, const dou
 int advec2_smag2_exec(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
                       const double*, const double*, const double*, const double*, double, const double*, int,
                       const double* const*, double* const*, const double* const*, const double* const*, const double*, double);
+int advec2_smag2_exec_rk(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
+                         const double*, const double*, const double*, const double*, double, const double*, int,
+                         const double* const*, double* const*, const double* const*, const double* const*, const double*, double,
+                         const double* const*, double* const*, int, int, double);
 int smag2_dnmul_bits(Ctx*, const double*, double, unsigned long long*);
 // boundary.cu
 int cyclic_exec(Ctx*, double*, int);
@@ -472,6 +476,22 @@ int mhh_advec2_smag2_exec(mhh_ctx* c, int surface_model, const double* u, const 
     if (c->order != 2 || c->gd.igc != 1 || c->gd.jgc != 1) { c->last_error = "mhh_advec2_smag2_exec needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
     if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
     return advec2_smag2_exec(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft, svisc, tPr);
+}
+
+int mhh_advec2_smag2_exec_rk(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                             double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
+                             double visc, const double* th_buoy, int ns, const double* const* s, double* const* st,
+                             const double* const* sfb, const double* const* sft, const double* svisc, double tPr,
+                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt)
+{
+    CTX_CHECK(c);
+    if (c->order != 2 || c->gd.igc != 1 || c->gd.jgc != 1) { c->last_error = "mhh_advec2_smag2_exec_rk needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
+    if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
+    if (s_new && rkorder != 3 && rkorder != 4) { c->last_error = "rkorder must be 3 or 4"; return MHH_ERR_ARG; }
+    if (s_new) for (int n = 0; n < ns; ++n) if (s_new[n] && s_new[n] == s[n])
+    { c->last_error = "mhh_advec2_smag2_exec_rk: s_new must not alias s (neighbouring tiles still read s)"; return MHH_ERR_ARG; }
+    return advec2_smag2_exec_rk(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft,
+                                svisc, tPr, sbuf, s_new, rkorder, substep, dt);
 }
 
 int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)

@@ -506,13 +506,29 @@ constexpr int UVW_SLOTS = 6;
     // ADVEC: the kernel first adds the 2nd-order scalar advection (advec_s, src/advec_2.cxx:191-202), so that the scalar,
     //        its tendency and evisc cross HBM once for both operators: (t + advection) + diffusion, bit-identical to
     //        Advec::exec followed by Diff::exec.
+    // Optional tail of the scalar pass (mhh_advec2_smag2_exec_rk), applied to the finished tendency t of a cell before it is
+    // stored — the terms that follow Diff::exec for a scalar in Model::exec when nothing else touches its tendency:
+    //   sig != NULL : Buffer::exec, t -= sigma(z_k) (a - abuf[k]) for k >= bufk            (src/buffer.cxx:37-58)
+    //   rk_mode 1/2 : Timeloop::exec, a_new = a + cB dt t ; t = cA t (mode 2: last substep, the caller zeroes the
+    //                 tendency array afterwards)                                            (src/timeloop.cxx:250-285)
+    // a_new is a SECOND array (neighbouring CTAs still read a); the caller swaps the two pointers.
+    struct ScalarTail
+    {
+        double* a_new;
+        double cB_dt, cA_next;
+        int rk_mode;
+        const double* sig;
+        const double* abuf;
+        int bufk;
+    };
+
     template<bool SURF, bool ADVEC, int TX, int TY>
     __global__ void __launch_bounds__(TX * TY, MHH_SCALAR_MINB)
     smag2_scalar_tile_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
                              const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
                              const double tPr, const double visc,
                              const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
-                             const GridD gd)
+                             const ScalarTail tail, const GridD gd)
     {
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4, NF = ADVEC ? 4 : 2;
@@ -623,7 +639,17 @@ constexpr int UVW_SLOTS = 6;
             if (bot)      ver = div_by( fd_t + rhoh_b * rare_load(fluxbot, ij), rho, rho_i ) * dzi;
             else if (top) ver = div_by( -rhoh_t * rare_load(fluxtop, ij) - fd_b, rho, rho_i ) * dzi;
             else          ver = div_by( fd_t - fd_b, rho, rho_i ) * dzi;
-            if (live) at[ijk] = at_c + (hor + ver);
+            double tn = at_c + (hor + ver);
+            if (tail.sig != nullptr && k >= tail.bufk) tn -= tail.sig[k] * (a_c - tail.abuf[k]);
+            if (live)
+            {
+                if (tail.rk_mode == 0) at[ijk] = tn;
+                else
+                {
+                    tail.a_new[ijk] = a_c + tail.cB_dt * tn;
+                    if (tail.rk_mode == 1) at[ijk] = tn * tail.cA_next;
+                }
+            }
             fd_b = fd_t;
             a_c = a_t; e_c = e_t;
             at_c = at_n;
@@ -761,14 +787,30 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
 }
 
 // Scalar tendency.  advec == 0: Diff_smag2's diff_c.  advec == 1: preceded in the same pass by Advec_2's advec_s.
-int smag2_tend_scalar(Ctx* c, int surface_model, int advec, double* at, const double* a, const double* evisc,
-                      const double* fluxbot, const double* fluxtop, double tPr, double visc,
-                      const double* u, const double* v, const double* w)
+void rk_coefs(int rkorder, int substep, double dt, double* cB_dt, double* cA_next, int* zero_all);
+
+// sbuf: Buffer profile of this scalar or NULL; a_new: RK target or NULL (then rkorder/substep/dt are unused)
+int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, const double* a, const double* evisc,
+                           const double* fluxbot, const double* fluxtop, double tPr, double visc,
+                           const double* u, const double* v, const double* w,
+                           const double* sbuf, double* a_new, int rkorder, int substep, double dt)
 {
     const GridD& gd = c->gd;
+    ScalarTail tail{nullptr, 0., 0., 0, nullptr, nullptr, 0};
+    if (sbuf)
+    {
+        if (!c->buffer_sigma_d) { c->last_error = "buffer not planned (mhh_buffer_plan)"; return MHH_ERR_STATE; }
+        tail.sig = c->buffer_sigma_d; tail.abuf = sbuf; tail.bufk = c->buffer_kstart;
+    }
+    if (a_new)
+    {
+        int zero_all = 0;
+        rk_coefs(rkorder, substep, dt, &tail.cB_dt, &tail.cA_next, &zero_all);
+        tail.a_new = a_new; tail.rk_mode = zero_all ? 2 : 1;
+    }
     constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
     const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    #define SC_LAUNCH(NAME, S, A) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, gd)))
+    #define SC_LAUNCH(NAME, S, A) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd)))
     if (!advec)
     {
         if (surface_model) SC_LAUNCH("smag2_diff_c_kernel", true, false);
@@ -781,6 +823,31 @@ int smag2_tend_scalar(Ctx* c, int surface_model, int advec, double* at, const do
     }
     #undef SC_LAUNCH
     MHH_LAUNCH_CHECK();
+    if (tail.rk_mode == 2)      // last substep: the whole tendency array (ghost cells too) is zero afterwards, src/timeloop.cu:34-70
+        MHH_CUDA_CHECK(cudaMemsetAsync(at, 0, sizeof(double) * gd.ncells, c->stream));
+    return MHH_OK;
+}
+
+int smag2_tend_scalar(Ctx* c, int surface_model, int advec, double* at, const double* a, const double* evisc,
+                      const double* fluxbot, const double* fluxtop, double tPr, double visc,
+                      const double* u, const double* v, const double* w)
+{
+    return smag2_tend_scalar_tail(c, surface_model, advec, at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, nullptr, nullptr, 0, 0, 0.);
+}
+
+// mhh_advec2_smag2_exec_rk: as advec2_smag2_exec; per scalar optionally the Buffer term and the RK update (see ScalarTail)
+int advec2_smag2_exec_rk(Ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                         double* ut, double* vt, double* wt,
+                         const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
+                         double visc, const double* th_buoy, int nscalars, const double* const* s, double* const* st,
+                         const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr,
+                         const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt)
+{
+    if (int e = smag2_tend_uvw(c, surface_model, 1, u, v, w, evisc, ut, vt, wt, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th_buoy)) return e;
+    for (int n = 0; n < nscalars; ++n)
+        if (int e = smag2_tend_scalar_tail(c, surface_model, 1, st[n], s[n], evisc, surface_model ? sfluxbot[n] : nullptr,
+                                           surface_model ? sfluxtop[n] : nullptr, tPr, svisc[n], u, v, w,
+                                           sbuf ? sbuf[n] : nullptr, s_new ? s_new[n] : nullptr, rkorder, substep, dt)) return e;
     return MHH_OK;
 }
 

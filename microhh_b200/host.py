@@ -408,9 +408,13 @@ class Diff:
                 L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
                 C.c_double(f.visc), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_smag2_exec")
 
-    def exec_with_advec2(self, th_buoy=None):
+    def exec_with_advec2(self, th_buoy=None, buffer=None, timeloop=None):
         """Thermo_dry::exec (when th_buoy is given) + Advec_2::exec + Diff_smag2::exec in one pass per prognostic field
-        (mhh_advec2_smag2_exec); bit-identical to the three calls in the time loop's order."""
+        (mhh_advec2_smag2_exec); bit-identical to the three calls in the time loop's order.
+        With ``timeloop`` (and optionally ``buffer``) the scalars' Buffer term and RK update ride in their pass
+        (mhh_advec2_smag2_exec_rk): the updated scalar lands in Field3d.fld_alt and the two tensors are swapped here, so on
+        return ``fields.sp[name].fld`` is the advanced field (ghost cells stale until the next set_*_bcs, as after
+        Timeloop::exec).  Only valid when nothing else adds to the scalar tendencies afterwards."""
         g, f = self.grid, self.fields
         if self.swdiff != "smag2" or g.order != 2:
             raise L.MhhError("the fused tendency pass needs swdiff=smag2 on the 2nd-order grid")
@@ -420,11 +424,24 @@ class Diff:
         svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
         sfb = L.ptr_array([f.sp[n].flux_bot for n in names])
         sft = L.ptr_array([f.sp[n].flux_top for n in names])
-        L.check(g.ctx, g.lib.mhh_advec2_smag2_exec(
-            g.ctx, self._surface_model(), L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sd["evisc"].fld),
-            L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
-            L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
-            C.c_double(f.visc), L.ptr(th_buoy), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_advec2_smag2_exec")
+        args = (g.ctx, self._surface_model(), L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sd["evisc"].fld),
+                L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
+                L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
+                C.c_double(f.visc), L.ptr(th_buoy), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr))
+        if timeloop is None:
+            L.check(g.ctx, g.lib.mhh_advec2_smag2_exec(*args), "mhh_advec2_smag2_exec")
+            return
+        for n in names:
+            if getattr(f.sp[n], "fld_alt", None) is None:
+                f.sp[n].fld_alt = torch.zeros_like(f.sp[n].fld)
+        s_new = L.ptr_array([f.sp[n].fld_alt for n in names])
+        sbuf = None
+        if buffer is not None and buffer.swbuffer:
+            sbuf = L.ptr_array([f.sp[n].fld_mean if buffer.swupdate else buffer.bufferprofs[n] for n in names])
+        L.check(g.ctx, g.lib.mhh_advec2_smag2_exec_rk(*args, sbuf, s_new, timeloop.rkorder, timeloop.substep, C.c_double(timeloop.dt)),
+                "mhh_advec2_smag2_exec_rk")
+        for n in names:
+            f.sp[n].fld, f.sp[n].fld_alt = f.sp[n].fld_alt, f.sp[n].fld
 
     def exec_with_advec4(self):
         """Advec_4::exec + set_ghost_cells_w(Normal) + Diff_4::exec (src/model.cxx:387-392) through mhh_advec4_diff4_exec:
@@ -597,11 +614,14 @@ class Buffer:
                 self.bufferprofs[name] = (_level_profile(grid, profs[name], name) if name in profs
                                           else torch.zeros(grid.kcells, dtype=torch.float64, device=grid.device))
 
-    def exec(self, stats=None):
+    def exec(self, stats=None, skip=()):
+        """`skip`: fields whose Buffer term was applied inside the fused scalar pass."""
         if not self.swbuffer:
             return
         g, f = self.grid, self.fields
         for name, fld in f.ap.items():
+            if name in skip:
+                continue
             abuf = fld.fld_mean if self.swupdate else self.bufferprofs[name]
             L.check(g.ctx, g.lib.mhh_buffer_exec(g.ctx, L.ptr(f.at[name].fld), L.ptr(fld.fld), L.ptr(abuf),
                                                  1 if name == "w" else 0), "mhh_buffer_exec")

@@ -101,6 +101,11 @@ class Model:
                            lslist=fo.get("lslist", ()), swwls=fo.get("swwls", "0"), swwls_mom=fo.get("swwls_mom", False),
                            swnudge=fo.get("swnudge", "0"), nudgelist=fo.get("nudgelist", ()), profs=profs,
                            utrans=gi.get("utrans", 0.), vtrans=gi.get("vtrans", 0.))
+        # the scalars' Buffer term and RK update ride in their tendency pass when no [force] term touches a scalar tendency
+        fo_ = self.force
+        scal = set(self.fields.sp)
+        self.fuse_scalar_rk = (self.fuse_tend and bool(scal) and npy == 1 and fo_.swwls == "0"
+                               and not (scal & set(fo_.lslist)) and not (scal & set(fo_.nudgelist)))
         self.surface = self.boundary.planes() if self.mo else (surface or {})
         self.boundary.set_values()
         self.pres.set_values()
@@ -118,7 +123,9 @@ class Model:
             b.exec(self.thermo)
             b.set_ghost_cells()
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
-            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None)
+            srk = self.fuse_scalar_rk
+            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None,
+                                       buffer=self.buffer if srk else None, timeloop=tl if srk else None)
         elif self.fuse_tend4:   # :387-392 in one call, the momentum diffusion inside the advection passes
             self.thermo.exec()                             # :366
             b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387
@@ -129,14 +136,15 @@ class Model:
             self.advec.exec()                              # :388
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :389
             self.diff.exec()                               # :392
-        self.buffer.exec()                                 # :395
+        done_s = tuple(self.fields.sp) if (self.fuse_tend and self.fuse_scalar_rk) else ()
+        self.buffer.exec(skip=done_s)                      # :395
         self.force.exec(tl.get_sub_time_step(), self.thermo)   # :404
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
         # :411 + :484 for u,v,w in one pass
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
         if not fused:
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :412 (inside the fused call otherwise)
-        tl.exec(skip=("u", "v", "w") if fused else ())     # :484
+        tl.exec(skip=(("u", "v", "w") if fused else ()) + done_s)     # :484
         tl.step_time()                                     # :487
 
     # ---- the reference's restart files (src/model.cxx:257-262,470-478; formats in microhh_b200.io) ----
@@ -208,8 +216,7 @@ class HostFeed:
         import torch
         self.model, self.torch = model, torch
         f = model.fields
-        self.targets = {**{n: f.mp[n].fld for n in f.mp}, **{n: f.sp[n].fld for n in f.sp}}
-        self.stage = [{n: torch.empty_like(t) for n, t in self.targets.items()} for _ in range(2)]
+        self.stage = [{n: torch.empty_like(fld.fld) for n, fld in f.ap.items()} for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=model.grid.device)
         self.ready = [torch.cuda.Event(), torch.cuda.Event()]      # upload into slot finished
         self.free = [torch.cuda.Event(), torch.cuda.Event()]       # slot has been consumed by adopt()
@@ -231,7 +238,7 @@ class HostFeed:
         slot = self.nadopt % 2
         cur = torch.cuda.current_stream(self.model.grid.device)
         cur.wait_event(self.ready[slot])
-        for n, dst in self.targets.items():
-            dst.copy_(self.stage[slot][n], non_blocking=True)
+        for n, fld in self.model.fields.ap.items():       # looked up now: the fused scalar pass swaps fld / fld_alt
+            fld.fld.copy_(self.stage[slot][n], non_blocking=True)
         self.free[slot].record(cur)
         self.nadopt += 1

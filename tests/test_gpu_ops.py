@@ -368,3 +368,52 @@ def test_fused_advec4_diff4_equals_separate_calls(cuda_lib, dims, nscal):
         assert np.array_equal(res[0][k], res[1][k]), k
     assert np.abs(res[0]["ut"]).max() > 1e-2
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("rkorder,substep", [(3, 0), (3, 2), (4, 2), (4, 4)])
+@pytest.mark.parametrize("swbuffer", [False, True])
+def test_fused_scalar_tail_equals_buffer_then_rk(cuda_lib, rkorder, substep, swbuffer):
+    """mhh_advec2_smag2_exec_rk: the scalars' Buffer term and RK update inside their tendency pass are bit-identical to
+    Advec/Diff::exec, Buffer::exec, Timeloop::exec — interior of the scalar (returned in the swapped second buffer), the whole
+    tendency array (zeroed with its ghost cells after the last substep), u, v, w tendencies untouched by the tail."""
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    case = make_case(itot=40, jtot=10, ktot=37, alpha=1.3, surface_model=1, anelastic=True, nscalars=2, zsize=3200.)
+    g, W = _worlds(case)
+    res = []
+    for fused in (False, True):
+        f = H.Fields(g, slist=["th", "q"], visc=1e-3, svisc=2e-3)
+        f.set_rhoref(case["rhoref"], case["rhorefh"])
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+        f.sp["th"].fld.copy_(_up(g, case["s"][0]))
+        f.sp["q"].fld.copy_(_up(g, case["s"][1]))
+        r = np.random.default_rng(3)
+        for n in f.at:
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        for fld in list(f.mp.values()) + list(f.sp.values()):
+            fld.flux_bot.copy_(_up(g, r.uniform(-1e-2, 1e-2, (W.jcells, W.icells))))
+            fld.flux_top.copy_(_up(g, r.uniform(-1e-2, 1e-2, (W.jcells, W.icells))))
+        t = Thermo(g, f, "dry", thref=np.full(W.kcells, 300.), threfh=np.full(W.kcells, 300.))
+        b = H.Boundary(g, f, swboundary="surface")
+        a = H.Advec.factory(g, f, "2")
+        d = H.Diff.factory(g, f, b, "smag2", cs=0.17, tPr=1. / 3.)
+        f.sd["evisc"].fld.copy_(_up(g, r.uniform(0.1, 1., W.shape)))
+        profs = {"th": 300. + r.uniform(0, 10, W.ktot), "q": r.uniform(0, 1, W.ktot), "u": r.uniform(-1, 1, W.ktot), "v": r.uniform(-1, 1, W.ktot)}
+        buf = H.Buffer(g, f, swbuffer=swbuffer, zstart=2000., sigma=0.00223, beta=2., profs=profs)
+        tl = H.Timeloop(g, f, rkorder=rkorder, dt=0.73)
+        tl.substep = substep
+        if fused:
+            d.exec_with_advec2(f.sp["th"].fld, buffer=buf, timeloop=tl)
+            buf.exec(skip=("th", "q"))
+            tl.exec(skip=("th", "q"))
+        else:
+            t.exec(); a.exec(); d.exec()
+            buf.exec()
+            tl.exec()
+        inner = (slice(W.kstart, W.kend), slice(W.jstart, W.jend), slice(W.istart, W.iend))
+        res.append({n: f.ap[n].fld.cpu().numpy()[inner].copy() for n in f.ap} | {n + "t": f.at[n].fld.cpu().numpy().copy() for n in f.at})
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    assert not np.array_equal(res[0]["th"], case["s"][0][W.kstart:W.kend, W.jstart:W.jend, W.istart:W.iend])
+    g.close(); W.close()
