@@ -3,35 +3,38 @@ python tools/make_profiles.py TAG   (expects gpurun_out/bench_512_TAG.json, laun
 import collections, csv, json, re, subprocess, sys
 tag = sys.argv[1]
 rep = f"gpurun_out/prof_{tag}_step.ncu-rep"
-# 1. --set full summary
-summ = subprocess.run([sys.executable, "tools/ncu_summary.py", rep], capture_output=True, text=True).stdout
-open(f"profiles/{tag}_ncu_full_step512_summary.txt", "w").write(
-    "# ncu --set full --clock-control none --import-source on, one RK substep of bench.py at 512^3 (12 launches)\n"
-    "# GB_rd/GB_wr = dram__bytes_read.sum / dram__bytes_write.sum per launch; fp64% = sm__pipe_fp64_cycles_active; st_* = warp stall reasons per issue\n" + summ)
-# 2. traffic table
-out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-r = list(csv.reader(out.splitlines())); h, u = r[0], r[1]
-def gb(row, name):
-    i = h.index(name); return float(row[i].replace(",", "")) / {"byte": 1e9, "Kbyte": 1e6, "Mbyte": 1e3, "Gbyte": 1.}[u[i]]
-t = {}
-for row in r[2:]:
-    kn = row[h.index("Kernel Name")]
-    v = round(gb(row, "dram__bytes_read.sum") + gb(row, "dram__bytes_write.sum"), 3)
-    key = None
-    if "pres2_out_rk_kernel" in kn: key = "pres2_out_rk_kernel"
-    elif "rk_kernel" in kn: key = "rk_kernel"
-    elif "evisc_kernel" in kn: key = "evisc_kernel"
-    elif "smag2_diff_uvw_tile_kernel" in kn: key = "advec2_smag2_uvw_kernel"
-    elif "smag2_scalar_tile_kernel" in kn: key = "advec2_smag2_c_kernel"
-    elif "pres2_in_kernel" in kn: key = "pres2_in_kernel"
-    elif "pres2_tdma_kernel" in kn: key = "pres2_tdma_kernel"
-    elif "fft_pow2_kernel<(int)-1, 0" in kn: key = "fft_fwd_x"
-    elif "fft_pow2_kernel<(int)-1, 1" in kn: key = "fft_fwd_y"
-    elif "fft_pow2_kernel<1, 1" in kn: key = "fft_bwd_y"
-    elif "fft_pow2_kernel<1, 0" in kn: key = "fft_bwd_x"
-    if key: t[key] = v
-json.dump({"n": 512, "source": f"profiles/{tag}_ncu_full_step512_summary.txt (ncu --set full --clock-control none, one RK substep of bench.py at 512^3)",
-           "gb_per_launch": t}, open("profiles/r01_traffic.json", "w"), indent=1)
+import os
+summ = ''; t = {}
+if os.path.exists(rep):
+    # 1. --set full summary
+    summ = subprocess.run([sys.executable, "tools/ncu_summary.py", rep], capture_output=True, text=True).stdout
+    open(f"profiles/{tag}_ncu_full_step512_summary.txt", "w").write(
+        "# ncu --set full --clock-control none --import-source on, one RK substep of bench.py at 512^3 (12 launches)\n"
+        "# GB_rd/GB_wr = dram__bytes_read.sum / dram__bytes_write.sum per launch; fp64% = sm__pipe_fp64_cycles_active; st_* = warp stall reasons per issue\n" + summ)
+    # 2. traffic table
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    r = list(csv.reader(out.splitlines())); h, u = r[0], r[1]
+    def gb(row, name):
+        i = h.index(name); return float(row[i].replace(",", "")) / {"byte": 1e9, "Kbyte": 1e6, "Mbyte": 1e3, "Gbyte": 1.}[u[i]]
+    t = {}
+    for row in r[2:]:
+        kn = row[h.index("Kernel Name")]
+        v = round(gb(row, "dram__bytes_read.sum") + gb(row, "dram__bytes_write.sum"), 3)
+        key = None
+        if "pres2_out_rk_kernel" in kn: key = "pres2_out_rk_kernel"
+        elif "rk_kernel" in kn: key = "rk_kernel"
+        elif "evisc_kernel" in kn: key = "evisc_kernel"
+        elif "smag2_diff_uvw_tile_kernel" in kn: key = "advec2_smag2_uvw_kernel"
+        elif "smag2_scalar_tile_kernel" in kn: key = "advec2_smag2_c_kernel"
+        elif "pres2_in_kernel" in kn: key = "pres2_in_kernel"
+        elif "pres2_tdma_kernel" in kn: key = "pres2_tdma_kernel"
+        elif "fft_pow2_kernel<(int)-1, 0" in kn: key = "fft_fwd_x"
+        elif "fft_pow2_kernel<(int)-1, 1" in kn: key = "fft_fwd_y"
+        elif "fft_pow2_kernel<1, 1" in kn: key = "fft_bwd_y"
+        elif "fft_pow2_kernel<1, 0" in kn: key = "fft_bwd_x"
+        if key: t[key] = v
+    json.dump({"n": 512, "source": f"profiles/{tag}_ncu_full_step512_summary.txt (ncu --set full --clock-control none, one RK substep of bench.py at 512^3)",
+               "gb_per_launch": t}, open("profiles/r01_traffic.json", "w"), indent=1)
 # 3. launch list + summary
 src = f"gpurun_out/launches_{tag}.csv"
 open(f"profiles/{tag}_ncu_launches_bench512.csv", "w").write(open(src).read())
