@@ -10,6 +10,9 @@
 // The horizontal and the vertical contributions are added to the tendency in two steps like the
 // reference's two passes.
 #include <cfloat>
+#ifndef MHH_ADVEC2I5_UNROLL_N
+#define MHH_ADVEC2I5_UNROLL_N 2
+#endif
 
 #include "ctx.h"
 
@@ -100,6 +103,7 @@ namespace
         if (COMP == 2) vflux<2>(a, w, ijk - kk, k0 - 1, sa, kk, gd, Fb, Fab);
         else           vflux<COMP>(a, w, ijk, k0, sa, kk, gd, Fb, Fab);
 
+        MHH_PRAGMA_UNROLL(MHH_ADVEC2I5_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             double t = at[ijk];
@@ -183,6 +187,7 @@ namespace
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         int ijk = i + j * jj + k0 * kk;
         double Fb = vflux_lim(s, w, ijk, k0, kk, gd);
+        MHH_PRAGMA_UNROLL(MHH_ADVEC2I5_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const double Ft = vflux_lim(s, w, ijk + kk, k + 1, kk, gd);

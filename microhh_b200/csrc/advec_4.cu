@@ -6,6 +6,9 @@
 // the reference's left-to-right summation order and the x, y, z contributions are subtracted from the
 // tendency one after the other, as the reference does, so results agree to rounding with the CPU build.
 #include "ctx.h"
+#ifndef MHH_ADVEC4_UNROLL_N
+#define MHH_ADVEC4_UNROLL_N 1
+#endif
 
 namespace mhh
 {
@@ -79,6 +82,7 @@ namespace
             f2 = face(k0 + 1, ci0 * qa + ci1 * qb + ci2 * qc + ci3 * qd);
         }
 
+        MHH_PRAGMA_UNROLL(MHH_ADVEC4_UNROLL_N)
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * jj + k * kk;

@@ -1,5 +1,8 @@
 // Constant-viscosity 2nd-order diffusion (src/diff_2.cxx:39-87), u/v/w fused in one launch.
 #include "ctx.h"
+#ifndef MHH_DIFF2_UNROLL_N
+#define MHH_DIFF2_UNROLL_N 1
+#endif
 
 namespace mhh
 {
@@ -31,6 +34,7 @@ namespace
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxidxi = 1 / (gd.dx * gd.dx), dyidyi = 1 / (gd.dy * gd.dy);
 
+        MHH_PRAGMA_UNROLL(MHH_DIFF2_UNROLL_N)
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * jj + k * kk;
@@ -55,6 +59,7 @@ namespace
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxidxi = 1 / (gd.dx * gd.dx), dyidyi = 1 / (gd.dy * gd.dy);
+        MHH_PRAGMA_UNROLL(MHH_DIFF2_UNROLL_N)
         for (int k = k0; k < k1; ++k)
         {
             const int ijk = i + j * jj + k * kk;

@@ -10,6 +10,23 @@
 
 #include "ctx.h"
 
+// k levels unrolled in the momentum kernel's march (the register queues rotate by renaming instead of by moves)
+#ifndef MHH_UVW_UNROLL_N
+#define MHH_UVW_UNROLL_N 2
+#endif
+#define MHH_UVW_UNROLL MHH_PRAGMA_UNROLL(MHH_UVW_UNROLL_N)
+// 1: the momentum kernel re-reads the seven level k-1 neighbour values of the w stencils from the plane ring (held one level
+// longer) instead of carrying them in registers
+#ifndef MHH_UVW_REREAD_B
+#define MHH_UVW_REREAD_B 0
+#endif
+#ifndef MHH_EVISC_UNROLL_N
+#define MHH_EVISC_UNROLL_N 3
+#endif
+#ifndef MHH_SCALAR_UNROLL_N
+#define MHH_SCALAR_UNROLL_N 6
+#endif
+
 namespace mhh
 {
 namespace
@@ -138,6 +155,7 @@ constexpr int UVW_SLOTS = 6;
             yz_n = 0.125 * pow2((v_n - v_nb) * dzhi_k + (w_n - w_c) * dyi);
         }
 
+        MHH_PRAGMA_UNROLL(MHH_EVISC_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
@@ -285,7 +303,9 @@ constexpr int UVW_SLOTS = 6;
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = UVW_SLOTS, NT = TX * TY;
         extern __shared__ __align__(16) double sm[];     // [slot][evisc,u,v,w][tile plane]: NS * 4 * PS doubles (dynamic)
-        __shared__ double met[8][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi, threfh, g/threfh at k0-1 .. k1
+        // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi, threfh, g/threfh, dzi/4, dzhi/4, 2 dzhi at k0-1 .. k1 (one array per
+        // metric: 16-byte records read as pairs cost this kernel registers it does not have, 3.20 -> 3.74 ms)
+        __shared__ double met[11][KCHUNK + 2];
         __shared__ unsigned long long full[NS], empty[NS];
 
         const int tid = threadIdx.y * TX + threadIdx.x;
@@ -297,6 +317,11 @@ constexpr int UVW_SLOTS = 6;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        // Scalings by powers of two commute with every rounding (no underflow at these magnitudes), so the reference's
+        // interp2(a,b) = 0.5 (a+b) is carried as the plain sum a+b and the factors are collected in the metric:
+        // (0.5 s1)(0.5 s2) - (0.5 s3)(0.5 s4) = 0.25 (s1 s2 - s3 s4), and (0.25 X) dxi = X (0.25 dxi), bit for bit.
+        // Likewise (X * 2.) * dxi = X * (2 dxi).
+        const double qdxi = 0.25 * dxi, qdyi = 0.25 * dyi, dxi2 = 2. * dxi, dyi2 = 2. * dyi;
 
         Map map;
         map.init(i0, j0, gd.icells, gd.jcells, tid);
@@ -330,6 +355,7 @@ constexpr int UVW_SLOTS = 6;
             met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
             met[3][tid] = gd.rhorefh_i[k]; met[4][tid] = gd.dzi[k]; met[5][tid] = gd.dzhi[k];
             if (BUOY) { met[6][tid] = threfh[k]; met[7][tid] = g_threfh[k]; }
+            met[8][tid] = 0.25 * gd.dzi[k]; met[9][tid] = 0.25 * gd.dzhi[k]; met[10][tid] = 2. * gd.dzhi[k];
         }
 
         // tile-plane offsets of the centre and its neighbours
@@ -337,39 +363,45 @@ constexpr int UVW_SLOTS = 6;
         const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W, cwn = c + W - 1, cws = c - W - 1, ces = c - W + 1;
 
         __syncthreads();                                 // met[] is complete
-        double e_b, e_c, e_wb, e_w, e_sb, e_s, e_eb, e_nb, u_b, u_c, u_eb, v_b, v_c, v_nb, w_b, w_c, w_w, w_s;
+        // Column state carried up the k march.  Besides the centre values of levels k-1 (…_b) and k (…_c):
+        //   f?_b, a?_b : diffusive / advective flux through the lower face (= the upper-face flux of the level below);
+        //   gu_b, gv_b : the vertical shear at the lower west / south edge, (u_c-u_b) dzhi + (w_c-w_w) dxi.  Diff u/v evaluate
+        //                it as the upper-edge shear of the level below and diff_w reads the same two products in the other
+        //                order (a + b = b + a), so it is evaluated once;
+        //   su_b, sv_b, sw_w, sw_s : the sums u_b+u_c, v_b+v_c, w_w+w_c, w_s+w_c of the advecting/advected interpolations,
+        //                which were u_c+u_t, v_c+v_t, w_wt+w_t, w_st+w_t one level below.
+        double e_b, e_c, e_wb, e_w, e_sb, e_s, e_eb, e_nb, u_c, u_eb, v_c, v_nb, w_c;
+        double fu_b, fv_b, fw_b, gu_b, gv_b, au_b = 0., av_b = 0., aw_b = 0., su_b = 0., sv_b = 0., sw_w = 0., sw_s = 0.;
         {
             const double* B = plane(0); const double* C = plane(1);
             e_b = B[c]; e_wb = B[cw]; e_sb = B[cs]; e_eb = B[ce]; e_nb = B[cn];
             e_c = C[c]; e_w = C[cw]; e_s = C[cs];
-            u_b = B[PS + c]; u_eb = B[PS + ce]; u_c = C[PS + c];
-            v_b = B[2 * PS + c]; v_nb = B[2 * PS + cn]; v_c = C[2 * PS + c];
-            w_b = B[3 * PS + c]; w_c = C[3 * PS + c]; w_w = C[3 * PS + cw]; w_s = C[3 * PS + cs];
-        }
-        mbar_arrive(&empty[0]);                          // plane k0-1 is not read again
-        // Vertical fluxes through the lower face of the first level.  In the loop the flux through the upper face of level k
-        // IS the flux through the lower face of level k+1 (same operands, same operations), so each is evaluated once and
-        // carried: 43 of the 308 FP64 instructions per point and level.
-        double fu_b, fv_b, fw_b, au_b = 0., av_b = 0., aw_b = 0.;
-        {
+            const double u_b = B[PS + c]; u_eb = B[PS + ce]; u_c = C[PS + c];
+            const double v_b = B[2 * PS + c]; v_nb = B[2 * PS + cn]; v_c = C[2 * PS + c];
+            const double w_b = B[3 * PS + c]; w_c = C[3 * PS + c];
+            const double w_w = C[3 * PS + cw], w_s = C[3 * PS + cs];
             const double rhoh_b = met[1][1], dzhi_b = met[5][1];
-            fu_b = rhoh_b * (0.25 * (e_wb + e_b + e_w + e_c) + visc) * ((u_c - u_b) * dzhi_b + (w_c - w_w) * dxi);
-            fv_b = rhoh_b * (0.25 * (e_sb + e_b + e_s + e_c) + visc) * ((v_c - v_b) * dzhi_b + (w_c - w_s) * dyi);
+            gu_b = (u_c - u_b) * dzhi_b + (w_c - w_w) * dxi;
+            gv_b = (v_c - v_b) * dzhi_b + (w_c - w_s) * dyi;
+            fu_b = rhoh_b * (0.25 * (e_wb + e_b + e_w + e_c) + visc) * gu_b;
+            fv_b = rhoh_b * (0.25 * (e_sb + e_b + e_s + e_c) + visc) * gv_b;
             fw_b = met[0][0] * (e_b + visc) * (w_c - w_b) * met[4][0];
             if (ADVEC)
             {
-                using fd::interp2;
-                au_b = rhoh_b * interp2(w_w, w_c) * interp2(u_b, u_c);
-                av_b = rhoh_b * interp2(w_s, w_c) * interp2(v_b, v_c);
-                aw_b = met[0][0] * interp2(w_b, w_c) * interp2(w_b, w_c);
+                su_b = u_b + u_c; sv_b = v_b + v_c; sw_w = w_w + w_c; sw_s = w_s + w_c;
+                au_b = rhoh_b * sw_w * su_b;             // 4 x the reference's flux: see qdxi above
+                av_b = rhoh_b * sw_s * sv_b;
+                aw_b = met[0][0] * (w_b + w_c) * (w_b + w_c);
             }
         }
+        if (!MHH_UVW_REREAD_B) mbar_arrive(&empty[0]);   // plane k0-1 is not read again
 
         int ijk = ij + k0 * kk;
         double ut_c = 0., vt_c = 0., wt_c = 0.;
         if (live) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
         double th_b = 0., th_c = 0., th_n = 0.;          // theta column (centre only), one level ahead from global memory
         if (BUOY) { th_b = th[ijk - kk]; th_c = th[ijk]; th_n = th[ijk + kk]; }
+        MHH_UVW_UNROLL
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const int it = k - k0;                       // level k: planes it+1 (this level) and it+2 (the level above)
@@ -397,42 +429,56 @@ constexpr int UVW_SLOTS = 6;
             const double v_wn = C[2 * PS + cwn];
             const double w_t = T[3 * PS + c], w_wt = T[3 * PS + cw], w_st = T[3 * PS + cs];
             const double w_e = C[3 * PS + ce], w_n = C[3 * PS + cn];
-            mbar_arrive(&empty[(it + 1) % NS]);   // this thread's last read of plane k
+            if (MHH_UVW_REREAD_B)
+            {
+                const double* B = sm + (it % NS) * 4 * PS;       // plane k-1
+                e_b = B[c]; e_wb = B[cw]; e_sb = B[cs]; e_eb = B[ce]; e_nb = B[cn];
+                u_eb = B[PS + ce]; v_nb = B[2 * PS + cn];
+                mbar_arrive(&empty[it % NS]);         // this thread's last read of plane k-1
+            }
+            else
+                mbar_arrive(&empty[(it + 1) % NS]);   // this thread's last read of plane k
 
             if (BUOY && k > gd.kstart)      // calc_buoyancy_tend_2nd, src/thermo_dry.cxx:43-62
                 wt_c = wt_c + met[7][km] * (fd::interp2(th_b, th_c) - met[6][km]);
             if (ADVEC)
             {
-                using fd::interp2;
+                const double qdzi = met[8][km], qdzhi_b = met[9][km];
+                // sums of the interpolation pairs (interp2 without its 0.5)
+                const double su_t = u_c + u_t, sv_t = v_c + v_t, sw_wt = w_wt + w_t, sw_st = w_st + w_t, sw_t = w_c + w_t;
+                const double su_e = u_c + u_e, su_w = u_w + u_c, su_n = u_c + u_n, su_s = u_s + u_c;
+                const double sv_e = v_c + v_e, sv_w = v_w + v_c, sv_n = v_c + v_n, sv_s = v_s + v_c;
                 // fluxes through the upper faces (the lower-face ones were the upper-face ones of the level below)
-                const double au_t = rhoh_t * interp2(w_wt, w_t) * interp2(u_c, u_t);
-                const double av_t = rhoh_t * interp2(w_st, w_t) * interp2(v_c, v_t);
-                const double aw_t = rho * interp2(w_c, w_t) * interp2(w_c, w_t);
+                const double au_t = rhoh_t * sw_wt * su_t;
+                const double av_t = rhoh_t * sw_st * sv_t;
+                const double aw_t = rho * sw_t * sw_t;
                 // advec_u, src/advec_2.cxx:98-109
                 ut_c = ut_c +
-                    ( - ( interp2(u_c, u_e) * interp2(u_c, u_e)
-                        - interp2(u_w, u_c) * interp2(u_w, u_c) ) * dxi
-                      - ( interp2(v_wn, v_n) * interp2(u_c, u_n)
-                        - interp2(v_w, v_c) * interp2(u_s, u_c) ) * dyi
-                      - div_by( au_t - au_b, rho, rho_i ) * dzi );
+                    ( - ( su_e * su_e
+                        - su_w * su_w ) * qdxi
+                      - ( (v_wn + v_n) * su_n
+                        - sv_w * su_s ) * qdyi
+                      - div_by( au_t - au_b, rho, rho_i ) * qdzi );
                 // advec_v, src/advec_2.cxx:129-140
                 vt_c = vt_c +
-                    ( - ( interp2(u_es, u_e) * interp2(v_c, v_e)
-                        - interp2(u_s, u_c) * interp2(v_w, v_c) ) * dxi
-                      - ( interp2(v_c, v_n) * interp2(v_c, v_n)
-                        - interp2(v_s, v_c) * interp2(v_s, v_c) ) * dyi
-                      - div_by( av_t - av_b, rho, rho_i ) * dzi );
+                    ( - ( (u_es + u_e) * sv_e
+                        - su_s * sv_w ) * qdxi
+                      - ( sv_n * sv_n
+                        - sv_s * sv_s ) * qdyi
+                      - div_by( av_t - av_b, rho, rho_i ) * qdzi );
                 // advec_w, src/advec_2.cxx:160-171 (k from kstart+1)
                 if (k > gd.kstart)
                     wt_c = wt_c +
-                        ( - ( interp2(u_eb, u_e) * interp2(w_c, w_e)
-                            - interp2(u_b, u_c) * interp2(w_w, w_c) ) * dxi
-                          - ( interp2(v_nb, v_n) * interp2(w_c, w_n)
-                            - interp2(v_b, v_c) * interp2(w_s, w_c) ) * dyi
-                          - div_by( aw_t - aw_b, rhoh_b, met[3][km] ) * dzhi_b );
+                        ( - ( (u_eb + u_e) * (w_c + w_e)
+                            - su_b * sw_w ) * qdxi
+                          - ( (v_nb + v_n) * (w_c + w_n)
+                            - sv_b * sw_s ) * qdyi
+                          - div_by( aw_t - aw_b, rhoh_b, met[3][km] ) * qdzhi_b );
                 au_b = au_t; av_b = av_t; aw_b = aw_t;
+                su_b = su_t; sv_b = sv_t; sw_w = sw_wt; sw_s = sw_st;
             }
             // ---- u: src/diff_smag2.cxx:395-467
+            double gu_t, gv_t;
             {
                 const double evisce = e_c + visc;
                 const double eviscw = e_w + visc;
@@ -442,11 +488,11 @@ constexpr int UVW_SLOTS = 6;
 
                 const double hor =
                     + ( evisce * (u_e - u_c) * dxi
-                      - eviscw * (u_c - u_w) * dxi ) * 2. * dxi
+                      - eviscw * (u_c - u_w) * dxi ) * dxi2
                     + ( eviscn * ((u_n - u_c) * dyi + (v_n - v_wn) * dxi)
                       - eviscs * ((u_c - u_s) * dyi + (v_c - v_w) * dxi) ) * dyi;
-                const double grad_t = (u_t - u_c) * dzhi_t + (w_t - w_wt) * dxi;
-                const double fu_t = rhoh_t * evisct * grad_t;
+                gu_t = (u_t - u_c) * dzhi_t + (w_t - w_wt) * dxi;
+                const double fu_t = rhoh_t * evisct * gu_t;
                 double ver;
                 if (bot)      ver = div_by( fu_t + rhoh_b * rare_load(ufluxbot, ij), rho, rho_i ) * dzi;
                 else if (top) ver = div_by( -rhoh_t * rare_load(ufluxtop, ij) - fu_b, rho, rho_i ) * dzi;
@@ -466,9 +512,9 @@ constexpr int UVW_SLOTS = 6;
                     + ( evisce * ((v_e - v_c) * dxi + (u_e - u_es) * dyi)
                       - eviscw * ((v_c - v_w) * dxi + (u_c - u_s) * dyi) ) * dxi
                     + ( eviscn * (v_n - v_c) * dyi
-                      - eviscs * (v_c - v_s) * dyi ) * 2. * dyi;
-                const double grad_t = (v_t - v_c) * dzhi_t + (w_t - w_st) * dyi;
-                const double fv_t = rhoh_t * evisct * grad_t;
+                      - eviscs * (v_c - v_s) * dyi ) * dyi2;
+                gv_t = (v_t - v_c) * dzhi_t + (w_t - w_st) * dyi;
+                const double fv_t = rhoh_t * evisct * gv_t;
                 double ver;
                 if (bot)      ver = div_by( fv_t + rhoh_b * rare_load(vfluxbot, ij), rho, rho_i ) * dzi;
                 else if (top) ver = div_by( -rhoh_t * rare_load(vfluxtop, ij) - fv_b, rho, rho_i ) * dzi;
@@ -484,20 +530,25 @@ constexpr int UVW_SLOTS = 6;
                 const double eviscw = 0.25 * (e_wb + e_w + e_b + e_c) + visc;
                 const double eviscn = 0.25 * (e_b + e_c + e_nb + e_n) + visc;
                 const double eviscs = 0.25 * (e_sb + e_s + e_b + e_c) + visc;
+                // west / south edge shear: (w_c - w_w) dxi + (u_c - u_b) dzhi_b = gu_b, (w_c - w_s) dyi + (v_c - v_b) dzhi_b = gv_b
                 const double wd =
                     + ( evisce * ((w_e - w_c) * dxi + (u_e - u_eb) * dzhi_b)
-                      - eviscw * ((w_c - w_w) * dxi + (u_c - u_b) * dzhi_b) ) * dxi
+                      - eviscw * gu_b ) * dxi
                     + ( eviscn * ((w_n - w_c) * dyi + (v_n - v_nb) * dzhi_b)
-                      - eviscs * ((w_c - w_s) * dyi + (v_c - v_b) * dzhi_b) ) * dyi
-                    + div_by( fw_t - fw_b, rhoh_b, met[3][km] ) * 2. * dzhi_b;
+                      - eviscs * gv_b ) * dyi
+                    + div_by( fw_t - fw_b, rhoh_b, met[3][km] ) * met[10][km];
                 if (live) wt[ijk] = wt_c + wd;
             }
-            fw_b = fw_t;
+            fw_b = fw_t; gu_b = gu_t; gv_b = gv_t;
             if (BUOY) { th_b = th_c; th_c = th_t; }
-            e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
-            u_b = u_c; u_c = u_t; u_eb = u_e;
-            v_b = v_c; v_c = v_t; v_nb = v_n;
-            w_c = w_t; w_w = w_wt; w_s = w_st;
+            if (MHH_UVW_REREAD_B) { e_c = e_t; e_w = e_wt; e_s = e_st; u_c = u_t; v_c = v_t; }
+            else
+            {
+                e_b = e_c; e_c = e_t; e_wb = e_w; e_w = e_wt; e_sb = e_s; e_s = e_st; e_eb = e_e; e_nb = e_n;
+                u_c = u_t; u_eb = u_e;
+                v_c = v_t; v_nb = v_n;
+            }
+            w_c = w_t;
             ut_c = ut_n; vt_c = vt_n; wt_c = wt_n;
         }
     }
@@ -533,7 +584,11 @@ constexpr int UVW_SLOTS = 6;
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4, NF = ADVEC ? 4 : 2;
         __shared__ double sm[NS][NF][PS];                // [slot][a, evisc(, u, v)][tile plane]
-        __shared__ double met[5][KCHUNK + 2];            // rhoref, rhorefh, 1/rhoref, dzi, dzhi at k0-1 .. k1
+        // per-level metric records at k0-1 .. k1, read as 16-byte pairs: {rhoref, 1/rhoref} {dzi, dzi/2} {rhorefh, dzhi}
+        constexpr int MR = 6;
+        __shared__ __align__(16) double met[(KCHUNK + 2) * MR];
+        auto met2 = [&](const int row, const int pair) -> double2
+        { return *reinterpret_cast<const double2*>(&met[row * MR + 2 * pair]); };
 
         const int tid = threadIdx.y * TX + threadIdx.x;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
@@ -546,6 +601,9 @@ constexpr int UVW_SLOTS = 6;
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
         const double tPr_i = 1. / tPr;
+        // Powers of two commute with every rounding: (0.5 s) / tPr = s / (2 tPr) through the same reciprocal sequence, and
+        // u (0.5 s) dxi = (u s) (0.5 dxi), bit for bit — the interp2 halvings are collected in the constants.
+        const double tPr2 = 2. * tPr, tPr_hi = 0.5 * tPr_i, hdxi = 0.5 * dxi, hdyi = 0.5 * dyi;
 
         Map map;
         map.init(i0, j0, gd.icells, gd.jcells, tid);
@@ -564,8 +622,9 @@ constexpr int UVW_SLOTS = 6;
         if (tid < KCHUNK + 2)
         {
             const int k = min(k0 - 1 + tid, gd.kcells - 1);
-            met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
-            met[3][tid] = gd.dzi[k]; met[4][tid] = gd.dzhi[k];
+            double* m = met + tid * MR;
+            m[0] = gd.rhoref[k]; m[1] = gd.rhoref_i[k]; m[2] = gd.dzi[k]; m[3] = 0.5 * gd.dzi[k];
+            m[4] = gd.rhorefh[k]; m[5] = gd.dzhi[k];
         }
 
         const int c = (threadIdx.y + 1) * W + threadIdx.x + 1;
@@ -585,10 +644,11 @@ constexpr int UVW_SLOTS = 6;
         double fd_b, fa_b = 0.;
         {
             const double a_b = sm[0][0][c], e_b = sm[0][1][c];
-            fd_b = met[1][1] * (div_by(0.5 * (e_b + e_c), tPr, tPr_i) + visc) * (a_c - a_b) * met[4][1];
-            if (ADVEC) fa_b = met[1][1] * w_c * fd::interp2(a_b, a_c);
+            fd_b = met[MR + 4] * (div_by(e_b + e_c, tPr2, tPr_hi) + visc) * (a_c - a_b) * met[MR + 5];
+            if (ADVEC) fa_b = met[MR + 4] * w_c * (a_b + a_c);     // 2 x the reference's flux
         }
 
+        MHH_PRAGMA_UNROLL(MHH_SCALAR_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
@@ -602,8 +662,8 @@ constexpr int UVW_SLOTS = 6;
             const double* C = sm[(k - k0 + 1) & (NS - 1)][0];
             const double* T = sm[(k - k0 + 2) & (NS - 1)][0];
             const int km = k - k0 + 1;                   // row of level k in met[]
-            const double rho = met[0][km], rho_i = met[2][km], rhoh_t = met[1][km + 1], rhoh_b = met[1][km];
-            const double dzi = met[3][km], dzhi_t = met[4][km + 1];
+            const double2 m_c = met2(km, 0), m_z = met2(km, 1), m_ht = met2(km + 1, 2);
+            const double rho = m_c.x, rho_i = m_c.y, dzi = m_z.x, rhoh_t = m_ht.x, dzhi_t = m_ht.y, rhoh_b = met[km * MR + 4];
             const bool bot = SURF && (k == gd.kstart);
             const bool top = SURF && (k == gd.kend - 1);
 
@@ -612,24 +672,23 @@ constexpr int UVW_SLOTS = 6;
 
             if (ADVEC)
             {
-                using fd::interp2;
                 const double u_c = C[2 * PS + c], u_e = C[2 * PS + ce], v_c = C[3 * PS + c], v_n = C[3 * PS + cn];
-                const double fa_t = rhoh_t * w_t * interp2(a_c, a_t);
+                const double fa_t = rhoh_t * w_t * (a_c + a_t);
                 // advec_s, src/advec_2.cxx:191-202
                 at_c = at_c +
-                    ( - ( u_e * interp2(a_c, a_e)
-                        - u_c * interp2(a_w, a_c) ) * dxi
-                      - ( v_n * interp2(a_c, a_n)
-                        - v_c * interp2(a_s, a_c) ) * dyi
-                      - div_by( fa_t - fa_b, rho, rho_i ) * dzi );
+                    ( - ( u_e * (a_c + a_e)
+                        - u_c * (a_w + a_c) ) * hdxi
+                      - ( v_n * (a_c + a_n)
+                        - v_c * (a_s + a_c) ) * hdyi
+                      - div_by( fa_t - fa_b, rho, rho_i ) * m_z.y );
                 fa_b = fa_t;
             }
 
-            const double evisce = div_by(0.5 * (e_c + e_e), tPr, tPr_i) + visc;
-            const double eviscw = div_by(0.5 * (e_w + e_c), tPr, tPr_i) + visc;
-            const double eviscn = div_by(0.5 * (e_c + e_n), tPr, tPr_i) + visc;
-            const double eviscs = div_by(0.5 * (e_s + e_c), tPr, tPr_i) + visc;
-            const double evisct = div_by(0.5 * (e_c + e_t), tPr, tPr_i) + visc;
+            const double evisce = div_by(e_c + e_e, tPr2, tPr_hi) + visc;
+            const double eviscw = div_by(e_w + e_c, tPr2, tPr_hi) + visc;
+            const double eviscn = div_by(e_c + e_n, tPr2, tPr_hi) + visc;
+            const double eviscs = div_by(e_s + e_c, tPr2, tPr_hi) + visc;
+            const double evisct = div_by(e_c + e_t, tPr2, tPr_hi) + visc;
 
             const double hor =
                 + ( evisce * (a_e - a_c) - eviscw * (a_c - a_w) ) * dxidxi

@@ -24,6 +24,10 @@
 #define MHH_TILE_KCHUNK 64
 #endif
 
+// `#pragma unroll n` with n a macro: the k marches rotate their register queues by renaming instead of by moves
+#define MHH_PRAGMA_STR(x) #x
+#define MHH_PRAGMA_UNROLL(n) _Pragma(MHH_PRAGMA_STR(unroll n))
+
 namespace mhh
 {
 

@@ -9,6 +9,12 @@
 //             ghost-celled p (replaces the copy loop :340-348)
 //   output  : bottom Neumann ghost row, cyclic halos, ut/vt/wt -= grad p                 (:352-387)
 #include <cmath>
+#ifndef MHH_PRES_OUT_UNROLL_N
+#define MHH_PRES_OUT_UNROLL_N 1
+#endif
+#ifndef MHH_PRES_IN_UNROLL_N
+#define MHH_PRES_IN_UNROLL_N 1
+#endif
 
 #include "ctx.h"
 #include "fft.h"
@@ -38,6 +44,7 @@ namespace
 
         int ijk = i + gd.igc + (j + gd.jgc) * jj + (k0 + gd.kgc) * kk;
         double wflux_b = wt[ijk] + w[ijk] * dti;
+        MHH_PRAGMA_UNROLL(MHH_PRES_IN_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const int ijkp = i + j * jjp + k * kkp;
@@ -175,6 +182,7 @@ namespace
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         int ijk = i + j * jj + k0 * kk;
         double p_b = p[ijk - kk];
+        MHH_PRAGMA_UNROLL(MHH_PRES_OUT_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const double p_c = p[ijk];

@@ -13,6 +13,12 @@
 // registers.  All rows use the reference's general elimination formulas; on the rows where the reference
 // drops terms the dropped operands are exact zeros, so the results are the same to the last bit.
 #include <cmath>
+#ifndef MHH_PRES_OUT_UNROLL_N
+#define MHH_PRES_OUT_UNROLL_N 1
+#endif
+#ifndef MHH_PRES_IN_UNROLL_N
+#define MHH_PRES_IN_UNROLL_N 2
+#endif
 
 #include "ctx.h"
 #include "fft.h"
@@ -63,6 +69,7 @@ namespace
         double f0 = wt[ijk - kk] + w[ijk - kk] * dti;
         double f1 = wt[ijk] + w[ijk] * dti;
         double f2 = wt[ijk + kk] + w[ijk + kk] * dti;
+        MHH_PRAGMA_UNROLL(MHH_PRES_IN_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const double f3 = wt[ijk + 2 * kk] + w[ijk + 2 * kk] * dti;
@@ -191,6 +198,7 @@ namespace
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         int ijk = i + j * jj + k0 * kk;
         double pm2 = p[ijk - 2 * kk], pm1 = p[ijk - kk], p0 = p[ijk];
+        MHH_PRAGMA_UNROLL(MHH_PRES_OUT_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             const double pp1 = p[ijk + kk];
