@@ -81,7 +81,7 @@ namespace
 
     // One Stockham stage of radix R at sub-transform length ns (log2 = lns): twiddle, butterfly,
     // and scatter of the 8 register values to their output slots in z (this pair's buffer).
-    template<int R, int DIR>
+    template<int R, int DIR, int ZSH = 0>
     __device__ __forceinline__ void stage(double2* v, double2* __restrict__ z, const double2* __restrict__ tw,
                                           const int tf, const int n8, const int lns, const bool first)
     {
@@ -118,13 +118,13 @@ namespace
             const int j0 = ((j >> lns) << lns) * R + k;
             #pragma unroll
             for (int q = 0; q < R; ++q)
-                z[pad(j0 + (q << lns))] = v[b + NB * q];
+                z[pad(j0 + (q << lns)) << ZSH] = v[b + NB * q];
         }
     }
 
     // Runs all stages. On return the transform is in registers in "position order": v[m] is element
     // tf + m*N/8 of the result (the last stage's output slots coincide with the read slots).
-    template<int DIR>
+    template<int DIR, int ZSH = 0>
     __device__ __forceinline__ void run(double2* v, double2* __restrict__ z, const P2Args& A, const int tf)
     {
         const int n8 = A.n >> 3;
@@ -173,12 +173,12 @@ namespace
             {
                 if (s > 0) __syncthreads();      // everyone has read its inputs of this stage
                 const double2* tw = A.tw + A.off[s];
-                if (R == 8) stage<8, DIR>(v, z, tw, tf, n8, lns, s == 0);
-                else if (R == 4) stage<4, DIR>(v, z, tw, tf, n8, lns, s == 0);
-                else stage<2, DIR>(v, z, tw, tf, n8, lns, s == 0);
+                if (R == 8) stage<8, DIR, ZSH>(v, z, tw, tf, n8, lns, s == 0);
+                else if (R == 4) stage<4, DIR, ZSH>(v, z, tw, tf, n8, lns, s == 0);
+                else stage<2, DIR, ZSH>(v, z, tw, tf, n8, lns, s == 0);
                 __syncthreads();
                 #pragma unroll
-                for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8)];
+                for (int m = 0; m < 8; ++m) v[m] = z[pad(tf + m * n8) << ZSH];
             }
             lns += (R == 8) ? 3 : (R == 4 ? 2 : 1);
         }
@@ -395,6 +395,87 @@ namespace
             }
         }
     }
+
+    // Strided (y) passes with the LANES ALONG THE LINES.  Two adjacent lines (i, i+1) are one complex transform whose
+    // elements are 16-byte (double2) words of the array itself, so a thread loads its eight elements straight into
+    // registers and stores its results straight from them; 2^CPL such pairs ride side by side in the CTA (thread =
+    // pair c + 2^CPL * tf), a row of the access is 2^CPL * 16 contiguous bytes, and the Stockham exchanges address
+    // shared memory as [slot][pair]: consecutive lanes hit consecutive 16-byte words.  Against the staged-tile kernel
+    // above this drops both tile passes through shared memory (5 -> 3 round trips forward, 4 -> 2 backward).
+    // Needs: s1 = s1o = 1, n1 = n1o a multiple of 2^(CPL+1), even strides and bases (fft_pow2_lines checks).
+    constexpr int CBLOCK = 512;
+    template<int DIR, int CPL, bool SPLIT>
+    __global__ void __launch_bounds__(CBLOCK, 2)
+    fft_pow2_col_kernel(const double* __restrict__ in, double* __restrict__ out, const P2Args A)
+    {
+        extern __shared__ double2 zbuf[];
+        constexpr int CP = 1 << CPL;
+        const int n = A.n, n8 = n >> 3, nh = n >> 1;
+        const int c = threadIdx.x & (CP - 1);
+        const int tf = threadIdx.x >> CPL;
+        const int l0 = blockIdx.x * (2 * CP);            // first line of this CTA; its 2 CP lines are adjacent in memory
+        const double* src = in + A.base_in + line_addr(l0, A.n1, A.s1, A.s2) + 2 * c;
+        double* dst = out + A.base_out + line_addr(l0, A.n1o, A.s1o, A.s2o) + 2 * c;
+        double2* z = zbuf + c;
+        double2 v[8];
+
+        if (DIR < 0)
+        {
+            #pragma unroll
+            for (int m = 0; m < 8; ++m)
+                v[m] = *reinterpret_cast<const double2*>(src + elem_off<SPLIT>(tf + m * n8, A.sn, A.esh_in, A.eseg_in));
+        }
+        else
+        {
+            // Z_pos = A_pos + i B_pos rebuilt from the two half-complex lines: element np holds the real parts (a, b),
+            // element n - np the imaginary parts; the mirrored word is a second (L1/L2-resident) load
+            #pragma unroll
+            for (int m = 0; m < 8; ++m)
+            {
+                const int pos = tf + m * n8;
+                const int np = pos <= nh ? pos : n - pos;
+                const bool self = (np == 0) || (np == nh);
+                const double sg = pos <= nh ? 1. : -1.;
+                const double2 re = *reinterpret_cast<const double2*>(src + elem_off<SPLIT>(np, A.sn, A.esh_in, A.eseg_in));
+                double2 im = make_double2(0., 0.);
+                if (!self) im = *reinterpret_cast<const double2*>(src + elem_off<SPLIT>(n - np, A.sn, A.esh_in, A.eseg_in));
+                v[m] = make_double2(re.x - sg * im.y, sg * im.x + re.y);
+            }
+        }
+
+        run<DIR, CPL>(v, z, A, tf);
+
+        if (DIR > 0)
+        {
+            #pragma unroll
+            for (int m = 0; m < 8; ++m)
+                *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(tf + m * n8, A.sno, A.esh_out, A.eseg_out))
+                    = make_double2(v[m].x * A.scale, v[m].y * A.scale);
+        }
+        else
+        {
+            // result to natural order in shared memory, then the Hermitian split; (a, b) leave as one 16-byte word
+            if (A.nst > 1) __syncthreads();
+            #pragma unroll
+            for (int m = 0; m < 8; ++m) z[pad(tf + m * n8) << CPL] = v[m];
+            __syncthreads();
+            #pragma unroll
+            for (int m = 0; m < 5; ++m)
+            {
+                if (m == 4 && tf != 0) break;
+                const int k = (m == 4) ? nh : tf + m * n8;
+                const int kn = (k == 0) ? 0 : n - k;
+                const double2 zk = z[pad(k) << CPL], zn = z[pad(kn) << CPL];
+                const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
+                const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
+                *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(k, A.sno, A.esh_out, A.eseg_out))
+                    = make_double2(are * A.scale, bre * A.scale);
+                if (k > 0 && k < nh)
+                    *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(n - k, A.sno, A.esh_out, A.eseg_out))
+                        = make_double2(aim * A.scale, bim * A.scale);
+            }
+        }
+    }
 }  // namespace
 
 bool fft_pow2_supported(int n) { return n >= 8 && n <= 8 * BLOCK && (n & (n - 1)) == 0; }
@@ -439,6 +520,40 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     A.n1o = L.n1o; A.s1o = L.s1o; A.s2o = L.s2o; A.sno = L.sno; A.base_out = L.base_out;
     A.scale = L.scale;
     const bool strided = (L.sn != 1) || (L.sno != 1);
+    const bool split = L.esplit_in > 0 || L.esplit_out > 0;
+    auto lg = [](int v) { int l = 0; while ((1 << l) < v) ++l; return l; };
+    if ((L.esplit_in > 0 && (L.esplit_in & (L.esplit_in - 1))) || (L.esplit_out > 0 && (L.esplit_out & (L.esplit_out - 1))))
+        return MHH_ERR_UNSUPPORTED;
+    A.esh_in = L.esplit_in > 0 ? lg(L.esplit_in) : 31;   A.eseg_in = L.eseg_in;
+    A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
+    // y passes whose lines are adjacent words: the lanes-along-the-lines kernel (n = 256, 512, 1024: 16, 8, 4 pairs per CTA)
+    {
+        static const bool col_off = []() { const char* e = getenv("MHH_FFT_NOCOL"); return e && atoi(e) != 0; }();
+        const int tfn = plan.n / 8;
+        const int cp = tfn > 0 ? CBLOCK / tfn : 0;
+        auto even = [](long v) { return (v & 1L) == 0; };
+        const bool aligned = even(L.s2) && even(L.sn) && even(L.base_in) && even(L.s2o) && even(L.sno) && even(L.base_out)
+                          && even(L.eseg_in) && even(L.eseg_out)
+                          && (reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+        if (!col_off && strided && (cp == 4 || cp == 8 || cp == 16) && L.s1 == 1 && L.s1o == 1 && L.n1 == L.n1o
+            && L.n1 % (2 * cp) == 0 && L.nlines % (2 * cp) == 0 && aligned)
+        {
+            const size_t smem_c = (size_t)(cp * (plan.n + plan.n / 8 + 1)) * sizeof(double2);
+            const int nb = L.nlines / (2 * cp);
+            const char* nm = dir < 0 ? "fft_fwd_y" : "fft_bwd_y";
+            #define P2C_LAUNCH(D, CPL, SP) do { \
+                static bool attr = false; \
+                if (!attr) { cudaFuncSetAttribute(fft_pow2_col_kernel<D, CPL, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); attr = true; } \
+                MHH_LAUNCH(c, nm, (fft_pow2_col_kernel<D, CPL, SP><<<nb, CBLOCK, smem_c, c->stream>>>(in, out, A))); } while (0)
+            #define P2C_DISPATCH(D, SP) do { if (cp == 4) P2C_LAUNCH(D, 2, SP); else if (cp == 8) P2C_LAUNCH(D, 3, SP); else P2C_LAUNCH(D, 4, SP); } while (0)
+            if (dir < 0) { if (split) P2C_DISPATCH(-1, true); else P2C_DISPATCH(-1, false); }
+            else         { if (split) P2C_DISPATCH(1, true);  else P2C_DISPATCH(1, false); }
+            #undef P2C_DISPATCH
+            #undef P2C_LAUNCH
+            MHH_LAUNCH_CHECK();
+            return MHH_OK;
+        }
+    }
     const int npairs = BLOCK / (plan.n / 8);
     // strided (y) passes: several pair groups per CTA (wider rows of the staged tile) while the tile fits the shared-memory
     // budget and the grid still fills the machine; MHH_FFT_NG (test hook) caps the group count
@@ -453,12 +568,6 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     const int lines = 2 * npairs * ng;
     const size_t smem = (size_t)npairs * ng * pair_bytes;
     const int nblocks = (L.nlines + lines - 1) / lines;
-    const bool split = L.esplit_in > 0 || L.esplit_out > 0;
-    auto lg = [](int v) { int l = 0; while ((1 << l) < v) ++l; return l; };
-    if ((L.esplit_in > 0 && (L.esplit_in & (L.esplit_in - 1))) || (L.esplit_out > 0 && (L.esplit_out & (L.esplit_out - 1))))
-        return MHH_ERR_UNSUPPORTED;
-    A.esh_in = L.esplit_in > 0 ? lg(L.esplit_in) : 31;   A.eseg_in = L.eseg_in;
-    A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
     const char* name = dir < 0 ? (strided ? "fft_fwd_y" : "fft_fwd_x") : (strided ? "fft_bwd_y" : "fft_bwd_x");
     #define P2_LAUNCH(D, S, G, SP) do { \
         static bool attr = false; \

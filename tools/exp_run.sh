@@ -1,7 +1,4 @@
 #!/bin/bash
-python -m pytest tests/test_gpu_ops.py tests/test_gpu_les_substep.py -m gpu -x -q 2>&1 | tail -2
-tools/exp1.sh final diff_smag2.cu "" 8
-tools/exp_dns.sh base ""
-tools/exp_dns.sh u2 "-DMHH_ADVEC4_UNROLL_N=2 -DMHH_ADVEC2I5_UNROLL_N=2 -DMHH_PRES_IN_UNROLL_N=2 -DMHH_DIFF2_UNROLL_N=2"
-tools/exp_dns.sh u4 "-DMHH_ADVEC4_UNROLL_N=4 -DMHH_ADVEC2I5_UNROLL_N=4 -DMHH_PRES_IN_UNROLL_N=4 -DMHH_DIFF2_UNROLL_N=4"
-tools/exp_dns.sh u3 "-DMHH_ADVEC4_UNROLL_N=3 -DMHH_ADVEC2I5_UNROLL_N=3 -DMHH_PRES_IN_UNROLL_N=8 -DMHH_DIFF2_UNROLL_N=8"
+python -m pytest tests/test_gpu_fft.py tests/test_gpu_slab.py tests/test_gpu_ops.py tests/test_gpu_les_substep.py tests/test_gpu_schemes.py -m gpu -x -q 2>&1 | tail -3
+tools/gpu_quick.sh colfft 2>/dev/null | head -14
+MHH_FFT_NOCOL=1 tools/gpu_quick.sh nocol 2>/dev/null | head -14 | grep "fft\|^4"
