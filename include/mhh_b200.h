@@ -120,6 +120,17 @@ int mhh_smag2_exec_viscosity_dry(mhh_ctx* ctx, int surface_model,
                                  const double* th, const double* dudz, const double* dvdz,
                                  const double* dbdz, const double* z0m,
                                  double cs, double tPr, double visc, double* evisc);
+/* mhh_smag2_exec_viscosity_dry plus the two maxima Model::set_time_step (src/model.cxx:731-751) asks for right after
+ * exec_viscosity of the first substep (src/model.cxx:354-357), taken in the same pass over u,v,w:
+ *  cfl_over_dt = Advec_2::get_cfl's maximum before the `* dt` (calc_cfl, src/advec_2.cxx:51-78),
+ *  dnmul       = Diff_smag2's calc_dnmul of the evisc just written (src/diff_smag2.cxx:712-735).
+ * Equal to mhh_advec_cfl(scheme 2) / dt and mhh_smag2_dnmul run afterwards (same expressions, exact maxima). */
+int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* ctx, int surface_model,
+                                        const double* u, const double* v, const double* w,
+                                        const double* th, const double* dudz, const double* dvdz,
+                                        const double* dbdz, const double* z0m,
+                                        double cs, double tPr, double visc, double* evisc,
+                                        double* cfl_over_dt, double* dnmul);
 /* Diff_smag2::exec — src/diff_smag2.cxx:939 (diff_u :370, diff_v :472, diff_w :575, diff_c :620). */
 int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
                    const double* u, const double* v, const double* w, const double* evisc,

@@ -30,7 +30,7 @@ int diff4_exec_scalars(Ctx*, int, const double* const*, double* const*, const do
 int diff2_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
 int diff4_exec(Ctx*, const double*, const double*, const double*, double*, double*, double*, double, int, const double* const*, double* const*, const double*);
 int smag2_exec_viscosity(Ctx*, int, const double*, const double*, const double*, const double*, const double*, const double*,
-                         const double*, const double*, double, double, double, double*, int);
+                         const double*, const double*, double, double, double, double*, int, unsigned long long* = nullptr);
 int smag2_exec(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
                const double*, const double*, const double*, const double*, double, int, const double* const*, double* const*,
                const double* const*, const double* const*, const double*, double);
@@ -447,6 +447,26 @@ int mhh_smag2_exec_viscosity_dry(mhh_ctx* c, int surface_model, const double* u,
     CTX_CHECK(c);
     if (!th) { c->last_error = "th is required"; return MHH_ERR_ARG; }
     return smag2_exec_viscosity(c, surface_model, u, v, w, th, dudz, dvdz, dbdz, z0m, cs, tPr, visc, evisc, 2);
+}
+
+// exec_viscosity of the first substep together with the two maxima Model::set_time_step asks for right after it
+// (Advec_2::get_time_limit and Diff_smag2::get_time_limit, src/model.cxx:354-357,731-751): the CFL sum and dnmul are
+// evaluated in the evisc pass, which already holds u,v,w and the new evisc, instead of two more sweeps over the fields.
+int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,
+                                        const double* th, const double* dudz, const double* dvdz, const double* dbdz,
+                                        const double* z0m, double cs, double tPr, double visc, double* evisc,
+                                        double* cfl_over_dt, double* dnmul)
+{
+    CTX_CHECK(c);
+    if (!th || !cfl_over_dt || !dnmul) { c->last_error = "th and the two outputs are required"; return MHH_ERR_ARG; }
+    unsigned long long* slots = c->max_bits_d + 4;
+    if (int e = smag2_exec_viscosity(c, surface_model, u, v, w, th, dudz, dvdz, dbdz, z0m, cs, tPr, visc, evisc, 2, slots)) return e;
+    unsigned long long* h = reinterpret_cast<unsigned long long*>(c->host_pinned);
+    MHH_CUDA_CHECK(cudaMemcpyAsync(h, slots, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    std::memcpy(cfl_over_dt, h, sizeof(double));
+    std::memcpy(dnmul, h + 1, sizeof(double));
+    return MHH_OK;
 }
 
 int mhh_smag2_strain2(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w,

@@ -67,13 +67,17 @@ constexpr int UVW_SLOTS = 6;
     // of 31 (ncu r01: L1 68 %, DRAM 30 %).
     // Shared-memory tiles: the (TX+2) x (TY+2) planes of u,v,w sit in a ring of four slots filled by cp.async two levels
     // ahead (see TileMap); the columns u_c, u_e, v_c, v_n (levels k-1, k) and the w star (level k) stay in registers.
-    template<bool SURF, int MODE, int TX, int TY>
+    // LIM: the time-step limits of the step ride along (the reference evaluates them right after exec_viscosity,
+    // src/model.cxx:354-357): lim[0] = max of calc_cfl's sum (src/advec_2.cxx:51-78, before the * dt), lim[1] = max of
+    // calc_dnmul (src/diff_smag2.cxx:712-735) of the evisc just computed — both read values this pass already holds.
+    template<bool SURF, int MODE, int TX, int TY, bool LIM = false>
     __global__ void __launch_bounds__(TX * TY, MHH_EVISC_MINB)
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
                  const double* __restrict__ dbdz, const double* __restrict__ z0m,
-                 const double* __restrict__ mlen0, const double tPr, const double visc, const GridD gd)
+                 const double* __restrict__ mlen0, const double tPr, const double visc, const GridD gd,
+                 unsigned long long* __restrict__ lim, const double tPrfac_i)
     {
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = 4;
@@ -90,6 +94,8 @@ constexpr int UVW_SLOTS = 6;
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         const double tPr_i = 1. / tPr;
+        const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);   // LIM only
+        unsigned long long m_cfl = 0ULL, m_dn = 0ULL;
 
         Map map;
         map.init(i0, j0, gd.icells, gd.jcells, tid);
@@ -261,11 +267,26 @@ constexpr int UVW_SLOTS = 6;
                 }
             }
             if (live) evisc[ijk] = ev;
+            if (LIM && live)
+            {
+                const double cf = fabs(fd::interp2(u_c, u_e)) * dxi + fabs(fd::interp2(v_c, v_n)) * dyi
+                                + fabs(fd::interp2(w_c, w_t)) * dzi_k;
+                const unsigned long long bc = abs_bits(cf);
+                m_cfl = bc > m_cfl ? bc : m_cfl;
+                const unsigned long long bd = abs_bits(ev * tPrfac_i * (dxidxi + dyidyi + dzi_k * dzi_k));
+                m_dn = bd > m_dn ? bd : m_dn;
+            }
             u_c = u_t; u_e = u_et;
             v_c = v_t; v_n = v_nt;
             w_c = w_t; w_w = w_wt; w_e = w_et; w_s = w_st; w_n = w_nt;
         }
         cp_async_wait<0>();
+        if (LIM)
+        {
+            block_max_bits(m_cfl, lim);
+            __syncthreads();                             // block_max_bits reuses its shared scratch
+            block_max_bits(m_dn, lim + 1);
+        }
     }
 
     // mirrored wall rows for resolved walls, src/diff_smag2.cxx:214-226, :300-312
@@ -757,9 +778,13 @@ static int smag2_upload_mlen0(Ctx* c, double cs)
 
 int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const double* v, const double* w,
                          const double* N2, const double* dudz, const double* dvdz, const double* dbdz,
-                         const double* z0m, double cs, double tPr, double visc, double* evisc, int strain_only)
+                         const double* z0m, double cs, double tPr, double visc, double* evisc, int strain_only,
+                         unsigned long long* lim)
 {
     const GridD& gd = c->gd;
+    if (lim != nullptr && strain_only != 2 && !(strain_only == 0 && N2 != nullptr)) return MHH_ERR_UNSUPPORTED;
+    if (lim != nullptr) MHH_CUDA_CHECK(cudaMemsetAsync(lim, 0, 2 * sizeof(unsigned long long), c->stream));
+    const double tPrfac_i = 1. / std::fmin(1., tPr);
     if (c->mlen0_cs != cs || c->mlen0_d == nullptr)
         if (int e = smag2_upload_mlen0(c, cs)) return e;
     if (strain_only == 2)
@@ -771,7 +796,7 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     }
     constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
     const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd
+    #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd, lim, tPrfac_i
     if (strain_only == 1)
     {
         if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 2, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
@@ -781,13 +806,23 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     }
     if (strain_only == 2)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        if (lim != nullptr)
+        {
+            if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+            else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        }
+        else if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else                    MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
     }
     else if (N2 != nullptr)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        if (lim != nullptr)
+        {
+            if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+            else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        }
+        else if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else                    MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
     }
     else
     {

@@ -329,8 +329,11 @@ class Advec:
         return out.value
 
     def get_time_limit(self, idt, dt):
-        cfl = max(self.cflmin, self.get_cfl(dt))
-        return int(idt * self.cflmax / cfl)
+        return self.time_limit_from(self.get_cfl(dt) , idt)
+
+    def time_limit_from(self, cfl, idt):
+        """Advec::get_time_limit (src/advec_2.cxx:281-294) from an already reduced cfl = dt * max(...)."""
+        return int(idt * self.cflmax / max(self.cflmin, cfl))
 
 
 class Diff:
@@ -365,14 +368,24 @@ class Diff:
     def _surface_model(self):
         return 1 if self.boundary.get_switch() != "default" else 0
 
-    def exec_viscosity(self, thermo=None, surface=None):
+    def exec_viscosity(self, thermo=None, surface=None, limits=False):
         """Diff_smag2::exec_viscosity, src/diff_smag2.cxx:1046. ``thermo`` supplies N2 (get_thermo_field("N2"));
-        ``surface`` supplies z0m/dudz/dvdz/dbdz planes when a surface model is on."""
+        ``surface`` supplies z0m/dudz/dvdz/dbdz planes when a surface model is on.
+        ``limits``: also return (max of calc_cfl before the * dt, dnmul) taken in the same pass (the two maxima
+        Model::set_time_step needs right after this call, src/model.cxx:354-357); None when the fused pass does not apply."""
         if self.swdiff != "smag2":
-            return
+            return None
         g, f = self.grid, self.fields
         sm = self._surface_model()
         planes = surface or {}
+        if limits and thermo is not None and getattr(thermo, "fuse_N2", False):
+            cfl_dt, dnmul = C.c_double(), C.c_double()
+            L.check(g.ctx, g.lib.mhh_smag2_exec_viscosity_dry_limits(
+                g.ctx, sm, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sp["th"].fld),
+                L.ptr(planes.get("dudz")), L.ptr(planes.get("dvdz")), L.ptr(planes.get("dbdz")), L.ptr(planes.get("z0m")),
+                C.c_double(self.cs), C.c_double(self.tPr), C.c_double(f.visc), L.ptr(f.sd["evisc"].fld),
+                C.byref(cfl_dt), C.byref(dnmul)), "mhh_smag2_exec_viscosity_dry_limits")
+            return cfl_dt.value, dnmul.value
         if thermo is not None and getattr(thermo, "fuse_N2", False):
             # Thermo_dry: N2 is evaluated inside the evisc kernel from th (no N2 field round trip through HBM)
             L.check(g.ctx, g.lib.mhh_smag2_exec_viscosity_dry(
@@ -473,7 +486,11 @@ class Diff:
     def get_time_limit(self, idt, dt):
         if self.swdiff == "0":
             return int(1e18)
-        dnmul = max(1.e-9, self._dnmul()) if self.swdiff == "smag2" else self._dnmul()
+        return self.time_limit_from(self._dnmul(), idt, dt)
+
+    def time_limit_from(self, dnmul, idt, dt):
+        """Diff::get_time_limit (src/diff_smag2.cxx:884-902, src/diff_2.cxx) from an already reduced dnmul."""
+        dnmul = max(1.e-9, dnmul) if self.swdiff == "smag2" else dnmul
         return int(idt * self.dnmax / (dt * dnmul))
 
 

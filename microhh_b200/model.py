@@ -87,6 +87,8 @@ class Model:
         # Thermo_dry + Advec_2 + Diff_smag2 tendencies in one pass per field (mhh_advec2_smag2_exec)
         self.fuse_tend = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo in ("0", "dry")
         self.fuse_tend4 = self.advec.swadvec == "4" and self.diff.swdiff == "4"     # mhh_advec4_diff4_exec
+        # Advec_2::get_time_limit + Diff_smag2::get_time_limit inside the evisc pass (mhh_smag2_exec_viscosity_dry_limits)
+        self.fuse_limits = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo == "dry" and npy == 1
         self.fuse_pres_rk = self.pres.swpres in ("2", "4")   # Pres::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
@@ -116,9 +118,14 @@ class Model:
         b.set_prognostic_cyclic_bcs()                      # src/model.cxx:346
         b.set_ghost_cells()                                # :348
         self.fields.exec()                                 # :351 (mean profiles, only when buffer/force asked for them)
-        self.diff.exec_viscosity(self.thermo, surface=self.surface)   # :354
-        if not tl.in_substep() and tl.adaptivestep:        # set_time_step, :357 -> :731-751
-            tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
+        set_dt = not tl.in_substep() and tl.adaptivestep
+        # :354; on the first substep of the 2nd-order LES path the two dt maxima ride in the same pass over u,v,w
+        lim = self.diff.exec_viscosity(self.thermo, surface=self.surface, limits=set_dt and self.fuse_limits)
+        if set_dt:                                         # set_time_step, :357 -> :731-751
+            if lim is not None:
+                tl.set_time_step(self.advec.time_limit_from(lim[0] * tl.dt, tl.idt), self.diff.time_limit_from(lim[1], tl.idt, tl.dt))
+            else:
+                tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
         if self.mo:             # :376-377 (Thermo::exec of :366 only adds to wt, which the surface layer does not read)
             b.exec(self.thermo)
             b.set_ghost_cells()

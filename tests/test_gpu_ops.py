@@ -218,6 +218,46 @@ def test_fused_dry_viscosity_equals_two_step_path(cuda_lib, sm):
     g.close(); W.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("sm", [0, 1])
+@pytest.mark.parametrize("dims", [(24, 16, 12), (40, 10, 37), (33, 9, 70)], ids=["even", "ragged_tile", "two_chunks"])
+def test_fused_viscosity_limits_equal_separate_reductions(cuda_lib, sm, dims):
+    """mhh_smag2_exec_viscosity_dry_limits: the evisc field is bit-identical to mhh_smag2_exec_viscosity_dry and the two
+    maxima equal mhh_advec_cfl / dt and mhh_smag2_dnmul run afterwards (same expressions, exact maxima); a NaN in the
+    velocity still propagates into the CFL maximum (the reference's guard, src/model.cxx:832-836)."""
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    itot, jtot, ktot = dims
+    case = make_case(itot=itot, jtot=jtot, ktot=ktot, alpha=1.3, surface_model=sm, anelastic=True)
+    g, W = _worlds(case)
+    f = H.Fields(g, slist=["th"])
+    b = H.Boundary(g, f, swboundary="surface" if sm else "default")
+    for n in "uvw":
+        f.mp[n].fld.copy_(_up(g, case[n]))
+        b.boundary_cyclic.exec(f.mp[n].fld)
+    f.sp["th"].fld.copy_(_up(g, case["s"][0]))
+    rng = np.random.default_rng(2)
+    t = Thermo(g, f, "dry", thref=300. + rng.uniform(0, 1, W.kcells), threfh=300. + rng.uniform(0, 1, W.kcells))
+    a = H.Advec.factory(g, f, "2")
+    d = H.Diff.factory(g, f, b, "smag2", cs=0.17, tPr=1. / 3.)
+    P = {k: _up(g, v) for k, v in case["planes"].items()}
+    lim = d.exec_viscosity(t, surface=P, limits=True)
+    assert lim is not None
+    fused = f.sd["evisc"].fld.cpu().numpy().copy()
+    f.sd["evisc"].fld.zero_()
+    assert d.exec_viscosity(t, surface=P) is None
+    assert np.array_equal(f.sd["evisc"].fld.cpu().numpy(), fused)
+    dt = 0.37
+    assert lim[0] * dt == a.get_cfl(dt)
+    assert lim[1] == d._dnmul()
+    assert a.time_limit_from(lim[0] * dt, 10**9) == a.get_time_limit(10**9, dt)
+    assert d.time_limit_from(lim[1], 10**9, dt) == d.get_time_limit(10**9, dt)
+    f.mp["u"].fld[g.kstart + 1, g.jstart + 2, g.istart + 3] = float("nan")
+    lim = d.exec_viscosity(t, surface=P, limits=True)
+    assert np.isnan(lim[0]) and np.isnan(a.get_cfl(dt))
+    g.close(); W.close()
+
+
 @pytest.mark.parametrize("rkorder,substep", [(3, 0), (3, 1), (3, 2), (4, 3), (4, 4)])
 def test_fused_pressure_tail_equals_output_then_rk(cuda_lib, rkorder, substep):
     """mhh_pres_exec_rk (Pres_2::output fused with Timeloop::exec for u,v,w) is bit-identical to mhh_pres_exec followed
