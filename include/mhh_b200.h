@@ -131,6 +131,12 @@ int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* ctx, int surface_model,
                                         const double* dbdz, const double* z0m,
                                         double cs, double tPr, double visc, double* evisc,
                                         double* cfl_over_dt, double* dnmul);
+/* Lazy-tendency mode of the fused 2nd-order LES path (off by default).  Timeloop::exec leaves every tendency at zero after
+ * the last substep (`at *= cA`, cA = 0: src/timeloop.cxx:250-285) and the next step's first tendency operator reads the zeros
+ * back.  With the mode on, the last-substep tails (mhh_pres_exec_rk: ut,vt,wt; mhh_advec2_smag2_exec_rk: the scalars' st)
+ * leave those arrays UNDEFINED, and the next mhh_advec2_smag2_exec[_rk] / mhh_smag2_exec call on the same arrays starts from 0
+ * without reading them.  Results are bit-identical; nothing else may read those arrays between the two calls. */
+int mhh_set_lazy_tendencies(mhh_ctx* ctx, int on);
 /* Diff_smag2::exec — src/diff_smag2.cxx:939 (diff_u :370, diff_v :472, diff_w :575, diff_c :620). */
 int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
                    const double* u, const double* v, const double* w, const double* evisc,

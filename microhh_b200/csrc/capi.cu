@@ -514,6 +514,24 @@ int mhh_advec2_smag2_exec_rk(mhh_ctx* c, int surface_model, const double* u, con
                                 svisc, tPr, sbuf, s_new, rkorder, substep, dt);
 }
 
+// Lazy-tendency mode of the fused 2nd-order LES path.  Timeloop::exec leaves every tendency at zero after the last substep
+// (at *= cA with cA = 0, src/timeloop.cxx:250-285) and the next step's first operator reads those zeros back.  With the mode
+// on, the last-substep tails (mhh_pres_exec_rk for ut,vt,wt; the scalars of mhh_advec2_smag2_exec_rk) leave the arrays
+// UNDEFINED instead, and the next mhh_advec2_smag2_exec[_rk] / mhh_smag2_exec call on the same arrays starts from 0 without
+// reading them: 3 + 3 (+ 2 per scalar) field passes less per step, results bit-identical.  Contract: between the end of a step
+// and that next call nothing else may read those tendency arrays.
+int mhh_set_lazy_tendencies(mhh_ctx* c, int on)
+{
+    CTX_CHECK(c);
+    c->lazy_tend = on != 0;
+    if (!on)
+    {
+        if (c->fresh_uvw[0] != nullptr) { c->last_error = "lazy-tendency mode switched off while tendencies are undefined"; return MHH_ERR_STATE; }
+        for (auto fp : c->fresh_s) if (fp != nullptr) { c->last_error = "lazy-tendency mode switched off while tendencies are undefined"; return MHH_ERR_STATE; }
+    }
+    return MHH_OK;
+}
+
 int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
 {
     CTX_CHECK(c);

@@ -41,6 +41,10 @@ struct Ctx
 
     // reductions
     unsigned long long* max_bits_d = nullptr;   // 8 slots
+    // lazy-tendency mode (mhh_set_lazy_tendencies): arrays the fused last-substep tails left undefined instead of zeroed
+    bool lazy_tend = false;
+    const double* fresh_uvw[3] = {nullptr, nullptr, nullptr};
+    const double* fresh_s[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double* sum_d = nullptr;                    // kcells + 16 slots
     double* host_pinned = nullptr;              // kcells + 16 doubles, pinned
 

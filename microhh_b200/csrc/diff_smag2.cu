@@ -319,7 +319,7 @@ constexpr int UVW_SLOTS = 6;
                                const double* __restrict__ ufluxbot, const double* __restrict__ ufluxtop,
                                const double* __restrict__ vfluxbot, const double* __restrict__ vfluxtop,
                                const double visc, const double* __restrict__ th, const double* __restrict__ threfh,
-                               const double* __restrict__ g_threfh, const GridD gd)
+                               const double* __restrict__ g_threfh, const GridD gd, const int fresh)
     {
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = Map::N, NS = UVW_SLOTS, NT = TX * TY;
@@ -333,6 +333,7 @@ constexpr int UVW_SLOTS = 6;
         const int i0 = blockIdx.x * TX + gd.istart, j0 = blockIdx.y * TY + gd.jstart;
         const int i = i0 + threadIdx.x, j = j0 + threadIdx.y;
         const bool live = (i < gd.iend) && (j < gd.jend);
+        const bool ldt = live && !fresh;                 // fresh: the tendency arrays hold no data (logically zero), start from 0
         const int jj = gd.icells, kk = gd.ijcells;
         const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
         const int k0 = gd.kstart + blockIdx.z * KCHUNK;
@@ -419,7 +420,7 @@ constexpr int UVW_SLOTS = 6;
 
         int ijk = ij + k0 * kk;
         double ut_c = 0., vt_c = 0., wt_c = 0.;
-        if (live) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
+        if (ldt) { ut_c = ut[ijk]; vt_c = vt[ijk]; wt_c = wt[ijk]; }
         double th_b = 0., th_c = 0., th_n = 0.;          // theta column (centre only), one level ahead from global memory
         if (BUOY) { th_b = th[ijk - kk]; th_c = th[ijk]; th_n = th[ijk + kk]; }
         MHH_UVW_UNROLL
@@ -429,7 +430,7 @@ constexpr int UVW_SLOTS = 6;
             stage(it + 4);                               // plane k+3, into the slot last read NS - 4 levels ago
             // tendencies of the next level: in flight during this level's arithmetic
             double ut_n = 0., vt_n = 0., wt_n = 0.;
-            if (live && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
+            if (ldt && k + 1 < k1) { ut_n = ut[ijk + kk]; vt_n = vt[ijk + kk]; wt_n = wt[ijk + kk]; }
             const double th_t = th_n;
             if (BUOY && k + 1 < k1) th_n = th[ijk + 2 * kk];
 
@@ -560,6 +561,7 @@ constexpr int UVW_SLOTS = 6;
                     + div_by( fw_t - fw_b, rhoh_b, met[3][km] ) * met[10][km];
                 if (live) wt[ijk] = wt_c + wd;
             }
+            else if (fresh && live) wt[ijk] = 0.;      // the row the pass never writes
             fw_b = fw_t; gu_b = gu_t; gv_b = gv_t;
             if (BUOY) { th_b = th_c; th_c = th_t; }
             if (MHH_UVW_REREAD_B) { e_c = e_t; e_w = e_wt; e_s = e_st; u_c = u_t; v_c = v_t; }
@@ -592,6 +594,7 @@ constexpr int UVW_SLOTS = 6;
         const double* sig;
         const double* abuf;
         int bufk;
+        int fresh;       // the tendency array holds no data (lazy-tendency mode): start from 0 instead of reading it
     };
 
     template<bool SURF, bool ADVEC, int TX, int TY>
@@ -652,8 +655,9 @@ constexpr int UVW_SLOTS = 6;
         const int cw = c - 1, ce = c + 1, cs = c - W, cn = c + W;
 
         int ijk = ij + k0 * kk;
+        const bool ldt = live && !tail.fresh;
         double at_c = 0.;
-        if (live) at_c = at[ijk];
+        if (ldt) at_c = at[ijk];
         double w_c = 0., w_n = 0.;                       // w column (centre only), one level ahead from global memory
         if (ADVEC) { w_c = w[ijk]; w_n = w[ijk + kk]; }
 
@@ -676,7 +680,7 @@ constexpr int UVW_SLOTS = 6;
             __syncthreads();                             // ... for every thread; everyone is done with plane k-1
             stage(k + 3);                                // into the slot of plane k-1
             double at_n = 0.;
-            if (live && k + 1 < k1) at_n = at[ijk + kk];
+            if (ldt && k + 1 < k1) at_n = at[ijk + kk];
             const double w_t = w_n;
             if (ADVEC && k + 1 < k1) w_n = w[ijk + 2 * kk];
 
@@ -853,7 +857,10 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
     const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
     const double* threfh = c->thref_d ? c->thref_d + gd.kcells : nullptr;
     const double* g_threfh = c->thref_d ? c->thref_d + 3 * gd.kcells : nullptr;
-    #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd
+    // lazy-tendency mode (mhh_set_lazy_tendencies): the arrays the last fused pressure tail left undefined start from 0
+    const int fresh = (c->fresh_uvw[0] == ut && c->fresh_uvw[1] == vt && c->fresh_uvw[2] == wt) ? 1 : 0;
+    c->fresh_uvw[0] = c->fresh_uvw[1] = c->fresh_uvw[2] = nullptr;
+    #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd, fresh
     constexpr size_t smem = (size_t)UVW_SLOTS * 4 * (TX + 2) * (TY + 2) * sizeof(double);
     #define UVW_LAUNCH(NAME, S, A, B) do { \
         static bool attr = false; \
@@ -890,7 +897,9 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
                            const double* sbuf, double* a_new, int rkorder, int substep, double dt)
 {
     const GridD& gd = c->gd;
-    ScalarTail tail{nullptr, 0., 0., 0, nullptr, nullptr, 0};
+    ScalarTail tail{nullptr, 0., 0., 0, nullptr, nullptr, 0, 0};
+    for (auto& fp : c->fresh_s)
+        if (fp == at && at != nullptr) { tail.fresh = 1; fp = nullptr; }
     if (sbuf)
     {
         if (!c->buffer_sigma_d) { c->last_error = "buffer not planned (mhh_buffer_plan)"; return MHH_ERR_STATE; }
@@ -918,7 +927,13 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
     #undef SC_LAUNCH
     MHH_LAUNCH_CHECK();
     if (tail.rk_mode == 2)      // last substep: the whole tendency array (ghost cells too) is zero afterwards, src/timeloop.cu:34-70
-        MHH_CUDA_CHECK(cudaMemsetAsync(at, 0, sizeof(double) * gd.ncells, c->stream));
+    {
+        bool lazy = false;
+        if (c->lazy_tend)       // ... or declared undefined until the next fused tendency pass, which then starts from 0
+            for (auto& fp : c->fresh_s)
+                if (fp == nullptr) { fp = at; lazy = true; break; }
+        if (!lazy) MHH_CUDA_CHECK(cudaMemsetAsync(at, 0, sizeof(double) * gd.ncells, c->stream));
+    }
     return MHH_OK;
 }
 

@@ -202,7 +202,7 @@ namespace
     pres2_out_rk_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                         double* __restrict__ u, double* __restrict__ v, double* __restrict__ w,
                         const double* __restrict__ p, const double cB_dt, const double cA_next, const int zero_all,
-                        const GridD gd)
+                        const GridD gd, const int keep_t)
     {
         const int ijk = blockIdx.x * blockDim.x + threadIdx.x;
         if (ijk >= gd.ncells) return;
@@ -223,11 +223,14 @@ namespace
             u[ijk] = u0 + cB_dt * tu;
             v[ijk] = v0 + cB_dt * tv;
             w[ijk] = w0 + cB_dt * tw;
-            ut[ijk] = zero_all ? 0. : tu * cA_next;
-            vt[ijk] = zero_all ? 0. : tv * cA_next;
-            wt[ijk] = zero_all ? 0. : tw * cA_next;
+            if (!keep_t)         // keep_t (lazy-tendency mode, last substep): the tendency arrays are left undefined
+            {
+                ut[ijk] = zero_all ? 0. : tu * cA_next;
+                vt[ijk] = zero_all ? 0. : tv * cA_next;
+                wt[ijk] = zero_all ? 0. : tw * cA_next;
+            }
         }
-        else if (zero_all)
+        else if (zero_all && !keep_t)
         {
             ut[ijk] = 0.; vt[ijk] = 0.; wt[ijk] = 0.;
         }
@@ -353,7 +356,9 @@ int pres2_output_rk(Ctx* c, double* ut, double* vt, double* wt, double* p, doubl
     double cB_dt, cA_next; int zero_all;
     rk_coefs(rkorder, substep, dt, &cB_dt, &cA_next, &zero_all);
     dim3 b(256), g((gd.ncells + 255) / 256);
-    MHH_LAUNCH(c, "pres2_out_rk_kernel", pres2_out_rk_kernel<<<g, b, 0, c->stream>>>(ut, vt, wt, u, v, w, p, cB_dt, cA_next, zero_all, gd));
+    const int keep_t = (zero_all && c->lazy_tend) ? 1 : 0;
+    MHH_LAUNCH(c, "pres2_out_rk_kernel", pres2_out_rk_kernel<<<g, b, 0, c->stream>>>(ut, vt, wt, u, v, w, p, cB_dt, cA_next, zero_all, gd, keep_t));
+    if (keep_t) { c->fresh_uvw[0] = ut; c->fresh_uvw[1] = vt; c->fresh_uvw[2] = wt; }
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

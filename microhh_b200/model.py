@@ -108,6 +108,11 @@ class Model:
         scal = set(self.fields.sp)
         self.fuse_scalar_rk = (self.fuse_tend and bool(scal) and npy == 1 and fo_.swwls == "0"
                                and not (scal & set(fo_.lslist)) and not (scal & set(fo_.nudgelist)))
+        # Tendencies left undefined (not zeroed) by the fused last-substep tails; the next fused tendency pass starts from 0
+        self.lazy_tend = bool(self.fuse_tend and self.fuse_pres_rk and self.pres.swpres == "2" and npy == 1
+                              and (not scal or self.fuse_scalar_rk) and ini.get("b200", {}).get("lazy_tendencies", True))
+        if self.lazy_tend:
+            L.check(self.grid.ctx, self.grid.lib.mhh_set_lazy_tendencies(self.grid.ctx, 1), "mhh_set_lazy_tendencies")
         self.surface = self.boundary.planes() if self.mo else (surface or {})
         self.boundary.set_values()
         self.pres.set_values()

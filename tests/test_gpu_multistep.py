@@ -177,6 +177,44 @@ def test_les_gabls1_with_buffer_and_geostrophic_forcing(cuda_lib):
     assert np.abs(res["got"]["v"][ks:ke, js:je, is_:ie].mean(axis=(1, 2))).max() > 1e-4
 
 
+@pytest.mark.parametrize("kind", ["gabls1_stable", "drycbl_from_rest"])
+def test_lazy_tendencies_and_fused_limits_are_bit_identical(cuda_lib, kind):
+    """The product path's two step-level shortcuts change no bit of the prognostic fields over 20 adaptive steps:
+    (i) lazy tendencies (mhh_set_lazy_tendencies: the last-substep tails leave ut,vt,wt,tht undefined and the next tendency
+    pass starts from 0) and (ii) the dt limits taken inside the evisc pass (mhh_smag2_exec_viscosity_dry_limits)."""
+    import torch
+    from microhh_b200.model import Model
+    ini, z, init, surface = les_case(kind, n=32)
+    dev = torch.device("cuda:0")
+    out = []
+    for shortcuts in (True, False):
+        ini2 = dict(ini, b200=dict(lazy_tendencies=shortcuts))
+        m = Model(ini2, z, device=dev)
+        assert m.lazy_tend == shortcuts
+        if not shortcuts:
+            m.fuse_limits = False
+        f = m.fields
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        for n in "uvw":
+            f.mp[n].fld.copy_(up(init[n]))
+        for n in f.sp:
+            f.sp[n].fld.copy_(up(init[n]))
+        if surface:
+            m.surface = {k: up(v) for k, v in surface.items()}
+            f.mp["u"].flux_bot.copy_(m.surface["ufluxbot"]); f.mp["v"].flux_bot.copy_(m.surface["vfluxbot"])
+            f.sp["th"].flux_bot.copy_(m.surface["sfluxbot"])
+        dts = []
+        for _ in range(20):
+            m.step()
+            dts.append(m.timeloop.idt)
+        out.append(({n: f.ap[n].fld.cpu().numpy().copy() for n in f.ap}, dts, m.print_status()))
+        m.grid.close()
+    assert out[0][1] == out[1][1]
+    for n in out[0][0]:
+        assert np.array_equal(out[0][0][n], out[1][0][n]), n
+    assert out[0][2] == out[1][2]
+
+
 def test_dns_order4_steps(cuda_lib):
     """moser180-like channel DNS: advec_4, diff_4, pres_4 on a tanh-stretched grid, RK3, no-slip walls; RK4 as well."""
     itot, jtot, ktot = 32, 24, 32

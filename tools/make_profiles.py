@@ -28,6 +28,8 @@ if os.path.exists(rep):
         elif "smag2_scalar_tile_kernel" in kn: key = "advec2_smag2_c_kernel"
         elif "pres2_in_kernel" in kn: key = "pres2_in_kernel"
         elif "pres2_tdma_kernel" in kn: key = "pres2_tdma_kernel"
+        elif "fft_pow2_col_kernel<(int)-1" in kn: key = "fft_fwd_y"
+        elif "fft_pow2_col_kernel<1" in kn: key = "fft_bwd_y"
         elif "fft_pow2_kernel<(int)-1, 0" in kn: key = "fft_fwd_x"
         elif "fft_pow2_kernel<(int)-1, 1" in kn: key = "fft_fwd_y"
         elif "fft_pow2_kernel<1, 1" in kn: key = "fft_bwd_y"
