@@ -23,6 +23,13 @@
 #ifndef MHH_EVISC_UNROLL_N
 #define MHH_EVISC_UNROLL_N 3
 #endif
+// the LIM variant of the evisc pass (once per step) carries two running maxima more: its own unroll / occupancy knobs
+#ifndef MHH_EVISC_LIM_UNROLL_N
+#define MHH_EVISC_LIM_UNROLL_N 1
+#endif
+#ifndef MHH_EVISC_LIM_MINB
+#define MHH_EVISC_LIM_MINB 2
+#endif
 #ifndef MHH_SCALAR_UNROLL_N
 #define MHH_SCALAR_UNROLL_N 6
 #endif
@@ -71,7 +78,7 @@ constexpr int UVW_SLOTS = 6;
     // src/model.cxx:354-357): lim[0] = max of calc_cfl's sum (src/advec_2.cxx:51-78, before the * dt), lim[1] = max of
     // calc_dnmul (src/diff_smag2.cxx:712-735) of the evisc just computed — both read values this pass already holds.
     template<bool SURF, int MODE, int TX, int TY, bool LIM = false>
-    __global__ void __launch_bounds__(TX * TY, MHH_EVISC_MINB)
+    __global__ void __launch_bounds__(TX * TY, (LIM ? MHH_EVISC_LIM_MINB : MHH_EVISC_MINB))
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
@@ -161,7 +168,7 @@ constexpr int UVW_SLOTS = 6;
             yz_n = 0.125 * pow2((v_n - v_nb) * dzhi_k + (w_n - w_c) * dyi);
         }
 
-        MHH_PRAGMA_UNROLL(MHH_EVISC_UNROLL_N)
+        MHH_PRAGMA_UNROLL((LIM ? MHH_EVISC_LIM_UNROLL_N : MHH_EVISC_UNROLL_N))
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
             cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)

@@ -233,10 +233,11 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* b, const unsigned 
                  :: "r"(smem_u32(b)), "r"(parity) : "memory");
 }
 
-template<int TX, int TY, int H>
+// NTH: threads that share the copy of one plane (default: one per tile column)
+template<int TX, int TY, int H, int NTH = TX * TY>
 struct TileMap
 {
-    static constexpr int W = TX + 2 * H, HT = TY + 2 * H, N = W * HT, NT = TX * TY, R = (N + NT - 1) / NT;
+    static constexpr int W = TX + 2 * H, HT = TY + 2 * H, N = W * HT, NT = NTH, R = (N + NT - 1) / NT;
     int g[R];      // offset of this thread's r-th element within a global (i,j) plane (clamped into the plane); -1: none
 
     // (i0, j0): first interior point of the tile
