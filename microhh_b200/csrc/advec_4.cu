@@ -25,6 +25,12 @@ namespace
     { return bi0 * p[o] + bi1 * p[o + s] + bi2 * p[o + 2 * s] + bi3 * p[o + 3 * s]; }
     __device__ __forceinline__ double T4(const double* __restrict__ p, int o, int s)
     { return ti0 * p[o] + ti1 * p[o + s] + ti2 * p[o + 2 * s] + ti3 * p[o + 3 * s]; }
+    // 16 x the ci / bi / ti interpolations, same roundings (see advec4_mom_kernel)
+    __device__ __forceinline__ double CS(double a, double b, double c, double d) { return ((9. * b - a) + 9. * c) - d; }
+    __device__ __forceinline__ double BS(double a, double b, double c, double d) { return ((5. * a + 15. * b) - 5. * c) + d; }
+    __device__ __forceinline__ double TS(double a, double b, double c, double d) { return ((a - 5. * b) + 15. * c) + 5. * d; }
+    __device__ __forceinline__ double I4S(const double* __restrict__ p, int o, int s)
+    { return CS(p[o], p[o + s], p[o + 2 * s], p[o + 3 * s]); }
     __device__ __forceinline__ double G4(double a, double b, double c, double d)
     { return cg0 * a + cg1 * b + cg2 * c + cg3 * d; }
 
@@ -50,7 +56,12 @@ namespace
         const int kfirst = (COMP == 2) ? gd.kstart + 1 : gd.kstart;
         const int k0 = kfirst + blockIdx.z * KCHUNK;
         const int k1 = min(k0 + KCHUNK, gd.kend);
+        // The interpolation weights are k/16 with k = -1, 9, 9, -1 (ci), 5, 15, -5, 1 (bi), 1, -5, 15, 5 (ti): a power-of-two
+        // scaling commutes with every rounding, so ci0*a + ci1*b + ci2*c + ci3*d = (((9b - a) + 9c) - d) / 16 bit for bit.  The
+        // march works on the unscaled sums (5 instead of 7 operations each), every flux is a product of two of them, and the
+        // 1/256 is collected in the metric: G4(P/256 ...) * dxi = G4(P ...) * (dxi / 256).
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
+        const double sdxi = dxi * (1. / 256.), sdyi = dyi * (1. / 256.);
         const double* __restrict__ a = (COMP == 0) ? u : (COMP == 1) ? v : w;
         const int sa = (COMP == 0) ? ii : (COMP == 1) ? jj : kk;     // staggering direction of a
         const double* __restrict__ mz = (COMP == 2) ? gd.dzhi4 : gd.dzi4;
@@ -61,7 +72,7 @@ namespace
         // interpolation for the biased one; those faces are used once (they leave the queue first / enter it last).
         const int ij = i + j * jj;
         auto face = [&](const int l, const double A) -> double
-        { return (COMP == 2) ? A * A : I4(w, ij + l * kk - 2 * sa, sa) * A; };
+        { return (COMP == 2) ? A * A : I4S(w, ij + l * kk - 2 * sa, sa) * A; };
         double qa = a[ij + (k0 - 1) * kk], qb = a[ij + k0 * kk], qc = a[ij + (k0 + 1) * kk], qd = a[ij + (k0 + 2) * kk];
         double f0, f1, f2;
         double qm2 = 0., qm3 = 0.;      // a[k-2], a[k-3]: only the diffusion stencil keeps them
@@ -75,11 +86,10 @@ namespace
         {
             const double am2 = a[ij + (k0 - 2) * kk], am3 = a[ij + (k0 - 3) * kk];
             if (DIFF) { qm2 = am2; qm3 = am3; }
-            const double A0 = (k0 == kfirst) ? bi0 * am2 + bi1 * qa + bi2 * qb + bi3 * qc
-                                             : ci0 * am3 + ci1 * am2 + ci2 * qa + ci3 * qb;
+            const double A0 = (k0 == kfirst) ? BS(am2, qa, qb, qc) : CS(am3, am2, qa, qb);
             f0 = face(k0 - 1, A0);
-            f1 = face(k0, ci0 * am2 + ci1 * qa + ci2 * qb + ci3 * qc);
-            f2 = face(k0 + 1, ci0 * qa + ci1 * qb + ci2 * qc + ci3 * qd);
+            f1 = face(k0, CS(am2, qa, qb, qc));
+            f2 = face(k0 + 1, CS(qa, qb, qc, qd));
         }
 
         MHH_PRAGMA_UNROLL(MHH_ADVEC4_UNROLL_N)
@@ -91,16 +101,16 @@ namespace
             // ---- x direction ----
             if (COMP == 0)
             {
-                const double f0 = I4(u, ijk - 3 * ii, ii), f1 = I4(u, ijk - 2 * ii, ii);
-                const double f2 = I4(u, ijk - ii, ii), f3 = I4(u, ijk, ii);
-                t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * dxi;
+                const double f0 = I4S(u, ijk - 3 * ii, ii), f1 = I4S(u, ijk - 2 * ii, ii);
+                const double f2 = I4S(u, ijk - ii, ii), f3 = I4S(u, ijk, ii);
+                t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * sdxi;
             }
             else
             {
-                t -= G4(I4(u, ijk - ii - 2 * sa, sa)     * I4(a, ijk - 3 * ii, ii),
-                        I4(u, ijk - 2 * sa, sa)          * I4(a, ijk - 2 * ii, ii),
-                        I4(u, ijk + ii - 2 * sa, sa)     * I4(a, ijk - ii, ii),
-                        I4(u, ijk + 2 * ii - 2 * sa, sa) * I4(a, ijk, ii)) * dxi;
+                t -= G4(I4S(u, ijk - ii - 2 * sa, sa)     * I4S(a, ijk - 3 * ii, ii),
+                        I4S(u, ijk - 2 * sa, sa)          * I4S(a, ijk - 2 * ii, ii),
+                        I4S(u, ijk + ii - 2 * sa, sa)     * I4S(a, ijk - ii, ii),
+                        I4S(u, ijk + 2 * ii - 2 * sa, sa) * I4S(a, ijk, ii)) * sdxi;
             }
 
             // ---- y direction ----
@@ -108,26 +118,25 @@ namespace
             {
                 if (COMP == 1)
                 {
-                    const double f0 = I4(v, ijk - 3 * jj, jj), f1 = I4(v, ijk - 2 * jj, jj);
-                    const double f2 = I4(v, ijk - jj, jj), f3 = I4(v, ijk, jj);
-                    t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * dyi;
+                    const double f0 = I4S(v, ijk - 3 * jj, jj), f1 = I4S(v, ijk - 2 * jj, jj);
+                    const double f2 = I4S(v, ijk - jj, jj), f3 = I4S(v, ijk, jj);
+                    t -= G4(f0 * f0, f1 * f1, f2 * f2, f3 * f3) * sdyi;
                 }
                 else
                 {
-                    t -= G4(I4(v, ijk - jj - 2 * sa, sa)     * I4(a, ijk - 3 * jj, jj),
-                            I4(v, ijk - 2 * sa, sa)          * I4(a, ijk - 2 * jj, jj),
-                            I4(v, ijk + jj - 2 * sa, sa)     * I4(a, ijk - jj, jj),
-                            I4(v, ijk + 2 * jj - 2 * sa, sa) * I4(a, ijk, jj)) * dyi;
+                    t -= G4(I4S(v, ijk - jj - 2 * sa, sa)     * I4S(a, ijk - 3 * jj, jj),
+                            I4S(v, ijk - 2 * sa, sa)          * I4S(a, ijk - 2 * jj, jj),
+                            I4S(v, ijk + jj - 2 * sa, sa)     * I4S(a, ijk - jj, jj),
+                            I4S(v, ijk + 2 * jj - 2 * sa, sa) * I4S(a, ijk, jj)) * sdyi;
                 }
             }
 
             // ---- z direction ----
             {
                 const double qe = a[ijk + 3 * kk];
-                const double A3 = (k == gd.kend - 1) ? ti0 * qa + ti1 * qb + ti2 * qc + ti3 * qd
-                                                     : ci0 * qb + ci1 * qc + ci2 * qd + ci3 * qe;
+                const double A3 = (k == gd.kend - 1) ? TS(qa, qb, qc, qd) : CS(qb, qc, qd, qe);
                 const double f3 = face(k + 2, A3);
-                t -= G4(f0, f1, f2, f3) * mz[k];
+                t -= G4(f0, f1, f2, f3) * (mz[k] * (1. / 256.));
                 f0 = f1; f1 = f2; f2 = f3;
                 if (DIFF)
                 {
