@@ -6,6 +6,9 @@
 // the reference's left-to-right summation order and the x, y, z contributions are subtracted from the
 // tendency one after the other, as the reference does, so results agree to rounding with the CPU build.
 #include "ctx.h"
+#ifndef MHH_ADVEC4_MINB
+#define MHH_ADVEC4_MINB 2
+#endif
 #ifndef MHH_ADVEC4_UNROLL_N
 #define MHH_ADVEC4_UNROLL_N 1
 #endif
@@ -44,7 +47,7 @@ namespace
     // (rows kstart-1 and kend+1, src/boundary.cxx:838-870) are evaluated in the kernel and substituted where the diffusion
     // stencil touches those rows.
     template<int COMP, bool DIM3, bool DIFF>
-    __global__ void __launch_bounds__(256, 2)
+    __global__ void __launch_bounds__(256, MHH_ADVEC4_MINB)
     advec4_mom_kernel(double* __restrict__ at, const double* __restrict__ u, const double* __restrict__ v,
                       const double* __restrict__ w, const double visc, const GridD gd)
     {

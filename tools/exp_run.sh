@@ -1,3 +1,7 @@
 #!/bin/bash
-python -m pytest tests/test_gpu_schemes.py tests/test_gpu_ops.py tests/test_gpu_golden.py tests/test_gpu_multistep.py -m gpu -x -q 2>&1 | tail -3
+for V in "-DMHH_ADVEC4_MINB=3" "-DMHH_ADVEC4_MINB=4"; do
+touch microhh_b200/csrc/advec_4.cu
+make -s -j16 -C microhh_b200/csrc EXTRA="$V" >/dev/null 2>&1 || echo BUILD FAILED
+echo "== $V"
 python tools/bench_dns4.py 2>/dev/null | grep "^== dns4\|advec4" | cut -c1-70
+done
