@@ -74,7 +74,8 @@ def main():
         from microhh_b200.multigpu import nccl_env_defaults
         nccl_env_defaults()
         dist.init_process_group("nccl", device_id=dev)
-    out, status, ref = run(rank, world, dev, dims=(64, 64, 32))
+    dims = tuple(int(v) for v in os.environ.get("SLAB_DIMS", "64,64,32").split(","))
+    out, status, ref = run(rank, world, dev, dims=dims)
     gathered = [None] * world
     if world > 1:
         dist.all_gather_object(gathered, out)

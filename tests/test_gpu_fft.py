@@ -26,7 +26,9 @@ def to_halfcomplex(x, axis):
 
 
 SIZES = [(8, 8, 3), (16, 32, 5), (64, 16, 4), (512, 8, 3), (32, 256, 2), (1024, 16, 2), (48, 24, 3), (20, 12, 5),
-         (96, 10, 2), (16, 1, 4), (36, 14, 3), (512, 512, 10), (1024, 64, 40), (8, 16, 2)]
+         (96, 10, 2), (16, 1, 4), (36, 14, 3), (512, 512, 10), (1024, 64, 40), (8, 16, 2),
+         # y passes on the lanes-along-the-lines kernel: 4 / 16 pairs per CTA; (24, 512): lines not in groups of 16 -> staged tile
+         (16, 1024, 2), (64, 256, 3), (24, 512, 2)]
 
 
 @pytest.mark.parametrize("itot,jtot,ktot", SIZES)
