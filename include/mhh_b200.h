@@ -137,6 +137,9 @@ int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* ctx, int surface_model,
  * leave those arrays UNDEFINED, and the next mhh_advec2_smag2_exec[_rk] / mhh_smag2_exec call on the same arrays starts from 0
  * without reading them.  Results are bit-identical; nothing else may read those arrays between the two calls. */
 int mhh_set_lazy_tendencies(mhh_ctx* ctx, int on);
+/* mhh_pres_exec / mhh_pres_exec_rk (2nd order, power-of-two itot, even jmax): evaluate Pres_2::input (src/pres_2.cxx:183-195)
+ * inside the forward x transform instead of writing the right-hand side and reading it back (bit-identical; off by default). */
+int mhh_pres_set_fused_input(mhh_ctx* ctx, int on);
 /* Diff_smag2::exec — src/diff_smag2.cxx:939 (diff_u :370, diff_v :472, diff_w :575, diff_c :620). */
 int mhh_smag2_exec(mhh_ctx* ctx, int surface_model,
                    const double* u, const double* v, const double* w, const double* evisc,

@@ -196,6 +196,36 @@ static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, 
     return fft_lines(c, c->plan_j, dir, in, out, L);
 }
 
+int pres2_in_fft_x(Ctx*, const FftPlan&, const double*, const double*, const double*, const double*, const double*, const double*,
+                   double, double*, const FftLayout&, int);   // fft_pow2.cu
+
+// Pres::input + FFT::exec_forward of the single-GPU pipeline: halos of the tendencies, then either the fused input + x pass
+// (2nd order, power-of-two itot) or the two separate stages; then the y pass.  The spectrum lands in c->work_p.
+static int fft_y(Ctx* c, int dir, double* data);
+static int pres_input_fft_forward(Ctx* c, const double* u, const double* v, const double* w,
+                                  double* ut, double* vt, double* wt, double dt)
+{
+    const GridD& gd = c->gd;
+    if (int e = cyclic_exec(c, ut, MHH_EDGE_EAST_WEST)) return e;       // src/pres_2.cxx:180-181 / src/pres_4.cxx:284-286
+    if (int e = cyclic_exec(c, vt, MHH_EDGE_NORTH_SOUTH)) return e;
+    int e = MHH_ERR_UNSUPPORTED;
+    if (c->order == 2)
+    {
+        FftLayout L;
+        L.nlines = gd.jmax * gd.kmax; L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0; L.base_out = 0;
+        L.n1o = L.n1; L.s1o = L.s1; L.s2o = L.s2; L.sno = L.sn; L.scale = 1.;
+        e = pres2_in_fft_x(c, c->plan_i, u, v, w, ut, vt, wt, dt, c->work_p, L, 0);
+    }
+    if (e == MHH_ERR_UNSUPPORTED)
+    {
+        e = (c->order == 2) ? pres2_input(c, u, v, w, ut, vt, wt, dt, c->work_p) : pres4_input(c, u, v, w, ut, vt, wt, dt, c->work_p);
+        if (e) return e;
+        e = fft_x(c, -1, c->work_p, nullptr);
+    }
+    if (e) return e;
+    return fft_y(c, -1, c->work_p);
+}
+
 static int fft_forward_inplace(Ctx* c, double* data)
 {
     if (c->npy != 1) return MHH_ERR_STATE;
@@ -661,6 +691,8 @@ int mhh_pres_input_to(mhh_ctx* c, const double* u, const double* v, const double
     if (c->order != 2) return MHH_ERR_UNSUPPORTED;
     return pres2_input(c, u, v, w, ut, vt, wt, dt, dst);
 }
+// Off by default: on B200 the fused pass (1.70 ms at 512^3) only equals pres2_in (1.16) + fft_fwd_x (0.53); it moves 16 B/pt less.
+int mhh_pres_set_fused_input(mhh_ctx* c, int on) { CTX_CHECK(c); c->fuse_pres_input = on != 0; return MHH_OK; }
 int mhh_fft_force_generic(mhh_ctx* c, int on) { CTX_CHECK(c); c->fft_force_generic = on != 0; return MHH_OK; }
 int mhh_fft_forward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_forward_inplace(c, data); }
 int mhh_fft_backward(mhh_ctx* c, double* data) { PRES_READY(c); return fft_backward_impl(c, data, nullptr); }
@@ -717,8 +749,7 @@ int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
     int e;
-    if ((e = mhh_pres_input(c, u, v, w, ut, vt, wt, dt))) return e;
-    if ((e = fft_forward_inplace(c, c->work_p))) return e;
+    if ((e = pres_input_fft_forward(c, u, v, w, ut, vt, wt, dt))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
     if ((e = fft_backward_impl(c, c->work_p, p))) return e;
     return mhh_pres_output(c, ut, vt, wt, p);
@@ -742,8 +773,7 @@ int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, do
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec_rk is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
     int e;
-    if ((e = mhh_pres_input(c, u, v, w, ut, vt, wt, dt_sub))) return e;
-    if ((e = fft_forward_inplace(c, c->work_p))) return e;
+    if ((e = pres_input_fft_forward(c, u, v, w, ut, vt, wt, dt_sub))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
     if ((e = fft_backward_impl(c, c->work_p, p))) return e;
     // 4th order: also leaves w's ghost rows in the Normal state of the not yet updated w (src/model.cxx:412)

@@ -41,6 +41,7 @@ struct Ctx
 
     // reductions
     unsigned long long* max_bits_d = nullptr;   // 8 slots
+    bool fuse_pres_input = false;   // mhh_pres_set_fused_input: Pres_2::input evaluated inside the forward x transform
     // lazy-tendency mode (mhh_set_lazy_tendencies): arrays the fused last-substep tails left undefined instead of zeroed
     bool lazy_tend = false;
     const double* fresh_uvw[3] = {nullptr, nullptr, nullptr};

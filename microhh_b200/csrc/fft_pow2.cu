@@ -476,6 +476,90 @@ namespace
             }
         }
     }
+
+    // Pres_2::input (src/pres_2.cxx:183-195) fused with the forward x pass: the right-hand side of the Poisson equation
+    //   p = rho [(ut + u/dt)_{i+1} - (ut + u/dt)_i] dxi + rho [(vt + v/dt)_{j+1} - (vt + v/dt)_j] dyi
+    //       + [rhoh_{k+1} (wt + w/dt)_{k+1} - rhoh_k (wt + w/dt)_k] dzi
+    // is evaluated straight into the registers of the transform that consumes it (two lines j, j+1 of one level per complex
+    // transform), so the ghost-free RHS array is never written and read back (16 of the 72 B/pt of the two passes).  The
+    // neighbour values (i+1: same line; j+1: the pair's other line or the next CTA's; k+1: the plane the CTAs of the next
+    // level read a moment later) are L1 / L2 hits.  Same expression as pres2_in_kernel, same transform: bit-identical.
+    struct PresInArgs
+    {
+        const double* u; const double* v; const double* w;
+        const double* ut; const double* vt; const double* wt;
+        double dti;
+        int k0;              // first level of this call (y-slab k ranges)
+        GridD gd;
+    };
+
+    template<bool SPLIT>
+    __global__ void __launch_bounds__(BLOCK, 3)
+    pres2_in_fft_x_kernel(const PresInArgs F, double* __restrict__ out, const P2Args A)
+    {
+        extern __shared__ double2 zbuf[];
+        const GridD& gd = F.gd;
+        const int n = A.n, n8 = n >> 3, nh = n >> 1;
+        const int tfn = n8;
+        const int npairs = BLOCK / tfn;
+        const int NP = pad(n) + 1;
+        const int p = threadIdx.x / tfn;
+        const int tf = threadIdx.x - p * tfn;
+        double2* z = zbuf + p * NP;
+        const int la = blockIdx.x * (2 * npairs) + 2 * p, lb = la + 1;    // jmax is even: both lines lie in one level
+        const bool va = la < A.nlines, vb = lb < A.nlines;
+        double2 v[8];
+        {
+            const int ls = va ? la : 0;
+            const int j = ls % gd.jmax, k = F.k0 + ls / gd.jmax;
+            const int jj = gd.icells, kk = gd.ijcells;
+            const long row = (long)gd.igc + (long)(j + gd.jgc) * jj + (long)(k + gd.kgc) * kk;
+            const double rho = gd.rhoref[k + gd.kgc], rhoh_t = gd.rhorefh[k + gd.kgc + 1], rhoh_b = gd.rhorefh[k + gd.kgc];
+            const double dzi = gd.dzi[k + gd.kgc];
+            const double dxi = 1. / gd.dx, dyi = 1. / gd.dy, dti = F.dti;
+            const double* __restrict__ u = F.u + row;   const double* __restrict__ ut = F.ut + row;
+            const double* __restrict__ vv = F.v + row;  const double* __restrict__ vt = F.vt + row;
+            const double* __restrict__ w = F.w + row;   const double* __restrict__ wt = F.wt + row;
+            #pragma unroll
+            for (int m = 0; m < 8; ++m)
+            {
+                const int i = tf + m * n8;
+                // line a (row j) and line b (row j + 1) share the v row between them
+                const double fv0 = vt[i] + vv[i] * dti, fv1 = vt[i + jj] + vv[i + jj] * dti, fv2 = vt[i + 2 * jj] + vv[i + 2 * jj] * dti;
+                const double pa = rho * ((ut[i + 1] + u[i + 1] * dti) - (ut[i] + u[i] * dti)) * dxi
+                                + rho * (fv1 - fv0) * dyi
+                                + (rhoh_t * (wt[i + kk] + w[i + kk] * dti) - rhoh_b * (wt[i] + w[i] * dti)) * dzi;
+                const double pb = rho * ((ut[i + jj + 1] + u[i + jj + 1] * dti) - (ut[i + jj] + u[i + jj] * dti)) * dxi
+                                + rho * (fv2 - fv1) * dyi
+                                + (rhoh_t * (wt[i + jj + kk] + w[i + jj + kk] * dti) - rhoh_b * (wt[i + jj] + w[i + jj] * dti)) * dzi;
+                v[m] = make_double2(va ? pa : 0., vb ? pb : 0.);
+            }
+        }
+
+        run<-1>(v, z, A, tf);
+
+        // result to natural order in shared memory, then the Hermitian split (as fft_pow2_kernel<-1, false>)
+        if (A.nst > 1) __syncthreads();
+        #pragma unroll
+        for (int m = 0; m < 8; ++m) z[pad(tf + m * n8)] = v[m];
+        __syncthreads();
+        double* qa = out + A.base_out + line_addr(va ? la : 0, A.n1o, A.s1o, A.s2o);
+        double* qb = out + A.base_out + line_addr(vb ? lb : 0, A.n1o, A.s1o, A.s2o);
+        #pragma unroll
+        for (int m = 0; m < 5; ++m)
+        {
+            if (m == 4 && tf != 0) break;
+            const int k = (m == 4) ? nh : tf + m * n8;
+            const int kn = (k == 0) ? 0 : n - k;
+            const double2 zk = z[pad(k)], zn = z[pad(kn)];
+            const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
+            const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
+            const bool has_im = (k > 0) && (k < nh);
+            const long ek = elem_off<SPLIT>(k, 1, A.esh_out, A.eseg_out), en = elem_off<SPLIT>(n - k, 1, A.esh_out, A.eseg_out);
+            if (va) { qa[ek] = are * A.scale; if (has_im) qa[en] = aim * A.scale; }
+            if (vb) { qb[ek] = bre * A.scale; if (has_im) qb[en] = bim * A.scale; }
+        }
+    }
 }  // namespace
 
 bool fft_pow2_supported(int n) { return n >= 8 && n <= 8 * BLOCK && (n & (n - 1)) == 0; }
@@ -506,6 +590,47 @@ int fft_pow2_plan(FftPlan* p)
     }
     MHH_CUDA_CHECK(cudaMalloc(&p->p2_tw, sizeof(double2) * tw.size()));
     MHH_CUDA_CHECK(cudaMemcpy(p->p2_tw, tw.data(), sizeof(double2) * tw.size(), cudaMemcpyHostToDevice));
+    return MHH_OK;
+}
+
+// Pres_2::input + forward x transform in one pass (pres2_in_fft_x_kernel).  L describes the OUTPUT side as for a forward
+// fft_lines call on the ghost-free layout [k][j < jmax][i < itot] (or the slab chunk layout); k0: first level of the call.
+// Returns MHH_ERR_UNSUPPORTED when the fused pass does not apply (the caller then runs the two separate stages).
+int pres2_in_fft_x(Ctx* c, const FftPlan& plan, const double* u, const double* v, const double* w,
+                   const double* ut, const double* vt, const double* wt, double dt, double* out, const FftLayout& L, int k0)
+{
+    const GridD& gd = c->gd;
+    if (!c->fuse_pres_input || plan.p2_nst <= 0 || plan.n != gd.itot || (gd.jmax & 1) || L.sno != 1 || c->order != 2 || plan.n / 8 > BLOCK)
+        return MHH_ERR_UNSUPPORTED;
+    if (L.esplit_out > 0 && (L.esplit_out & (L.esplit_out - 1))) return MHH_ERR_UNSUPPORTED;
+    P2Args A;
+    A.n = plan.n; A.nst = plan.p2_nst;
+    A.log2n = 0; while ((1 << A.log2n) < plan.n) ++A.log2n;
+    for (int s = 0; s < plan.p2_nst; ++s) { A.rad[s] = plan.p2_rad[s]; A.off[s] = plan.p2_off[s]; }
+    A.tw = plan.p2_tw;
+    A.nlines = L.nlines; A.n1 = L.n1; A.s1 = L.s1; A.s2 = L.s2; A.sn = L.sn; A.base_in = L.base_in;
+    A.n1o = L.n1o; A.s1o = L.s1o; A.s2o = L.s2o; A.sno = L.sno; A.base_out = L.base_out;
+    A.scale = L.scale;
+    auto lg = [](int x) { int l = 0; while ((1 << l) < x) ++l; return l; };
+    A.esh_in = 31; A.eseg_in = 0;
+    A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
+    PresInArgs F{u, v, w, ut, vt, wt, 1. / dt, k0, gd};
+    const int npairs = BLOCK / (plan.n / 8);
+    const size_t smem = (size_t)npairs * ((plan.n + plan.n / 8) + 1) * sizeof(double2);
+    const int nblocks = (L.nlines + 2 * npairs - 1) / (2 * npairs);
+    if (L.esplit_out > 0)
+    {
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(pres2_in_fft_x_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024); attr = true; }
+        MHH_LAUNCH(c, "pres2_in_fft_x", (pres2_in_fft_x_kernel<true><<<nblocks, BLOCK, smem, c->stream>>>(F, out, A)));
+    }
+    else
+    {
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(pres2_in_fft_x_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024); attr = true; }
+        MHH_LAUNCH(c, "pres2_in_fft_x", (pres2_in_fft_x_kernel<false><<<nblocks, BLOCK, smem, c->stream>>>(F, out, A)));
+    }
+    MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
 

@@ -334,6 +334,40 @@ def test_fused_tendency_pass_equals_thermo_advec_diff(cuda_lib, sm, thermo, dims
     g.close(); W.close()
 
 
+@pytest.mark.parametrize("dims", [(64, 16, 12), (512, 8, 3), (16, 6, 5)], ids=["n64", "n512", "n16"])
+def test_fused_pressure_input_equals_input_then_fft(cuda_lib, dims):
+    """mhh_pres_set_fused_input: Pres_2::input evaluated inside the forward x transform gives the same p and tendencies,
+    bit for bit, as the separate input and transform stages."""
+    from microhh_b200 import host as H
+    from microhh_b200 import lib as L
+    itot, jtot, ktot = dims
+    case = make_case(itot=itot, jtot=jtot, ktot=ktot, alpha=1.3, anelastic=True)
+    g, W = _worlds(case)
+    res = []
+    for fused in (0, 1):
+        f = H.Fields(g, slist=[])
+        f.set_rhoref(case["rhoref"], case["rhorefh"])
+        b = H.Boundary(g, f)
+        for n in "uvw":
+            f.mp[n].fld.copy_(_up(g, case[n]))
+            b.boundary_cyclic.exec(f.mp[n].fld)
+        r = np.random.default_rng(11)
+        for n in "uvw":
+            f.at[n].fld.copy_(_up(g, r.uniform(-1e-2, 1e-2, W.shape)))
+        f.mt["w"].fld[:g.kstart + 1] = 0.
+        f.mt["w"].fld[g.kend:] = 0.
+        pres = H.Pres.factory(g, f, "2")
+        pres.set_values()
+        L.check(g.ctx, g.lib.mhh_pres_set_fused_input(g.ctx, fused), "mhh_pres_set_fused_input")
+        pres.exec(0.37)
+        res.append({n + "t": f.mt[n].fld.cpu().numpy().copy() for n in "uvw"} | {"p": f.sd["p"].fld.cpu().numpy().copy()})
+    L.check(g.ctx, g.lib.mhh_pres_set_fused_input(g.ctx, 0), "mhh_pres_set_fused_input")
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    assert np.abs(res[0]["p"]).max() > 0.
+    g.close(); W.close()
+
+
 @pytest.mark.parametrize("rkorder,substep", [(3, 0), (3, 2), (4, 4)])
 def test_fused_pressure_tail_order4(cuda_lib, rkorder, substep):
     """4th order: mhh_pres_exec_rk = Pres_4::exec, Boundary::set_ghost_cells_w(Normal), Timeloop::exec(u,v,w) — bit-identical
