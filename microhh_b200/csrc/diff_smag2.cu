@@ -378,13 +378,13 @@ constexpr int UVW_SLOTS = 6;
             return sm + (q % NS) * 4 * PS;
         };
         stage(0); stage(1); stage(2); stage(3);
-        if (tid < KCHUNK + 2)
+        for (int t = tid; t < KCHUNK + 2; t += NT)       // (the chunk may be longer than the CTA has threads)
         {
-            const int k = min(k0 - 1 + tid, gd.kcells - 1);
-            met[0][tid] = gd.rhoref[k]; met[1][tid] = gd.rhorefh[k]; met[2][tid] = gd.rhoref_i[k];
-            met[3][tid] = gd.rhorefh_i[k]; met[4][tid] = gd.dzi[k]; met[5][tid] = gd.dzhi[k];
-            if (BUOY) { met[6][tid] = threfh[k]; met[7][tid] = g_threfh[k]; }
-            met[8][tid] = 0.25 * gd.dzi[k]; met[9][tid] = 0.25 * gd.dzhi[k]; met[10][tid] = 2. * gd.dzhi[k];
+            const int k = min(k0 - 1 + t, gd.kcells - 1);
+            met[0][t] = gd.rhoref[k]; met[1][t] = gd.rhorefh[k]; met[2][t] = gd.rhoref_i[k];
+            met[3][t] = gd.rhorefh_i[k]; met[4][t] = gd.dzi[k]; met[5][t] = gd.dzhi[k];
+            if (BUOY) { met[6][t] = threfh[k]; met[7][t] = g_threfh[k]; }
+            met[8][t] = 0.25 * gd.dzi[k]; met[9][t] = 0.25 * gd.dzhi[k]; met[10][t] = 2. * gd.dzhi[k];
         }
 
         // tile-plane offsets of the centre and its neighbours
