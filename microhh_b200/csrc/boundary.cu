@@ -15,8 +15,9 @@ namespace
         if (n >= gd.igc * gd.jcells) return;
         const int g = n % gd.igc, j = n / gd.igc;
         const int base = j * gd.icells + k * gd.ijcells;
-        a[base + g] = a[base + gd.iend - gd.igc + g];
-        a[base + gd.iend + g] = a[base + gd.istart + g];
+        const double east = a[base + gd.iend - gd.igc + g], west = a[base + gd.istart + g];   // both loads in flight
+        a[base + g] = east;
+        a[base + gd.iend + g] = west;
     }
 
     __global__ void cyclic_y_kernel(double* __restrict__ a, const GridD gd)
@@ -26,8 +27,9 @@ namespace
         const int k = blockIdx.z;
         if (i >= gd.icells) return;
         const int base = i + k * gd.ijcells;
-        a[base + g * gd.icells] = a[base + (gd.jend - gd.jgc + g) * gd.icells];
-        a[base + (gd.jend + g) * gd.icells] = a[base + (gd.jstart + g) * gd.icells];
+        const double north = a[base + (gd.jend - gd.jgc + g) * gd.icells], south = a[base + (gd.jstart + g) * gd.icells];
+        a[base + g * gd.icells] = north;
+        a[base + (gd.jend + g) * gd.icells] = south;
     }
 
     // 2-D run (jtot == 1): replicate the single row, interior k only (src/boundary_cyclic.cxx:428-441)
