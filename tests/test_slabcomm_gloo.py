@@ -55,6 +55,11 @@ def _worker(rank, world, port, q):
     ok &= np.array_equal(Yk, Y)
     ok &= comm.allreduce_max(float(rank), "cpu") == world - 1
     ok &= float(comm.allreduce_sum([1.0, float(rank)], "cpu")[1]) == sum(range(world))
+    # the pair of dt maxima in one collective; a NaN on ANY rank must come out as NaN on every rank (the CFL guard)
+    m = comm.allreduce_max_many([1.5 + rank, 7. - rank], "cpu")
+    ok &= m == [1.5 + world - 1, 7.]
+    m = comm.allreduce_max_many([float("nan") if rank == 1 else 3., 2.], "cpu")
+    ok &= all(v != v for v in m)
     q.put((rank, ok))
     dist.destroy_process_group()
 
