@@ -1,11 +1,12 @@
 #!/usr/bin/env python
 """bench.py — grid-point-steps/s of a full RK3 LES step (BASELINE.json metric) on N B200s.
 
-Workload (config.workload): gabls1-like LES (advec_2, diff_smag2 with surface-model rows, thermo dry,
-pres_2, RK3) scaled to a 512^3 synthetic grid per GPU (BASELINE.json configs[2]); for N > 1 the domain
-is itot x (N*jtot) x ktot split into y-slabs (weak scaling).
-One "step" = 3 RK substeps, each = cyclic + ghost BCs, evisc, buoyancy, advection, diffusion,
-pressure solve, RK update; the CFL/diffusion-number maxima once per step.
+Workload (config.workload): cases/gabls1 as shipped (advec_2, diff_smag2, thermo dry, swboundary=surface with the
+Monin-Obukhov surface layer solved on the device every substep, swbuffer=1, swlspres=geo fc=1.39e-4, pres_2, RK3;
+only the time-dependent surface temperature, Timedep, is left out) scaled to a 512^3 synthetic grid per GPU
+(BASELINE.json configs[2]); for N > 1 the domain is split into y-slabs (weak scaling).
+One "step" = 3 RK substeps, each = cyclic + ghost BCs, evisc, surface layer, buoyancy, advection, diffusion,
+sponge layer, Coriolis force, pressure solve, RK update; the CFL/diffusion-number maxima once per step.
 
   python bench.py --gpus N --steps K --warmup W            # CUDA path (this repo)
   python bench.py --impl reference ...                      # the reference's own CPU code (oracle/_ref)
@@ -47,6 +48,10 @@ BYTES_PER_POINT = {
     "n2_kernel": 16, "buoyancy_tend_kernel": 24,
     "advec2_cfl_kernel": 24, "smag2_dnmul_kernel": 8,
 }
+# the same launches on SURVEY 8(d)'s unfused rows (roofline.frac_survey)
+SURVEY_BYTES_PER_POINT = {"advec2_smag2_uvw_kernel": 72 + 80, "advec2_smag2_c_kernel": 48 + 32 + 32, "evisc_kernel": 40,
+                          "pres2_out_rk_kernel": 56 + 96, "pres2_in_kernel": 56, "pres2_tdma_kernel": 32,
+                          "fft_fwd_x": 16, "fft_fwd_y": 16, "fft_bwd_y": 16, "fft_bwd_x": 16}
 BYTES_PER_STEP = 3 * 608 + 32       # 1856 B / grid-point-step (the reference's operator-by-operator passes)
 # what this implementation's fused passes move: evisc 40, momentum 88, scalar + its RK 64, pres_in 56, 4 FFT passes 64,
 # tdma 28 (two sweeps over p + pivot checkpoints), output+RK 104 per substep; the cfl / dnmul maxima ride in the evisc pass;
@@ -58,7 +63,10 @@ def ncu_traffic(kernel, n):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch (GB) from the committed ncu --set full capture of this
     workload (profiles/r01_traffic.json), or None."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+        path = os.path.join(ROOT, "profiles", "r02_traffic.json")
+        if not os.path.exists(path):
+            path = os.path.join(ROOT, "profiles", "r01_traffic.json")
+        with open(path) as f:
             t = json.load(f)
         return t["gb_per_launch"].get(kernel) if t.get("n") == n else None
     except (OSError, ValueError, KeyError):
@@ -87,15 +95,24 @@ def les_ini(itot, jtot, ktot):
         "diff": dict(swdiff="smag2", cs=0.1, dnmax=0.3, tPr=1. / 3.),
         "pres": dict(swpres="2"),
         "thermo": dict(swthermo="dry", thref0=263.5),
-        "boundary": dict(mbcbot="noslip", mbctop="freeslip", swboundary="surface",
-                         sbc={"th": dict(sbcbot="dirichlet", sbctop="neumann", sbot=265., stop=0.01)}),
+        # cases/gabls1/gabls1.ini: [boundary] (without swtimedep), [buffer] (zstart = 300 of 400 m), [force]
+        "boundary": dict(mbcbot="noslip", mbctop="freeslip", swboundary="surface", z0m=0.1, z0h=0.1,
+                         sbc={"th": dict(sbcbot="dirichlet", sbctop="flux", sbot=265., stop=0.)}),
+        "buffer": dict(swbuffer=True, zstart=0.75 * size * ktot, sigma=0.00223, beta=2.),
+        "force": dict(swlspres="geo", fc=1.39e-4),
         "fields": dict(visc=1e-5, svisc=1e-5),
         "time": dict(rkorder=3, dt=1.0, dtmax=60., adaptivestep=True),
     }
 
 
+def les_profs(z):
+    """cases/gabls1/gabls1_input.py: u = u_geo = 8, th = 265 up to 100 m, then 0.01 K/m."""
+    n = len(z)
+    return dict(u=np.full(n, 8.), v=np.zeros(n), th=265. + 0.01 * np.clip(z - 100., 0., None), u_geo=np.full(n, 8.), v_geo=np.zeros(n))
+
+
 def synthetic_fields(shape, ks, ke, z, seed, jslice=None):
-    """u,v ~ U(-1,1)+8, w ~ 0.2 U(-1,1) (0 at walls), th = 263.5 + 0.003 z + U(-0.05,0.05)."""
+    """u,v ~ U(-1,1)+8, w ~ 0.2 U(-1,1) (0 at walls), th = gabls1's profile + U(-0.05,0.05)."""
     rng = np.random.default_rng(seed)
     kc = shape[0]
     zf = np.zeros(kc)
@@ -105,14 +122,8 @@ def synthetic_fields(shape, ks, ke, z, seed, jslice=None):
     w = 0.2 * rng.uniform(-1, 1, shape)
     w[:ks + 1] = 0.
     w[ke:] = 0.
-    th = 263.5 + 0.003 * zf[:, None, None] + rng.uniform(-0.05, 0.05, shape)
+    th = (265. + 0.01 * np.clip(zf - 100., 0., None))[:, None, None] + rng.uniform(-0.05, 0.05, shape)
     return dict(u=u, v=v, w=w, th=th)
-
-
-def surface_planes(shape2d, rng):
-    return dict(z0m=np.full(shape2d, 0.1), dudz=rng.uniform(0.05, 0.1, shape2d), dvdz=rng.uniform(-0.01, 0.01, shape2d),
-                dbdz=rng.uniform(-1e-5, 1e-5, shape2d), ufluxbot=rng.uniform(-0.02, 0., shape2d),
-                vfluxbot=rng.uniform(-0.002, 0.002, shape2d), sfluxbot=rng.uniform(-0.01, 0., shape2d))
 
 
 class ClockSampler(threading.Thread):
@@ -175,19 +186,20 @@ def cpu_reference_run(n, steps, warmup):
 
 
 def _cpu_reference_run(n, steps, warmup):
-    """The reference's own CPU code (oracle/_ref, 1 thread: its non-MPI build is single-threaded,
-    src/model.cxx:325) on a bounded n^3 sample of the same LES configuration."""
+    """The reference's own CPU code (oracle/_ref timing build, 1 thread: its non-MPI build is single-threaded,
+    src/model.cxx:325) on a bounded n^3 sample of the same gabls1 configuration (surface layer, sponge, Coriolis included)."""
+    import oracle.ref as R
+    R.use_perf_build()
     from oracle.les import OracleLES
     ini = les_ini(n, n, n)
     g = ini["grid"]
     z = (np.arange(n) + 0.5) * (g["zsize"] / n)
     shape = (n + 2, n + 2, n + 2)
     f = synthetic_fields(shape, 1, n + 1, z, seed=666)
-    S = surface_planes(shape[1:], np.random.default_rng(7))
-    S.update(ufluxtop=np.zeros(shape[1:]), vfluxtop=np.zeros(shape[1:]), sfluxtop=np.zeros(shape[1:]))
+    bi = ini["boundary"]
     o = OracleLES(n, n, n, g["xsize"], g["ysize"], g["zsize"], z, f, swadvec="2", swdiff="smag2", visc=1e-5, svisc=1e-5,
-                  cs=0.1, tPr=1. / 3., thref0=263.5, surface=S, mbcbot="noslip", mbctop="freeslip",
-                  sbc=ini["boundary"]["sbc"], dt=1.0, dtmax=60., dnmax=0.3)
+                  cs=0.1, tPr=1. / 3., thref0=263.5, mbcbot="noslip", mbctop="freeslip", sbc=bi["sbc"], dt=1.0, dtmax=60.,
+                  dnmax=0.3, buffer=ini["buffer"], force=ini["force"], profs=les_profs(z), mo=dict(z0m=bi["z0m"], z0h=bi["z0h"]))
     for _ in range(warmup):
         o.step()
     t0 = time.perf_counter()
@@ -200,7 +212,9 @@ def _cpu_reference_run(n, steps, warmup):
 
 def _cpu_worker(n, steps, warmup, barrier, q):
     with quiet_stdout():
-        from oracle.les import OracleLES  # noqa: F401  (loads oracle/_ref before the barrier)
+        import oracle.ref as R
+        R.use_perf_build()
+        R.lib()                     # loads oracle/_ref before the barrier
         barrier.wait()
         q.put(_cpu_reference_run(n, steps, warmup))
 
@@ -211,6 +225,10 @@ def cpu_reference_run_all_cores(n, steps, warmup):
     decomposition of one domain could reach (no halo exchange, no transposes), sharing the host's memory bandwidth.
     Returns (aggregate grid-point-steps/s from the slowest replica, seconds per step, P)."""
     import multiprocessing as mp
+    import oracle.ref as R
+    R.use_perf_build()
+    with quiet_stdout():
+        R.lib()                     # also in the parent: the driver's loaded-library record then lists liboracle_ref*.so
     P = max(1, min(len(os.sched_getaffinity(0)), 64))
     if P == 1:
         v, sps = cpu_reference_run(n, steps, warmup)
@@ -227,6 +245,107 @@ def cpu_reference_run_all_cores(n, steps, warmup):
     return P * n ** 3 / sps, sps, P
 
 
+WORKLOAD = ("cases/gabls1 LES {shape} (advec_2, smag2, thermo dry, MO surface layer on device, swbuffer=1, swlspres=geo, pres_2, RK3; "
+            "Timedep surface temperature left out), {n}^3 grid points per GPU, y-slabs")
+
+
+class HostDrain:
+    """Device -> host return of the prognostic fields for a host model that keeps its state in (pinned) host memory: the
+    download of step n runs on its own copy stream while step n+1 computes (two device staging slots)."""
+
+    def __init__(self, model, pinned_out):
+        import torch
+        self.model, self.torch, self.out = model, torch, pinned_out
+        f = model.fields
+        self.stage = [{n: torch.empty_like(fld.fld) for n, fld in f.ap.items()} for _ in range(2)]
+        self.stream = torch.cuda.Stream(device=model.grid.device)
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]
+        self.n = 0
+
+    def submit(self):
+        torch = self.torch
+        slot = self.n % 2
+        cur = torch.cuda.current_stream(self.model.grid.device)
+        if self.n >= 2:
+            cur.wait_event(self.done[slot])
+        for n, fld in self.model.fields.ap.items():
+            self.stage[slot][n].copy_(fld.fld, non_blocking=True)
+        self.ready[slot].record(cur)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.ready[slot])
+            for n, dst in self.out.items():
+                dst.copy_(self.stage[slot][n], non_blocking=True)
+            self.done[slot].record(self.stream)
+        self.n += 1
+
+    def finish(self):
+        self.stream.synchronize()
+
+
+def secondary_benches(dev, steps=3):
+    """Driver-visible numbers for the other BASELINE configs on one GPU (ms per full step, CUDA events, after 2 warm-up steps):
+    drycblles 64^3 (configs[0], launch-bound), moser180 256x192x128 and a 512x512x256 channel (configs[3]: advec_4, diff_4,
+    pres_4, RK3, tanh-stretched z, uflux forcing)."""
+    import torch
+    from microhh_b200.model import Model
+    out = {}
+
+    def run(tag, ini, z, init, mo=False, profs=None):
+        m = Model(ini, z, device=dev, mo=mo, profs=profs)
+        g, f = m.grid, m.fields
+        for n, a in init(g).items():
+            f.ap[n].fld.copy_(torch.from_numpy(a).to(dev))
+        for _ in range(2):
+            m.step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = g.launch_count()
+        e0.record()
+        for _ in range(steps):
+            m.step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        pts = g.itot * g.jtot * g.ktot
+        st = m.print_status()
+        out[tag] = {"ms_per_step": round(ms, 4), "grid_point_steps_per_s": round(pts / (ms * 1e-3), 1),
+                    "launches_per_step": (g.launch_count() - l0) // steps, "div": st["div"], "cfl": st["cfl"]}
+        g.close()
+
+    def dns_ini(itot, jtot, ktot):
+        return {"grid": dict(itot=itot, jtot=jtot, ktot=ktot, xsize=6.28, ysize=3.14, zsize=2., swspatialorder="4"),
+                "advec": dict(swadvec="4", cflmax=1.0), "diff": dict(swdiff="4", dnmax=0.4), "pres": dict(swpres="4"),
+                "boundary": dict(mbcbot="noslip", mbctop="noslip"), "fields": dict(visc=1e-5),
+                "force": dict(swlspres="uflux", uflux=0.0282), "time": dict(rkorder=3, dt=1e-3, dtmax=0.1, adaptivestep=True)}
+
+    def dns_z(ktot, alpha=2.0):
+        zh = 0.5 * 2. * (1. + np.tanh(alpha * (2. * np.arange(ktot + 1) / ktot - 1.)) / np.tanh(alpha))
+        return 0.5 * (zh[1:] + zh[:-1])
+
+    def dns_init(z):
+        def init(g):
+            rng = np.random.default_rng(1)
+            zf = np.zeros(g.kcells); zf[g.kstart:g.kend] = z
+            r = {}
+            for n, amp, mean in (("u", 0.01, 0.11), ("v", 0.01, 0.), ("w", 0.01, 0.)):
+                a = (zf * (2. - zf))[:, None, None] * mean + amp * rng.uniform(-1, 1, g.shape)
+                if n == "w":
+                    a[:g.kstart + 1] = 0.; a[g.kend:] = 0.
+                r[n] = a
+            return r
+        return init
+
+    for tag, dims in (("dns4_256x192x128", (256, 192, 128)), ("dns4_512x512x256", (512, 512, 256))):
+        z = dns_z(dims[2])
+        run(tag, dns_ini(*dims), z, dns_init(z))
+    n = 64
+    ini = les_ini(n, n, n)
+    z = (np.arange(n) + 0.5) * (ini["grid"]["zsize"] / n)
+    run("les_gabls1_64x64x64", ini, z, lambda g: synthetic_fields(g.shape, g.kstart, g.kend, z, seed=5), mo=True, profs=les_profs(z))
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -234,8 +353,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--size", type=int, default=512, help="itot = jtot(per GPU) = ktot")
-    ap.add_argument("--cpu-size", type=int, default=96)
+    ap.add_argument("--cpu-size", type=int, default=None, help="edge of the CPU sample grid (default 96 for cpu_baseline, 192 for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -245,15 +365,22 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        ns = args.cpu_size
-        value, s_per_step, cores = cpu_reference_run_all_cores(ns, max(args.steps, 1), min(args.warmup, 1))
+        # DRAM-resident sample (192^3: 57 MB per field, far beyond a core's cache share, like 512^3); at most 1 warm-up and
+        # 5 timed steps per replica so that the arm ends within a few minutes whatever --steps says
+        ns = args.cpu_size or 192
+        steps = max(1, min(args.steps, 5))
+        value, s_per_step, cores = cpu_reference_run_all_cores(ns, steps, min(args.warmup, 1))
+        import oracle.ref as R
         line = {"impl": "reference", "metric": "grid-point-steps/s (full RK3 step)", "value": value, "unit": "grid-point-steps/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * s_per_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"gabls1-like LES {n}^3 per GPU (advec_2, smag2+surface rows, thermo dry, pres_2, RK3)",
-                           "sample": f"{ns}^3"},
+                "config": {"workload": WORKLOAD.format(shape=f"{n}^3", n=n), "sample": f"{ns}^3 per core",
+                           "timed_steps_per_replica": steps,
+                           "differences_from_the_gpu_arm": f"{ns}^3 grid per core instead of one {n}^3 grid (the reference's multi-core mode is "
+                                                           "MPI, absent here), FFTW replaced by the oracle's DFT shim"},
                 "cpu_baseline": {"value": value, "unit": "grid-point-steps/s", "cores": cores, "kind": "reference",
-                                 "sample": f"{args.steps} full RK3 steps of the same LES configuration on a {ns}^3 grid per core, "
+                                 "build": os.path.basename(R.LIB_PATH) + " (g++ -O3 -march=x86-64-v3; the reference's default is -O3 -march=native)",
+                                 "sample": f"{steps} full RK3 steps of the same gabls1 configuration on a {ns}^3 grid per core, "
                                            f"{cores} concurrent serial replicas (the reference's MPI build is absent; its serial build is "
                                            "single-threaded), reference sources compiled in place (oracle/_ref), FFTW replaced by the "
                                            "oracle's DFT shim"},
@@ -274,26 +401,28 @@ def main():
         nccl_env_defaults()
         dist.init_process_group("nccl", device_id=dev)
 
+    # ---- multi-GPU values, driver-visible: the slab decomposition against one GPU on a small case, before anything is timed
+    slab_parity = None
+    if world > 1:
+        from tests.slab_parity import parity_check
+        slab_parity = parity_check(rank, world, dev, dims=(64, 64 * world, 32))
+
     itot, jtot, ktot = weak_scaling_shape(n, world)
     ini = les_ini(itot, jtot, ktot)
     z = (np.arange(ktot) + 0.5) * (ini["grid"]["zsize"] / ktot)
+    profs = les_profs(z)
     if world > 1:
         from microhh_b200.multigpu import SlabModel
-        model = SlabModel(ini, z, device=dev, rank=rank, world=world)
+        model = SlabModel(ini, z, device=dev, rank=rank, world=world, profs=profs, mo=True)
     else:
-        model = Model(ini, z, device=dev)
+        model = Model(ini, z, device=dev, profs=profs, mo=True)
     g = model.grid
     host = synthetic_fields(g.shape, g.kstart, g.kend, z, seed=666 + rank)
-    S = surface_planes(g.shape2d, np.random.default_rng(7 + rank))
-    model.surface = {k: torch.from_numpy(v).to(dev) for k, v in S.items()}
     f = model.fields
-    f.mp["u"].flux_bot.copy_(model.surface["ufluxbot"]); f.mp["v"].flux_bot.copy_(model.surface["vfluxbot"])
-    f.sp["th"].flux_bot.copy_(model.surface["sfluxbot"])
-    # pinned host staging of the prognostic fields (e2e leg copies from here every step)
+    # pinned host staging of the prognostic fields (e2e leg copies from / to here every step)
     pinned = {k: torch.from_numpy(v).pin_memory() for k, v in host.items()}
-    prog = {"u": f.mp["u"].fld, "v": f.mp["v"].fld, "w": f.mp["w"].fld, "th": f.sp["th"].fld}
-    for k in prog:
-        prog[k].copy_(pinned[k], non_blocking=True)
+    for k in pinned:
+        f.ap[k].fld.copy_(pinned[k], non_blocking=True)
     torch.cuda.synchronize()
 
     def barrier():
@@ -328,15 +457,17 @@ def main():
     ms = float(t.item())
     points = n * n * n * world
     value = points * args.steps / (ms * 1e-3)
+    status_timed = model.print_status()
 
-    # ---- e2e: same step through the public API with HOST buffers: H2D of the prognostic fields from pinned
-    # memory every step, D2H of the step's status line (cfl, dn, div, mom, tke, mass) -----------------------
+    # ---- e2e: the same step for a host model that keeps its state in HOST memory (the reference's CPU build): every step
+    # uploads the four prognostic fields from pinned memory, runs the step through the public API (Model.step), and
+    # downloads the four updated fields plus the status line.  Upload of step n+1 and download of step n-1 overlap the
+    # compute of step n on two copy streams; every copy, including the first upload and the last download, is timed.
     h2d = sum(v.numel() * 8 for v in pinned.values())
-    # The upload of step n+1 (copy stream, second staging slot) overlaps the compute of step n (model.HostFeed); every
-    # step's upload, including the first, lies inside the timed region.
     from microhh_b200.model import HostFeed
     e2e_steps = max(2, min(args.steps, 10))
-    feed = HostFeed(model)
+    pinned_out = {k: torch.empty_like(v).pin_memory() for k, v in pinned.items()}
+    feed, drain = HostFeed(model), HostDrain(model, pinned_out)
     barrier()
     ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ee0.record()
@@ -348,7 +479,9 @@ def main():
             feed.submit(pinned)
         model.timeloop.dt, model.timeloop.idt = 1.0, int(1e9)
         model.step()
+        drain.submit()
         status = model.print_status()        # device reductions + D2H of 6 scalars
+    drain.finish()
     ee1.record()
     barrier()
     ems = ee0.elapsed_time(ee1)
@@ -356,6 +489,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = points * e2e_steps / (float(t.item()) * 1e-3)
+    del feed, drain, pinned_out
 
     if rank != 0:
         if world > 1:
@@ -376,36 +510,53 @@ def main():
         bpp.update({"advec2_smag2_uvw_kernel": 80, "pres2_out_rk_kernel": 96, "advec2_smag2_c_kernel": 58.67})
     algo_bytes = bpp.get(dom_name, 0) * pts_local
     achieved = algo_bytes / (dom_ms / dom_count * 1e-3) / 1e9 if dom_count else 0.
+    survey_bytes = SURVEY_BYTES_PER_POINT.get(dom_name, 0) * pts_local
     kernels = {k: {"ms_per_launch": round(v[0] / v[1], 4), "launches": v[1], "share": round(v[0] / total_kernel_ms, 4),
                    "gbs": round(bpp[k] * pts_local / (v[0] / v[1] * 1e-3) / 1e9, 1) if k in bpp else None}
                for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}
+    step_s = ms / args.steps * 1e-3
 
     line = {
         "metric": "grid-point-steps/s (full RK3 step)", "value": value, "unit": "grid-point-steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"gabls1-like LES {itot}x{jtot}x{ktot} (advec_2, smag2+surface rows, thermo dry, pres_2, RK3), "
-                               f"{n}^3 grid points per GPU, y-slabs", "l2": "inputs larger than L2 (each 3-D field 1.09 GB)",
-                   "bytes_per_gridpoint_step": BYTES_PER_STEP},
+        "config": {"workload": WORKLOAD.format(shape=f"{itot}x{jtot}x{ktot}", n=n),
+                   "l2": "inputs larger than L2 (each 3-D field 1.09 GB)",
+                   "bytes_per_gridpoint_step_moved": BYTES_PER_STEP_FUSED, "bytes_per_gridpoint_step_survey_8d": BYTES_PER_STEP},
         "clocks": sampler.summary(),
-        "e2e": {"value": e2e_value, "unit": "grid-point-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 6 * 8,
-                "steps": e2e_steps},
+        "e2e": {"value": e2e_value, "unit": "grid-point-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": h2d + 6 * 8,
+                "steps": e2e_steps,
+                "host_model": "state in pinned host memory: 4 prognostic fields up and back down every step (double-buffered on two "
+                              "copy streams) + the status line; PCIe-bound.  A device-resident host (the reference's USECUDA build, "
+                              "src/model.cxx:561-579) moves only the status line and runs at `value`."},
         "gpu_launches": int(launches),
-        "step_hbm_frac": round(BYTES_PER_STEP * pts_local / (ms / args.steps * 1e-3) / 1e9 / peak, 4),
-        "step_hbm_frac_fused_passes": round(BYTES_PER_STEP_FUSED * pts_local / (ms / args.steps * 1e-3) / 1e9 / peak, 4),
+        # the fraction of the measured HBM peak on the bytes the fused passes actually move (headline), and — labelled — the
+        # same time expressed in the reference's operator-by-operator traffic of SURVEY 8(d) (an equivalent-work speed-up)
+        "step_hbm_frac": round(BYTES_PER_STEP_FUSED * pts_local / step_s / 1e9 / peak, 4),
+        "step_equivalent_reference_traffic_frac": round(BYTES_PER_STEP * pts_local / step_s / 1e9 / peak, 4),
         "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": round(achieved, 1), "peak": peak, "peak_kind": peak_kind,
-                     "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom_name, n) if world == 1 else None,
+                     "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "frac_survey": round(survey_bytes / (dom_ms / dom_count * 1e-3) / 1e9 / peak, 4) if dom_count else None,
+                     "frac_survey_note": "the same launch time on SURVEY 8(d)'s unfused rows (advec uvw 72 + diff_smag2 uvw 80 B/pt)",
+                     "traffic": ncu_traffic(dom_name, n) if world == 1 else None,
                      "traffic_unit": "GB per launch (ncu dram read+write; the captured launch is one that reads the tendencies, "
                                      "88 B/pt = 11.81 GB algorithmic)",
                      "algorithmic_gb_per_launch": round(algo_bytes / 1e9, 3)},
         "kernels": kernels,
-        "status": status,
+        "status": status_timed,
     }
+    if slab_parity is not None:
+        line["slab_parity"] = slab_parity
+    if world == 1 and not args.no_secondary:
+        del model
+        torch.cuda.empty_cache()
+        line["secondary"] = secondary_benches(dev)
     if not args.no_cpu_baseline and world == 1:
-        ns = args.cpu_size
+        ns = args.cpu_size or 96
         v, s_per_step = cpu_reference_run(ns, 3, 1)
         line["cpu_baseline"] = {"value": v, "unit": "grid-point-steps/s", "cores": 1, "kind": "reference",
-                                "sample": f"3 full RK3 steps of the same LES configuration on a {ns}^3 grid (oracle/_ref)"}
+                                "sample": f"3 full RK3 steps of the same gabls1 configuration on a {ns}^3 grid "
+                                          "(oracle/_ref timing build, -O3 -march=x86-64-v3)"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -218,6 +218,11 @@ typedef struct mhh_surface_args
 /* Boundary_surface::exec, src/boundary_surface.cxx:827-981: calc_dutot, stability / stability_neutral, surfm, surfs(th),
  * calc_duvdz_mo, calc_dbdz_mo with the cyclic fills in between. */
 int mhh_boundary_surface_exec(mhh_ctx* ctx, const mhh_surface_args* args);
+/* The same in stages for a y-slab rank (the MPI build's boundary_cyclic.exec_2d calls inside Boundary_surface::exec,
+ * src/boundary_surface.cxx:850,930-931, become neighbour exchanges between the stages): stages is a mask of
+ * 1 = calc_dutot (+ east/west fill), 2 = stability + surfm fluxes (+ east/west fills of ufluxbot, vfluxbot), 4 = the rest.
+ * The caller exchanges the north/south rows of dutot after stage 1 and of ufluxbot, vfluxbot after stage 2. */
+int mhh_boundary_surface_exec_stages(mhh_ctx* ctx, const mhh_surface_args* args, int stages);
 /* surfs for a further scalar, src/boundary_surface.cxx:294-343,935-946 */
 int mhh_surface_scalar(mhh_ctx* ctx, int bcbot, const double* var, double* varbot, double* vargradbot, double* varfluxbot,
                        const double* ustar, const double* obuk, const double* z0h);

@@ -80,7 +80,7 @@ struct SurfaceArgs
     double *dutot, *dudz, *dvdz, *dbdz;
 };
 int surface_lut(Ctx*, int, int, double, double);
-int surface_exec(Ctx*, const SurfaceArgs&);
+int surface_exec(Ctx*, const SurfaceArgs&, int stages);
 int surface_scalar(Ctx*, int, const double*, double*, double*, double*, const double*, const double*, const double*);
 // pres_2.cu / pres_4.cu
 int pres2_set_values(Ctx*);
@@ -106,6 +106,32 @@ static int read_max(Ctx* c, unsigned long long* slot, double* out)
     *out = d;
     return MHH_OK;
 }
+
+// Lazy-tendency guard: a tendency array the fused last-substep tails left UNDEFINED (mhh_set_lazy_tendencies) is logically zero.
+// Only mhh_advec2_smag2_exec[_rk] / mhh_smag2_exec start from 0 without reading it; every other entry that reads or accumulates
+// into a tendency calls this first, which writes the zeros on demand (u,v,w tendencies as a group: the fused pass tests all three).
+static int materialize_tend(Ctx* c, const double* p)
+{
+    if (!c->lazy_tend || p == nullptr) return MHH_OK;
+    const size_t bytes = sizeof(double) * c->gd.ncells;
+    if (c->fresh_uvw[0] != nullptr && (p == c->fresh_uvw[0] || p == c->fresh_uvw[1] || p == c->fresh_uvw[2]))
+    {
+        for (auto& fp : c->fresh_uvw)
+        {
+            MHH_CUDA_CHECK(cudaMemsetAsync(const_cast<double*>(fp), 0, bytes, c->stream));
+            fp = nullptr;
+        }
+    }
+    for (auto& fp : c->fresh_s)
+        if (fp == p)
+        {
+            MHH_CUDA_CHECK(cudaMemsetAsync(const_cast<double*>(fp), 0, bytes, c->stream));
+            fp = nullptr;
+        }
+    return MHH_OK;
+}
+#define MHH_TEND(p) do { if (int e__ = mhh::materialize_tend(c, p)) return e__; } while (0)
+#define MHH_TENDS(arr, n) do { if (arr) for (int q__ = 0; q__ < (n); ++q__) MHH_TEND((arr)[q__]); } while (0)
 
 // FFT stages (src/fft.cxx:335-448 serial, :452-583 MPI). x lines live in the slab layout
 // X = [k][j<jmax][i<itot]; y lines in Y = [k][j<jtot][ii<iblock] (identical when npy == 1).
@@ -385,6 +411,7 @@ int mhh_advec_exec(mhh_ctx* c, int scheme, const double* u, const double* v, con
                    const int* limit_flags)
 {
     CTX_CHECK(c);
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt); MHH_TENDS(st, ns);
     switch (scheme)
     {
         case MHH_ADVEC_2: return advec2_exec(c, u, v, w, ut, vt, wt, ns, s, st);
@@ -426,17 +453,18 @@ int mhh_advec_time_limit(mhh_ctx* c, int scheme, const double* u, const double* 
 // ---------------------------------------------------------------- Diff
 int mhh_diff2_exec(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
                    double visc, int ns, const double* const* s, double* const* st, const double* svisc)
-{ CTX_CHECK(c); return diff2_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
+{ CTX_CHECK(c); MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt); MHH_TENDS(st, ns); return diff2_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
 
 int mhh_diff4_exec(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt,
                    double visc, int ns, const double* const* s, double* const* st, const double* svisc)
-{ CTX_CHECK(c); return diff4_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
+{ CTX_CHECK(c); MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt); MHH_TENDS(st, ns); return diff4_exec(c, u, v, w, ut, vt, wt, visc, ns, s, st, svisc); }
 
 int mhh_advec4_diff4_exec(mhh_ctx* c, const double* u, const double* v, double* w, double* ut, double* vt, double* wt,
                           double visc, int ns, const double* const* s, double* const* st, const double* svisc)
 {
     CTX_CHECK(c);
     if (c->order != 4) { c->last_error = "mhh_advec4_diff4_exec needs swspatialorder=4"; return MHH_ERR_ARG; }
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt); MHH_TENDS(st, ns);
     // src/model.cxx:387-392: [w ghost rows Conservation-type on entry] advec->exec; set_ghost_cells_w(Normal); diff->exec
     if (int e = advec4_exec_diff_uv(c, u, v, w, ut, vt, wt, ns, s, st, visc)) return e;
     if (int e = ghost_cells_w_exec(c, w, 0)) return e;
@@ -571,7 +599,7 @@ int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
 
 // ---------------------------------------------------------------- Thermo_dry (next row)
 int mhh_thermo_set_ref(mhh_ctx* c, const double* thref, const double* threfh) { CTX_CHECK(c); return thermo_set_ref(c, thref, threfh); }
-int mhh_thermo_dry_exec(mhh_ctx* c, double* wt, const double* th) { CTX_CHECK(c); return thermo_buoyancy_tend(c, wt, th); }
+int mhh_thermo_dry_exec(mhh_ctx* c, double* wt, const double* th) { CTX_CHECK(c); MHH_TEND(wt); return thermo_buoyancy_tend(c, wt, th); }
 int mhh_thermo_dry_N2(mhh_ctx* c, const double* th, double* N2) { CTX_CHECK(c); return thermo_n2(c, N2, th); }
 
 // ---- Boundary_surface ----
@@ -586,16 +614,18 @@ int mhh_surface_get_lut(mhh_ctx* c, float* zL, float* f)
     std::memcpy(f, c->surf_lut_host.data() + n, n * sizeof(float));
     return MHH_OK;
 }
-int mhh_boundary_surface_exec(mhh_ctx* c, const mhh_surface_args* a)
+int mhh_boundary_surface_exec_stages(mhh_ctx* c, const mhh_surface_args* a, int stages)
 {
     CTX_CHECK(c);
     if (!a || !a->u || !a->v || !a->ustar || !a->obuk || !a->dutot || !a->z0m || (a->thermo && (!a->th || !a->nobuk)))
     { c->last_error = "mhh_boundary_surface_exec: null pointer"; return MHH_ERR_ARG; }
+    if (stages < 1 || stages > 7) { c->last_error = "mhh_boundary_surface_exec_stages: stages is a mask of 1, 2, 4"; return MHH_ERR_ARG; }
     SurfaceArgs s{a->mbcbot, a->thermo, a->thermobc, a->u, a->v, a->ubot, a->vbot, a->ufluxbot, a->vfluxbot, a->ugradbot,
                   a->vgradbot, a->th, a->thbot, a->thgradbot, a->thfluxbot, a->ustar, a->obuk, a->nobuk, a->z0m, a->z0h,
                   a->dutot, a->dudz, a->dvdz, a->dbdz};
-    return surface_exec(c, s);
+    return surface_exec(c, s, stages);
 }
+int mhh_boundary_surface_exec(mhh_ctx* c, const mhh_surface_args* a) { return mhh_boundary_surface_exec_stages(c, a, 7); }
 int mhh_surface_scalar(mhh_ctx* c, int bcbot, const double* var, double* varbot, double* vargradbot, double* varfluxbot,
                        const double* ustar, const double* obuk, const double* z0h)
 { CTX_CHECK(c); return surface_scalar(c, bcbot, var, varbot, vargradbot, varfluxbot, ustar, obuk, z0h); }
@@ -610,13 +640,14 @@ int mhh_buffer_plan(mhh_ctx* c, double zstart, double sigma, double beta, int* b
     return MHH_OK;
 }
 int mhh_buffer_exec(mhh_ctx* c, double* at, const double* a, const double* abuf, int is_w)
-{ CTX_CHECK(c); if (!at || !a || !abuf) { c->last_error = "mhh_buffer_exec: null pointer"; return MHH_ERR_ARG; } return buffer_exec(c, at, a, abuf, is_w); }
+{ CTX_CHECK(c); if (!at || !a || !abuf) { c->last_error = "mhh_buffer_exec: null pointer"; return MHH_ERR_ARG; } MHH_TEND(at); return buffer_exec(c, at, a, abuf, is_w); }
 int mhh_force_pressure(mhh_ctx* c, double* ut, double fbody)
-{ CTX_CHECK(c); return force_level_source(c, 0, ut, fbody, nullptr, nullptr, nullptr); }
+{ CTX_CHECK(c); MHH_TEND(ut); return force_level_source(c, 0, ut, fbody, nullptr, nullptr, nullptr); }
 int mhh_force_fixed_flux(mhh_ctx* c, double* ut, const double* u, double uflux, double utrans, double dt, double* fbody_out)
 {
     CTX_CHECK(c);
     // enforce_fixed_flux, src/force.cxx:63-75, with the two calc_mean calls of Force::exec :593-594
+    MHH_TEND(ut);
     double u_mean, ut_mean;
     if (int e = mhh_mean(c, u, &u_mean)) return e;
     if (int e = mhh_mean(c, ut, &ut_mean)) return e;
@@ -626,13 +657,13 @@ int mhh_force_fixed_flux(mhh_ctx* c, double* ut, const double* u, double uflux, 
 }
 int mhh_force_coriolis(mhh_ctx* c, double* ut, double* vt, const double* u, const double* v, const double* ug,
                        const double* vg, double fc, double utrans, double vtrans)
-{ CTX_CHECK(c); return force_coriolis(c, ut, vt, u, v, ug, vg, fc, utrans, vtrans); }
+{ CTX_CHECK(c); MHH_TEND(ut); MHH_TEND(vt); return force_coriolis(c, ut, vt, u, v, ug, vg, fc, utrans, vtrans); }
 int mhh_force_large_scale_source(mhh_ctx* c, double* st, const double* sls)
-{ CTX_CHECK(c); return force_level_source(c, 1, st, 0., sls, nullptr, nullptr); }
+{ CTX_CHECK(c); MHH_TEND(st); return force_level_source(c, 1, st, 0., sls, nullptr, nullptr); }
 int mhh_force_nudge(mhh_ctx* c, double* at, const double* fldmean, const double* ref, const double* factor)
-{ CTX_CHECK(c); return force_level_source(c, 2, at, 0., fldmean, ref, factor); }
+{ CTX_CHECK(c); MHH_TEND(at); return force_level_source(c, 2, at, 0., fldmean, ref, factor); }
 int mhh_force_subsidence(mhh_ctx* c, int mode, double* st, const double* s, const double* wls)
-{ CTX_CHECK(c); return force_wls(c, mode, st, s, wls); }
+{ CTX_CHECK(c); MHH_TEND(st); return force_wls(c, mode, st, s, wls); }
 
 // ---------------------------------------------------------------- Pres
 int mhh_pres_set_values(mhh_ctx* c)
@@ -673,6 +704,7 @@ double* mhh_pres_work(mhh_ctx* c) { return c ? c->work_p : nullptr; }
 int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt, double dt)
 {
     PRES_READY(c);
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
     // cyclic BCs of the tendencies, src/pres_2.cxx:180-181 / src/pres_4.cxx:284-286
     if (c->npy == 1)
     {
@@ -689,6 +721,7 @@ int mhh_pres_input_to(mhh_ctx* c, const double* u, const double* v, const double
 {
     PRES_READY(c);
     if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
     return pres2_input(c, u, v, w, ut, vt, wt, dt, dst);
 }
 // Off by default: on B200 the fused pass (1.70 ms at 512^3) only equals pres2_in (1.16) + fft_fwd_x (0.53); it moves 16 B/pt less.
@@ -748,6 +781,7 @@ int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
 {
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
     int e;
     if ((e = pres_input_fft_forward(c, u, v, w, ut, vt, wt, dt))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
@@ -772,6 +806,7 @@ int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, do
 {
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec_rk is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
+    MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
     int e;
     if ((e = pres_input_fft_forward(c, u, v, w, ut, vt, wt, dt_sub))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
@@ -819,7 +854,7 @@ int mhh_set_bc(mhh_ctx* c, double* a, double* agrad, double* aflux, int sw, doub
 
 // ---------------------------------------------------------------- Timeloop
 int mhh_rk_substep(mhh_ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
-{ CTX_CHECK(c); return rk_substep(c, rkorder, substep, dt, nfields, a, at); }
+{ CTX_CHECK(c); MHH_TENDS(at, nfields); return rk_substep(c, rkorder, substep, dt, nfields, a, at); }
 double mhh_rk_sub_dt(int rkorder, int substep, double dt) { return rk_sub_dt(rkorder, substep, dt); }
 
 // ---------------------------------------------------------------- Field3d_operators / diagnostics

@@ -287,7 +287,10 @@ struct SurfaceArgs
 };
 
 // Boundary_surface<TF>::exec, src/boundary_surface.cxx:827-981 (swconstantz0 = true, no Charnock)
-int surface_exec(Ctx* c, const SurfaceArgs& a)
+// stages: 1 = total wind (+ its halo), 2 = stability + momentum fluxes (+ their halos), 4 = gradients / scalar / MO gradients.
+// A y-slab rank (npy > 1) runs the stages one by one with the north/south exchange of dutot (after 1) and of the two flux
+// planes (after 2) in between: the cyclic fills in here are east/west only on such a rank (cyclic_exec_k).
+int surface_exec(Ctx* c, const SurfaceArgs& a, const int stages)
 {
     const GridD& gd = c->gd;
     if (a.mbcbot == BC_NEUMANN) { c->last_error = "Neumann bc is not supported in surface model"; return MHH_ERR_ARG; }
@@ -300,32 +303,41 @@ int surface_exec(Ctx* c, const SurfaceArgs& a)
     const dim3 bi(128), gi((gd.imax + 127) / 128, gd.jmax);
     const int nb = (gd.ijcells + 255) / 256;
     int e;
-    MHH_LAUNCH(c, "surf_dutot_kernel", dutot_kernel<<<gi, bi, 0, c->stream>>>(a.dutot, a.u, a.v, a.ubot, a.vbot, gd));
-    MHH_LAUNCH_CHECK();
-    if ((e = cyclic_exec_2d(c, a.dutot))) return e;
     const double thref_k = a.thermo ? c->thref_ks : 1., threfh_k = a.thermo ? c->threfh_ks : 1.;
     const double g_thref = kGrav / thref_k, g_threfh = kGrav / threfh_k;
     const double db_ref = g_thref * (thref_k - threfh_k);          // Thermo_dry::get_db_ref, src/thermo_dry.cxx:629-633
-    MHH_LAUNCH(c, "surf_stability_kernel", stability_kernel<<<nb, 256, 0, c->stream>>>(
-        a.ustar, a.obuk, a.nobuk, a.th, a.thbot, a.thfluxbot, a.dutot, a.z0m, c->surf_lut_d, c->surf_lut_d ? c->surf_lut_d + NLUT : nullptr,
-        a.thermo, a.mbcbot, a.thermobc, g_thref, thref_k, g_threfh, threfh_k, db_ref, zsl, gd));
-    MHH_LAUNCH_CHECK();
-    MHH_LAUNCH(c, "surfm_flux_kernel", surfm_flux_kernel<<<gi, bi, 0, c->stream>>>(
-        a.ufluxbot, a.vfluxbot, a.ustar, a.obuk, a.u, a.ubot, a.v, a.vbot, a.z0m, zsl, a.mbcbot, gd));
-    MHH_LAUNCH_CHECK();
-    if ((e = cyclic_exec_2d(c, a.ufluxbot))) return e;
-    if ((e = cyclic_exec_2d(c, a.vfluxbot))) return e;
-    MHH_LAUNCH(c, "surf_grad_kernel", surf_grad_kernel<<<nb, 256, 0, c->stream>>>(a.ugradbot, a.vgradbot, a.u, a.ubot, a.v, a.vbot, zsl, gd));
-    MHH_LAUNCH_CHECK();
-    if (a.thermo)
+    if (stages & 1)
     {
-        MHH_LAUNCH(c, "surfs_kernel", surfs_kernel<<<nb, 256, 0, c->stream>>>(
-            a.thbot, a.thgradbot, a.thfluxbot, a.ustar, a.obuk, a.th, a.z0h, zsl, a.thermobc, gd));
+        MHH_LAUNCH(c, "surf_dutot_kernel", dutot_kernel<<<gi, bi, 0, c->stream>>>(a.dutot, a.u, a.v, a.ubot, a.vbot, gd));
+        MHH_LAUNCH_CHECK();
+        if ((e = cyclic_exec_2d(c, a.dutot))) return e;
+    }
+    if (stages & 2)
+    {
+        MHH_LAUNCH(c, "surf_stability_kernel", stability_kernel<<<nb, 256, 0, c->stream>>>(
+            a.ustar, a.obuk, a.nobuk, a.th, a.thbot, a.thfluxbot, a.dutot, a.z0m, c->surf_lut_d, c->surf_lut_d ? c->surf_lut_d + NLUT : nullptr,
+            a.thermo, a.mbcbot, a.thermobc, g_thref, thref_k, g_threfh, threfh_k, db_ref, zsl, gd));
+        MHH_LAUNCH_CHECK();
+        MHH_LAUNCH(c, "surfm_flux_kernel", surfm_flux_kernel<<<gi, bi, 0, c->stream>>>(
+            a.ufluxbot, a.vfluxbot, a.ustar, a.obuk, a.u, a.ubot, a.v, a.vbot, a.z0m, zsl, a.mbcbot, gd));
+        MHH_LAUNCH_CHECK();
+        if ((e = cyclic_exec_2d(c, a.ufluxbot))) return e;
+        if ((e = cyclic_exec_2d(c, a.vfluxbot))) return e;
+    }
+    if (stages & 4)
+    {
+        MHH_LAUNCH(c, "surf_grad_kernel", surf_grad_kernel<<<nb, 256, 0, c->stream>>>(a.ugradbot, a.vgradbot, a.u, a.ubot, a.v, a.vbot, zsl, gd));
+        MHH_LAUNCH_CHECK();
+        if (a.thermo)
+        {
+            MHH_LAUNCH(c, "surfs_kernel", surfs_kernel<<<nb, 256, 0, c->stream>>>(
+                a.thbot, a.thgradbot, a.thfluxbot, a.ustar, a.obuk, a.th, a.z0h, zsl, a.thermobc, gd));
+            MHH_LAUNCH_CHECK();
+        }
+        MHH_LAUNCH(c, "surf_mo_grad_kernel", mo_grad_kernel<<<gi, bi, 0, c->stream>>>(
+            a.dudz, a.dvdz, a.thermo ? a.dbdz : nullptr, a.u, a.v, a.ubot, a.vbot, a.thfluxbot, a.ustar, a.obuk, a.z0m, g_threfh, zsl, gd));
         MHH_LAUNCH_CHECK();
     }
-    MHH_LAUNCH(c, "surf_mo_grad_kernel", mo_grad_kernel<<<gi, bi, 0, c->stream>>>(
-        a.dudz, a.dvdz, a.thermo ? a.dbdz : nullptr, a.u, a.v, a.ubot, a.vbot, a.thfluxbot, a.ustar, a.obuk, a.z0m, g_threfh, zsl, gd));
-    MHH_LAUNCH_CHECK();
     return MHH_OK;
 }
 

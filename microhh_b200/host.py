@@ -123,6 +123,7 @@ class Fields:
         self.rhoref = np.ones(grid.kcells)
         self.rhorefh = np.ones(grid.kcells)
         self.calc_mean_profs = False
+        self.comm = None          # set by a decomposed model (multigpu.SlabComm): sums over ranks as Master::sum does
 
     def set_calc_mean_profs(self, sw):
         self.calc_mean_profs = bool(sw)
@@ -133,6 +134,16 @@ class Fields:
             return
         g = self.grid
         prof = np.zeros(g.kcells)
+        if self.comm is not None and self.comm.world > 1:
+            # calc_mean_profile on MPI: per-rank level sums, master.sum, then the division (src/field3d_operators.cxx:46-66)
+            flds = list(self.ap.values())
+            sums = np.zeros((len(flds), g.kcells))
+            for q, fld in enumerate(flds):
+                L.check(g.ctx, g.lib.mhh_level_sums(g.ctx, L.ptr(fld.fld), sums[q].ctypes.data_as(C.c_void_p)), "mhh_level_sums")
+            tot = self.comm.allreduce_sum(sums, g.device).reshape(len(flds), g.kcells) / (g.itot * g.jtot)
+            for q, fld in enumerate(flds):
+                fld.fld_mean.copy_(tot[q])
+            return
         for fld in self.ap.values():
             L.check(g.ctx, g.lib.mhh_mean_profile(g.ctx, L.ptr(fld.fld), prof.ctypes.data_as(C.c_void_p)), "mhh_mean_profile")
             fld.fld_mean.copy_(torch.from_numpy(prof))
@@ -544,7 +555,7 @@ class Timeloop:
     """Timeloop (include/timeloop.h; src/timeloop.cxx): integer-nanosecond clock + low-storage RK."""
     ifactor = 1e9
 
-    def __init__(self, grid, fields, rkorder=3, dt=0.1, dtmax=1e9, adaptivestep=True, starttime=0., endtime=1e9):
+    def __init__(self, grid, fields, rkorder=3, dt=0.1, dtmax=1e9, adaptivestep=True, starttime=0., endtime=1e9, savetime=None):
         if rkorder not in (3, 4):
             raise L.MhhError("rkorder must be 3 or 4")
         self.grid, self.fields = grid, fields
@@ -555,6 +566,7 @@ class Timeloop:
         self.iendtime = int(self.ifactor * endtime + 0.5)
         self.idt = int(self.ifactor * dt + 0.5)
         self.idtmax = int(self.ifactor * dtmax + 0.5)
+        self.isavetime = None if savetime is None else int(self.ifactor * savetime + 0.5)
         self.time = starttime
         self.iteration = 0
 
@@ -565,8 +577,12 @@ class Timeloop:
         return self.grid.lib.mhh_rk_sub_dt(self.rkorder, self.substep, C.c_double(self.dt))
 
     def set_time_step_limit(self):
-        """src/timeloop.cxx:138-152 (no save/stat-time limits in this harness)"""
-        self.idtlim = min(self.idtmax, self.iendtime - self.itime) if self.iendtime > self.itime else self.idtmax
+        """src/timeloop.cxx:138-152 (no wall-clock limit; the savetime term only when [time] savetime was given)"""
+        self.idtlim = self.idtmax
+        if self.isavetime:
+            self.idtlim = min(self.idtlim, self.isavetime - self.itime % self.isavetime)
+        if self.itime < self.iendtime:
+            self.idtlim = min(self.idtlim, self.iendtime - self.itime)
 
     def set_time_step(self, *limits):
         """src/timeloop.cxx:229-245 + src/model.cxx:731-751"""
@@ -574,7 +590,9 @@ class Timeloop:
             return
         self.set_time_step_limit()
         idtlim = min([self.idtlim, *limits])
-        self.idt = max(int(idtlim), 1)
+        if self.idt == 0:           # src/timeloop.cxx:237-241: the previous step's limit fell below the clock's precision
+            raise L.MhhError(f"Required time step less than precision {1. / self.ifactor:f} of the time stepping")
+        self.idt = max(int(idtlim), 0)
         self.dt = self.idt / self.ifactor
 
     def step_time(self):
@@ -693,7 +711,16 @@ class Force:
 
     def exec(self, dt, thermo=None, stats=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
-        if self.swlspres == "uflux":
+        if self.swlspres == "uflux" and f.comm is not None and f.comm.world > 1:
+            # enforce_fixed_flux with the two volume means summed over the ranks (Field3d_operators::calc_mean -> master.sum):
+            # mhh_mean divides this rank's sum by the GLOBAL itot*jtot*zsize, so the rank values add up to the mean
+            um, utm = C.c_double(), C.c_double()
+            L.check(g.ctx, lib.mhh_mean(g.ctx, L.ptr(f.mp["u"].fld), C.byref(um)), "mhh_mean")
+            L.check(g.ctx, lib.mhh_mean(g.ctx, L.ptr(f.mt["u"].fld), C.byref(utm)), "mhh_mean")
+            um, utm = f.comm.allreduce_sum([um.value, utm.value], g.device).tolist()
+            fbody = (self.uflux - um - self.utrans) / dt - utm
+            L.check(g.ctx, lib.mhh_force_pressure(g.ctx, L.ptr(f.mt["u"].fld), C.c_double(fbody)), "mhh_force_pressure")
+        elif self.swlspres == "uflux":
             L.check(g.ctx, lib.mhh_force_fixed_flux(g.ctx, L.ptr(f.mt["u"].fld), L.ptr(f.mp["u"].fld), C.c_double(self.uflux),
                                                     C.c_double(self.utrans), C.c_double(dt), None), "mhh_force_fixed_flux")
         elif self.swlspres == "dpdx":
@@ -791,7 +818,18 @@ class Boundary_surface(Boundary):
             a.th, a.thbot, a.thgradbot, a.thfluxbot = p(th.fld), p(th.fld_bot), p(th.grad_bot), p(th.flux_bot)
         a.ustar, a.obuk, a.nobuk, a.z0m, a.z0h = p(self.ustar), p(self.obuk), p(self.nobuk), p(self.z0m), p(self.z0h)
         a.dutot, a.dudz, a.dvdz, a.dbdz = p(self._dutot), p(self.dudz_mo), p(self.dvdz_mo), p(self.dbdz_mo)
-        L.check(g.ctx, g.lib.mhh_boundary_surface_exec(g.ctx, C.byref(a)), "mhh_boundary_surface_exec")
+        if g.npy == 1:
+            L.check(g.ctx, g.lib.mhh_boundary_surface_exec(g.ctx, C.byref(a)), "mhh_boundary_surface_exec")
+        else:
+            # y-slab rank: the cyclic fills inside Boundary_surface::exec (src/boundary_surface.cxx:850,930-931) need the
+            # neighbours' rows -> the call runs in stages with the ring exchange (self.boundary_cyclic) in between
+            st = g.lib.mhh_boundary_surface_exec_stages
+            L.check(g.ctx, st(g.ctx, C.byref(a), 1), "mhh_boundary_surface_exec_stages 1")
+            self.boundary_cyclic.exec_2d(self._dutot)
+            L.check(g.ctx, st(g.ctx, C.byref(a), 2), "mhh_boundary_surface_exec_stages 2")
+            self.boundary_cyclic.exec_2d(u.flux_bot)
+            self.boundary_cyclic.exec_2d(v.flux_bot)
+            L.check(g.ctx, st(g.ctx, C.byref(a), 4), "mhh_boundary_surface_exec_stages 4")
         for name, fld in f.sp.items():
             if dry and name == "th":
                 continue

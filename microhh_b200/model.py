@@ -88,12 +88,13 @@ class Model:
         self.fuse_tend = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo in ("0", "dry")
         self.fuse_tend4 = self.advec.swadvec == "4" and self.diff.swdiff == "4"     # mhh_advec4_diff4_exec
         # Advec_2::get_time_limit + Diff_smag2::get_time_limit inside the evisc pass (mhh_smag2_exec_viscosity_dry_limits)
-        self.fuse_limits = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo == "dry" and npy == 1
+        self.fuse_limits = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo == "dry"
         self.fuse_pres_rk = self.pres.swpres in ("2", "4")   # Pres::output + Timeloop::exec(u,v,w) in one kernel (mhh_pres_exec_rk)
         ti = ini.get("time", {})
         self.timeloop = Timeloop(self.grid, self.fields, rkorder=ti.get("rkorder", 3), dt=ti.get("dt", 0.1),
                                  dtmax=ti.get("dtmax", 1e9), adaptivestep=ti.get("adaptivestep", True),
-                                 starttime=ti.get("starttime", 0.), endtime=ti.get("endtime", 1e9))
+                                 starttime=ti.get("starttime", 0.), endtime=ti.get("endtime", 1e9),
+                                 savetime=ti.get("savetime"))
         # [buffer] / [force]; `profs` = the case's init profiles (ktot values each: u, v, th, u_geo, ...)
         bu, fo = ini.get("buffer", {}), ini.get("force", {})
         self.buffer = Buffer(self.grid, self.fields, swbuffer=bu.get("swbuffer", False), swupdate=bu.get("swupdate", False),
@@ -106,10 +107,10 @@ class Model:
         # the scalars' Buffer term and RK update ride in their tendency pass when no [force] term touches a scalar tendency
         fo_ = self.force
         scal = set(self.fields.sp)
-        self.fuse_scalar_rk = (self.fuse_tend and bool(scal) and npy == 1 and fo_.swwls == "0"
+        self.fuse_scalar_rk = (self.fuse_tend and bool(scal) and fo_.swwls == "0"
                                and not (scal & set(fo_.lslist)) and not (scal & set(fo_.nudgelist)))
         # Tendencies left undefined (not zeroed) by the fused last-substep tails; the next fused tendency pass starts from 0
-        self.lazy_tend = bool(self.fuse_tend and self.fuse_pres_rk and self.pres.swpres == "2" and npy == 1
+        self.lazy_tend = bool(self.fuse_tend and self.fuse_pres_rk and self.pres.swpres == "2"
                               and (not scal or self.fuse_scalar_rk) and ini.get("b200", {}).get("lazy_tendencies", True))
         if self.lazy_tend:
             L.check(self.grid.ctx, self.grid.lib.mhh_set_lazy_tendencies(self.grid.ctx, 1), "mhh_set_lazy_tendencies")
@@ -118,19 +119,36 @@ class Model:
         self.pres.set_values()
         self.diff.create()
 
+    # ---- hooks a decomposed model overrides (multigpu.SlabModel): halo fills and cross-rank reductions -------------------
+    def _cyclic_prognostic(self):
+        self.boundary.set_prognostic_cyclic_bcs()
+
+    def _after_viscosity(self):
+        pass
+
+    def _reduce_max(self, values):
+        return values
+
     def exec_substep(self):
         b, tl = self.boundary, self.timeloop
-        b.set_prognostic_cyclic_bcs()                      # src/model.cxx:346
+        self._cyclic_prognostic()                          # src/model.cxx:346
         b.set_ghost_cells()                                # :348
         self.fields.exec()                                 # :351 (mean profiles, only when buffer/force asked for them)
         set_dt = not tl.in_substep() and tl.adaptivestep
         # :354; on the first substep of the 2nd-order LES path the two dt maxima ride in the same pass over u,v,w
         lim = self.diff.exec_viscosity(self.thermo, surface=self.surface, limits=set_dt and self.fuse_limits)
+        self._after_viscosity()
         if set_dt:                                         # set_time_step, :357 -> :731-751
             if lim is not None:
-                tl.set_time_step(self.advec.time_limit_from(lim[0] * tl.dt, tl.idt), self.diff.time_limit_from(lim[1], tl.idt, tl.dt))
+                cfl_dt, dnmul = self._reduce_max(lim)
+                tl.set_time_step(self.advec.time_limit_from(cfl_dt * tl.dt, tl.idt), self.diff.time_limit_from(dnmul, tl.idt, tl.dt))
             else:
-                tl.set_time_step(self.advec.get_time_limit(tl.idt, tl.dt), self.diff.get_time_limit(tl.idt, tl.dt))
+                cfl, = self._reduce_max([self.advec.get_cfl(tl.dt)])
+                lims = [self.advec.time_limit_from(cfl, tl.idt)]
+                if self.diff.swdiff != "0":
+                    dnmul, = self._reduce_max([self.diff._dnmul()])
+                    lims.append(self.diff.time_limit_from(dnmul, tl.idt, tl.dt))
+                tl.set_time_step(*lims)
         if self.mo:             # :376-377 (Thermo::exec of :366 only adds to wt, which the surface layer does not read)
             b.exec(self.thermo)
             b.set_ghost_cells()

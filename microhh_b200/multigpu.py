@@ -222,60 +222,28 @@ class SlabPres(Pres):
 
 
 class SlabModel(Model):
-    """Model on one y-slab of an npy = world decomposition."""
+    """Model on one y-slab of an npy = world decomposition: the same Model::exec sequence (fields.exec, exec_viscosity, the
+    surface layer, tendencies, Buffer, Force, pressure, RK — Model.exec_substep), with the halo fills going through the ring
+    neighbours and every maximum / mean reduced over the ranks (Master::max / Master::sum)."""
 
-    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None):
-        super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank)
+    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None, profs=None, mo=False):
+        super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank, profs=profs, mo=mo)
         self.comm = SlabComm(rank, world, group)
+        self.fields.comm = self.comm
         self.cyclic = SlabBoundaryCyclic(self.grid, self.comm)
         self.boundary.boundary_cyclic = self.cyclic
         self.pres = SlabPres(self.grid, self.fields, self.pres.swpres, self.comm, self.cyclic)
-        # the per-rank shortcuts of the single-GPU product path (Model.__init__ switches them off for npy > 1): this driver
-        # runs no Buffer / Force terms, so nothing touches a scalar tendency after its tendency pass
-        swthermo = self.thermo.swthermo
-        self.fuse_scalar_rk = bool(self.fuse_tend and self.fields.sp)
-        self.fuse_limits = self.advec.swadvec == "2" and self.diff.swdiff == "smag2" and swthermo == "dry"
-        self.lazy_tend = bool(self.fuse_tend and self.fuse_pres_rk and self.pres.swpres == "2"
-                              and (not self.fields.sp or self.fuse_scalar_rk) and ini.get("b200", {}).get("lazy_tendencies", True))
-        if self.lazy_tend:
-            L.check(self.grid.ctx, self.grid.lib.mhh_set_lazy_tendencies(self.grid.ctx, 1), "mhh_set_lazy_tendencies")
 
-    def exec_substep(self):
-        b, tl, dev = self.boundary, self.timeloop, self.grid.device
+    def _cyclic_prognostic(self):
         self.cyclic.exec_many(fld.fld for fld in self.fields.ap.values())      # set_prognostic_cyclic_bcs, one exchange
-        b.set_ghost_cells()
-        set_dt = not tl.in_substep() and tl.adaptivestep
-        own = self.diff.exec_viscosity(self.thermo, surface=self.surface, limits=set_dt and self.fuse_limits)
+
+    def _after_viscosity(self):
         if self.diff.swdiff == "smag2":
             self.cyclic.exec(self.fields.sd["evisc"].fld, L.EDGE_NORTH_SOUTH)   # east/west was done inside the call
-        if set_dt:
-            if own is not None:       # both maxima came out of the evisc pass: one collective for the pair
-                cfl_dt, dnmul = self.comm.allreduce_max_many(own, dev)
-                lim = [self.advec.time_limit_from(cfl_dt * tl.dt, tl.idt), self.diff.time_limit_from(dnmul, tl.idt, tl.dt)]
-            else:
-                cfl = max(self.advec.cflmin, self.comm.allreduce_max(self.advec.get_cfl(tl.dt), dev))
-                lim = [int(tl.idt * self.advec.cflmax / cfl)]
-                if self.diff.swdiff != "0":
-                    dnmul = self.comm.allreduce_max(self.diff._dnmul(), dev)
-                    dnmul = max(1.e-9, dnmul) if self.diff.swdiff == "smag2" else dnmul
-                    lim.append(int(tl.idt * self.diff.dnmax / (tl.dt * dnmul)))
-            tl.set_time_step(*lim)
-        done_s = ()
-        if self.fuse_tend:
-            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None,
-                                       timeloop=tl if self.fuse_scalar_rk else None)
-            done_s = tuple(self.fields.sp) if self.fuse_scalar_rk else ()
-        else:
-            self.thermo.exec()
-            b.set_ghost_cells_w(L.BCW_CONSERVATION)
-            self.advec.exec()
-            b.set_ghost_cells_w(L.BCW_NORMAL)
-            self.diff.exec()
-        b.set_ghost_cells_w(L.BCW_CONSERVATION)
-        fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
-        b.set_ghost_cells_w(L.BCW_NORMAL)
-        tl.exec(skip=(("u", "v", "w") if fused else ()) + done_s)
-        tl.step_time()
+
+    def _reduce_max(self, values):
+        """Master::max over the ranks; several maxima travel in one collective (a NaN flag rides along)."""
+        return self.comm.allreduce_max_many(values, self.grid.device)
 
     def print_status(self):
         g, f, tl, dev = self.grid, self.fields, self.timeloop, self.grid.device

@@ -14,9 +14,20 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "liboracle_ref.so")
+# the timing build (-O3 -march=x86-64-v3, FP contraction on: oracle/Makefile) — bench.py's CPU legs call use_perf_build()
+# BEFORE the first lib(); parity tests always use the plain build above
+PERF_LIB_PATH = os.path.join(_HERE, "_ref", "liboracle_ref_perf.so")
 
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _lib = None
+
+
+def use_perf_build() -> bool:
+    """Select the timing build for this process (no effect once the library is loaded, or when it was not built)."""
+    global LIB_PATH
+    if _lib is None and os.path.exists(PERF_LIB_PATH):
+        LIB_PATH = PERF_LIB_PATH
+    return LIB_PATH == PERF_LIB_PATH
 
 
 def available() -> bool:

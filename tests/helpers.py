@@ -20,7 +20,7 @@ def stretched_z(ktot, zsize, alpha=0.0):
 
 
 def make_case(itot=32, jtot=32, ktot=32, xsize=3200., ysize=3200., zsize=3200., seed=666, order=2, gc=None,
-              alpha=0.0, anelastic=False, surface_model=0, nscalars=1):
+              alpha=0.0, anelastic=False, surface_model=0, nscalars=1, mbc="freeslip"):
     """Synthetic inputs in the style of kernel_tuner/helpers.py:10-48, physically scaled."""
     rng = np.random.default_rng(seed)
     if gc is None:
@@ -62,7 +62,7 @@ def make_case(itot=32, jtot=32, ktot=32, xsize=3200., ysize=3200., zsize=3200., 
             planes[nm] = np.zeros((jc, ic))
     return dict(itot=itot, jtot=jtot, ktot=ktot, xsize=xsize, ysize=ysize, zsize=zsize, z=z, order=order, gc=gc,
                 u=u, v=v, w=w, s=scal, rhoref=rhoref, rhorefh=rhorefh, thref=300., planes=planes,
-                surface_model=surface_model, visc=1e-5, svisc=1e-5, cs=0.23, tPr=1. / 3., dt=2.0, substep=0,
+                surface_model=surface_model, mbc=mbc, visc=1e-5, svisc=1e-5, cs=0.23, tPr=1. / 3., dt=2.0, substep=0,
                 ks=ks, ke=ke)
 
 
@@ -79,8 +79,9 @@ def rel_err(got, ref):
 
 
 # ------------------------------------------------------------------------------------------------
-def run_substep_oracle(case):
-    """One LES RK3 substep with the reference's own code (oracle/_ref)."""
+def run_substep_oracle(case, buoyancy=False):
+    """One LES RK3 substep with the reference's own code (oracle/_ref).  buoyancy: Thermo_dry::exec on wt before the
+    advection (src/model.cxx:366), as the product path's fused tendency pass includes it."""
     from oracle.ref import RefWorld
     c = case
     W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], order=c["order"], gc=c["gc"],
@@ -96,8 +97,9 @@ def run_substep_oracle(case):
     # boundary->set_prognostic_cyclic_bcs, set_ghost_cells (src/model.cxx:346-348)
     for f in (u, v, w, *s):
         W.call("ref_cyclic", f, 2)
+    mbc = 0 if c.get("mbc", "freeslip") == "noslip" else 1      # Boundary_type: Dirichlet (value 0) / Neumann (gradient 0)
     for f in (u, v):
-        W.call("ref_ghost_cells", f, 1, 1, zero2.copy(), zero2.copy(), zero2.copy(), zero2.copy())
+        W.call("ref_ghost_cells", f, mbc, mbc, zero2.copy(), zero2.copy(), zero2.copy(), zero2.copy())
     for f in s:
         W.call("ref_ghost_cells", f, 1, 1, zero2.copy(), zero2.copy(), np.full_like(zero2, 0.003), np.full_like(zero2, 0.003))
     # diff->exec_viscosity
@@ -109,6 +111,8 @@ def run_substep_oracle(case):
         W.call("ref_smag2_evisc_neutral", sm, evisc, u, v, w, P.get("z0m"), c["cs"], c["visc"])
     cfl = W.call("ref_advec2_cfl", u, v, w, c["dt"])
     dnmul = W.call("ref_smag2_dnmul", evisc, c["tPr"])
+    if buoyancy and s:
+        W.call("ref_thermo_buoyancy_tend", wt, s[0], np.full(W.kcells, c["thref"]))
     # advec, diff
     W.call("ref_advec2_uvw", ut, vt, wt, u, v, w)
     for a, at in zip(s, st):
@@ -153,7 +157,7 @@ def run_substep_gpu(case):
     for n, a in zip(names, c["s"]):
         f.sp[n].fld.copy_(up(a))
     sm = c["surface_model"]
-    b = H.Boundary(g, f, mbcbot="freeslip", mbctop="freeslip",
+    b = H.Boundary(g, f, mbcbot=c.get("mbc", "freeslip"), mbctop=c.get("mbc", "freeslip"),
                    sbc={n: dict(sbot=0.003, stop=0.003, sbcbot="neumann", sbctop="neumann") for n in names},
                    swboundary="surface" if sm else "default")
     b.set_values()
@@ -200,6 +204,75 @@ def run_substep_gpu(case):
         f.mp[n].fld.copy_(keep[n])
     out = dict(u=f.mp["u"].fld.cpu().numpy(), v=f.mp["v"].fld.cpu().numpy(), w=f.mp["w"].fld.cpu().numpy(),
                p=f.sd["p"].fld.cpu().numpy(), evisc=f.sd["evisc"].fld.cpu().numpy(), ut_after=f.mt["u"].fld.cpu().numpy(),
+               **{f"s{n}": f.sp[nm].fld.cpu().numpy() for n, nm in enumerate(names)}, **tend)
+    out["scalars"] = dict(cfl=cfl, dnmul=dnmul, div=div, sub_dt=sub_dt)
+    g.close()
+    return out
+
+
+def run_substep_gpu_product(case, scalar_rk=False, limits=True):
+    """The same substep through the entry points the product path (microhh_b200.model.Model) uses: the fused viscosity pass
+    with N2 from th and both dt maxima (mhh_smag2_exec_viscosity_dry[_limits]), the one-pass tendencies
+    (mhh_advec2_smag2_exec[_rk]: buoyancy + advec_2 + diff_smag2, optionally the scalars' RK update) and the pressure tail
+    fused with the RK update of u,v,w (mhh_pres_exec_rk).  The first scalar is th (thermo dry, thref = case["thref"])."""
+    import torch
+    from microhh_b200 import host as H
+    from microhh_b200 import lib as L
+    from microhh_b200.model import Thermo
+    c = case
+    dev = torch.device("cuda:0")
+    g = H.Grid(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], swspatialorder=str(c["order"]),
+               gc=c["gc"], device=dev)
+    names = ["th"] + [f"s{n}" for n in range(1, len(c["s"]))]
+    f = H.Fields(g, slist=names, visc=c["visc"], svisc=c["svisc"])
+    f.set_rhoref(c["rhoref"], c["rhorefh"])
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    f.mp["u"].fld.copy_(up(c["u"])); f.mp["v"].fld.copy_(up(c["v"])); f.mp["w"].fld.copy_(up(c["w"]))
+    for n, a in zip(names, c["s"]):
+        f.sp[n].fld.copy_(up(a))
+    sm = c["surface_model"]
+    b = H.Boundary(g, f, mbcbot=c.get("mbc", "freeslip"), mbctop=c.get("mbc", "freeslip"),
+                   sbc={n: dict(sbot=0.003, stop=0.003, sbcbot="neumann", sbctop="neumann") for n in names},
+                   swboundary="surface" if sm else "default")
+    b.set_values()
+    P = {k: up(v) for k, v in c["planes"].items()}
+    if sm:
+        f.mp["u"].flux_bot.copy_(P["ufluxbot"]); f.mp["v"].flux_bot.copy_(P["vfluxbot"])
+        f.mp["u"].flux_top.copy_(P["ufluxtop"]); f.mp["v"].flux_top.copy_(P["vfluxtop"])
+        for n in names:
+            f.sp[n].flux_bot.copy_(P["sfluxbot"]); f.sp[n].flux_top.copy_(P["sfluxtop"])
+    advec = H.Advec.factory(g, f, "2")
+    diff = H.Diff.factory(g, f, b, "smag2", cs=c["cs"], tPr=c["tPr"])
+    pres = H.Pres.factory(g, f, "2")
+    pres.set_values()
+    thermo = Thermo(g, f, "dry", thref0=c["thref"])
+    tl = H.Timeloop(g, f, rkorder=3, dt=c["dt"], adaptivestep=False)
+    tl.substep = c["substep"]
+    b.set_prognostic_cyclic_bcs()
+    b.set_ghost_cells()
+    lim = diff.exec_viscosity(thermo, surface=P, limits=limits)
+    if lim is not None:
+        cfl, dnmul = lim[0] * c["dt"], lim[1]
+    else:
+        cfl, dnmul = advec.get_cfl(c["dt"]), diff.get_dn(1.0)
+    evisc = f.sd["evisc"].fld.cpu().numpy().copy()
+    diff.exec_with_advec2(f.sp["th"].fld, timeloop=tl if scalar_rk else None)
+    tend = {}
+    if not scalar_rk:
+        tend = dict(ut=f.mt["u"].fld.cpu().numpy().copy(), vt=f.mt["v"].fld.cpu().numpy().copy(), wt=f.mt["w"].fld.cpu().numpy().copy(),
+                    **{f"st{n}": f.st[nm].fld.cpu().numpy().copy() for n, nm in enumerate(names)})
+    sub_dt = tl.get_sub_time_step()
+    fused = pres.exec(sub_dt, timeloop=tl)
+    assert fused
+    tl.exec(skip=("u", "v", "w") + (tuple(names) if scalar_rk else ()))
+    keep = {n: f.mp[n].fld.clone() for n in "uvw"}
+    for n in "uvw":
+        b.boundary_cyclic.exec(f.mp[n].fld)
+    div = pres.check_divergence()
+    for n in "uvw":
+        f.mp[n].fld.copy_(keep[n])
+    out = dict(u=f.mp["u"].fld.cpu().numpy(), v=f.mp["v"].fld.cpu().numpy(), w=f.mp["w"].fld.cpu().numpy(),
+               p=f.sd["p"].fld.cpu().numpy(), evisc=evisc, ut_after=f.mt["u"].fld.cpu().numpy(),
                **{f"s{n}": f.sp[nm].fld.cpu().numpy() for n, nm in enumerate(names)}, **tend)
     out["scalars"] = dict(cfl=cfl, dnmul=dnmul, div=div, sub_dt=sub_dt)
     g.close()

@@ -12,7 +12,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def global_case(itot, jtot, ktot, seed=11):
+def global_case(itot, jtot, ktot, seed=11, full=True):
+    """full: the terms of cases/gabls1 that a decomposed run must treat like the single-GPU one — the Monin-Obukhov surface
+    layer (2-D halo exchanges inside Boundary_surface::exec), the sponge layer and the geostrophic / Coriolis forcing."""
     rng = np.random.default_rng(seed)
     shape = (ktot + 2, jtot + 2, itot + 2)
     z = (np.arange(ktot) + 0.5) * (1000. / ktot)
@@ -25,6 +27,14 @@ def global_case(itot, jtot, ktot, seed=11):
            "thermo": dict(swthermo="dry", thref0=300.),
            "boundary": dict(mbcbot="noslip", mbctop="freeslip", sbc={"th": dict(sbcbot="neumann", sbctop="neumann", sbot=0.003, stop=0.003)}),
            "fields": dict(visc=1e-5, svisc=1e-5), "time": dict(rkorder=3, dt=0.5, dtmax=10., adaptivestep=True)}
+    profs = None
+    if full:
+        ini["boundary"] = dict(mbcbot="noslip", mbctop="freeslip", swboundary="surface", z0m=0.1, z0h=0.1,
+                               sbc={"th": dict(sbcbot="dirichlet", sbctop="neumann", sbot=300.5, stop=0.003)})
+        ini["buffer"] = dict(swbuffer=True, zstart=750., sigma=0.00223, beta=2.)
+        ini["force"] = dict(swlspres="geo", fc=1.39e-4)
+        profs = dict(u=np.full(ktot, 2.), v=np.zeros(ktot), th=300. + 0.003 * z, u_geo=np.full(ktot, 2.), v_geo=np.zeros(ktot))
+    ini["_profs"], ini["_mo"] = profs, bool(full)
     return ini, z, f
 
 
@@ -36,14 +46,15 @@ def load(model, f, j0, j1):
         t.copy_(torch.from_numpy(np.ascontiguousarray(f[k][:, j0:j1 + 2, :])).to(g.device))
 
 
-def run(rank, world, device, nsteps=2, dims=(32, 32, 16), group=None):
+def run(rank, world, device, nsteps=2, dims=(32, 32, 16), group=None, full=True):
     import torch
     from microhh_b200.model import Model
     from microhh_b200.multigpu import SlabModel
     itot, jtot, ktot = dims
-    ini, z, f = global_case(itot, jtot, ktot)
+    ini, z, f = global_case(itot, jtot, ktot, full=full)
+    profs, mo = ini.pop("_profs"), ini.pop("_mo")
     jm = jtot // world
-    slab = SlabModel(ini, z, device=device, rank=rank, world=world, group=group)
+    slab = SlabModel(ini, z, device=device, rank=rank, world=world, group=group, profs=profs, mo=mo)
     load(slab, f, rank * jm, (rank + 1) * jm)
     for _ in range(nsteps):
         slab.step()
@@ -53,14 +64,39 @@ def run(rank, world, device, nsteps=2, dims=(32, 32, 16), group=None):
     out = {k: t.fld[1:-1, 1:-1, 1:-1].cpu().numpy() for k, t in {**slab.fields.mp, **slab.fields.sp, "p": slab.fields.sd["p"]}.items()}
     ref = None
     if rank == 0:
-        single = Model(ini, z, device=device)
+        single = Model(ini, z, device=device, profs=profs, mo=mo)
         load(single, f, 0, jtot)
         for _ in range(nsteps):
             single.step()
         st = single.print_status()
         ref = {k: t.fld[1:-1, 1:-1, 1:-1].cpu().numpy() for k, t in {**single.fields.mp, **single.fields.sp, "p": single.fields.sd["p"]}.items()}
         ref["status"] = st
+    slab.grid.close()
+    if rank == 0:
+        single.grid.close()
     return out, status, ref
+
+
+def parity_check(rank, world, device, dims, nsteps=2):
+    """Runs `run` on every rank, gathers the slabs on rank 0 and compares with the single-GPU fields: returns (on rank 0)
+    {"dims", "nsteps", "max_abs_diff", "status_rel_diff", "ok"}; bit-identical means max_abs_diff == 0.0."""
+    import torch.distributed as dist
+    out, status, ref = run(rank, world, device, nsteps=nsteps, dims=dims)
+    gathered = [None] * world
+    if world > 1:
+        dist.all_gather_object(gathered, out)
+    else:
+        gathered = [out]
+    if rank != 0:
+        return None
+    worst, per = 0., {}
+    for k in ("u", "v", "w", "th", "p"):
+        full = np.concatenate([g[k] for g in gathered], axis=1)
+        per[k] = float(np.abs(full - ref[k]).max())
+        worst = max(worst, per[k])
+    srel = max(abs(status[k] - ref["status"][k]) / max(abs(ref["status"][k]), 1e-30) for k in ("cfl", "dn", "mom", "tke", "mass", "dt"))
+    return {"dims": list(dims), "nsteps": nsteps, "case": "gabls1-like: MO surface layer, sponge, Coriolis", "max_abs_diff": worst,
+            "per_field": per, "status_rel_diff": float(srel), "ok": bool(worst == 0.0 and srel <= 1e-12)}
 
 
 def main():
