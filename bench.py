@@ -409,6 +409,8 @@ def main():
 
     itot, jtot, ktot = weak_scaling_shape(n, world)
     ini = les_ini(itot, jtot, ktot)
+    if os.environ.get("MHH_FUSE_FORCE") == "0":     # experiments: sponge / Coriolis as separate passes
+        ini["b200"] = dict(fuse_force=False)
     z = (np.arange(ktot) + 0.5) * (ini["grid"]["zsize"] / ktot)
     profs = les_profs(z)
     if world > 1:

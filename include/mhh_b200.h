@@ -131,6 +131,17 @@ int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* ctx, int surface_model,
                                         const double* dbdz, const double* z0m,
                                         double cs, double tPr, double visc, double* evisc,
                                         double* cfl_over_dt, double* dnmul);
+/* Buffer::exec (src/buffer.cxx:163; calc_buffer :37-58) and the swlspres=geo branch of Force::exec (src/force.cxx:609-625,
+ * calc_coriolis_2nd :76-107) for u,v,w, applied inside the fused momentum pass of mhh_advec2_smag2_exec[_rk] to the finished
+ * tendency of each cell in the time loop's order (bit-identical to mhh_buffer_exec + mhh_force_coriolis run afterwards, without
+ * their passes over u,v,ut,vt,wt).  ubuf/vbuf/wbuf: device profiles (kcells) or all NULL; sigma comes from mhh_buffer_plan.
+ * ug/vg: device profiles (kcells).  The setting persists until changed; the caller then skips those two calls for u,v,w. */
+int mhh_advec2_smag2_set_force_tail(mhh_ctx* ctx, const double* ubuf, const double* vbuf, const double* wbuf, int coriolis,
+                                    double fc, const double* ug, const double* vg, double ugrid, double vgrid);
+/* Tile-plane staging of the k-marching stencil kernels: TMA bulk tensor copies (cp.async.bulk.tensor, default where icells is
+ * even) or per-thread cp.async (on = 0).  Both give identical results; tests compare them. */
+int mhh_set_tma(mhh_ctx* ctx, int on);
+int mhh_tma_active(mhh_ctx* ctx);
 /* Lazy-tendency mode of the fused 2nd-order LES path (off by default).  Timeloop::exec leaves every tendency at zero after
  * the last substep (`at *= cA`, cA = 0: src/timeloop.cxx:250-285) and the next step's first tendency operator reads the zeros
  * back.  With the mode on, the last-substep tails (mhh_pres_exec_rk: ut,vt,wt; mhh_advec2_smag2_exec_rk: the scalars' st)

@@ -66,6 +66,9 @@ int buffer_exec(Ctx*, double*, const double*, const double*, int);
 int force_level_source(Ctx*, int, double*, double, const double*, const double*, const double*);
 int force_coriolis(Ctx*, double*, double*, const double*, const double*, const double*, const double*, double, double, double);
 int force_wls(Ctx*, int, double*, const double*, const double*);
+// tma.cu
+bool tma_planes_supported(const Ctx*, int);
+#define MHH_TILE_X_PUB 32
 // surface.cu
 struct SurfaceArgs
 {
@@ -589,6 +592,27 @@ int mhh_set_lazy_tendencies(mhh_ctx* c, int on)
     }
     return MHH_OK;
 }
+
+// Buffer::exec (src/buffer.cxx:163) and Force::exec's swlspres=geo branch (src/force.cxx:609-625) for u,v,w inside the fused
+// momentum pass of mhh_advec2_smag2_exec[_rk]: armed here, applied by every later call until cleared (all NULL / 0).
+int mhh_advec2_smag2_set_force_tail(mhh_ctx* c, const double* ubuf, const double* vbuf, const double* wbuf, int coriolis,
+                                    double fc, const double* ug, const double* vg, double ugrid, double vgrid)
+{
+    CTX_CHECK(c);
+    if (c->order != 2) { c->last_error = "mhh_advec2_smag2_set_force_tail needs swspatialorder=2"; return MHH_ERR_ARG; }
+    const bool buf = ubuf || vbuf || wbuf;
+    if (buf && !(ubuf && vbuf && wbuf)) { c->last_error = "mhh_advec2_smag2_set_force_tail: give all three buffer profiles or none"; return MHH_ERR_ARG; }
+    if (buf && !c->buffer_sigma_d) { c->last_error = "buffer not planned (mhh_buffer_plan)"; return MHH_ERR_STATE; }
+    if (coriolis && !(ug && vg)) { c->last_error = "mhh_advec2_smag2_set_force_tail: coriolis needs ug and vg"; return MHH_ERR_ARG; }
+    auto& t = c->uvw_tail;
+    t.buffer = buf; t.ubuf = ubuf; t.vbuf = vbuf; t.wbuf = wbuf;
+    t.coriolis = coriolis != 0; t.fc = fc; t.ug = ug; t.vg = vg; t.ugrid = ugrid; t.vgrid = vgrid;
+    return MHH_OK;
+}
+
+// 0: stage the tile planes with per-thread cp.async (LDGSTS) instead of TMA bulk tensor copies (default on where the layout allows)
+int mhh_set_tma(mhh_ctx* c, int on) { CTX_CHECK(c); c->tma_off = on == 0; return MHH_OK; }
+int mhh_tma_active(mhh_ctx* c) { CTX_CHECK(c); return tma_planes_supported(c, MHH_TILE_X_PUB + 2) ? 1 : 0; }
 
 int mhh_smag2_dnmul(mhh_ctx* c, const double* evisc, double tPr, double* out)
 {

@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>
+
 #include "mhh_common.cuh"
 
 namespace mhh
@@ -79,6 +81,19 @@ struct Ctx
     // Buffer (sponge layer): sigma(z[k]) (kcells) followed by sigma(zh[k]) (kcells); first levels inside the layer
     double* buffer_sigma_d = nullptr;
     int buffer_kstart = 0, buffer_kstarth = 0;
+
+    // Buffer / Coriolis terms of u,v,w applied inside the fused momentum pass (mhh_advec2_smag2_set_force_tail)
+    struct UvwTail
+    {
+        bool buffer = false, coriolis = false;
+        const double *ubuf = nullptr, *vbuf = nullptr, *wbuf = nullptr, *ug = nullptr, *vg = nullptr;
+        double fc = 0., ugrid = 0., vgrid = 0.;
+    } uvw_tail;
+
+    // TMA tensor maps of the fields the tile kernels stage (tma.cu); keyed by (pointer, box): the host model's arrays are stable
+    struct TmaEntry { const double* fld; int boxx, boxy; CUtensorMap map; };
+    std::vector<TmaEntry> tma_cache;
+    bool tma_off = false;           // mhh_set_tma(ctx, 0): force the cp.async (LDGSTS) plane ring (tests compare the two)
 
     // launch accounting / live per-kernel timing (bench.py: gpu_launches and roofline.achieved)
     unsigned long long launches = 0;

@@ -9,6 +9,7 @@
 #include <cmath>
 
 #include "ctx.h"
+#include "tma.cuh"
 
 // k levels unrolled in the momentum kernel's march (the register queues rotate by renaming instead of by moves)
 #ifndef MHH_UVW_UNROLL_N
@@ -77,18 +78,21 @@ constexpr int UVW_SLOTS = 6;
     // LIM: the time-step limits of the step ride along (the reference evaluates them right after exec_viscosity,
     // src/model.cxx:354-357): lim[0] = max of calc_cfl's sum (src/advec_2.cxx:51-78, before the * dt), lim[1] = max of
     // calc_dnmul (src/diff_smag2.cxx:712-735) of the evisc just computed — both read values this pass already holds.
-    template<bool SURF, int MODE, int TX, int TY, bool LIM = false>
+    // TMA: the planes are staged by one elected thread with cp.async.bulk.tensor (tma.cuh); `full[slot]` then carries the
+    // transaction bytes and replaces cp.async.wait_group; the per-level __syncthreads() still frees the slot of plane k-1.
+    template<bool SURF, int MODE, int TX, int TY, bool LIM = false, bool TMA = false>
     __global__ void __launch_bounds__(TX * TY, (LIM ? MHH_EVISC_LIM_MINB : MHH_EVISC_MINB))
     evisc_kernel(double* __restrict__ evisc,
                  const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                  const double* __restrict__ N2, const double* __restrict__ dudz, const double* __restrict__ dvdz,
                  const double* __restrict__ dbdz, const double* __restrict__ z0m,
                  const double* __restrict__ mlen0, const double tPr, const double visc, const GridD gd,
-                 unsigned long long* __restrict__ lim, const double tPrfac_i)
+                 unsigned long long* __restrict__ lim, const double tPrfac_i, const __grid_constant__ TmaMaps4 maps)
     {
         using Map = TileMap<TX, TY, 1>;
-        constexpr int W = Map::W, PS = Map::N, NS = 4;
-        __shared__ double sm[NS][3][PS];                 // [slot][u,v,w][tile plane]
+        constexpr int W = Map::W, PS = TMA ? tma_plane_pitch(Map::W, Map::HT) : Map::N, NS = 4;
+        __shared__ __align__(128) double sm[NS][3][PS];  // [slot][u,v,w][tile plane]
+        __shared__ unsigned long long full[NS];
         __shared__ double met[5][KCHUNK + 2];            // dzi, dzhi, z, mlen0 (thermo: mlen0^2 or its inverse), g/thref at k0-1 .. k1
 
         const int tid = threadIdx.y * TX + threadIdx.x;
@@ -105,9 +109,26 @@ constexpr int UVW_SLOTS = 6;
         unsigned long long m_cfl = 0ULL, m_dn = 0ULL;
 
         Map map;
-        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        if (!TMA) map.init(i0, j0, gd.icells, gd.jcells, tid);
+        if (TMA && tid == 0)
+        {
+            for (int sl = 0; sl < NS; ++sl) mbar_init(&full[sl], 1);
+            fence_mbar_init();
+        }
         auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
         {
+            if (TMA)
+            {
+                if (tid == 0 && k <= k1)
+                {
+                    const int sl = (k - k0 + 1) & (NS - 1);
+                    mbar_expect_tx(&full[sl], 3u * Map::N * (unsigned)sizeof(double));
+                    tma_load_plane(sm[sl][0], &maps.m[0], i0 - 1, j0 - 1, k, &full[sl]);
+                    tma_load_plane(sm[sl][1], &maps.m[1], i0 - 1, j0 - 1, k, &full[sl]);
+                    tma_load_plane(sm[sl][2], &maps.m[2], i0 - 1, j0 - 1, k, &full[sl]);
+                }
+                return;
+            }
             if (k <= k1)
             {
                 const int sl = (k - k0 + 1) & (NS - 1);
@@ -116,6 +137,8 @@ constexpr int UVW_SLOTS = 6;
             }
             cp_async_commit();
         };
+        // plane k is the ((k - k0 + 1) >> 2)-th fill of its slot
+        auto landed = [&](const int k) { mbar_wait(&full[(k - k0 + 1) & (NS - 1)], ((k - k0 + 1) >> 2) & 1); };
         stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
         if (tid < KCHUNK + 2)
         {
@@ -150,8 +173,9 @@ constexpr int UVW_SLOTS = 6;
         if (MODE == 3) { th_b = N2[ijk - kk]; th_c = N2[ijk]; th_n = N2[ijk + kk]; }
         if (MODE == 0) n2_n = N2[ijk];
 
-        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        if (!TMA) cp_async_wait<2>();                    // planes k0-1 and k0 have landed
         __syncthreads();
+        if (TMA) { landed(k0 - 1); landed(k0); }
         double u_b, u_c, u_eb, u_e, v_b, v_c, v_nb, v_n, w_c, w_w, w_e, w_s, w_n;
         {
             const double* B = sm[0][0]; const double* C = sm[1][0];
@@ -171,7 +195,8 @@ constexpr int UVW_SLOTS = 6;
         MHH_PRAGMA_UNROLL((LIM ? MHH_EVISC_LIM_UNROLL_N : MHH_EVISC_UNROLL_N))
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            if (TMA) landed(k + 1);
+            else cp_async_wait<1>();                     // plane k+1 has landed (k+2 may still be in flight)
             __syncthreads();                             // ... for every thread; everyone is done with plane k-1
             stage(k + 3);                                // into the slot of plane k-1
             const double th_t = th_n, n2_c = n2_n;
@@ -287,7 +312,7 @@ constexpr int UVW_SLOTS = 6;
             v_c = v_t; v_n = v_nt;
             w_c = w_t; w_w = w_wt; w_e = w_et; w_s = w_st; w_n = w_nt;
         }
-        cp_async_wait<0>();
+        if (!TMA) cp_async_wait<0>();
         if (LIM)
         {
             block_max_bits(m_cfl, lim);
@@ -318,7 +343,22 @@ constexpr int UVW_SLOTS = 6;
     //        (src/thermo_dry.cxx:43-62).  The sums are formed in the time loop's order, ((t + buoyancy) + advection) +
     //        diffusion, so the result is bit-identical to Thermo::exec, Advec::exec, Diff::exec run one after the other,
     //        at 11 instead of 22 field passes over HBM.
-    template<bool SURF, bool ADVEC, bool BUOY, int TX, int TY>
+    // FORCE: the terms that follow Diff::exec for u,v,w in Model::exec ride in the pass, applied to the finished tendency of a
+    //        cell in the time loop's order (so the result is bit-identical to Buffer::exec and Force::exec run afterwards):
+    //   sig != NULL : Buffer::exec, t -= sigma(z_k) (a - abuf[k]) for k >= bufk (w: sigma(zh_k), bufkh)   (src/buffer.cxx:37-58)
+    //   coriolis    : Force::exec swlspres=geo, calc_coriolis_2nd                                         (src/force.cxx:76-107)
+    struct ForceTail
+    {
+        const double* sig;       // sigma(z[k]) (kcells) followed by sigma(zh[k]) (kcells), or NULL
+        const double* ubuf; const double* vbuf; const double* wbuf;
+        int bufk, bufkh;
+        int coriolis;
+        double fc, ugrid, vgrid;
+        const double* ug; const double* vg;
+    };
+
+    // TMA: the tile planes are staged by cp.async.bulk.tensor (one elected thread, tma.cuh) instead of per-thread cp.async
+    template<bool SURF, bool ADVEC, bool BUOY, int TX, int TY, bool TMA = false, bool FORCE = false>
     __global__ void __launch_bounds__(TX * TY, 384 / (TX * TY))
     smag2_diff_uvw_tile_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                                const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
@@ -326,14 +366,17 @@ constexpr int UVW_SLOTS = 6;
                                const double* __restrict__ ufluxbot, const double* __restrict__ ufluxtop,
                                const double* __restrict__ vfluxbot, const double* __restrict__ vfluxtop,
                                const double visc, const double* __restrict__ th, const double* __restrict__ threfh,
-                               const double* __restrict__ g_threfh, const GridD gd, const int fresh)
+                               const double* __restrict__ g_threfh, const GridD gd, const int fresh,
+                               const ForceTail ft, const __grid_constant__ TmaMaps4 maps)
     {
         using Map = TileMap<TX, TY, 1>;
-        constexpr int W = Map::W, PS = Map::N, NS = UVW_SLOTS, NT = TX * TY;
-        extern __shared__ __align__(16) double sm[];     // [slot][evisc,u,v,w][tile plane]: NS * 4 * PS doubles (dynamic)
+        // PS: doubles per staged plane; the TMA destinations must stay 128-byte aligned
+        constexpr int W = Map::W, PS = TMA ? tma_plane_pitch(Map::W, Map::HT) : Map::N, NS = UVW_SLOTS, NT = TX * TY;
+        extern __shared__ __align__(128) double sm[];    // [slot][evisc,u,v,w][tile plane]: NS * 4 * PS doubles (dynamic)
         // rhoref, rhorefh, 1/rhoref, 1/rhorefh, dzi, dzhi, threfh, g/threfh, dzi/4, dzhi/4, 2 dzhi at k0-1 .. k1 (one array per
-        // metric: 16-byte records read as pairs cost this kernel registers it does not have, 3.20 -> 3.74 ms)
-        __shared__ double met[11][KCHUNK + 2];
+        // metric: 16-byte records read as pairs cost this kernel registers it does not have, 3.20 -> 3.74 ms);
+        // FORCE: + sigma(z), sigma(zh), ubuf, vbuf, wbuf, vg, ug
+        __shared__ double met[FORCE ? 18 : 11][KCHUNK + 2];
         __shared__ unsigned long long full[NS], empty[NS];
 
         const int tid = threadIdx.y * TX + threadIdx.x;
@@ -353,20 +396,41 @@ constexpr int UVW_SLOTS = 6;
         const double qdxi = 0.25 * dxi, qdyi = 0.25 * dyi, dxi2 = 2. * dxi, dyi2 = 2. * dyi;
 
         Map map;
-        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        if (!TMA) map.init(i0, j0, gd.icells, gd.jcells, tid);
         // Plane ring of NS slots.  Plane k has ordinal q = k - (k0-1) and lives in slot q & (NS-1); it is the (q / NS)-th fill
-        // of that slot.  full[slot] completes when all NT threads' copies of a fill have landed, empty[slot] when all NT
-        // threads have read the fill for the last time (as level k of iteration q-1).
+        // of that slot.  full[slot] completes when all copies of a fill have landed (cp.async: every thread's arrival; TMA: the
+        // issuing thread's arrival plus the transaction bytes of the four bulk copies), empty[slot] when all NT threads have
+        // read the fill for the last time (as level k of iteration q-1).
         if (tid == 0)
-            for (int sl = 0; sl < NS; ++sl) { mbar_init(&full[sl], NT); mbar_init(&empty[sl], NT); }
+        {
+            for (int sl = 0; sl < NS; ++sl) { mbar_init(&full[sl], TMA ? 1 : NT); mbar_init(&empty[sl], NT); }
+            if (TMA)
+            {
+                fence_mbar_init();
+                tma_prefetch_map(&maps.m[0]); tma_prefetch_map(&maps.m[1]); tma_prefetch_map(&maps.m[2]); tma_prefetch_map(&maps.m[3]);
+            }
+        }
         __syncthreads();
         auto stage = [&](const int q)
         {
             const int k = k0 - 1 + q;
             if (k > k1) return;
             const int sl = q % NS;
-            if (q >= NS) mbar_wait(&empty[sl], ((q / NS) - 1) & 1);     // the previous fill has been read by everyone
             double* dst = sm + sl * 4 * PS;
+            if (TMA)
+            {
+                if (tid == 0)
+                {
+                    if (q >= NS) mbar_wait(&empty[sl], ((q / NS) - 1) & 1);     // the previous fill has been read by everyone
+                    mbar_expect_tx(&full[sl], 4u * Map::N * (unsigned)sizeof(double));
+                    tma_load_plane(dst, &maps.m[0], i0 - 1, j0 - 1, k, &full[sl]);
+                    tma_load_plane(dst + PS, &maps.m[1], i0 - 1, j0 - 1, k, &full[sl]);
+                    tma_load_plane(dst + 2 * PS, &maps.m[2], i0 - 1, j0 - 1, k, &full[sl]);
+                    tma_load_plane(dst + 3 * PS, &maps.m[3], i0 - 1, j0 - 1, k, &full[sl]);
+                }
+                return;
+            }
+            if (q >= NS) mbar_wait(&empty[sl], ((q / NS) - 1) & 1);     // the previous fill has been read by everyone
             const long off = (long)k * kk;
             map.issue(dst, evisc + off, tid);      map.issue(dst + PS, u + off, tid);
             map.issue(dst + 2 * PS, v + off, tid); map.issue(dst + 3 * PS, w + off, tid);
@@ -385,6 +449,15 @@ constexpr int UVW_SLOTS = 6;
             met[3][t] = gd.rhorefh_i[k]; met[4][t] = gd.dzi[k]; met[5][t] = gd.dzhi[k];
             if (BUOY) { met[6][t] = threfh[k]; met[7][t] = g_threfh[k]; }
             met[8][t] = 0.25 * gd.dzi[k]; met[9][t] = 0.25 * gd.dzhi[k]; met[10][t] = 2. * gd.dzhi[k];
+            if (FORCE)
+            {
+                const bool sp = ft.sig != nullptr;
+                met[11][t] = (sp && k >= ft.bufk) ? ft.sig[k] : 0.;
+                met[12][t] = (sp && k >= ft.bufkh) ? ft.sig[gd.kcells + k] : 0.;
+                met[13][t] = sp ? ft.ubuf[k] : 0.; met[14][t] = sp ? ft.vbuf[k] : 0.; met[15][t] = sp ? ft.wbuf[k] : 0.;
+                met[16][t] = ft.coriolis ? ft.vg[k] : 0.;
+                met[17][t] = ft.coriolis ? ft.ug[k] : 0.;
+            }
         }
 
         // tile-plane offsets of the centre and its neighbours
@@ -526,7 +599,13 @@ constexpr int UVW_SLOTS = 6;
                 if (bot)      ver = div_by( fu_t + rhoh_b * rare_load(ufluxbot, ij), rho, rho_i ) * dzi;
                 else if (top) ver = div_by( -rhoh_t * rare_load(ufluxtop, ij) - fu_b, rho, rho_i ) * dzi;
                 else          ver = div_by( fu_t - fu_b, rho, rho_i ) * dzi;
-                if (live) ut[ijk] = ut_c + (hor + ver);
+                double tn = ut_c + (hor + ver);
+                if (FORCE)
+                {
+                    if (ft.sig != nullptr) tn = tn - met[11][km] * (u_c - met[13][km]);
+                    if (ft.coriolis) tn = tn + ft.fc * (0.25 * (v_w + v_c + v_wn + v_n) + ft.vgrid - met[16][km]);
+                }
+                if (live) ut[ijk] = tn;
                 fu_b = fu_t;
             }
             // ---- v: src/diff_smag2.cxx:497-569
@@ -548,7 +627,13 @@ constexpr int UVW_SLOTS = 6;
                 if (bot)      ver = div_by( fv_t + rhoh_b * rare_load(vfluxbot, ij), rho, rho_i ) * dzi;
                 else if (top) ver = div_by( -rhoh_t * rare_load(vfluxtop, ij) - fv_b, rho, rho_i ) * dzi;
                 else          ver = div_by( fv_t - fv_b, rho, rho_i ) * dzi;
-                if (live) vt[ijk] = vt_c + (hor + ver);
+                double tn = vt_c + (hor + ver);
+                if (FORCE)
+                {
+                    if (ft.sig != nullptr) tn = tn - met[11][km] * (v_c - met[14][km]);
+                    if (ft.coriolis) tn = tn - ft.fc * (0.25 * (u_s + u_c + u_es + u_e) + ft.ugrid - met[17][km]);
+                }
+                if (live) vt[ijk] = tn;
                 fv_b = fv_t;
             }
             // ---- w: src/diff_smag2.cxx:594-614 (k from kstart+1)
@@ -566,7 +651,9 @@ constexpr int UVW_SLOTS = 6;
                     + ( eviscn * ((w_n - w_c) * dyi + (v_n - v_nb) * dzhi_b)
                       - eviscs * gv_b ) * dyi
                     + div_by( fw_t - fw_b, rhoh_b, met[3][km] ) * met[10][km];
-                if (live) wt[ijk] = wt_c + wd;
+                double tn = wt_c + wd;
+                if (FORCE && ft.sig != nullptr) tn = tn - met[12][km] * (w_c - met[15][km]);
+                if (live) wt[ijk] = tn;
             }
             else if (fresh && live) wt[ijk] = 0.;      // the row the pass never writes
             fw_b = fw_t; gu_b = gu_t; gv_b = gv_t;
@@ -604,17 +691,18 @@ constexpr int UVW_SLOTS = 6;
         int fresh;       // the tendency array holds no data (lazy-tendency mode): start from 0 instead of reading it
     };
 
-    template<bool SURF, bool ADVEC, int TX, int TY>
+    template<bool SURF, bool ADVEC, int TX, int TY, bool TMA = false>
     __global__ void __launch_bounds__(TX * TY, MHH_SCALAR_MINB)
     smag2_scalar_tile_kernel(double* __restrict__ at, const double* __restrict__ a, const double* __restrict__ evisc,
                              const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
                              const double tPr, const double visc,
                              const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
-                             const ScalarTail tail, const GridD gd)
+                             const ScalarTail tail, const GridD gd, const __grid_constant__ TmaMaps4 maps)
     {
         using Map = TileMap<TX, TY, 1>;
-        constexpr int W = Map::W, PS = Map::N, NS = 4, NF = ADVEC ? 4 : 2;
-        __shared__ double sm[NS][NF][PS];                // [slot][a, evisc(, u, v)][tile plane]
+        constexpr int W = Map::W, PS = TMA ? tma_plane_pitch(Map::W, Map::HT) : Map::N, NS = 4, NF = ADVEC ? 4 : 2;
+        __shared__ __align__(128) double sm[NS][NF][PS]; // [slot][a, evisc(, u, v)][tile plane]
+        __shared__ unsigned long long full[NS];
         // per-level metric records at k0-1 .. k1, read as 16-byte pairs: {rhoref, 1/rhoref} {dzi, dzi/2} {rhorefh, dzhi}
         constexpr int MR = 6;
         __shared__ __align__(16) double met[(KCHUNK + 2) * MR];
@@ -637,9 +725,25 @@ constexpr int UVW_SLOTS = 6;
         const double tPr2 = 2. * tPr, tPr_hi = 0.5 * tPr_i, hdxi = 0.5 * dxi, hdyi = 0.5 * dyi;
 
         Map map;
-        map.init(i0, j0, gd.icells, gd.jcells, tid);
+        if (!TMA) map.init(i0, j0, gd.icells, gd.jcells, tid);
+        if (TMA && tid == 0)
+        {
+            for (int sl = 0; sl < NS; ++sl) mbar_init(&full[sl], 1);
+            fence_mbar_init();
+        }
         auto stage = [&](const int k)                    // plane k -> slot (k - k0 + 1) & 3; always one commit group
         {
+            if (TMA)
+            {
+                if (tid == 0 && k <= k1)
+                {
+                    const int sl = (k - k0 + 1) & (NS - 1);
+                    mbar_expect_tx(&full[sl], (unsigned)NF * Map::N * (unsigned)sizeof(double));
+                    #pragma unroll
+                    for (int q = 0; q < NF; ++q) tma_load_plane(sm[sl][q], &maps.m[q], i0 - 1, j0 - 1, k, &full[sl]);
+                }
+                return;
+            }
             if (k <= k1)
             {
                 const int sl = (k - k0 + 1) & (NS - 1);
@@ -649,6 +753,7 @@ constexpr int UVW_SLOTS = 6;
             }
             cp_async_commit();
         };
+        auto landed = [&](const int k) { mbar_wait(&full[(k - k0 + 1) & (NS - 1)], ((k - k0 + 1) >> 2) & 1); };
         stage(k0 - 1); stage(k0); stage(k0 + 1); stage(k0 + 2);
         if (tid < KCHUNK + 2)
         {
@@ -668,8 +773,9 @@ constexpr int UVW_SLOTS = 6;
         double w_c = 0., w_n = 0.;                       // w column (centre only), one level ahead from global memory
         if (ADVEC) { w_c = w[ijk]; w_n = w[ijk + kk]; }
 
-        cp_async_wait<2>();                              // planes k0-1 and k0 have landed
+        if (!TMA) cp_async_wait<2>();                    // planes k0-1 and k0 have landed
         __syncthreads();
+        if (TMA) { landed(k0 - 1); landed(k0); }
         double a_c = sm[1][0][c], e_c = sm[1][1][c];
         // vertical fluxes through the lower face of the first level; in the loop the upper-face flux of level k is carried
         // as the lower-face flux of level k+1 (same operands, same operations)
@@ -683,7 +789,8 @@ constexpr int UVW_SLOTS = 6;
         MHH_PRAGMA_UNROLL(MHH_SCALAR_UNROLL_N)
         for (int k = k0; k < k1; ++k, ijk += kk)
         {
-            cp_async_wait<1>();                          // plane k+1 has landed (k+2 may still be in flight)
+            if (TMA) landed(k + 1);
+            else cp_async_wait<1>();                     // plane k+1 has landed (k+2 may still be in flight)
             __syncthreads();                             // ... for every thread; everyone is done with plane k-1
             stage(k + 3);                                // into the slot of plane k-1
             double at_n = 0.;
@@ -745,7 +852,7 @@ constexpr int UVW_SLOTS = 6;
             a_c = a_t; e_c = e_t;
             at_c = at_n;
         }
-        cp_async_wait<0>();
+        if (!TMA) cp_async_wait<0>();
     }
 
     // calc_dnmul, src/diff_smag2.cxx:712-735, fused with the max reduction
@@ -807,11 +914,26 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     }
     constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
     const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd, lim, tPrfac_i
+    TmaMaps4 maps;
+    bool tma = tma_planes_supported(c, TX + 2);
+    if (tma)
+    {
+        const double* flds[3] = {u, v, w};
+        for (int q = 0; q < 3 && tma; ++q)
+        {
+            const int e = tma_plane_map(c, flds[q], TX + 2, TY + 2, &maps.m[q]);
+            if (e == MHH_ERR_CUDA) return e;
+            tma = (e == MHH_OK);
+        }
+    }
+    #define EV_ARGS evisc, u, v, w, N2, dudz, dvdz, dbdz, z0m, c->mlen0_d, tPr, visc, gd, lim, tPrfac_i, maps
+    #define EV_LAUNCH(S, M, L) do { \
+        if (tma) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<S, M, TX, TY, L, true><<<tg, tb, 0, c->stream>>>(EV_ARGS))); \
+        else     MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<S, M, TX, TY, L, false><<<tg, tb, 0, c->stream>>>(EV_ARGS))); } while (0)
     if (strain_only == 1)
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 2, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 2, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        if (surface_model) EV_LAUNCH(true, 2, false);
+        else               EV_LAUNCH(false, 2, false);
         MHH_LAUNCH_CHECK();
         return MHH_OK;
     }
@@ -819,27 +941,28 @@ int smag2_exec_viscosity(Ctx* c, int surface_model, const double* u, const doubl
     {
         if (lim != nullptr)
         {
-            if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-            else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+            if (surface_model) EV_LAUNCH(true, 3, true);
+            else               EV_LAUNCH(false, 3, true);
         }
-        else if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else                    MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 3, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else if (surface_model) EV_LAUNCH(true, 3, false);
+        else                    EV_LAUNCH(false, 3, false);
     }
     else if (N2 != nullptr)
     {
         if (lim != nullptr)
         {
-            if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-            else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY, true><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+            if (surface_model) EV_LAUNCH(true, 0, true);
+            else               EV_LAUNCH(false, 0, true);
         }
-        else if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else                    MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 0, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        else if (surface_model) EV_LAUNCH(true, 0, false);
+        else                    EV_LAUNCH(false, 0, false);
     }
     else
     {
-        if (surface_model) MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<true, 1, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
-        else               MHH_LAUNCH(c, "evisc_kernel", (evisc_kernel<false, 1, TX, TY><<<tg, tb, 0, c->stream>>>(EV_ARGS)));
+        if (surface_model) EV_LAUNCH(true, 1, false);
+        else               EV_LAUNCH(false, 1, false);
     }
+    #undef EV_LAUNCH
     #undef EV_ARGS
     MHH_LAUNCH_CHECK();
     if (!surface_model)
@@ -867,12 +990,44 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
     // lazy-tendency mode (mhh_set_lazy_tendencies): the arrays the last fused pressure tail left undefined start from 0
     const int fresh = (c->fresh_uvw[0] == ut && c->fresh_uvw[1] == vt && c->fresh_uvw[2] == wt) ? 1 : 0;
     c->fresh_uvw[0] = c->fresh_uvw[1] = c->fresh_uvw[2] = nullptr;
-    #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd, fresh
-    constexpr size_t smem = (size_t)UVW_SLOTS * 4 * (TX + 2) * (TY + 2) * sizeof(double);
-    #define UVW_LAUNCH(NAME, S, A, B) do { \
+    // the Buffer / Coriolis tail armed by mhh_advec2_smag2_set_force_tail rides in the fused advection + diffusion pass only
+    ForceTail ft{nullptr, nullptr, nullptr, nullptr, 0, 0, 0, 0., 0., 0., nullptr, nullptr};
+    const bool force = advec && (c->uvw_tail.buffer || c->uvw_tail.coriolis);
+    if (force)
+    {
+        const auto& t = c->uvw_tail;
+        if (t.buffer)
+        {
+            if (!c->buffer_sigma_d) { c->last_error = "buffer not planned (mhh_buffer_plan)"; return MHH_ERR_STATE; }
+            ft.sig = c->buffer_sigma_d; ft.ubuf = t.ubuf; ft.vbuf = t.vbuf; ft.wbuf = t.wbuf;
+            ft.bufk = c->buffer_kstart; ft.bufkh = c->buffer_kstarth;
+        }
+        if (t.coriolis) { ft.coriolis = 1; ft.fc = t.fc; ft.ugrid = t.ugrid; ft.vgrid = t.vgrid; ft.ug = t.ug; ft.vg = t.vg; }
+    }
+    // plane staging: TMA bulk tensor copies where the layout allows (icells even), else per-thread cp.async
+    TmaMaps4 maps;
+    bool tma = tma_planes_supported(c, TX + 2);
+    if (tma)
+    {
+        const double* flds[4] = {evisc, u, v, w};
+        for (int q = 0; q < 4 && tma; ++q)
+        {
+            const int e = tma_plane_map(c, flds[q], TX + 2, TY + 2, &maps.m[q]);
+            if (e == MHH_ERR_CUDA) return e;
+            tma = (e == MHH_OK);
+        }
+    }
+    #define UVW_ARGS ut, vt, wt, u, v, w, evisc, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th, threfh, g_threfh, gd, fresh, ft, maps
+    constexpr size_t smem_ldgsts = (size_t)UVW_SLOTS * 4 * (TX + 2) * (TY + 2) * sizeof(double);
+    constexpr size_t smem_tma = (size_t)UVW_SLOTS * 4 * tma_plane_pitch(TX + 2, TY + 2) * sizeof(double);
+    #define UVW_LAUNCH1(NAME, S, A, B, T, F) do { \
         static bool attr = false; \
-        if (!attr) { cudaFuncSetAttribute(smag2_diff_uvw_tile_kernel<S, A, B, TX, TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; } \
-        MHH_LAUNCH(c, NAME, (smag2_diff_uvw_tile_kernel<S, A, B, TX, TY><<<tg, tb, smem, c->stream>>>(UVW_ARGS))); } while (0)
+        const size_t smem = T ? smem_tma : smem_ldgsts; \
+        if (!attr) { cudaFuncSetAttribute(smag2_diff_uvw_tile_kernel<S, A, B, TX, TY, T, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; } \
+        MHH_LAUNCH(c, NAME, (smag2_diff_uvw_tile_kernel<S, A, B, TX, TY, T, F><<<tg, tb, smem, c->stream>>>(UVW_ARGS))); } while (0)
+    #define UVW_LAUNCH(NAME, S, A, B) do { \
+        if (force) { if (tma) UVW_LAUNCH1(NAME, S, A, B, true, A); else UVW_LAUNCH1(NAME, S, A, B, false, A); } \
+        else       { if (tma) UVW_LAUNCH1(NAME, S, A, B, true, false); else UVW_LAUNCH1(NAME, S, A, B, false, false); } } while (0)
     if (!advec)
     {
         if (surface_model) UVW_LAUNCH("smag2_diff_uvw_kernel", true, false, false);
@@ -889,6 +1044,7 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
         else               UVW_LAUNCH("advec2_smag2_uvw_kernel", false, true, true);
     }
     #undef UVW_LAUNCH
+    #undef UVW_LAUNCH1
     #undef UVW_ARGS
     MHH_LAUNCH_CHECK();
     return MHH_OK;
@@ -920,7 +1076,21 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
     }
     constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
     const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
-    #define SC_LAUNCH(NAME, S, A) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd)))
+    TmaMaps4 maps;
+    bool tma = tma_planes_supported(c, TX + 2);
+    if (tma)
+    {
+        const double* flds[4] = {a, evisc, u, v};
+        for (int q = 0; q < (advec ? 4 : 2) && tma; ++q)
+        {
+            const int e = tma_plane_map(c, flds[q], TX + 2, TY + 2, &maps.m[q]);
+            if (e == MHH_ERR_CUDA) return e;
+            tma = (e == MHH_OK);
+        }
+    }
+    #define SC_LAUNCH(NAME, S, A) do { \
+        if (tma) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, true><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps))); \
+        else     MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, false><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps))); } while (0)
     if (!advec)
     {
         if (surface_model) SC_LAUNCH("smag2_diff_c_kernel", true, false);

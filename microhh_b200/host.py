@@ -8,6 +8,7 @@ PyTorch is used only to own device memory (``torch.empty(..., device="cuda")``) 
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -36,6 +37,8 @@ class Grid:
             err = self.lib.mhh_create(C.byref(d), z.ctypes.data_as(C.c_void_p), C.byref(self.ctx))
         if err:
             raise L.MhhError(f"mhh_create failed with code {err}")
+        if os.environ.get("MHH_TMA") == "0":       # experiments: per-thread cp.async plane staging instead of TMA
+            self.lib.mhh_set_tma(self.ctx, 0)
         dims = (C.c_int * 20)()
         self.lib.mhh_get_dims(self.ctx, dims)
         (self.itot, self.jtot, self.ktot, self.imax, self.jmax, self.kmax, self.igc, self.jgc, self.kgc,
@@ -709,7 +712,8 @@ class Force:
                 self.nudgeprofs[n] = _level_profile(grid, p, n + "_nudge")
             fields.set_calc_mean_profs(True)
 
-    def exec(self, dt, thermo=None, stats=None):
+    def exec(self, dt, thermo=None, stats=None, skip_coriolis=False):
+        """`skip_coriolis`: the swlspres=geo term was applied inside the fused momentum pass (mhh_advec2_smag2_set_force_tail)."""
         g, f, lib = self.grid, self.fields, self.grid.lib
         if self.swlspres == "uflux" and f.comm is not None and f.comm.world > 1:
             # enforce_fixed_flux with the two volume means summed over the ranks (Field3d_operators::calc_mean -> master.sum):
@@ -725,7 +729,7 @@ class Force:
                                                     C.c_double(self.utrans), C.c_double(dt), None), "mhh_force_fixed_flux")
         elif self.swlspres == "dpdx":
             L.check(g.ctx, lib.mhh_force_pressure(g.ctx, L.ptr(f.mt["u"].fld), C.c_double(-1. * self.dpdx)), "mhh_force_pressure")
-        elif self.swlspres == "geo":
+        elif self.swlspres == "geo" and not skip_coriolis:
             L.check(g.ctx, lib.mhh_force_coriolis(g.ctx, L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mp["u"].fld),
                                                   L.ptr(f.mp["v"].fld), L.ptr(self.ug), L.ptr(self.vg), C.c_double(self.fc),
                                                   C.c_double(self.utrans), C.c_double(self.vtrans)), "mhh_force_coriolis")

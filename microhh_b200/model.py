@@ -114,6 +114,17 @@ class Model:
                               and (not scal or self.fuse_scalar_rk) and ini.get("b200", {}).get("lazy_tendencies", True))
         if self.lazy_tend:
             L.check(self.grid.ctx, self.grid.lib.mhh_set_lazy_tendencies(self.grid.ctx, 1), "mhh_set_lazy_tendencies")
+        # Buffer::exec and the Coriolis branch of Force::exec for u,v,w inside the fused momentum pass (same order of terms)
+        bf, fo_ = self.buffer, self.force
+        self.fuse_force = bool(self.fuse_tend and (bf.swbuffer or fo_.swlspres == "geo")
+                               and ini.get("b200", {}).get("fuse_force", True))
+        if self.fuse_force:
+            prof = lambda n: (self.fields.mp[n].fld_mean if bf.swupdate else bf.bufferprofs[n]) if bf.swbuffer else None
+            geo = fo_.swlspres == "geo"
+            L.check(self.grid.ctx, self.grid.lib.mhh_advec2_smag2_set_force_tail(
+                self.grid.ctx, L.ptr(prof("u")), L.ptr(prof("v")), L.ptr(prof("w")), 1 if geo else 0,
+                C.c_double(fo_.fc if geo else 0.), L.ptr(fo_.ug if geo else None), L.ptr(fo_.vg if geo else None),
+                C.c_double(fo_.utrans), C.c_double(fo_.vtrans)), "mhh_advec2_smag2_set_force_tail")
         self.surface = self.boundary.planes() if self.mo else (surface or {})
         self.boundary.set_values()
         self.pres.set_values()
@@ -167,8 +178,9 @@ class Model:
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :389
             self.diff.exec()                               # :392
         done_s = tuple(self.fields.sp) if (self.fuse_tend and self.fuse_scalar_rk) else ()
-        self.buffer.exec(skip=done_s)                      # :395
-        self.force.exec(tl.get_sub_time_step(), self.thermo)   # :404
+        done_m = ("u", "v", "w") if self.fuse_force else ()     # their sponge / Coriolis terms rode in the momentum pass
+        self.buffer.exec(skip=done_s + done_m)             # :395
+        self.force.exec(tl.get_sub_time_step(), self.thermo, skip_coriolis=self.fuse_force)   # :404
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
         # :411 + :484 for u,v,w in one pass
         fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)

@@ -491,3 +491,65 @@ def test_fused_scalar_tail_equals_buffer_then_rk(cuda_lib, rkorder, substep, swb
         assert np.array_equal(res[0][k], res[1][k]), k
     assert not np.array_equal(res[0]["th"], case["s"][0][W.kstart:W.kend, W.jstart:W.jend, W.istart:W.iend])
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("dims", [(64, 20, 70), (100, 12, 40)], ids=["2chunks", "ragged"])
+def test_tma_and_cp_async_plane_staging_are_bit_identical(cuda_lib, dims):
+    """The tile kernels stage their planes with TMA bulk tensor copies (default) or per-thread cp.async (mhh_set_tma(ctx, 0)):
+    same values in shared memory, so evisc, all tendencies, the updated scalar and the dt maxima must agree bit for bit."""
+    from tests.helpers import run_substep_gpu_product
+    import microhh_b200.host as H
+    case = make_case(itot=dims[0], jtot=dims[1], ktot=dims[2], surface_model=1, anelastic=True, alpha=1.3)
+    out = []
+    for tma in (True, False):
+        os_env = __import__("os").environ
+        if not tma:
+            os_env["MHH_TMA"] = "0"
+        try:
+            out.append(run_substep_gpu_product(case, scalar_rk=False, limits=True))
+            out.append(run_substep_gpu_product(case, scalar_rk=True, limits=False))
+        finally:
+            os_env.pop("MHH_TMA", None)
+    for a, b in ((out[0], out[2]), (out[1], out[3])):
+        for n in a:
+            if n == "scalars":
+                assert a[n] == b[n]
+            else:
+                assert np.array_equal(a[n], b[n]), n
+    # and TMA is really the active path on this (even icells) grid
+    g = H.Grid(dims[0], dims[1], dims[2], 100., 100., 100., case["z"] * 100. / 3200., swspatialorder="2", gc=(1, 1, 1))
+    assert g.lib.mhh_tma_active(g.ctx) == 1
+    g.close()
+
+
+def test_fused_force_tail_equals_separate_buffer_and_coriolis(cuda_lib):
+    """mhh_advec2_smag2_set_force_tail: Buffer::exec and calc_coriolis_2nd of u,v,w inside the fused momentum pass against the
+    same terms as separate passes (mhh_buffer_exec, mhh_force_coriolis) — the same operations in the same order: bit-identical
+    fields, dt history and status over 6 adaptive steps of a gabls1-like case (MO surface layer, sponge, geostrophic wind)."""
+    import torch
+    from microhh_b200.model import Model
+    from tests.test_gpu_multistep import les_case
+    ini, z, init, _ = les_case("gabls1_stable", n=(40, 24, 72))
+    n = ini["grid"]["ktot"]
+    ini["buffer"] = dict(swbuffer=True, zstart=250., sigma=0.00223, beta=2.)
+    ini["force"] = dict(swlspres="geo", fc=1.39e-4)
+    profs = dict(u=np.full(n, 8.), v=np.zeros(n), th=265. + 0.01 * np.clip(z - 100., 0., None), u_geo=np.full(n, 7.5), v_geo=np.full(n, 0.3))
+    dev = torch.device("cuda:0")
+    out = []
+    for fuse in (True, False):
+        m = Model(dict(ini, b200=dict(fuse_force=fuse)), z, device=dev, profs=profs, mo=True)
+        assert m.fuse_force == fuse
+        f = m.fields
+        for nm in f.ap:
+            f.ap[nm].fld.copy_(torch.from_numpy(np.ascontiguousarray(init[nm])).to(dev))
+        dts = []
+        for _ in range(6):
+            m.step()
+            dts.append(m.timeloop.idt)
+        out.append(({nm: f.ap[nm].fld.cpu().numpy().copy() for nm in f.ap}, dts, m.print_status()))
+        m.grid.close()
+    assert out[0][1] == out[1][1]
+    for nm in out[0][0]:
+        assert np.array_equal(out[0][0][nm], out[1][0][nm]), nm
+    assert out[0][2] == out[1][2]
+    assert np.abs(out[0][0]["v"]).max() > 1e-4

@@ -32,9 +32,9 @@ def _compare(case, got, want, names, tol=TOL):
 SEAM_CASES = [
     dict(itot=100, jtot=44, ktot=200, anelastic=True, alpha=1.2, surface_model=1),      # 4 ragged x tiles, 4 k chunks (64,64,64,8)
     dict(itot=100, jtot=44, ktot=200, anelastic=True, alpha=1.2, surface_model=0),
-    dict(itot=96, jtot=37, ktot=129, surface_model=1),                                   # a 1-level last chunk, odd jtot
+    dict(itot=96, jtot=39, ktot=129, surface_model=1),                                   # a 1-level last chunk, odd jtot
 ]
-SEAM_IDS = ["100x44x200_surf_anel_stretched", "100x44x200_nosurf_anel_stretched", "96x37x129_surf"]
+SEAM_IDS = ["100x44x200_surf_anel_stretched", "100x44x200_nosurf_anel_stretched", "96x39x129_surf"]
 
 
 @pytest.mark.parametrize("kw", SEAM_CASES, ids=SEAM_IDS)
