@@ -51,6 +51,13 @@ constexpr int UVW_SLOTS = 6;
 #ifndef MHH_SCALAR_MINB
 #define MHH_SCALAR_MINB 4
 #endif
+// 1: the momentum kernel stages its planes by TMA; 0 (default): per-thread cp.async.  Measured at 512^3 (r02b): TMA makes
+// the scalar pass 1.63 -> 1.29 ms and the evisc pass 1.71 -> 1.54 ms, but the momentum pass 3.12 -> 3.76 ms — it runs without
+// a per-level __syncthreads() and at its register limit; the one issuing thread's wait / issue sequence sits on the critical
+// path of its warp, which every other warp then waits for.
+#ifndef MHH_UVW_TMA
+#define MHH_UVW_TMA 0
+#endif
 #ifndef MHH_UVW_TILE_Y
 #define MHH_UVW_TILE_Y 4      // 32 x 4 columns per CTA, four CTAs per SM: shorter barrier waits than 32 x 8 (4.91 -> 4.66 ms)
 #endif
@@ -359,7 +366,10 @@ constexpr int UVW_SLOTS = 6;
 
     // TMA: the tile planes are staged by cp.async.bulk.tensor (one elected thread, tma.cuh) instead of per-thread cp.async
     template<bool SURF, bool ADVEC, bool BUOY, int TX, int TY, bool TMA = false, bool FORCE = false>
-    __global__ void __launch_bounds__(TX * TY, 384 / (TX * TY))
+#ifndef MHH_UVW_MINB
+#define MHH_UVW_MINB (384 / (MHH_TILE_X * MHH_UVW_TILE_Y))
+#endif
+    __global__ void __launch_bounds__(TX * TY, MHH_UVW_MINB)
     smag2_diff_uvw_tile_kernel(double* __restrict__ ut, double* __restrict__ vt, double* __restrict__ wt,
                                const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
                                const double* __restrict__ evisc,
@@ -419,7 +429,8 @@ constexpr int UVW_SLOTS = 6;
             double* dst = sm + sl * 4 * PS;
             if (TMA)
             {
-                if (tid == 0)
+                // the issuing role rotates over the warps, level by level: no warp carries the whole cost of the waits
+                if (tid == ((q % (NT / 32)) << 5))
                 {
                     if (q >= NS) mbar_wait(&empty[sl], ((q / NS) - 1) & 1);     // the previous fill has been read by everyone
                     mbar_expect_tx(&full[sl], 4u * Map::N * (unsigned)sizeof(double));
@@ -1006,7 +1017,7 @@ int smag2_tend_uvw(Ctx* c, int surface_model, int advec, const double* u, const 
     }
     // plane staging: TMA bulk tensor copies where the layout allows (icells even), else per-thread cp.async
     TmaMaps4 maps;
-    bool tma = tma_planes_supported(c, TX + 2);
+    bool tma = MHH_UVW_TMA && tma_planes_supported(c, TX + 2);
     if (tma)
     {
         const double* flds[4] = {evisc, u, v, w};

@@ -124,7 +124,7 @@ def test_evisc_neutral_matches_reference(cuda_lib, kw):
     else:
         # resolved walls: no-slip (u_tau comes from the wall shear), and a domain / viscosity at which the van Driest factor
         # is neither 0 nor saturated near the walls
-        case = make_case(nscalars=0, mbc="noslip", zsize=100., **kw)
+        case = make_case(nscalars=0, mbc="noslip", xsize=100., ysize=100., zsize=100., **kw)
         case["visc"] = 1e-3
         case["u"] *= 0.05; case["v"] *= 0.05
     got = run_substep_gpu(case)
