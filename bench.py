@@ -406,6 +406,7 @@ def main():
     if world > 1:
         from tests.slab_parity import parity_check
         slab_parity = parity_check(rank, world, dev, dims=(64, 64 * world, 32))
+        dist.barrier()
 
     itot, jtot, ktot = weak_scaling_shape(n, world)
     ini = les_ini(itot, jtot, ktot)
@@ -549,6 +550,7 @@ def main():
     }
     if slab_parity is not None:
         line["slab_parity"] = slab_parity
+        line["config"]["slab_path"] = getattr(model, "path", None)
     if world == 1 and not args.no_secondary:
         del model
         torch.cuda.empty_cache()

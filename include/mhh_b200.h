@@ -301,6 +301,33 @@ int mhh_fft_y(mhh_ctx* ctx, int dir, double* data_Y);
 int mhh_fft_x_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, double* p_or_null, int k0, int nk);
 int mhh_fft_y_chunks(mhh_ctx* ctx, int dir, const double* in, double* out, int k0, int nk);
 int mhh_fft_chunks_supported(mhh_ctx* ctx);
+
+/* --- peer-memory data path of the y-slab decomposition (no reference counterpart: replaces the MPI messages of
+ * Boundary_cyclic::exec, src/boundary_cyclic.cxx:139-174, and of Transpose::exec_xy/exec_yx, src/transpose.cxx:163-217) ---
+ * Every rank allocates one exchange arena (mhh_peer_alloc: cudaMalloc, zeroed), places its halo-exchanged fields, the solver's
+ * receive buffers and 32 flag words in it at the SAME offsets on all ranks, exports it (64-byte CUDA IPC handle), imports the
+ * other ranks' handles and registers the table of bases.  From then on data moves with stores to peer addresses: */
+int mhh_peer_alloc(mhh_ctx* ctx, unsigned long long bytes, void** ptr);
+int mhh_peer_free(mhh_ctx* ctx, void* ptr);
+int mhh_peer_export(mhh_ctx* ctx, void* ptr, unsigned char* handle64);
+int mhh_peer_import(mhh_ctx* ctx, const unsigned char* handle64, void** mapped_ptr);
+int mhh_peer_unmap(mhh_ctx* ctx, void* mapped_ptr);
+/* bases[r]: rank r's arena as mapped in this process (bases[me] == my_base); flags_offset: byte offset of the 32 flag words. */
+int mhh_peer_register(mhh_ctx* ctx, int world, int me, void* my_base, unsigned long long bytes, void* const* bases,
+                      unsigned long long flags_offset);
+/* North/south halo rows of up to 8 fields (3-D, or 2-D planes with is2d): my top interior rows are stored into the north
+ * neighbour's south ghost rows and my bottom rows into the south neighbour's north ghost rows; returns (stream-ordered)
+ * when both neighbours' rows have arrived in mine.  The east/west fill (mhh_cyclic) comes first, so corners are right. */
+int mhh_peer_halo_push(mhh_ctx* ctx, int nfields, double* const* flds, int is2d);
+/* All ranks have completed and made visible everything stream-ordered before this call. */
+int mhh_peer_barrier(mhh_ctx* ctx);
+int mhh_peer_error(mhh_ctx* ctx, int* err);    /* 1 after a flag wait timed out (a peer was lost) */
+/* Forward x transform / inverse y transform whose chunk-layout output (mhh_fft_x_chunks dir < 0, mhh_fft_y_chunks dir > 0) is
+ * written straight into the peers' receive buffers — peer_out[r] = rank r's buffer as mapped here; segment r of every line
+ * lands in slot `rank_y` of rank r's buffer: the all-to-all happens inside the transform, tile by tile over NVLink.  Follow
+ * with mhh_peer_barrier before the receiving transform (mhh_fft_y_chunks dir < 0 / mhh_fft_x_chunks dir > 0) reads. */
+int mhh_fft_x_chunks_to_peers(mhh_ctx* ctx, const double* in, double* const* peer_out, int k0, int nk);
+int mhh_fft_y_chunks_to_peers(mhh_ctx* ctx, const double* in, double* const* peer_out, int k0, int nk);
 int mhh_transpose_copy(mhh_ctx* ctx, int mode, double* dst, const double* src);
 int mhh_pres_solve_spectral_ws(mhh_ctx* ctx, double* data_Y, double* work3d);
 int mhh_pres_output_stage(mhh_ctx* ctx, int stage, double* ut, double* vt, double* wt, double* p);

@@ -68,6 +68,10 @@ int force_coriolis(Ctx*, double*, double*, const double*, const double*, const d
 int force_wls(Ctx*, int, double*, const double*, const double*);
 // tma.cu
 bool tma_planes_supported(const Ctx*, int);
+// peer.cu
+int peer_halo_push(Ctx*, int, double* const*, int);
+int peer_barrier(Ctx*);
+int peer_error(Ctx*, int*);
 #define MHH_TILE_X_PUB 32
 // surface.cu
 struct SurfaceArgs
@@ -173,7 +177,16 @@ static int fft_y(Ctx* c, int dir, double* data)
 // [k0, k0+nk): the k range handled by this call.  The chunk buffer of a k range is laid out on its own,
 // [k0 .. ][r][k' < nk][j < jmax][ii < iblock], so that the all-to-all of one k range can run while the transforms of the
 // next are computed (nk = kmax: one collective for the whole slab).
-static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* p, int k0, int nk)
+// peers != nullptr (send sides only): peers[r] = rank r's receive buffer as mapped in this process (peer.cu); the transform
+// then writes segment r of every line into slot `me` of rank r's buffer instead of into a local chunk buffer.
+static void peer_segtab(Ctx* c, FftLayout& L, double* const* peers, long R)
+{
+    L.use_segtab_out = true;
+    for (int r = 0; r < c->npy && r < 8; ++r)
+        L.segtab_out[r] = (long)(peers[r] - peers[c->rank_y]) + (long)c->rank_y * R;
+}
+
+static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* p, int k0, int nk, double* const* peers = nullptr)
 {
     const GridD& gd = c->gd;
     if (nk <= 0) { k0 = 0; nk = gd.kmax; }
@@ -187,6 +200,7 @@ static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* 
     {
         L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = xbase;
         L.n1o = L.nlines; L.s1o = c->iblock; L.s2o = 0; L.sno = 1; L.esplit_out = c->iblock; L.eseg_out = R; L.base_out = cbase;
+        if (peers) { peer_segtab(c, L, peers, R); out = peers[c->rank_y]; }
         return fft_lines(c, c->plan_i, -1, in, out, L);
     }
     L.n1 = L.nlines; L.s1 = c->iblock; L.s2 = 0; L.sn = 1; L.esplit_in = c->iblock; L.eseg_in = R; L.base_in = cbase;
@@ -200,7 +214,7 @@ static int fft_x_chunks(Ctx* c, int dir, const double* in, double* out, double* 
     return fft_lines(c, c->plan_i, +1, in, out, L);
 }
 
-static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, int nk)
+static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, int nk, double* const* peers = nullptr)
 {
     const GridD& gd = c->gd;
     if (nk <= 0) { k0 = 0; nk = gd.kmax; }
@@ -221,6 +235,7 @@ static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, 
     {
         L.s2 = (long)c->iblock * gd.jtot; L.base_in = ybase;
         L.s2o = (long)gd.jmax * c->iblock; L.esplit_out = gd.jmax; L.eseg_out = R; L.base_out = cbase;
+        if (peers) { peer_segtab(c, L, peers, R); out = peers[c->rank_y]; }
     }
     return fft_lines(c, c->plan_j, dir, in, out, L);
 }
@@ -880,6 +895,66 @@ int mhh_set_bc(mhh_ctx* c, double* a, double* agrad, double* aflux, int sw, doub
 int mhh_rk_substep(mhh_ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
 { CTX_CHECK(c); MHH_TENDS(at, nfields); return rk_substep(c, rkorder, substep, dt, nfields, a, at); }
 double mhh_rk_sub_dt(int rkorder, int substep, double dt) { return rk_sub_dt(rkorder, substep, dt); }
+
+// ---------------------------------------------------------------- peer-memory data path of the y-slab decomposition
+int mhh_peer_alloc(mhh_ctx* c, unsigned long long bytes, void** ptr)
+{
+    CTX_CHECK(c);
+    if (!ptr || bytes == 0) return MHH_ERR_ARG;
+    MHH_CUDA_CHECK(cudaMalloc(ptr, bytes));
+    MHH_CUDA_CHECK(cudaMemset(*ptr, 0, bytes));
+    return MHH_OK;
+}
+int mhh_peer_free(mhh_ctx* c, void* ptr) { CTX_CHECK(c); MHH_CUDA_CHECK(cudaFree(ptr)); return MHH_OK; }
+int mhh_peer_export(mhh_ctx* c, void* ptr, unsigned char* handle64)
+{
+    CTX_CHECK(c);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    MHH_CUDA_CHECK(cudaIpcGetMemHandle(&h, ptr));
+    std::memcpy(handle64, &h, 64);
+    return MHH_OK;
+}
+int mhh_peer_import(mhh_ctx* c, const unsigned char* handle64, void** ptr)
+{
+    CTX_CHECK(c);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    MHH_CUDA_CHECK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return MHH_OK;
+}
+int mhh_peer_unmap(mhh_ctx* c, void* ptr) { CTX_CHECK(c); MHH_CUDA_CHECK(cudaIpcCloseMemHandle(ptr)); return MHH_OK; }
+int mhh_peer_register(mhh_ctx* c, int world, int me, void* my_base, unsigned long long bytes, void* const* bases,
+                      unsigned long long flags_offset)
+{
+    CTX_CHECK(c);
+    if (world < 1 || world > 8 || me < 0 || me >= world || !my_base || !bases || flags_offset + 32 * 8 > bytes || (flags_offset & 7))
+    { c->last_error = "mhh_peer_register: bad arguments (world <= 8)"; return MHH_ERR_ARG; }
+    if (world != c->npy || me != c->rank_y) { c->last_error = "mhh_peer_register: world / rank differ from the grid's npy / rank_y"; return MHH_ERR_ARG; }
+    auto& P = c->peer;
+    P.world = world; P.me = me; P.north = (me + 1) % world; P.south = (me + world - 1) % world;
+    P.base = my_base; P.bytes = bytes;
+    for (int r = 0; r < world; ++r) P.delta[r] = (long)(reinterpret_cast<const char*>(bases[r]) - reinterpret_cast<const char*>(my_base));
+    if (P.delta[me] != 0) { c->last_error = "mhh_peer_register: bases[me] must be my_base"; return MHH_ERR_ARG; }
+    P.flags = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(my_base) + flags_offset);
+    P.halo_epoch = P.barrier_epoch = 0;
+    return MHH_OK;
+}
+int mhh_peer_halo_push(mhh_ctx* c, int nfields, double* const* flds, int is2d) { CTX_CHECK(c); return peer_halo_push(c, nfields, flds, is2d); }
+int mhh_peer_barrier(mhh_ctx* c) { CTX_CHECK(c); return peer_barrier(c); }
+int mhh_peer_error(mhh_ctx* c, int* err) { CTX_CHECK(c); if (!err) return MHH_ERR_ARG; return peer_error(c, err); }
+int mhh_fft_x_chunks_to_peers(mhh_ctx* c, const double* in, double* const* peer_out, int k0, int nk)
+{
+    PRES_READY(c);
+    if (!peer_out) return MHH_ERR_ARG;
+    return fft_x_chunks(c, -1, in, nullptr, nullptr, k0, nk, peer_out);
+}
+int mhh_fft_y_chunks_to_peers(mhh_ctx* c, const double* in, double* const* peer_out, int k0, int nk)
+{
+    PRES_READY(c);
+    if (!peer_out) return MHH_ERR_ARG;
+    return fft_y_chunks(c, +1, in, nullptr, k0, nk, peer_out);
+}
 
 // ---------------------------------------------------------------- Field3d_operators / diagnostics
 int mhh_mean_profile(mhh_ctx* c, const double* fld, double* prof)

@@ -90,6 +90,18 @@ struct Ctx
         double fc = 0., ugrid = 0., vgrid = 0.;
     } uvw_tail;
 
+    // peer-memory data path of the y-slab decomposition (peer.cu): this rank's exchange arena and where the same arena of
+    // every other rank is mapped in this process (delta[r] = rank r's base - my base, bytes)
+    struct Peer
+    {
+        int world = 1, me = 0, north = 0, south = 0;
+        void* base = nullptr;
+        size_t bytes = 0;
+        long delta[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        unsigned long long* flags = nullptr;        // 32 words inside the arena
+        unsigned long long halo_epoch = 0, barrier_epoch = 0;
+    } peer;
+
     // TMA tensor maps of the fields the tile kernels stage (tma.cu); keyed by (pointer, box): the host model's arrays are stable
     struct TmaEntry { const double* fld; int boxx, boxy; CUtensorMap map; };
     std::vector<TmaEntry> tma_cache;

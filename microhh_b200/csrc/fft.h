@@ -17,6 +17,10 @@ struct FftLayout
     double scale;
     int esplit_in = 0;  long eseg_in = 0;
     int esplit_out = 0; long eseg_out = 0;
+    // with use_segtab_out, output segment r = m / esplit_out starts at segtab_out[r] (elements, relative to `out`) instead of
+    // r*eseg_out: the segments are the receive buffers of the peer ranks (peer.cu), the transform writes them directly
+    bool use_segtab_out = false;
+    long segtab_out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 int fft_plan_create(FftPlan* p, int n);

@@ -41,6 +41,8 @@ namespace
         double scale;
         int esh_in, esh_out;          // log2 of the element split (31: none)
         long eseg_in, eseg_out;
+        int use_tab;                  // output segments start at segtab[r] (peer receive buffers) instead of r * eseg_out
+        long segtab[8];
     };
 
     __device__ __forceinline__ double2 cmul(double2 a, double2 b)
@@ -195,6 +197,14 @@ namespace
         if (!SPLIT) return (long)m * sn;
         return (long)(m >> esh) * eseg + (long)(m & ((1 << esh) - 1)) * sn;
     }
+    // output side: the segments may be the peers' receive buffers (P2Args::segtab)
+    template<bool SPLIT> __device__ __forceinline__ long elem_off_out(int m, long sn, const P2Args& A)
+    {
+        if (!SPLIT) return (long)m * sn;
+        const int r = m >> A.esh_out;
+        const long seg = A.use_tab ? A.segtab[r & 7] : (long)r * A.eseg_out;
+        return seg + (long)(m & ((1 << A.esh_out) - 1)) * sn;
+    }
 
     // DIR = -1: real lines -> half-complex; +1: half-complex -> real lines (unnormalised * scale).
     // STRIDED: element stride sn != 1 (lines adjacent in memory): tiles are staged through shared memory.
@@ -326,7 +336,7 @@ namespace
                     for (int m = 0; m < 8; ++m)
                     {
                         const int pos = tf + m * n8;
-                        const long eo = elem_off<SPLIT>(pos, 1, A.esh_out, A.eseg_out);
+                        const long eo = elem_off_out<SPLIT>(pos, 1, A);
                         if (va) qa[eo] = v[m].x * A.scale;
                         if (vb) qb[eo] = v[m].y * A.scale;
                     }
@@ -363,7 +373,7 @@ namespace
                     const bool has_im = (k > 0) && (k < nh);
                     if (!STRIDED)
                     {
-                        const long ek = elem_off<SPLIT>(k, 1, A.esh_out, A.eseg_out), en = elem_off<SPLIT>(n - k, 1, A.esh_out, A.eseg_out);
+                        const long ek = elem_off_out<SPLIT>(k, 1, A), en = elem_off_out<SPLIT>(n - k, 1, A);
                         if (va) { qa[ek] = are * A.scale; if (has_im) qa[en] = aim * A.scale; }
                         if (vb) { qb[ek] = bre * A.scale; if (has_im) qb[en] = bim * A.scale; }
                     }
@@ -391,7 +401,7 @@ namespace
                 const double* src = zr + 2 * ((ll >> 1) * NP) + (ll & 1);
                 #pragma unroll 8
                 for (int m = threadIdx.x >> llog; m < n; m += mstep)
-                    dst[elem_off<SPLIT>(m, A.sno, A.esh_out, A.eseg_out)] = src[2 * pad(m)] * A.scale;
+                    dst[elem_off_out<SPLIT>(m, A.sno, A)] = src[2 * pad(m)] * A.scale;
             }
         }
     }
@@ -449,7 +459,7 @@ namespace
         {
             #pragma unroll
             for (int m = 0; m < 8; ++m)
-                *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(tf + m * n8, A.sno, A.esh_out, A.eseg_out))
+                *reinterpret_cast<double2*>(dst + elem_off_out<SPLIT>(tf + m * n8, A.sno, A))
                     = make_double2(v[m].x * A.scale, v[m].y * A.scale);
         }
         else
@@ -468,10 +478,10 @@ namespace
                 const double2 zk = z[pad(k) << CPL], zn = z[pad(kn) << CPL];
                 const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
                 const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
-                *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(k, A.sno, A.esh_out, A.eseg_out))
+                *reinterpret_cast<double2*>(dst + elem_off_out<SPLIT>(k, A.sno, A))
                     = make_double2(are * A.scale, bre * A.scale);
                 if (k > 0 && k < nh)
-                    *reinterpret_cast<double2*>(dst + elem_off<SPLIT>(n - k, A.sno, A.esh_out, A.eseg_out))
+                    *reinterpret_cast<double2*>(dst + elem_off_out<SPLIT>(n - k, A.sno, A))
                         = make_double2(aim * A.scale, bim * A.scale);
             }
         }
@@ -555,7 +565,7 @@ namespace
             const double are = 0.5 * (zk.x + zn.x), aim = 0.5 * (zk.y - zn.y);
             const double bre = 0.5 * (zk.y + zn.y), bim = -0.5 * (zk.x - zn.x);
             const bool has_im = (k > 0) && (k < nh);
-            const long ek = elem_off<SPLIT>(k, 1, A.esh_out, A.eseg_out), en = elem_off<SPLIT>(n - k, 1, A.esh_out, A.eseg_out);
+            const long ek = elem_off_out<SPLIT>(k, 1, A), en = elem_off_out<SPLIT>(n - k, 1, A);
             if (va) { qa[ek] = are * A.scale; if (has_im) qa[en] = aim * A.scale; }
             if (vb) { qb[ek] = bre * A.scale; if (has_im) qb[en] = bim * A.scale; }
         }
@@ -614,6 +624,8 @@ int pres2_in_fft_x(Ctx* c, const FftPlan& plan, const double* u, const double* v
     auto lg = [](int x) { int l = 0; while ((1 << l) < x) ++l; return l; };
     A.esh_in = 31; A.eseg_in = 0;
     A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
+    A.use_tab = L.use_segtab_out ? 1 : 0;
+    for (int r = 0; r < 8; ++r) A.segtab[r] = L.segtab_out[r];
     PresInArgs F{u, v, w, ut, vt, wt, 1. / dt, k0, gd};
     const int npairs = BLOCK / (plan.n / 8);
     const size_t smem = (size_t)npairs * ((plan.n + plan.n / 8) + 1) * sizeof(double2);
@@ -651,6 +663,9 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
         return MHH_ERR_UNSUPPORTED;
     A.esh_in = L.esplit_in > 0 ? lg(L.esplit_in) : 31;   A.eseg_in = L.eseg_in;
     A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
+    A.use_tab = L.use_segtab_out ? 1 : 0;
+    for (int r = 0; r < 8; ++r) A.segtab[r] = L.segtab_out[r];
+    if (L.use_segtab_out && (L.esplit_out <= 0 || plan.n / L.esplit_out > 8)) return MHH_ERR_UNSUPPORTED;
     // y passes whose lines are adjacent words: the lanes-along-the-lines kernel (n = 256, 512, 1024: 16, 8, 4 pairs per CTA)
     {
         static const bool col_off = []() { const char* e = getenv("MHH_FFT_NOCOL"); return e && atoi(e) != 0; }();
@@ -659,6 +674,8 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
         auto even = [](long v) { return (v & 1L) == 0; };
         const bool aligned = even(L.s2) && even(L.sn) && even(L.base_in) && even(L.s2o) && even(L.sno) && even(L.base_out)
                           && even(L.eseg_in) && even(L.eseg_out)
+                          && (!L.use_segtab_out || (even(L.segtab_out[0]) && even(L.segtab_out[1]) && even(L.segtab_out[2]) && even(L.segtab_out[3])
+                                                    && even(L.segtab_out[4]) && even(L.segtab_out[5]) && even(L.segtab_out[6]) && even(L.segtab_out[7])))
                           && (reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
         if (!col_off && strided && (cp == 4 || cp == 8 || cp == 16) && L.s1 == 1 && L.s1o == 1 && L.n1 == L.n1o
             && L.n1 % (2 * cp) == 0 && L.nlines % (2 * cp) == 0 && aligned)

@@ -17,11 +17,93 @@ import torch
 from . import lib as L
 
 
+class _RawCuda:
+    """A raw device allocation seen through the CUDA array interface (torch.as_tensor wraps it without a copy)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerArena:
+    """The exchange arena of a y-slab rank (include/mhh_b200.h, "peer-memory data path"): one cudaMalloc'ed block that holds
+    every array other ranks write into — the halo-exchanged fields and planes, the pressure solver's receive buffers and the
+    flag words — at the SAME offsets on all ranks (all ranks allocate in the same order), so that the address of any of my
+    arrays in rank r's arena is  bases[r] + (ptr - bases[me])."""
+    ALIGN = 512
+
+    def __init__(self, grid, nbytes):
+        self.grid, self.nbytes = grid, int(nbytes)
+        p = C.c_void_p()
+        L.check(grid.ctx, grid.lib.mhh_peer_alloc(grid.ctx, C.c_ulonglong(self.nbytes), C.byref(p)), "mhh_peer_alloc")
+        self.base = p.value
+        self.raw = torch.as_tensor(_RawCuda(self.base, self.nbytes), device=grid.device)
+        assert self.raw.data_ptr() == self.base
+        self.flags_offset = 0
+        self.top = 4096                      # the first page: 32 flag words
+        self.bases = None                    # filled by connect()
+        self.mapped = []
+
+    def alloc(self, shape, dtype=torch.float64):
+        n = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        off = (self.top + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        if off + n > self.nbytes:
+            return None
+        self.top = off + n
+        return self.raw[off:off + n].view(dtype).view(*shape)      # zero-filled by mhh_peer_alloc
+
+    def contains(self, t):
+        return self.base <= t.data_ptr() and t.data_ptr() + t.numel() * t.element_size() <= self.base + self.nbytes
+
+    def connect(self, comm):
+        """Exchange the CUDA IPC handles over torch.distributed, map the other ranks' arenas, register the table."""
+        g = self.grid
+        world, me = comm.world, comm.rank
+        bases = [None] * world
+        bases[me] = self.base
+        if world > 1:
+            import torch.distributed as dist
+            h = (C.c_ubyte * 64)()
+            L.check(g.ctx, g.lib.mhh_peer_export(g.ctx, C.c_void_p(self.base), h), "mhh_peer_export")
+            handles = [None] * world
+            dist.all_gather_object(handles, (bytes(h), self.nbytes, self.top), group=comm.group)
+            for r, (hb, nb, top) in enumerate(handles):
+                if nb != self.nbytes or top != self.top:
+                    raise L.MhhError("peer arenas differ between ranks (all ranks must allocate the same arrays in the same order)")
+                if r == me:
+                    continue
+                q = C.c_void_p()
+                hr = (C.c_ubyte * 64).from_buffer_copy(hb)
+                L.check(g.ctx, g.lib.mhh_peer_import(g.ctx, hr, C.byref(q)), "mhh_peer_import")
+                bases[r] = q.value
+                self.mapped.append(q.value)
+        arr = (C.c_void_p * world)(*bases)
+        L.check(g.ctx, g.lib.mhh_peer_register(g.ctx, world, me, C.c_void_p(self.base), C.c_ulonglong(self.nbytes), arr,
+                                               C.c_ulonglong(self.flags_offset)), "mhh_peer_register")
+        self.bases = bases
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=comm.group)
+
+    def peer_ptrs(self, t):
+        """C array: the address of my tensor `t` in every rank's arena."""
+        off = t.data_ptr() - self.base
+        return (C.c_void_p * len(self.bases))(*[b + off for b in self.bases])
+
+    def close(self):
+        g = self.grid
+        if getattr(self, "base", None) and getattr(g, "ctx", None):
+            self.raw = None
+            for q in self.mapped:
+                g.lib.mhh_peer_unmap(g.ctx, C.c_void_p(q))
+            g.lib.mhh_peer_free(g.ctx, C.c_void_p(self.base))
+            self.base = None
+
+
 class Grid:
     """Grid / Grid_data (include/grid.h:50-135). ``settings`` holds the [grid] keys of the .ini."""
 
     def __init__(self, itot, jtot, ktot, xsize, ysize, zsize, z, swspatialorder="2", gc=(0, 0, 0),
-                 npy=1, rank_y=0, device=None):
+                 npy=1, rank_y=0, device=None, peer_arena=False):
         if not torch.cuda.is_available():
             raise L.MhhError("microhh_b200 needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -52,6 +134,11 @@ class Grid:
         self.shape2d = (self.jcells, self.icells)
         for name in ("z", "zh", "dz", "dzh", "dzi", "dzhi", "dzi4", "dzhi4"):
             setattr(self, name, self.metric(name))
+        # y-slab rank with the peer-memory data path: every array made by zeros() / zeros2d() lives in the exchange arena
+        self.arena = None
+        if peer_arena:
+            nfree = self.imax * self.jmax * self.kmax
+            self.arena = PeerArena(self, 8 * (16 * self.ncells + 3 * nfree + 96 * self.ijcells) + (8 << 20))
 
     def metric(self, name):
         a = np.zeros(self.kcells)
@@ -82,13 +169,19 @@ class Grid:
         return {keys[i]: (ms[i], int(cnt[i])) for i in range(min(n, len(keys)))}
 
     def zeros(self):
-        return torch.zeros(self.shape, dtype=torch.float64, device=self.device)
+        t = self.arena.alloc(self.shape) if self.arena is not None else None
+        return t if t is not None else torch.zeros(self.shape, dtype=torch.float64, device=self.device)
 
     def zeros2d(self):
-        return torch.zeros(self.shape2d, dtype=torch.float64, device=self.device)
+        t = self.arena.alloc(self.shape2d) if self.arena is not None else None
+        return t if t is not None else torch.zeros(self.shape2d, dtype=torch.float64, device=self.device)
 
     def close(self):
         if getattr(self, "ctx", None):
+            if getattr(self, "arena", None) is not None:
+                torch.cuda.synchronize(self.device)
+                self.arena.close()
+                self.arena = None
             self.lib.mhh_destroy(self.ctx)
             self.ctx = None
 
@@ -460,7 +553,7 @@ class Diff:
             return
         for n in names:
             if getattr(f.sp[n], "fld_alt", None) is None:
-                f.sp[n].fld_alt = torch.zeros_like(f.sp[n].fld)
+                f.sp[n].fld_alt = g.zeros()
         s_new = L.ptr_array([f.sp[n].fld_alt for n in names])
         sbuf = None
         if buffer is not None and buffer.swbuffer:
@@ -784,7 +877,7 @@ class Boundary_surface(Boundary):
         self.dudz_mo, self.dvdz_mo, self.dbdz_mo = z2(), z2(), z2()
         self.z0m, self.z0h = z2(z0m), z2(z0h)
         self.nobuk = torch.zeros(grid.shape2d, dtype=torch.int32, device=grid.device)
-        self._dutot = z2()
+        self._dutot = grid.zeros2d()      # exchanged between y-slab ranks: from the grid's arena when there is one
 
     def set_values(self):
         """Boundary_surface::set_values, src/boundary_surface.cxx:749-779"""

@@ -47,6 +47,8 @@ EXPORTS = [
     "mhh_fft_force_generic", "mhh_fft_forward", "mhh_fft_backward", "mhh_pres_solve_spectral", "mhh_pres_output", "mhh_pres_scatter",
     "mhh_pres_get_coefs", "mhh_pres_input_to", "mhh_fft_x", "mhh_fft_y", "mhh_transpose_copy", "mhh_pres_solve_spectral_ws",
     "mhh_pres_output_stage", "mhh_halo_ns", "mhh_fft_x_chunks", "mhh_fft_y_chunks", "mhh_fft_chunks_supported",
+    "mhh_peer_alloc", "mhh_peer_free", "mhh_peer_export", "mhh_peer_import", "mhh_peer_unmap", "mhh_peer_register", "mhh_peer_halo_push",
+    "mhh_peer_barrier", "mhh_peer_error", "mhh_fft_x_chunks_to_peers", "mhh_fft_y_chunks_to_peers",
     "mhh_cyclic", "mhh_cyclic_2d", "mhh_ghost_cells", "mhh_ghost_cells_w", "mhh_set_bc",
     "mhh_rk_substep", "mhh_rk_sub_dt", "mhh_pres_output_rk", "mhh_pres_exec_rk",
     "mhh_mean_profile", "mhh_level_sums", "mhh_mean", "mhh_mean_2d", "mhh_max",

@@ -49,7 +49,7 @@ class Model:
     [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
     (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
 
-    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None, mo=False):
+    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None, mo=False, peer_arena=False):
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
@@ -57,7 +57,7 @@ class Model:
         if swadvec == "2i5":
             gc = (3, 3, 2 if ini.get("advec", {}).get("fluxlimit_list") else 1)   # src/advec_2i5.cxx:42-45
         self.grid = Grid(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z,
-                         swspatialorder=order, gc=gc, device=device, npy=npy, rank_y=rank_y)
+                         swspatialorder=order, gc=gc, device=device, npy=npy, rank_y=rank_y, peer_arena=peer_arena)
         fi = ini.get("fields", {})
         slist = list(fi.get("slist", []))
         th = ini.get("thermo", {})

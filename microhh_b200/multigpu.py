@@ -7,12 +7,19 @@ Decomposition = the reference's MPI layout with npx = 1, npy = N (src/grid.cxx:1
     -> inverse y FFT -> all-to-all (exec_yx) -> inverse x FFT  (src/fft.cxx:452-583 with npx = 1);
   * CFL / dnmul / divergence maxima and means: all-reduce (Master::max/sum, src/master_parallel.cxx:233-256).
 
-``SlabComm`` is pure ``torch.distributed`` (tested with gloo on CPU, world_size 2); the pack/unpack around
-each collective are CUDA kernels of libmhh_b200 (``mhh_transpose_copy``, ``mhh_halo_ns``).
+Two data paths:
+  * peer (default on GPUs): every rank's exchange arena is mapped into the other ranks (CUDA IPC over NVLink / NVSwitch,
+    ``host.PeerArena``); halos are ONE kernel per exchange that stores my edge rows into the neighbours' ghost rows
+    (``mhh_peer_halo_push``), and the two all-to-alls of the solver happen INSIDE the forward x / inverse y transforms, which
+    write their chunk-layout output straight into the peers' receive buffers (``mhh_fft_x/y_chunks_to_peers``), followed by a
+    device-side barrier (``mhh_peer_barrier``).  No pack / unpack passes, no host waits; NCCL only carries the reductions.
+  * nccl (MHH_SLAB_PATH=nccl, and the gloo CPU tests): ``SlabComm`` send/recv + all_to_all_single with the pack/unpack kernels
+    ``mhh_halo_ns`` / chunk-layout transforms around them.
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -96,13 +103,30 @@ class SlabBoundaryCyclic(Boundary_cyclic):
     def __init__(self, grid, comm):
         super().__init__(grid)
         self.comm = comm
+        self.peer = False            # SlabModel switches it on once the arenas are connected
         n3 = grid.kcells * grid.jgc * grid.icells
         mk = lambda n: torch.empty(n, dtype=torch.float64, device=grid.device)
-        self.to_n, self.to_s, self.from_s, self.from_n = mk(n3), mk(n3), mk(n3), mk(n3)
+        if grid.arena is None:
+            self.to_n, self.to_s, self.from_s, self.from_n = mk(n3), mk(n3), mk(n3), mk(n3)
+        else:
+            self.to_n = self.to_s = self.from_s = self.from_n = mk(0)
+
+    def _push(self, flds, is2d):
+        """North/south rows of up to 8 fields per launch straight into the neighbours' ghost rows (peer path)."""
+        g = self.grid
+        for q in range(0, len(flds), 8):
+            part = flds[q:q + 8]
+            L.check(g.ctx, g.lib.mhh_peer_halo_push(g.ctx, len(part), L.ptr_array(part), int(is2d)), "mhh_peer_halo_push")
 
     def _ns(self, fld, is2d):
         g = self.grid
+        if self.peer:
+            self._push([fld], is2d)
+            return
         n = (1 if is2d else g.kcells) * g.jgc * g.icells
+        if self.to_n.numel() < n:
+            mk = lambda: torch.empty(g.kcells * g.jgc * g.icells, dtype=torch.float64, device=g.device)
+            self.to_n, self.to_s, self.from_s, self.from_n = mk(), mk(), mk(), mk()
         L.check(g.ctx, g.lib.mhh_halo_ns(g.ctx, L.ptr(fld), L.ptr(self.to_n), L.ptr(self.to_s), 0, int(is2d)), "mhh_halo_ns pack")
         self.comm.halo_exchange(self.to_n[:n], self.to_s[:n], self.from_s[:n], self.from_n[:n])
         L.check(g.ctx, g.lib.mhh_halo_ns(g.ctx, L.ptr(fld), L.ptr(self.from_n), L.ptr(self.from_s), 1, int(is2d)), "mhh_halo_ns unpack")
@@ -115,6 +139,9 @@ class SlabBoundaryCyclic(Boundary_cyclic):
         for fld in flds:
             L.check(g.ctx, g.lib.mhh_cyclic(g.ctx, L.ptr(fld), L.EDGE_EAST_WEST), "mhh_cyclic")
         if g.jtot <= 1 or not flds:
+            return
+        if self.peer:
+            self._push(flds, False)
             return
         n = g.kcells * g.jgc * g.icells
         if self.to_n.numel() < n * len(flds):
@@ -151,10 +178,34 @@ class SlabPres(Pres):
             raise L.MhhError("the y-slab pressure pipeline is built for swpres=2 this round")
         self.comm, self.cyclic = comm, cyclic
         n = grid.imax * grid.jmax * grid.kmax
-        self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
-        self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
+        self.peer = False          # SlabModel switches it on once the arenas are connected
+        if grid.arena is not None:
+            # X: this rank's work array; R1 / R2: receive buffers the peers' forward x / inverse y transforms write into
+            self.A, self.R1, self.R2 = (grid.arena.alloc((n,)) for _ in range(3))
+            if self.R2 is None:
+                raise L.MhhError("peer arena too small for the pressure solver's buffers")
+            self.B = self.R1
+        else:
+            self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
+            self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
-        self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours
+        self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours (nccl path)
+
+    def _exec_peer_transforms(self, p):
+        """Forward transforms, tridiagonal solve, inverse transforms with the all-to-alls fused into the transforms' stores."""
+        g, lib = self.grid, self.grid.lib
+        ck = lambda err, what: L.check(g.ctx, err, what)
+        X, R1, R2 = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2)
+        if self._r1_peers is None:
+            self._r1_peers, self._r2_peers = g.arena.peer_ptrs(self.R1), g.arena.peer_ptrs(self.R2)
+        ck(lib.mhh_fft_x_chunks_to_peers(g.ctx, X, self._r1_peers, 0, g.kmax), "fft_x fwd -> peers")
+        ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+        ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, 0, g.kmax), "chunks -> fft_y fwd")
+        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")      # R1 is free until the peers' next forward pass
+        ck(lib.mhh_fft_y_chunks_to_peers(g.ctx, X, self._r2_peers, 0, g.kmax), "fft_y bwd -> peers")
+        ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+        ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
+    _r1_peers = None
 
     def exec(self, dt, stats=None, timeloop=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
@@ -169,7 +220,9 @@ class SlabPres(Pres):
         self.cyclic.exec(ut, L.EDGE_EAST_WEST)
         self.cyclic.exec(vt, L.EDGE_NORTH_SOUTH)
         ck(lib.mhh_pres_input_to(g.ctx, L.ptr(u), L.ptr(v), L.ptr(w), L.ptr(ut), L.ptr(vt), L.ptr(wt), C.c_double(dt), A), "pres_input")
-        if self.chunk_fft:
+        if self.peer and self.chunk_fft:
+            self._exec_peer_transforms(p)
+        elif self.chunk_fft:
             # The transforms read / write the all-to-all chunk layout themselves (no pack / unpack passes), and the slab is
             # cut into k ranges: the collective of one range runs on NCCL's stream while the transforms of the next are
             # computed (the tridiagonal solve in the middle needs all levels and is the only join).
@@ -226,13 +279,30 @@ class SlabModel(Model):
     surface layer, tendencies, Buffer, Force, pressure, RK — Model.exec_substep), with the halo fills going through the ring
     neighbours and every maximum / mean reduced over the ranks (Master::max / Master::sum)."""
 
-    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None, profs=None, mo=False):
-        super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank, profs=profs, mo=mo)
+    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None, profs=None, mo=False, path=None):
+        path = path or os.environ.get("MHH_SLAB_PATH", "peer")
+        if path not in ("peer", "nccl"):
+            raise L.MhhError("MHH_SLAB_PATH / path must be peer or nccl")
+        if world > 8:
+            path = "nccl"            # the peer tables hold 8 ranks (one NVSwitch box)
+        super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank, profs=profs, mo=mo,
+                         peer_arena=(path == "peer"))
         self.comm = SlabComm(rank, world, group)
         self.fields.comm = self.comm
         self.cyclic = SlabBoundaryCyclic(self.grid, self.comm)
         self.boundary.boundary_cyclic = self.cyclic
         self.pres = SlabPres(self.grid, self.fields, self.pres.swpres, self.comm, self.cyclic)
+        self.path = path
+        if path == "peer":
+            self.grid.arena.connect(self.comm)       # CUDA IPC handles over torch.distributed; host barrier
+            self.cyclic.peer = self.pres.peer = True
+
+    def check_peers(self):
+        """Raises when a device-side flag wait of the peer path timed out (a rank was lost)."""
+        err = C.c_int()
+        L.check(self.grid.ctx, self.grid.lib.mhh_peer_error(self.grid.ctx, C.byref(err)), "mhh_peer_error")
+        if err.value:
+            raise L.MhhError("peer-memory exchange timed out waiting for a neighbour's flag")
 
     def _cyclic_prognostic(self):
         self.cyclic.exec_many(fld.fld for fld in self.fields.ap.values())      # set_prognostic_cyclic_bcs, one exchange
@@ -247,6 +317,8 @@ class SlabModel(Model):
 
     def print_status(self):
         g, f, tl, dev = self.grid, self.fields, self.timeloop, self.grid.device
+        if self.path == "peer":
+            self.check_peers()
         for fld in f.mp.values():
             self.cyclic.exec(fld.fld)
         # per-rank sums are already divided by the GLOBAL itot*jtot*zsize inside the library

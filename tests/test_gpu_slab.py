@@ -11,24 +11,29 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+@pytest.mark.parametrize("path", ["peer", "nccl"])
 @pytest.mark.parametrize("dims", [(32, 32, 16), (32, 256, 8)], ids=["staged_fft", "col_fft_chunks"])
-def test_slab_world1_bit_identical(cuda_lib, dims):
-    """dims (32, 256, 8): the y passes run on the lanes-along-the-lines kernel in its chunk-layout (SPLIT) form."""
+def test_slab_world1_bit_identical(cuda_lib, dims, path, monkeypatch):
+    """dims (32, 256, 8): the y passes run on the lanes-along-the-lines kernel in its chunk-layout (SPLIT) form.
+    path peer: the exchange arena, the halo push kernel, the device barrier and the transforms that write the peers' receive
+    buffers, with this rank as its own neighbour; path nccl: the pack / unpack kernels around torch.distributed."""
     import torch
     from tests.slab_parity import run
+    monkeypatch.setenv("MHH_SLAB_PATH", path)
     out, status, ref = run(0, 1, torch.device("cuda:0"), dims=dims)
     for k in ("u", "v", "w", "th", "p"):
         assert np.array_equal(out[k], ref[k]), k
     assert status["dt"] == ref["status"]["dt"]
 
 
+@pytest.mark.parametrize("path", ["peer", "nccl"])
 @pytest.mark.parametrize("dims", ["64,64,32", "32,512,8"], ids=["staged_fft", "col_fft_chunks"])
-def test_slab_two_ranks_nccl(cuda_lib, dims):
+def test_slab_two_ranks_nccl(cuda_lib, dims, path):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29533", os.path.join(ROOT, "tests", "slab_parity.py")], capture_output=True, text=True, timeout=600,
-                       env=dict(os.environ, SLAB_DIMS=dims))
+                       env=dict(os.environ, SLAB_DIMS=dims, MHH_SLAB_PATH=path))
     print(r.stdout[-3000:], r.stderr[-2000:])
     assert r.returncode == 0 and "SLAB PARITY OK" in r.stdout
