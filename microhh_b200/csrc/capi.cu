@@ -569,7 +569,7 @@ int mhh_advec2_smag2_exec(mhh_ctx* c, int surface_model, const double* u, const 
                           const double* const* sfb, const double* const* sft, const double* svisc, double tPr)
 {
     CTX_CHECK(c);
-    if (c->order != 2 || c->gd.igc != 1 || c->gd.jgc != 1) { c->last_error = "mhh_advec2_smag2_exec needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
+    if (c->order != 2) { c->last_error = "mhh_advec2_smag2_exec needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
     if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
     return advec2_smag2_exec(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft, svisc, tPr);
 }
@@ -581,7 +581,7 @@ int mhh_advec2_smag2_exec_rk(mhh_ctx* c, int surface_model, const double* u, con
                              const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt)
 {
     CTX_CHECK(c);
-    if (c->order != 2 || c->gd.igc != 1 || c->gd.jgc != 1) { c->last_error = "mhh_advec2_smag2_exec_rk needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
+    if (c->order != 2) { c->last_error = "mhh_advec2_smag2_exec_rk needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
     if (surface_model && (!ufb || !uft || !vfb || !vft)) return MHH_ERR_ARG;
     if (s_new && rkorder != 3 && rkorder != 4) { c->last_error = "rkorder must be 3 or 4"; return MHH_ERR_ARG; }
     if (s_new) for (int n = 0; n < ns; ++n) if (s_new[n] && s_new[n] == s[n])

@@ -27,7 +27,9 @@ namespace
 bool tma_planes_supported(const Ctx* c, const int boxx)
 {
     const GridD& gd = c->gd;
-    return !c->tma_off && (gd.icells % 2 == 0) && (boxx % 2 == 0) && boxx <= 256 && encode_fn() != nullptr;
+    // the box of tile t starts at element t*TX + igc - 1 of a row: kept 16-byte aligned (odd igc, even TX) — with igc = 2 the
+    // copies raised "illegal instruction" on B200 (r02f), so such grids take the cp.async path
+    return !c->tma_off && (gd.icells % 2 == 0) && (gd.igc % 2 == 1) && (boxx % 2 == 0) && boxx <= 256 && encode_fn() != nullptr;
 }
 
 int tma_plane_map(Ctx* c, const double* fld, const int boxx, const int boxy, CUtensorMap* out)

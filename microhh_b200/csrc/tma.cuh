@@ -6,7 +6,8 @@
 // completes the slot's `full` mbarrier through complete_tx; parts of the box outside the array are zero-filled by the
 // hardware (they only feed threads that store nothing).  This replaces the per-thread 8-byte cp.async (LDGSTS) copies of
 // TileMap and their address arithmetic.  Requirements of the tiled mode: 16-byte aligned base and row pitch (icells even),
-// box rows a multiple of 16 bytes (TX + 2H even), 128-byte aligned shared-memory destinations.
+// box rows a multiple of 16 bytes (TX + 2H even), box starts on 16-byte boundaries (odd igc), 128-byte aligned shared-memory
+// destinations.
 #pragma once
 
 #include <cuda.h>

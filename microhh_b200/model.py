@@ -53,7 +53,7 @@ class Model:
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
-        gc = (0, 0, 0)
+        gc = tuple(gi.get("gc", (0, 0, 0)))        # optional extra ghost cells (the library takes the scheme's minimum at least)
         if swadvec == "2i5":
             gc = (3, 3, 2 if ini.get("advec", {}).get("fluxlimit_list") else 1)   # src/advec_2i5.cxx:42-45
         self.grid = Grid(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z,

@@ -18,15 +18,17 @@ TOL_FIELD = 1e-12
     dict(itot=32, jtot=32, ktot=32, surface_model=1),
     dict(itot=64, jtot=32, ktot=16, surface_model=1, anelastic=True, alpha=1.5),
     dict(itot=32, jtot=48, ktot=20, nscalars=2),
-], ids=["cube32", "anelastic", "surface", "surface_anelastic_stretched", "two_scalars"])
+    dict(itot=40, jtot=24, ktot=70, surface_model=1, gc=(2, 2, 1)),       # more ghost cells than the scheme's minimum
+], ids=["cube32", "anelastic", "surface", "surface_anelastic_stretched", "two_scalars", "gc221"])
 def test_les_substep_matches_reference(cuda_lib, kw):
     case = make_case(**kw)
     got = run_substep_gpu(case)
     want = run_substep_oracle(case)
     ks, ke = case["ks"], case["ke"]
     errs = {}
+    gi, gj = case["gc"][0], case["gc"][1]
     for name in ("ut", "vt", "wt", "st0", "evisc", "u", "v", "w", "s0", "p"):
-        errs[name] = rel_err(got[name][ks:ke, 1:-1, 1:-1], want[name][ks:ke, 1:-1, 1:-1])
+        errs[name] = rel_err(got[name][ks:ke, gj:-gj, gi:-gi], want[name][ks:ke, gj:-gj, gi:-gi])
     print(errs, got["scalars"], want["scalars"])
     for name in ("ut", "vt", "wt", "st0"):
         assert errs[name] <= TOL_TEND, (name, errs[name])
