@@ -450,6 +450,7 @@ def main():
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    slab_timing = model.pres.timing_report() if getattr(getattr(model, "pres", None), "timing", None) is not None else None
     launches = g.launch_count() - launches0
     prof = g.profile_report()
     g.profile_enable(False)
@@ -551,6 +552,9 @@ def main():
     if slab_parity is not None:
         line["slab_parity"] = slab_parity
         line["config"]["slab_path"] = getattr(model, "path", None)
+        line["config"]["slab_a2a"] = getattr(model.pres, "a2a", None)
+        if slab_timing:
+            line["slab_exchange_timing"] = slab_timing
     if world == 1 and not args.no_secondary:
         del model
         torch.cuda.empty_cache()

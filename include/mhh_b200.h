@@ -131,6 +131,18 @@ int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* ctx, int surface_model,
                                         const double* dbdz, const double* z0m,
                                         double cs, double tPr, double visc, double* evisc,
                                         double* cfl_over_dt, double* dnmul);
+/* mhh_advec2_smag2_exec_rk in parts: the momentum pass (do_uvw) and / or the scalar passes (do_scalars) restricted to the
+ * 64-level k chunks [kc0, kc0 + nkc) (nkc <= 0: up to the top).  The scalar passes do not depend on the pressure solver; a
+ * y-slab caller issues them on a second stream in halves that run while the copy engines carry the solver's all-to-all
+ * chunks.  The parts of one substep together are bit-identical to one mhh_advec2_smag2_exec_rk call. */
+int mhh_advec2_smag2_exec_rk_parts(mhh_ctx* ctx, int surface_model,
+                                   const double* u, const double* v, const double* w, const double* evisc,
+                                   double* ut, double* vt, double* wt,
+                                   const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
+                                   double visc, const double* th_buoy, int nscalars, const double* const* s, double* const* st,
+                                   const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr,
+                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt,
+                                   int do_uvw, int do_scalars, int kc0, int nkc);
 /* Buffer::exec (src/buffer.cxx:163; calc_buffer :37-58) and the swlspres=geo branch of Force::exec (src/force.cxx:609-625,
  * calc_coriolis_2nd :76-107) for u,v,w, applied inside the fused momentum pass of mhh_advec2_smag2_exec[_rk] to the finished
  * tendency of each cell in the time loop's order (bit-identical to mhh_buffer_exec + mhh_force_coriolis run afterwards, without

@@ -41,6 +41,10 @@ int advec2_smag2_exec_rk(Ctx*, int, const double*, const double*, const double*,
                          const double*, const double*, const double*, const double*, double, const double*, int,
                          const double* const*, double* const*, const double* const*, const double* const*, const double*, double,
                          const double* const*, double* const*, int, int, double);
+int advec2_smag2_exec_rk_parts(Ctx*, int, const double*, const double*, const double*, const double*, double*, double*, double*,
+                               const double*, const double*, const double*, const double*, double, const double*, int,
+                               const double* const*, double* const*, const double* const*, const double* const*, const double*, double,
+                               const double* const*, double* const*, int, int, double, int, int, int, int);
 int smag2_dnmul_bits(Ctx*, const double*, double, unsigned long long*);
 // boundary.cu
 int cyclic_exec(Ctx*, double*, int);
@@ -588,6 +592,27 @@ int mhh_advec2_smag2_exec_rk(mhh_ctx* c, int surface_model, const double* u, con
     { c->last_error = "mhh_advec2_smag2_exec_rk: s_new must not alias s (neighbouring tiles still read s)"; return MHH_ERR_ARG; }
     return advec2_smag2_exec_rk(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft,
                                 svisc, tPr, sbuf, s_new, rkorder, substep, dt);
+}
+
+// mhh_advec2_smag2_exec_rk in parts: the momentum pass (do_uvw) and / or the scalar passes (do_scalars) on the 64-level chunks
+// [kc0, kc0 + nkc) of the column (nkc <= 0: to the top).  The scalar passes are independent of the pressure solver, so a
+// decomposed caller issues them on a second stream in two halves that run while the copy engines move the solver's
+// all-to-all chunks (multigpu.SlabModel).  The parts of one substep together equal one mhh_advec2_smag2_exec_rk call.
+int mhh_advec2_smag2_exec_rk_parts(mhh_ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                                   double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
+                                   double visc, const double* th_buoy, int ns, const double* const* s, double* const* st,
+                                   const double* const* sfb, const double* const* sft, const double* svisc, double tPr,
+                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt,
+                                   int do_uvw, int do_scalars, int kc0, int nkc)
+{
+    CTX_CHECK(c);
+    if (c->order != 2) { c->last_error = "mhh_advec2_smag2_exec_rk_parts needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
+    if (ns < 0 || ns > 8 || (ns > 0 && (!s || !st || !svisc)) || kc0 < 0) return MHH_ERR_ARG;
+    if (s_new && rkorder != 3 && rkorder != 4) { c->last_error = "rkorder must be 3 or 4"; return MHH_ERR_ARG; }
+    if (s_new) for (int n = 0; n < ns; ++n) if (s_new[n] && s_new[n] == s[n])
+    { c->last_error = "mhh_advec2_smag2_exec_rk_parts: s_new must not alias s"; return MHH_ERR_ARG; }
+    return advec2_smag2_exec_rk_parts(c, surface_model, u, v, w, evisc, ut, vt, wt, ufb, uft, vfb, vft, visc, th_buoy, ns, s, st, sfb, sft,
+                                      svisc, tPr, sbuf, s_new, rkorder, substep, dt, do_uvw, do_scalars, kc0, nkc);
 }
 
 // Lazy-tendency mode of the fused 2nd-order LES path.  Timeloop::exec leaves every tendency at zero after the last substep

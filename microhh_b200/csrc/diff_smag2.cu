@@ -708,7 +708,7 @@ constexpr int UVW_SLOTS = 6;
                              const double* __restrict__ fluxbot, const double* __restrict__ fluxtop,
                              const double tPr, const double visc,
                              const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ w,
-                             const ScalarTail tail, const GridD gd, const __grid_constant__ TmaMaps4 maps)
+                             const ScalarTail tail, const GridD gd, const __grid_constant__ TmaMaps4 maps, const int kc0)
     {
         using Map = TileMap<TX, TY, 1>;
         constexpr int W = Map::W, PS = TMA ? tma_plane_pitch(Map::W, Map::HT) : Map::N, NS = 4, NF = ADVEC ? 4 : 2;
@@ -726,7 +726,7 @@ constexpr int UVW_SLOTS = 6;
         const bool live = (i < gd.iend) && (j < gd.jend);
         const int jj = gd.icells, kk = gd.ijcells;
         const int ij = min(i, gd.icells - 1) + min(j, gd.jcells - 1) * jj;
-        const int k0 = gd.kstart + blockIdx.z * KCHUNK;
+        const int k0 = gd.kstart + (blockIdx.z + kc0) * KCHUNK;     // kc0: first chunk of this call (k-range parts)
         const int k1 = min(k0 + KCHUNK, gd.kend);
         const double dxi = 1. / gd.dx, dyi = 1. / gd.dy;
         const double dxidxi = 1. / (gd.dx * gd.dx), dyidyi = 1. / (gd.dy * gd.dy);
@@ -1072,8 +1072,15 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
 {
     const GridD& gd = c->gd;
     ScalarTail tail{nullptr, 0., 0., 0, nullptr, nullptr, 0, 0};
+    // k-range parts (mhh_advec2_smag2_exec_rk_parts): chunks [kc0, kc0 + nkc) of the column; bookkeeping that concerns the
+    // whole tendency array (lazy-tendency flags, the zeroing after the last substep) happens with the part that ends the column
+    const int nchunks = (gd.kmax + KCHUNK - 1) / KCHUNK;
+    const int kc0 = c->sc_kc0 < 0 ? 0 : (c->sc_kc0 > nchunks ? nchunks : c->sc_kc0);
+    const int nkc = (c->sc_nkc <= 0 || kc0 + c->sc_nkc > nchunks) ? nchunks - kc0 : c->sc_nkc;
+    const bool last_part = kc0 + nkc >= nchunks;
+    if (nkc <= 0) return MHH_OK;
     for (auto& fp : c->fresh_s)
-        if (fp == at && at != nullptr) { tail.fresh = 1; fp = nullptr; }
+        if (fp == at && at != nullptr) { tail.fresh = 1; if (last_part) fp = nullptr; }
     if (sbuf)
     {
         if (!c->buffer_sigma_d) { c->last_error = "buffer not planned (mhh_buffer_plan)"; return MHH_ERR_STATE; }
@@ -1086,7 +1093,7 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
         tail.a_new = a_new; tail.rk_mode = zero_all ? 2 : 1;
     }
     constexpr int TX = MHH_TILE_X, TY = 256 / MHH_TILE_X;
-    const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, (gd.kmax + KCHUNK - 1) / KCHUNK);
+    const dim3 tb(TX, TY, 1), tg((gd.imax + TX - 1) / TX, (gd.jmax + TY - 1) / TY, nkc);
     TmaMaps4 maps;
     bool tma = tma_planes_supported(c, TX + 2);
     if (tma)
@@ -1100,8 +1107,8 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
         }
     }
     #define SC_LAUNCH(NAME, S, A) do { \
-        if (tma) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, true><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps))); \
-        else     MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, false><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps))); } while (0)
+        if (tma) MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, true><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps, kc0))); \
+        else     MHH_LAUNCH(c, NAME, (smag2_scalar_tile_kernel<S, A, TX, TY, false><<<tg, tb, 0, c->stream>>>(at, a, evisc, fluxbot, fluxtop, tPr, visc, u, v, w, tail, gd, maps, kc0))); } while (0)
     if (!advec)
     {
         if (surface_model) SC_LAUNCH("smag2_diff_c_kernel", true, false);
@@ -1114,7 +1121,7 @@ int smag2_tend_scalar_tail(Ctx* c, int surface_model, int advec, double* at, con
     }
     #undef SC_LAUNCH
     MHH_LAUNCH_CHECK();
-    if (tail.rk_mode == 2)      // last substep: the whole tendency array (ghost cells too) is zero afterwards, src/timeloop.cu:34-70
+    if (tail.rk_mode == 2 && last_part)      // last substep: the whole tendency array (ghost cells too) is zero afterwards, src/timeloop.cu:34-70
     {
         bool lazy = false;
         if (c->lazy_tend)       // ... or declared undefined until the next fused tendency pass, which then starts from 0
@@ -1146,6 +1153,28 @@ int advec2_smag2_exec_rk(Ctx* c, int surface_model, const double* u, const doubl
                                            surface_model ? sfluxtop[n] : nullptr, tPr, svisc[n], u, v, w,
                                            sbuf ? sbuf[n] : nullptr, s_new ? s_new[n] : nullptr, rkorder, substep, dt)) return e;
     return MHH_OK;
+}
+
+// mhh_advec2_smag2_exec_rk_parts: the momentum pass and / or the scalar passes restricted to the 64-level chunks [kc0, kc0 + nkc)
+int advec2_smag2_exec_rk_parts(Ctx* c, int surface_model, const double* u, const double* v, const double* w, const double* evisc,
+                               double* ut, double* vt, double* wt,
+                               const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
+                               double visc, const double* th_buoy, int nscalars, const double* const* s, double* const* st,
+                               const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr,
+                               const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt,
+                               int do_uvw, int do_scalars, int kc0, int nkc)
+{
+    if (do_uvw)
+        if (int e = smag2_tend_uvw(c, surface_model, 1, u, v, w, evisc, ut, vt, wt, ufluxbot, ufluxtop, vfluxbot, vfluxtop, visc, th_buoy)) return e;
+    if (!do_scalars) return MHH_OK;
+    c->sc_kc0 = kc0; c->sc_nkc = nkc;
+    int err = MHH_OK;
+    for (int n = 0; n < nscalars && !err; ++n)
+        err = smag2_tend_scalar_tail(c, surface_model, 1, st[n], s[n], evisc, surface_model ? sfluxbot[n] : nullptr,
+                                     surface_model ? sfluxtop[n] : nullptr, tPr, svisc[n], u, v, w,
+                                     sbuf ? sbuf[n] : nullptr, s_new ? s_new[n] : nullptr, rkorder, substep, dt);
+    c->sc_kc0 = 0; c->sc_nkc = 0;
+    return err;
 }
 
 // Thermo_dry::exec (th_buoy != nullptr) + Advec_2::exec + Diff_smag2::exec: one pass per prognostic field

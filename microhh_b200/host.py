@@ -528,13 +528,15 @@ class Diff:
                 L.ptr(f.mp["u"].flux_bot), L.ptr(f.mp["u"].flux_top), L.ptr(f.mp["v"].flux_bot), L.ptr(f.mp["v"].flux_top),
                 C.c_double(f.visc), len(names), s, st, sfb, sft, svisc, C.c_double(self.tPr)), "mhh_smag2_exec")
 
-    def exec_with_advec2(self, th_buoy=None, buffer=None, timeloop=None):
+    def exec_with_advec2(self, th_buoy=None, buffer=None, timeloop=None, parts=None):
         """Thermo_dry::exec (when th_buoy is given) + Advec_2::exec + Diff_smag2::exec in one pass per prognostic field
         (mhh_advec2_smag2_exec); bit-identical to the three calls in the time loop's order.
         With ``timeloop`` (and optionally ``buffer``) the scalars' Buffer term and RK update ride in their pass
         (mhh_advec2_smag2_exec_rk): the updated scalar lands in Field3d.fld_alt and the two tensors are swapped here, so on
         return ``fields.sp[name].fld`` is the advanced field (ghost cells stale until the next set_*_bcs, as after
-        Timeloop::exec).  Only valid when nothing else adds to the scalar tendencies afterwards."""
+        Timeloop::exec).  Only valid when nothing else adds to the scalar tendencies afterwards.
+        ``parts`` = (do_uvw, do_scalars, kc0, nkc): only the momentum pass and / or the scalar passes on the 64-level chunks
+        [kc0, kc0 + nkc) (mhh_advec2_smag2_exec_rk_parts); the caller swaps fld / fld_alt (swap_scalars) after the last part."""
         g, f = self.grid, self.fields
         if self.swdiff != "smag2" or g.order != 2:
             raise L.MhhError("the fused tendency pass needs swdiff=smag2 on the 2nd-order grid")
@@ -558,10 +560,19 @@ class Diff:
         sbuf = None
         if buffer is not None and buffer.swbuffer:
             sbuf = L.ptr_array([f.sp[n].fld_mean if buffer.swupdate else buffer.bufferprofs[n] for n in names])
+        if parts is not None:
+            L.check(g.ctx, g.lib.mhh_advec2_smag2_exec_rk_parts(*args, sbuf, s_new, timeloop.rkorder, timeloop.substep,
+                                                                C.c_double(timeloop.dt), *[int(x) for x in parts]),
+                    "mhh_advec2_smag2_exec_rk_parts")
+            return
         L.check(g.ctx, g.lib.mhh_advec2_smag2_exec_rk(*args, sbuf, s_new, timeloop.rkorder, timeloop.substep, C.c_double(timeloop.dt)),
                 "mhh_advec2_smag2_exec_rk")
-        for n in names:
-            f.sp[n].fld, f.sp[n].fld_alt = f.sp[n].fld_alt, f.sp[n].fld
+        self.swap_scalars()
+
+    def swap_scalars(self):
+        """After the scalars' fused RK update: Field3d.fld_alt holds the advanced scalar."""
+        for fld in self.fields.sp.values():
+            fld.fld, fld.fld_alt = fld.fld_alt, fld.fld
 
     def exec_with_advec4(self):
         """Advec_4::exec + set_ghost_cells_w(Normal) + Diff_4::exec (src/model.cxx:387-392) through mhh_advec4_diff4_exec:
@@ -621,10 +632,12 @@ class Pres:
         g = self.grid
         L.check(g.ctx, g.lib.mhh_pres_set_values(g.ctx), "mhh_pres_set_values")
 
-    def exec(self, dt, stats=None, timeloop=None):
+    def exec(self, dt, stats=None, timeloop=None, hooks=None):
         """Pres::exec.  With `timeloop` the gradient stage is fused with Timeloop::exec for u,v,w (mhh_pres_exec_rk):
         returns True, and the caller must run timeloop.exec(skip=("u", "v", "w")) and must NOT call
         set_ghost_cells_w(Normal) in between (4th order: the fused call has done it on the not yet updated w)."""
+        for h in hooks or ():       # independent work a decomposed solver overlaps with its exchanges: here simply run first
+            h()
         if self.swpres == "0":
             return False
         g, f = self.grid, self.fields

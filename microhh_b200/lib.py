@@ -38,7 +38,7 @@ EXPORTS = [
     "mhh_launch_count", "mhh_profile_enable", "mhh_profile_report",
     "mhh_advec_exec", "mhh_advec_cfl", "mhh_advec_time_limit",
     "mhh_diff2_exec", "mhh_diff4_exec", "mhh_advec4_diff4_exec", "mhh_diff_const_dnmul",
-    "mhh_smag2_exec_viscosity", "mhh_smag2_exec_viscosity_dry", "mhh_smag2_exec_viscosity_dry_limits", "mhh_smag2_exec", "mhh_advec2_smag2_exec", "mhh_advec2_smag2_exec_rk", "mhh_smag2_strain2", "mhh_smag2_dnmul", "mhh_set_lazy_tendencies", "mhh_advec2_smag2_set_force_tail", "mhh_set_tma", "mhh_tma_active", "mhh_pres_set_fused_input",
+    "mhh_smag2_exec_viscosity", "mhh_smag2_exec_viscosity_dry", "mhh_smag2_exec_viscosity_dry_limits", "mhh_smag2_exec", "mhh_advec2_smag2_exec", "mhh_advec2_smag2_exec_rk", "mhh_advec2_smag2_exec_rk_parts", "mhh_smag2_strain2", "mhh_smag2_dnmul", "mhh_set_lazy_tendencies", "mhh_advec2_smag2_set_force_tail", "mhh_set_tma", "mhh_tma_active", "mhh_pres_set_fused_input",
     "mhh_thermo_set_ref", "mhh_thermo_dry_exec", "mhh_thermo_dry_N2",
     "mhh_surface_init_solver", "mhh_surface_get_lut", "mhh_boundary_surface_exec", "mhh_boundary_surface_exec_stages", "mhh_surface_scalar",
     "mhh_buffer_plan", "mhh_buffer_exec", "mhh_force_pressure", "mhh_force_fixed_flux", "mhh_force_coriolis",

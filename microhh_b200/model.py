@@ -140,6 +140,11 @@ class Model:
     def _reduce_max(self, values):
         return values
 
+    def _scalar_halves(self):
+        """True: the scalars' fused tendency + RK passes are issued in two k halves from inside Pres::exec (hooks), where a
+        decomposed solver overlaps them with its exchanges (multigpu.SlabModel)."""
+        return False
+
     def exec_substep(self):
         b, tl = self.boundary, self.timeloop
         self._cyclic_prognostic()                          # src/model.cxx:346
@@ -163,10 +168,18 @@ class Model:
         if self.mo:             # :376-377 (Thermo::exec of :366 only adds to wt, which the surface layer does not read)
             b.exec(self.thermo)
             b.set_ghost_cells()
+        hooks = None
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
             srk = self.fuse_scalar_rk
-            self.diff.exec_with_advec2(self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None,
-                                       buffer=self.buffer if srk else None, timeloop=tl if srk else None)
+            th_b = self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None
+            if srk and self._scalar_halves():
+                nch = (self.grid.kmax + 63) // 64
+                half = max(1, nch // 2)               # chunks of the first half; a second part starting at nch is a no-op
+                part = lambda *p: (lambda: self.diff.exec_with_advec2(th_b, buffer=self.buffer, timeloop=tl, parts=p))
+                part(1, 0, 0, 0)()                                     # the momentum pass now
+                hooks = (part(0, 1, 0, half), part(0, 1, half, 0))     # the scalar passes from inside the pressure solver
+            else:
+                self.diff.exec_with_advec2(th_b, buffer=self.buffer if srk else None, timeloop=tl if srk else None)
         elif self.fuse_tend4:   # :387-392 in one call, the momentum diffusion inside the advection passes
             self.thermo.exec()                             # :366
             b.set_ghost_cells_w(L.BCW_CONSERVATION)        # :387
@@ -183,7 +196,9 @@ class Model:
         self.force.exec(tl.get_sub_time_step(), self.thermo, skip_coriolis=self.fuse_force)   # :404
         b.set_ghost_cells_w(L.BCW_CONSERVATION)            # :410
         # :411 + :484 for u,v,w in one pass
-        fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None)
+        fused = self.pres.exec(tl.get_sub_time_step(), timeloop=tl if self.fuse_pres_rk else None, hooks=hooks)
+        if hooks:
+            self.diff.swap_scalars()
         if not fused:
             b.set_ghost_cells_w(L.BCW_NORMAL)              # :412 (inside the fused call otherwise)
         tl.exec(skip=(("u", "v", "w") if fused else ()) + done_s)     # :484

@@ -190,27 +190,156 @@ class SlabPres(Pres):
             self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
         self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
         self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours (nccl path)
+        # how the peer path moves the all-to-all chunks.  Measured on 2 x B200 at 512^3 per GPU (r02i-r02l): fused 44.4 ms/step,
+        # fused_pipe 44.6, ce 45.3, ce_overlap 48.5 — the copy engines reach 763 GB/s alone (tools/bench_peer_copy.py) but only
+        # half of that next to an HBM-saturating kernel (copies 1.76 ms instead of 0.87 next to the scalar pass)
+        self.a2a = os.environ.get("MHH_SLAB_A2A", "fused")
+        self.timing = [] if os.environ.get("MHH_SLAB_TIMING") else None     # ce_overlap: CUDA events of every exchange
 
-    def _exec_peer_transforms(self, p):
-        """Forward transforms, tridiagonal solve, inverse transforms with the all-to-alls fused into the transforms' stores."""
+    def timing_report(self):
+        """ms, averaged over the recorded exchanges: copies, barrier wait after the copies, hook kernel, main stream stalled."""
+        torch.cuda.synchronize(self.grid.device)
+        rows = [(a.elapsed_time(b), b.elapsed_time(c), a.elapsed_time(d), d.elapsed_time(e)) for a, b, c, d, e in self.timing]
+        self.timing.clear()
+        n = max(len(rows), 1)
+        return dict(exchanges=len(rows), copies_ms=sum(r[0] for r in rows) / n, barrier_ms=sum(r[1] for r in rows) / n,
+                    hook_ms=sum(r[2] for r in rows) / n, main_stalled_ms=sum(r[3] for r in rows) / n)
+
+    def _exec_ce_overlap(self, p, hooks):
+        """MHH_SLAB_A2A=ce_overlap: the sending transforms write their chunks locally, the copy engines move them into the
+        peers' receive buffers (one cudaMemcpyAsync per peer on a side stream, SMs not involved), and in the meantime the
+        main stream runs `hooks[0]` / `hooks[1]` — the two k halves of the scalar tendency + RK pass, which do not depend on
+        the pressure — before it waits for the device barrier and runs the receiving transforms."""
+        g, lib = self.grid, self.grid.lib
+        ck = lambda err, what: L.check(g.ctx, err, what)
+        X, R1, R2, S = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2), L.ptr(self.S)
+        world, me = self.comm.world, self.comm.rank
+        R = g.kmax * g.jmax * (g.itot // world)
+        main, xfer = torch.cuda.current_stream(g.device), self._side[0]
+        on = lambda st: lib.mhh_set_stream(g.ctx, C.c_void_p(st.cuda_stream))
+
+        T = self.timing is not None
+        mk = lambda: torch.cuda.Event(enable_timing=T)
+
+        def exchange(peers_t, hook):
+            ev = mk(); ev.record(main)
+            xfer.wait_event(ev)
+            with torch.cuda.stream(xfer):
+                for d in range(world):
+                    r = (me + d) % world
+                    peers_t[r][me * R:(me + 1) * R].copy_(self.S[r * R:(r + 1) * R], non_blocking=True)
+            ev_c = mk(); ev_c.record(xfer)
+            on(xfer)
+            ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+            ev2 = mk(); ev2.record(xfer)
+            on(main)
+            if hook is not None:
+                hook()
+            ev_h = mk(); ev_h.record(main)
+            main.wait_event(ev2)
+            ev_w = mk(); ev_w.record(main)
+            if T:       # (send transform done, copies done, barrier done, hook done, main resumes)
+                self.timing.append((ev, ev_c, ev2, ev_h, ev_w))
+
+        ck(lib.mhh_fft_x_chunks(g.ctx, -1, X, S, None, 0, g.kmax), "fft_x fwd -> chunks")
+        exchange(self._r1_t, hooks[0] if hooks else None)
+        ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, 0, g.kmax), "chunks -> fft_y fwd")
+        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")
+        ck(lib.mhh_fft_y_chunks(g.ctx, +1, X, S, 0, g.kmax), "fft_y bwd -> chunks")
+        exchange(self._r2_t, hooks[1] if hooks else None)
+        ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
+
+    def _exec_peer_transforms(self, p, hooks=None):
+        """Forward transforms, tridiagonal solve, inverse transforms with the all-to-alls fused into the transforms' stores
+        (MHH_SLAB_A2A=fused, one k range), the same cut into k ranges whose NVLink-bound sending transform overlaps the
+        receiving transform of the previous range on a second stream (fused_pipe, default), or the chunks written locally and
+        moved by the copy engines, one cudaMemcpyAsync per peer and k range, while the SMs transform the next range (ce)."""
         g, lib = self.grid, self.grid.lib
         ck = lambda err, what: L.check(g.ctx, err, what)
         X, R1, R2 = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2)
         if self._r1_peers is None:
             self._r1_peers, self._r2_peers = g.arena.peer_ptrs(self.R1), g.arena.peer_ptrs(self.R2)
-        ck(lib.mhh_fft_x_chunks_to_peers(g.ctx, X, self._r1_peers, 0, g.kmax), "fft_x fwd -> peers")
-        ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
-        ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, 0, g.kmax), "chunks -> fft_y fwd")
-        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")      # R1 is free until the peers' next forward pass
-        ck(lib.mhh_fft_y_chunks_to_peers(g.ctx, X, self._r2_peers, 0, g.kmax), "fft_y bwd -> peers")
-        ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
-        ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
+            if self.a2a not in ("fused", "fused_pipe", "ce", "ce_overlap"):
+                raise L.MhhError("MHH_SLAB_A2A must be fused, fused_pipe, ce or ce_overlap")
+            if self.a2a != "fused":
+                self._side = [torch.cuda.Stream(device=g.device), torch.cuda.Stream(device=g.device)]
+            if self.a2a in ("ce", "ce_overlap"):
+                from .host import _RawCuda
+                nb = self.R1.numel() * 8
+                wrap = lambda ptr: torch.as_tensor(_RawCuda(ptr, nb), device=g.device).view(torch.float64)
+                self._r1_t = [wrap(q) for q in self._r1_peers]
+                self._r2_t = [wrap(q) for q in self._r2_peers]
+                self.S = torch.empty_like(self.A)
+        if self.a2a == "ce_overlap":
+            return self._exec_ce_overlap(p, hooks)
+        for h in hooks or ():
+            h()
+        if self.a2a == "fused":
+            ck(lib.mhh_fft_x_chunks_to_peers(g.ctx, X, self._r1_peers, 0, g.kmax), "fft_x fwd -> peers")
+            ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+            ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, 0, g.kmax), "chunks -> fft_y fwd")
+            ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")      # R1 is free until the peers' next forward pass
+            ck(lib.mhh_fft_y_chunks_to_peers(g.ctx, X, self._r2_peers, 0, g.kmax), "fft_y bwd -> peers")
+            ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+            ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
+            return
+        nc = self.kranges if g.kmax % self.kranges == 0 else 1
+        nk = g.kmax // nc
+        world, me = self.comm.world, self.comm.rank
+        R = nk * g.jmax * (g.itot // world)                  # one peer's chunk of one k range (elements)
+        main = torch.cuda.current_stream(g.device)
+        xfer, recv = self._side
+        ce = self.a2a == "ce"
+        S = L.ptr(self.S) if ce else None
+        on = lambda st: lib.mhh_set_stream(g.ctx, C.c_void_p(st.cuda_stream))
+
+        def half(send, recv_fn, peers_t):
+            """send(c): the sending transform of range c on the main stream; then on `xfer`: (ce: the copies,) the barrier;
+            then on `recv`: the receiving transform of range c."""
+            for c in range(nc):
+                on(main)
+                send(c)
+                ev = torch.cuda.Event(); ev.record(main)
+                xfer.wait_event(ev)
+                if ce:
+                    with torch.cuda.stream(xfer):
+                        base = c * world * R
+                        for d in range(world):
+                            r = (me + d) % world          # start with my own chunk, then round the ring
+                            peers_t[r][base + me * R: base + (me + 1) * R].copy_(self.S[base + r * R: base + (r + 1) * R], non_blocking=True)
+                on(xfer)
+                ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+                ev2 = torch.cuda.Event(); ev2.record(xfer)
+                recv.wait_event(ev2)
+                on(recv)
+                recv_fn(c)
+            ev3 = torch.cuda.Event(); ev3.record(recv)
+            main.wait_event(ev3)
+            on(main)
+
+        if ce:
+            half(lambda c: ck(lib.mhh_fft_x_chunks(g.ctx, -1, X, S, None, c * nk, nk), "fft_x fwd -> chunks"),
+                 lambda c: ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, c * nk, nk), "chunks -> fft_y fwd"), self._r1_t)
+        else:
+            half(lambda c: ck(lib.mhh_fft_x_chunks_to_peers(g.ctx, X, self._r1_peers, c * nk, nk), "fft_x fwd -> peers"),
+                 lambda c: ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, c * nk, nk), "chunks -> fft_y fwd"), None)
+        ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")
+        if ce:
+            half(lambda c: ck(lib.mhh_fft_y_chunks(g.ctx, +1, X, S, c * nk, nk), "fft_y bwd -> chunks"),
+                 lambda c: ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), c * nk, nk), "chunks -> fft_x bwd"), self._r2_t)
+        else:
+            half(lambda c: ck(lib.mhh_fft_y_chunks_to_peers(g.ctx, X, self._r2_peers, c * nk, nk), "fft_y bwd -> peers"),
+                 lambda c: ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), c * nk, nk), "chunks -> fft_x bwd"), None)
     _r1_peers = None
 
-    def exec(self, dt, stats=None, timeloop=None):
+    def exec(self, dt, stats=None, timeloop=None, hooks=None):
         g, f, lib = self.grid, self.fields, self.grid.lib
         if self.chunk_fft is None:
             self.chunk_fft = bool(lib.mhh_fft_chunks_supported(g.ctx))
+        if hooks and not (self.peer and self.chunk_fft):
+            for h in hooks:
+                h()
+            hooks = None
         u, v, w = (f.mp[n].fld for n in "uvw")
         ut, vt, wt = (f.mt[n].fld for n in "uvw")
         p = f.sd["p"].fld
@@ -221,7 +350,7 @@ class SlabPres(Pres):
         self.cyclic.exec(vt, L.EDGE_NORTH_SOUTH)
         ck(lib.mhh_pres_input_to(g.ctx, L.ptr(u), L.ptr(v), L.ptr(w), L.ptr(ut), L.ptr(vt), L.ptr(wt), C.c_double(dt), A), "pres_input")
         if self.peer and self.chunk_fft:
-            self._exec_peer_transforms(p)
+            self._exec_peer_transforms(p, hooks)
         elif self.chunk_fft:
             # The transforms read / write the all-to-all chunk layout themselves (no pack / unpack passes), and the slab is
             # cut into k ranges: the collective of one range runs on NCCL's stream while the transforms of the next are
@@ -314,6 +443,9 @@ class SlabModel(Model):
     def _reduce_max(self, values):
         """Master::max over the ranks; several maxima travel in one collective (a NaN flag rides along)."""
         return self.comm.allreduce_max_many(values, self.grid.device)
+
+    def _scalar_halves(self):
+        return self.path == "peer" and self.pres.a2a == "ce_overlap"
 
     def print_status(self):
         g, f, tl, dev = self.grid, self.fields, self.timeloop, self.grid.device
