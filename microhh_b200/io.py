@@ -231,6 +231,14 @@ def _fname(name, itime, directory="."):
     return os.path.join(directory, "%s.%07d" % (name, itime))
 
 
+def grid_coordinates(itot, jtot, xsize, ysize):
+    """x, xh, y, yh of the interior as Grid::calculate forms them (src/grid.cxx:241-262, serial: no process offset):
+    x[i] = 0.5 dx + i dx (in this order of operations: the files are compared byte for byte)."""
+    dx, dy = xsize / itot, ysize / jtot
+    i, j = np.arange(itot, dtype=np.float64), np.arange(jtot, dtype=np.float64)
+    return 0.5 * dx + i * dx, i * dx, 0.5 * dy + j * dy, j * dy
+
+
 def save_grid(x, xh, y, yh, z, zh, directory="."):
     """Grid::save_grid, src/grid_serial.cxx:46-77: x, xh, y, yh, z, zh interiors back to back (fopen "wbx": no overwrite)."""
     with open(_fname("grid", 0, directory), "xb") as fh:

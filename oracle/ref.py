@@ -42,7 +42,8 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         _lib.ref_world_create.restype = C.c_void_p
         for name in ("ref_mean_2d", "ref_mean", "ref_advec2_cfl", "ref_pres2_divergence", "ref_pres4_divergence",
-                     "ref_smag2_dnmul", "ref_rk_subdt", "ref_advec2i5_cfl", "ref_advec4_cfl"):
+                     "ref_smag2_dnmul", "ref_rk_subdt", "ref_advec2i5_cfl", "ref_advec4_cfl",
+                     "ref_check_momentum", "ref_check_tke", "ref_check_mass"):
             if hasattr(_lib, name):
                 getattr(_lib, name).restype = C.c_double
     return _lib

@@ -1,7 +1,7 @@
 """GPU parity, per call, of the small operators around the stencils: Boundary_cyclic, vertical ghost rows (2nd/4th order,
 every Boundary_type), set_bc, RK3/RK4 substeps, Field3d_operators reductions, Fields diagnostics, thermo_dry pieces —
-each through the C ABI against the reference's own code (oracle/_ref) or, for src/fields.cxx (not compilable here),
-the numpy restatement in oracle/restate.py.  Copies and ghost rows are bit-exact; arithmetic is within 1e-13."""
+each through the C ABI against the reference's own code (oracle/_ref), src/fields.cxx included (compiled in place through
+Boost / NetCDF shims); the numpy restatement in oracle/restate.py is checked beside it.  Copies and ghost rows are bit-exact; arithmetic is within 1e-13."""
 import ctypes as C
 
 import numpy as np
@@ -146,9 +146,13 @@ def test_reductions_and_diagnostics(cuda_lib, kw):
             f.mp[n].fld.copy_(_up(g, case[n]))
         f.sp["s0"].fld.copy_(d)
         u, v, w = case["u"], case["v"], case["w"]
-        for got, want in ((f.check_momentum(), RS.check_momentum(W, u, v, w)), (f.check_tke(), RS.check_tke(W, u, v, w)),
-                          (f.check_mass(), RS.check_mass(W, th))):
+        # Fields::check_momentum/tke/mass: the reference's own calc_momentum_2nd / calc_tke_2nd / calc_mass compiled in place
+        # (oracle/ref_harness/k_fields.cxx), and the numpy restatement beside it
+        for got, want, rs in ((f.check_momentum(), W.call("ref_check_momentum", u, v, w), RS.check_momentum(W, u, v, w)),
+                              (f.check_tke(), W.call("ref_check_tke", u, v, w), RS.check_tke(W, u, v, w)),
+                              (f.check_mass(), W.call("ref_check_mass", th), RS.check_mass(W, th))):
             assert abs(got - want) <= 1e-12 * max(abs(want), 1e-3), (got, want)
+            assert abs(rs - want) <= 1e-12 * max(abs(want), 1e-3), (rs, want)
     g.close(); W.close()
 
 

@@ -123,3 +123,54 @@ def test_out_row_matches_c_printf(tmp_path):
     assert lines[0].split() == ["ITER", "TIME", "CPUDT", "DT", "CFL", "DNUM", "DIV", "MOM", "TKE"]
     rows = IO.read_out(os.path.join(str(tmp_path), "case.out"))
     assert rows[0]["iter"] == 120 and abs(rows[0]["tke"] - 32.2384) < 1e-7
+
+
+def test_binary_files_against_the_reference_writers(tmp_path, monkeypatch):
+    """The restart files either side of the path, byte for byte against files the reference's own code writes
+    (oracle/ref_harness/k_io.cxx, k_timeloop.cxx: Field3d_io::save_field3d / load_field3d src/field3d_io.cxx:671-751,
+    Grid::save_grid src/grid_serial.cxx:46-77, Timeloop::save / load src/timeloop.cxx:445-525 compiled in place), and each
+    side reading what the other wrote."""
+    import ctypes as C
+    from oracle.ref import RefWorld, lib
+    from tests.helpers import make_case
+    c = make_case(itot=12, jtot=10, ktot=9, alpha=1.3)
+    W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"])
+    shape = dict(itot=12, jtot=10, ktot=9, igc=1, jgc=1, kgc=1)
+    refdir, mydir = tmp_path / "ref", tmp_path / "mine"
+    refdir.mkdir(); mydir.mkdir()
+    L = lib()
+    u = c["u"].copy()
+    # --- fields (with a Galilean offset, as Fields::save passes utrans)
+    monkeypatch.chdir(refdir)
+    assert L.ref_save_field3d(W.h, u.ctypes.data_as(C.c_void_p), b"u.0000600", C.c_double(1.25)) == 0
+    IO.save_field3d(u, shape, "u", 600, offset=1.25, directory=str(mydir))
+    assert (refdir / "u.0000600").read_bytes() == (mydir / "u.0000600").read_bytes()
+    assert L.ref_save_field3d(W.h, u.ctypes.data_as(C.c_void_p), b"u.0000600", C.c_double(0.)) == 1      # "wbx": never overwrites
+    with pytest.raises(FileExistsError):
+        IO.save_field3d(u, shape, "u", 600, directory=str(mydir))
+    mine = IO.load_field3d(shape, "u", 600, offset=1.25, directory=str(refdir))                           # I read the reference's file
+    back = np.zeros_like(u)
+    monkeypatch.chdir(mydir)
+    assert L.ref_load_field3d(W.h, back.ctypes.data_as(C.c_void_p), b"u.0000600", C.c_double(1.25)) == 0   # it reads mine
+    assert np.array_equal(mine[1:-1, 1:-1, 1:-1], back[1:-1, 1:-1, 1:-1])
+    assert np.abs(back[1:-1, 1:-1, 1:-1] - u[1:-1, 1:-1, 1:-1]).max() <= 4e-16 * 2.25                      # (u + o) - o
+    assert L.ref_load_field3d(W.h, back.ctypes.data_as(C.c_void_p), b"nope.0000000", C.c_double(0.)) == 1
+    # --- grid
+    monkeypatch.chdir(refdir)
+    L.ref_save_grid(W.h)
+    x, xh, y, yh = IO.grid_coordinates(12, 10, c["xsize"], c["ysize"])
+    IO.save_grid(x, xh, y, yh, W.z[1:-1], W.zh[1:-1], directory=str(mydir))
+    assert (refdir / "grid.0000000").read_bytes() == (mydir / "grid.0000000").read_bytes()
+    got = IO.load_grid(12, 10, 9, directory=str(refdir))
+    assert np.array_equal(got["z"], c["z"]) and np.array_equal(got["xh"], xh)
+    # --- time
+    L.ref_time_save.argtypes = [C.c_void_p, C.c_int, C.c_ulong, C.c_ulong, C.c_int]
+    L.ref_time_save(W.h, 600, 600123456789, 1500000000, 4242)
+    IO.save_time(600, 600123456789, 1500000000, 4242, directory=str(mydir))
+    assert (refdir / "time.0000600").read_bytes() == (mydir / "time.0000600").read_bytes()
+    assert IO.load_time(600, directory=str(refdir)) == (600123456789, 1500000000, 4242)
+    out = (C.c_ulong * 3)()
+    monkeypatch.chdir(mydir)
+    L.ref_time_load(W.h, 600, out)
+    assert tuple(out) == (600123456789, 1500000000, 4242)
+    W.close()

@@ -161,3 +161,18 @@ def test_restatement_closed_forms():
     assert abs(RS.check_mass(W, 7. * one) - 7.) < 1e-13
     assert abs(W.call("ref_mean", 7. * one) - 7.) < 1e-13
     W.close()
+
+
+def test_fields_diagnostics_reference_vs_restatement():
+    """Fields::check_momentum/tke/mass (src/fields.cxx:144-234) compiled in place (k_fields.cxx: Boost and NetCDF shimmed) pin
+    the numpy restatement on random fields, 2nd- and 4th-order ghost depths, stretched z."""
+    from oracle import restate as RS
+    from oracle.ref import RefWorld
+    for kw in (dict(itot=12, jtot=10, ktot=14, alpha=1.4), dict(itot=16, jtot=1, ktot=8), dict(itot=10, jtot=8, ktot=12, order=4, alpha=1.2)):
+        c = make_case(**kw)
+        W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], order=c["order"], gc=c["gc"])
+        u, v, w, th = c["u"], c["v"], c["w"], c["s"][0]
+        for ref, rs in ((W.call("ref_check_momentum", u, v, w), RS.check_momentum(W, u, v, w)),
+                        (W.call("ref_check_tke", u, v, w), RS.check_tke(W, u, v, w)), (W.call("ref_check_mass", th), RS.check_mass(W, th))):
+            assert abs(ref - rs) <= 1e-13 * max(abs(ref), 1e-3), (kw, ref, rs)
+        W.close()
