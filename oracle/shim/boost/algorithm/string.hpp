@@ -1,5 +1,6 @@
 /* TEST INFRASTRUCTURE ONLY — minimal stand-in for <boost/algorithm/string.hpp> (Boost is absent here): just what
- * src/fields.cxx:259 uses, boost::split(container, string, boost::is_any_of(" "), boost::token_compress_on). */
+ * src/fields.cxx:259 and src/input.cxx:101-146,373,410 use: boost::split(container, string, boost::is_any_of(..)
+ * [, boost::token_compress_on]) and boost::trim(string) (both ends, std::isspace in the "C" locale). */
 #pragma once
 #include <string>
 #include <vector>
@@ -26,5 +27,20 @@ namespace boost
         }
         out.push_back(cur);
         return out;
+    }
+
+    inline void to_lower(std::string& s)          // include/input_tools.h:74 (bool items: "TRUE" -> "true")
+    {
+        for (char& ch : s)
+            if (ch >= 'A' && ch <= 'Z') ch = static_cast<char>(ch - 'A' + 'a');
+    }
+
+    inline void trim(std::string& s)
+    {
+        const char* ws = " \t\n\v\f\r";
+        const std::size_t b = s.find_first_not_of(ws);
+        if (b == std::string::npos) { s.clear(); return; }
+        const std::size_t e = s.find_last_not_of(ws);
+        s = s.substr(b, e - b + 1);
     }
 }

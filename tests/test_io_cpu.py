@@ -174,3 +174,93 @@ def test_binary_files_against_the_reference_writers(tmp_path, monkeypatch):
     L.ref_time_load(W.h, 600, out)
     assert tuple(out) == (600123456789, 1500000000, 4242)
     W.close()
+
+
+class _RefInput:
+    """The reference's own Input class (src/input.cxx compiled in place, oracle/_ref/liboracle_input.so)."""
+
+    def __init__(self, path):
+        import ctypes as C
+        so = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "liboracle_input.so")
+        if not os.path.exists(so):
+            pytest.skip("oracle/_ref/liboracle_input.so not built (needs /root/reference)")
+        self.C, self.lib = C, C.CDLL(so)
+        self.lib.refin_open.restype = C.c_void_p
+        err = C.create_string_buffer(512)
+        self.h = self.lib.refin_open(str(path).encode(), err, 512)
+        self.error = None if self.h else err.value.decode()
+
+    def get(self, typ, block, item, sub="", default=None):
+        C = self.C
+        out = C.create_string_buffer(1024)
+        code = {int: b"i", float: b"d", bool: b"b", str: b"s"}[typ]
+        d = "" if default is None else ("true" if default is True else "false" if default is False else str(default))
+        rc = self.lib.refin_get(C.c_void_p(self.h), C.c_char(code), block.encode(), item.encode(), sub.encode(),
+                                0 if default is None else 1, d.encode(), out, 1024)
+        return rc, out.value.decode()
+
+    def get_list(self, typ, block, item, sub=""):
+        C = self.C
+        out = C.create_string_buffer(1024)
+        code = {int: b"i", float: b"d", bool: b"b", str: b"s"}[typ]
+        rc = self.lib.refin_get_list(C.c_void_p(self.h), C.c_char(code), block.encode(), item.encode(), sub.encode(), out, 1024)
+        return rc, out.value.decode()
+
+
+def _mine(inp, typ, block, item, sub="", default=None):
+    try:
+        v = inp.get_item(typ, block, item, sub) if default is None else inp.get_item(typ, block, item, sub, default)
+    except IO.InputError as e:
+        return 1, str(e)
+    return 0, ("true" if v is True else "false" if v is False else repr(float(v)) if typ is float else str(v))
+
+
+def test_ini_reader_against_the_reference_reader(tmp_path):
+    """IO.Input against the reference's Input (src/input.cxx:76-330, include/input_tools.h) on the same files: values,
+    fall-back from sub-item to item, defaults, type errors and every error text."""
+    path = os.path.join(HERE, "golden", "gabls1_like.ini")
+    ref, mine = _RefInput(path), IO.Input(path)
+    assert ref.error is None
+    queries = [(int, "grid", "ktot"), (float, "grid", "xsize"), (str, "advec", "swadvec"), (bool, "buffer", "swbuffer"),
+               (float, "boundary", "sbot", "th"), (float, "boundary", "sbot", "qt"), (float, "boundary", "stop", "th"),
+               (bool, "time", "adaptivestep", "", False), (float, "grid", "utrans", "", 0.5), (int, "time", "rkorder", "", 3),
+               (str, "thermo", "swbasestate", "", "x"), (int, "nope", "x"), (int, "grid", "x"), (int, "grid", "xsize"),
+               (bool, "grid", "itot"), (int, "grid", "xsize", "", 3), (float, "fields", "visc"), (str, "boundary", "sbcbot", "th")]
+    for q in queries:
+        r, m = ref.get(*q), _mine(mine, *q)
+        assert r[0] == m[0], (q, r, m)
+        if r[0] == 0 and q[0] is float:
+            assert float(r[1]) == float(m[1]), (q, r, m)
+        else:
+            assert r[1].strip() == m[1].strip(), (q, r, m)
+    # lists and malformed files
+    good = tmp_path / "lists.ini"
+    good.write_text("[fields]\nslist = s1, s2 ,s3\nvals=1,2.5,3e2   # a comment\n[t]\nflags=1,false,TRUE\nn = 4,5\n")
+    ref2, mine2 = _RefInput(good), IO.Input(str(good))
+    for typ, b, i in ((str, "fields", "slist"), (float, "fields", "vals"), (bool, "t", "flags"), (int, "t", "n"), (int, "fields", "vals"),
+                      (int, "t", "absent")):
+        r = ref2.get_list(typ, b, i)
+        try:
+            v = mine2.get_list(typ, b, i)
+            m = (0, v)
+        except IO.InputError as e:
+            m = (1, str(e))
+        assert r[0] == m[0], (typ, b, i, r, m)
+        if r[0] == 0:
+            conv = {str: str, float: float, int: int, bool: lambda t: t == "true"}[typ]
+            assert [conv(t) for t in r[1].split(",")] == m[1], (r, m)
+        else:
+            assert r[1].strip() == m[1].strip(), (r, m)
+    for n, text in enumerate(("a=1\n", "[x]\na=b=c\n", "[x]\nhello\n", "[x]\na[b=1\n", "[bad name]\n")):
+        bad = tmp_path / f"bad{n}.ini"
+        bad.write_text(text)
+        r = _RefInput(bad)
+        try:
+            IO.Input(str(bad))
+            m = None
+        except IO.InputError as e:
+            m = str(e)
+        assert (r.error is None) == (m is None), (text, r.error, m)
+        if m is not None:
+            assert r.error.strip() == m.strip(), (text, r.error, m)
+    assert _RefInput(tmp_path / "missing.ini").error.strip().startswith('"' + str(tmp_path / "missing.ini") + '" cannot be opened')
