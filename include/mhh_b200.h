@@ -237,6 +237,12 @@ typedef struct mhh_surface_args
     const double *z0m, *z0h; /* ijcells */
     double* dutot;           /* ijcells scratch (the reference borrows a tmp field) */
     double *dudz, *dvdz, *dbdz;   /* dudz_mo, dvdz_mo, dbdz_mo: the bottom-row inputs of mhh_smag2_exec_viscosity */
+    /* [boundary] swconstantz0=false: the iterative Obukhov-length solver on heterogeneous z0m / z0h planes
+     * (calc_obuk_noslip_*_iterative, include/boundary_surface_kernels.h:287-470) instead of the z/L lookup; 0 = lookup.
+     * swcharnock=true (needs the iterative solver): z0m, z0h are first updated from the previous u* (calc_z0_charnock,
+     * src/boundary_surface.cxx:342-365) with the three [boundary] alpha_* constants, and must then be writable. */
+    int iterative_solver, charnock;
+    double alpha_m, alpha_ch, alpha_h;
 } mhh_surface_args;
 /* Boundary_surface::exec, src/boundary_surface.cxx:827-981: calc_dutot, stability / stability_neutral, surfm, surfs(th),
  * calc_duvdz_mo, calc_dbdz_mo with the cyclic fills in between. */

@@ -89,6 +89,8 @@ struct SurfaceArgs
     int* nobuk;
     const double *z0m, *z0h;
     double *dutot, *dudz, *dvdz, *dbdz;
+    int constant_z0 = 1, charnock = 0;
+    double alpha_m = 0., alpha_ch = 0., alpha_h = 0.;
 };
 int surface_lut(Ctx*, int, int, double, double);
 int surface_exec(Ctx*, const SurfaceArgs&, int stages);
@@ -687,6 +689,8 @@ int mhh_boundary_surface_exec_stages(mhh_ctx* c, const mhh_surface_args* a, int 
     SurfaceArgs s{a->mbcbot, a->thermo, a->thermobc, a->u, a->v, a->ubot, a->vbot, a->ufluxbot, a->vfluxbot, a->ugradbot,
                   a->vgradbot, a->th, a->thbot, a->thgradbot, a->thfluxbot, a->ustar, a->obuk, a->nobuk, a->z0m, a->z0h,
                   a->dutot, a->dudz, a->dvdz, a->dbdz};
+    s.constant_z0 = a->iterative_solver ? 0 : 1; s.charnock = a->charnock;
+    s.alpha_m = a->alpha_m; s.alpha_ch = a->alpha_ch; s.alpha_h = a->alpha_h;
     return surface_exec(c, s, stages);
 }
 int mhh_boundary_surface_exec(mhh_ctx* c, const mhh_surface_args* a) { return mhh_boundary_surface_exec_stages(c, a, 7); }

@@ -53,6 +53,80 @@ namespace
                          : kKappa / (log(zsl / z0h) - psih_stable(zsl / L) + psih_stable(z0h / L));
     }
 
+    // ---- iterative Obukhov-length solvers for heterogeneous z0 (swconstantz0=false), include/boundary_surface_kernels.h:
+    // calc_obuk_noslip_flux_iterative :287-375 and calc_obuk_noslip_dirichlet_iterative :377-470.  Newton iteration on
+    // f(L) = zsl/L - Ri-like term with a +-0.1 % finite-difference slope, one restart with a safe start value, the result
+    // limited to the z/L range of the lookup solver.  FLUX: the first form (bfluxbot), else the second (db, z0h).
+    template<bool FLUX>
+    __device__ inline double obuk_iterative(double L, const double du, double bf, const double zsl, const double z0m, const double z0h)
+    {
+        constexpr double kDsmallS = 1.e-9, Lmax = 1.e16;
+        const double L_min_stable = zsl / kZLmax;
+        if (!FLUX)
+        {
+            // no zero crossing for large Ri: the reference returns the stable limit
+            const double Ri = kKappa * bf * zsl / (du * du);
+            if (Ri > 0.13) return L_min_stable;
+        }
+        if (bf >= 0.) bf = fmax(kDsmallS, bf); else bf = fmin(-kDsmallS, bf);
+        auto fx_of = [&](const double l) -> double
+        {
+            if (FLUX) { const double a = du * most_fm(zsl, z0m, l); return zsl / l + kKappa * zsl * bf / (a * a * a); }
+            const double a = du * most_fm(zsl, z0m, l);
+            return zsl / l - kKappa * zsl * bf * most_fh(zsl, z0h, l) / (a * a);
+        };
+        int m = 0, nlim = 10;
+        double L0;
+        while (m <= 1)
+        {
+            // the stability changed sign, or the last attempt did not converge: restart from a safe value
+            const bool reset = FLUX ? (m == 1 || L * bf >= 0.) : (m == 1 || L * bf <= 0.);
+            if (reset)
+            {
+                nlim = 200;
+                if (FLUX) L = (bf >= 0.) ? -kDsmallS : L_min_stable;
+                else      L = (bf >= 0.) ? L_min_stable : -kDsmallS;
+            }
+            if (FLUX) L0 = (bf >= 0.) ? -kDhugeS : kDhugeS;
+            else      L0 = (bf >= 0.) ? kDhugeS : -kDhugeS;
+            int n = 0;
+            while (fabs((L - L0) / L0) > 0.001 && n < nlim && fabs(L) < Lmax)
+            {
+                L0 = L;
+                const double fx = fx_of(L);
+                const double Lstart = L - 0.001 * L, Lend = L + 0.001 * L;
+                const double fxdif = (fx_of(Lend) - fx_of(Lstart)) / (Lend - Lstart);
+                if (fabs(fxdif) < 1e-16) break;
+                L = L - fx / fxdif;
+                if (L >= 0. && L < L_min_stable) L = L_min_stable;
+                ++n;
+            }
+            if (n < nlim && fabs(L) < Lmax) break;
+            ++m;
+            nlim = 200;
+        }
+        if (m > 1)
+        {
+            if (fabs(L) > Lmax) L = (FLUX ? -copysign(1., bf) : copysign(1., bf)) * Lmax;
+            else L = L_min_stable;
+        }
+        return zsl / fmin(fmax(zsl / L, kZLmin), kZLmax);
+    }
+
+    // calc_z0_charnock, src/boundary_surface.cxx:342-365 (interior; the cyclic fills follow)
+    __global__ void charnock_kernel(double* __restrict__ z0m, double* __restrict__ z0h, const double* __restrict__ ustar,
+                                    const double alpha_m, const double alpha_ch, const double alpha_h, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x + gd.istart;
+        const int j = blockIdx.y + gd.jstart;
+        if (i >= gd.iend) return;
+        const int ij = i + j * gd.icells;
+        const double visc = 1.5e-5, gi = 1. / kGrav, min_ustar = 1e-8;
+        const double ustar_lim = fmax(ustar[ij], min_ustar);
+        z0m[ij] = alpha_m * visc / ustar_lim + alpha_ch * (ustar_lim * ustar_lim) * gi;
+        z0h[ij] = alpha_h * visc / ustar_lim;
+    }
+
     // find_zL, include/boundary_surface_kernels.h:249-263 (float comparisons, the search resumes at the cell's last index)
     __device__ inline double find_zL(const float* __restrict__ zL, const float* __restrict__ f, int& n, const float Ri)
     {
@@ -92,7 +166,8 @@ namespace
     __global__ void stability_kernel(double* __restrict__ ustar, double* __restrict__ obuk, int* __restrict__ nobuk,
                                      const double* __restrict__ th, const double* __restrict__ thbot,
                                      const double* __restrict__ thfluxbot, const double* __restrict__ dutot,
-                                     const double* __restrict__ z0m, const float* __restrict__ zL_sl,
+                                     const double* __restrict__ z0m, const double* __restrict__ z0h, const int constant_z0,
+                                     const float* __restrict__ zL_sl,
                                      const float* __restrict__ f_sl, const int thermo, const int mbcbot, const int thermobc,
                                      const double g_thref, const double thref_k, const double g_threfh, const double threfh_k,
                                      const double db_ref, const double zsl, const GridD gd)
@@ -121,10 +196,16 @@ namespace
         else if (mbcbot == BC_DIRICHLET && thermobc == BC_FLUX)
         {
             const double du = dutot[ij];
-            const float Ri = -kKappa * (g_threfh * thfluxbot[ij]) * zsl / (du * du * du);
-            int n = nobuk[ij];
-            const double L = zsl / find_zL(zL_sl, f_sl, n, Ri);
-            nobuk[ij] = n;
+            double L;
+            if (constant_z0)
+            {
+                const float Ri = -kKappa * (g_threfh * thfluxbot[ij]) * zsl / (du * du * du);
+                int n = nobuk[ij];
+                L = zsl / find_zL(zL_sl, f_sl, n, Ri);
+                nobuk[ij] = n;
+            }
+            else
+                L = obuk_iterative<true>(obuk[ij], du, g_threfh * thfluxbot[ij], zsl, z0m[ij], 0.);
             obuk[ij] = L;
             ustar[ij] = du * most_fm(zsl, z0m[ij], L);
         }
@@ -134,10 +215,16 @@ namespace
             const double b = g_thref * (th[ij + gd.kstart * gd.ijcells] - thref_k);      // calc_buoyancy_bot, src/thermo_dry.cxx:129-146
             const double bbot = g_threfh * (thbot[ij] - threfh_k);
             const double db = b - bbot + db_ref;
-            const float Ri = kKappa * db * zsl / (du * du);
-            int n = nobuk[ij];
-            const double L = zsl / find_zL(zL_sl, f_sl, n, Ri);
-            nobuk[ij] = n;
+            double L;
+            if (constant_z0)
+            {
+                const float Ri = kKappa * db * zsl / (du * du);
+                int n = nobuk[ij];
+                L = zsl / find_zL(zL_sl, f_sl, n, Ri);
+                nobuk[ij] = n;
+            }
+            else
+                L = obuk_iterative<false>(obuk[ij], du, db, zsl, z0m[ij], z0h[ij]);
             obuk[ij] = L;
             ustar[ij] = du * most_fm(zsl, z0m[ij], L);
         }
@@ -284,9 +371,12 @@ struct SurfaceArgs
     int* nobuk;
     const double *z0m, *z0h;
     double *dutot, *dudz, *dvdz, *dbdz;
+    int constant_z0 = 1, charnock = 0;
+    double alpha_m = 0., alpha_ch = 0., alpha_h = 0.;
 };
 
-// Boundary_surface<TF>::exec, src/boundary_surface.cxx:827-981 (swconstantz0 = true, no Charnock)
+// Boundary_surface<TF>::exec, src/boundary_surface.cxx:827-981 (swconstantz0 true: lookup solver, false: iterative solver
+// on heterogeneous z0m / z0h, optionally updated by the Charnock relation)
 // stages: 1 = total wind (+ its halo), 2 = stability + momentum fluxes (+ their halos), 4 = gradients / scalar / MO gradients.
 // A y-slab rank (npy > 1) runs the stages one by one with the north/south exchange of dutot (after 1) and of the two flux
 // planes (after 2) in between: the cyclic fills in here are east/west only on such a rank (cyclic_exec_k).
@@ -298,7 +388,9 @@ int surface_exec(Ctx* c, const SurfaceArgs& a, const int stages)
     if (a.thermo && a.thermobc == BC_DIRICHLET && a.mbcbot == BC_USTAR)
     { c->last_error = "Fixed Ustar bc in combination with Dirichlet bc for scalars is not supported"; return MHH_ERR_ARG; }
     if (a.thermo && !c->thref_d) { c->last_error = "thermo reference profiles not set"; return MHH_ERR_STATE; }
-    if (a.thermo && a.mbcbot == BC_DIRICHLET && !c->surf_lut_d) { c->last_error = "surface solver not prepared (mhh_surface_init_solver)"; return MHH_ERR_STATE; }
+    if (a.thermo && a.mbcbot == BC_DIRICHLET && a.constant_z0 && !c->surf_lut_d) { c->last_error = "surface solver not prepared (mhh_surface_init_solver)"; return MHH_ERR_STATE; }
+    if (a.charnock && a.constant_z0) { c->last_error = "\"swcharnock=true\" requires \"swconstantz0=false\""; return MHH_ERR_ARG; }
+    if (!a.constant_z0 && !a.z0h) { c->last_error = "swconstantz0=false needs the z0h plane"; return MHH_ERR_ARG; }
     const double zsl = c->z[gd.kstart];
     const dim3 bi(128), gi((gd.imax + 127) / 128, gd.jmax);
     const int nb = (gd.ijcells + 255) / 256;
@@ -306,6 +398,16 @@ int surface_exec(Ctx* c, const SurfaceArgs& a, const int stages)
     const double thref_k = a.thermo ? c->thref_ks : 1., threfh_k = a.thermo ? c->threfh_ks : 1.;
     const double g_thref = kGrav / thref_k, g_threfh = kGrav / threfh_k;
     const double db_ref = g_thref * (thref_k - threfh_k);          // Thermo_dry::get_db_ref, src/thermo_dry.cxx:629-633
+    if ((stages & 1) && a.charnock)
+    {
+        // roughness lengths from the previous step's u* (src/boundary_surface.cxx:836-851); on a y-slab rank the caller
+        // exchanges the north/south rows of z0m, z0h together with dutot's after this stage
+        double* z0m = const_cast<double*>(a.z0m); double* z0h = const_cast<double*>(a.z0h);
+        MHH_LAUNCH(c, "surf_charnock_kernel", charnock_kernel<<<gi, bi, 0, c->stream>>>(z0m, z0h, a.ustar, a.alpha_m, a.alpha_ch, a.alpha_h, gd));
+        MHH_LAUNCH_CHECK();
+        if ((e = cyclic_exec_2d(c, z0m))) return e;
+        if ((e = cyclic_exec_2d(c, z0h))) return e;
+    }
     if (stages & 1)
     {
         MHH_LAUNCH(c, "surf_dutot_kernel", dutot_kernel<<<gi, bi, 0, c->stream>>>(a.dutot, a.u, a.v, a.ubot, a.vbot, gd));
@@ -315,7 +417,8 @@ int surface_exec(Ctx* c, const SurfaceArgs& a, const int stages)
     if (stages & 2)
     {
         MHH_LAUNCH(c, "surf_stability_kernel", stability_kernel<<<nb, 256, 0, c->stream>>>(
-            a.ustar, a.obuk, a.nobuk, a.th, a.thbot, a.thfluxbot, a.dutot, a.z0m, c->surf_lut_d, c->surf_lut_d ? c->surf_lut_d + NLUT : nullptr,
+            a.ustar, a.obuk, a.nobuk, a.th, a.thbot, a.thfluxbot, a.dutot, a.z0m, a.z0h, a.constant_z0,
+            c->surf_lut_d, c->surf_lut_d ? c->surf_lut_d + NLUT : nullptr,
             a.thermo, a.mbcbot, a.thermobc, g_thref, thref_k, g_threfh, threfh_k, db_ref, zsl, gd));
         MHH_LAUNCH_CHECK();
         MHH_LAUNCH(c, "surfm_flux_kernel", surfm_flux_kernel<<<gi, bi, 0, c->stream>>>(

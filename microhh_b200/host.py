@@ -862,14 +862,19 @@ class SurfaceArgs(C.Structure):
     _fields_ = ([("mbcbot", C.c_int), ("thermo", C.c_int), ("thermobc", C.c_int)]
                 + [(n, C.c_void_p) for n in ("u", "v", "ubot", "vbot", "ufluxbot", "vfluxbot", "ugradbot", "vgradbot", "th",
                                              "thbot", "thgradbot", "thfluxbot", "ustar", "obuk", "nobuk", "z0m", "z0h",
-                                             "dutot", "dudz", "dvdz", "dbdz")])
+                                             "dutot", "dudz", "dvdz", "dbdz")]
+                + [("iterative_solver", C.c_int), ("charnock", C.c_int), ("alpha_m", C.c_double), ("alpha_ch", C.c_double),
+                   ("alpha_h", C.c_double)])
 
 
 class Boundary_surface(Boundary):
     """Boundary_surface (include/boundary_surface.h, src/boundary_surface.cxx): swboundary=surface, the Monin-Obukhov
-    surface layer.  swconstantz0=true (homogeneous z0m/z0h, lookup solver); mbcbot in {noslip, ustar}."""
+    surface layer; mbcbot in {noslip, ustar}.  swconstantz0=true: homogeneous z0m/z0h and the z/L lookup solver;
+    swconstantz0=false: z0m / z0h may be 2-D arrays (jcells x icells) and the iterative solver runs; swcharnock=true (with
+    swconstantz0=false) updates them from u* every step with alpha_m, alpha_ch, alpha_h (src/boundary_surface.cxx:462-480)."""
 
-    def __init__(self, grid, fields, z0m=0.1, z0h=0.1, ustar=None, **kw):
+    def __init__(self, grid, fields, z0m=0.1, z0h=0.1, ustar=None, swconstantz0=True, swcharnock=False, alpha_m=None,
+                 alpha_ch=None, alpha_h=None, **kw):
         mbcbot = kw.pop("mbcbot", "noslip")
         super().__init__(grid, fields, mbcbot=mbcbot, swboundary="surface", **kw)
         if self.mbcbot == L.BC_NEUMANN:
@@ -882,9 +887,20 @@ class Boundary_surface(Boundary):
         if self.mbcbot == L.BC_USTAR and ustar is None:
             raise L.MhhError('Item "ustar" in group "boundary" does not exist')
         self.ustarin = ustar
+        self.swconstantz0, self.swcharnock = bool(swconstantz0), bool(swcharnock)
+        if self.swcharnock and self.swconstantz0:
+            raise L.MhhError('"swcharnock=true" requires "swconstantz0=false"')                 # src/boundary_surface.cxx:472-473
+        if self.swcharnock and None in (alpha_m, alpha_ch, alpha_h):
+            raise L.MhhError('Item "alpha_m" in group "boundary" does not exist')
+        self.alpha = tuple(float(a or 0.) for a in (alpha_m, alpha_ch, alpha_h))
         self.thermobc = self.sbc["th"].bcbot if "th" in self.sbc else L.BC_FLUX          # :514-521
-        self.z0m_hom, self.z0h_hom = float(z0m), float(z0h)
-        z2 = lambda v=0.: torch.full(grid.shape2d, float(v), dtype=torch.float64, device=grid.device)
+        if self.swconstantz0:
+            self.z0m_hom, self.z0h_hom = float(z0m), float(z0h)
+
+        def z2(v=0.):
+            if np.ndim(v) == 2:
+                return torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64)).to(grid.device)
+            return torch.full(grid.shape2d, float(v), dtype=torch.float64, device=grid.device)
         # init_surface, src/boundary_surface.cxx:536-572
         self.obuk, self.ustar = z2(1e-9), z2(1e-2)
         self.dudz_mo, self.dvdz_mo, self.dbdz_mo = z2(), z2(), z2()
@@ -905,8 +921,9 @@ class Boundary_surface(Boundary):
                 self._set_bc(fld.fld_bot, fld.grad_bot, fld.flux_bot, self.mbcbot, val, f.visc, 0.)
             self.ustar.fill_(max(0.0001, self.ustarin))
         g = self.grid
-        L.check(g.ctx, g.lib.mhh_surface_init_solver(g.ctx, self.mbcbot, self.thermobc, C.c_double(self.z0m_hom),
-                                                     C.c_double(self.z0h_hom)), "mhh_surface_init_solver")
+        if self.swconstantz0:       # the z/L lookup table of the homogeneous-z0 solver (prepare_lut)
+            L.check(g.ctx, g.lib.mhh_surface_init_solver(g.ctx, self.mbcbot, self.thermobc, C.c_double(self.z0m_hom),
+                                                         C.c_double(self.z0h_hom)), "mhh_surface_init_solver")
 
     def planes(self):
         """The bottom-row inputs of Diff_smag2 (exec_viscosity: z0m, dudz, dvdz, dbdz)."""
@@ -928,6 +945,8 @@ class Boundary_surface(Boundary):
             a.th, a.thbot, a.thgradbot, a.thfluxbot = p(th.fld), p(th.fld_bot), p(th.grad_bot), p(th.flux_bot)
         a.ustar, a.obuk, a.nobuk, a.z0m, a.z0h = p(self.ustar), p(self.obuk), p(self.nobuk), p(self.z0m), p(self.z0h)
         a.dutot, a.dudz, a.dvdz, a.dbdz = p(self._dutot), p(self.dudz_mo), p(self.dvdz_mo), p(self.dbdz_mo)
+        a.iterative_solver, a.charnock = 0 if self.swconstantz0 else 1, 1 if self.swcharnock else 0
+        a.alpha_m, a.alpha_ch, a.alpha_h = self.alpha
         if g.npy == 1:
             L.check(g.ctx, g.lib.mhh_boundary_surface_exec(g.ctx, C.byref(a)), "mhh_boundary_surface_exec")
         else:
@@ -935,6 +954,9 @@ class Boundary_surface(Boundary):
             # neighbours' rows -> the call runs in stages with the ring exchange (self.boundary_cyclic) in between
             st = g.lib.mhh_boundary_surface_exec_stages
             L.check(g.ctx, st(g.ctx, C.byref(a), 1), "mhh_boundary_surface_exec_stages 1")
+            if self.swcharnock:
+                self.boundary_cyclic.exec_2d(self.z0m)
+                self.boundary_cyclic.exec_2d(self.z0h)
             self.boundary_cyclic.exec_2d(self._dutot)
             L.check(g.ctx, st(g.ctx, C.byref(a), 2), "mhh_boundary_surface_exec_stages 2")
             self.boundary_cyclic.exec_2d(u.flux_bot)

@@ -73,7 +73,9 @@ class Model:
         self.mo = bool(mo) and bi.get("swboundary", "default") == "surface"
         if self.mo:
             self.boundary = Boundary_surface(self.grid, self.fields, z0m=bi.get("z0m", 0.1), z0h=bi.get("z0h", 0.1),
-                                             ustar=bi.get("ustar"), **bkw)
+                                             ustar=bi.get("ustar"), swconstantz0=bi.get("swconstantz0", True),
+                                             swcharnock=bi.get("swcharnock", False), alpha_m=bi.get("alpha_m"),
+                                             alpha_ch=bi.get("alpha_ch"), alpha_h=bi.get("alpha_h"), **bkw)
         else:
             self.boundary = Boundary(self.grid, self.fields, swboundary=bi.get("swboundary", "default"), **bkw)
         ai = ini.get("advec", {})

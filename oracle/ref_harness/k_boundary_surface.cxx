@@ -24,17 +24,26 @@ API void ref_surface_lut(void* h, int mbcbot, int thermobc, double z0m, double z
 }
 
 /* thermo: 0 = neutral, 1 = dry (th, thbot, thfluxbot, thgradbot with bc type thermobc; thref/threfh profiles) */
-API void ref_surface_exec(void* h, int mbcbot, int thermo, int thermobc,
-                          const double* u, const double* v, double* ubot, double* vbot,
-                          double* ufluxbot, double* vfluxbot, double* ugradbot, double* vgradbot,
-                          const double* th, double* thbot, double* thgradbot, double* thfluxbot,
-                          const double* thref, const double* threfh,
-                          double* ustar, double* obuk, int* nobuk, const double* z0m, const double* z0h,
-                          double* dutot, double* dudz, double* dvdz, double* dbdz)
+/* iterative != 0: swconstantz0=false (stability<TF,false>: the iterative Obukhov solver on the z0m / z0h planes);
+ * charnock != 0: calc_z0_charnock from the previous ustar first, with its two cyclic fills (src/boundary_surface.cxx:836-851) */
+API void ref_surface_exec_z0(void* h, int mbcbot, int thermo, int thermobc,
+                             const double* u, const double* v, double* ubot, double* vbot,
+                             double* ufluxbot, double* vfluxbot, double* ugradbot, double* vgradbot,
+                             const double* th, double* thbot, double* thgradbot, double* thfluxbot,
+                             const double* thref, const double* threfh,
+                             double* ustar, double* obuk, int* nobuk, double* z0m, double* z0h,
+                             double* dutot, double* dudz, double* dvdz, double* dbdz,
+                             int iterative, int charnock, double alpha_m, double alpha_ch, double alpha_h)
 {
     World* W = static_cast<World*>(h);
     const Grid_data<double>& gd = W->grid->get_grid_data();
     const Boundary_type mb = static_cast<Boundary_type>(mbcbot), tb = static_cast<Boundary_type>(thermobc);
+    if (charnock)
+    {
+        calc_z0_charnock<double>(z0m, z0h, ustar, alpha_m, alpha_ch, alpha_h, gd.istart, gd.iend, gd.jstart, gd.jend, gd.icells);
+        W->cyclic->exec_2d(z0m);
+        W->cyclic->exec_2d(z0h);
+    }
     bsk::calc_dutot<double>(dutot, u, v, ubot, vbot, gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart,
                             gd.icells, gd.jcells, gd.ijcells, *W->cyclic);
     std::vector<double> b, bbot(gd.ijcells), bflux(gd.ijcells);
@@ -52,9 +61,14 @@ API void ref_surface_exec(void* h, int mbcbot, int thermo, int thermobc,
             bflux[ij] = kGrav / threfh[gd.kstart] * thfluxbot[ij];
         }
         const double db_ref = kGrav / thref[gd.kstart] * (thref[gd.kstart] - threfh[gd.kstart]);   /* get_db_ref :629 */
-        stability<double, true>(ustar, obuk, bflux.data(), b.data(), bbot.data(), dutot, gd.z.data(), z0m, z0h,
-                                lut_zL.data(), lut_f.data(), nobuk, db_ref, gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart,
-                                gd.icells, gd.jcells, gd.ijcells, mb, tb, *W->cyclic);
+        if (iterative)
+            stability<double, false>(ustar, obuk, bflux.data(), b.data(), bbot.data(), dutot, gd.z.data(), z0m, z0h,
+                                     lut_zL.data(), lut_f.data(), nobuk, db_ref, gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart,
+                                     gd.icells, gd.jcells, gd.ijcells, mb, tb, *W->cyclic);
+        else
+            stability<double, true>(ustar, obuk, bflux.data(), b.data(), bbot.data(), dutot, gd.z.data(), z0m, z0h,
+                                    lut_zL.data(), lut_f.data(), nobuk, db_ref, gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart,
+                                    gd.icells, gd.jcells, gd.ijcells, mb, tb, *W->cyclic);
     }
     surfm<double>(ufluxbot, vfluxbot, ugradbot, vgradbot, ustar, obuk, u, ubot, v, vbot, z0m, gd.z[gd.kstart], mb,
                   gd.istart, gd.iend, gd.jstart, gd.jend, gd.kstart, gd.icells, gd.jcells, gd.ijcells, *W->cyclic);
@@ -71,6 +85,19 @@ API void ref_surface_exec(void* h, int mbcbot, int thermo, int thermobc,
             bflux[ij] = kGrav / threfh[gd.kstart] * thfluxbot[ij];      /* second get_buoyancy_fluxbot, :966 */
         bsk::calc_dbdz_mo<double>(dbdz, bflux.data(), ustar, obuk, gd.z[gd.kstart], gd.istart, gd.iend, gd.jstart, gd.jend, gd.icells);
     }
+}
+
+API void ref_surface_exec(void* h, int mbcbot, int thermo, int thermobc,
+                          const double* u, const double* v, double* ubot, double* vbot,
+                          double* ufluxbot, double* vfluxbot, double* ugradbot, double* vgradbot,
+                          const double* th, double* thbot, double* thgradbot, double* thfluxbot,
+                          const double* thref, const double* threfh,
+                          double* ustar, double* obuk, int* nobuk, const double* z0m, const double* z0h,
+                          double* dutot, double* dudz, double* dvdz, double* dbdz)
+{
+    ref_surface_exec_z0(h, mbcbot, thermo, thermobc, u, v, ubot, vbot, ufluxbot, vfluxbot, ugradbot, vgradbot, th, thbot, thgradbot,
+                        thfluxbot, thref, threfh, ustar, obuk, nobuk, const_cast<double*>(z0m), const_cast<double*>(z0h),
+                        dutot, dudz, dvdz, dbdz, 0, 0, 0., 0., 0.);
 }
 
 /* surfs for one more scalar (src/boundary_surface.cxx:935-946) */

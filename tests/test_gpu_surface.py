@@ -120,3 +120,68 @@ def test_surface_model_rejects_unsupported_bcs(cuda_lib):
     with pytest.raises(L.MhhError, match="Fixed Ustar bc in combination with Dirichlet"):
         H.Boundary_surface(g, f, mbcbot="ustar", ustar=0.3, sbc={"th": dict(sbcbot="dirichlet")})
     g.close(); W.close()
+
+
+@pytest.mark.parametrize("mode", ["dirichlet_stable", "dirichlet_unstable", "flux_unstable", "flux_stable", "flux_charnock"])
+def test_boundary_surface_iterative_solver_heterogeneous_z0(cuda_lib, mode):
+    """[boundary] swconstantz0=false: the iterative Obukhov-length solvers (calc_obuk_noslip_dirichlet_iterative /
+    calc_obuk_noslip_flux_iterative, include/boundary_surface_kernels.h:287-470) on heterogeneous z0m / z0h planes, and
+    swcharnock=true (calc_z0_charnock, src/boundary_surface.cxx:342-365, from the previous call's u*), three calls in a row
+    (each starts from the Obukhov length of the previous one) against the reference's stability<TF,false>."""
+    from microhh_b200 import host as H
+    from microhh_b200.model import Thermo
+    from oracle.ref import lib, _p
+    case = make_case(itot=24, jtot=16, ktot=8, xsize=400., ysize=400., zsize=400.)
+    g, W = _worlds(case)
+    rng = np.random.default_rng(5)
+    sb = "dirichlet" if mode.startswith("dirichlet") else "flux"
+    sbot = {"dirichlet_stable": 299.2, "dirichlet_unstable": 301.5, "flux_unstable": 0.08, "flux_stable": -0.01, "flux_charnock": 0.05}[mode]
+    charnock = mode == "flux_charnock"
+    f = H.Fields(g, slist=["th"], visc=1e-5, svisc=1e-5)
+    u = 4. + case["u"]; v = 0.5 * case["v"]
+    f.mp["u"].fld.copy_(_up(g, u)); f.mp["v"].fld.copy_(_up(g, v))
+    th = case["s"][0]
+    f.sp["th"].fld.copy_(_up(g, th))
+    z0m = np.exp(rng.uniform(np.log(0.01), np.log(0.5), (W.jcells, W.icells)))      # 1 cm .. 50 cm
+    z0h = z0m * rng.uniform(0.05, 0.5, (W.jcells, W.icells))
+    b = H.Boundary_surface(g, f, z0m=z0m, z0h=z0h, mbcbot="noslip", mbctop="freeslip", swconstantz0=False, swcharnock=charnock,
+                           alpha_m=0.11, alpha_ch=0.018, alpha_h=0.4,
+                           sbc={"th": dict(sbcbot=sb, sbctop="neumann", sbot=sbot, stop=0.003)})
+    b.boundary_cyclic.exec_2d(b.z0m); b.boundary_cyclic.exec_2d(b.z0h)
+    b.set_values()
+    b.set_prognostic_cyclic_bcs()
+    thermo = Thermo(g, f, "dry", thref0=300.)
+    z2 = lambda val=0.: np.full((W.jcells, W.icells), float(val))
+    tbc = 0 if sb == "dirichlet" else 2
+    ua, va, tha = f.mp["u"].fld.cpu().numpy(), f.mp["v"].fld.cpu().numpy(), f.sp["th"].fld.cpu().numpy()
+    o = dict(ubot=z2(), vbot=z2(), uflux=z2(), vflux=z2(), ugrad=z2(), vgrad=z2(),
+             thbot=z2(sbot if sb == "dirichlet" else 0.), thgrad=z2(), thflux=z2(sbot if sb == "flux" else 0.),
+             ustar=z2(1e-2), obuk=z2(1e-9), nobuk=np.zeros((W.jcells, W.icells), dtype=np.int32),
+             z0m=b.z0m.cpu().numpy().copy(), z0h=b.z0h.cpu().numpy().copy(), dutot=z2(), dudz=z2(), dvdz=z2(), dbdz=z2())
+    thref = np.full(W.kcells, 300.)
+    fn = lib().ref_surface_exec_z0
+    for rep in range(3):
+        b.exec(thermo)
+        fn(W.h, C.c_int(0), C.c_int(1), C.c_int(tbc), _p(ua), _p(va), _p(o["ubot"]), _p(o["vbot"]),
+           _p(o["uflux"]), _p(o["vflux"]), _p(o["ugrad"]), _p(o["vgrad"]), _p(tha), _p(o["thbot"]), _p(o["thgrad"]),
+           _p(o["thflux"]), _p(thref), _p(thref), _p(o["ustar"]), _p(o["obuk"]), o["nobuk"].ctypes.data_as(C.c_void_p),
+           _p(o["z0m"]), _p(o["z0h"]), _p(o["dutot"]), _p(o["dudz"]), _p(o["dvdz"]), _p(o["dbdz"]),
+           C.c_int(1), C.c_int(1 if charnock else 0), C.c_double(0.11), C.c_double(0.018), C.c_double(0.4))
+        inner = (slice(W.jstart, W.jend), slice(W.istart, W.iend))
+        got = dict(uflux=f.mp["u"].flux_bot, vflux=f.mp["v"].flux_bot, ustar=b.ustar, obuk=b.obuk, dudz=b.dudz_mo, dvdz=b.dvdz_mo,
+                   thbot=f.sp["th"].fld_bot, thgrad=f.sp["th"].grad_bot, thflux=f.sp["th"].flux_bot, dbdz=b.dbdz_mo, z0m=b.z0m, z0h=b.z0h)
+        for k, t in got.items():
+            a = t.cpu().numpy()
+            sel = inner if k in ("dudz", "dvdz", "dbdz") else (slice(None), slice(None))
+            # the Newton iteration stops on a 0.1 % criterion; CUDA's log/pow/exp are within 2 ulp of glibc's, so the iterates
+            # agree to ~1e-13 and the stopping decisions with them
+            assert rel_err(a[sel], o[k][sel]) <= 1e-10, (k, rep, rel_err(a[sel], o[k][sel]))
+        us = b.ustar.cpu().numpy()[inner]
+        assert us.min() > 0. and us.max() < 2.
+        ua = ua * 1.04; f.mp["u"].fld.mul_(1.04)
+    L = b.obuk.cpu().numpy()[inner]
+    assert (L.max() < 0.) if mode in ("dirichlet_unstable", "flux_unstable", "flux_charnock") else (L.min() > 0.)
+    assert np.unique(np.round(L, 6)).size > 100          # heterogeneous z0: a different Obukhov length per column
+    if charnock:
+        assert not np.array_equal(b.z0m.cpu().numpy()[inner], z0m[inner])
+    g.close(); W.close()
