@@ -388,6 +388,14 @@ double mhh_rk_sub_dt(int rkorder, int substep, double dt);   /* Timeloop::get_su
 /* --- Field3d_operators<TF> (include/field3d_operators.h:40-51) and Fields diagnostics -------------------- */
 int mhh_mean_profile(mhh_ctx* ctx, const double* fld, double* prof_host /* kcells */);
 int mhh_level_sums(mhh_ctx* ctx, const double* fld, double* sums_host /* kcells, this rank only */);
+/* Stats profiles over the default mask (every point), the observables of "stats profiles after N steps": src/stats.cxx
+ * calc_mean :264, calc_moment :342 (sum of (fld - fld_mean[k] + offset)^power), calc_cov :368 (the product of two such
+ * factors, e.g. w'th').  Host profiles of kcells values; levels kstart..kend are filled (half-level fields own level kend),
+ * each divided by the GLOBAL itot*jtot: on a y-slab rank the profiles of the ranks add up (master.sum, src/stats.cxx:1887). */
+int mhh_stats_mean(mhh_ctx* ctx, const double* fld, double* prof_host);
+int mhh_stats_moment(mhh_ctx* ctx, const double* fld, const double* fld_mean_host, double offset, int power, double* prof_host);
+int mhh_stats_cov(mhh_ctx* ctx, const double* fld1, const double* mean1_host, double offset1, int pow1,
+                  const double* fld2, const double* mean2_host, double offset2, int pow2, double* prof_host);
 int mhh_mean(mhh_ctx* ctx, const double* fld, double* mean_out);
 int mhh_mean_2d(mhh_ctx* ctx, const double* fld2d, double* mean_out);
 int mhh_max(mhh_ctx* ctx, const double* fld, double* max_out);   /* calc_max_g: max over interior */

@@ -60,6 +60,7 @@ int level_sums(Ctx*, const double*, double*);
 int weighted_sum(Ctx*, int, const double*, const double*, const double*, double*);
 int interior_max(Ctx*, const double*, double*);
 int plane_sum(Ctx*, const double*, double*);
+int stats_profile(Ctx*, const double*, const double*, double, int, const double*, const double*, double, int, double*);
 // thermo.cu
 int thermo_set_ref(Ctx*, const double*, const double*);
 int thermo_buoyancy_tend(Ctx*, double*, const double*);
@@ -995,6 +996,19 @@ int mhh_mean_profile(mhh_ctx* c, const double* fld, double* prof)
     return MHH_OK;
 }
 int mhh_level_sums(mhh_ctx* c, const double* fld, double* sums) { CTX_CHECK(c); return level_sums(c, fld, sums); }
+
+// Stats profiles over the default mask, src/stats.cxx:264-398 (calc_mean, calc_moment, calc_cov): levels kstart .. kend
+int mhh_stats_mean(mhh_ctx* c, const double* fld, double* prof)
+{ CTX_CHECK(c); if (!fld || !prof) return MHH_ERR_ARG; return stats_profile(c, fld, nullptr, 0., 1, nullptr, nullptr, 0., 1, prof); }
+int mhh_stats_moment(mhh_ctx* c, const double* fld, const double* fld_mean, double offset, int power, double* prof)
+{ CTX_CHECK(c); if (!fld || !fld_mean || !prof) return MHH_ERR_ARG; return stats_profile(c, fld, fld_mean, offset, power, nullptr, nullptr, 0., 1, prof); }
+int mhh_stats_cov(mhh_ctx* c, const double* fld1, const double* mean1, double offset1, int pow1,
+                  const double* fld2, const double* mean2, double offset2, int pow2, double* prof)
+{
+    CTX_CHECK(c);
+    if (!fld1 || !mean1 || !fld2 || !mean2 || !prof) return MHH_ERR_ARG;
+    return stats_profile(c, fld1, mean1, offset1, pow1, fld2, mean2, offset2, pow2, prof);
+}
 
 int mhh_mean(mhh_ctx* c, const double* fld, double* out)
 {

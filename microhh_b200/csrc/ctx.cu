@@ -228,7 +228,7 @@ void ctx_free(Ctx* c)
     for (auto e : c->prof_pool) cudaEventDestroy(e);
     cudaFree(c->metrics_d);
     cudaFree(c->max_bits_d);
-    cudaFree(c->sum_d);
+    cudaFree(c->sum_d); cudaFree(c->stats_d);
     if (c->host_pinned) cudaFreeHost(c->host_pinned);
     cudaFree(c->bmati_d); cudaFree(c->bmatj_d); cudaFree(c->pres_a_d); cudaFree(c->pres_c_d); cudaFree(c->bands_d);
     cudaFree(c->work_p); cudaFree(c->work_c); cudaFree(c->work_h);

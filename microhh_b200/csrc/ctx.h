@@ -49,6 +49,7 @@ struct Ctx
     const double* fresh_uvw[3] = {nullptr, nullptr, nullptr};
     const double* fresh_s[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double* sum_d = nullptr;                    // kcells + 16 slots
+    double* stats_d = nullptr;                  // 2 * kcells: the mean profiles of mhh_stats_moment / mhh_stats_cov
     double* host_pinned = nullptr;              // kcells + 16 doubles, pinned
 
     // pressure solver

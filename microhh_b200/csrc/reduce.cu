@@ -78,6 +78,28 @@ namespace
         if (threadIdx.x == 0) out[0] = s;
     }
 
+    // Stats profiles over the default mask (every point), src/stats.cxx: calc_mean :264 (m1 == NULL, p1 = 1), calc_moment :342
+    // (f2 == NULL), calc_cov :368 — per level the sum of pow(f1 - m1[k] + o1, p1) * pow(f2 - m2[k] + o2, p2)
+    __global__ void __launch_bounds__(256)
+    stats_level_kernel(double* __restrict__ out, const double* __restrict__ f1, const double* __restrict__ m1, const double o1,
+                       const int p1, const double* __restrict__ f2, const double* __restrict__ m2, const double o2, const int p2,
+                       const GridD gd)
+    {
+        const int k = blockIdx.x + gd.kstart;
+        const int n = gd.imax * gd.jmax;
+        const double mean1 = m1 ? m1[k] : 0., mean2 = m2 ? m2[k] : 0.;
+        double acc = 0.;
+        for (int t = threadIdx.x; t < n; t += blockDim.x)
+        {
+            const int ijk = (t % gd.imax + gd.istart) + (t / gd.imax + gd.jstart) * gd.icells + k * gd.ijcells;
+            double term = m1 ? pow(f1[ijk] - mean1 + o1, (double)p1) : f1[ijk];
+            if (f2) term *= pow(f2[ijk] - mean2 + o2, (double)p2);
+            acc += term;
+        }
+        const double s = block_sum(acc);
+        if (threadIdx.x == 0) out[blockIdx.x] = s;
+    }
+
     template<int OP>
     int run_levels(Ctx* c, const double* a, const double* b, const double* w, int kfirst, int nk)
     {
@@ -122,6 +144,40 @@ int interior_max(Ctx* c, const double* a, double* out)
         m = (x > m || x != x) ? x : m;
     }
     *out = m;
+    return MHH_OK;
+}
+
+// levels kstart .. kend (inclusive: half-level fields carry one level more, src/stats.cxx:271); this rank's sums divided by
+// the GLOBAL itot*jtot, so that the ranks' profiles add up to the statistic (master.sum in Stats::calc_stats)
+int stats_profile(Ctx* c, const double* f1, const double* mean1_host, double o1, int p1,
+                  const double* f2, const double* mean2_host, double o2, int p2, double* prof_host)
+{
+    const GridD& gd = c->gd;
+    const int nk = gd.kmax + 1;
+    if (!c->stats_d) MHH_CUDA_CHECK(cudaMalloc(&c->stats_d, 2 * gd.kcells * sizeof(double)));
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));      // host_pinned is about to be reused
+    double* m1 = nullptr; double* m2 = nullptr;
+    if (mean1_host)
+    {
+        for (int k = 0; k < gd.kcells; ++k) c->host_pinned[k] = mean1_host[k];
+        MHH_CUDA_CHECK(cudaMemcpyAsync(c->stats_d, c->host_pinned, gd.kcells * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        m1 = c->stats_d;
+    }
+    if (f2 && mean2_host)
+    {
+        for (int k = 0; k < gd.kcells; ++k) c->host_pinned[k] = mean2_host[k];
+        MHH_CUDA_CHECK(cudaMemcpyAsync(c->stats_d + gd.kcells, c->host_pinned, gd.kcells * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        m2 = c->stats_d + gd.kcells;
+    }
+    MHH_LAUNCH(c, "stats_level_kernel", stats_level_kernel<<<nk, 256, 0, c->stream>>>(c->sum_d, f1, m1, o1, p1, f2, m2, o2, p2, gd));
+    MHH_LAUNCH_CHECK();
+    MHH_CUDA_CHECK(cudaMemcpyAsync(c->host_pinned, c->sum_d, nk * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    const double n = (double)gd.itot * gd.jtot;
+    for (int k = 0; k < gd.kcells; ++k) prof_host[k] = 0.;
+    for (int k = 0; k < nk; ++k) prof_host[gd.kstart + k] = c->host_pinned[k] / n;
     return MHH_OK;
 }
 

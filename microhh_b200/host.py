@@ -310,6 +310,52 @@ class Field3d_operators:
         return self._scalar(self.grid.lib.mhh_max, fld)
 
 
+class Stats:
+    """The profile statistics of Stats (include/stats.h, src/stats.cxx:264-398) over the default mask: xy means, central
+    moments and covariances per level, computed on the device.  Profiles are numpy arrays of kcells values (levels
+    kstart..kend filled).  On a y-slab rank pass ``comm`` (multigpu.SlabComm): the ranks' profiles are summed (master.sum)."""
+
+    def __init__(self, grid: Grid, comm=None):
+        self.grid, self.comm = grid, comm
+
+    def _reduce(self, prof):
+        if self.comm is not None and self.comm.world > 1:
+            return self.comm.allreduce_sum(prof, self.grid.device).cpu().numpy()
+        return prof
+
+    def calc_mean(self, fld):
+        g = self.grid
+        prof = np.zeros(g.kcells)
+        L.check(g.ctx, g.lib.mhh_stats_mean(g.ctx, L.ptr(fld), prof.ctypes.data_as(C.c_void_p)), "mhh_stats_mean")
+        return self._reduce(prof)
+
+    def calc_moment(self, fld, fld_mean, power, offset=0.):
+        g = self.grid
+        prof, mean = np.zeros(g.kcells), np.ascontiguousarray(fld_mean, dtype=np.float64)
+        L.check(g.ctx, g.lib.mhh_stats_moment(g.ctx, L.ptr(fld), mean.ctypes.data_as(C.c_void_p), C.c_double(offset), int(power),
+                                              prof.ctypes.data_as(C.c_void_p)), "mhh_stats_moment")
+        return self._reduce(prof)
+
+    def calc_cov(self, fld1, mean1, fld2, mean2, pow1=1, pow2=1, offset1=0., offset2=0.):
+        g = self.grid
+        prof = np.zeros(g.kcells)
+        m1, m2 = np.ascontiguousarray(mean1, dtype=np.float64), np.ascontiguousarray(mean2, dtype=np.float64)
+        L.check(g.ctx, g.lib.mhh_stats_cov(g.ctx, L.ptr(fld1), m1.ctypes.data_as(C.c_void_p), C.c_double(offset1), int(pow1),
+                                           L.ptr(fld2), m2.ctypes.data_as(C.c_void_p), C.c_double(offset2), int(pow2),
+                                           prof.ctypes.data_as(C.c_void_p)), "mhh_stats_cov")
+        return self._reduce(prof)
+
+    def profiles(self, fields):
+        """Means and variances of every prognostic field, and the resolved flux w'th' when th exists."""
+        out = {}
+        for n, f in fields.ap.items():
+            out[n] = self.calc_mean(f.fld)
+            out[n + "_2"] = self.calc_moment(f.fld, out[n], 2)
+        if "th" in fields.sp:
+            out["wth"] = self.calc_cov(fields.mp["w"].fld, np.zeros(self.grid.kcells), fields.sp["th"].fld, out["th"])
+        return out
+
+
 class Boundary_cyclic:
     """Boundary_cyclic (include/boundary_cyclic.h:36-49)."""
 

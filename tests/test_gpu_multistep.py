@@ -67,10 +67,22 @@ def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=
         dts.append((m.timeloop.idt, o.idt))
     got = {n: f.ap[n].fld.cpu().numpy() for n in names}
     want = {n: o.a[n] for n in names}
+    # the same observables from the Stats kernels on both sides: device profiles (mhh_stats_*) of the GPU fields, the
+    # reference's calc_mean / calc_moment / calc_cov (src/stats.cxx) of the oracle's fields
+    from microhh_b200.host import Stats
+    dev_prof = Stats(g).profiles(f)
+    ref_prof = {}
+    for n in names:
+        ref_prof[n] = np.zeros(g.kcells); o.W.call("ref_stats_mean", ref_prof[n], o.a[n])
+        ref_prof[n + "_2"] = np.zeros(g.kcells); o.W.call("ref_stats_moment", ref_prof[n + "_2"], o.a[n], ref_prof[n], 0., 2)
+    if "th" in names:
+        ref_prof["wth"] = np.zeros(g.kcells)
+        o.W.call("ref_stats_cov", ref_prof["wth"], o.a["w"], np.zeros(g.kcells), 0., 1, o.a["th"], ref_prof["th"], 0., 1)
     st = m.print_status()
     odiv = o.divergence()
     dims = (g.kstart, g.kend, g.jstart, g.jend, g.istart, g.iend)
-    res = dict(got=got, want=want, dts=dts, status=st, odiv=odiv, dims=dims, time=(m.timeloop.itime, o.itime))
+    res = dict(got=got, want=want, dts=dts, status=st, odiv=odiv, dims=dims, time=(m.timeloop.itime, o.itime),
+               dev_prof=dev_prof, ref_prof=ref_prof)
     o.close(); g.close()
     return res
 
@@ -84,6 +96,11 @@ def check_profiles(res, tol=1e-9, dt_ns=None):
     print("status", res["status"], "oracle div", res["odiv"])
     for k, e in errs.items():
         assert e <= tol, (k, e)
+    if "dev_prof" in res:       # Stats kernels on the device vs the reference's Stats functions, same tolerance and scales
+        ks, ke = res["dims"][0], res["dims"][1]
+        for k, ref in res["ref_prof"].items():
+            e = float(np.abs(res["dev_prof"][k][ks:ke] - ref[ks:ke]).max() / scale[k])
+            assert e <= tol, ("stats kernel", k, e)
     ddt = max(abs(a - b) for a, b in res["dts"])
     print("max |idt_gpu - idt_ref| =", ddt, "ns")
     if dt_ns is not None:

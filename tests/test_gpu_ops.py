@@ -557,3 +557,37 @@ def test_fused_force_tail_equals_separate_buffer_and_coriolis(cuda_lib):
         assert np.array_equal(out[0][0][nm], out[1][0][nm]), nm
     assert out[0][2] == out[1][2]
     assert np.abs(out[0][0]["v"]).max() > 1e-4
+
+
+@pytest.mark.parametrize("kw", [dict(itot=32, jtot=24, ktot=16, alpha=1.2), dict(itot=20, jtot=12, ktot=10, order=4)], ids=["o2", "o4"])
+def test_stats_profiles(cuda_lib, kw):
+    """mhh_stats_mean / _moment / _cov against the reference's calc_mean, calc_moment (powers 2, 3, 4) and calc_cov
+    (src/stats.cxx:264-398 compiled in place, oracle/ref_harness/k_stats.cxx) over the default mask."""
+    from microhh_b200 import host as H
+    case = make_case(**kw)
+    g, W = _worlds(case)
+    st = H.Stats(g)
+    w, th = case["w"], case["s"][0]
+    dw, dth = _up(g, w), _up(g, th)
+    ks, ke = W.kstart, W.kend + 1
+    for a, d in ((w, dw), (th, dth)):
+        ref = np.zeros(W.kcells)
+        W.call("ref_stats_mean", ref, a)
+        got = st.calc_mean(d)
+        assert np.abs(got[ks:ke] - ref[ks:ke]).max() <= 1e-13 * max(np.abs(ref).max(), 1e-300)
+        for power in (2, 3, 4):
+            r2 = np.zeros(W.kcells)
+            W.call("ref_stats_moment", r2, a, ref, 0.25, power)
+            g2 = st.calc_moment(d, ref, power, offset=0.25)
+            assert np.abs(g2[ks:ke] - r2[ks:ke]).max() <= 1e-12 * np.abs(r2).max(), power
+    mw, mth = np.zeros(W.kcells), np.zeros(W.kcells)
+    W.call("ref_stats_mean", mw, w); W.call("ref_stats_mean", mth, th)
+    rc = np.zeros(W.kcells)
+    W.call("ref_stats_cov", rc, w, mw, 0., 1, th, mth, 0., 1)
+    gc = st.calc_cov(dw, mw, dth, mth)
+    assert np.abs(gc[ks:ke] - rc[ks:ke]).max() <= 1e-12 * np.abs(rc).max()
+    rc2 = np.zeros(W.kcells)
+    W.call("ref_stats_cov", rc2, w, mw, 0.1, 2, th, mth, -0.2, 1)
+    gc2 = st.calc_cov(dw, mw, dth, mth, pow1=2, pow2=1, offset1=0.1, offset2=-0.2)
+    assert np.abs(gc2[ks:ke] - rc2[ks:ke]).max() <= 1e-12 * np.abs(rc2).max()
+    g.close(); W.close()
