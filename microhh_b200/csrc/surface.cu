@@ -58,7 +58,7 @@ namespace
     // f(L) = zsl/L - Ri-like term with a +-0.1 % finite-difference slope, one restart with a safe start value, the result
     // limited to the z/L range of the lookup solver.  FLUX: the first form (bfluxbot), else the second (db, z0h).
     template<bool FLUX>
-    __device__ inline double obuk_iterative(double L, const double du, double bf, const double zsl, const double z0m, const double z0h)
+    __host__ __device__ inline double obuk_iterative(double L, const double du, double bf, const double zsl, const double z0m, const double z0h)
     {
         constexpr double kDsmallS = 1.e-9, Lmax = 1.e16;
         const double L_min_stable = zsl / kZLmax;
