@@ -27,6 +27,12 @@ extern "C" {
 #endif
 
 typedef struct mhh_ctx mhh_ctx;
+/* always IEEE double, in the `_f32` symbol set too (include/mhh_b200_f32.h): time steps — the reference's rk3_g / rk4_g take
+ * `mhh_double dt` for TF = float as well (src/timeloop.cu:35,74) and Advec/Diff/Pres take `mhh_double dt` (include/advec.h:57-58) */
+#ifndef MHH_DOUBLE_DEFINED
+#define MHH_DOUBLE_DEFINED
+typedef double mhh_double;
+#endif
 
 /* Boundary_type, include/boundary.h:51 */
 enum { MHH_BC_DIRICHLET = 0, MHH_BC_NEUMANN = 1, MHH_BC_FLUX = 2, MHH_BC_USTAR = 3, MHH_BC_OFF = 4 };
@@ -67,7 +73,7 @@ const double* mhh_get_metric_device(const mhh_ctx* ctx, const char* name);
 unsigned long long mhh_launch_count(const mhh_ctx* ctx);          /* kernels launched so far by this ctx */
 int mhh_profile_enable(mhh_ctx* ctx, int on);                     /* bracket every launch with CUDA events */
 /* Sums recorded intervals per kernel since the last report. names: ';'-joined. Returns the entry count. */
-int mhh_profile_report(mhh_ctx* ctx, char* names, int names_size, double* ms, long* counts, int max_entries);
+int mhh_profile_report(mhh_ctx* ctx, char* names, int names_size, mhh_double* ms, long* counts, int max_entries);
 
 /* --- Advec<TF> (include/advec.h:54-60) ------------------------------------------------------ */
 /* Advec_2/2i5/4::exec — src/advec_2.cxx:298, src/advec_2i5.cxx:977, src/advec_4.cxx:592.
@@ -78,10 +84,10 @@ int mhh_advec_exec(mhh_ctx* ctx, int scheme,
                    int nscalars, const double* const* s, double* const* st, const int* limit_flags);
 /* Advec_*::get_cfl — src/advec_2.cxx:267 (calc_cfl :51): cfl = dt * max(|u|/dx + |v|/dy + |w|/dz). */
 int mhh_advec_cfl(mhh_ctx* ctx, int scheme, const double* u, const double* v, const double* w,
-                  double dt, double* cfl_out);
+                  mhh_double dt, double* cfl_out);
 /* Advec_*::get_time_limit — src/advec_2.cxx:281: idt * cflmax / max(cflmin, cfl). */
 int mhh_advec_time_limit(mhh_ctx* ctx, int scheme, const double* u, const double* v, const double* w,
-                         unsigned long idt, double dt, double cflmax, unsigned long* idtlim_out);
+                         unsigned long idt, mhh_double dt, double cflmax, unsigned long* idtlim_out);
 
 /* --- Diff<TF> (include/diff.h:45-64) ---------------------------------------------------------- */
 /* Diff_2::exec src/diff_2.cxx:162 (diff_c :39 for u,v,scalars; diff_w :64). svisc[n] per scalar. */
@@ -141,7 +147,7 @@ int mhh_advec2_smag2_exec_rk_parts(mhh_ctx* ctx, int surface_model,
                                    const double* ufluxbot, const double* ufluxtop, const double* vfluxbot, const double* vfluxtop,
                                    double visc, const double* th_buoy, int nscalars, const double* const* s, double* const* st,
                                    const double* const* sfluxbot, const double* const* sfluxtop, const double* svisc, double tPr,
-                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt,
+                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, mhh_double dt,
                                    int do_uvw, int do_scalars, int kc0, int nkc);
 /* Buffer::exec (src/buffer.cxx:163; calc_buffer :37-58) and the swlspres=geo branch of Force::exec (src/force.cxx:609-625,
  * calc_coriolis_2nd :76-107) for u,v,w, applied inside the fused momentum pass of mhh_advec2_smag2_exec[_rk] to the finished
@@ -202,7 +208,7 @@ int mhh_advec2_smag2_exec_rk(mhh_ctx* ctx, int surface_model,
                              int nscalars, const double* const* s, double* const* st,
                              const double* const* sfluxbot, const double* const* sfluxtop,
                              const double* svisc, double tPr,
-                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt);
+                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, mhh_double dt);
 /* calc_strain2 alone (src/diff_smag2.cxx:48) — stage check for parity tests; the product path fuses it. */
 int mhh_smag2_strain2(mhh_ctx* ctx, int surface_model, const double* u, const double* v, const double* w,
                       const double* dudz, const double* dvdz, double* strain2);
@@ -269,7 +275,7 @@ int mhh_buffer_exec(mhh_ctx* ctx, double* at, const double* a, const double* abu
 /* swlspres=dpdx: add_pressure_force(ut, -dpdx), src/force.cxx:46-60,603-611 */
 int mhh_force_pressure(mhh_ctx* ctx, double* ut, double fbody);
 /* swlspres=uflux: enforce_fixed_flux with the two calc_mean reductions, src/force.cxx:63-75,590-601 */
-int mhh_force_fixed_flux(mhh_ctx* ctx, double* ut, const double* u, double uflux, double utrans, double dt, double* fbody_out);
+int mhh_force_fixed_flux(mhh_ctx* ctx, double* ut, const double* u, double uflux, double utrans, mhh_double dt, double* fbody_out);
 /* swlspres=geo: calc_coriolis_2nd/_4th, src/force.cxx:78-144,613-634; ug, vg device profiles (kcells) */
 int mhh_force_coriolis(mhh_ctx* ctx, double* ut, double* vt, const double* u, const double* v,
                        const double* ug, const double* vg, double fc, double utrans, double vtrans);
@@ -286,7 +292,7 @@ int mhh_force_subsidence(mhh_ctx* ctx, int mode, double* st, const double* s, co
 int mhh_pres_set_values(mhh_ctx* ctx);
 /* Pres_2/4::exec(dt) — src/pres_2.cxx:66, src/pres_4.cxx:77: input, solve, output. p is ghosted. */
 int mhh_pres_exec(mhh_ctx* ctx, const double* u, const double* v, const double* w,
-                  double* ut, double* vt, double* wt, double* p, double dt);
+                  double* ut, double* vt, double* wt, double* p, mhh_double dt);
 /* Pres_2/4::check_divergence — src/pres_2.cxx:99,391; src/pres_4.cxx:144,733. */
 int mhh_pres_check_divergence(mhh_ctx* ctx, const double* u, const double* v, const double* w,
                               double* divmax_out);
@@ -297,7 +303,7 @@ int mhh_pres_check_divergence(mhh_ctx* ctx, const double* u, const double* v, co
  *  output: scatter + ghost rows + cyclic + Pres_*::output src/pres_2.cxx:340-387 */
 double* mhh_pres_work(mhh_ctx* ctx);
 int mhh_pres_input(mhh_ctx* ctx, const double* u, const double* v, const double* w,
-                   double* ut, double* vt, double* wt, double dt);
+                   double* ut, double* vt, double* wt, mhh_double dt);
 int mhh_fft_force_generic(mhh_ctx* ctx, int on);   /* tests: use the mixed-radix kernel even for 2^k sizes */
 int mhh_fft_forward(mhh_ctx* ctx, double* data);
 int mhh_fft_backward(mhh_ctx* ctx, double* data);      /* normalised by 1/(itot*jtot), in place */
@@ -308,7 +314,7 @@ int mhh_pres_output(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p)
  *                  2 Y->chunks, 3 chunks->X (Transpose::exec_yx, :191-217); chunk r = [k][j<jmax][ii<iblock].
  * The all-to-all between pack and unpack is the host's (NCCL over NVLink). dir: -1 forward, +1 backward. */
 int mhh_pres_input_to(mhh_ctx* ctx, const double* u, const double* v, const double* w, const double* ut,
-                      const double* vt, const double* wt, double dt, double* dst_X);
+                      const double* vt, const double* wt, mhh_double dt, double* dst_X);
 int mhh_fft_x(mhh_ctx* ctx, int dir, double* data_X, double* p_or_null);
 int mhh_fft_y(mhh_ctx* ctx, int dir, double* data_Y);
 /* FFT stages that read / write the all-to-all chunk layout directly (chunk for peer r = [k][j<jmax][ii<iblock]), fusing
@@ -372,7 +378,7 @@ int mhh_set_bc(mhh_ctx* ctx, double* a2d, double* agrad2d, double* aflux2d, int 
                double visc, double offset);
 
 /* --- Timeloop<TF>::exec (src/timeloop.cxx:358; rk3 :250, rk4 :288) -------------------------------------- */
-int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, double dt,
+int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, mhh_double dt,
                    int nfields, double* const* a, double* const* at);
 /* Fused tail of the substep (no reference counterpart: Pres_2::output src/pres_2.cxx:365-387 / Pres_4::output
  * src/pres_4.cxx:533-571 immediately followed by Timeloop::exec src/timeloop.cxx:358-411 for u,v,w).  Bit-identical to
@@ -380,10 +386,10 @@ int mhh_rk_substep(mhh_ctx* ctx, int rkorder, int substep, double dt,
  * fields with the same substep.  4th order (mhh_pres_exec_rk only): the call also performs
  * Boundary::set_ghost_cells_w(Normal) on w (src/model.cxx:412) before the update, so the caller must not repeat it. */
 int mhh_pres_output_rk(mhh_ctx* ctx, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
-                       int rkorder, int substep, double dt);
+                       int rkorder, int substep, mhh_double dt);
 int mhh_pres_exec_rk(mhh_ctx* ctx, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,
-                     double dt_sub, int rkorder, int substep, double dt);
-double mhh_rk_sub_dt(int rkorder, int substep, double dt);   /* Timeloop::get_sub_time_step :415 */
+                     mhh_double dt_sub, int rkorder, int substep, mhh_double dt);
+mhh_double mhh_rk_sub_dt(int rkorder, int substep, mhh_double dt);   /* Timeloop::get_sub_time_step :415 */
 
 /* --- Field3d_operators<TF> (include/field3d_operators.h:40-51) and Fields diagnostics -------------------- */
 int mhh_mean_profile(mhh_ctx* ctx, const double* fld, double* prof_host /* kcells */);

@@ -5,6 +5,7 @@
 // Layout: thread (i,j) of a 2-D tile marches a chunk of k with the k-1/k/k+1 values of
 // u,v,w held in registers (each array element is loaded from global once per thread for
 // the centre column; the i+-1 / j+-1 neighbours come from L1/L2).
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

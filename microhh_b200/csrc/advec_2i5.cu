@@ -9,6 +9,7 @@
 // reference drops a term get an exact 0 for it, which leaves the sum unchanged to the last bit.
 // The horizontal and the vertical contributions are added to the tendency in two steps like the
 // reference's two passes.
+#include "sys.h"
 #include <cfloat>
 #ifndef MHH_ADVEC2I5_UNROLL_N
 #define MHH_ADVEC2I5_UNROLL_N 2

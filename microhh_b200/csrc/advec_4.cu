@@ -5,6 +5,7 @@
 // One thread per (i,j) column marches a chunk of k; every 4-point interpolation is written out with
 // the reference's left-to-right summation order and the x, y, z contributions are subtracted from the
 // tendency one after the other, as the reference does, so results agree to rounding with the CPU build.
+#include "sys.h"
 #include "ctx.h"
 #ifndef MHH_ADVEC4_MINB
 #define MHH_ADVEC4_MINB 2

@@ -1,6 +1,7 @@
 // Periodic halos (src/boundary_cyclic.cxx:369-443) and vertical ghost rows (src/boundary.cxx:687-907).
 // Single-GPU version: in-place copies. East/west first, then north/south including the freshly
 // filled east/west ghosts, so corners come out as in the reference.
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

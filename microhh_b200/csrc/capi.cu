@@ -1,4 +1,5 @@
 // extern "C" surface declared in include/mhh_b200.h.
+#include "sys.h"
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -53,8 +54,8 @@ int ghost_cells_exec(Ctx*, double*, int, int, double*, double*, const double*, c
 int ghost_cells_w_exec(Ctx*, double*, int);
 int set_bc_exec(Ctx*, double*, double*, double*, int, double, double, double);
 // timeloop.cu
-int rk_substep(Ctx*, int, int, double, int, double* const*, double* const*);
-double rk_sub_dt(int, int, double);
+int rk_substep(Ctx*, int, int, mhh_f64, int, double* const*, double* const*);
+mhh_f64 rk_sub_dt(int, int, mhh_f64);
 // reduce.cu
 int level_sums(Ctx*, const double*, double*);
 int weighted_sum(Ctx*, int, const double*, const double*, const double*, double*);
@@ -115,8 +116,8 @@ static int read_max(Ctx* c, unsigned long long* slot, double* out)
     unsigned long long* h = reinterpret_cast<unsigned long long*>(c->host_pinned);
     MHH_CUDA_CHECK(cudaMemcpyAsync(h, slot, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    double d;
-    std::memcpy(&d, h, sizeof(double));
+    mhh_f64 d;                                   // the slot holds the bit pattern of a double in either build
+    std::memcpy(&d, h, sizeof(mhh_f64));
     *out = d;
     return MHH_OK;
 }
@@ -254,7 +255,7 @@ int pres2_in_fft_x(Ctx*, const FftPlan&, const double*, const double*, const dou
 // (2nd order, power-of-two itot) or the two separate stages; then the y pass.  The spectrum lands in c->work_p.
 static int fft_y(Ctx* c, int dir, double* data);
 static int pres_input_fft_forward(Ctx* c, const double* u, const double* v, const double* w,
-                                  double* ut, double* vt, double* wt, double dt)
+                                  double* ut, double* vt, double* wt, mhh_double dt)
 {
     const GridD& gd = c->gd;
     if (int e = cyclic_exec(c, ut, MHH_EDGE_EAST_WEST)) return e;       // src/pres_2.cxx:180-181 / src/pres_4.cxx:284-286
@@ -412,7 +413,7 @@ const double* mhh_get_metric_device(const mhh_ctx* c, const char* name)
 // ---------------------------------------------------------------- launch accounting / live kernel timing
 unsigned long long mhh_launch_count(const mhh_ctx* c) { return c ? c->launches : 0ULL; }
 int mhh_profile_enable(mhh_ctx* c, int on) { CTX_CHECK(c); c->prof_on = on != 0; return MHH_OK; }
-int mhh_profile_report(mhh_ctx* c, char* names, int names_size, double* ms, long* counts, int max_entries)
+int mhh_profile_report(mhh_ctx* c, char* names, int names_size, mhh_double* ms, long* counts, int max_entries)
 {
     CTX_CHECK(c);
     std::vector<double> t; std::vector<long> n;
@@ -446,7 +447,7 @@ int mhh_advec_exec(mhh_ctx* c, int scheme, const double* u, const double* v, con
     }
 }
 
-int mhh_advec_cfl(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w, double dt, double* cfl)
+int mhh_advec_cfl(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w, mhh_double dt, double* cfl)
 {
     CTX_CHECK(c);
     int e;
@@ -465,7 +466,7 @@ int mhh_advec_cfl(mhh_ctx* c, int scheme, const double* u, const double* v, cons
 }
 
 int mhh_advec_time_limit(mhh_ctx* c, int scheme, const double* u, const double* v, const double* w,
-                         unsigned long idt, double dt, double cflmax, unsigned long* out)
+                         unsigned long idt, mhh_double dt, double cflmax, unsigned long* out)
 {
     double cfl;
     if (int e = mhh_advec_cfl(c, scheme, u, v, w, dt, &cfl)) return e;
@@ -547,8 +548,9 @@ int mhh_smag2_exec_viscosity_dry_limits(mhh_ctx* c, int surface_model, const dou
     unsigned long long* h = reinterpret_cast<unsigned long long*>(c->host_pinned);
     MHH_CUDA_CHECK(cudaMemcpyAsync(h, slots, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    std::memcpy(cfl_over_dt, h, sizeof(double));
-    std::memcpy(dnmul, h + 1, sizeof(double));
+    mhh_f64 m[2];                                // bit patterns of doubles in either build
+    std::memcpy(m, h, 2 * sizeof(mhh_f64));
+    *cfl_over_dt = m[0]; *dnmul = m[1];
     return MHH_OK;
 }
 
@@ -585,7 +587,7 @@ int mhh_advec2_smag2_exec_rk(mhh_ctx* c, int surface_model, const double* u, con
                              double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
                              double visc, const double* th_buoy, int ns, const double* const* s, double* const* st,
                              const double* const* sfb, const double* const* sft, const double* svisc, double tPr,
-                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt)
+                             const double* const* sbuf, double* const* s_new, int rkorder, int substep, mhh_double dt)
 {
     CTX_CHECK(c);
     if (c->order != 2) { c->last_error = "mhh_advec2_smag2_exec_rk needs the 2nd-order grid"; return MHH_ERR_UNSUPPORTED; }
@@ -605,7 +607,7 @@ int mhh_advec2_smag2_exec_rk_parts(mhh_ctx* c, int surface_model, const double* 
                                    double* ut, double* vt, double* wt, const double* ufb, const double* uft, const double* vfb, const double* vft,
                                    double visc, const double* th_buoy, int ns, const double* const* s, double* const* st,
                                    const double* const* sfb, const double* const* sft, const double* svisc, double tPr,
-                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, double dt,
+                                   const double* const* sbuf, double* const* s_new, int rkorder, int substep, mhh_double dt,
                                    int do_uvw, int do_scalars, int kc0, int nkc)
 {
     CTX_CHECK(c);
@@ -712,7 +714,7 @@ int mhh_buffer_exec(mhh_ctx* c, double* at, const double* a, const double* abuf,
 { CTX_CHECK(c); if (!at || !a || !abuf) { c->last_error = "mhh_buffer_exec: null pointer"; return MHH_ERR_ARG; } MHH_TEND(at); return buffer_exec(c, at, a, abuf, is_w); }
 int mhh_force_pressure(mhh_ctx* c, double* ut, double fbody)
 { CTX_CHECK(c); MHH_TEND(ut); return force_level_source(c, 0, ut, fbody, nullptr, nullptr, nullptr); }
-int mhh_force_fixed_flux(mhh_ctx* c, double* ut, const double* u, double uflux, double utrans, double dt, double* fbody_out)
+int mhh_force_fixed_flux(mhh_ctx* c, double* ut, const double* u, double uflux, double utrans, mhh_double dt, double* fbody_out)
 {
     CTX_CHECK(c);
     // enforce_fixed_flux, src/force.cxx:63-75, with the two calc_mean calls of Force::exec :593-594
@@ -770,7 +772,7 @@ double* mhh_pres_work(mhh_ctx* c) { return c ? c->work_p : nullptr; }
 
 #define PRES_READY(c) do { CTX_CHECK(c); if (!(c)->pres_ready) { if (int e__ = mhh_pres_set_values(c)) return e__; } } while (0)
 
-int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt, double dt)
+int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w, double* ut, double* vt, double* wt, mhh_double dt)
 {
     PRES_READY(c);
     MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
@@ -786,7 +788,7 @@ int mhh_pres_input(mhh_ctx* c, const double* u, const double* v, const double* w
 
 // Pres_2::input into a caller-supplied ghost-free array (y-slab driver); halos of ut/vt are the caller's.
 int mhh_pres_input_to(mhh_ctx* c, const double* u, const double* v, const double* w, const double* ut, const double* vt,
-                      const double* wt, double dt, double* dst)
+                      const double* wt, mhh_double dt, double* dst)
 {
     PRES_READY(c);
     if (c->order != 2) return MHH_ERR_UNSUPPORTED;
@@ -846,7 +848,7 @@ int mhh_pres_output_stage(mhh_ctx* c, int stage, double* ut, double* vt, double*
 int mhh_pres_scatter(mhh_ctx* c, double* p, const double* src) { CTX_CHECK(c); return pres_scatter(c, p, src); }
 
 int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
-                  double* ut, double* vt, double* wt, double* p, double dt)
+                  double* ut, double* vt, double* wt, double* p, mhh_double dt)
 {
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
@@ -861,7 +863,7 @@ int mhh_pres_exec(mhh_ctx* c, const double* u, const double* v, const double* w,
 // Pres_2::output's gradient stage fused with Timeloop::exec for u,v,w (the caller still runs mhh_rk_substep on the
 // remaining prognostic fields with the same substep).  p must carry its ghost row and halos (output stage 0).
 int mhh_pres_output_rk(mhh_ctx* c, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
-                       int rkorder, int substep, double dt)
+                       int rkorder, int substep, mhh_double dt)
 {
     PRES_READY(c);
     if (c->order != 2) return MHH_ERR_UNSUPPORTED;
@@ -871,7 +873,7 @@ int mhh_pres_output_rk(mhh_ctx* c, double* ut, double* vt, double* wt, double* p
 // mhh_pres_exec with the fused last stage: on return u,v,w hold the substep's new velocities and ut,vt,wt the scaled
 // tendencies the next substep starts from
 int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,
-                     double dt_sub, int rkorder, int substep, double dt)
+                     mhh_double dt_sub, int rkorder, int substep, mhh_double dt)
 {
     PRES_READY(c);
     if (c->npy != 1) { c->last_error = "mhh_pres_exec_rk is the single-GPU pipeline; y-slab ranks drive the stages"; return MHH_ERR_STATE; }
@@ -922,9 +924,9 @@ int mhh_set_bc(mhh_ctx* c, double* a, double* agrad, double* aflux, int sw, doub
 { CTX_CHECK(c); return set_bc_exec(c, a, agrad, aflux, sw, aval, visc, offset); }
 
 // ---------------------------------------------------------------- Timeloop
-int mhh_rk_substep(mhh_ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
+int mhh_rk_substep(mhh_ctx* c, int rkorder, int substep, mhh_double dt, int nfields, double* const* a, double* const* at)
 { CTX_CHECK(c); MHH_TENDS(at, nfields); return rk_substep(c, rkorder, substep, dt, nfields, a, at); }
-double mhh_rk_sub_dt(int rkorder, int substep, double dt) { return rk_sub_dt(rkorder, substep, dt); }
+mhh_double mhh_rk_sub_dt(int rkorder, int substep, mhh_double dt) { return rk_sub_dt(rkorder, substep, dt); }
 
 // ---------------------------------------------------------------- peer-memory data path of the y-slab decomposition
 int mhh_peer_alloc(mhh_ctx* c, unsigned long long bytes, void** ptr)

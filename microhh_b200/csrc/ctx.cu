@@ -1,6 +1,7 @@
 // Context creation: grid dimensions (Grid::init, src/grid.cxx:106-189) and vertical metrics
 // (Grid::calculate, src/grid.cxx:237-368) computed on the host exactly as the reference does,
 // then uploaded once.  y-slab decomposition: npx = 1, jmax = jtot/npy (src/grid.cxx:142-150).
+#include "sys.h"
 #include <cstring>
 
 #include "ctx.h"
@@ -163,8 +164,8 @@ int ctx_alloc_scratch(Ctx* c)
     const size_t nred = (size_t)gd.kcells + 64;
     MHH_CUDA_CHECK(cudaMalloc(&c->max_bits_d, sizeof(unsigned long long) * 8));
     MHH_CUDA_CHECK(cudaMemset(c->max_bits_d, 0, sizeof(unsigned long long) * 8));
-    MHH_CUDA_CHECK(cudaMalloc(&c->sum_d, sizeof(double) * nred));
-    MHH_CUDA_CHECK(cudaMallocHost(&c->host_pinned, sizeof(double) * nred));
+    MHH_CUDA_CHECK(cudaMalloc(&c->sum_d, sizeof(mhh_f64) * nred));
+    MHH_CUDA_CHECK(cudaMallocHost(&c->host_pinned, sizeof(mhh_f64) * nred));
     return MHH_OK;
 }
 

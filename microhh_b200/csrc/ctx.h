@@ -4,6 +4,7 @@
 // owned by the host model and arrive as device pointers.
 #pragma once
 
+#include "sys.h"
 #include <string>
 #include <vector>
 
@@ -48,9 +49,9 @@ struct Ctx
     bool lazy_tend = false;
     const double* fresh_uvw[3] = {nullptr, nullptr, nullptr};
     const double* fresh_s[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    double* sum_d = nullptr;                    // kcells + 16 slots
+    mhh_f64* sum_d = nullptr;                   // kcells + 16 slots; sums are accumulated in double in either build
     double* stats_d = nullptr;                  // 2 * kcells: the mean profiles of mhh_stats_moment / mhh_stats_cov
-    double* host_pinned = nullptr;              // kcells + 16 doubles, pinned
+    mhh_f64* host_pinned = nullptr;             // kcells + 16 doubles, pinned
 
     // pressure solver
     bool pres_ready = false;

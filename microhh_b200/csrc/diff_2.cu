@@ -1,4 +1,5 @@
 // Constant-viscosity 2nd-order diffusion (src/diff_2.cxx:39-87), u/v/w fused in one launch.
+#include "sys.h"
 #include "ctx.h"
 #ifndef MHH_DIFF2_UNROLL_N
 #define MHH_DIFF2_UNROLL_N 1

@@ -5,6 +5,7 @@
 // the x and y neighbours (3 each side) come from L1/L2 (rows are contiguous in i).
 // Arithmetic keeps the reference's expression trees: three separate `at +=` terms (x, y, z), sums
 // evaluated left to right, biased bg*/tg* rows at the walls.
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

@@ -6,6 +6,7 @@
 //    Smagorinsky length cs*pow(dx*dy*dz[k], 1/3) is tabulated on the host with std::pow.
 //  - the u,v,w stress divergences are fused in one pass (diff_u :370, diff_v :472, diff_w :575).
 // Expression trees are kept term by term for FP64 parity (built with -fmad=false).
+#include "sys.h"
 #include <cmath>
 
 #include "ctx.h"
@@ -895,11 +896,10 @@ static int smag2_upload_mlen0(Ctx* c, double cs)
     // mlen0[k] = cs * pow(dx*dy*dz[k], 1/3): src/diff_smag2.cxx:192,237,282,319,346 (host std::pow, as the CPU build)
     const GridD& gd = c->gd;
     if (!c->mlen0_d) MHH_CUDA_CHECK(cudaMalloc(&c->mlen0_d, 2 * gd.kcells * sizeof(double)));
-    MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // host_pinned may still be in flight
-    double* h = c->host_pinned;
+    std::vector<double> h(gd.kcells);
     for (int k = 0; k < gd.kcells; ++k)
         h[k] = cs * std::pow(gd.dx * gd.dy * c->dz[k], 1. / 3.);
-    MHH_CUDA_CHECK(cudaMemcpyAsync(c->mlen0_d, h, gd.kcells * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    MHH_CUDA_CHECK(cudaMemcpyAsync(c->mlen0_d, h.data(), gd.kcells * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     MHH_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     c->mlen0_cs = cs;
     return MHH_OK;

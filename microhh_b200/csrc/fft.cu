@@ -11,6 +11,7 @@
 //   A_k = (Z_k + conj(Z_{n-k}))/2,   B_k = (Z_k - conj(Z_{n-k}))/(2i).
 // A CTA transforms `lines` consecutive lines; for strided (y) transforms consecutive threads
 // touch consecutive lines so global accesses stay coalesced along i.
+#include "sys.h"
 #include <cmath>
 
 #include "ctx.h"
@@ -256,10 +257,10 @@ int fft_plan_create(FftPlan* p, int n)
         while (m % r == 0 && p->nfac < 20) { p->fac[p->nfac++] = r; m /= r; }
     if (m != 1) return MHH_ERR_UNSUPPORTED;   // prime factor > 13
     std::vector<double2> tw(n);
-    const long double pi = std::acos(-1.0L);
+    const mhh_f80 pi = std::acos(-1.0L);
     for (int k = 0; k < n; ++k)
     {
-        const long double ang = -2.0L * pi * (long double)k / (long double)n;
+        const mhh_f80 ang = -2.0L * pi * (mhh_f80)k / (mhh_f80)n;
         tw[k] = make_double2((double)std::cos(ang), (double)std::sin(ang));
     }
     MHH_CUDA_CHECK(cudaMalloc(&p->tw, sizeof(double2) * n));

@@ -1,5 +1,6 @@
 // Batched real <-> half-complex line FFTs (fft.cu).
 #pragma once
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

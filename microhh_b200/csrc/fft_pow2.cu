@@ -13,6 +13,7 @@
 //     straight from registers (the backward pass scatters into the ghost-celled pressure field);
 //     strided (y) transforms stage a [n][line] tile through the same buffer so that global
 //     accesses stay coalesced along i.
+#include "sys.h"
 #include <cmath>
 #include <vector>
 
@@ -584,7 +585,7 @@ int fft_pow2_plan(FftPlan* p)
     if (m == 2) { p->p2_rad[nst++] = 2; m = 1; }
     p->p2_nst = nst;
     std::vector<double2> tw;
-    const long double pi = std::acos(-1.0L);
+    const mhh_f80 pi = std::acos(-1.0L);
     int ns = 1;
     for (int s = 0; s < nst; ++s)
     {
@@ -593,7 +594,7 @@ int fft_pow2_plan(FftPlan* p)
         for (int r = 1; r < R; ++r)
             for (int k = 0; k < ns; ++k)
             {
-                const long double ang = -2.0L * pi * (long double)k * (long double)r / ((long double)ns * R);
+                const mhh_f80 ang = -2.0L * pi * (mhh_f80)k * (mhh_f80)r / ((mhh_f80)ns * R);
                 tw.push_back(make_double2((double)std::cos(ang), (double)std::sin(ang)));
             }
         ns *= R;

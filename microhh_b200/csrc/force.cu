@@ -7,6 +7,7 @@
 // 48 B/pt (Coriolis, u and v in one pass).  Per-level scalars (sigma(z), the source profiles) live in small device tables;
 // the sponge strength sigma*((z-zstart)/(zsize-zstart))^beta is evaluated ONCE on the host with std::pow, as the CPU
 // reference does per level (src/buffer.cxx:49), so the table holds the reference's own values.
+#include "sys.h"
 #include <cmath>
 
 #include "ctx.h"

@@ -5,6 +5,7 @@
 // (reference: src/grid.cxx:153-166, src/advec_2.cxx:69).
 #pragma once
 
+#include "sys.h"
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -133,13 +134,14 @@ __device__ __forceinline__ void block_max_bits(unsigned long long v, unsigned lo
     }
 }
 
-// Deterministic block sum (fixed tree order) of doubles; result valid in thread 0.
-__device__ __forceinline__ double block_sum(double v)
+// Deterministic block sum (fixed tree order) of doubles — mhh_f64 in the single-precision build too: the reference
+// accumulates its means in `double` for TF = float (src/field3d_operators.cxx:53,139); result valid in thread 0.
+__device__ __forceinline__ mhh_f64 block_sum(mhh_f64 v)
 {
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
         v += __shfl_down_sync(0xffffffffu, v, o);
-    __shared__ double warp_sum[32];
+    __shared__ mhh_f64 warp_sum[32];
     const int tid = threadIdx.x + threadIdx.y * blockDim.x;
     const int nwarps = (blockDim.x * blockDim.y + 31) >> 5;
     if ((tid & 31) == 0) warp_sum[tid >> 5] = v;
@@ -181,18 +183,25 @@ __device__ __forceinline__ void prefetch_l2(const void* p)
 // the ~20-instruction IEEE division sequence.  Used where a quotient feeds an iterative solve, not a compared tendency.
 __device__ __forceinline__ double fast_rcp(const double x)
 {
+#ifdef MHH_F32
+    return 1.f / x;
+#else
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
     double e = fma(-x, r, 1.);
     r = fma(r, e, r);
     e = fma(-x, r, 1.);
     return fma(r, e, r);
+#endif
 }
 
 // sqrt(x) to within ~1 ulp for normal, positive x: hardware seed (rsqrt.approx) + two Newton steps on 1/sqrt(x) and one
 // correction of the root, instead of the IEEE sqrt sequence.
 __device__ __forceinline__ double fast_sqrt(const double x)
 {
+#ifdef MHH_F32
+    return sqrtf(x);
+#else
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
     const double hx = 0.5 * x;
@@ -200,6 +209,7 @@ __device__ __forceinline__ double fast_sqrt(const double x)
     y = fma(y, fma(-hx * y, y, 0.5), y);
     const double s = x * y;
     return fma(0.5 * y, fma(-s, s, x), s);        // s += (x - s^2) y / 2
+#endif
 }
 
 // ---- asynchronous staging of ghost-celled (i,j) tiles into shared memory ---------------------------------------------
@@ -210,7 +220,11 @@ __device__ __forceinline__ double fast_sqrt(const double x)
 __device__ __forceinline__ void cp_async8(double* smem, const double* g)
 {
     const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+#if MHH_REAL_BYTES == 8
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(s), "l"(g) : "memory");
+#else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(s), "l"(g) : "memory");
+#endif
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template<int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }

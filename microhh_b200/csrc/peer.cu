@@ -14,6 +14,7 @@
 //   data  : "my rows for this epoch are in your ghost rows"
 // A rank writes its flags INTO THE NEIGHBOUR'S arena (slots from_south / from_north) and spins only on its own memory.
 // Spins give up after ~20 s (clock64) and raise the arena's error word, so a lost peer cannot hang the GPU.
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

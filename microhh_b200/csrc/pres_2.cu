@@ -8,6 +8,7 @@
 //   backward: y then x half-complex->real, normalised; the x pass scatters straight into the
 //             ghost-celled p (replaces the copy loop :340-348)
 //   output  : bottom Neumann ghost row, cyclic halos, ut/vt/wt -= grad p                 (:352-387)
+#include "sys.h"
 #include <cmath>
 #ifndef MHH_PRES_OUT_UNROLL_N
 #define MHH_PRES_OUT_UNROLL_N 1

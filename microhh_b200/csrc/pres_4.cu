@@ -12,6 +12,7 @@
 // rows and y go to HBM, and the backward substitution streams them back.  The four boundary rows never leave
 // registers.  All rows use the reference's general elimination formulas; on the rows where the reference
 // drops terms the dropped operands are exact zeros, so the results are the same to the last bit.
+#include "sys.h"
 #include <cmath>
 #ifndef MHH_PRES_OUT_UNROLL_N
 #define MHH_PRES_OUT_UNROLL_N 1

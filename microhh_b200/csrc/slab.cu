@@ -6,6 +6,7 @@
 // Layouts (i fastest):  X = [k][j < jmax][i < itot]   (this rank's slab, ghost-free)
 //                       Y = [k][j < jtot][ii < iblock] (this rank's block of x wavenumbers, all y)
 //                       chunk for peer r: [k][j < jmax][ii < iblock], chunks ordered by r.
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

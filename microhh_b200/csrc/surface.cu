@@ -8,6 +8,7 @@
 //
 // Not bit-exact by construction: log/pow/exp come from the CUDA math library instead of glibc (<= 2 ulp each); parity is
 // checked at 1e-12 relative in tests/test_gpu_surface.py.
+#include "sys.h"
 #include <cmath>
 #include <vector>
 

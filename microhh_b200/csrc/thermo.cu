@@ -1,6 +1,7 @@
 // Thermo_dry pieces that sit inside the dynamical-core substep:
 // buoyancy tendency on w (src/thermo_dry.cxx:165-198) and N2 = g/thref * dth/dz (:66-79), the
 // stability input of Diff_smag2::exec_viscosity (src/diff_smag2.cxx:1143).
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh

@@ -3,6 +3,7 @@
 // instead of the reference's launch per field (src/timeloop.cu:138-183).
 // CPU semantics are kept: after the last substep EVERY cell of the tendency (ghosts too) is zeroed
 // (src/timeloop.cxx:268-273), otherwise only interior tendencies are rescaled.
+#include "sys.h"
 #include "ctx.h"
 
 namespace mhh
@@ -17,7 +18,7 @@ namespace
     };
 
     __global__ void __launch_bounds__(256)
-    rk_kernel(const FieldTable tab, const double cB_dt, const double cA_next, const int zero_all, const GridD gd)
+    rk_kernel(const FieldTable tab, const mhh_f64 cB_dt, const double cA_next, const int zero_all, const GridD gd)
     {
         double* __restrict__ a = tab.a[blockIdx.y];
         double* __restrict__ at = tab.at[blockIdx.y];
@@ -39,22 +40,22 @@ namespace
     }
 }  // namespace
 
-static const double rk3_cA[] = {0., -5. / 9., -153. / 128.};
-static const double rk3_cB[] = {1. / 3., 15. / 16., 8. / 15.};
-static const double rk4_cA[] = {
+static const mhh_f64 rk3_cA[] = {0., -5. / 9., -153. / 128.};
+static const mhh_f64 rk3_cB[] = {1. / 3., 15. / 16., 8. / 15.};
+static const mhh_f64 rk4_cA[] = {
     0.,
     -567301805773. / 1357537059087.,
     -2404267990393. / 2016746695238.,
     -3550918686646. / 2091501179385.,
     -1275806237668. / 842570457699.};
-static const double rk4_cB[] = {
+static const mhh_f64 rk4_cB[] = {
     1432997174477. / 9575080441755.,
     5161836677717. / 13612068292357.,
     1720146321549. / 2090206949498.,
     3134564353537. / 4481467310338.,
     2277821191437. / 14882151754819.};
 
-double rk_sub_dt(int rkorder, int substep, double dt)
+mhh_f64 rk_sub_dt(int rkorder, int substep, mhh_f64 dt)
 {
     return (rkorder == 3 ? rk3_cB[substep] : rk4_cB[substep]) * dt;
 }
@@ -69,15 +70,16 @@ void rk_coefs(int rkorder, int substep, double dt, double* cB_dt, double* cA_nex
     *zero_all = substepn == 0;
 }
 
-int rk_substep(Ctx* c, int rkorder, int substep, double dt, int nfields, double* const* a, double* const* at)
+int rk_substep(Ctx* c, int rkorder, int substep, mhh_f64 dt, int nfields, double* const* a, double* const* at)
 {
     if ((rkorder != 3 && rkorder != 4) || substep < 0 || substep >= (rkorder == 3 ? 3 : 5))
         return MHH_ERR_ARG;
     const GridD& gd = c->gd;
     const int nsub = rkorder == 3 ? 3 : 5;
     const int substepn = (substep + 1) % nsub;
-    // cB[substep]*dt is formed first, then multiplied by at: (cB*dt)*at as in the reference expression
-    const double cB_dt = (rkorder == 3 ? rk3_cB[substep] : rk4_cB[substep]) * dt;
+    // cB[substep]*dt is formed first, then multiplied by at: (cB*dt)*at as in the reference expression; in double for
+    // TF = float too (rk3_g / rk4_g take `double dt`, src/timeloop.cu:35,74)
+    const mhh_f64 cB_dt = (rkorder == 3 ? rk3_cB[substep] : rk4_cB[substep]) * dt;
     const double cA_next = rkorder == 3 ? rk3_cA[substepn] : rk4_cA[substepn];
     for (int f0 = 0; f0 < nfields; f0 += MAXF)
     {

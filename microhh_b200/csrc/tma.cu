@@ -1,4 +1,5 @@
 // Host side of tma.cuh: tensor-map encoding through the driver entry point (no link-time dependency on libcuda).
+#include "sys.h"
 #include "ctx.h"
 #include "tma.cuh"
 
@@ -26,6 +27,9 @@ namespace
 
 bool tma_planes_supported(const Ctx* c, const int boxx)
 {
+#ifdef MHH_F32
+    return false;     // 4-byte elements: a 34-wide box row is 136 bytes, not a multiple of 16 -> the cp.async path
+#endif
     const GridD& gd = c->gd;
     // the box of tile t starts at element t*TX + igc - 1 of a row: kept 16-byte aligned (odd igc, even TX) — with igc = 2 the
     // copies raised "illegal instruction" on B200 (r02f), so such grids take the cp.async path

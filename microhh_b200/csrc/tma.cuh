@@ -10,6 +10,7 @@
 // destinations.
 #pragma once
 
+#include "sys.h"
 #include <cuda.h>
 
 #include "mhh_common.cuh"

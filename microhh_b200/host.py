@@ -103,16 +103,21 @@ class Grid:
     """Grid / Grid_data (include/grid.h:50-135). ``settings`` holds the [grid] keys of the .ini."""
 
     def __init__(self, itot, jtot, ktot, xsize, ysize, zsize, z, swspatialorder="2", gc=(0, 0, 0),
-                 npy=1, rank_y=0, device=None, peer_arena=False):
+                 npy=1, rank_y=0, device=None, peer_arena=False, precision="f64"):
+        """precision: "f64" (the reference's default build) or "f32" (its -DUSESP build: the `_f32` symbol set of the library,
+        every field and profile in float; time steps stay double)."""
         if not torch.cuda.is_available():
             raise L.MhhError("microhh_b200 needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
-        self.lib = L.load()
+        self.precision = precision
+        self.lib = L.Api(precision)
+        self.dtype = torch.float64 if precision == "f64" else torch.float32
+        self.npdtype = np.float64 if precision == "f64" else np.float32
         order = int(swspatialorder)
         if order not in (2, 4):
             raise L.MhhError(f"{swspatialorder} is an illegal value for swspatialorder")
-        d = L.GridDesc(itot, jtot, ktot, gc[0], gc[1], gc[2], xsize, ysize, zsize, order, npy, rank_y)
-        z = np.ascontiguousarray(z, dtype=np.float64)
+        d = self.lib.GridDesc(itot, jtot, ktot, gc[0], gc[1], gc[2], xsize, ysize, zsize, order, npy, rank_y)
+        z = np.ascontiguousarray(z, dtype=self.npdtype)
         assert z.shape == (ktot,)
         self.ctx = C.c_void_p()
         with torch.cuda.device(self.device):
@@ -138,16 +143,17 @@ class Grid:
         self.arena = None
         if peer_arena:
             nfree = self.imax * self.jmax * self.kmax
-            self.arena = PeerArena(self, 8 * (16 * self.ncells + 3 * nfree + 96 * self.ijcells) + (8 << 20))
+            esize = 8 if precision == "f64" else 4
+            self.arena = PeerArena(self, esize * (16 * self.ncells + 3 * nfree + 96 * self.ijcells) + (8 << 20))
 
     def metric(self, name):
-        a = np.zeros(self.kcells)
+        a = np.zeros(self.kcells, dtype=self.npdtype)
         L.check(self.ctx, self.lib.mhh_get_metric(self.ctx, name.encode(), a.ctypes.data_as(C.c_void_p)), "mhh_get_metric")
         return a
 
     def set_rhoref(self, rhoref, rhorefh):
-        rhoref = np.ascontiguousarray(rhoref, dtype=np.float64)
-        rhorefh = np.ascontiguousarray(rhorefh, dtype=np.float64)
+        rhoref = np.ascontiguousarray(rhoref, dtype=self.npdtype)
+        rhorefh = np.ascontiguousarray(rhorefh, dtype=self.npdtype)
         assert rhoref.shape == (self.kcells,) and rhorefh.shape == (self.kcells,)
         L.check(self.ctx, self.lib.mhh_set_rhoref(self.ctx, rhoref.ctypes.data_as(C.c_void_p),
                                                   rhorefh.ctypes.data_as(C.c_void_p)), "mhh_set_rhoref")
@@ -169,12 +175,12 @@ class Grid:
         return {keys[i]: (ms[i], int(cnt[i])) for i in range(min(n, len(keys)))}
 
     def zeros(self):
-        t = self.arena.alloc(self.shape) if self.arena is not None else None
-        return t if t is not None else torch.zeros(self.shape, dtype=torch.float64, device=self.device)
+        t = self.arena.alloc(self.shape, self.dtype) if self.arena is not None else None
+        return t if t is not None else torch.zeros(self.shape, dtype=self.dtype, device=self.device)
 
     def zeros2d(self):
-        t = self.arena.alloc(self.shape2d) if self.arena is not None else None
-        return t if t is not None else torch.zeros(self.shape2d, dtype=torch.float64, device=self.device)
+        t = self.arena.alloc(self.shape2d, self.dtype) if self.arena is not None else None
+        return t if t is not None else torch.zeros(self.shape2d, dtype=self.dtype, device=self.device)
 
     def close(self):
         if getattr(self, "ctx", None):
@@ -198,7 +204,7 @@ class Field3d:
     def __init__(self, grid: Grid, name: str, visc: float = 0.0):
         self.name, self.visc = name, visc
         self.fld = grid.zeros()
-        self.fld_mean = torch.zeros(grid.kcells, dtype=torch.float64, device=self.fld.device)   # Field3d::fld_mean
+        self.fld_mean = torch.zeros(grid.kcells, dtype=grid.dtype, device=self.fld.device)   # Field3d::fld_mean
         self.fld_bot, self.fld_top = grid.zeros2d(), grid.zeros2d()
         self.grad_bot, self.grad_top = grid.zeros2d(), grid.zeros2d()
         self.flux_bot, self.flux_top = grid.zeros2d(), grid.zeros2d()
@@ -229,20 +235,20 @@ class Fields:
         if not self.calc_mean_profs:
             return
         g = self.grid
-        prof = np.zeros(g.kcells)
+        prof = np.zeros(g.kcells, dtype=g.npdtype)
         if self.comm is not None and self.comm.world > 1:
             # calc_mean_profile on MPI: per-rank level sums, master.sum, then the division (src/field3d_operators.cxx:46-66)
             flds = list(self.ap.values())
-            sums = np.zeros((len(flds), g.kcells))
+            sums = np.zeros((len(flds), g.kcells), dtype=g.npdtype)
             for q, fld in enumerate(flds):
                 L.check(g.ctx, g.lib.mhh_level_sums(g.ctx, L.ptr(fld.fld), sums[q].ctypes.data_as(C.c_void_p)), "mhh_level_sums")
             tot = self.comm.allreduce_sum(sums, g.device).reshape(len(flds), g.kcells) / (g.itot * g.jtot)
             for q, fld in enumerate(flds):
-                fld.fld_mean.copy_(tot[q])
+                fld.fld_mean.copy_(tot[q].to(g.dtype))
             return
         for fld in self.ap.values():
             L.check(g.ctx, g.lib.mhh_mean_profile(g.ctx, L.ptr(fld.fld), prof.ctypes.data_as(C.c_void_p)), "mhh_mean_profile")
-            fld.fld_mean.copy_(torch.from_numpy(prof))
+            fld.fld_mean.copy_(torch.from_numpy(prof))       # prof has the working type
 
     def init_prognostic_field(self, name, visc):
         self.sp[name] = Field3d(self.grid, name, visc)
@@ -261,7 +267,7 @@ class Fields:
         return {**self.mt, **self.st}
 
     def set_rhoref(self, rhoref, rhorefh):
-        self.rhoref, self.rhorefh = np.asarray(rhoref, dtype=np.float64), np.asarray(rhorefh, dtype=np.float64)
+        self.rhoref, self.rhorefh = np.asarray(rhoref, dtype=self.grid.npdtype), np.asarray(rhorefh, dtype=self.grid.npdtype)
         self.grid.set_rhoref(self.rhoref, self.rhorefh)
 
     # Fields::check_momentum/tke/mass, src/fields.cxx:1175-1217
@@ -290,7 +296,7 @@ class Field3d_operators:
         self.grid = grid
 
     def calc_mean_profile(self, fld):
-        prof = np.zeros(self.grid.kcells)
+        prof = np.zeros(self.grid.kcells, dtype=self.grid.npdtype)
         L.check(self.grid.ctx, self.grid.lib.mhh_mean_profile(self.grid.ctx, L.ptr(fld), prof.ctypes.data_as(C.c_void_p)),
                 "mhh_mean_profile")
         return prof
@@ -325,21 +331,21 @@ class Stats:
 
     def calc_mean(self, fld):
         g = self.grid
-        prof = np.zeros(g.kcells)
+        prof = np.zeros(g.kcells, dtype=g.npdtype)
         L.check(g.ctx, g.lib.mhh_stats_mean(g.ctx, L.ptr(fld), prof.ctypes.data_as(C.c_void_p)), "mhh_stats_mean")
         return self._reduce(prof)
 
     def calc_moment(self, fld, fld_mean, power, offset=0.):
         g = self.grid
-        prof, mean = np.zeros(g.kcells), np.ascontiguousarray(fld_mean, dtype=np.float64)
+        prof, mean = np.zeros(g.kcells, dtype=g.npdtype), np.ascontiguousarray(fld_mean, dtype=g.npdtype)
         L.check(g.ctx, g.lib.mhh_stats_moment(g.ctx, L.ptr(fld), mean.ctypes.data_as(C.c_void_p), C.c_double(offset), int(power),
                                               prof.ctypes.data_as(C.c_void_p)), "mhh_stats_moment")
         return self._reduce(prof)
 
     def calc_cov(self, fld1, mean1, fld2, mean2, pow1=1, pow2=1, offset1=0., offset2=0.):
         g = self.grid
-        prof = np.zeros(g.kcells)
-        m1, m2 = np.ascontiguousarray(mean1, dtype=np.float64), np.ascontiguousarray(mean2, dtype=np.float64)
+        prof = np.zeros(g.kcells, dtype=g.npdtype)
+        m1, m2 = np.ascontiguousarray(mean1, dtype=g.npdtype), np.ascontiguousarray(mean2, dtype=g.npdtype)
         L.check(g.ctx, g.lib.mhh_stats_cov(g.ctx, L.ptr(fld1), m1.ctypes.data_as(C.c_void_p), C.c_double(offset1), int(pow1),
                                            L.ptr(fld2), m2.ctypes.data_as(C.c_void_p), C.c_double(offset2), int(pow2),
                                            prof.ctypes.data_as(C.c_void_p)), "mhh_stats_cov")
@@ -559,7 +565,7 @@ class Diff:
         names = list(f.sp)
         s = L.ptr_array([f.sp[n].fld for n in names])
         st = L.ptr_array([f.st[n].fld for n in names])
-        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        svisc = (g.lib.real * max(len(names), 1))(*[f.sp[n].visc for n in names])
         u, v, w = (L.ptr(f.mp[n].fld) for n in "uvw")
         ut, vt, wt = (L.ptr(f.mt[n].fld) for n in "uvw")
         if self.swdiff == "2":
@@ -589,7 +595,7 @@ class Diff:
         names = list(f.sp)
         s = L.ptr_array([f.sp[n].fld for n in names])
         st = L.ptr_array([f.st[n].fld for n in names])
-        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        svisc = (g.lib.real * max(len(names), 1))(*[f.sp[n].visc for n in names])
         sfb = L.ptr_array([f.sp[n].flux_bot for n in names])
         sft = L.ptr_array([f.sp[n].flux_top for n in names])
         args = (g.ctx, self._surface_model(), L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld), L.ptr(f.sd["evisc"].fld),
@@ -630,7 +636,7 @@ class Diff:
         names = list(f.sp)
         s = L.ptr_array([f.sp[n].fld for n in names])
         st = L.ptr_array([f.st[n].fld for n in names])
-        svisc = (C.c_double * max(len(names), 1))(*[f.sp[n].visc for n in names])
+        svisc = (g.lib.real * max(len(names), 1))(*[f.sp[n].visc for n in names])
         u, v, w = (L.ptr(f.mp[n].fld) for n in "uvw")
         ut, vt, wt = (L.ptr(f.mt[n].fld) for n in "uvw")
         L.check(g.ctx, g.lib.mhh_advec4_diff4_exec(g.ctx, u, v, w, ut, vt, wt, C.c_double(f.visc), len(names), s, st, svisc),
@@ -771,8 +777,8 @@ class Timeloop:
 
 def _level_profile(grid, prof, name):
     """ktot values -> device profile of kcells in the reference layout (std::rotate by kstart, src/buffer.cxx:139-141)."""
-    a = np.zeros(grid.kcells)
-    p = np.asarray(prof, dtype=np.float64)
+    a = np.zeros(grid.kcells, dtype=grid.npdtype)
+    p = np.asarray(prof, dtype=grid.npdtype)
     if p.shape != (grid.ktot,):
         raise L.MhhError(f"profile {name} must have ktot={grid.ktot} values")
     a[grid.kstart:grid.kend] = p
@@ -802,7 +808,7 @@ class Buffer:
             profs = profs or {}
             for name in fields.ap:      # w (and anything not given) relaxes to zero, src/buffer.cxx:94-96
                 self.bufferprofs[name] = (_level_profile(grid, profs[name], name) if name in profs
-                                          else torch.zeros(grid.kcells, dtype=torch.float64, device=grid.device))
+                                          else torch.zeros(grid.kcells, dtype=grid.dtype, device=grid.device))
 
     def exec(self, stats=None, skip=()):
         """`skip`: fields whose Buffer term was applied inside the fused scalar pass."""
@@ -903,9 +909,14 @@ class Force:
                                                L.ptr(self.nudgeprofs[name]), L.ptr(self.nudge_factor)), "mhh_force_nudge")
 
 
-class SurfaceArgs(C.Structure):
-    """mhh_surface_args, include/mhh_b200.h"""
-    _fields_ = ([("mbcbot", C.c_int), ("thermo", C.c_int), ("thermobc", C.c_int)]
+def _surface_args_type(real):
+    """mhh_surface_args / mhh_surface_args_f32 (the three alpha_* scalars have the working type)"""
+    class Args(C.Structure):
+        _fields_ = _SURFACE_FIELDS[:-3] + [(n, real) for n in ("alpha_m", "alpha_ch", "alpha_h")]
+    return Args
+
+
+_SURFACE_FIELDS = ([("mbcbot", C.c_int), ("thermo", C.c_int), ("thermobc", C.c_int)]
                 + [(n, C.c_void_p) for n in ("u", "v", "ubot", "vbot", "ufluxbot", "vfluxbot", "ugradbot", "vgradbot", "th",
                                              "thbot", "thgradbot", "thfluxbot", "ustar", "obuk", "nobuk", "z0m", "z0h",
                                              "dutot", "dudz", "dvdz", "dbdz")]
@@ -933,6 +944,7 @@ class Boundary_surface(Boundary):
         if self.mbcbot == L.BC_USTAR and ustar is None:
             raise L.MhhError('Item "ustar" in group "boundary" does not exist')
         self.ustarin = ustar
+        self._args_t = _surface_args_type(grid.lib.real)
         self.swconstantz0, self.swcharnock = bool(swconstantz0), bool(swcharnock)
         if self.swcharnock and self.swconstantz0:
             raise L.MhhError('"swcharnock=true" requires "swconstantz0=false"')                 # src/boundary_surface.cxx:472-473
@@ -945,8 +957,8 @@ class Boundary_surface(Boundary):
 
         def z2(v=0.):
             if np.ndim(v) == 2:
-                return torch.from_numpy(np.ascontiguousarray(v, dtype=np.float64)).to(grid.device)
-            return torch.full(grid.shape2d, float(v), dtype=torch.float64, device=grid.device)
+                return torch.from_numpy(np.ascontiguousarray(v, dtype=grid.npdtype)).to(grid.device)
+            return torch.full(grid.shape2d, float(v), dtype=grid.dtype, device=grid.device)
         # init_surface, src/boundary_surface.cxx:536-572
         self.obuk, self.ustar = z2(1e-9), z2(1e-2)
         self.dudz_mo, self.dvdz_mo, self.dbdz_mo = z2(), z2(), z2()
@@ -980,7 +992,7 @@ class Boundary_surface(Boundary):
         g, f = self.grid, self.fields
         dry = thermo is not None and thermo.get_switch() != "0"
         u, v = f.mp["u"], f.mp["v"]
-        a = SurfaceArgs()
+        a = self._args_t()
         a.mbcbot, a.thermo, a.thermobc = self.mbcbot, 1 if dry else 0, self.thermobc
         p = lambda t: t.data_ptr() if t is not None else None
         a.u, a.v = p(u.fld), p(v.fld)

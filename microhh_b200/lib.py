@@ -25,6 +25,14 @@ class GridDesc(C.Structure):
                 ("order", C.c_int), ("npy", C.c_int), ("rank_y", C.c_int)]
 
 
+class GridDescF32(C.Structure):
+    """mhh_grid_desc_f32 (include/mhh_b200_f32.h)"""
+    _fields_ = [("itot", C.c_int), ("jtot", C.c_int), ("ktot", C.c_int),
+                ("igc", C.c_int), ("jgc", C.c_int), ("kgc", C.c_int),
+                ("xsize", C.c_float), ("ysize", C.c_float), ("zsize", C.c_float),
+                ("order", C.c_int), ("npy", C.c_int), ("rank_y", C.c_int)]
+
+
 class MhhError(RuntimeError):
     pass
 
@@ -94,3 +102,86 @@ def check(ctx, err, what):
     if err != 0:
         msg = load().mhh_last_error(ctx).decode() if ctx else ""
         raise MhhError(f"{what} failed with code {err}: {msg}")
+
+
+# ---- precision-aware view of the library ------------------------------------------------------------------------------
+_PROTO = None
+
+
+def _prototypes():
+    """{function name: [parameter kind]} parsed from include/mhh_b200.h: 'real' (a `double` scalar: float in the _f32 set),
+    'f64' (`mhh_double`: always double), 'ptr' (any pointer), 'int' (everything else)."""
+    global _PROTO
+    if _PROTO is None:
+        import re
+        src = open(os.path.join(os.path.dirname(_HERE), "include", "mhh_b200.h")).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        _PROTO = {}
+        for m in re.finditer(r"\b(mhh_[A-Za-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+            kinds = []
+            for prm in m.group(2).split(","):
+                prm = prm.strip()
+                if not prm or prm == "void":
+                    continue
+                if "*" in prm:
+                    kinds.append("ptr")
+                elif re.match(r"(const\s+)?mhh_double\b", prm):
+                    kinds.append("f64")
+                elif re.match(r"(const\s+)?double\b", prm):
+                    kinds.append("real")
+                else:
+                    kinds.append("int")
+            _PROTO[m.group(1)] = kinds
+    return _PROTO
+
+
+class Api:
+    """The library as one precision sees it: ``Api("f64").mhh_xxx`` is the export itself; ``Api("f32").mhh_xxx`` calls
+    ``mhh_xxx_f32`` and adapts the arguments the double-precision host code passes: `double` scalars become float (time
+    steps, `mhh_double`, stay double) and by-reference double outputs go through a float temporary.  Arrays are the caller's
+    business: every device tensor and host array must already have the working type (Grid.dtype / Grid.npdtype)."""
+
+    def __init__(self, precision="f64"):
+        if precision not in ("f64", "f32"):
+            raise MhhError("precision must be f64 or f32")
+        self.precision, self._lib, self._cache = precision, load(), {}
+        self.real = C.c_double if precision == "f64" else C.c_float
+        self.GridDesc = GridDesc if precision == "f64" else GridDescF32
+
+    def __getattr__(self, name):
+        if not name.startswith("mhh_"):
+            raise AttributeError(name)
+        fn = self._cache.get(name)
+        if fn is None:
+            fn = self._cache[name] = self._make(name)
+        return fn
+
+    def _make(self, name):
+        if self.precision == "f64":
+            return getattr(self._lib, name)
+        raw = getattr(self._lib, name + "_f32")
+        raw.restype = getattr(self._lib, name).restype
+        kinds = _prototypes().get(name)
+        byref_t = type(C.byref(C.c_int()))
+
+        def call(*args):
+            conv, fix = [], []
+            for n, a in enumerate(args):
+                if isinstance(a, C.c_double):
+                    kind = kinds[n] if kinds and n < len(kinds) else "real"
+                    conv.append(a if kind == "f64" else C.c_float(a.value))
+                elif isinstance(a, float):
+                    kind = kinds[n] if kinds and n < len(kinds) else "real"
+                    conv.append(C.c_double(a) if kind == "f64" else C.c_float(a))
+                elif isinstance(a, byref_t) and isinstance(a._obj, C.c_double):
+                    tmp = C.c_float()
+                    conv.append(C.byref(tmp))
+                    fix.append((a._obj, tmp))
+                else:
+                    conv.append(a)
+            r = raw(*conv)
+            for dst, tmp in fix:
+                dst.value = tmp.value
+            return r
+        call.__name__ = name
+        return call

@@ -19,8 +19,8 @@ class Thermo:
         if swthermo not in ("0", "dry"):
             raise L.MhhError(f"{swthermo} is an illegal value for swthermo (this path supports 0 and dry)")
         if swthermo == "dry":
-            self.thref = np.full(grid.kcells, thref0) if thref is None else np.ascontiguousarray(thref, dtype=np.float64)
-            self.threfh = np.full(grid.kcells, thref0) if threfh is None else np.ascontiguousarray(threfh, dtype=np.float64)
+            self.thref = np.ascontiguousarray(np.full(grid.kcells, thref0) if thref is None else thref, dtype=grid.npdtype)
+            self.threfh = np.ascontiguousarray(np.full(grid.kcells, thref0) if threfh is None else threfh, dtype=grid.npdtype)
             L.check(grid.ctx, grid.lib.mhh_thermo_set_ref(grid.ctx, self.thref.ctypes.data_as(C.c_void_p),
                                                           self.threfh.ctypes.data_as(C.c_void_p)), "mhh_thermo_set_ref")
             self._n2 = grid.zeros()
@@ -49,7 +49,8 @@ class Model:
     [boundary], [fields], [time], [thermo]); the operators are selected through the same keys
     (swadvec=2/2i5/4, swdiff=smag2/2/4, swpres=2/4)."""
 
-    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None, mo=False, peer_arena=False):
+    def __init__(self, ini, z, device=None, surface=None, npy=1, rank_y=0, profs=None, mo=False, peer_arena=False,
+                 precision="f64"):
         gi = ini["grid"]
         order = str(gi.get("swspatialorder", "2"))
         swadvec = str(ini.get("advec", {}).get("swadvec", order))
@@ -57,7 +58,8 @@ class Model:
         if swadvec == "2i5":
             gc = (3, 3, 2 if ini.get("advec", {}).get("fluxlimit_list") else 1)   # src/advec_2i5.cxx:42-45
         self.grid = Grid(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z,
-                         swspatialorder=order, gc=gc, device=device, npy=npy, rank_y=rank_y, peer_arena=peer_arena)
+                         swspatialorder=order, gc=gc, device=device, npy=npy, rank_y=rank_y, peer_arena=peer_arena,
+                         precision=precision)
         fi = ini.get("fields", {})
         slist = list(fi.get("slist", []))
         th = ini.get("thermo", {})

@@ -105,7 +105,7 @@ class SlabBoundaryCyclic(Boundary_cyclic):
         self.comm = comm
         self.peer = False            # SlabModel switches it on once the arenas are connected
         n3 = grid.kcells * grid.jgc * grid.icells
-        mk = lambda n: torch.empty(n, dtype=torch.float64, device=grid.device)
+        mk = lambda n: torch.empty(n, dtype=grid.dtype, device=grid.device)
         if grid.arena is None:
             self.to_n, self.to_s, self.from_s, self.from_n = mk(n3), mk(n3), mk(n3), mk(n3)
         else:
@@ -125,7 +125,7 @@ class SlabBoundaryCyclic(Boundary_cyclic):
             return
         n = (1 if is2d else g.kcells) * g.jgc * g.icells
         if self.to_n.numel() < n:
-            mk = lambda: torch.empty(g.kcells * g.jgc * g.icells, dtype=torch.float64, device=g.device)
+            mk = lambda: torch.empty(g.kcells * g.jgc * g.icells, dtype=g.dtype, device=g.device)
             self.to_n, self.to_s, self.from_s, self.from_n = mk(), mk(), mk(), mk()
         L.check(g.ctx, g.lib.mhh_halo_ns(g.ctx, L.ptr(fld), L.ptr(self.to_n), L.ptr(self.to_s), 0, int(is2d)), "mhh_halo_ns pack")
         self.comm.halo_exchange(self.to_n[:n], self.to_s[:n], self.from_s[:n], self.from_n[:n])
@@ -145,7 +145,7 @@ class SlabBoundaryCyclic(Boundary_cyclic):
             return
         n = g.kcells * g.jgc * g.icells
         if self.to_n.numel() < n * len(flds):
-            mk = lambda: torch.empty(n * len(flds), dtype=torch.float64, device=g.device)
+            mk = lambda: torch.empty(n * len(flds), dtype=g.dtype, device=g.device)
             self.to_n, self.to_s, self.from_s, self.from_n = mk(), mk(), mk(), mk()
         seg = lambda buf, q: L.ptr(buf[q * n:(q + 1) * n])
         for q, fld in enumerate(flds):
@@ -181,13 +181,13 @@ class SlabPres(Pres):
         self.peer = False          # SlabModel switches it on once the arenas are connected
         if grid.arena is not None:
             # X: this rank's work array; R1 / R2: receive buffers the peers' forward x / inverse y transforms write into
-            self.A, self.R1, self.R2 = (grid.arena.alloc((n,)) for _ in range(3))
+            self.A, self.R1, self.R2 = (grid.arena.alloc((n,), grid.dtype) for _ in range(3))
             if self.R2 is None:
                 raise L.MhhError("peer arena too small for the pressure solver's buffers")
             self.B = self.R1
         else:
-            self.A = torch.empty(n, dtype=torch.float64, device=grid.device)
-            self.B = torch.empty(n, dtype=torch.float64, device=grid.device)
+            self.A = torch.empty(n, dtype=grid.dtype, device=grid.device)
+            self.B = torch.empty(n, dtype=grid.dtype, device=grid.device)
         self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
         self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours (nccl path)
         # how the peer path moves the all-to-all chunks.  Measured on 2 x B200 at 512^3 per GPU (r02i-r02l): fused 44.4 ms/step,
@@ -265,8 +265,8 @@ class SlabPres(Pres):
                 self._side = [torch.cuda.Stream(device=g.device), torch.cuda.Stream(device=g.device)]
             if self.a2a in ("ce", "ce_overlap"):
                 from .host import _RawCuda
-                nb = self.R1.numel() * 8
-                wrap = lambda ptr: torch.as_tensor(_RawCuda(ptr, nb), device=g.device).view(torch.float64)
+                nb = self.R1.numel() * self.R1.element_size()
+                wrap = lambda ptr: torch.as_tensor(_RawCuda(ptr, nb), device=g.device).view(g.dtype)
                 self._r1_t = [wrap(q) for q in self._r1_peers]
                 self._r2_t = [wrap(q) for q in self._r2_peers]
                 self.S = torch.empty_like(self.A)
@@ -408,14 +408,15 @@ class SlabModel(Model):
     surface layer, tendencies, Buffer, Force, pressure, RK — Model.exec_substep), with the halo fills going through the ring
     neighbours and every maximum / mean reduced over the ranks (Master::max / Master::sum)."""
 
-    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None, profs=None, mo=False, path=None):
+    def __init__(self, ini, z, device=None, rank=0, world=1, surface=None, group=None, profs=None, mo=False, path=None,
+                 precision="f64"):
         path = path or os.environ.get("MHH_SLAB_PATH", "peer")
         if path not in ("peer", "nccl"):
             raise L.MhhError("MHH_SLAB_PATH / path must be peer or nccl")
         if world > 8:
             path = "nccl"            # the peer tables hold 8 ranks (one NVSwitch box)
         super().__init__(ini, z, device=device, surface=surface, npy=world, rank_y=rank, profs=profs, mo=mo,
-                         peer_arena=(path == "peer"))
+                         peer_arena=(path == "peer"), precision=precision)
         self.comm = SlabComm(rank, world, group)
         self.fields.comm = self.comm
         self.cyclic = SlabBoundaryCyclic(self.grid, self.comm)

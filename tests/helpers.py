@@ -210,7 +210,7 @@ def run_substep_gpu(case):
     return out
 
 
-def run_substep_gpu_product(case, scalar_rk=False, limits=True):
+def run_substep_gpu_product(case, scalar_rk=False, limits=True, precision="f64"):
     """The same substep through the entry points the product path (microhh_b200.model.Model) uses: the fused viscosity pass
     with N2 from th and both dt maxima (mhh_smag2_exec_viscosity_dry[_limits]), the one-pass tendencies
     (mhh_advec2_smag2_exec[_rk]: buoyancy + advec_2 + diff_smag2, optionally the scalars' RK update) and the pressure tail
@@ -222,11 +222,11 @@ def run_substep_gpu_product(case, scalar_rk=False, limits=True):
     c = case
     dev = torch.device("cuda:0")
     g = H.Grid(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], swspatialorder=str(c["order"]),
-               gc=c["gc"], device=dev)
+               gc=c["gc"], device=dev, precision=precision)
     names = ["th"] + [f"s{n}" for n in range(1, len(c["s"]))]
     f = H.Fields(g, slist=names, visc=c["visc"], svisc=c["svisc"])
     f.set_rhoref(c["rhoref"], c["rhorefh"])
-    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=g.npdtype)).to(dev)
     f.mp["u"].fld.copy_(up(c["u"])); f.mp["v"].fld.copy_(up(c["v"])); f.mp["w"].fld.copy_(up(c["w"]))
     for n, a in zip(names, c["s"]):
         f.sp[n].fld.copy_(up(a))

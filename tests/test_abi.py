@@ -42,3 +42,17 @@ def test_rk_sub_dt_host_only():
     lib = L.load()
     assert lib.mhh_rk_sub_dt(3, 0, ctypes.c_double(3.0)) == 1.0
     assert abs(lib.mhh_rk_sub_dt(3, 2, ctypes.c_double(1.0)) - 8. / 15.) < 1e-16
+
+
+def test_f32_symbol_set():
+    """The single-precision symbol set: generated headers up to date, and every declared function exported with `_f32`."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gen_f32_header as G
+    names, body = G.generate()
+    assert open(os.path.join(ROOT, "include", "mhh_b200_f32_names.h")).read() == names, "run tools/gen_f32_header.py"
+    assert open(os.path.join(ROOT, "include", "mhh_b200_f32.h")).read() == body, "run tools/gen_f32_header.py"
+    lib = ctypes.CDLL(L.LIB_PATH)
+    missing = [s + "_f32" for s in header_symbols() if not hasattr(lib, s + "_f32")]
+    assert not missing, missing
+    assert L.Api("f32").mhh_rk_sub_dt(3, 2, 1.0) == 8. / 15.        # time steps stay double in the f32 set

@@ -27,14 +27,15 @@ def profiles(fields, ks, ke, js, je, is_, ie):
     return out
 
 
-def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=False):
+def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=False, precision="f64"):
+    """precision="f32": the GPU side runs the single-precision symbol set; the oracle stays the double-precision reference."""
     import torch
     from microhh_b200.model import Model
     from oracle.les import OracleLES
     dev = torch.device("cuda:0")
-    m = Model(ini, z, device=dev, profs=profs, mo=mo)
+    m = Model(ini, z, device=dev, profs=profs, mo=mo, precision=precision)
     g, f = m.grid, m.fields
-    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=g.npdtype)).to(dev)
     for n in "uvw":
         f.mp[n].fld.copy_(up(init[n]))
     for n in f.sp:
@@ -45,8 +46,8 @@ def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=
         if "th" in f.sp:
             f.sp["th"].flux_bot.copy_(m.surface["sfluxbot"])
         # the top fluxes are the ones Boundary::set_values derived from the top BCs (flux = -visc * grad, src/boundary.cxx:51-91)
-        surface = dict(surface, ufluxtop=f.mp["u"].flux_top.cpu().numpy(), vfluxtop=f.mp["v"].flux_top.cpu().numpy(),
-                       **({"sfluxtop": f.sp["th"].flux_top.cpu().numpy()} if "th" in f.sp else {}))
+        surface = dict(surface, ufluxtop=f.mp["u"].flux_top.double().cpu().numpy(), vfluxtop=f.mp["v"].flux_top.double().cpu().numpy(),
+                       **({"sfluxtop": f.sp["th"].flux_top.double().cpu().numpy()} if "th" in f.sp else {}))
     gi, ti, di, ai, bi, fi = ini["grid"], ini.get("time", {}), ini.get("diff", {}), ini.get("advec", {}), ini.get("boundary", {}), ini.get("fields", {})
     names = ["u", "v", "w"] + list(f.sp)
     o = OracleLES(gi["itot"], gi["jtot"], gi["ktot"], gi["xsize"], gi["ysize"], gi["zsize"], z, {n: init[n] for n in names},
@@ -65,7 +66,7 @@ def run_both(ini, z, init, nsteps, surface=None, oracle_kw=None, profs=None, mo=
         m.step()
         o.step()
         dts.append((m.timeloop.idt, o.idt))
-    got = {n: f.ap[n].fld.cpu().numpy() for n in names}
+    got = {n: f.ap[n].fld.double().cpu().numpy() for n in names}
     want = {n: o.a[n] for n in names}
     # the same observables from the Stats kernels on both sides: device profiles (mhh_stats_*) of the GPU fields, the
     # reference's calc_mean / calc_moment / calc_cov (src/stats.cxx) of the oracle's fields
