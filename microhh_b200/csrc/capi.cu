@@ -107,8 +107,9 @@ int pres_scatter(Ctx*, double*, const double*);
 int pres4_set_values(Ctx*);
 int pres4_input(Ctx*, const double*, const double*, const double*, const double*, const double*, double*, double, double*);
 int pres4_solve_spectral(Ctx*, double*);
-int pres4_output(Ctx*, double*, double*, double*, double*);
-int pres4_output_rk(Ctx*, double*, double*, double*, double*, double*, double*, double*, int, int, double);
+int pres4_output(Ctx*, double*, double*, double*, double*, bool with_ghosts = true);
+int pres4_output_rk(Ctx*, double*, double*, double*, double*, double*, double*, double*, int, int, double, bool with_ghosts = true);
+int pres4_output_ghosts(Ctx*, double*);
 int pres4_divergence_bits(Ctx*, const double*, const double*, const double*, unsigned long long*);
 
 static int read_max(Ctx* c, unsigned long long* slot, double* out)
@@ -791,8 +792,9 @@ int mhh_pres_input_to(mhh_ctx* c, const double* u, const double* v, const double
                       const double* wt, mhh_double dt, double* dst)
 {
     PRES_READY(c);
-    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
     MHH_TEND(ut); MHH_TEND(vt); MHH_TEND(wt);
+    // Pres_4::input also mirrors wt's ghost rows (src/pres_4.cxx:290-303): wt is written there
+    if (c->order == 4) return pres4_input(c, u, v, w, ut, vt, const_cast<double*>(wt), dt, dst);
     return pres2_input(c, u, v, w, ut, vt, wt, dt, dst);
 }
 // Off by default: on B200 the fused pass (1.70 ms at 512^3) only equals pres2_in (1.16) + fft_fwd_x (0.53); it moves 16 B/pt less.
@@ -835,13 +837,13 @@ int mhh_halo_ns(mhh_ctx* c, double* fld, double* north, double* south, int unpac
 int mhh_pres_solve_spectral_ws(mhh_ctx* c, double* data, double* work3d)
 {
     PRES_READY(c);
-    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    if (c->order == 4) return pres4_solve_spectral(c, data);      // the 7-band factors live in the context's own scratch
     return pres2_solve_spectral_ws(c, data, work3d);
 }
 int mhh_pres_output_stage(mhh_ctx* c, int stage, double* ut, double* vt, double* wt, double* p)
 {
     PRES_READY(c);
-    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    if (c->order == 4) return stage == 0 ? pres4_output_ghosts(c, p) : pres4_output(c, ut, vt, wt, p, false);
     return pres2_output_stage(c, stage, ut, vt, wt, p);
 }
 
@@ -866,7 +868,9 @@ int mhh_pres_output_rk(mhh_ctx* c, double* ut, double* vt, double* wt, double* p
                        int rkorder, int substep, mhh_double dt)
 {
     PRES_READY(c);
-    if (c->order != 2) return MHH_ERR_UNSUPPORTED;
+    // 4th order: p's ghost rows and halos are stage 0 of mhh_pres_output_stage; this stage also puts w's ghost rows in
+    // their Normal state (src/model.cxx:412) before the update
+    if (c->order == 4) return pres4_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt, false);
     return pres2_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
 }
 

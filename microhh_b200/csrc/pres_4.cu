@@ -380,16 +380,23 @@ int pres4_solve_spectral(Ctx* c, double* data)
     return MHH_OK;
 }
 
-// p already holds the interior (scattered by the backward x FFT); ghost rows, halos, gradient.
-int pres4_output(Ctx* c, double* ut, double* vt, double* wt, double* p)
+// stage 0 of Pres_4's tail: the two ghost rows of p at each wall (src/pres_4.cxx:508-525) and the halo fill — on a y-slab
+// rank (npy > 1) only its east/west part; the caller then exchanges the three north/south rows before the gradient stage
+int pres4_output_ghosts(Ctx* c, double* p)
 {
     const GridD& gd = c->gd;
-    {
-        dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
-        MHH_LAUNCH(c, "pres4_ghost_kernel", pres4_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
-        MHH_LAUNCH_CHECK();
-    }
-    if (int e = cyclic_exec(c, p, 2)) return e;
+    dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
+    MHH_LAUNCH(c, "pres4_ghost_kernel", pres4_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
+    MHH_LAUNCH_CHECK();
+    return cyclic_exec(c, p, 2);
+}
+
+// p already holds the interior (scattered by the backward x FFT); ghost rows, halos (with_ghosts), gradient.
+int pres4_output(Ctx* c, double* ut, double* vt, double* wt, double* p, const bool with_ghosts)
+{
+    const GridD& gd = c->gd;
+    if (with_ghosts)
+        if (int e = pres4_output_ghosts(c, p)) return e;
     Launch3 l = launch_interior(gd.imax, gd.jmax, (gd.kmax + KCHUNK - 1) / KCHUNK);
     if (gd.jtot == 1)
         MHH_LAUNCH(c, "pres4_out_kernel", (pres4_out_kernel<false><<<l.grid, l.block, 0, c->stream>>>(ut, vt, wt, p, gd)));
@@ -405,16 +412,12 @@ int ghost_cells_w_exec(Ctx* c, double* w, int type);
 // ghost rows + halos of p, then w's ghost rows in their Normal state (the reference sets them between Pres::exec and
 // Timeloop::exec, src/model.cxx:412, from the not yet updated w), then the gradient fused with the RK substep of u,v,w
 int pres4_output_rk(Ctx* c, double* ut, double* vt, double* wt, double* p, double* u, double* v, double* w,
-                    int rkorder, int substep, double dt)
+                    int rkorder, int substep, double dt, const bool with_ghosts)
 {
     if ((rkorder != 3 && rkorder != 4) || substep < 0 || substep >= (rkorder == 3 ? 3 : 5)) return MHH_ERR_ARG;
     const GridD& gd = c->gd;
-    {
-        dim3 b(128), g((gd.imax + 127) / 128, gd.jmax);
-        MHH_LAUNCH(c, "pres4_ghost_kernel", pres4_ghost_kernel<<<g, b, 0, c->stream>>>(p, gd));
-        MHH_LAUNCH_CHECK();
-    }
-    if (int e = cyclic_exec(c, p, 2)) return e;
+    if (with_ghosts)
+        if (int e = pres4_output_ghosts(c, p)) return e;
     if (int e = ghost_cells_w_exec(c, w, 0 /* MHH_BCW_NORMAL */)) return e;
     double cB_dt, cA_next; int zero_all;
     rk_coefs(rkorder, substep, dt, &cB_dt, &cA_next, &zero_all);

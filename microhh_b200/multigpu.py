@@ -170,12 +170,13 @@ class SlabBoundaryCyclic(Boundary_cyclic):
 
 
 class SlabPres(Pres):
-    """Pres_2 on y-slabs: the stage calls of the C ABI with the two all-to-alls in between."""
+    """Pres_2 / Pres_4 on y-slabs (src/pres_2.cxx:267-361, src/pres_4.cxx:320-529 with src/fft.cxx:452-583, npx = 1): the stage
+    calls of the C ABI with the two all-to-alls in between; the vertical solve (Thomas / 7-band LU) is column-local."""
 
     def __init__(self, grid, fields, swpres, comm, cyclic):
         super().__init__(grid, fields, swpres)
-        if swpres != "2":
-            raise L.MhhError("the y-slab pressure pipeline is built for swpres=2 this round")
+        if swpres not in ("2", "4"):
+            raise L.MhhError("the y-slab pressure pipeline needs swpres=2 or 4")
         self.comm, self.cyclic = comm, cyclic
         n = grid.imax * grid.jmax * grid.kmax
         self.peer = False          # SlabModel switches it on once the arenas are connected

@@ -27,6 +27,32 @@ def test_slab_world1_bit_identical(cuda_lib, dims, path, monkeypatch):
 
 
 @pytest.mark.parametrize("path", ["peer", "nccl"])
+def test_slab_world1_order4_bit_identical(cuda_lib, path, monkeypatch):
+    """The 4th-order pipeline (advec_4 + diff_4, Pres_4 with its 7-band solve, three-deep halos, uflux forcing) through the
+    slab driver's stage calls equals the single-GPU pipeline bit for bit."""
+    import torch
+    from tests.slab_parity import run
+    monkeypatch.setenv("MHH_SLAB_PATH", path)
+    out, status, ref = run(0, 1, torch.device("cuda:0"), dims=(32, 32, 24), case="dns4")
+    for k in ("u", "v", "w", "p"):
+        assert np.array_equal(out[k], ref[k]), k
+    assert status["dt"] == ref["status"]["dt"]
+
+
+@pytest.mark.parametrize("uflux", ["0", "1"], ids=["bitwise", "uflux_1e-13"])
+@pytest.mark.parametrize("path", ["peer", "nccl"])
+def test_slab_two_ranks_order4(cuda_lib, path, uflux):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29534", os.path.join(ROOT, "tests", "slab_parity.py")], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, SLAB_DIMS="64,64,32", MHH_SLAB_PATH=path, SLAB_CASE="dns4", SLAB_UFLUX=uflux))
+    print(r.stdout[-3000:], r.stderr[-2000:])
+    assert r.returncode == 0 and "SLAB PARITY OK" in r.stdout
+
+
+@pytest.mark.parametrize("path", ["peer", "nccl"])
 @pytest.mark.parametrize("dims", ["64,64,32", "32,512,8"], ids=["staged_fft", "col_fft_chunks"])
 def test_slab_two_ranks_nccl(cuda_lib, dims, path):
     import torch
