@@ -219,8 +219,8 @@ class Fields:
         for n in ("u", "v", "w"):
             self.mp[n] = Field3d(grid, n, visc)
             self.mt[n] = Field3d(grid, n + "t")
-        for n in slist:
-            self.init_prognostic_field(n, svisc)
+        for n in slist:       # svisc: one value for all scalars, or {name: value}
+            self.init_prognostic_field(n, svisc.get(n, 0.) if isinstance(svisc, dict) else svisc)
         self.sd["p"] = Field3d(grid, "p")
         self.rhoref = np.ones(grid.kcells)
         self.rhorefh = np.ones(grid.kcells)

@@ -179,14 +179,24 @@ def model_ini(inp: Input):
     ini["pres"] = dict(swpres=inp.get_item(str, "pres", "swpres", "", order))
     swthermo = inp.get_item(str, "thermo", "swthermo", "", "0")
     ini["thermo"] = dict(swthermo=swthermo)
+    if swthermo not in ("0", "dry"):
+        raise InputError(f'swthermo={swthermo} is outside this path (0 and dry are built; SURVEY 2.4)')
     if swthermo == "dry":
         ini["thermo"]["thref0"] = inp.get_item(float, "thermo", "thref0")          # src/thermo_dry.cxx:424
+        base = inp.get_item(str, "thermo", "swbasestate", "", "boussinesq")
+        if base not in ("boussinesq", "anelastic"):
+            raise InputError(f'"{base}" is an illegal value for swbasestate')       # src/thermo_dry.cxx:435-442
+        if base == "anelastic":
+            raise InputError("swbasestate=anelastic: the hydrostatic base state (rhoref, thref profiles) is computed by the "
+                             "reference's Thermo_dry::create, which is outside this path; pass rhoref / thref to Model instead")
     slist = inp.get_list(str, "fields", "slist", "", [])
     if swthermo == "dry" and "th" not in slist:
         slist = ["th"] + slist
     visc = inp.get_item(float, "fields", "visc")
     svisc = [inp.get_item(float, "fields", "svisc", s) for s in slist]
-    ini["fields"] = dict(visc=visc, svisc=svisc[0] if svisc else 0., slist=[s for s in slist if s != "th"] if swthermo == "dry" else slist)
+    # svisc is per scalar (svisc[name] falls back to svisc, src/fields.cxx): a dict when the scalars differ
+    sv = dict(zip(slist, svisc))
+    ini["fields"] = dict(visc=visc, svisc=(svisc[0] if len(set(svisc)) <= 1 and svisc else sv) if svisc else 0., slist=[s for s in slist if s != "th"] if swthermo == "dry" else slist)
     b = dict(mbcbot=inp.get_item(str, "boundary", "mbcbot"), mbctop=inp.get_item(str, "boundary", "mbctop"),
              swboundary=inp.get_item(str, "boundary", "swboundary", "", "default"))
     for k in ("ubot", "utop", "vbot", "vtop"):
@@ -194,9 +204,22 @@ def model_ini(inp: Input):
     b["sbc"] = {s: dict(sbcbot=inp.get_item(str, "boundary", "sbcbot", s), sbctop=inp.get_item(str, "boundary", "sbctop", s),
                         sbot=inp.get_item(float, "boundary", "sbot", s), stop=inp.get_item(float, "boundary", "stop", s))
                 for s in slist}
+    if inp.get_item(bool, "boundary", "swtimedep", "", False):
+        raise InputError("[boundary] swtimedep=1 (time-dependent surface values, Timedep) is outside this path: "
+                         "the surface boundary values are constant in time here")
+    if b["swboundary"] not in ("default", "surface"):
+        raise InputError(f'swboundary={b["swboundary"]} is outside this path (default and surface are built)')
     if b["swboundary"] == "surface":
-        b["z0m"] = inp.get_item(float, "boundary", "z0m", "", 0.1)
-        b["z0h"] = inp.get_item(float, "boundary", "z0h", "", 0.1)
+        b["swconstantz0"] = inp.get_item(bool, "boundary", "swconstantz0", "", True)
+        b["swcharnock"] = inp.get_item(bool, "boundary", "swcharnock", "", False)
+        if b["swconstantz0"]:
+            b["z0m"] = inp.get_item(float, "boundary", "z0m", "", 0.1)
+            b["z0h"] = inp.get_item(float, "boundary", "z0h", "", 0.1)
+        if b["swcharnock"]:
+            for k in ("alpha_m", "alpha_ch", "alpha_h"):
+                b[k] = inp.get_item(float, "boundary", k)
+        if b["mbcbot"] == "ustar":
+            b["ustar"] = inp.get_item(float, "boundary", "ustar")
     ini["boundary"] = b
     dtmax = inp.get_item(float, "time", "dtmax", "", DBIG)
     ini["time"] = dict(starttime=inp.get_item(float, "time", "starttime", "", 0.), endtime=inp.get_item(float, "time", "endtime"),
@@ -208,6 +231,9 @@ def model_ini(inp: Input):
         ini["buffer"] = dict(swbuffer=True, swupdate=inp.get_item(bool, "buffer", "swupdate", "", False),
                              zstart=inp.get_item(float, "buffer", "zstart"), sigma=inp.get_item(float, "buffer", "sigma", "", 2.),
                              beta=inp.get_item(float, "buffer", "beta", "", 2.))
+    for k in ("swtimedep_ls", "swtimedep_geo", "swtimedep_wls", "swtimedep_nudge"):
+        if inp.get_item(bool, "force", k, "", False):
+            raise InputError(f"[force] {k}=1 (time-dependent forcings, Timedep) is outside this path")
     f = dict(swlspres=inp.get_item(str, "force", "swlspres", "", "0"), swls=inp.get_item(str, "force", "swls", "", "0"),
              swwls=inp.get_item(str, "force", "swwls", "", "0"), swnudge=inp.get_item(str, "force", "swnudge", "", "0"))
     if f["swlspres"] == "uflux":

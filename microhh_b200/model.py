@@ -242,7 +242,12 @@ class Model:
         import os
         from . import io as IO
         directory = os.path.dirname(os.path.abspath(ini_path)) if directory is None else directory
-        ini = IO.model_ini(IO.Input(ini_path))
+        inp = IO.Input(ini_path)
+        ini = IO.model_ini(inp)
+        unused = inp.unused_items()             # Input::print_unused_items (src/input.cxx): keys nothing on this path reads
+        if unused:
+            import sys
+            print("microhh_b200: input items not used by the in-scope dynamical core: " + ", ".join(unused), file=sys.stderr)
         gi = ini["grid"]
         z = IO.load_grid(gi["itot"], gi["jtot"], gi["ktot"], directory=directory)["z"]
         m = cls(ini, z, device=device, surface=surface, profs=profs, mo=surface is None)

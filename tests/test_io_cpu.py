@@ -264,3 +264,24 @@ def test_ini_reader_against_the_reference_reader(tmp_path):
         if m is not None:
             assert r.error.strip() == m.strip(), (text, r.error, m)
     assert _RefInput(tmp_path / "missing.ini").error.strip().startswith('"' + str(tmp_path / "missing.ini") + '" cannot be opened')
+
+
+def test_model_ini_rejects_switches_outside_the_path():
+    """Case files whose keys this path cannot honour raise instead of running different physics silently (cases/gabls1 as
+    shipped sets swtimedep=1 for th_sbot)."""
+    base = ("[grid]\nitot=8\njtot=8\nktot=8\nxsize=1\nysize=1\nzsize=1\nswspatialorder=2\n[fields]\nvisc=1e-5\nsvisc=1e-5\n"
+            "[time]\nendtime=10\n[boundary]\nmbcbot=noslip\nmbctop=freeslip\nsbcbot=dirichlet\nsbctop=neumann\nsbot=1\nstop=0\n")
+    assert IO.model_ini(IO.Input(text=base))["boundary"]["swboundary"] == "default"
+    for extra, msg in (("swtimedep=1\n", "swtimedep=1"), ("swboundary=surface_bulk\n", "outside this path")):
+        with pytest.raises(IO.InputError, match=msg):
+            IO.model_ini(IO.Input(text=base + extra))
+    with pytest.raises(IO.InputError, match="anelastic"):
+        IO.model_ini(IO.Input(text=base + "[thermo]\nswthermo=dry\nthref0=300\nswbasestate=anelastic\n"))
+    with pytest.raises(IO.InputError, match="illegal value for swbasestate"):
+        IO.model_ini(IO.Input(text=base + "[thermo]\nswthermo=dry\nthref0=300\nswbasestate=foo\n"))
+    with pytest.raises(IO.InputError, match="swthermo=moist"):
+        IO.model_ini(IO.Input(text=base + "[thermo]\nswthermo=moist\n"))
+    with pytest.raises(IO.InputError, match="swtimedep_geo"):
+        IO.model_ini(IO.Input(text=base + "[force]\nswtimedep_geo=1\n"))
+    two = IO.model_ini(IO.Input(text=base.replace("svisc=1e-5", "svisc=1e-5\nsvisc[q]=2e-5\nslist=q,s")))
+    assert two["fields"]["svisc"] == {"q": 2e-5, "s": 1e-5}
