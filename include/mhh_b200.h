@@ -405,6 +405,14 @@ int mhh_stats_cov(mhh_ctx* ctx, const double* fld1, const double* mean1_host, do
 int mhh_mean(mhh_ctx* ctx, const double* fld, double* mean_out);
 int mhh_mean_2d(mhh_ctx* ctx, const double* fld2d, double* mean_out);
 int mhh_max(mhh_ctx* ctx, const double* fld, double* max_out);   /* calc_max_g: max over interior */
+/* No counterpart in the reference.  mhh_mean for callers that must not
+ * allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the per-level partial sums live in a
+ * file-scope static __device__ array of 4096 FP64 slots (32 KiB per GPU that loads the library, held until exit) instead of
+ * the context's cudaMalloc'ed scratch.  fld and mean_out are DEVICE pointers (mean_out: one value); the two kernels are
+ * queued on the context's stream, nothing is waited for, and no cudaMalloc / cudaFree / allocating routine is called.
+ * ktot > 4096 is rejected with MHH_ERR_ARG (mhh_last_error says so).  All calls on one device share the array: calls that
+ * overlap on the GPU race; consecutive calls on one stream do not (every slot is rewritten before it is read). */
+int mhh_mean_static(mhh_ctx* ctx, const double* fld_dev, double* mean_out_dev);
 /* Fields::check_momentum/tke/mass — src/fields.cxx:144,175,209 */
 int mhh_check_momentum(mhh_ctx* ctx, const double* u, const double* v, const double* w, double* out);
 int mhh_check_tke(mhh_ctx* ctx, const double* u, const double* v, const double* w, double* out);

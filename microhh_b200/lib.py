@@ -60,7 +60,7 @@ EXPORTS = [
     "mhh_cyclic", "mhh_cyclic_2d", "mhh_ghost_cells", "mhh_ghost_cells_w", "mhh_set_bc",
     "mhh_rk_substep", "mhh_rk_sub_dt", "mhh_pres_output_rk", "mhh_pres_exec_rk",
     "mhh_mean_profile", "mhh_level_sums", "mhh_stats_mean", "mhh_stats_moment", "mhh_stats_cov", "mhh_mean", "mhh_mean_2d", "mhh_max",
-    "mhh_check_momentum", "mhh_check_tke", "mhh_check_mass",
+    "mhh_check_momentum", "mhh_check_tke", "mhh_check_mass", "mhh_mean_static",
 ]
 
 
