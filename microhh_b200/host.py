@@ -1017,8 +1017,12 @@ class Boundary_surface(Boundary):
                 self.boundary_cyclic.exec_2d(self.z0h)
             self.boundary_cyclic.exec_2d(self._dutot)
             L.check(g.ctx, st(g.ctx, C.byref(a), 2), "mhh_boundary_surface_exec_stages 2")
-            self.boundary_cyclic.exec_2d(u.flux_bot)
-            self.boundary_cyclic.exec_2d(v.flux_bot)
+            many = getattr(self.boundary_cyclic, "exec_2d_many", None)
+            if many is not None:
+                many([u.flux_bot, v.flux_bot])           # one ring exchange for both planes on y-slabs
+            else:
+                self.boundary_cyclic.exec_2d(u.flux_bot)
+                self.boundary_cyclic.exec_2d(v.flux_bot)
             L.check(g.ctx, st(g.ctx, C.byref(a), 4), "mhh_boundary_surface_exec_stages 4")
         for name, fld in f.sp.items():
             if dry and name == "th":

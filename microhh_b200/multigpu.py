@@ -168,6 +168,19 @@ class SlabBoundaryCyclic(Boundary_cyclic):
         if g.jtot > 1:
             self._ns(fld2d, True)
 
+    def exec_2d_many(self, planes):
+        """Boundary_cyclic::exec_2d of several planes with one ring exchange on the peer path (the two momentum flux planes
+        of Boundary_surface::exec, src/boundary_surface.cxx:894-895)."""
+        g = self.grid
+        planes = list(planes)
+        if not (self.peer and g.jtot > 1):
+            for pl in planes:
+                self.exec_2d(pl)
+            return
+        for pl in planes:
+            L.check(g.ctx, g.lib.mhh_cyclic_2d(g.ctx, L.ptr(pl)), "mhh_cyclic_2d")
+        self._push(planes, True)
+
 
 class SlabPres(Pres):
     """Pres_2 / Pres_4 on y-slabs (src/pres_2.cxx:267-361, src/pres_4.cxx:320-529 with src/fft.cxx:452-583, npx = 1): the stage
@@ -191,10 +204,12 @@ class SlabPres(Pres):
             self.B = torch.empty(n, dtype=grid.dtype, device=grid.device)
         self.chunk_fft = None      # decided at the first exec (needs the solver's plans): mhh_fft_chunks_supported
         self.kranges = 4           # k ranges whose all-to-alls overlap the transforms of their neighbours (nccl path)
-        # how the peer path moves the all-to-all chunks.  Measured on 2 x B200 at 512^3 per GPU (r02i-r02l): fused 44.4 ms/step,
-        # fused_pipe 44.6, ce 45.3, ce_overlap 48.5 — the copy engines reach 763 GB/s alone (tools/bench_peer_copy.py) but only
-        # half of that next to an HBM-saturating kernel (copies 1.76 ms instead of 0.87 next to the scalar pass)
-        self.a2a = os.environ.get("MHH_SLAB_A2A", "fused")
+        # how the peer path moves the all-to-all chunks (MHH_SLAB_A2A).  Measured at 512^3 per GPU (r02y, r02v):
+        #   2 x B200: ce_overlap 44.6 ms/step, fused 45.0, fused_pipe 44.6, ce 45.3;   8 x B200: ce_overlap 49.6, nccl 50.1, fused 50.4.
+        # ce_overlap: own chunk written in place, one copy-engine transfer per peer on parallel streams while the SMs run the
+        # scalar tendency pass (which does not depend on the pressure); fused: the transforms store straight into the peers'
+        # buffers (no staging, but the NVLink-bound stores hold the SMs: fft_fwd_x 1.01 instead of 0.51 ms at N = 2).
+        self.a2a = os.environ.get("MHH_SLAB_A2A", "ce_overlap")
         self.timing = [] if os.environ.get("MHH_SLAB_TIMING") else None     # ce_overlap: CUDA events of every exchange
 
     def timing_report(self):
@@ -224,11 +239,19 @@ class SlabPres(Pres):
 
         def exchange(peers_t, hook):
             ev = mk(); ev.record(main)
-            xfer.wait_event(ev)
-            with torch.cuda.stream(xfer):
-                for d in range(world):
-                    r = (me + d) % world
+            for n, d in enumerate(range(1, world)):     # my own chunk is already in place (_ce_tables)
+                st = self._copy_streams[n % len(self._copy_streams)]
+                if n < len(self._copy_streams):
+                    st.wait_event(ev)
+                r = (me + d) % world
+                with torch.cuda.stream(st):
                     peers_t[r][me * R:(me + 1) * R].copy_(self.S[r * R:(r + 1) * R], non_blocking=True)
+            for st in self._copy_streams[:max(world - 1, 0)]:
+                if st is not xfer:
+                    e = torch.cuda.Event(); e.record(st)
+                    xfer.wait_event(e)
+            if world == 1:
+                xfer.wait_event(ev)
             ev_c = mk(); ev_c.record(xfer)
             on(xfer)
             ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
@@ -242,13 +265,29 @@ class SlabPres(Pres):
             if T:       # (send transform done, copies done, barrier done, hook done, main resumes)
                 self.timing.append((ev, ev_c, ev2, ev_h, ev_w))
 
-        ck(lib.mhh_fft_x_chunks(g.ctx, -1, X, S, None, 0, g.kmax), "fft_x fwd -> chunks")
+        t1, t2 = self._ce_tabs
+        ck(lib.mhh_fft_x_chunks_to_peers(g.ctx, X, t1, 0, g.kmax), "fft_x fwd -> chunks")
         exchange(self._r1_t, hooks[0] if hooks else None)
         ck(lib.mhh_fft_y_chunks(g.ctx, -1, R1, X, 0, g.kmax), "chunks -> fft_y fwd")
         ck(lib.mhh_pres_solve_spectral_ws(g.ctx, X, R1), "tdma")
-        ck(lib.mhh_fft_y_chunks(g.ctx, +1, X, S, 0, g.kmax), "fft_y bwd -> chunks")
+        ck(lib.mhh_fft_y_chunks_to_peers(g.ctx, X, t2, 0, g.kmax), "fft_y bwd -> chunks")
         exchange(self._r2_t, hooks[1] if hooks else None)
         ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
+
+    def _ce_tables(self):
+        """Destination tables for the sending transforms of ce_overlap (mhh_fft_*_chunks_to_peers writes segment r at
+        table[r] + rank * R): the segments for the other ranks land at S[r * R] in the local staging array, from where the
+        copy engines take them; my own segment goes straight into my receive buffer, so no local device-to-device copy
+        competes with the kernels for HBM."""
+        g = self.grid
+        world, me = self.comm.world, self.comm.rank
+        R = g.kmax * g.jmax * (g.itot // world)
+        es = self.S.element_size()
+
+        def table(recv):
+            ptrs = [recv.data_ptr() if r == me else self.S.data_ptr() + (r - me) * R * es for r in range(world)]
+            return (C.c_void_p * 8)(*(ptrs + [0] * (8 - world)))
+        return table(self.R1), table(self.R2)
 
     def _exec_peer_transforms(self, p, hooks=None):
         """Forward transforms, tridiagonal solve, inverse transforms with the all-to-alls fused into the transforms' stores
@@ -271,6 +310,11 @@ class SlabPres(Pres):
                 self._r1_t = [wrap(q) for q in self._r1_peers]
                 self._r2_t = [wrap(q) for q in self._r2_peers]
                 self.S = torch.empty_like(self.A)
+            if self.a2a == "ce_overlap":
+                # one cudaMemcpyAsync per peer, spread over a few streams so that several copy engines / NVLink ports are busy
+                ncs = max(1, int(os.environ.get("MHH_SLAB_COPY_STREAMS", "4")))
+                self._copy_streams = [self._side[0]] + [torch.cuda.Stream(device=g.device) for _ in range(ncs - 1)]
+                self._ce_tabs = self._ce_tables()
         if self.a2a == "ce_overlap":
             return self._exec_ce_overlap(p, hooks)
         for h in hooks or ():

@@ -1,5 +1,5 @@
 """Builds the committed profile summaries from one gpurun capture:
-python tools/make_profiles.py TAG   (expects gpurun_out/bench_512_TAG.json, launches_TAG.csv, prof_TAG_step.ncu-rep)"""
+python tools/make_profiles.py TAG   (expects gpurun_out/bench_512_TAG.json or bench_TAG.json, launches_TAG.csv, prof_TAG_step.ncu-rep)"""
 import collections, csv, json, re, subprocess, sys
 tag = sys.argv[1]
 rep = f"gpurun_out/prof_{tag}_step.ncu-rep"
@@ -36,7 +36,7 @@ if os.path.exists(rep):
         elif "fft_pow2_kernel<1, 0" in kn: key = "fft_bwd_x"
         if key: t[key] = v
     json.dump({"n": 512, "source": f"profiles/{tag}_ncu_full_step512_summary.txt (ncu --set full --clock-control none, one RK substep of bench.py at 512^3)",
-               "gb_per_launch": t}, open("profiles/r01_traffic.json", "w"), indent=1)
+               "gb_per_launch": t}, open(f"profiles/{tag[:3]}_traffic.json", "w"), indent=1)
 # 3. launch list + summary
 src = f"gpurun_out/launches_{tag}.csv"
 open(f"profiles/{tag}_ncu_launches_bench512.csv", "w").write(open(src).read())
@@ -53,5 +53,6 @@ lines = ["# ncu --metrics gpu__time_duration.sum --clock-control none -c 400, py
 for k, (c, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     lines.append("%-72s %4d %10.3f %9.4f %7.4f" % (k, c, ms, ms / c, ms / tot))
 open(f"profiles/{tag}_ncu_launches_bench512_summary.txt", "w").write("\n".join(lines) + "\n")
-open(f"profiles/{tag}_bench_512.json", "w").write(open(f"gpurun_out/bench_512_{tag}.json").read())
+bsrc = f"gpurun_out/bench_512_{tag}.json" if os.path.exists(f"gpurun_out/bench_512_{tag}.json") else f"gpurun_out/bench_{tag}.json"
+open(f"profiles/{tag}_bench_512.json", "w").write(open(bsrc).read())
 print(summ); print("\n".join(lines[:16])); print(t)
