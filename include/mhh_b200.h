@@ -352,6 +352,20 @@ int mhh_peer_error(mhh_ctx* ctx, int* err);    /* 1 after a flag wait timed out 
  * with mhh_peer_barrier before the receiving transform (mhh_fft_y_chunks dir < 0 / mhh_fft_x_chunks dir > 0) reads. */
 int mhh_fft_x_chunks_to_peers(mhh_ctx* ctx, const double* in, double* const* peer_out, int k0, int nk);
 int mhh_fft_y_chunks_to_peers(mhh_ctx* ctx, const double* in, double* const* peer_out, int k0, int nk);
+/* The solver's transforms on kx SUB-BLOCKS of a rank's block (nsub per rank, ib = iblock / nsub columns each; nsub divides
+ * iblock, ranks * nsub <= 32), so that the y transforms and the vertical solve of sub-block b run while the copy engines move
+ * sub-blocks b+1 (forward) and b-1 (return) — Pres_2::solve (src/pres_2.cxx:267-349) stops being a join between the two
+ * transposes (src/transpose.cxx:163-217).  Segment v = r * nsub + b of an x line (rank r's sub-block b) is
+ * [k][j < jmax][ii < ib], Rb = kmax * jmax * ib elements; a receive buffer holds segment v (v over the source ranks) at v * Rb;
+ * Y_b = [k][j < jtot][ii < ib] sits at b * kmax * jtot * ib of the Y array.
+ *   x_fwd : X -> segments, segment v of every line written at segptrs[v] (v < ranks * nsub: staging array or a buffer itself)
+ *   y_fwd : the received segments of sub-block b -> Y_b            solve : Thomas sweep of Y_b (Pres_2; work >= Y_b / 16 + a plane)
+ *   y_bwd : Y_b -> segments by destination rank r at segptrs[r]     x_bwd : all received segments -> the ghost-celled p */
+int mhh_slab_fft_x_fwd_sub(mhh_ctx* ctx, const double* in_X, double* const* segptrs, int nsub);
+int mhh_slab_fft_y_fwd_sub(mhh_ctx* ctx, const double* in_segments, double* out_Y, int b, int nsub);
+int mhh_slab_solve_sub(mhh_ctx* ctx, double* Y, double* work, int b, int nsub);
+int mhh_slab_fft_y_bwd_sub(mhh_ctx* ctx, const double* in_Y, double* const* segptrs, int b, int nsub);
+int mhh_slab_fft_x_bwd_sub(mhh_ctx* ctx, const double* in_segments, double* p, int nsub);
 int mhh_transpose_copy(mhh_ctx* ctx, int mode, double* dst, const double* src);
 int mhh_pres_solve_spectral_ws(mhh_ctx* ctx, double* data_Y, double* work3d);
 int mhh_pres_output_stage(mhh_ctx* ctx, int stage, double* ut, double* vt, double* wt, double* p);
@@ -389,6 +403,11 @@ int mhh_pres_output_rk(mhh_ctx* ctx, double* ut, double* vt, double* wt, double*
                        int rkorder, int substep, mhh_double dt);
 int mhh_pres_exec_rk(mhh_ctx* ctx, double* u, double* v, double* w, double* ut, double* vt, double* wt, double* p,
                      mhh_double dt_sub, int rkorder, int substep, mhh_double dt);
+/* One-shot: the next mhh_pres_exec_rk makes its stream wait for `cuda_event` (a cudaEvent_t) right before the kernel that
+ * updates u, v, w — so that independent work issued on ANOTHER stream that still reads the old velocities (the scalars'
+ * tendency + RK pass, which Model::exec orders before Pres::exec, src/model.cxx:388-411) may overlap the solver's input,
+ * transforms and vertical solve.  The caller records the event on that other stream after the work. */
+int mhh_pres_set_output_wait(mhh_ctx* ctx, void* cuda_event);
 mhh_double mhh_rk_sub_dt(int rkorder, int substep, mhh_double dt);   /* Timeloop::get_sub_time_step :415 */
 
 /* --- Field3d_operators<TF> (include/field3d_operators.h:40-51) and Fields diagnostics -------------------- */

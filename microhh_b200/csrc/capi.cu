@@ -249,6 +249,71 @@ static int fft_y_chunks(Ctx* c, int dir, const double* in, double* out, int k0, 
     return fft_lines(c, c->plan_j, dir, in, out, L);
 }
 
+// ---- the same four transforms on kx SUB-BLOCKS of a rank's block (nsub per rank, ib = iblock / nsub columns each), so that
+// the y transforms and the vertical solve of sub-block b run while the copy engines move sub-blocks b+1 (forward) and b-1
+// (return): the solve stops being a join between the two all-to-alls.  Segment v = r * nsub + b of a line (rank r's
+// sub-block b) is [k][j < jmax][ii < ib], Rb = kmax * jmax * ib elements; in the receive / staging buffers segment v sits at
+// v * Rb (v counted over the SOURCE ranks on the receiving side).  Y_b = [k][j < jtot][ii < ib] at b * kmax * jtot * ib.
+static int sub_check(Ctx* c, int nsub, int b)
+{
+    if (nsub < 1 || c->iblock % nsub != 0 || c->npy * nsub > FFT_SEGTAB || b < 0 || b >= nsub)
+    { c->last_error = "kx sub-blocks: nsub must divide iblock, ranks * nsub <= 32, 0 <= b < nsub"; return MHH_ERR_ARG; }
+    return MHH_OK;
+}
+static void ptr_segtab(FftLayout& L, double* const* ptrs, int n)
+{
+    L.use_segtab_out = true;
+    for (int v = 0; v < n; ++v) L.segtab_out[v] = (long)(ptrs[v] - ptrs[0]);
+}
+// X -> segments; segptrs[v], v < ranks * nsub: where segment v of every line goes (staging array, or straight into a buffer)
+static int fft_x_fwd_sub(Ctx* c, const double* in, double* const* segptrs, int nsub)
+{
+    const GridD& gd = c->gd;
+    const int ib = c->iblock / nsub;
+    FftLayout L;
+    L.nlines = gd.jmax * gd.kmax; L.scale = 1.;
+    L.n1 = L.nlines; L.s1 = gd.itot; L.s2 = 0; L.sn = 1; L.base_in = 0;
+    L.n1o = L.nlines; L.s1o = ib; L.s2o = 0; L.sno = 1; L.esplit_out = ib; L.eseg_out = (long)gd.kmax * gd.jmax * ib; L.base_out = 0;
+    ptr_segtab(L, segptrs, c->npy * nsub);
+    return fft_lines(c, c->plan_i, -1, in, segptrs[0], L);
+}
+// received segments of sub-block b (from every rank) -> Y_b
+static int fft_y_fwd_sub(Ctx* c, const double* in, double* out, int b, int nsub)
+{
+    const GridD& gd = c->gd;
+    const int ib = c->iblock / nsub;
+    const long Rb = (long)gd.kmax * gd.jmax * ib;
+    FftLayout L;
+    L.nlines = ib * gd.kmax; L.scale = 1.;
+    L.n1 = ib; L.s1 = 1; L.sn = ib; L.s2 = (long)gd.jmax * ib; L.esplit_in = gd.jmax; L.eseg_in = (long)nsub * Rb; L.base_in = (long)b * Rb;
+    L.n1o = ib; L.s1o = 1; L.sno = ib; L.s2o = (long)ib * gd.jtot; L.base_out = (long)b * gd.kmax * gd.jtot * ib;
+    return fft_lines(c, c->plan_j, -1, in, out, L);
+}
+// Y_b -> segments by destination rank; segptrs[r], r < ranks
+static int fft_y_bwd_sub(Ctx* c, const double* in, double* const* segptrs, int b, int nsub)
+{
+    const GridD& gd = c->gd;
+    const int ib = c->iblock / nsub;
+    FftLayout L;
+    L.nlines = ib * gd.kmax; L.scale = 1. / gd.jtot;
+    L.n1 = ib; L.s1 = 1; L.sn = ib; L.s2 = (long)ib * gd.jtot; L.base_in = (long)b * gd.kmax * gd.jtot * ib;
+    L.n1o = ib; L.s1o = 1; L.sno = ib; L.s2o = (long)gd.jmax * ib; L.esplit_out = gd.jmax; L.eseg_out = 0; L.base_out = 0;
+    ptr_segtab(L, segptrs, c->npy);
+    return fft_lines(c, c->plan_j, +1, in, segptrs[0], L);
+}
+// received segments (all sub-blocks, segment v at v * Rb) -> the ghost-celled p
+static int fft_x_bwd_sub(Ctx* c, const double* in, double* p, int nsub)
+{
+    const GridD& gd = c->gd;
+    const int ib = c->iblock / nsub;
+    FftLayout L;
+    L.nlines = gd.jmax * gd.kmax; L.scale = 1. / gd.itot;
+    L.n1 = L.nlines; L.s1 = ib; L.s2 = 0; L.sn = 1; L.esplit_in = ib; L.eseg_in = (long)gd.kmax * gd.jmax * ib; L.base_in = 0;
+    L.n1o = gd.jmax; L.s1o = gd.icells; L.s2o = gd.ijcells; L.sno = 1;
+    L.base_out = gd.igc + (long)gd.jgc * gd.icells + (long)gd.kgc * gd.ijcells;
+    return fft_lines(c, c->plan_i, +1, in, p, L);
+}
+
 int pres2_in_fft_x(Ctx*, const FftPlan&, const double*, const double*, const double*, const double*, const double*, const double*,
                    double, double*, const FftLayout&, int);   // fft_pow2.cu
 
@@ -296,6 +361,7 @@ static int fft_backward_impl(Ctx* c, double* data, double* p)
 int transpose_copy(Ctx*, int, double*, const double*);
 int halo_ns(Ctx*, double*, double*, double*, int, int);
 int pres2_solve_spectral_ws(Ctx*, double*, double*);
+int pres2_solve_spectral_sub(Ctx*, double*, double*, int, int);
 int pres2_output_stage(Ctx*, int, double*, double*, double*, double*);
 int pres2_output_rk(Ctx*, double*, double*, double*, double*, double*, double*, double*, int, int, double);
 }  // namespace mhh
@@ -840,6 +906,22 @@ int mhh_pres_solve_spectral_ws(mhh_ctx* c, double* data, double* work3d)
     if (c->order == 4) return pres4_solve_spectral(c, data);      // the 7-band factors live in the context's own scratch
     return pres2_solve_spectral_ws(c, data, work3d);
 }
+int mhh_slab_fft_x_fwd_sub(mhh_ctx* c, const double* in, double* const* segptrs, int nsub)
+{ PRES_READY(c); if (!in || !segptrs) return MHH_ERR_ARG; if (int e = sub_check(c, nsub, 0)) return e; return fft_x_fwd_sub(c, in, segptrs, nsub); }
+int mhh_slab_fft_y_fwd_sub(mhh_ctx* c, const double* in, double* out_Y, int b, int nsub)
+{ PRES_READY(c); if (!in || !out_Y) return MHH_ERR_ARG; if (int e = sub_check(c, nsub, b)) return e; return fft_y_fwd_sub(c, in, out_Y, b, nsub); }
+int mhh_slab_solve_sub(mhh_ctx* c, double* Y, double* work, int b, int nsub)
+{
+    PRES_READY(c);
+    if (!Y || !work) return MHH_ERR_ARG;
+    if (int e = sub_check(c, nsub, b)) return e;
+    if (c->order != 2) { c->last_error = "mhh_slab_solve_sub: Pres_2 only"; return MHH_ERR_UNSUPPORTED; }
+    return pres2_solve_spectral_sub(c, Y, work, b, nsub);
+}
+int mhh_slab_fft_y_bwd_sub(mhh_ctx* c, const double* in_Y, double* const* segptrs, int b, int nsub)
+{ PRES_READY(c); if (!in_Y || !segptrs) return MHH_ERR_ARG; if (int e = sub_check(c, nsub, b)) return e; return fft_y_bwd_sub(c, in_Y, segptrs, b, nsub); }
+int mhh_slab_fft_x_bwd_sub(mhh_ctx* c, const double* in, double* p, int nsub)
+{ PRES_READY(c); if (!in || !p) return MHH_ERR_ARG; if (int e = sub_check(c, nsub, 0)) return e; return fft_x_bwd_sub(c, in, p, nsub); }
 int mhh_pres_output_stage(mhh_ctx* c, int stage, double* ut, double* vt, double* wt, double* p)
 {
     PRES_READY(c);
@@ -886,11 +968,19 @@ int mhh_pres_exec_rk(mhh_ctx* c, double* u, double* v, double* w, double* ut, do
     if ((e = pres_input_fft_forward(c, u, v, w, ut, vt, wt, dt_sub))) return e;
     if ((e = mhh_pres_solve_spectral(c, c->work_p))) return e;
     if ((e = fft_backward_impl(c, c->work_p, p))) return e;
+    if (c->out_wait)        // work on another stream still reads the old u,v,w (mhh_pres_set_output_wait)
+    {
+        MHH_CUDA_CHECK(cudaStreamWaitEvent(c->stream, c->out_wait, 0));
+        c->out_wait = nullptr;
+    }
     // 4th order: also leaves w's ghost rows in the Normal state of the not yet updated w (src/model.cxx:412)
     if (c->order == 4) return pres4_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
     if ((e = pres2_output_stage(c, 0, ut, vt, wt, p))) return e;
     return pres2_output_rk(c, ut, vt, wt, p, u, v, w, rkorder, substep, dt);
 }
+
+int mhh_pres_set_output_wait(mhh_ctx* c, void* cuda_event)
+{ CTX_CHECK(c); c->out_wait = static_cast<cudaEvent_t>(cuda_event); return MHH_OK; }
 
 int mhh_pres_check_divergence(mhh_ctx* c, const double* u, const double* v, const double* w, double* out)
 {

@@ -104,6 +104,7 @@ struct Ctx
         unsigned long long halo_epoch = 0, barrier_epoch = 0;
     } peer;
 
+    cudaEvent_t out_wait = nullptr;  // mhh_pres_set_output_wait: the next fused pressure call waits for it before it updates u,v,w
     int sc_kc0 = 0, sc_nkc = 0;     // k-chunk window of the scalar tendency pass (mhh_advec2_smag2_exec_rk_parts); 0,0: whole column
 
     // TMA tensor maps of the fields the tile kernels stage (tma.cu); keyed by (pointer, box): the host model's arrays are stable

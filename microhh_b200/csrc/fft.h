@@ -10,6 +10,7 @@ namespace mhh
 //   output address = base_out + (l % n1o)*s1o + (l / n1o)*s2o + m*sno
 // Optional two-level element index (the all-to-all chunk layouts of the y-slab solver, slab.cu): with esplit > 0 (a power
 // of two) element m sits at (m / esplit)*eseg + (m % esplit)*sn instead of m*sn.  register-resident pow2 kernel only.
+constexpr int FFT_SEGTAB = 32;    // output segments a line can be scattered to (ranks x kx sub-blocks)
 struct FftLayout
 {
     int nlines;
@@ -21,7 +22,7 @@ struct FftLayout
     // with use_segtab_out, output segment r = m / esplit_out starts at segtab_out[r] (elements, relative to `out`) instead of
     // r*eseg_out: the segments are the receive buffers of the peer ranks (peer.cu), the transform writes them directly
     bool use_segtab_out = false;
-    long segtab_out[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long segtab_out[FFT_SEGTAB] = {};
 };
 
 int fft_plan_create(FftPlan* p, int n);

@@ -43,7 +43,7 @@ namespace
         int esh_in, esh_out;          // log2 of the element split (31: none)
         long eseg_in, eseg_out;
         int use_tab;                  // output segments start at segtab[r] (peer receive buffers) instead of r * eseg_out
-        long segtab[8];
+        long segtab[FFT_SEGTAB];
     };
 
     __device__ __forceinline__ double2 cmul(double2 a, double2 b)
@@ -203,7 +203,7 @@ namespace
     {
         if (!SPLIT) return (long)m * sn;
         const int r = m >> A.esh_out;
-        const long seg = A.use_tab ? A.segtab[r & 7] : (long)r * A.eseg_out;
+        const long seg = A.use_tab ? A.segtab[r & (FFT_SEGTAB - 1)] : (long)r * A.eseg_out;
         return seg + (long)(m & ((1 << A.esh_out) - 1)) * sn;
     }
 
@@ -626,7 +626,7 @@ int pres2_in_fft_x(Ctx* c, const FftPlan& plan, const double* u, const double* v
     A.esh_in = 31; A.eseg_in = 0;
     A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
     A.use_tab = L.use_segtab_out ? 1 : 0;
-    for (int r = 0; r < 8; ++r) A.segtab[r] = L.segtab_out[r];
+    for (int r = 0; r < FFT_SEGTAB; ++r) A.segtab[r] = L.segtab_out[r];
     PresInArgs F{u, v, w, ut, vt, wt, 1. / dt, k0, gd};
     const int npairs = BLOCK / (plan.n / 8);
     const size_t smem = (size_t)npairs * ((plan.n + plan.n / 8) + 1) * sizeof(double2);
@@ -665,18 +665,19 @@ int fft_pow2_lines(Ctx* c, const FftPlan& plan, int dir, const double* in, doubl
     A.esh_in = L.esplit_in > 0 ? lg(L.esplit_in) : 31;   A.eseg_in = L.eseg_in;
     A.esh_out = L.esplit_out > 0 ? lg(L.esplit_out) : 31; A.eseg_out = L.eseg_out;
     A.use_tab = L.use_segtab_out ? 1 : 0;
-    for (int r = 0; r < 8; ++r) A.segtab[r] = L.segtab_out[r];
-    if (L.use_segtab_out && (L.esplit_out <= 0 || plan.n / L.esplit_out > 8)) return MHH_ERR_UNSUPPORTED;
+    for (int r = 0; r < FFT_SEGTAB; ++r) A.segtab[r] = L.segtab_out[r];
+    if (L.use_segtab_out && (L.esplit_out <= 0 || plan.n / L.esplit_out > FFT_SEGTAB)) return MHH_ERR_UNSUPPORTED;
     // y passes whose lines are adjacent words: the lanes-along-the-lines kernel (n = 256, 512, 1024: 16, 8, 4 pairs per CTA)
     {
         static const bool col_off = []() { const char* e = getenv("MHH_FFT_NOCOL"); return e && atoi(e) != 0; }();
         const int tfn = plan.n / 8;
         const int cp = tfn > 0 ? CBLOCK / tfn : 0;
         auto even = [](long v) { return (v & 1L) == 0; };
+        bool tab_even = true;
+        if (L.use_segtab_out) for (int r = 0; r < FFT_SEGTAB; ++r) tab_even = tab_even && even(L.segtab_out[r]);
         const bool aligned = even(L.s2) && even(L.sn) && even(L.base_in) && even(L.s2o) && even(L.sno) && even(L.base_out)
                           && even(L.eseg_in) && even(L.eseg_out)
-                          && (!L.use_segtab_out || (even(L.segtab_out[0]) && even(L.segtab_out[1]) && even(L.segtab_out[2]) && even(L.segtab_out[3])
-                                                    && even(L.segtab_out[4]) && even(L.segtab_out[5]) && even(L.segtab_out[6]) && even(L.segtab_out[7])))
+                          && tab_even
                           && (reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
         if (!col_off && strided && (cp == 4 || cp == 8 || cp == 16) && L.s1 == 1 && L.s1o == 1 && L.n1 == L.n1o
             && L.n1 % (2 * cp) == 0 && L.nlines % (2 * cp) == 0 && aligned)

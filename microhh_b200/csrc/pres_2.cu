@@ -309,6 +309,21 @@ int pres2_solve_spectral_ws(Ctx* c, double* data, double* work3d)
     return MHH_OK;
 }
 
+// kx sub-block b of nsub (capi.cu: mhh_slab_*_sub): Y_b = [k][j < jtot][ii < ib] at b * kmax * jtot * ib, columns
+// kx = rank * iblock + b * ib + ii (src/pres_2.cxx:297-299); work: kmax / 16 + 1 planes of jtot * ib
+int pres2_solve_spectral_sub(Ctx* c, double* data, double* work, int b, int nsub)
+{
+    const GridD& gd = c->gd;
+    const int ib = c->iblock / nsub;
+    const int bx = ib >= 128 ? 128 : (ib >= 64 ? 64 : 32);
+    dim3 blk(bx), g((ib + bx - 1) / bx, c->jblock);
+    MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, blk, 0, c->stream>>>(data + (long)b * gd.kmax * c->jblock * ib, work,
+                                              c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+                                              ib, c->jblock, c->rank_y * c->iblock + b * ib, 0, gd));
+    MHH_LAUNCH_CHECK();
+    return MHH_OK;
+}
+
 int pres2_solve_spectral(Ctx* c, double* data) { return pres2_solve_spectral_ws(c, data, c->work_c); }
 
 int pres_scatter(Ctx* c, double* p, const double* src)

@@ -669,6 +669,8 @@ class Pres:
 
     def __init__(self, grid, fields, swpres):
         self.grid, self.fields, self.swpres = grid, fields, swpres
+        self._side, self._side_done = None, None
+        self.overlap_hooks = os.environ.get("MHH_SCALAR_OVERLAP", "0") != "0"
 
     @staticmethod
     def factory(grid, fields, swpres=None):
@@ -688,12 +690,29 @@ class Pres:
         """Pres::exec.  With `timeloop` the gradient stage is fused with Timeloop::exec for u,v,w (mhh_pres_exec_rk):
         returns True, and the caller must run timeloop.exec(skip=("u", "v", "w")) and must NOT call
         set_ghost_cells_w(Normal) in between (4th order: the fused call has done it on the not yet updated w)."""
-        for h in hooks or ():       # independent work a decomposed solver overlaps with its exchanges: here simply run first
-            h()
+        g, f = self.grid, self.fields
+        fused = timeloop is not None and self.swpres in ("2", "4") and g.npy == 1
+        if hooks and fused and self.overlap_hooks:
+            # `hooks` (the scalars' tendency + RK passes) read u,v,w but nothing the solver writes before its last kernel: they
+            # run on a second stream beside the solver's input, transforms and vertical solve (HBM-bound passes next to
+            # latency-bound ones), and the kernel that updates u,v,w waits for them (mhh_pres_set_output_wait)
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=g.device)
+            main, side = torch.cuda.current_stream(g.device), self._side
+            ev = torch.cuda.Event(); ev.record(main)
+            side.wait_event(ev)
+            g.lib.mhh_set_stream(g.ctx, C.c_void_p(side.cuda_stream))
+            for h in hooks:
+                h()
+            g.lib.mhh_set_stream(g.ctx, C.c_void_p(main.cuda_stream))
+            self._side_done = torch.cuda.Event(); self._side_done.record(side)
+            L.check(g.ctx, g.lib.mhh_pres_set_output_wait(g.ctx, C.c_void_p(self._side_done.cuda_event)), "mhh_pres_set_output_wait")
+        else:
+            for h in hooks or ():       # independent work a decomposed solver overlaps with its exchanges: here simply run first
+                h()
         if self.swpres == "0":
             return False
-        g, f = self.grid, self.fields
-        if timeloop is not None and self.swpres in ("2", "4") and g.npy == 1:
+        if fused:
             L.check(g.ctx, g.lib.mhh_pres_exec_rk(g.ctx, L.ptr(f.mp["u"].fld), L.ptr(f.mp["v"].fld), L.ptr(f.mp["w"].fld),
                                                   L.ptr(f.mt["u"].fld), L.ptr(f.mt["v"].fld), L.ptr(f.mt["w"].fld),
                                                   L.ptr(f.sd["p"].fld), C.c_double(dt), timeloop.rkorder, timeloop.substep,

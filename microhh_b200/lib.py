@@ -61,6 +61,7 @@ EXPORTS = [
     "mhh_rk_substep", "mhh_rk_sub_dt", "mhh_pres_output_rk", "mhh_pres_exec_rk",
     "mhh_mean_profile", "mhh_level_sums", "mhh_stats_mean", "mhh_stats_moment", "mhh_stats_cov", "mhh_mean", "mhh_mean_2d", "mhh_max",
     "mhh_check_momentum", "mhh_check_tke", "mhh_check_mass", "mhh_mean_static",
+    "mhh_pres_set_output_wait", "mhh_slab_fft_x_fwd_sub", "mhh_slab_fft_y_fwd_sub", "mhh_slab_solve_sub", "mhh_slab_fft_y_bwd_sub", "mhh_slab_fft_x_bwd_sub",
 ]
 
 

@@ -3,6 +3,8 @@ from __future__ import annotations
 
 import ctypes as C
 
+import os
+
 import numpy as np
 
 from . import lib as L
@@ -113,6 +115,8 @@ class Model:
         scal = set(self.fields.sp)
         self.fuse_scalar_rk = (self.fuse_tend and bool(scal) and fo_.swwls == "0"
                                and not (scal & set(fo_.lslist)) and not (scal & set(fo_.nudgelist)))
+        # single GPU: the scalars' fused pass on a second stream beside the pressure solver (Pres.exec); opt-in, MHH_SCALAR_OVERLAP=1: measured 40.5 / 40.8 ms against 40.6 / 40.4 without (r02ab) — both sides fill the GPU, the block scheduler runs them one after the other
+        self.scalar_overlap = self.grid.npy == 1 and os.environ.get("MHH_SCALAR_OVERLAP", "0") != "0"
         # Tendencies left undefined (not zeroed) by the fused last-substep tails; the next fused tendency pass starts from 0
         self.lazy_tend = bool(self.fuse_tend and self.fuse_pres_rk and self.pres.swpres == "2"
                               and (not scal or self.fuse_scalar_rk) and ini.get("b200", {}).get("lazy_tendencies", True))
@@ -176,12 +180,15 @@ class Model:
         if self.fuse_tend:      # :366 + :388 + :392, one pass per prognostic field (set_ghost_cells_w is a 4th-order no-op)
             srk = self.fuse_scalar_rk
             th_b = self.fields.sp["th"].fld if self.thermo.swthermo == "dry" else None
+            part = lambda *p: (lambda: self.diff.exec_with_advec2(th_b, buffer=self.buffer, timeloop=tl, parts=p))
             if srk and self._scalar_halves():
                 nch = (self.grid.kmax + 63) // 64
                 half = max(1, nch // 2)               # chunks of the first half; a second part starting at nch is a no-op
-                part = lambda *p: (lambda: self.diff.exec_with_advec2(th_b, buffer=self.buffer, timeloop=tl, parts=p))
                 part(1, 0, 0, 0)()                                     # the momentum pass now
                 hooks = (part(0, 1, 0, half), part(0, 1, half, 0))     # the scalar passes from inside the pressure solver
+            elif srk and self.scalar_overlap and self.fuse_pres_rk and self.fields.sp:
+                part(1, 0, 0, 0)()
+                hooks = (part(0, 1, 0, 0),)            # the scalar passes on a second stream beside the pressure solver (Pres.exec)
             else:
                 self.diff.exec_with_advec2(th_b, buffer=self.buffer if srk else None, timeloop=tl if srk else None)
         elif self.fuse_tend4:   # :387-392 in one call, the momentum diffusion inside the advection passes

@@ -209,12 +209,19 @@ class SlabPres(Pres):
         # ce_overlap: own chunk written in place, one copy-engine transfer per peer on parallel streams while the SMs run the
         # scalar tendency pass (which does not depend on the pressure); fused: the transforms store straight into the peers'
         # buffers (no staging, but the NVLink-bound stores hold the SMs: fft_fwd_x 1.01 instead of 0.51 ms at N = 2).
-        self.a2a = os.environ.get("MHH_SLAB_A2A", "ce_overlap")
+        self.a2a = os.environ.get("MHH_SLAB_A2A", "ce_sub")
         self.timing = [] if os.environ.get("MHH_SLAB_TIMING") else None     # ce_overlap: CUDA events of every exchange
 
     def timing_report(self):
-        """ms, averaged over the recorded exchanges: copies, barrier wait after the copies, hook kernel, main stream stalled."""
+        """ms, averaged over the recorded exchanges.  ce_overlap: copies, barrier wait after the copies, hook kernel, main stream
+        stalled; ce_sub: the main stream's waits for a sub-block (arrival or return), per wait and per solve."""
         torch.cuda.synchronize(self.grid.device)
+        if self.a2a == "ce_sub":
+            waits = [a.elapsed_time(b) for a, b in self.timing]
+            self.timing.clear()
+            per = 1          # one wait per solve: the last sub-block's return
+            return dict(mode="ce_sub", nsub=self.nsub, waits=len(waits), wait_ms=sum(waits) / max(len(waits), 1),
+                        stalled_ms_per_solve=sum(waits) / max(len(waits) // per, 1))
         rows = [(a.elapsed_time(b), b.elapsed_time(c), a.elapsed_time(d), d.elapsed_time(e)) for a, b, c, d, e in self.timing]
         self.timing.clear()
         n = max(len(rows), 1)
@@ -274,6 +281,92 @@ class SlabPres(Pres):
         exchange(self._r2_t, hooks[1] if hooks else None)
         ck(lib.mhh_fft_x_chunks(g.ctx, +1, R2, None, L.ptr(p), 0, g.kmax), "chunks -> fft_x bwd")
 
+    def _sub_setup(self):
+        """MHH_SLAB_A2A=ce_sub: tables of the kx sub-block pipeline (mhh_slab_*_sub, include/mhh_b200.h)."""
+        g = self.grid
+        world, me = self.comm.world, self.comm.rank
+        iblock = g.itot // world
+        B = max(1, int(os.environ.get("MHH_SLAB_NSUB", "4")))
+        while B > 1 and (iblock % B or world * B > 32 or iblock // B < 8):
+            B //= 2
+        self.nsub = B
+        ib = iblock // B
+        self._Rb = Rb = g.kmax * g.jmax * ib
+        es = self.S.element_size()
+        at = lambda t, v: t.data_ptr() + v * Rb * es
+        # forward x pass: segment v = r * B + b of every line -> staging S (sent by the copy engines), mine straight into R1
+        self._sub_xtab = (C.c_void_p * (world * B))(*[at(self.R1 if r == me else self.S, r * B + b) for r in range(world) for b in range(B)])
+        # inverse y pass of sub-block b: the rows of rank r -> staging slot (r, b), mine straight into slot (me, b) of R2
+        self._sub_ytab = [(C.c_void_p * world)(*[at(self.R2, me * B + b) if r == me else at(self.S, r * B + b) for r in range(world)])
+                          for b in range(B)]
+        ncomp = max(1, int(os.environ.get("MHH_SLAB_SUB_STREAMS", "2")))
+        self._comp = [torch.cuda.Stream(device=g.device, priority=-1) for _ in range(ncomp)]
+        self._W = [torch.empty((g.kmax // 16 + 2) * g.jtot * ib, dtype=g.dtype, device=g.device) for _ in range(ncomp)]   # pivot checkpoints
+        self._bar = torch.cuda.Stream(device=g.device, priority=-1)
+
+    def _exec_ce_sub(self, p, hooks):
+        """MHH_SLAB_A2A=ce_sub: the solve pipelined over kx sub-blocks.  The forward x pass writes its segments into a staging
+        array; the copy engines send sub-block b of every peer's block (one cudaMemcpyAsync per peer), and as soon as sub-block
+        b has arrived from everyone (device barrier on its own stream) the main stream runs y transform -> Thomas sweep ->
+        inverse y transform on it, while sub-block b+1 is still in flight; its rows then travel back while b+1 is computed.
+        The vertical solve is no longer a join between the two all-to-alls; what stays exposed is the first sub-block's
+        forward transfer and the last one's return, and the two scalar-pass halves (`hooks`) run in those two gaps."""
+        g, lib = self.grid, self.grid.lib
+        ck = lambda err, what: L.check(g.ctx, err, what)
+        X, R1, R2 = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2)
+        world, me, B, Rb = self.comm.world, self.comm.rank, self.nsub, self._Rb
+        main, bar = torch.cuda.current_stream(g.device), self._bar
+        cs = self._copy_streams[:max(1, min(len(self._copy_streams), world - 1))]
+        on = lambda st: lib.mhh_set_stream(g.ctx, C.c_void_p(st.cuda_stream))
+        T = self.timing is not None
+
+        def transfer(peers_t, b, after):
+            """Sub-block b to every peer's buffer, then the barrier: returns the event 'sub-block b is complete everywhere'."""
+            for st in cs:
+                st.wait_event(after)
+            for n, d in enumerate(range(1, world)):
+                r = (me + d) % world
+                with torch.cuda.stream(cs[n % len(cs)]):
+                    peers_t[r][(me * B + b) * Rb:(me * B + b + 1) * Rb].copy_(self.S[(r * B + b) * Rb:(r * B + b + 1) * Rb], non_blocking=True)
+            for st in cs:
+                e = torch.cuda.Event(); e.record(st)
+                bar.wait_event(e)
+            on(bar)
+            ck(lib.mhh_peer_barrier(g.ctx), "peer barrier")
+            on(main)
+            done = torch.cuda.Event(); done.record(bar)
+            return done
+
+        def wait(ev):
+            if T:
+                a = torch.cuda.Event(enable_timing=True); a.record(main)
+            main.wait_event(ev)
+            if T:
+                b_ = torch.cuda.Event(enable_timing=True); b_.record(main)
+                self.timing.append((a, b_))
+
+        ck(lib.mhh_slab_fft_x_fwd_sub(g.ctx, X, self._sub_xtab, B), "fft_x fwd -> sub-block segments")
+        ev = torch.cuda.Event(); ev.record(main)
+        arrived = [transfer(self._r1_t, b, ev) for b in range(B)]
+        # The sub-blocks alternate between two high-priority streams: a sub-block's Thomas sweep has too few columns to fill
+        # the GPU on its own (k-sequential, latency bound), so it shares the SMs with the next sub-block's transforms and with
+        # the scalar tendency pass (`hooks`, HBM bound), which the main stream runs meanwhile.
+        back = []
+        for b in range(B):
+            st = self._comp[b % len(self._comp)]
+            st.wait_event(arrived[b])
+            on(st)
+            ck(lib.mhh_slab_fft_y_fwd_sub(g.ctx, R1, X, b, B), "segments -> fft_y fwd")
+            ck(lib.mhh_slab_solve_sub(g.ctx, X, L.ptr(self._W[b % len(self._comp)]), b, B), "tdma")
+            ck(lib.mhh_slab_fft_y_bwd_sub(g.ctx, X, self._sub_ytab[b], b, B), "fft_y bwd -> segments")
+            ev = torch.cuda.Event(); ev.record(st)
+            on(main)
+            back.append(transfer(self._r2_t, b, ev))
+        for h in hooks or ():
+            h()
+        wait(back[-1])          # the barrier stream is ordered: the last return implies the earlier ones
+        ck(lib.mhh_slab_fft_x_bwd_sub(g.ctx, R2, L.ptr(p), B), "segments -> fft_x bwd")
+
     def _ce_tables(self):
         """Destination tables for the sending transforms of ce_overlap (mhh_fft_*_chunks_to_peers writes segment r at
         table[r] + rank * R): the segments for the other ranks land at S[r * R] in the local staging array, from where the
@@ -299,24 +392,30 @@ class SlabPres(Pres):
         X, R1, R2 = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2)
         if self._r1_peers is None:
             self._r1_peers, self._r2_peers = g.arena.peer_ptrs(self.R1), g.arena.peer_ptrs(self.R2)
-            if self.a2a not in ("fused", "fused_pipe", "ce", "ce_overlap"):
-                raise L.MhhError("MHH_SLAB_A2A must be fused, fused_pipe, ce or ce_overlap")
+            if self.a2a not in ("fused", "fused_pipe", "ce", "ce_overlap", "ce_sub"):
+                raise L.MhhError("MHH_SLAB_A2A must be fused, fused_pipe, ce, ce_overlap or ce_sub")
+            if self.a2a == "ce_sub" and self.swpres != "2":
+                self.a2a = "ce_overlap"          # the sub-block sweep exists for the tridiagonal solve only
             if self.a2a != "fused":
                 self._side = [torch.cuda.Stream(device=g.device), torch.cuda.Stream(device=g.device)]
-            if self.a2a in ("ce", "ce_overlap"):
+            if self.a2a in ("ce", "ce_overlap", "ce_sub"):
                 from .host import _RawCuda
                 nb = self.R1.numel() * self.R1.element_size()
                 wrap = lambda ptr: torch.as_tensor(_RawCuda(ptr, nb), device=g.device).view(g.dtype)
                 self._r1_t = [wrap(q) for q in self._r1_peers]
                 self._r2_t = [wrap(q) for q in self._r2_peers]
                 self.S = torch.empty_like(self.A)
-            if self.a2a == "ce_overlap":
+            if self.a2a in ("ce_overlap", "ce_sub"):
                 # one cudaMemcpyAsync per peer, spread over a few streams so that several copy engines / NVLink ports are busy
                 ncs = max(1, int(os.environ.get("MHH_SLAB_COPY_STREAMS", "4")))
                 self._copy_streams = [self._side[0]] + [torch.cuda.Stream(device=g.device) for _ in range(ncs - 1)]
                 self._ce_tabs = self._ce_tables()
+                if self.a2a == "ce_sub":
+                    self._sub_setup()
         if self.a2a == "ce_overlap":
             return self._exec_ce_overlap(p, hooks)
+        if self.a2a == "ce_sub":
+            return self._exec_ce_sub(p, hooks)
         for h in hooks or ():
             h()
         if self.a2a == "fused":
@@ -491,7 +590,7 @@ class SlabModel(Model):
         return self.comm.allreduce_max_many(values, self.grid.device)
 
     def _scalar_halves(self):
-        return self.path == "peer" and self.pres.a2a == "ce_overlap"
+        return self.path == "peer" and self.pres.a2a in ("ce_overlap", "ce_sub")
 
     def print_status(self):
         g, f, tl, dev = self.grid, self.fields, self.timeloop, self.grid.device
