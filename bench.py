@@ -356,6 +356,7 @@ def main():
     ap.add_argument("--cpu-size", type=int, default=None, help="edge of the CPU sample grid (default 96 for cpu_baseline, 192 for --impl reference)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="experiments only: skip the host-resident leg (e2e value null)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -469,14 +470,15 @@ def main():
     # compute of step n on two copy streams; every copy, including the first upload and the last download, is timed.
     h2d = sum(v.numel() * 8 for v in pinned.values())
     from microhh_b200.model import HostFeed
-    e2e_steps = max(2, min(args.steps, 10))
+    e2e_steps = 0 if args.no_e2e else max(2, min(args.steps, 10))
     pinned_out = {k: torch.empty_like(v).pin_memory() for k, v in pinned.items()}
     feed, drain = HostFeed(model), HostDrain(model, pinned_out)
     barrier()
     ee0, ee1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ee0.record()
     status = None
-    feed.submit(pinned)
+    if e2e_steps:
+        feed.submit(pinned)
     for s_ in range(e2e_steps):
         feed.adopt()
         if s_ + 1 < e2e_steps:
@@ -492,7 +494,7 @@ def main():
     t = torch.tensor([ems], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = points * e2e_steps / (float(t.item()) * 1e-3)
+    e2e_value = points * e2e_steps / (float(t.item()) * 1e-3) if e2e_steps else None
     del feed, drain, pinned_out
 
     if rank != 0:

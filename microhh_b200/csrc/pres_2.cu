@@ -149,6 +149,105 @@ namespace
         }
     }
 
+    // The same sweep, software-pipelined for launches that cannot fill the GPU (kx sub-blocks of the y-slab solver, long
+    // columns on few ranks): there the sweep runs at the latency of its dependent chain, and in pres2_tdma_kernel every level's
+    // loads (p from L2, the level's metrics) are issued only after the previous level's store — the compiler may not move them
+    // across it.  Here the loads of level k+2 (p) and k+1 (metrics) are issued before the chain of level k, and the back
+    // substitution fetches the 16 p values of a block before it recomputes the block's c'.  Same operations in the same order
+    // on every value: bit-identical to pres2_tdma_kernel.  More registers, so the GPU-filling launches keep the other kernel.
+    __global__ void __launch_bounds__(128)
+    pres2_tdma_pipe_kernel(double* __restrict__ p, double* __restrict__ ckpt,
+                           const double* __restrict__ a, const double* __restrict__ c,
+                           const double* __restrict__ bmati, const double* __restrict__ bmatj,
+                           const int iblock, const int jblock, const int ioff, const int joff, const GridD gd)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        const int j = blockIdx.y;
+        if (i >= iblock) return;
+        const int kmax = gd.kmax, kgc = gd.kgc;
+        const long kk = (long)iblock * jblock;
+        const long ij = i + (long)j * iblock;
+        const int iindex = ioff + i, jindex = joff + j;
+        const double bm = bmati[iindex] + bmatj[jindex];
+        const bool mode0 = (iindex == 0 && jindex == 0);
+        const double* __restrict__ dzp = gd.dz + kgc;
+        const double* __restrict__ rhop = gd.rhoref + kgc;
+
+        // level record: dz, rho, a, c of level k (read-only path: free to move across the stores)
+        struct Lev { double dz, rho, a, c; };
+        auto lev = [&](int k) -> Lev { return Lev{__ldg(dzp + k), __ldg(rhop + k), __ldg(a + k), __ldg(c + k)}; };
+        auto bdiag = [&](int k, const Lev& l) -> double
+        {
+            double b = l.dz * l.dz * l.rho * bm - (l.a + l.c);
+            if (k == 0) b += l.a;
+            if (k == kmax - 1) { if (mode0) b -= l.c; else b += l.c; }
+            return b;
+        };
+
+        Lev l0 = lev(0);
+        double r = fast_rcp(bdiag(0, l0));
+        double pprev = (l0.dz * l0.dz * p[ij]) * r;
+        p[ij] = pprev;
+        ckpt[ij] = r;
+        double cprev = l0.c;
+        Lev ln = lev(kmax > 1 ? 1 : 0);
+        double p1 = kmax > 1 ? p[ij + kk] : 0., p2 = kmax > 2 ? p[ij + 2 * kk] : 0.;
+        for (int k = 1; k < kmax; ++k)
+        {
+            const Lev l = ln;
+            const double praw = p1;
+            if (k + 1 < kmax) ln = lev(k + 1);
+            p1 = p2;
+            if (k + 2 < kmax) p2 = p[ij + (k + 2) * kk];
+            if (k + 6 < kmax) prefetch_l2(p + ij + (k + 6) * kk);
+            const double w3 = cprev * r;
+            r = fast_rcp(bdiag(k, l) - l.a * w3);
+            double pk = l.dz * l.dz * praw;
+            pk -= l.a * pprev;
+            pk *= r;
+            p[ij + k * kk] = pk;
+            pprev = pk;
+            cprev = l.c;
+            if ((k & (TDMA_M - 1)) == 0) ckpt[ij + (k / TDMA_M) * kk] = r;
+        }
+        for (int kb = ((kmax - 1) / TDMA_M) * TDMA_M; kb >= 0; kb -= TDMA_M)
+        {
+            // the block's p values first: their latency hides behind the recomputation of c'
+            double pv[TDMA_M];
+            #pragma unroll
+            for (int m = 0; m < TDMA_M; ++m)
+                pv[m] = (kb + m < kmax - 1) ? p[ij + (kb + m) * kk] : 0.;
+            double w3[TDMA_M];
+            double rr = ckpt[ij + (kb / TDMA_M) * kk];
+            if (kb >= TDMA_M) prefetch_l2(ckpt + ij + (kb / TDMA_M - 1) * kk);
+            #pragma unroll
+            for (int m = 0; m < TDMA_M; ++m)
+            {
+                const int k = kb + m + 1;
+                if (k < kmax)
+                {
+                    const Lev l = lev(k);
+                    w3[m] = __ldg(c + k - 1) * rr;
+                    if (m + 1 < TDMA_M) rr = fast_rcp(bdiag(k, l) - l.a * w3[m]);
+                }
+                else
+                    w3[m] = 0.;
+            }
+            #pragma unroll
+            for (int m = TDMA_M - 1; m >= 0; --m)
+            {
+                const int k = kb + m;
+                if (k < kmax - 1)
+                {
+                    double pk = pv[m];
+                    pk -= w3[m] * pprev;
+                    p[ij + k * kk] = pk;
+                    pprev = pk;
+                }
+            }
+        }
+    }
+
     // p[kstart-1] = p[kstart] on interior columns, src/pres_2.cxx:352-358
     __global__ void pres2_bottom_ghost_kernel(double* __restrict__ p, const GridD gd)
     {
@@ -317,9 +416,18 @@ int pres2_solve_spectral_sub(Ctx* c, double* data, double* work, int b, int nsub
     const int ib = c->iblock / nsub;
     const int bx = ib >= 128 ? 128 : (ib >= 64 ? 64 : 32);
     dim3 blk(bx), g((ib + bx - 1) / bx, c->jblock);
-    MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, blk, 0, c->stream>>>(data + (long)b * gd.kmax * c->jblock * ib, work,
-                                              c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
-                                              ib, c->jblock, c->rank_y * c->iblock + b * ib, 0, gd));
+    // launches of few columns run at the latency of the sweep's chain: the software-pipelined kernel (0.54 instead of 0.84 ms
+    // for 32 x 1024 columns of 1024 levels, tools/bench_tdma_sub.py); GPU-filling ones keep the leaner kernel (0.95 against 1.17)
+    static const int pipe_env = []() { const char* e = getenv("MHH_TDMA_PIPE"); return e ? atoi(e) : -1; }();
+    const bool pipe = pipe_env >= 0 ? pipe_env != 0 : (long)ib * c->jblock <= 40000;
+    double* d = data + (long)b * gd.kmax * c->jblock * ib;
+    const int ioff = c->rank_y * c->iblock + b * ib;
+    if (pipe)
+        MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_pipe_kernel<<<g, blk, 0, c->stream>>>(d, work, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+                                                                                              ib, c->jblock, ioff, 0, gd));
+    else
+        MHH_LAUNCH(c, "pres2_tdma_kernel", pres2_tdma_kernel<<<g, blk, 0, c->stream>>>(d, work, c->pres_a_d, c->pres_c_d, c->bmati_d, c->bmatj_d,
+                                                                                         ib, c->jblock, ioff, 0, gd));
     MHH_LAUNCH_CHECK();
     return MHH_OK;
 }

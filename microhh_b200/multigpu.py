@@ -209,7 +209,7 @@ class SlabPres(Pres):
         # ce_overlap: own chunk written in place, one copy-engine transfer per peer on parallel streams while the SMs run the
         # scalar tendency pass (which does not depend on the pressure); fused: the transforms store straight into the peers'
         # buffers (no staging, but the NVLink-bound stores hold the SMs: fft_fwd_x 1.01 instead of 0.51 ms at N = 2).
-        self.a2a = os.environ.get("MHH_SLAB_A2A", "ce_sub")
+        self.a2a = os.environ.get("MHH_SLAB_A2A", "ce_sub" if comm.world <= 4 else "ce_overlap")
         self.timing = [] if os.environ.get("MHH_SLAB_TIMING") else None     # ce_overlap: CUDA events of every exchange
 
     def timing_report(self):
@@ -217,11 +217,13 @@ class SlabPres(Pres):
         stalled; ce_sub: the main stream's waits for a sub-block (arrival or return), per wait and per solve."""
         torch.cuda.synchronize(self.grid.device)
         if self.a2a == "ce_sub":
-            waits = [a.elapsed_time(b) for a, b in self.timing]
+            n = max(len(self.timing), 1)
+            names = list(self.timing[0]) if self.timing else []
+            out = dict(mode="ce_sub", nsub=self.nsub, streams=len(self._comp), solves=len(self.timing),
+                       timeline_ms={k: round(sum(t["start"].elapsed_time(t[k]) for t in self.timing) / n, 3) for k in names if k != "start"},
+                       stalled_ms_per_solve=round(sum(t["hooks"].elapsed_time(t["resumed"]) for t in self.timing) / n, 3))
             self.timing.clear()
-            per = 1          # one wait per solve: the last sub-block's return
-            return dict(mode="ce_sub", nsub=self.nsub, waits=len(waits), wait_ms=sum(waits) / max(len(waits), 1),
-                        stalled_ms_per_solve=sum(waits) / max(len(waits) // per, 1))
+            return out
         rows = [(a.elapsed_time(b), b.elapsed_time(c), a.elapsed_time(d), d.elapsed_time(e)) for a, b, c, d, e in self.timing]
         self.timing.clear()
         n = max(len(rows), 1)
@@ -299,10 +301,11 @@ class SlabPres(Pres):
         # inverse y pass of sub-block b: the rows of rank r -> staging slot (r, b), mine straight into slot (me, b) of R2
         self._sub_ytab = [(C.c_void_p * world)(*[at(self.R2, me * B + b) if r == me else at(self.S, r * B + b) for r in range(world)])
                           for b in range(B)]
-        ncomp = max(1, int(os.environ.get("MHH_SLAB_SUB_STREAMS", "2")))
+        ncomp = max(1, int(os.environ.get("MHH_SLAB_SUB_STREAMS", str(B))))
         self._comp = [torch.cuda.Stream(device=g.device, priority=-1) for _ in range(ncomp)]
         self._W = [torch.empty((g.kmax // 16 + 2) * g.jtot * ib, dtype=g.dtype, device=g.device) for _ in range(ncomp)]   # pivot checkpoints
         self._bar = torch.cuda.Stream(device=g.device, priority=-1)
+        self._hooks_first = os.environ.get("MHH_SLAB_SUB_HOOKS", "first" if world >= 8 else "overlap") == "first"
 
     def _exec_ce_sub(self, p, hooks):
         """MHH_SLAB_A2A=ce_sub: the solve pipelined over kx sub-blocks.  The forward x pass writes its segments into a staging
@@ -337,35 +340,58 @@ class SlabPres(Pres):
             done = torch.cuda.Event(); done.record(bar)
             return done
 
-        def wait(ev):
-            if T:
-                a = torch.cuda.Event(enable_timing=True); a.record(main)
-            main.wait_event(ev)
-            if T:
-                b_ = torch.cuda.Event(enable_timing=True); b_.record(main)
-                self.timing.append((a, b_))
+        # MHH_SLAB_TIMING: the solve's timeline, events on the streams they belong to (offsets from the start of the x pass)
+        tl = {} if T else None
 
+        def mark(name, st):
+            if T:
+                e = torch.cuda.Event(enable_timing=True); e.record(st)
+                tl[name] = e
+
+        mark("start", main)
+        # The scalar tendency pass saturates HBM, and copy-engine traffic next to it all but stops (r02n8b timeline on 8 GPUs:
+        # the first quarter of the forward transfer arrived 0.57 ms after the pass ended, 2.3 ms after it was issued).  With 7
+        # peers the transfers are the critical path, so there the pass runs first and the transfers overlap only the
+        # sub-blocks' transforms and sweeps; with 1-3 peers the pass runs beside them (nothing stalls: r02z3).
+        first = self._hooks_first
+        if first:
+            for h in hooks or ():
+                h()
         ck(lib.mhh_slab_fft_x_fwd_sub(g.ctx, X, self._sub_xtab, B), "fft_x fwd -> sub-block segments")
         ev = torch.cuda.Event(); ev.record(main)
-        arrived = [transfer(self._r1_t, b, ev) for b in range(B)]
-        # The sub-blocks alternate between two high-priority streams: a sub-block's Thomas sweep has too few columns to fill
-        # the GPU on its own (k-sequential, latency bound), so it shares the SMs with the next sub-block's transforms and with
-        # the scalar tendency pass (`hooks`, HBM bound), which the main stream runs meanwhile.
+        mark("x_fwd", main)
+        arrived = []
+        for b in range(B):
+            arrived.append(transfer(self._r1_t, b, ev))
+            mark(f"arrived{b}", bar)
+        # Every sub-block has its own high-priority stream: a sub-block's Thomas sweep has too few columns to fill the GPU
+        # (k-sequential: it runs at the latency of its chain, tools/bench_tdma_sub.py), so the sweeps of the sub-blocks share
+        # the SMs with each other, with the transforms and with the scalar tendency pass (`hooks`, HBM bound) on the main stream.
         back = []
         for b in range(B):
             st = self._comp[b % len(self._comp)]
             st.wait_event(arrived[b])
             on(st)
             ck(lib.mhh_slab_fft_y_fwd_sub(g.ctx, R1, X, b, B), "segments -> fft_y fwd")
+            mark(f"y_fwd{b}", st)
             ck(lib.mhh_slab_solve_sub(g.ctx, X, L.ptr(self._W[b % len(self._comp)]), b, B), "tdma")
+            mark(f"tdma{b}", st)
             ck(lib.mhh_slab_fft_y_bwd_sub(g.ctx, X, self._sub_ytab[b], b, B), "fft_y bwd -> segments")
             ev = torch.cuda.Event(); ev.record(st)
+            mark(f"y_bwd{b}", st)
             on(main)
             back.append(transfer(self._r2_t, b, ev))
-        for h in hooks or ():
-            h()
-        wait(back[-1])          # the barrier stream is ordered: the last return implies the earlier ones
+            mark(f"back{b}", bar)
+        if not first:
+            for h in hooks or ():
+                h()
+        mark("hooks", main)
+        main.wait_event(back[-1])          # the barrier stream is ordered: the last return implies the earlier ones
+        mark("resumed", main)
         ck(lib.mhh_slab_fft_x_bwd_sub(g.ctx, R2, L.ptr(p), B), "segments -> fft_x bwd")
+        mark("x_bwd", main)
+        if T:
+            self.timing.append(tl)
 
     def _ce_tables(self):
         """Destination tables for the sending transforms of ce_overlap (mhh_fft_*_chunks_to_peers writes segment r at

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 for mode in $MODES; do
   echo "######## $mode"
   [ -z "$SKIP_PARITY" ] && MHH_SLAB_A2A=$mode SLAB_DIMS=32,512,8 MHH_SLAB_PATH=peer timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tests/slab_parity.py 2>&1 | grep -E "SLAB PARITY|Error|error" | head -5
-  MHH_SLAB_A2A=$mode MHH_SLAB_PATH=peer timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/bench_${TAG}_n${N}_$mode.json 2> gpurun_out/bench_${TAG}_n${N}_$mode.err; echo "== $mode exit $?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/bench_${TAG}_n${N}_$mode.err | tail -4
+  MHH_SLAB_A2A=$mode MHH_SLAB_PATH=peer timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 $BENCH_EXTRA > gpurun_out/bench_${TAG}_n${N}_$mode.json 2> gpurun_out/bench_${TAG}_n${N}_$mode.err; echo "== $mode exit $?"; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/bench_${TAG}_n${N}_$mode.err | tail -4
   python - <<PY
 import json
 try:
