@@ -182,6 +182,30 @@ class SlabBoundaryCyclic(Boundary_cyclic):
         self._push(planes, True)
 
 
+def sub_block_count(iblock, world, wanted=4):
+    """kx sub-blocks per rank: the largest power-of-two fraction of `wanted` that divides the rank's block, keeps at least 8
+    columns per sub-block and fits ranks x sub-blocks into the transforms' 32-entry segment table."""
+    B = max(1, wanted)
+    while B > 1 and (iblock % B or world * B > 32 or iblock // B < 8):
+        B //= 2
+    return B
+
+
+def sub_block_plan(world, me, nsub):
+    """Where the segments of the kx sub-block pipeline live (pure index arithmetic; segment = [k][j < jmax][ii < ib], slots
+    counted in segments).  Segment v = r * nsub + b of my x lines is rank r's sub-block b.
+      x_fwd[v]    : (buffer, slot) the forward x pass writes segment v to — the staging array S, or for my own block my
+                    receive buffer R1, where slot (source rank) * nsub + b is what the y pass of sub-block b reads;
+      y_bwd[b][r] : (buffer, slot) the inverse y pass of sub-block b writes the rows of rank r to — S, or my R2;
+      copies[b]   : (peer r, destination slot in r's R1 / R2, source slot in my S) of the transfers of sub-block b, starting
+                    with the next rank round the ring (the same list serves the forward and the return transfer)."""
+    B = nsub
+    x_fwd = [("R1" if r == me else "S", r * B + b) for r in range(world) for b in range(B)]
+    y_bwd = [[("R2", me * B + b) if r == me else ("S", r * B + b) for r in range(world)] for b in range(B)]
+    copies = [[((me + d) % world, me * B + b, ((me + d) % world) * B + b) for d in range(1, world)] for b in range(B)]
+    return dict(x_fwd=x_fwd, y_bwd=y_bwd, copies=copies)
+
+
 class SlabPres(Pres):
     """Pres_2 / Pres_4 on y-slabs (src/pres_2.cxx:267-361, src/pres_4.cxx:320-529 with src/fft.cxx:452-583, npx = 1): the stage
     calls of the C ABI with the two all-to-alls in between; the vertical solve (Thomas / 7-band LU) is column-local."""
@@ -287,20 +311,16 @@ class SlabPres(Pres):
         """MHH_SLAB_A2A=ce_sub: tables of the kx sub-block pipeline (mhh_slab_*_sub, include/mhh_b200.h)."""
         g = self.grid
         world, me = self.comm.world, self.comm.rank
-        iblock = g.itot // world
-        B = max(1, int(os.environ.get("MHH_SLAB_NSUB", "4")))
-        while B > 1 and (iblock % B or world * B > 32 or iblock // B < 8):
-            B //= 2
-        self.nsub = B
-        ib = iblock // B
+        self.nsub = B = sub_block_count(g.itot // world, world, int(os.environ.get("MHH_SLAB_NSUB", "4")))
+        ib = g.itot // world // B
         self._Rb = Rb = g.kmax * g.jmax * ib
         es = self.S.element_size()
-        at = lambda t, v: t.data_ptr() + v * Rb * es
-        # forward x pass: segment v = r * B + b of every line -> staging S (sent by the copy engines), mine straight into R1
-        self._sub_xtab = (C.c_void_p * (world * B))(*[at(self.R1 if r == me else self.S, r * B + b) for r in range(world) for b in range(B)])
-        # inverse y pass of sub-block b: the rows of rank r -> staging slot (r, b), mine straight into slot (me, b) of R2
-        self._sub_ytab = [(C.c_void_p * world)(*[at(self.R2, me * B + b) if r == me else at(self.S, r * B + b) for r in range(world)])
-                          for b in range(B)]
+        plan = sub_block_plan(world, me, B)
+        buf = dict(S=self.S, R1=self.R1, R2=self.R2)
+        at = lambda where: buf[where[0]].data_ptr() + where[1] * Rb * es
+        self._sub_xtab = (C.c_void_p * (world * B))(*[at(w) for w in plan["x_fwd"]])
+        self._sub_ytab = [(C.c_void_p * world)(*[at(w) for w in plan["y_bwd"][b]]) for b in range(B)]
+        self._sub_copies = plan["copies"]
         ncomp = max(1, int(os.environ.get("MHH_SLAB_SUB_STREAMS", str(B))))
         self._comp = [torch.cuda.Stream(device=g.device, priority=-1) for _ in range(ncomp)]
         self._W = [torch.empty((g.kmax // 16 + 2) * g.jtot * ib, dtype=g.dtype, device=g.device) for _ in range(ncomp)]   # pivot checkpoints
@@ -327,10 +347,9 @@ class SlabPres(Pres):
             """Sub-block b to every peer's buffer, then the barrier: returns the event 'sub-block b is complete everywhere'."""
             for st in cs:
                 st.wait_event(after)
-            for n, d in enumerate(range(1, world)):
-                r = (me + d) % world
+            for n, (r, dst, src) in enumerate(self._sub_copies[b]):
                 with torch.cuda.stream(cs[n % len(cs)]):
-                    peers_t[r][(me * B + b) * Rb:(me * B + b + 1) * Rb].copy_(self.S[(r * B + b) * Rb:(r * B + b + 1) * Rb], non_blocking=True)
+                    peers_t[r][dst * Rb:(dst + 1) * Rb].copy_(self.S[src * Rb:(src + 1) * Rb], non_blocking=True)
             for st in cs:
                 e = torch.cuda.Event(); e.record(st)
                 bar.wait_event(e)
