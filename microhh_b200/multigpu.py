@@ -330,10 +330,12 @@ class SlabPres(Pres):
     def _exec_ce_sub(self, p, hooks):
         """MHH_SLAB_A2A=ce_sub: the solve pipelined over kx sub-blocks.  The forward x pass writes its segments into a staging
         array; the copy engines send sub-block b of every peer's block (one cudaMemcpyAsync per peer), and as soon as sub-block
-        b has arrived from everyone (device barrier on its own stream) the main stream runs y transform -> Thomas sweep ->
-        inverse y transform on it, while sub-block b+1 is still in flight; its rows then travel back while b+1 is computed.
-        The vertical solve is no longer a join between the two all-to-alls; what stays exposed is the first sub-block's
-        forward transfer and the last one's return, and the two scalar-pass halves (`hooks`) run in those two gaps."""
+        b has arrived from everyone (device barrier on its own stream) a high-priority stream of its own runs y transform ->
+        Thomas sweep -> inverse y transform on it, while sub-block b+1 is still in flight; its rows then travel back while
+        b+1 is computed.  The vertical solve is no longer a join between the two all-to-alls.  The scalar tendency pass
+        (`hooks`) runs on the main stream beside all of this (or first, see `_hooks_first`); the main stream waits only for
+        the last sub-block's return before the inverse x pass.  Measured: 43.5 against 45.4 ms/step (2 GPUs), 46.9 against
+        48.0 (4), 52.0 against 50.8 (8) next to ce_overlap on the same boxes (profiles/r02_n8_phases.txt)."""
         g, lib = self.grid, self.grid.lib
         ck = lambda err, what: L.check(g.ctx, err, what)
         X, R1, R2 = L.ptr(self.A), L.ptr(self.R1), L.ptr(self.R2)
