@@ -16,6 +16,7 @@ for tag in G.KERNEL_CASES:
 _, les = G.oracle_les_substep()
 np.savez(os.path.join(G.GOLDEN_DIR, "les_substep.npz"), **les)
 np.savez(os.path.join(G.GOLDEN_DIR, "dns4_steps.npz"), **G.oracle_dns4_steps())
+np.savez(os.path.join(G.GOLDEN_DIR, "kernels_r02.npz"), **G.oracle_r02())
 for f in sorted(os.listdir(G.GOLDEN_DIR)):
     if f.endswith(".npz"):
         print(f, os.path.getsize(os.path.join(G.GOLDEN_DIR, f)))

@@ -128,5 +128,52 @@ def oracle_dns4_steps(nsteps=3):
     return out
 
 
+def oracle_r02():
+    """Outputs of the reference for what round 2 added to the path: Diff_smag2 without a thermo scalar (calc_evisc_neutral, both
+    wall treatments), Stats profiles, dry buoyancy, sponge layer, Coriolis force — small seeded cases."""
+    from oracle.ref import RefWorld
+    out = {}
+    for tag, kw in (("mason", dict(surface_model=1)), ("vandriest", dict(surface_model=0, mbc="noslip", xsize=100., ysize=100., zsize=100.))):
+        c = make_case(itot=12, jtot=8, ktot=10, nscalars=0, seed=201, **kw)
+        if tag == "vandriest":
+            c["visc"] = 1e-3
+            c["u"] *= 0.05; c["v"] *= 0.05
+        o = run_substep_oracle(c)
+        for k in ("evisc", "ut", "vt", "wt", "p"):
+            out[f"neutral_{tag}_{k}"] = o[k]
+    c = make_case(itot=12, jtot=8, ktot=10, zsize=3200., seed=202)
+    W = RefWorld(c["itot"], c["jtot"], c["ktot"], c["xsize"], c["ysize"], c["zsize"], c["z"], order=c["order"], gc=c["gc"],
+                 rhoref=c["rhoref"], rhorefh=c["rhorefh"])
+    u, v, w, th = c["u"], c["v"], c["w"], c["s"][0]
+    prof = lambda: np.zeros(W.kcells)
+    mw, mth = prof(), prof()
+    W.call("ref_stats_mean", mw, w); W.call("ref_stats_mean", mth, th)
+    m2, m3, cov = prof(), prof(), prof()
+    W.call("ref_stats_moment", m2, th, mth, 0., 2)
+    W.call("ref_stats_moment", m3, w, mw, 0.25, 3)
+    W.call("ref_stats_cov", cov, w, mw, 0., 1, th, mth, 0., 1)
+    out.update(stats_mean_w=mw, stats_mean_th=mth, stats_th2=m2, stats_w3=m3, stats_wth=cov)
+    rng = np.random.default_rng(203)
+    threfh = 300. + 0.003 * W.zh
+    bt = np.zeros(W.shape)
+    W.call("ref_thermo_buoyancy_tend", bt, th, threfh)
+    out["buoyancy_wt"] = bt
+    abuf = prof(); abuf[W.kstart:W.kend] = rng.uniform(-1, 1, W.ktot)
+    for name, fld, is_w in (("u", u, 0), ("w", w, 1)):
+        t = np.zeros(W.shape)
+        W.call("ref_buffer", t, fld, abuf, 2300., 0.00223, 2., is_w)
+        out["buffer_" + name + "t"] = t
+    g2 = [a.copy() for a in (u, v)]
+    for a in g2:
+        W.call("ref_cyclic", a, 2)
+    ug, vg = prof(), prof()
+    ug[W.kstart:W.kend] = rng.uniform(5, 10, W.ktot); vg[W.kstart:W.kend] = rng.uniform(-1, 1, W.ktot)
+    cut, cvt = np.zeros(W.shape), np.zeros(W.shape)
+    W.call("ref_force_coriolis", cut, cvt, g2[0], g2[1], ug, vg, 1.39e-4, 0.5, -0.25)
+    out.update(coriolis_ut=cut, coriolis_vt=cvt)
+    W.close()
+    return out
+
+
 def load(name):
     return dict(np.load(os.path.join(GOLDEN_DIR, name + ".npz")))

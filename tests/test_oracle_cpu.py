@@ -38,6 +38,17 @@ def test_oracle_reproduces_golden_steps():
     assert int(got["idt"]) == int(want["idt"])
 
 
+def test_oracle_reproduces_golden_round2_features():
+    """calc_evisc_neutral (Mason / van Driest), Stats profiles, dry buoyancy, sponge layer, Coriolis: the reference's outputs
+    on seeded cases against the committed vectors (tests/golden/kernels_r02.npz)."""
+    want = G.load("kernels_r02")
+    got = G.oracle_r02()
+    assert sorted(got) == sorted(want)
+    for k in want:
+        assert _close(got[k], want[k]), k
+        assert np.abs(want[k]).max() > 0., k          # no vector is trivially zero
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 def oracle_taylorgreen(itot, ktot, order):
     from oracle.les import OracleLES
